@@ -1,0 +1,68 @@
+/* hs_litdb.h -- C ABI of libhs_litdb.so: a host-side writer of pure-literal, block-mode databases
+ * in the Vectorscan 5.4.11 bytecode format.
+ *
+ * It is the stand-in, for literal sets only, for the reference's host compiler entry point
+ *     hs_compile_lit_multi()      /root/reference/src/hs_compile.h:640-648, src/hs.cpp:437-445
+ * which cannot be built in this image (needs Boost + Ragel).  Where the real compiler is available
+ * it is used unchanged and this library is not needed: the GPU runtime consumes any hs_database_t.
+ * The emitted blob is accepted and scanned by the unmodified reference runtime (hs_scan).
+ */
+#ifndef HS_LITDB_H
+#define HS_LITDB_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+struct hs_database;
+typedef struct hs_database hs_database_t; /* same opaque type as src/hs_common.h:56 */
+
+#define HSB_LIT_SUCCESS 0
+#define HSB_LIT_COMPILER_ERROR (-4) /* HS_COMPILER_ERROR, src/hs_common.h:503 */
+
+/* per-literal flags: same values as HS_FLAG_CASELESS / HS_FLAG_SINGLEMATCH (src/hs_compile.h:869,911) */
+#define HSB_FLAG_CASELESS 1u
+#define HSB_FLAG_SINGLEMATCH 8u
+
+#define HSB_MODE_BLOCK 1u /* HS_MODE_BLOCK, src/hs_compile.h:1156 */
+
+/* literal-matcher choice; AUTO follows the reference's rules: 1 fragment -> noodle, <= 48 fragments
+ * that pack into 8 buckets -> Teddy, else FDR (src/hwlm/hwlm_build.cpp:201-256). */
+#define HSB_LIT_ENGINE_AUTO 0
+#define HSB_LIT_ENGINE_FDR 1
+#define HSB_LIT_ENGINE_TEDDY 2
+#define HSB_LIT_ENGINE_NOODLE 3
+
+/* The knobs the reference exposes through its Grey box / test hints (src/grey.h, fdr_compile.cpp:861-865);
+ * zero-initialise for reference-default behaviour. */
+typedef struct hsb_lit_options {
+    int engine;      /* HSB_LIT_ENGINE_* */
+    int fdr_domain;  /* 9..15, 0 = chooseEngine's pick */
+    int fdr_stride;  /* 1, 2, 4, 0 = chooseEngine's pick */
+    int teddy_masks; /* 1..4, 0 = chooseTeddyEngine's pick */
+    int no_flood;    /* 1 = Grey::fdrAllowFlood off */
+} hsb_lit_options;
+
+/* Same parameter meaning as hs_compile_lit_multi; `platform` is replaced by `options` (the blob is
+ * always stamped for the generic x86 platform so every ISA build of the reference runtime accepts it),
+ * `error` receives a malloc'ed message (hsb_free_error). Only HSB_MODE_BLOCK is supported. */
+int hsb_compile_lit_multi(const char *const *expressions, const unsigned *flags, const unsigned *ids,
+                          const size_t *lens, unsigned elements, unsigned mode,
+                          const hsb_lit_options *options, hs_database_t **db, char **error);
+void hsb_free_database(hs_database_t *db);
+void hsb_free_error(char *error);
+
+/* hs_database_size / hs_serialize_database / hs_deserialize_database (src/database.c:62-110,243-300):
+ * byte-compatible with the reference's serialized form. */
+int hsb_database_size(const hs_database_t *db, size_t *size);
+int hsb_serialize_database(const hs_database_t *db, char **bytes, size_t *length);
+int hsb_deserialize_database(const char *bytes, size_t length, hs_database_t **db);
+
+unsigned hsb_crc32c(const void *p, size_t n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,234 @@
+// hsb_layout.h -- byte layout of the Vectorscan 5.4.11 block-mode bytecode, as read (GPU runtime)
+// and written (literal-set database writer) by this repository.
+//
+// This is an interop/wire-format description, not code taken from the reference: every constant is
+// the byte offset or size the reference's x86-64 ABI gives the named field, and
+// tests/test_layout.py pins each one against sizeof/offsetof printed by oracle/_ref/layout_probe
+// (built from the reference's own headers).  All values are little-endian.
+//
+//   hs_database header        /root/reference/src/database.h:103-114
+//   RoseEngine                /root/reference/src/rose/rose_internal.h:330-483
+//   HWLM                      /root/reference/src/hwlm/hwlm_internal.h:48-57
+//   FDR / Teddy headers       /root/reference/src/fdr/fdr_internal.h:69-86, teddy_internal.h:57-64
+//   FDRConfirm / LitInfo      /root/reference/src/fdr/fdr_confirm.h:57-92
+//   FDRFlood                  /root/reference/src/fdr/fdr_internal.h:50-62
+//   noodTable                 /root/reference/src/hwlm/noodle_internal.h:38-49
+//   Rose program opcodes      /root/reference/src/rose/rose_program.h:44-724
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <cstring>
+
+#if defined(__CUDACC__)
+#define HSB_HD __host__ __device__ __forceinline__
+#else
+#define HSB_HD inline
+#endif
+
+namespace hsb {
+
+using u8 = uint8_t;
+using u16 = uint16_t;
+using u32 = uint32_t;
+using u64 = uint64_t;
+using s32 = int32_t;
+
+// ---- unaligned little-endian field access (host and device) --------------------------------
+HSB_HD u8 rd8(const void *p, size_t off) { return reinterpret_cast<const u8 *>(p)[off]; }
+HSB_HD u16 rd16(const void *p, size_t off) {
+    const u8 *b = reinterpret_cast<const u8 *>(p) + off;
+    return (u16)(b[0] | (b[1] << 8));
+}
+HSB_HD u32 rd32(const void *p, size_t off) {
+    const u8 *b = reinterpret_cast<const u8 *>(p) + off;
+    return (u32)b[0] | ((u32)b[1] << 8) | ((u32)b[2] << 16) | ((u32)b[3] << 24);
+}
+HSB_HD u64 rd64(const void *p, size_t off) {
+    return (u64)rd32(p, off) | ((u64)rd32(p, off + 4) << 32);
+}
+inline void wr8(void *p, size_t off, u8 v) { reinterpret_cast<u8 *>(p)[off] = v; }
+inline void wr16(void *p, size_t off, u16 v) { std::memcpy(reinterpret_cast<u8 *>(p) + off, &v, 2); }
+inline void wr32(void *p, size_t off, u32 v) { std::memcpy(reinterpret_cast<u8 *>(p) + off, &v, 4); }
+inline void wr64(void *p, size_t off, u64 v) { std::memcpy(reinterpret_cast<u8 *>(p) + off, &v, 8); }
+
+constexpr size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+constexpr size_t CACHELINE = 64;
+
+// ---- hs_database_t header ---------------------------------------------------------------------
+namespace db {
+constexpr u32 MAGIC = 0xdbdbdbdbu;
+constexpr u32 VERSION_5_4_11 = (5u << 24) | (4u << 16) | (11u << 8);
+constexpr size_t magic = 0, version = 4, length = 8, platform = 16, crc32 = 24, reserved0 = 28,
+                 reserved1 = 32, bytecode = 36, padding = 40, bytes = 104, SIZE = 104;
+// platform bits: a database stamped with all three is accepted by every x86 build of the reference
+// runtime (src/database.c:115-124) and rules out the AVX2-only fat Teddy engines.
+constexpr u64 NOAVX2 = 4u << 13, NOAVX512 = 8u << 13, NOAVX512VBMI = 0x10u << 13;
+constexpr u64 PLATFORM_GENERIC = NOAVX2 | NOAVX512 | NOAVX512VBMI;
+// serialized form (src/database.c:62-110,130-176): SIZE + length bytes; packed header
+// {magic, version, length, platform(8), crc32, reserved0, reserved1} = 32 bytes, then the bytecode
+constexpr size_t SER_HEADER = 32;
+// in-memory images written by this repo: 64-byte aligned base, bytecode at +64 (inside `padding`)
+constexpr size_t IMAGE_BYTECODE = 64;
+}  // namespace db
+
+constexpr u32 MODE_BLOCK = 1, MODE_STREAM = 2, MODE_VECTORED = 4;
+
+// ---- RoseEngine -------------------------------------------------------------------------------
+namespace rose {
+constexpr size_t SIZE = 472;
+constexpr size_t pureLiteral = 0, noFloatingRoots = 1, requiresEodCheck = 2, hasOutfixesInSmallBlock = 3,
+                 runtimeImpl = 4, mpvTriggeredByLeaf = 5, canExhaust = 6, hasSom = 7, somHorizon = 8,
+                 mode = 12, historyRequired = 16, ekeyCount = 20, lkeyCount = 24, lopCount = 28,
+                 ckeyCount = 32, logicalTreeOffset = 36, combInfoMapOffset = 40, dkeyCount = 44,
+                 dkeyLogSize = 48, invDkeyOffset = 52, somLocationCount = 56,
+                 somLocationFatbitSize = 60, rolesWithStateCount = 64, stateSize = 68,
+                 anchorStateSize = 72, tStateSize = 76, scratchStateSize = 80, smallWriteOffset = 84,
+                 amatcherOffset = 88, ematcherOffset = 92, fmatcherOffset = 96, drmatcherOffset = 100,
+                 sbmatcherOffset = 104, longLitTableOffset = 108, amatcherMinWidth = 112,
+                 fmatcherMinWidth = 116, eodmatcherMinWidth = 120, amatcherMaxBiAnchoredWidth = 124,
+                 fmatcherMaxBiAnchoredWidth = 128, reportProgramOffset = 132, reportProgramCount = 136,
+                 delayProgramOffset = 140, anchoredProgramOffset = 144, activeArrayCount = 148,
+                 activeLeftCount = 152, queueCount = 156, activeQueueArraySize = 160,
+                 eagerIterOffset = 164, handledKeyCount = 168, handledKeyFatbitSize = 172,
+                 leftOffset = 176, roseCount = 180, eodProgramOffset = 184, flushCombProgramOffset = 188,
+                 lastFlushCombProgramOffset = 192, lastByteHistoryIterOffset = 196, minWidth = 200,
+                 minWidthExcludingBoundaries = 204, maxBiAnchoredWidth = 208, anchoredDistance = 212,
+                 anchoredMinDistance = 216, floatingDistance = 220, floatingMinDistance = 224,
+                 smallBlockDistance = 228, floatingMinLiteralMatchOffset = 232, nfaInfoOffset = 236,
+                 initialGroups = 240, floating_group_mask = 248, size = 256, delay_count = 260,
+                 delay_fatbit_size = 264, anchored_count = 268, anchored_fatbit_size = 272,
+                 maxFloatingDelayedMatch = 276, delayRebuildLength = 280, stateOffsets = 284,
+                 boundary = 376, totalNumLiterals = 388, asize = 392, outfixBeginQueue = 396,
+                 outfixEndQueue = 400, leftfixBeginQueue = 404, initMpvNfa = 408, rosePrefixCount = 412,
+                 activeLeftIterOffset = 416, ematcherRegionSize = 420, somRevCount = 424,
+                 somRevOffsetOffset = 428, longLitStreamState = 432, state_init = 436;
+// RoseStateOffsets, relative to rose::stateOffsets
+namespace so {
+constexpr size_t history = 0, exhausted = 4, exhausted_size = 8, logicalVec = 12, logicalVec_size = 16,
+                 combVec = 20, combVec_size = 24, activeLeafArray = 28, activeLeafArray_size = 32,
+                 activeLeftArray = 36, activeLeftArray_size = 40, leftfixLagTable = 44, anchorState = 48,
+                 groups = 52, groups_size = 56, longLitState = 60, longLitState_size = 64,
+                 somLocation = 68, somValid = 72, somWritable = 76, somMultibit_size = 80,
+                 nfaStateBegin = 84, end = 88, SIZE = 92;
+}
+// RoseBoundaryReports, relative to rose::boundary
+namespace bd {
+constexpr size_t reportEodOffset = 0, reportZeroOffset = 4, reportZeroEodOffset = 8;
+}
+constexpr u8 RUNTIME_FULL_ROSE = 0, RUNTIME_PURE_LITERAL = 1, RUNTIME_SINGLE_OUTFIX = 2;
+constexpr u32 BOUND_INF = 0xffffffffu;
+}  // namespace rose
+
+// ---- HWLM -------------------------------------------------------------------------------------
+namespace hwlm {
+constexpr size_t type = 0, accel1_groups = 8, accel1 = 16, accel0 = 96, SIZE = 176;
+constexpr size_t ACCEL_AUX_SIZE = 80;
+constexpr size_t BODY = 192;  // ROUNDUP_CL(sizeof(HWLM)): engine body follows here
+constexpr u8 ENGINE_NOOD = 16, ENGINE_FDR = 12;
+}  // namespace hwlm
+
+// ---- AccelAux (src/nfa/accel.h:72-142) -----------------------------------------------------------
+namespace accel {
+constexpr u8 NONE = 0, VERM = 1, VERM_NOCASE = 2, DVERM = 3, DVERM_NOCASE = 4, SHUFTI = 13,
+             DSHUFTI = 14, TRUFFLE = 15, RED_TAPE = 16, DVERM_MASKED = 17;
+// every variant starts {u8 accel_type; u8 offset;}
+constexpr size_t type = 0, offset = 1;
+constexpr size_t verm_c = 2;               // .verm {type, offset, c}
+constexpr size_t dverm_c1 = 2, dverm_c2 = 3, dverm_m1 = 4, dverm_m2 = 5;
+constexpr size_t shufti_lo = 16, shufti_hi = 32;       // m128 each (16-byte aligned)
+constexpr size_t truffle_mask1 = 16, truffle_mask2 = 32;
+}  // namespace accel
+
+// ---- FDR / Teddy header -----------------------------------------------------------------------
+namespace fdr {
+constexpr size_t engineID = 0, size = 4, maxStringLen = 8, numStrings = 12, confOffset = 16,
+                 floodOffset = 20, stride = 24, domain = 25, domainMask = 26, tabSize = 28, start = 32,
+                 SIZE = 48;
+constexpr size_t TABLE = 64;  // ROUNDUP_CL(sizeof(FDR)): u64 ft[1 << domain] follows here
+constexpr u32 NUM_BUCKETS = 8;
+}  // namespace fdr
+namespace teddy {
+constexpr size_t SIZE = 24;   // engineID..floodOffset shared with fdr::
+constexpr size_t MASKS = 64;  // ROUNDUP_CL(sizeof(Teddy)): nibble masks follow here
+constexpr u32 ENGINE_FIRST = 11, ENGINE_LAST = 18;  // 8-bucket Teddy, 1..4 masks, plain/packed
+constexpr u32 FAT_FIRST = 3, FAT_LAST = 10;         // 16-bucket (AVX2-only) Teddy
+constexpr size_t REINFORCE_ROWS = 257;              // (N_CHARS + 1) u64 per mask
+}  // namespace teddy
+
+namespace conf {  // struct FDRConfirm, then u32 litIndex[1 << nBits], then LitInfo[]
+constexpr size_t andmsk = 0, mult = 8, nBits = 16, groups = 24, SIZE = 32;
+constexpr u64 MULT = 0x0b4e0ef37bc32127ull;
+}
+namespace lit {  // struct LitInfo
+constexpr size_t v = 0, msk = 8, groups = 16, id = 24, size = 28, flags = 29, next = 30, SIZE = 32;
+constexpr u8 FLAG_NOREPEAT = 1;
+}
+namespace flood {  // u32 index[256], then FDRFlood[]
+constexpr size_t allGroups = 0, suffix = 8, idCount = 12, ids = 16, groups = 80, SIZE = 208;
+constexpr u32 MAX_IDS = 16;
+}
+namespace nood {  // struct noodTable
+constexpr size_t id = 0, msk = 8, cmp = 16, msk_len = 24, key_offset = 25, nocase = 26, single = 27,
+                 key0 = 28, key1 = 29, SIZE = 32;
+}
+
+// ---- Rose program instructions ------------------------------------------------------------------
+// Every instruction is a C struct starting with `u8 code`, padded to ROSE_INSTR_MIN_ALIGN (8).
+namespace op {
+enum : u8 {
+    END = 0, ANCHORED_DELAY = 1, CHECK_LIT_EARLY = 2, CHECK_GROUPS = 3, CHECK_ONLY_EOD = 4,
+    CHECK_BOUNDS = 5, CHECK_NOT_HANDLED = 6, CHECK_SINGLE_LOOKAROUND = 7, CHECK_LOOKAROUND = 8,
+    CHECK_MASK = 9, CHECK_MASK_32 = 10, CHECK_BYTE = 11, CHECK_SHUFTI_16x8 = 12,
+    CHECK_SHUFTI_32x8 = 13, CHECK_SHUFTI_16x16 = 14, CHECK_SHUFTI_32x16 = 15, CHECK_INFIX = 16,
+    CHECK_PREFIX = 17, PUSH_DELAYED = 18, DUMMY_NOP = 19, CATCH_UP = 20, CATCH_UP_MPV = 21,
+    SOM_ADJUST = 22, SOM_LEFTFIX = 23, SOM_FROM_REPORT = 24, SOM_ZERO = 25, TRIGGER_INFIX = 26,
+    TRIGGER_SUFFIX = 27, DEDUPE = 28, DEDUPE_SOM = 29, REPORT_CHAIN = 30, REPORT_SOM_INT = 31,
+    REPORT_SOM_AWARE = 32, REPORT = 33, REPORT_EXHAUST = 34, REPORT_SOM = 35, REPORT_SOM_EXHAUST = 36,
+    DEDUPE_AND_REPORT = 37, FINAL_REPORT = 38, CHECK_EXHAUSTED = 39, CHECK_MIN_LENGTH = 40,
+    SET_STATE = 41, SET_GROUPS = 42, SQUASH_GROUPS = 43, CHECK_STATE = 44, SPARSE_ITER_BEGIN = 45,
+    SPARSE_ITER_NEXT = 46, SPARSE_ITER_ANY = 47, ENGINES_EOD = 48, SUFFIXES_EOD = 49,
+    MATCHER_EOD = 50, CHECK_LONG_LIT = 51, CHECK_LONG_LIT_NOCASE = 52, CHECK_MED_LIT = 53,
+    CHECK_MED_LIT_NOCASE = 54, CLEAR_WORK_DONE = 55, MULTIPATH_LOOKAROUND = 56,
+    CHECK_MULTIPATH_SHUFTI_16x8 = 57, CHECK_MULTIPATH_SHUFTI_32x8 = 58,
+    CHECK_MULTIPATH_SHUFTI_32x16 = 59, CHECK_MULTIPATH_SHUFTI_64 = 60, INCLUDED_JUMP = 61,
+    SET_LOGICAL = 62, SET_COMBINATION = 63, FLUSH_COMBINATION = 64, SET_EXHAUST = 65,
+    LAST_FLUSH_COMBINATION = 66, CHECK_SHUFTI_64x8 = 67, CHECK_SHUFTI_64x16 = 68, CHECK_MASK_64 = 69,
+    LAST = 69
+};
+constexpr size_t ALIGN = 8;
+// operand offsets + padded sizes for the opcodes this runtime executes
+namespace check_groups { constexpr size_t groups = 8, SIZE = 16; }
+namespace check_mask { constexpr size_t and_mask = 8, cmp_mask = 16, neg_mask = 24, offset = 32, fail_jump = 36, SIZE = 40; }
+namespace check_mask32 { constexpr size_t and_mask = 1, cmp_mask = 33, neg_mask = 68, offset = 72, fail_jump = 76, SIZE = 80; }
+namespace check_byte { constexpr size_t and_mask = 1, cmp_mask = 2, negation = 3, offset = 4, fail_jump = 8, SIZE = 16; }
+namespace check_shufti_16x8 { constexpr size_t nib_mask = 1, bucket_select_mask = 33, neg_mask = 52, offset = 56, fail_jump = 60, SIZE = 64; }
+namespace check_shufti_32x8 { constexpr size_t hi_mask = 1, lo_mask = 17, bucket_select_mask = 33, neg_mask = 68, offset = 72, fail_jump = 76, SIZE = 80; }
+namespace check_shufti_16x16 { constexpr size_t hi_mask = 1, lo_mask = 33, bucket_select_mask = 65, neg_mask = 100, offset = 104, fail_jump = 108, SIZE = 112; }
+namespace check_shufti_32x16 { constexpr size_t hi_mask = 1, lo_mask = 33, bucket_select_mask_hi = 65, bucket_select_mask_lo = 97, neg_mask = 132, offset = 136, fail_jump = 140, SIZE = 144; }
+namespace dedupe { constexpr size_t quash_som = 1, dkey = 4, offset_adjust = 8, fail_jump = 12, SIZE = 16; }
+namespace report { constexpr size_t onmatch = 4, offset_adjust = 8, SIZE = 16; }           // REPORT, FINAL_REPORT
+namespace report_exhaust { constexpr size_t onmatch = 4, offset_adjust = 8, ekey = 12, SIZE = 16; }
+namespace dedupe_and_report { constexpr size_t quash_som = 1, dkey = 4, onmatch = 8, offset_adjust = 12, fail_jump = 16, SIZE = 24; }
+namespace check_exhausted { constexpr size_t ekey = 4, fail_jump = 8, SIZE = 16; }
+namespace squash_groups { constexpr size_t groups = 8, SIZE = 16; }
+namespace check_lit { constexpr size_t lit_offset = 4, lit_length = 8, fail_jump = 12, SIZE = 16; }  // CHECK_{MED,LONG}_LIT[_NOCASE]
+namespace included_jump { constexpr size_t squash = 1, child_offset = 4, SIZE = 8; }
+namespace set_exhaust { constexpr size_t ekey = 4, SIZE = 8; }
+constexpr size_t SIZE_1 = 8;  // END, CATCH_UP, CLEAR_WORK_DONE, ... (code byte only)
+}  // namespace op
+
+constexpr u32 INVALID_EKEY = 0xffffffffu;
+constexpr u32 INVALID_DKEY = 0xffffffffu;  // MO_INVALID_IDX
+
+// src/util/multibit_build.cpp:49-73 -- bytes of a multibit holding total_bits keys
+inline u32 mmbit_size(u32 total_bits) {
+    if (total_bits <= 256) return (u32)(round_up(total_bits, 8) / 8);
+    u64 level = 1, total = 0;
+    while (level * 64 < total_bits) { total += level; level <<= 6; }
+    total += ((u64)total_bits + 63) / 64;
+    return (u32)(total * 8);
+}
+// src/util/fatbit_build.cpp:40-42 -- struct fatbit is at least 32 bytes
+inline u32 fatbit_size(u32 total_bits) { u32 m = mmbit_size(total_bits); return m < 32 ? 32 : m; }
+
+}  // namespace hsb

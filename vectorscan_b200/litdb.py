@@ -1,0 +1,114 @@
+"""ctypes binding of libhs_litdb.so -- the literal-set database writer (include/hs_litdb.h).
+
+Mirrors the reference's hs_compile_lit_multi (/root/reference/src/hs_compile.h:640-648): literals,
+per-literal flags, ids -> an hs_database_t in the Vectorscan 5.4.11 bytecode format.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+HS_FLAG_CASELESS = 1
+HS_FLAG_SINGLEMATCH = 8
+HS_MODE_BLOCK = 1
+
+ENGINE_AUTO, ENGINE_FDR, ENGINE_TEDDY, ENGINE_NOODLE = 0, 1, 2, 3
+
+
+class LitOptions(C.Structure):
+    _fields_ = [("engine", C.c_int), ("fdr_domain", C.c_int), ("fdr_stride", C.c_int),
+                ("teddy_masks", C.c_int), ("no_flood", C.c_int)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        path = os.path.join(_HERE, "libhs_litdb.so")
+        if not os.path.exists(path):
+            raise RuntimeError(f"{path} missing: run `python -c 'import __graft_entry__ as g; g.build()'`")
+        L = C.CDLL(path)
+        L.hsb_compile_lit_multi.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_uint), C.POINTER(C.c_uint),
+                                            C.POINTER(C.c_size_t), C.c_uint, C.c_uint, C.POINTER(LitOptions),
+                                            C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+        L.hsb_compile_lit_multi.restype = C.c_int
+        L.hsb_free_database.argtypes = [C.c_void_p]
+        L.hsb_free_error.argtypes = [C.c_void_p]
+        L.hsb_database_size.argtypes = [C.c_void_p, C.POINTER(C.c_size_t)]
+        L.hsb_serialize_database.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
+        L.hsb_deserialize_database.argtypes = [C.c_char_p, C.c_size_t, C.POINTER(C.c_void_p)]
+        L.hsb_crc32c.argtypes = [C.c_char_p, C.c_size_t]
+        L.hsb_crc32c.restype = C.c_uint
+        _lib = L
+    return _lib
+
+
+class CompileError(Exception):
+    pass
+
+
+class Database:
+    """Owns an hs_database_t produced by the writer (or deserialized)."""
+
+    def __init__(self, ptr):
+        self.ptr = C.c_void_p(ptr)
+
+    def __del__(self):
+        try:
+            if self.ptr:
+                lib().hsb_free_database(self.ptr)
+                self.ptr = None
+        except Exception:
+            pass
+
+    @property
+    def size(self):
+        n = C.c_size_t()
+        lib().hsb_database_size(self.ptr, C.byref(n))
+        return n.value
+
+    def raw(self):
+        """The in-memory image (header + padding + bytecode)."""
+        return C.string_at(self.ptr, self.size)
+
+    def bytecode(self):
+        raw = self.raw()
+        off = int.from_bytes(raw[36:40], "little")
+        return raw[off:]
+
+    def serialize(self):
+        out, n = C.c_void_p(), C.c_size_t()
+        if lib().hsb_serialize_database(self.ptr, C.byref(out), C.byref(n)) != 0:
+            raise RuntimeError("serialize failed")
+        data = C.string_at(out, n.value)
+        C.CDLL(None).free(out)
+        return data
+
+    @staticmethod
+    def deserialize(data):
+        db = C.c_void_p()
+        if lib().hsb_deserialize_database(data, len(data), C.byref(db)) != 0:
+            raise RuntimeError("deserialize failed")
+        return Database(db.value)
+
+
+def compile_lit_multi(literals, flags=None, ids=None, mode=HS_MODE_BLOCK, engine=ENGINE_AUTO, fdr_domain=0,
+                      fdr_stride=0, teddy_masks=0, no_flood=0):
+    """literals: list of bytes. Returns Database. Same argument meaning as hs_compile_lit_multi."""
+    n = len(literals)
+    lits = [bytes(x) for x in literals]
+    arr = (C.c_char_p * n)(*lits)
+    lens = (C.c_size_t * n)(*[len(x) for x in lits])
+    fl = (C.c_uint * n)(*(flags if flags is not None else [0] * n))
+    idv = (C.c_uint * n)(*(ids if ids is not None else list(range(n))))
+    opt = LitOptions(engine, fdr_domain, fdr_stride, teddy_masks, no_flood)
+    db, err = C.c_void_p(), C.c_void_p()
+    rv = lib().hsb_compile_lit_multi(arr, fl, idv, lens, n, mode, C.byref(opt), C.byref(db), C.byref(err))
+    if rv != 0:
+        msg = C.string_at(err).decode() if err else "error"
+        if err:
+            lib().hsb_free_error(err)
+        raise CompileError(msg)
+    return Database(db.value)
