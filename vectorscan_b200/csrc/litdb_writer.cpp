@@ -683,8 +683,13 @@ int build(const std::vector<FullLit> &fulls_in, const hsb_lit_options &opt, std:
     for (auto &fr : frags)
         for (u32 i : fr.fulls)
             if (fulls[i].s.size() > 8) {
+                // caseless literals are stored upper-cased: cmpForward folds only the scanned text
+                // (src/util/compare.h:143-175)
                 lit_text_off[i] = (u32)rose.grow(fulls[i].s.size());
-                std::memcpy(rose.at(lit_text_off[i]), fulls[i].s.data(), fulls[i].s.size());
+                for (size_t k = 0; k < fulls[i].s.size(); k++) {
+                    u8 c = (u8)fulls[i].s[k];
+                    *rose.at(lit_text_off[i] + k) = fulls[i].nocase ? to_upper(c) : c;
+                }
             }
     rose.align(8);
 
@@ -772,7 +777,15 @@ int build(const std::vector<FullLit> &fulls_in, const hsb_lit_options &opt, std:
         if (masks < 1 || masks > 4) { err = "teddy_masks must be 1..4"; return HSB_LIT_COMPILER_ERROR; }
         if (hl.size() > 48) { err = "too many literal fragments for Teddy (max 48)"; return HSB_LIT_COMPILER_ERROR; }
         engine = build_teddy(hl, masks, packed, allow_flood, err);
-        if (engine.empty()) return HSB_LIT_COMPILER_ERROR;
+        if (engine.empty()) {
+            // as fdrBuildProtoInternal does: "build with teddy failed, will try with FDR"
+            if (opt.engine != HSB_LIT_ENGINE_AUTO) return HSB_LIT_COMPILER_ERROR;
+            err.clear();
+            engine_choice = HSB_LIT_ENGINE_FDR;
+        }
+    }
+    if (engine_choice == HSB_LIT_ENGINE_NOODLE || engine_choice == HSB_LIT_ENGINE_TEDDY) {
+        // built above
     } else if (engine_choice == HSB_LIT_ENGINE_FDR) {
         FdrShape shape = choose_fdr_shape(hl);
         if (opt.fdr_domain) shape.domain = (u32)opt.fdr_domain;
