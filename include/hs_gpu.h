@@ -1,0 +1,139 @@
+/* hs_gpu.h -- C ABI of libhs_gpu.so: the B200 (sm_100a) block-mode scanning runtime for Vectorscan
+ * databases.  Plain pointers and sizes only; no torch / CUDA types in any signature.
+ *
+ * Each entry point replaces, for block-mode databases, the reference runtime interface cited beside
+ * it (paths under /root/reference).  Databases are the reference's own hs_database_t bytecode blobs
+ * (from the unchanged host compiler, from hs_deserialize_database, or from hs_litdb.h).  Error codes are
+ * the reference's (src/hs_common.h:474-584).  There is no CPU fallback: without a CUDA device every
+ * scanning call returns HS_ARCH_ERROR.
+ */
+#ifndef HS_GPU_H
+#define HS_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+struct hs_database;
+typedef struct hs_database hs_database_t; /* src/hs_common.h:56 */
+struct hs_gpu_scratch;
+typedef struct hs_gpu_scratch hs_gpu_scratch_t; /* stands where hs_scratch_t stands, src/hs_common.h:466 */
+struct hs_gpu_corpus;
+typedef struct hs_gpu_corpus hs_gpu_corpus_t;
+
+typedef int hs_error_t;
+#define HS_SUCCESS 0
+#define HS_INVALID (-1)
+#define HS_NOMEM (-2)
+#define HS_SCAN_TERMINATED (-3)
+#define HS_COMPILER_ERROR (-4)
+#define HS_DB_VERSION_ERROR (-5)
+#define HS_DB_PLATFORM_ERROR (-6)
+#define HS_DB_MODE_ERROR (-7)
+#define HS_BAD_ALIGN (-8)
+#define HS_BAD_ALLOC (-9)
+#define HS_SCRATCH_IN_USE (-10)
+#define HS_ARCH_ERROR (-11)
+#define HS_INSUFFICIENT_SPACE (-12)
+#define HS_UNKNOWN_ERROR (-13)
+
+/* src/hs_runtime.h:125-129.  from is always 0 (no SOM), flags always 0; non-zero return stops delivery
+ * and makes the scan call return HS_SCAN_TERMINATED. */
+typedef int (*match_event_handler)(unsigned int id, unsigned long long from, unsigned long long to,
+                                   unsigned int flags, void *context);
+
+/* One reported match of a batch scan: sorted by (buffer, to, id). */
+typedef struct hs_gpu_match {
+    uint32_t buffer; /* index into the data[] array of the call */
+    uint32_t id;     /* pattern id */
+    uint64_t to;     /* offset one past the last byte of the match, relative to its buffer */
+} hs_gpu_match_t;
+
+/* Per-call counters and device timings (CUDA events on the scratch's stream). */
+typedef struct hs_gpu_stats {
+    uint64_t bytes;        /* sum of buffer lengths scanned */
+    uint64_t buffers;
+    uint64_t matches;      /* delivered (after dedupe / single-match resolution) */
+    uint64_t raw_matches;  /* written to the device match arena */
+    uint64_t candidates;   /* positions that survived the front-end filter */
+    uint64_t confirms;     /* literal-confirm table probes */
+    float h2d_ms;          /* host->device copy of the inputs (0 for a resident corpus) */
+    float scan_ms;         /* front end + confirm + program + arena write */
+    float sort_ms;         /* device sort / compaction of the arena */
+    float d2h_ms;          /* device->host copy of the matches */
+    uint32_t scan_launches; /* kernels of this library launched by the call */
+    uint32_t arena_retries; /* re-runs forced by match arena growth */
+} hs_gpu_stats_t;
+
+/* hs_alloc_scratch(db, &scratch)                       src/hs_runtime.h:555-556, src/scratch.c:244-389
+ * *scratch == NULL allocates; otherwise the scratch is grown to also serve this database.  The database
+ * is parsed, checked (block mode, supported engines and Rose opcodes only -> else HS_ARCH_ERROR /
+ * HS_DB_MODE_ERROR) and uploaded to the device once. */
+hs_error_t hs_gpu_alloc_scratch(const hs_database_t *db, hs_gpu_scratch_t **scratch);
+/* hs_clone_scratch / hs_scratch_size / hs_free_scratch  src/hs_runtime.h:576,593,609 */
+hs_error_t hs_gpu_clone_scratch(const hs_gpu_scratch_t *src, hs_gpu_scratch_t **dest);
+hs_error_t hs_gpu_scratch_size(const hs_gpu_scratch_t *scratch, size_t *host_bytes, size_t *device_bytes);
+hs_error_t hs_gpu_free_scratch(hs_gpu_scratch_t *scratch);
+
+/* hs_scan(db, data, length, flags, scratch, onEvent, context)      src/hs_runtime.h:479-482, src/runtime.c:316-475
+ * One buffer.  Matches are delivered in (to, id) order after the device pass completes. */
+hs_error_t hs_gpu_scan(const hs_database_t *db, const char *data, unsigned int length, unsigned int flags,
+                       hs_gpu_scratch_t *scratch, match_event_handler onEvent, void *context);
+
+/* Batch of `count` INDEPENDENT block-mode scans -- the loop of hs_scan calls that examples/pcapscan.cc:305-316
+ * and tools/hsbench/main.cpp:486-512 run -- with the parameter list of hs_scan_vector (src/hs_runtime.h:522-527).
+ * Offsets are per buffer.  Matches are delivered buffer by buffer in index order.  (The reference's
+ * hs_scan_vector itself has stream semantics on HS_MODE_VECTORED databases; see DESIGN.md.) */
+hs_error_t hs_gpu_scan_vector(const hs_database_t *db, const char *const *data, const unsigned int *length,
+                              unsigned int count, unsigned int flags, hs_gpu_scratch_t *scratch,
+                              match_event_handler onEvent, void *context);
+/* Same, with one callback context per buffer (contexts[i] may differ; NULL = no context). */
+hs_error_t hs_gpu_scan_batch(const hs_database_t *db, const char *const *data, const unsigned int *length,
+                             unsigned int count, unsigned int flags, hs_gpu_scratch_t *scratch,
+                             match_event_handler onEvent, void *const *contexts);
+/* Same, without callbacks: *matches points at the scratch-owned, sorted match array (valid until the next
+ * call on this scratch), *n_matches is its length. */
+hs_error_t hs_gpu_scan_vector_ex(const hs_database_t *db, const char *const *data, const unsigned int *length,
+                                 unsigned int count, unsigned int flags, hs_gpu_scratch_t *scratch,
+                                 const hs_gpu_match_t **matches, uint64_t *n_matches);
+
+/* Device-resident corpora: upload once, scan many times (what hsbench does with its in-memory corpus,
+ * tools/hsbench/main.cpp:486-512).  The corpus is `count` buffers; `flat` holds them back to back and
+ * offsets[i]..offsets[i+1] delimits buffer i (offsets has count+1 entries, offsets[0] == 0). */
+hs_error_t hs_gpu_corpus_create(const char *flat, const uint64_t *offsets, unsigned int count,
+                                hs_gpu_corpus_t **corpus);
+hs_error_t hs_gpu_corpus_free(hs_gpu_corpus_t *corpus);
+/* Scan a resident corpus; matches stay on the device until fetched.  Only device work is done. */
+hs_error_t hs_gpu_scan_corpus(const hs_database_t *db, const hs_gpu_corpus_t *corpus, hs_gpu_scratch_t *scratch,
+                              uint64_t *n_matches);
+hs_error_t hs_gpu_fetch_matches(hs_gpu_scratch_t *scratch, const hs_gpu_match_t **matches, uint64_t *n_matches);
+
+hs_error_t hs_gpu_last_stats(const hs_gpu_scratch_t *scratch, hs_gpu_stats_t *stats);
+
+/* Host memory the library can DMA from without a staging copy (cudaHostAlloc). */
+void *hs_gpu_host_alloc(size_t bytes);
+void hs_gpu_host_free(void *p);
+
+/* Runtime knobs.  front end: 0 = auto, 1 = "native" (the database's own FDR/Teddy tables and FDRConfirm
+ * structures), 2 = "turbo" (tables re-encoded at upload for shared memory; identical results). */
+hs_error_t hs_gpu_set_option(hs_gpu_scratch_t *scratch, const char *name, long value);
+int hs_gpu_device_count(void);
+hs_error_t hs_gpu_set_device(int device);
+const char *hs_gpu_version(void);
+
+/* Byte-class primitives over a device-staged buffer, with the reference's return convention
+ * (offset of the first byte in class, `len` if none; reverse variants: offset of the last, -1 if none):
+ * shuftiExec/rshuftiExec  src/nfa/shufti.h ; truffleExec/rtruffleExec  src/nfa/truffle.h ;
+ * vermicelliExec/rvermicelliExec/vermicelliDoubleExec  src/nfa/vermicelli.hpp */
+long long hs_gpu_shufti(const uint8_t lo[16], const uint8_t hi[16], const uint8_t *buf, size_t len, int reverse);
+long long hs_gpu_truffle(const uint8_t mask1[16], const uint8_t mask2[16], const uint8_t *buf, size_t len, int reverse);
+long long hs_gpu_vermicelli(uint8_t c, int nocase, const uint8_t *buf, size_t len, int reverse, int negate);
+long long hs_gpu_vermicelli_double(uint8_t c1, uint8_t c2, int nocase, const uint8_t *buf, size_t len);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

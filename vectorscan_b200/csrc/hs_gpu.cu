@@ -1,0 +1,1401 @@
+// hs_gpu.cu -- libhs_gpu.so: B200 (sm_100a) block-mode scanning runtime for Vectorscan databases.
+//
+// Path restated (see DESIGN.md for the full map; citations are into /root/reference):
+//   hs_scan gates / engine switch        src/runtime.c:316-475         -> host side of hs_gpu_scan*
+//   hwlmExec -> fdrExec                  src/hwlm/hwlm.c:178-205, src/fdr/fdr.c:801-825
+//   FDR shift-or filter                  src/fdr/fdr.c:144-296,663-764 -> k_scan<FdrNative>  (position-local form)
+//   Teddy nibble filter                  src/fdr/teddy.c:920-1066      -> k_scan<TeddyNative>
+//   noodle single literal                src/hwlm/noodle_engine.cpp:75-133 -> k_scan<Noodle>
+//   bucket confirm                       src/fdr/fdr.c:298-333, src/fdr/fdr_confirm_runtime.h:43-102 -> confirm_entry()
+//   roseCallback + roseRunProgram_l      src/rose/match.c:479-534, src/rose/program_runtime.c:3083-3504 -> run_program()
+//   dedupe / report / exhaustion         src/report.h:54-153,300-340   -> match arena + finalize pass
+//   scratch                              src/scratch.c:244-389         -> hs_gpu_scratch (device arenas, stream)
+//
+// Data-parallel formulation.  The reference walks one buffer sequentially carrying a 128-bit shift-or
+// state.  Here the whole batch is one flat byte array in HBM (buffers back to back, offsets[] on the
+// side) and every end position is decided independently: the FDR candidate bit for (end e, bucket b)
+// depends only on bytes [e-7, e+1], so a warp takes a contiguous strip, each lane a 16-byte chunk per
+// 512-byte row (one coalesced LDG.128 per lane), and the 7-byte state overhang travels between
+// neighbouring lanes by shuffle instead of between loop iterations.  Buffer boundaries are ignored by
+// the filter (it stays sound: it can only over-approximate) and enforced exactly by the confirm step.
+// Candidates are compacted per warp into a shared-memory queue, confirmed one lane per candidate
+// against the database's own FDRConfirm/LitInfo structures, the literal's Rose program is interpreted,
+// and reports are appended to a device match arena (staged per warp in shared memory, one global
+// atomic per flush).  A finalize pass sorts the arena by (buffer, to, id) and applies dedupe keys.
+#include "hsb_layout.h"
+#include "hsb_dbview.h"
+#include "hs_gpu.h"
+
+#include <cuda_runtime.h>
+#include <cub/cub.cuh>
+
+#include <algorithm>
+#include <atomic>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+using namespace hsb;
+
+#define HSG_VERSION "hs-gpu 0.1 (sm_100a) for Vectorscan 5.4.11 bytecode"
+
+namespace {
+
+// ------------------------------------------------------------------------------------------------
+// geometry
+// ------------------------------------------------------------------------------------------------
+constexpr int WARPS = 8;
+constexpr int THREADS = WARPS * 32;
+constexpr int CHUNK = 16;                      // bytes per lane per row
+constexpr int ROW_BYTES = 32 * CHUNK;          // 512: one coalesced warp load
+constexpr int STRIP_ROWS = 32;
+constexpr int STRIP_BYTES = STRIP_ROWS * ROW_BYTES;  // 16 KiB per warp strip
+constexpr int QCAP = 1024;                     // candidate queue entries per warp
+constexpr int STAGE_CAP = 96;                  // staged match records per warp
+constexpr size_t FRONT_PAD = 1024, BACK_PAD = 2048;  // zero bytes around the flat text in HBM
+
+struct __align__(16) Rec {  // device match record
+    u32 buf, to, id, aux;
+};
+constexpr u32 AUX_DEDUPE = 0x80000000u, AUX_EKEY = 0x40000000u, AUX_QUIET = 0x20000000u, AUX_KEYMASK = 0x1fffffffu;
+
+struct ConfHdr {  // FDRConfirm header cached in shared memory
+    u64 andmsk, mult, groups;
+    u32 nbits, base;  // base: absolute bytecode offset of the FDRConfirm (0 = empty bucket)
+};
+
+struct DevDb {
+    const u8 *bc;         // device copy of the bytecode (256-byte aligned)
+    const u64 *fdr_tab;   // FDR reach table, folded to <= 2^14 rows (device global)
+    const u32 *teddy_tab; // per byte value: byte j = lo_j[c&15] | hi_j[c>>4]
+    u64 groups;
+    u64 nood_msk, nood_cmp;
+    u32 fdr_mask;         // rows - 1
+    u32 fdr_stride;
+    u32 conf_base;
+    u32 n_buckets;
+    u32 teddy_masks;
+    u32 nood_len, nood_id;
+    u32 min_width, min_width_excl, max_bi_width;
+    u32 bc_len;
+};
+
+struct DevCorpus {
+    const u8 *text;          // FRONT_PAD zero bytes precede, BACK_PAD follow
+    const u64 *off;          // count + 1 offsets
+    const u32 *strip_first;  // nstrips + 1: buffer containing the first byte of each strip
+    u64 total;
+    u32 count;
+    u32 nstrips;
+};
+
+struct DevArena {
+    Rec *recs;
+    unsigned long long *count;  // records wanted (may exceed cap)
+    unsigned long long *stats;  // [0] candidates, [1] confirm probes
+    u32 *error;                 // sticky device-side error flag
+    u64 cap;
+};
+
+struct WarpShared {
+    u32 q[QCAP];
+    Rec stage[STAGE_CAP];
+    u32 stage_n;
+    u32 pad[3];
+};
+
+// ------------------------------------------------------------------------------------------------
+// small device helpers
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ u32 lane_id() { return threadIdx.x & 31; }
+__device__ __forceinline__ u32 ld32(const u8 *bc, u32 off) { return *reinterpret_cast<const u32 *>(bc + off); }
+__device__ __forceinline__ u64 ld64(const u8 *bc, u32 off) { return *reinterpret_cast<const u64 *>(bc + off); }
+
+// 8 text bytes ending at global position g (last byte in the top byte), from 8-byte aligned loads
+__device__ __forceinline__ u64 load_tail8(const u8 *text, u64 g) {
+    const long long a = (long long)g - 7;           // may be negative: FRONT_PAD covers it
+    const u8 *p = text + a;
+    const uintptr_t ap = reinterpret_cast<uintptr_t>(p);
+    const u64 *q = reinterpret_cast<const u64 *>(ap & ~(uintptr_t)7);
+    const unsigned sh = (unsigned)(ap & 7) * 8;
+    u64 lo = q[0];
+    if (!sh) return lo;
+    u64 hi = q[1];
+    return (lo >> sh) | (hi << (64 - sh));
+}
+
+struct Ctx {
+    const DevDb &db;
+    const DevCorpus &cp;
+    const DevArena &ar;
+    WarpShared *ws;
+    const ConfHdr *conf;
+};
+
+__device__ __forceinline__ void emit(const Ctx &c, u32 buf, u32 to, u32 id, u32 aux) {
+    Rec r{buf, to, id, aux};
+    u32 slot = atomicAdd(&c.ws->stage_n, 1u);
+    if (slot < STAGE_CAP) {
+        c.ws->stage[slot] = r;
+    } else {  // staging full: slow path straight to the arena
+        unsigned long long idx = atomicAdd(c.ar.count, 1ull);
+        if (idx < c.ar.cap) c.ar.recs[idx] = r;
+    }
+}
+
+// warp-synchronous: move staged records to the arena with one global atomic
+__device__ __forceinline__ void flush_stage(const Ctx &c) {
+    __syncwarp();
+    u32 n = *(volatile u32 *)&c.ws->stage_n;
+    if (n > STAGE_CAP) n = STAGE_CAP;
+    if (n) {
+        unsigned long long base = 0;
+        if (lane_id() == 0) base = atomicAdd(c.ar.count, (unsigned long long)n);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        for (u32 i = lane_id(); i < n; i += 32)
+            if (base + i < c.ar.cap) c.ar.recs[base + i] = c.ws->stage[i];
+    }
+    __syncwarp();
+    if (lane_id() == 0) c.ws->stage_n = 0;
+    __syncwarp();
+}
+
+// ------------------------------------------------------------------------------------------------
+// Rose program interpreter (pure-literal subset of roseRunProgram_l).  `to` = end offset of the literal
+// (one past its last byte) relative to the buffer [btext, btext + blen).
+// Exhaustion cannot be evaluated in parallel; CHECK_EXHAUSTED always passes and reports carrying an
+// ekey are resolved to "earliest offset per (buffer, ekey)" afterwards.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ u8 upcase(u8 c) { return (c >= 'a' && c <= 'z') ? (u8)(c - 0x20) : c; }
+
+__device__ bool check_literal(const u8 *bc, u32 lit_off, u32 lit_len, bool nocase, const u8 *btext, u32 to) {
+    if (to < lit_len) return false;  // roseCheckMediumLiteral: "too short"
+    const u8 *t = btext + (to - lit_len);
+    const u8 *l = bc + lit_off;
+    if (nocase) {
+        for (u32 i = 0; i < lit_len; i++)
+            if (upcase(t[i]) != l[i]) return false;  // literal text is stored upper-cased
+    } else {
+        for (u32 i = 0; i < lit_len; i++)
+            if (t[i] != l[i]) return false;
+    }
+    return true;
+}
+
+// roseCheckMask (src/rose/program_runtime.c:644-727) in block mode: bytes outside the buffer are don't-care
+__device__ bool check_mask8(u64 and_mask, u64 cmp_mask, u64 neg_mask, int check_off, const u8 *btext, u32 blen, u32 to) {
+    if (check_off < 0 && (u32)(-check_off) > to) return false;
+    const long long base = (long long)to + check_off;
+    for (int k = 0; k < 8; k++) {
+        long long o = base + k;
+        if (o < 0 || o >= (long long)blen) continue;
+        u8 a = (u8)(and_mask >> (8 * k)), cm = (u8)(cmp_mask >> (8 * k)), ng = (u8)(neg_mask >> (8 * k));
+        u8 r = (u8)((btext[o] & a) ^ cm);
+        if (ng ? (r == 0) : (r != 0)) return false;  // negated bytes must differ, plain bytes must be equal
+    }
+    return true;
+}
+
+__device__ bool check_byte(u8 and_mask, u8 cmp_mask, u8 negation, int check_off, const u8 *btext, u32 blen, u32 to) {
+    if (check_off < 0 && (u32)(-check_off) > to) return false;
+    const long long o = (long long)to + check_off;
+    if (o < 0 || o >= (long long)blen) return true;
+    const bool differ = (btext[o] & and_mask) != cmp_mask;
+    return !(differ ^ (negation != 0));
+}
+
+__device__ void run_program(const Ctx &c, u32 prog, u32 buf, const u8 *btext, u32 blen, u32 to) {
+    const u8 *bc = c.db.bc;
+    u32 pc = prog;
+    for (int guard = 0; guard < 4096; guard++) {
+        const u8 code = bc[pc];
+        switch (code) {
+        case op::END:
+            return;
+        case op::CHECK_GROUPS:
+            if (!(ld64(bc, pc + op::check_groups::groups) & c.db.groups)) return;
+            pc += op::check_groups::SIZE;
+            break;
+        case op::CHECK_MASK:
+            if (!check_mask8(ld64(bc, pc + op::check_mask::and_mask), ld64(bc, pc + op::check_mask::cmp_mask),
+                             ld64(bc, pc + op::check_mask::neg_mask), (int)ld32(bc, pc + op::check_mask::offset),
+                             btext, blen, to)) {
+                pc += ld32(bc, pc + op::check_mask::fail_jump);
+            } else {
+                pc += op::check_mask::SIZE;
+            }
+            break;
+        case op::CHECK_BYTE:
+            if (!check_byte(bc[pc + op::check_byte::and_mask], bc[pc + op::check_byte::cmp_mask],
+                            bc[pc + op::check_byte::negation], (int)ld32(bc, pc + op::check_byte::offset), btext,
+                            blen, to)) {
+                pc += ld32(bc, pc + op::check_byte::fail_jump);
+            } else {
+                pc += op::check_byte::SIZE;
+            }
+            break;
+        case op::CATCH_UP:
+        case op::CLEAR_WORK_DONE:
+            pc += op::SIZE_1;
+            break;
+        case op::CHECK_LONG_LIT:
+        case op::CHECK_MED_LIT:
+        case op::CHECK_LONG_LIT_NOCASE:
+        case op::CHECK_MED_LIT_NOCASE: {
+            const bool nocase = code == op::CHECK_LONG_LIT_NOCASE || code == op::CHECK_MED_LIT_NOCASE;
+            if (!check_literal(bc, ld32(bc, pc + op::check_lit::lit_offset), ld32(bc, pc + op::check_lit::lit_length),
+                               nocase, btext, to)) {
+                pc += ld32(bc, pc + op::check_lit::fail_jump);
+            } else {
+                pc += op::check_lit::SIZE;
+            }
+            break;
+        }
+        case op::CHECK_EXHAUSTED:
+            pc += op::check_exhausted::SIZE;  // resolved after the scan
+            break;
+        case op::SQUASH_GROUPS:
+            pc += op::squash_groups::SIZE;  // result-neutral once exhaustion is exact
+            break;
+        case op::INCLUDED_JUMP:
+            pc += op::included_jump::SIZE;  // every candidate bit is confirmed independently: no squash, no jump
+            break;
+        case op::DEDUPE: {
+            // the dedupe key rides on the following report; a DEDUPE is always followed by REPORT_EXHAUST
+            // or a quiet SET_EXHAUST in pure-literal programs (makeReport), handled by tagging below
+            const u32 dkey = ld32(bc, pc + op::dedupe::dkey);
+            pc += op::dedupe::SIZE;
+            const u8 nxt = bc[pc];
+            if (nxt == op::REPORT_EXHAUST) {
+                const u32 id = ld32(bc, pc + op::report_exhaust::onmatch);
+                const int adj = (int)ld32(bc, pc + op::report_exhaust::offset_adjust);
+                const u32 ekey = ld32(bc, pc + op::report_exhaust::ekey);
+                emit(c, buf, (u32)((int)to + adj), id, AUX_DEDUPE | AUX_EKEY | (ekey & AUX_KEYMASK));
+                pc += op::report_exhaust::SIZE;
+            } else if (nxt == op::REPORT) {
+                emit(c, buf, (u32)((int)to + (int)ld32(bc, pc + op::report::offset_adjust)),
+                     ld32(bc, pc + op::report::onmatch), AUX_DEDUPE);
+                pc += op::report::SIZE;
+            } else if (nxt == op::SET_EXHAUST) {
+                emit(c, buf, to, 0, AUX_QUIET | AUX_EKEY | (ld32(bc, pc + op::set_exhaust::ekey) & AUX_KEYMASK));
+                pc += op::set_exhaust::SIZE;
+            } else {
+                (void)dkey;
+                atomicOr(c.ar.error, 2u);
+                return;
+            }
+            break;
+        }
+        case op::REPORT:
+            emit(c, buf, (u32)((int)to + (int)ld32(bc, pc + op::report::offset_adjust)),
+                 ld32(bc, pc + op::report::onmatch), 0);
+            pc += op::report::SIZE;
+            break;
+        case op::FINAL_REPORT:
+            emit(c, buf, (u32)((int)to + (int)ld32(bc, pc + op::report::offset_adjust)),
+                 ld32(bc, pc + op::report::onmatch), 0);
+            return;
+        case op::REPORT_EXHAUST:
+            emit(c, buf, (u32)((int)to + (int)ld32(bc, pc + op::report_exhaust::offset_adjust)),
+                 ld32(bc, pc + op::report_exhaust::onmatch),
+                 AUX_EKEY | (ld32(bc, pc + op::report_exhaust::ekey) & AUX_KEYMASK));
+            pc += op::report_exhaust::SIZE;
+            break;
+        case op::DEDUPE_AND_REPORT:
+            emit(c, buf, (u32)((int)to + (int)ld32(bc, pc + op::dedupe_and_report::offset_adjust)),
+                 ld32(bc, pc + op::dedupe_and_report::onmatch), AUX_DEDUPE);
+            pc += op::dedupe_and_report::SIZE;
+            break;
+        case op::SET_EXHAUST:
+            emit(c, buf, to, 0, AUX_QUIET | AUX_EKEY | (ld32(bc, pc + op::set_exhaust::ekey) & AUX_KEYMASK));
+            pc += op::set_exhaust::SIZE;
+            break;
+        default:
+            atomicOr(c.ar.error, 1u);  // cannot happen: the census rejected such databases
+            return;
+        }
+    }
+    atomicOr(c.ar.error, 4u);
+}
+
+// ------------------------------------------------------------------------------------------------
+// buffer lookup + bucket confirm (do_confirm_fdr + confWithBit)
+// ------------------------------------------------------------------------------------------------
+struct BufRef {
+    u32 idx;
+    u64 start;
+    u32 len;
+};
+
+__device__ __forceinline__ BufRef find_buffer(const DevCorpus &cp, u32 strip, u64 g) {
+    u32 lo = cp.strip_first[strip], hi = cp.strip_first[strip + 1];
+    // largest b in [lo, hi] with off[b] <= g
+    while (lo < hi) {
+        u32 mid = (lo + hi + 1) >> 1;
+        if (cp.off[mid] <= g) lo = mid; else hi = mid - 1;
+    }
+    const u64 s = cp.off[lo], e = cp.off[lo + 1];
+    return BufRef{lo, s, (u32)(e - s)};
+}
+
+__device__ __forceinline__ bool passes_gates(const DevDb &db, u32 blen) {
+    if (blen < db.min_width || blen < db.min_width_excl) return false;                 // src/runtime.c:346-350,385-389
+    if (db.max_bi_width != rose::BOUND_INF && blen > db.max_bi_width) return false;     // :393-398
+    return true;
+}
+
+// One candidate: global end position g, bitmask of buckets to confirm.
+__device__ void confirm_entry(const Ctx &c, u32 strip, u64 g, u32 bucket_mask, u32 &n_probe) {
+    if (g >= c.cp.total) return;
+    const BufRef b = find_buffer(c.cp, strip, g);
+    if (!passes_gates(c.db, b.len)) return;
+    const u32 i = (u32)(g - b.start);  // index of the candidate's last byte inside its buffer
+    u64 v = load_tail8(c.cp.text, g);
+    if (i < 7) v &= ~0ull << (8 * (7 - i));  // bytes before the buffer start read as zero (block mode has no history)
+    const u8 *btext = c.cp.text + b.start;
+    const u8 *bc = c.db.bc;
+    while (bucket_mask) {
+        const u32 bk = __ffs(bucket_mask) - 1;
+        bucket_mask &= bucket_mask - 1;
+        const ConfHdr &h = c.conf[bk];
+        if (!h.base || !(h.groups & c.db.groups)) continue;
+        n_probe++;
+        const u32 hash = (u32)(((v & h.andmsk) * h.mult) >> (64 - h.nbits));
+        const u32 start = ld32(bc, h.base + (u32)conf::SIZE + 4 * hash);
+        if (!start) continue;
+        u32 li = h.base + start;
+        for (;;) {
+            const u64 lv = ld64(bc, li + lit::v), lm = ld64(bc, li + lit::msk);
+            const u64 tail = ld64(bc, li + lit::id);  // id | size << 32 | flags << 40 | next << 48
+            const u32 size = (u32)(tail >> 32) & 0xff;
+            if ((v & lm) == lv && size <= i + 1 && (ld64(bc, li + lit::groups) & c.db.groups))
+                run_program(c, (u32)tail, b.idx, btext, b.len, i + 1);
+            if (!((tail >> 48) & 0xff)) break;
+            li += (u32)lit::SIZE;
+        }
+    }
+}
+
+// noodle has no confirm tables: its queue entries run the literal's program directly
+__device__ void confirm_entry_noodle(const Ctx &c, u32 strip, u64 g) {
+    if (g >= c.cp.total) return;
+    const BufRef b = find_buffer(c.cp, strip, g);
+    if (!passes_gates(c.db, b.len)) return;
+    const u32 i = (u32)(g - b.start);
+    if (i + 1 < c.db.nood_len) return;  // literal would start before the buffer
+    run_program(c, c.db.nood_id, b.idx, c.cp.text + b.start, b.len, i + 1);
+}
+
+// warp-synchronous drain of the candidate queue: one lane per entry
+template <bool NOODLE>
+__device__ void drain_queue(const Ctx &c, u32 strip, u64 strip_base, u32 count, u32 &n_probe) {
+    for (u32 base = 0; base < count; base += 32) {
+        const u32 idx = base + lane_id();
+        if (idx < count) {
+            const u32 e = c.ws->q[idx];
+            if (NOODLE) confirm_entry_noodle(c, strip, strip_base + (e >> 8));
+            else confirm_entry(c, strip, strip_base + (e >> 8), e & 0xff, n_probe);
+        }
+        __syncwarp();
+        if (*(volatile u32 *)&c.ws->stage_n >= STAGE_CAP / 2) flush_stage(c);
+    }
+}
+
+// Push this row's candidate bytes (cw[k] covers chunk bytes 4k..4k+3, one bucket bit per bit) into
+// the warp queue.  Warp-synchronous; returns the new queue length.
+__device__ __forceinline__ u32 push_candidates(const Ctx &c, const u32 cw[4], u32 pos_in_strip, u32 qn) {
+    u32 nz = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        u32 w = cw[k];
+        nz |= ((w & 0xffu) ? 1u : 0u) << (4 * k);
+        nz |= ((w & 0xff00u) ? 2u : 0u) << (4 * k);
+        nz |= ((w & 0xff0000u) ? 4u : 0u) << (4 * k);
+        nz |= ((w & 0xff000000u) ? 8u : 0u) << (4 * k);
+    }
+    const u32 n = __popc(nz);
+    u32 incl = n;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        u32 t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane_id() >= (u32)d) incl += t;
+    }
+    u32 slot = qn + incl - n;
+    while (nz) {
+        const u32 k = __ffs(nz) - 1;
+        nz &= nz - 1;
+        const u32 byte = (cw[k >> 2] >> (8 * (k & 3))) & 0xff;
+        c.ws->q[slot++] = ((pos_in_strip + k) << 8) | byte;
+    }
+    return qn + __shfl_sync(0xffffffffu, incl, 31);
+}
+
+// ------------------------------------------------------------------------------------------------
+// front ends.  Each provides:  smem_bytes(db), setup(smem, db) [CTA-wide], and
+//   row(chunk words w[0..3], following word nxt, trailing words of the previous chunk, carry) -> cw[4]
+// ------------------------------------------------------------------------------------------------
+
+// ---- FDR, database's own reach table (position-local restatement of get_conf_stride_N) -----------
+struct FdrNative {
+    static __host__ size_t smem_bytes(const DevDb &db) { return ((size_t)db.fdr_mask + 1) * 8; }
+
+    const u64 *tab;
+    u32 mask;
+    u32 stride;
+    u32 carry4, carry5;  // state overhang of lane 31's previous chunk
+
+    __device__ void setup(u8 *smem, const DevDb &db) {
+        u64 *t = reinterpret_cast<u64 *>(smem);
+        const uint4 *src = reinterpret_cast<const uint4 *>(db.fdr_tab);
+        uint4 *dst = reinterpret_cast<uint4 *>(t);
+        const u32 n16 = (db.fdr_mask + 1) / 2;
+        for (u32 i = threadIdx.x; i < n16; i += blockDim.x) dst[i] = src[i];
+        tab = t;
+        mask = db.fdr_mask;
+        stride = db.fdr_stride;
+        carry4 = carry5 = 0;
+    }
+    __device__ void reset_carry() { carry4 = carry5 = 0; }
+
+    // S = OR over probed x of row(x) << 8x for the 16 positions of this chunk (184 bits in 6 words)
+    template <int STRIDE>
+    __device__ __forceinline__ void probe(const u32 w[5], u32 S[6]) const {
+        u32 A[4][5];
+#pragma unroll
+        for (int s = 0; s < 4; s++)
+#pragma unroll
+            for (int k = 0; k < 5; k++) A[s][k] = 0;
+#pragma unroll
+        for (int x = 0; x < 16; x += STRIDE) {
+            const int wi = x >> 2, sh = x & 3;
+            const u32 key = __funnelshift_r(w[wi], w[wi + 1], 8 * sh) & mask;
+            const u64 r = tab[key];
+            A[sh][wi] |= (u32)r;
+            A[sh][wi + 1] |= (u32)(r >> 32);
+        }
+#pragma unroll
+        for (int k = 0; k < 6; k++) {
+            u32 v = k < 5 ? A[0][k] : 0;
+#pragma unroll
+            for (int s = STRIDE; s < 4; s += STRIDE) {
+                const u32 lo = k >= 1 ? A[s][k - 1] : 0, hi = k < 5 ? A[s][k] : 0;
+                v |= __funnelshift_l(lo, hi, 8 * s);
+            }
+            S[k] = v;
+        }
+    }
+
+    __device__ __forceinline__ void row(const u32 w[5], u32 cw[4], bool warmup) {
+        u32 S[6];
+        if (stride == 1) probe<1>(w, S);
+        else if (stride == 2) probe<2>(w, S);
+        else probe<4>(w, S);
+        u32 in4 = __shfl_up_sync(0xffffffffu, S[4], 1), in5 = __shfl_up_sync(0xffffffffu, S[5], 1);
+        if (lane_id() == 0) { in4 = carry4; in5 = carry5; }
+        carry4 = __shfl_sync(0xffffffffu, S[4], 31);
+        carry5 = __shfl_sync(0xffffffffu, S[5], 31);
+        if (warmup) return;
+        cw[0] = ~(S[0] | in4);
+        cw[1] = ~(S[1] | in5);
+        cw[2] = ~S[2];
+        cw[3] = ~S[3];
+    }
+};
+
+// ---- Teddy, database's own nibble masks folded into one u32 per byte value -----------------------
+// T[c] byte j = lo_j[c & 15] | hi_j[c >> 4]  (bit b set = bucket b cannot have c as its (j+1)-th byte from
+// the end); candidate byte for end i = ~(T[c_i].b0 | T[c_{i-1}].b1 | T[c_{i-2}].b2 | T[c_{i-3}].b3).
+// The table is replicated once per bank (word index c * 32 + lane) so lookups never conflict.
+struct TeddyNative {
+    static __host__ size_t smem_bytes(const DevDb &) { return 256 * 32 * 4; }
+    const u32 *tab;
+    u32 c1, c2, c3;  // T of the last three bytes of lane 31's previous chunk
+
+    __device__ void setup(u8 *smem, const DevDb &db) {
+        u32 *t = reinterpret_cast<u32 *>(smem);
+        for (u32 i = threadIdx.x; i < 256 * 32; i += blockDim.x) t[i] = db.teddy_tab[i >> 5];
+        tab = t;
+        c1 = c2 = c3 = 0;
+    }
+    __device__ void reset_carry() { c1 = c2 = c3 = 0; }
+
+    __device__ __forceinline__ void row(const u32 w[5], u32 cw[4], bool warmup) {
+        u32 t[19];  // t[3 + i] = T[c_i]; t[0..2] = previous three bytes
+        const u32 ln = lane_id();
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            const u32 ch = (w[i >> 2] >> (8 * (i & 3))) & 0xff;
+            t[3 + i] = tab[ch * 32 + ln];
+        }
+        u32 p1 = __shfl_up_sync(0xffffffffu, t[18], 1), p2 = __shfl_up_sync(0xffffffffu, t[17], 1),
+            p3 = __shfl_up_sync(0xffffffffu, t[16], 1);
+        if (ln == 0) { p1 = c1; p2 = c2; p3 = c3; }
+        c1 = __shfl_sync(0xffffffffu, t[18], 31);
+        c2 = __shfl_sync(0xffffffffu, t[17], 31);
+        c3 = __shfl_sync(0xffffffffu, t[16], 31);
+        if (warmup) return;
+        t[2] = p1; t[1] = p2; t[0] = p3;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            u32 word = 0;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int i = 4 * k + j;
+                const u32 m = (t[3 + i] & 0xff) | ((t[2 + i] >> 8) & 0xff) | ((t[1 + i] >> 16) & 0xff) | (t[i] >> 24);
+                word |= (~m & 0xff) << (8 * j);
+            }
+            cw[k] = word;
+        }
+    }
+};
+
+// ---- noodle: one literal of <= 8 bytes, compared directly (msk/cmp of the noodTable) ---------------
+struct Noodle {
+    static __host__ size_t smem_bytes(const DevDb &) { return 16; }
+    u64 msk, cmp;
+    u32 len;
+    u32 cw2, cw3;  // last 8 bytes of lane 31's previous chunk
+
+    __device__ void setup(u8 *, const DevDb &db) {
+        // noodTable msk/cmp hold the literal's first byte in the low byte; align so its LAST byte is the top byte
+        const u32 sh = 8 * (8 - db.nood_len);
+        msk = db.nood_msk << sh;
+        cmp = db.nood_cmp << sh;
+        len = db.nood_len;
+        cw2 = cw3 = 0;
+    }
+    __device__ void reset_carry() { cw2 = cw3 = 0; }
+
+    __device__ __forceinline__ void row(const u32 w[5], u32 cw[4], bool warmup) {
+        u32 p2 = __shfl_up_sync(0xffffffffu, w[2], 1), p3 = __shfl_up_sync(0xffffffffu, w[3], 1);
+        if (lane_id() == 0) { p2 = cw2; p3 = cw3; }
+        cw2 = __shfl_sync(0xffffffffu, w[2], 31);
+        cw3 = __shfl_sync(0xffffffffu, w[3], 31);
+        if (warmup) return;
+        const u32 e[6] = {p2, p3, w[0], w[1], w[2], w[3]};  // 24 bytes: 8 before the chunk + the chunk
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            u32 word = 0;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int i = 4 * k + j;            // end position inside the chunk
+                const int first = i + 1;            // byte index in e[] of the window's first byte (8 + i - 7)
+                const int wi = first >> 2, sh = (first & 3) * 8;
+                const u32 lo = __funnelshift_r(e[wi], e[wi + 1], sh);
+                const u32 hi = __funnelshift_r(e[wi + 1], wi + 2 < 6 ? e[wi + 2] : 0, sh);
+                const u64 v = ((u64)hi << 32) | lo;
+                word |= (((v & msk) == cmp) ? 1u : 0u) << (8 * j);  // single pseudo-bucket 0
+            }
+            cw[k] = word;
+        }
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
+// the scan kernel: persistent CTAs, one strip per warp at a time
+// ------------------------------------------------------------------------------------------------
+template <class FE, bool NOODLE>
+__global__ void __launch_bounds__(THREADS, 1) k_scan(const DevDb db, const DevCorpus cp, const DevArena ar) {
+    extern __shared__ __align__(16) u8 smem[];
+    __shared__ WarpShared wsh[WARPS];
+    __shared__ ConfHdr conf[16];
+
+    FE fe;
+    fe.setup(smem, db);
+    if (threadIdx.x < 16) {
+        ConfHdr h{0, 0, 0, 0, 0};
+        if (!NOODLE && threadIdx.x < db.n_buckets) {
+            const u32 cf = ld32(db.bc, db.conf_base + 4 * threadIdx.x);
+            if (cf) {
+                h.base = db.conf_base + cf;
+                h.andmsk = ld64(db.bc, h.base + (u32)conf::andmsk);
+                h.mult = ld64(db.bc, h.base + (u32)conf::mult);
+                h.nbits = ld32(db.bc, h.base + (u32)conf::nBits);
+                h.groups = ld64(db.bc, h.base + (u32)conf::groups);
+            }
+        }
+        conf[threadIdx.x] = h;
+    }
+    const u32 warp = threadIdx.x >> 5, ln = lane_id();
+    if (ln == 0) wsh[warp].stage_n = 0;
+    __syncthreads();
+
+    const Ctx c{db, cp, ar, &wsh[warp], conf};
+    u32 n_cand = 0, n_probe = 0;
+    const u32 warps_total = gridDim.x * WARPS;
+    for (u32 strip = blockIdx.x * WARPS + warp; strip < cp.nstrips; strip += warps_total) {
+        const u64 strip_base = (u64)strip * STRIP_BYTES;
+        u32 qn = 0;
+        fe.reset_carry();
+        for (int row = strip_base ? -1 : 0; row < STRIP_ROWS; row++) {
+            const long long g0 = (long long)strip_base + (long long)row * ROW_BYTES + ln * CHUNK;
+            if (row >= 0 && (u64)((long long)strip_base + (long long)row * ROW_BYTES) >= cp.total) break;
+            const uint4 v = *reinterpret_cast<const uint4 *>(cp.text + g0);
+            u32 w[5] = {v.x, v.y, v.z, v.w, 0};
+            w[4] = __shfl_down_sync(0xffffffffu, v.x, 1);
+            if (ln == 31) w[4] = *reinterpret_cast<const u32 *>(cp.text + g0 + CHUNK);
+            u32 cw[4] = {0, 0, 0, 0};
+            fe.row(w, cw, row < 0);
+            if (row < 0) continue;
+            // clip end positions beyond the corpus
+            const long long left = (long long)cp.total - g0;
+            if (left < CHUNK) {
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const long long lw = left - 4 * k;
+                    if (lw <= 0) cw[k] = 0;
+                    else if (lw < 4) cw[k] &= (1u << (8 * (int)lw)) - 1;
+                }
+            }
+            if (__any_sync(0xffffffffu, (cw[0] | cw[1] | cw[2] | cw[3]) != 0)) {
+                const u32 before = qn;
+                qn = push_candidates(c, cw, (u32)row * ROW_BYTES + ln * CHUNK, qn);
+                n_cand += qn - before;
+                __syncwarp();
+                if (qn > QCAP - ROW_BYTES) {
+                    drain_queue<NOODLE>(c, strip, strip_base, qn, n_probe);
+                    qn = 0;
+                }
+            }
+        }
+        if (qn) drain_queue<NOODLE>(c, strip, strip_base, qn, n_probe);
+    }
+    flush_stage(c);
+    // per-warp statistics: n_cand is warp-uniform, n_probe is per lane
+#pragma unroll
+    for (int d = 16; d; d >>= 1) n_probe += __shfl_down_sync(0xffffffffu, n_probe, d);
+    if (ln == 0) {
+        if (n_cand) atomicAdd(&ar.stats[0], (unsigned long long)n_cand);
+        if (n_probe) atomicAdd(&ar.stats[1], (unsigned long long)n_probe);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// finalize: Rec (sorted, deduped) -> hs_gpu_match_t
+// ------------------------------------------------------------------------------------------------
+struct RecLess {
+    __host__ __device__ bool operator()(const Rec &a, const Rec &b) const {
+        if (a.buf != b.buf) return a.buf < b.buf;
+        if (a.to != b.to) return a.to < b.to;
+        if (a.id != b.id) return a.id < b.id;
+        return a.aux < b.aux;
+    }
+};
+struct RecDup {  // equal = second is a dedupe-key duplicate of the first
+    __host__ __device__ bool operator()(const Rec &a, const Rec &b) const {
+        return (a.aux & b.aux & AUX_DEDUPE) && a.buf == b.buf && a.to == b.to && a.id == b.id &&
+               ((a.aux ^ b.aux) & AUX_QUIET) == 0;
+    }
+};
+
+// keep[i] = 0 iff record i repeats record i-1 under a dedupe key (dedupeCatchup, src/report.h:83-93)
+__global__ void k_flag_dups(const Rec *in, u8 *keep, u64 n) {
+    const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) keep[i] = (i && RecDup()(in[i - 1], in[i])) ? 0 : 1;
+}
+
+__global__ void k_convert(const Rec *in, hs_gpu_match_t *out, u64 n) {
+    const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        const Rec r = in[i];
+        out[i] = hs_gpu_match_t{r.buf, r.id, (uint64_t)r.to};
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+#define CU_OK(expr)                                                                          \
+    do {                                                                                     \
+        cudaError_t e__ = (expr);                                                            \
+        if (e__ != cudaSuccess) {                                                            \
+            if (getenv("HS_GPU_DEBUG"))                                                      \
+                fprintf(stderr, "hs_gpu: %s -> %s (%s:%d)\n", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+            return e__ == cudaErrorMemoryAllocation ? HS_NOMEM : HS_UNKNOWN_ERROR;           \
+        }                                                                                    \
+    } while (0)
+
+template <class T>
+struct DevBuf {  // grow-only device allocation
+    T *p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = n + n / 4 + 64;
+        cudaError_t e = cudaMalloc((void **)&p, want * sizeof(T));
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    size_t bytes() const { return cap * sizeof(T); }
+};
+
+struct DbImage {  // one uploaded database
+    const void *host_db = nullptr;
+    u32 crc = 0, bc_len = 0;
+    DbView view;
+    DevDb dev{};
+    u8 *d_bc = nullptr;
+    u64 *d_fdr = nullptr;
+    u32 *d_teddy = nullptr;
+    size_t device_bytes = 0;
+    void release() {
+        if (d_bc) cudaFree(d_bc);
+        if (d_fdr) cudaFree(d_fdr);
+        if (d_teddy) cudaFree(d_teddy);
+        d_bc = nullptr; d_fdr = nullptr; d_teddy = nullptr;
+    }
+};
+
+}  // namespace
+
+struct hs_gpu_corpus {
+    u32 magic = 0x43525053;
+    int device = 0;
+    DevBuf<u8> text;          // FRONT_PAD + total + BACK_PAD
+    DevBuf<u64> off;
+    DevBuf<u32> strip_first;
+    u64 total = 0;
+    u32 count = 0, nstrips = 0;
+    DevCorpus dev() const {
+        return DevCorpus{text.p + FRONT_PAD, off.p, strip_first.p, total, count, nstrips};
+    }
+};
+
+struct hs_gpu_scratch {
+    u32 magic = 0x47505553;  // 'GPUS'
+    std::atomic<int> in_use{0};
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    std::vector<DbImage *> dbs;
+    hs_gpu_corpus staging;       // device staging for host-buffer scans
+    u8 *h_stage = nullptr;       // pinned host staging
+    size_t h_stage_cap = 0;
+    std::vector<u64> h_off;
+    std::vector<u32> h_strip_first;
+    DevBuf<Rec> recs, recs2;
+    DevBuf<hs_gpu_match_t> d_matches;
+    DevBuf<u8> cub_tmp, keep;
+    unsigned long long *d_ctl = nullptr;  // [0] arena count, [1] candidates, [2] probes, [3] error(u32), [4] n_selected
+    unsigned long long *h_ctl = nullptr;  // pinned mirror
+    hs_gpu_match_t *h_matches = nullptr;  // pinned
+    size_t h_matches_cap = 0;
+    u64 n_matches = 0;           // valid entries in d_matches
+    bool fetched = false;
+    void *last_image = nullptr;  // DbImage that produced the current matches
+    hs_gpu_stats_t stats{};
+    int sm_count = 148;
+    long opt_frontend = 0;
+    long opt_grid = 0;
+    u64 arena_hint = 1 << 16;
+};
+
+namespace {
+
+std::mutex g_init_mutex;
+
+hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage **out) {
+    // cached by (pointer, crc)
+    const u32 crc = rd32(db, db::crc32);
+    for (DbImage *im : s->dbs)
+        if (im->host_db == db && im->crc == crc) { *out = im; return HS_SUCCESS; }
+    DbImage *im = new DbImage();
+    std::string why;
+    int rv = parse_database(db, im->view, why);
+    if (rv != E_SUCCESS) {
+        if (getenv("HS_GPU_DEBUG")) fprintf(stderr, "hs_gpu: database refused: %s\n", why.c_str());
+        delete im;
+        return rv;
+    }
+    const DbView &v = im->view;
+    im->host_db = db;
+    im->crc = crc;
+    im->bc_len = v.bc_len;
+    cudaError_t e = cudaMalloc((void **)&im->d_bc, round_up(v.bc_len, 256) + 256);
+    if (e != cudaSuccess) { delete im; return HS_NOMEM; }
+    cudaMemcpyAsync(im->d_bc, v.bc, v.bc_len, cudaMemcpyHostToDevice, s->stream);
+    im->device_bytes = round_up(v.bc_len, 256) + 256;
+    DevDb &d = im->dev;
+    d.bc = im->d_bc;
+    d.groups = v.groups;
+    d.conf_base = v.conf_base;
+    d.n_buckets = v.n_buckets;
+    d.min_width = v.min_width;
+    d.min_width_excl = v.min_width_excl;
+    d.max_bi_width = v.max_bi_width;
+    d.bc_len = v.bc_len;
+    std::vector<u64> folded;
+    std::vector<u32> ttab;
+    if (v.kind == ENG_FDR) {
+        // Reach table for shared memory: domains up to 14 are used as they are; a domain-15 table (256 KiB)
+        // is folded to 2^14 rows by AND-ing the two rows that differ in key bit 14.  A cleared bit means
+        // "possible", so the fold only over-approximates: the filter stays sound, confirm stays exact.
+        const u32 rows = 1u << v.fdr_domain, keep = std::min<u32>(rows, 1u << 14);
+        folded.resize(keep);
+        for (u32 i = 0; i < keep; i++) {
+            u64 r = rd64(v.bc, v.fdr_tab + 8 * (size_t)i);
+            for (u32 j = i + keep; j < rows; j += keep) r &= rd64(v.bc, v.fdr_tab + 8 * (size_t)j);
+            folded[i] = r;
+        }
+        e = cudaMalloc((void **)&im->d_fdr, keep * 8);
+        if (e != cudaSuccess) { im->release(); delete im; return HS_NOMEM; }
+        cudaMemcpyAsync(im->d_fdr, folded.data(), keep * 8, cudaMemcpyHostToDevice, s->stream);
+        im->device_bytes += keep * 8;
+        d.fdr_tab = im->d_fdr;
+        d.fdr_mask = keep - 1;
+        d.fdr_stride = v.fdr_stride;
+    } else if (v.kind == ENG_TEDDY) {
+        ttab.assign(256, 0);
+        for (u32 cch = 0; cch < 256; cch++) {
+            u32 t = 0;
+            for (u32 j = 0; j < v.teddy_masks; j++) {
+                const u8 lo = rd8(v.bc, v.teddy_mask_off + (size_t)(2 * j) * 16 + (cch & 15));
+                const u8 hi = rd8(v.bc, v.teddy_mask_off + (size_t)(2 * j + 1) * 16 + (cch >> 4));
+                t |= (u32)(lo | hi) << (8 * j);
+            }
+            ttab[cch] = t;
+        }
+        e = cudaMalloc((void **)&im->d_teddy, 256 * 4);
+        if (e != cudaSuccess) { im->release(); delete im; return HS_NOMEM; }
+        cudaMemcpyAsync(im->d_teddy, ttab.data(), 256 * 4, cudaMemcpyHostToDevice, s->stream);
+        im->device_bytes += 1024;
+        d.teddy_tab = im->d_teddy;
+        d.teddy_masks = v.teddy_masks;
+    } else {
+        d.nood_msk = v.nood_msk;
+        d.nood_cmp = v.nood_cmp;
+        d.nood_len = v.nood_len;
+        d.nood_id = v.nood_id;
+    }
+    if (cudaStreamSynchronize(s->stream) != cudaSuccess) { im->release(); delete im; return HS_UNKNOWN_ERROR; }
+    s->dbs.push_back(im);
+    *out = im;
+    return HS_SUCCESS;
+}
+
+void build_strip_first(const u64 *off, u32 count, u64 total, std::vector<u32> &out, u32 &nstrips) {
+    nstrips = (u32)((total + STRIP_BYTES - 1) / STRIP_BYTES);
+    out.resize((size_t)nstrips + 1);
+    u32 b = 0;
+    for (u32 s = 0; s <= nstrips; s++) {
+        u64 pos = std::min<u64>((u64)s * STRIP_BYTES, total ? total - 1 : 0);
+        while (b + 1 < count && off[b + 1] <= pos) b++;
+        out[s] = b;
+    }
+}
+
+template <class FE, bool NOODLE>
+hs_error_t launch_scan(hs_gpu_scratch *s, const DevDb &db, const DevCorpus &cp, const DevArena &ar) {
+    const size_t dyn = FE::smem_bytes(db);
+    static size_t configured = 0;
+    if (dyn > configured) {
+        CU_OK(cudaFuncSetAttribute(k_scan<FE, NOODLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+        configured = dyn;
+    }
+    u32 grid = s->opt_grid > 0 ? (u32)s->opt_grid : (u32)s->sm_count;
+    const u32 need = (cp.nstrips + WARPS - 1) / WARPS;
+    if (grid > need) grid = need ? need : 1;
+    k_scan<FE, NOODLE><<<grid, THREADS, dyn, s->stream>>>(db, cp, ar);
+    CU_OK(cudaGetLastError());
+    return HS_SUCCESS;
+}
+
+// Device pass over a resident corpus: scan (+ retry on arena growth), sort, dedupe, convert.
+hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corpus) {
+    hs_gpu_stats_t &st = s->stats;
+    st.bytes = corpus.total;
+    st.buffers = corpus.count;
+    st.scan_launches = 0;
+    st.arena_retries = 0;
+    s->n_matches = 0;
+    s->fetched = false;
+    s->last_image = im;
+    if (!corpus.total || !corpus.count) {
+        st.matches = st.raw_matches = st.candidates = st.confirms = 0;
+        st.scan_ms = st.sort_ms = 0;
+        return HS_SUCCESS;
+    }
+    CU_OK(s->recs.reserve(s->arena_hint));
+    const DevCorpus cp = corpus.dev();
+    u64 raw = 0;
+    CU_OK(cudaEventRecord(s->ev[1], s->stream));
+    for (int attempt = 0;; attempt++) {
+        CU_OK(cudaMemsetAsync(s->d_ctl, 0, 8 * sizeof(unsigned long long), s->stream));
+        DevArena ar{s->recs.p, s->d_ctl + 0, s->d_ctl + 1, reinterpret_cast<u32 *>(s->d_ctl + 3), s->recs.cap};
+        hs_error_t rv;
+        switch (im->view.kind) {
+        case ENG_FDR: rv = launch_scan<FdrNative, false>(s, im->dev, cp, ar); break;
+        case ENG_TEDDY: rv = launch_scan<TeddyNative, false>(s, im->dev, cp, ar); break;
+        default: rv = launch_scan<Noodle, true>(s, im->dev, cp, ar); break;
+        }
+        if (rv != HS_SUCCESS) return rv;
+        st.scan_launches++;
+        CU_OK(cudaMemcpyAsync(s->h_ctl, s->d_ctl, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
+        CU_OK(cudaStreamSynchronize(s->stream));
+        if ((u32)s->h_ctl[3]) return HS_UNKNOWN_ERROR;
+        raw = s->h_ctl[0];
+        if (raw <= s->recs.cap) break;
+        if (attempt >= 3) return HS_NOMEM;
+        st.arena_retries++;
+        s->arena_hint = raw + raw / 8 + 1024;
+        CU_OK(s->recs.reserve(s->arena_hint));
+    }
+    CU_OK(cudaEventRecord(s->ev[2], s->stream));
+    st.raw_matches = raw;
+    st.candidates = s->h_ctl[1];
+    st.confirms = s->h_ctl[2];
+    u64 n_out = 0;
+    if (raw) {
+        size_t tmp1 = 0, tmp2 = 0;
+        CU_OK(s->recs2.reserve(raw));
+        CU_OK(s->d_matches.reserve(raw));
+        cub::DeviceMergeSort::SortKeys((void *)nullptr, tmp1, s->recs.p, (long long)raw, RecLess(), s->stream);
+        CU_OK(s->keep.reserve(raw));
+        cub::DeviceSelect::Flagged((void *)nullptr, tmp2, s->recs.p, s->keep.p, s->recs2.p,
+                                   (unsigned long long *)nullptr, (long long)raw, s->stream);
+        CU_OK(s->cub_tmp.reserve(std::max(tmp1, tmp2)));
+        size_t tb = s->cub_tmp.bytes();
+        CU_OK(cub::DeviceMergeSort::SortKeys(s->cub_tmp.p, tb, s->recs.p, (long long)raw, RecLess(), s->stream));
+        tb = s->cub_tmp.bytes();
+        k_flag_dups<<<(unsigned)((raw + 255) / 256), 256, 0, s->stream>>>(s->recs.p, s->keep.p, raw);
+        CU_OK(cudaGetLastError());
+        CU_OK(cub::DeviceSelect::Flagged(s->cub_tmp.p, tb, s->recs.p, s->keep.p, s->recs2.p, s->d_ctl + 4,
+                                         (long long)raw, s->stream));
+        CU_OK(cudaMemcpyAsync(s->h_ctl + 4, s->d_ctl + 4, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
+        CU_OK(cudaStreamSynchronize(s->stream));
+        n_out = s->h_ctl[4];
+        k_convert<<<(unsigned)((n_out + 255) / 256), 256, 0, s->stream>>>(s->recs2.p, s->d_matches.p, n_out);
+        CU_OK(cudaGetLastError());
+    }
+    CU_OK(cudaEventRecord(s->ev[3], s->stream));
+    CU_OK(cudaEventSynchronize(s->ev[3]));
+    cudaEventElapsedTime(&st.scan_ms, s->ev[1], s->ev[2]);
+    cudaEventElapsedTime(&st.sort_ms, s->ev[2], s->ev[3]);
+    s->n_matches = n_out;
+    st.matches = n_out;
+    return HS_SUCCESS;
+}
+
+// Single-match (exhaustion key) resolution and removal of quiet records, on the host copy.
+// Records arrive sorted by (buffer, to, id): the first record of an (buffer, ekey) pair is the earliest.
+u64 resolve_exhaustion(hs_gpu_scratch *s, const Rec *recs, u64 n, hs_gpu_match_t *out) {
+    (void)s;
+    std::map<std::pair<u32, u32>, bool> seen;
+    u64 m = 0;
+    for (u64 i = 0; i < n; i++) {
+        const Rec &r = recs[i];
+        if (r.aux & AUX_EKEY) {
+            auto key = std::make_pair(r.buf, r.aux & AUX_KEYMASK);
+            if (seen.count(key)) continue;
+            seen[key] = true;
+        }
+        if (r.aux & AUX_QUIET) continue;
+        out[m++] = hs_gpu_match_t{r.buf, r.id, (uint64_t)r.to};
+    }
+    return m;
+}
+
+hs_error_t fetch_matches(hs_gpu_scratch *s, DbImage *im) {
+    hs_gpu_stats_t &st = s->stats;
+    st.d2h_ms = 0;
+    if (s->fetched) return HS_SUCCESS;
+    const u64 n = s->n_matches;
+    if (n > s->h_matches_cap) {
+        if (s->h_matches) cudaFreeHost(s->h_matches);
+        s->h_matches = nullptr;
+        s->h_matches_cap = 0;
+        const size_t want = n + n / 4 + 1024;
+        // room for either representation (both are 16 bytes)
+        CU_OK(cudaHostAlloc((void **)&s->h_matches, want * sizeof(hs_gpu_match_t), cudaHostAllocDefault));
+        s->h_matches_cap = want;
+    }
+    if (n) {
+        CU_OK(cudaEventRecord(s->ev[4], s->stream));
+        const bool need_recs = im && im->view.ekey_count > 0;
+        static_assert(sizeof(Rec) == sizeof(hs_gpu_match_t), "record sizes");
+        CU_OK(cudaMemcpyAsync(s->h_matches, need_recs ? (const void *)s->recs2.p : (const void *)s->d_matches.p,
+                              n * sizeof(hs_gpu_match_t), cudaMemcpyDeviceToHost, s->stream));
+        CU_OK(cudaEventRecord(s->ev[5], s->stream));
+        CU_OK(cudaEventSynchronize(s->ev[5]));
+        cudaEventElapsedTime(&st.d2h_ms, s->ev[4], s->ev[5]);
+        if (need_recs) {
+            std::vector<Rec> tmp(n);
+            std::memcpy(tmp.data(), s->h_matches, n * sizeof(Rec));
+            s->n_matches = resolve_exhaustion(s, tmp.data(), n, s->h_matches);
+            st.matches = s->n_matches;
+        }
+    }
+    s->fetched = true;
+    return HS_SUCCESS;
+}
+
+hs_error_t ensure_device(hs_gpu_scratch *s) {
+    int cur = -1;
+    if (cudaGetDevice(&cur) != cudaSuccess) return HS_ARCH_ERROR;
+    if (cur != s->device && cudaSetDevice(s->device) != cudaSuccess) return HS_ARCH_ERROR;
+    return HS_SUCCESS;
+}
+
+struct InUseGuard {
+    hs_gpu_scratch *s;
+    bool ok;
+    explicit InUseGuard(hs_gpu_scratch *s_) : s(s_) { int z = 0; ok = s->in_use.compare_exchange_strong(z, 1); }
+    ~InUseGuard() { if (ok) s->in_use.store(0); }
+};
+
+hs_error_t stage_host_buffers(hs_gpu_scratch *s, const char *const *data, const unsigned int *length, unsigned count) {
+    hs_gpu_corpus &cp = s->staging;
+    s->h_off.resize((size_t)count + 1);
+    u64 total = 0;
+    bool contiguous = true;
+    for (unsigned i = 0; i < count; i++) {
+        if (!data[i] && length[i]) return HS_INVALID;
+        s->h_off[i] = total;
+        if (i && length[i] && data[i] != data[i - 1] + length[i - 1]) contiguous = false;
+        total += length[i];
+    }
+    s->h_off[count] = total;
+    cp.total = total;
+    cp.count = count;
+    build_strip_first(s->h_off.data(), count, total, s->h_strip_first, cp.nstrips);
+    CU_OK(cp.text.reserve(FRONT_PAD + total + BACK_PAD));
+    CU_OK(cp.off.reserve((size_t)count + 1));
+    CU_OK(cp.strip_first.reserve((size_t)cp.nstrips + 1));
+    const u8 *src = nullptr;
+    if (contiguous && count && total) {
+        // zero-copy source when the caller's buffers are one pinned region (hs_gpu_host_alloc)
+        const char *first = nullptr;
+        for (unsigned i = 0; i < count && !first; i++) if (length[i]) first = data[i];
+        cudaPointerAttributes at{};
+        if (first && cudaPointerGetAttributes(&at, first) == cudaSuccess && at.type == cudaMemoryTypeHost)
+            src = reinterpret_cast<const u8 *>(first);
+        else
+            cudaGetLastError();
+    }
+    if (!src && total) {
+        if (total > s->h_stage_cap) {
+            if (s->h_stage) cudaFreeHost(s->h_stage);
+            s->h_stage = nullptr;
+            s->h_stage_cap = 0;
+            const size_t want = total + total / 4 + 4096;
+            CU_OK(cudaHostAlloc((void **)&s->h_stage, want, cudaHostAllocDefault));
+            s->h_stage_cap = want;
+        }
+        for (unsigned i = 0; i < count; i++)
+            if (length[i]) std::memcpy(s->h_stage + s->h_off[i], data[i], length[i]);
+        src = s->h_stage;
+    }
+    CU_OK(cudaEventRecord(s->ev[0], s->stream));
+    // zero the pads (the front pad is read by look-behind, the back pad by the last rows)
+    CU_OK(cudaMemsetAsync(cp.text.p, 0, FRONT_PAD, s->stream));
+    CU_OK(cudaMemsetAsync(cp.text.p + FRONT_PAD + total, 0, BACK_PAD, s->stream));
+    if (total) CU_OK(cudaMemcpyAsync(cp.text.p + FRONT_PAD, src, total, cudaMemcpyHostToDevice, s->stream));
+    CU_OK(cudaMemcpyAsync(cp.off.p, s->h_off.data(), ((size_t)count + 1) * 8, cudaMemcpyHostToDevice, s->stream));
+    CU_OK(cudaMemcpyAsync(cp.strip_first.p, s->h_strip_first.data(), ((size_t)cp.nstrips + 1) * 4,
+                          cudaMemcpyHostToDevice, s->stream));
+    return HS_SUCCESS;
+}
+
+hs_error_t scan_host_batch(const hs_database_t *db, const char *const *data, const unsigned int *length,
+                           unsigned count, hs_gpu_scratch *s, DbImage **im_out) {
+    hs_error_t rv = ensure_device(s);
+    if (rv != HS_SUCCESS) return rv;
+    DbImage *im = nullptr;
+    rv = upload_database(s, db, &im);
+    if (rv != HS_SUCCESS) return rv;
+    *im_out = im;
+    rv = stage_host_buffers(s, data, length, count);
+    if (rv != HS_SUCCESS) return rv;
+    cudaEvent_t h2d_begin = s->ev[0];
+    rv = scan_device(s, im, s->staging);
+    if (rv != HS_SUCCESS) return rv;
+    // ev[1] was re-recorded by scan_device right after the copies were queued: h2d = ev0 -> ev1
+    cudaEventElapsedTime(&s->stats.h2d_ms, h2d_begin, s->ev[1]);
+    return fetch_matches(s, im);
+}
+
+hs_error_t validate_scan_args(const hs_database_t *db, hs_gpu_scratch *s) {
+    if (!s || s->magic != 0x47505553) return HS_INVALID;
+    if (!db || rd32(db, db::magic) != db::MAGIC) return HS_INVALID;
+    if (rd32(db, db::version) != db::VERSION_5_4_11) return HS_DB_VERSION_ERROR;
+    return HS_SUCCESS;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+// C ABI
+// ------------------------------------------------------------------------------------------------
+extern "C" {
+
+const char *hs_gpu_version(void) { return HSG_VERSION; }
+
+int hs_gpu_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+hs_error_t hs_gpu_set_device(int device) { return cudaSetDevice(device) == cudaSuccess ? HS_SUCCESS : HS_ARCH_ERROR; }
+
+void *hs_gpu_host_alloc(size_t bytes) {
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+void hs_gpu_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+hs_error_t hs_gpu_alloc_scratch(const hs_database_t *db, hs_gpu_scratch_t **scratch) {
+    if (!db || !scratch) return HS_INVALID;
+    // database sanity first, as hs_alloc_scratch does (dbIsValid)
+    DbView probe;
+    std::string why;
+    int prv = parse_database(db, probe, why);
+    if (prv != E_SUCCESS) {
+        if (getenv("HS_GPU_DEBUG")) fprintf(stderr, "hs_gpu: database refused: %s\n", why.c_str());
+        return prv;
+    }
+    if (hs_gpu_device_count() <= 0) return HS_ARCH_ERROR;  // no CPU fallback
+    hs_gpu_scratch *s = *scratch;
+    bool fresh = false;
+    if (s) {
+        if (s->magic != 0x47505553) return HS_INVALID;
+        int z = 0;
+        if (!s->in_use.compare_exchange_strong(z, 1)) return HS_SCRATCH_IN_USE;
+    } else {
+        s = new (std::nothrow) hs_gpu_scratch();
+        if (!s) return HS_NOMEM;
+        fresh = true;
+        s->in_use.store(1);
+        if (cudaGetDevice(&s->device) != cudaSuccess) { delete s; return HS_ARCH_ERROR; }
+        cudaDeviceProp prop{};
+        if (cudaGetDeviceProperties(&prop, s->device) == cudaSuccess) s->sm_count = prop.multiProcessorCount;
+        if (cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) != cudaSuccess) { delete s; return HS_UNKNOWN_ERROR; }
+        for (auto &e : s->ev) cudaEventCreate(&e);
+        if (cudaMalloc((void **)&s->d_ctl, 8 * sizeof(unsigned long long)) != cudaSuccess ||
+            cudaHostAlloc((void **)&s->h_ctl, 8 * sizeof(unsigned long long), cudaHostAllocDefault) != cudaSuccess) {
+            hs_gpu_free_scratch(s);
+            return HS_NOMEM;
+        }
+        if (const char *g = getenv("HS_GPU_GRID")) s->opt_grid = atol(g);
+    }
+    DbImage *im = nullptr;
+    hs_error_t rv = upload_database(s, db, &im);
+    s->in_use.store(0);
+    if (rv != HS_SUCCESS) {
+        if (fresh) { hs_gpu_free_scratch(s); }
+        return rv;
+    }
+    *scratch = s;
+    return HS_SUCCESS;
+}
+
+hs_error_t hs_gpu_clone_scratch(const hs_gpu_scratch_t *src, hs_gpu_scratch_t **dest) {
+    if (!src || !dest || src->magic != 0x47505553) return HS_INVALID;
+    *dest = nullptr;
+    hs_gpu_scratch *d = nullptr;
+    for (DbImage *im : src->dbs) {
+        hs_error_t rv = hs_gpu_alloc_scratch(reinterpret_cast<const hs_database_t *>(im->host_db), &d);
+        if (rv != HS_SUCCESS) { if (d) hs_gpu_free_scratch(d); return rv; }
+    }
+    if (!d) return HS_INVALID;
+    d->opt_frontend = src->opt_frontend;
+    d->opt_grid = src->opt_grid;
+    *dest = d;
+    return HS_SUCCESS;
+}
+
+hs_error_t hs_gpu_scratch_size(const hs_gpu_scratch_t *s, size_t *host_bytes, size_t *device_bytes) {
+    if (!s || s->magic != 0x47505553) return HS_INVALID;
+    size_t dev = 8 * sizeof(unsigned long long);
+    for (DbImage *im : s->dbs) dev += im->device_bytes;
+    dev += s->staging.text.bytes() + s->staging.off.bytes() + s->staging.strip_first.bytes();
+    dev += s->recs.bytes() + s->recs2.bytes() + s->d_matches.bytes() + s->cub_tmp.bytes();
+    if (host_bytes) *host_bytes = sizeof(*s) + s->h_stage_cap + s->h_matches_cap * sizeof(hs_gpu_match_t);
+    if (device_bytes) *device_bytes = dev;
+    return HS_SUCCESS;
+}
+
+hs_error_t hs_gpu_free_scratch(hs_gpu_scratch_t *s) {
+    if (!s) return HS_SUCCESS;
+    if (s->magic != 0x47505553) return HS_INVALID;
+    if (s->stream) cudaStreamSynchronize(s->stream);
+    for (DbImage *im : s->dbs) { im->release(); delete im; }
+    s->dbs.clear();
+    s->staging.text.release();
+    s->staging.off.release();
+    s->staging.strip_first.release();
+    s->recs.release();
+    s->recs2.release();
+    s->d_matches.release();
+    s->cub_tmp.release();
+    s->keep.release();
+    if (s->h_stage) cudaFreeHost(s->h_stage);
+    if (s->h_matches) cudaFreeHost(s->h_matches);
+    if (s->h_ctl) cudaFreeHost(s->h_ctl);
+    if (s->d_ctl) cudaFree(s->d_ctl);
+    for (auto &e : s->ev) if (e) cudaEventDestroy(e);
+    if (s->stream) cudaStreamDestroy(s->stream);
+    s->magic = 0;
+    delete s;
+    return HS_SUCCESS;
+}
+
+static hs_error_t deliver(hs_gpu_scratch *s, match_event_handler onEvent, void *context, void *const *contexts) {
+    if (!onEvent) return HS_SUCCESS;  // matches suppressed, as with a NULL callback in the reference
+    const hs_gpu_match_t *m = s->h_matches;
+    for (u64 i = 0; i < s->n_matches; i++) {
+        void *ctx = contexts ? contexts[m[i].buffer] : context;
+        if (onEvent(m[i].id, 0, m[i].to, 0, ctx)) return HS_SCAN_TERMINATED;
+    }
+    return HS_SUCCESS;
+}
+
+hs_error_t hs_gpu_scan_batch(const hs_database_t *db, const char *const *data, const unsigned int *length,
+                             unsigned int count, unsigned int flags, hs_gpu_scratch_t *scratch,
+                             match_event_handler onEvent, void *const *contexts) {
+    (void)flags;
+    if (!scratch || !data || !length) return HS_INVALID;
+    hs_error_t rv = validate_scan_args(db, scratch);
+    if (rv != HS_SUCCESS) return rv;
+    InUseGuard g(scratch);
+    if (!g.ok) return HS_SCRATCH_IN_USE;
+    DbImage *im = nullptr;
+    rv = scan_host_batch(db, data, length, count, scratch, &im);
+    if (rv != HS_SUCCESS) return rv;
+    return deliver(scratch, onEvent, nullptr, contexts);
+}
+
+hs_error_t hs_gpu_scan_vector(const hs_database_t *db, const char *const *data, const unsigned int *length,
+                              unsigned int count, unsigned int flags, hs_gpu_scratch_t *scratch,
+                              match_event_handler onEvent, void *context) {
+    (void)flags;
+    if (!scratch || !data || !length) return HS_INVALID;
+    hs_error_t rv = validate_scan_args(db, scratch);
+    if (rv != HS_SUCCESS) return rv;
+    InUseGuard g(scratch);
+    if (!g.ok) return HS_SCRATCH_IN_USE;
+    DbImage *im = nullptr;
+    rv = scan_host_batch(db, data, length, count, scratch, &im);
+    if (rv != HS_SUCCESS) return rv;
+    return deliver(scratch, onEvent, context, nullptr);
+}
+
+hs_error_t hs_gpu_scan_vector_ex(const hs_database_t *db, const char *const *data, const unsigned int *length,
+                                 unsigned int count, unsigned int flags, hs_gpu_scratch_t *scratch,
+                                 const hs_gpu_match_t **matches, uint64_t *n_matches) {
+    (void)flags;
+    if (!scratch || !data || !length || !matches || !n_matches) return HS_INVALID;
+    hs_error_t rv = validate_scan_args(db, scratch);
+    if (rv != HS_SUCCESS) return rv;
+    InUseGuard g(scratch);
+    if (!g.ok) return HS_SCRATCH_IN_USE;
+    DbImage *im = nullptr;
+    rv = scan_host_batch(db, data, length, count, scratch, &im);
+    if (rv != HS_SUCCESS) return rv;
+    *matches = scratch->h_matches;
+    *n_matches = scratch->n_matches;
+    return HS_SUCCESS;
+}
+
+hs_error_t hs_gpu_scan(const hs_database_t *db, const char *data, unsigned int length, unsigned int flags,
+                       hs_gpu_scratch_t *scratch, match_event_handler onEvent, void *context) {
+    if (!scratch || !data) return HS_INVALID;
+    const char *one[1] = {data};
+    unsigned int len[1] = {length};
+    return hs_gpu_scan_vector(db, one, len, 1, flags, scratch, onEvent, context);
+}
+
+hs_error_t hs_gpu_corpus_create(const char *flat, const uint64_t *offsets, unsigned int count, hs_gpu_corpus_t **out) {
+    if (!offsets || !out || !count || offsets[0] != 0) return HS_INVALID;
+    for (unsigned i = 0; i < count; i++) {
+        if (offsets[i + 1] < offsets[i] || offsets[i + 1] - offsets[i] > 0xffffffffull) return HS_INVALID;
+    }
+    const u64 total = offsets[count];
+    if (total && !flat) return HS_INVALID;
+    if (hs_gpu_device_count() <= 0) return HS_ARCH_ERROR;
+    hs_gpu_corpus *c = new (std::nothrow) hs_gpu_corpus();
+    if (!c) return HS_NOMEM;
+    cudaGetDevice(&c->device);
+    c->total = total;
+    c->count = count;
+    std::vector<u32> sf;
+    build_strip_first(offsets, count, total, sf, c->nstrips);
+    if (c->text.reserve(FRONT_PAD + total + BACK_PAD) != cudaSuccess || c->off.reserve((size_t)count + 1) != cudaSuccess ||
+        c->strip_first.reserve(sf.size()) != cudaSuccess) {
+        hs_gpu_corpus_free(c);
+        return HS_NOMEM;
+    }
+    cudaMemset(c->text.p, 0, FRONT_PAD);
+    cudaMemset(c->text.p + FRONT_PAD + total, 0, BACK_PAD);
+    if (total) cudaMemcpy(c->text.p + FRONT_PAD, flat, total, cudaMemcpyHostToDevice);
+    cudaMemcpy(c->off.p, offsets, ((size_t)count + 1) * 8, cudaMemcpyHostToDevice);
+    cudaMemcpy(c->strip_first.p, sf.data(), sf.size() * 4, cudaMemcpyHostToDevice);
+    if (cudaDeviceSynchronize() != cudaSuccess) { hs_gpu_corpus_free(c); return HS_UNKNOWN_ERROR; }
+    *out = c;
+    return HS_SUCCESS;
+}
+
+hs_error_t hs_gpu_corpus_free(hs_gpu_corpus_t *c) {
+    if (!c) return HS_SUCCESS;
+    if (c->magic != 0x43525053) return HS_INVALID;
+    c->text.release();
+    c->off.release();
+    c->strip_first.release();
+    c->magic = 0;
+    delete c;
+    return HS_SUCCESS;
+}
+
+hs_error_t hs_gpu_scan_corpus(const hs_database_t *db, const hs_gpu_corpus_t *corpus, hs_gpu_scratch_t *scratch,
+                              uint64_t *n_matches) {
+    if (!corpus || corpus->magic != 0x43525053) return HS_INVALID;
+    hs_error_t rv = validate_scan_args(db, scratch);
+    if (rv != HS_SUCCESS) return rv;
+    InUseGuard g(scratch);
+    if (!g.ok) return HS_SCRATCH_IN_USE;
+    if ((rv = ensure_device(scratch)) != HS_SUCCESS) return rv;
+    DbImage *im = nullptr;
+    if ((rv = upload_database(scratch, db, &im)) != HS_SUCCESS) return rv;
+    scratch->stats.h2d_ms = 0;
+    scratch->stats.d2h_ms = 0;
+    rv = scan_device(scratch, im, *corpus);
+    if (rv != HS_SUCCESS) return rv;
+    if (n_matches) *n_matches = scratch->n_matches;
+    return HS_SUCCESS;
+}
+
+hs_error_t hs_gpu_fetch_matches(hs_gpu_scratch_t *scratch, const hs_gpu_match_t **matches, uint64_t *n_matches) {
+    if (!scratch || scratch->magic != 0x47505553 || !matches || !n_matches) return HS_INVALID;
+    InUseGuard g(scratch);
+    if (!g.ok) return HS_SCRATCH_IN_USE;
+    hs_error_t rv = fetch_matches(scratch, static_cast<DbImage *>(scratch->last_image));
+    if (rv != HS_SUCCESS) return rv;
+    *matches = scratch->h_matches;
+    *n_matches = scratch->n_matches;
+    return HS_SUCCESS;
+}
+
+hs_error_t hs_gpu_last_stats(const hs_gpu_scratch_t *scratch, hs_gpu_stats_t *stats) {
+    if (!scratch || scratch->magic != 0x47505553 || !stats) return HS_INVALID;
+    *stats = scratch->stats;
+    return HS_SUCCESS;
+}
+
+hs_error_t hs_gpu_set_option(hs_gpu_scratch_t *scratch, const char *name, long value) {
+    if (!scratch || scratch->magic != 0x47505553 || !name) return HS_INVALID;
+    if (!strcmp(name, "frontend")) { scratch->opt_frontend = value; return HS_SUCCESS; }
+    if (!strcmp(name, "grid")) { scratch->opt_grid = value; return HS_SUCCESS; }
+    if (!strcmp(name, "arena")) { scratch->arena_hint = value > 0 ? (u64)value : 1; return HS_SUCCESS; }
+    return HS_INVALID;
+}
+
+}  // extern "C"

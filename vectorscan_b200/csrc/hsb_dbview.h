@@ -1,0 +1,215 @@
+// hsb_dbview.h -- host-side reader of a block-mode hs_database_t: header checks with the reference's
+// error codes (src/runtime.c:316-340, src/database.c:330-364), location of the literal matcher and its
+// confirm structures, and the ENGINE / OPCODE CENSUS that refuses (HS_ARCH_ERROR, never a fallback) any
+// database using something the device path does not implement.
+#pragma once
+#include "hsb_layout.h"
+
+#include <set>
+#include <string>
+#include <vector>
+
+namespace hsb {
+
+constexpr int E_SUCCESS = 0, E_INVALID = -1, E_NOMEM = -2, E_DB_VERSION = -5, E_DB_PLATFORM = -6,
+              E_DB_MODE = -7, E_BAD_ALIGN = -8, E_ARCH = -11, E_UNKNOWN = -13;
+
+enum EngineKind : u32 { ENG_FDR = 0, ENG_TEDDY = 1, ENG_NOODLE = 2 };
+
+struct LitRec {  // one LitInfo, flattened
+    u64 v, msk, groups;
+    u32 program;  // Rose program offset (LitInfo.id)
+    u8 size, flags, bucket;
+};
+
+struct DbView {
+    const u8 *bc = nullptr;  // bytecode (RoseEngine) base inside the caller's database
+    u32 bc_len = 0, crc = 0;
+    u32 min_width = 0, min_width_excl = 0, max_bi_width = 0;
+    u32 ekey_count = 0, dkey_count = 0;
+    u64 groups = 0;  // initialGroups & floating_group_mask
+    u32 hwlm_off = 0, eng_off = 0;
+    EngineKind kind = ENG_FDR;
+    u32 engine_id = 0, n_buckets = 8, max_string_len = 0, n_strings = 0;
+    u32 conf_base = 0;  // absolute offset of u32 confBase[n_buckets]
+    // FDR
+    u32 fdr_tab = 0, fdr_domain = 0, fdr_stride = 0;
+    u64 fdr_start = 0;
+    // Teddy
+    u32 teddy_masks = 0, teddy_mask_off = 0;
+    // noodle
+    u64 nood_msk = 0, nood_cmp = 0;
+    u32 nood_len = 0, nood_id = 0;
+    std::vector<LitRec> lits;  // every literal of every bucket (empty for noodle)
+    std::vector<u32> programs; // distinct program offsets reachable from the literal matcher
+    u32 max_lit_len = 0;       // longest CHECK_*_LIT length seen (bounds look-behind)
+};
+
+inline bool in_range(const DbView &d, size_t off, size_t n) { return off <= d.bc_len && n <= d.bc_len - off; }
+
+// Walk one Rose program; collect opcodes; follow nothing outside it (INCLUDED_JUMP children are
+// programs of other literals and are walked on their own).
+inline int census_program(const DbView &d, u32 prog, std::string &why, u32 &max_lit_len) {
+    size_t pc = prog;
+    for (int guard = 0; guard < 4096; guard++) {
+        if (!in_range(d, pc, 8)) { why = "program runs past the bytecode"; return E_INVALID; }
+        const u8 code = rd8(d.bc, pc);
+        size_t sz = 0;
+        switch (code) {
+        case op::END: return E_SUCCESS;
+        case op::CHECK_GROUPS: sz = op::check_groups::SIZE; break;
+        case op::CHECK_MASK: sz = op::check_mask::SIZE; break;
+        case op::CHECK_BYTE: sz = op::check_byte::SIZE; break;
+        case op::CATCH_UP: case op::CLEAR_WORK_DONE: sz = op::SIZE_1; break;
+        case op::DEDUPE: sz = op::dedupe::SIZE; break;
+        case op::REPORT: sz = op::report::SIZE; break;
+        case op::FINAL_REPORT: return E_SUCCESS;  // always terminates the program
+        case op::REPORT_EXHAUST: sz = op::report_exhaust::SIZE; break;
+        case op::DEDUPE_AND_REPORT: sz = op::dedupe_and_report::SIZE; break;
+        case op::CHECK_EXHAUSTED: sz = op::check_exhausted::SIZE; break;
+        case op::SQUASH_GROUPS: sz = op::squash_groups::SIZE; break;
+        case op::SET_EXHAUST: sz = op::set_exhaust::SIZE; break;
+        case op::INCLUDED_JUMP: sz = op::included_jump::SIZE; break;
+        case op::CHECK_LONG_LIT: case op::CHECK_LONG_LIT_NOCASE:
+        case op::CHECK_MED_LIT: case op::CHECK_MED_LIT_NOCASE: {
+            sz = op::check_lit::SIZE;
+            u32 lo = rd32(d.bc, pc + op::check_lit::lit_offset), ll = rd32(d.bc, pc + op::check_lit::lit_length);
+            if (!in_range(d, lo, ll)) { why = "literal text outside the bytecode"; return E_INVALID; }
+            if (ll > max_lit_len) max_lit_len = ll;
+            break;
+        }
+        default:
+            why = "Rose opcode " + std::to_string((int)code) + " is not implemented on the device path";
+            return E_ARCH;
+        }
+        pc += sz;
+    }
+    why = "program too long";
+    return E_INVALID;
+}
+
+// `db` is the caller's in-memory hs_database_t.
+inline int parse_database(const void *db, DbView &d, std::string &why) {
+    if (!db) return E_INVALID;
+    if (rd32(db, db::magic) != db::MAGIC) { why = "bad magic"; return E_INVALID; }
+    if (rd32(db, db::version) != db::VERSION_5_4_11) { why = "database version mismatch"; return E_DB_VERSION; }
+    const u32 bc_off = rd32(db, db::bytecode);
+    d.bc = reinterpret_cast<const u8 *>(db) + bc_off;
+    d.bc_len = rd32(db, db::length);
+    d.crc = rd32(db, db::crc32);
+    if ((reinterpret_cast<uintptr_t>(d.bc) & 15) != 0) { why = "bytecode not 16-byte aligned"; return E_INVALID; }
+    if (d.bc_len < rose::SIZE) { why = "bytecode too short"; return E_INVALID; }
+    const u8 *r = d.bc;
+    if (rd32(r, rose::mode) != MODE_BLOCK) { why = "not a block-mode database"; return E_DB_MODE; }
+    if (rd32(r, rose::size) > d.bc_len) { why = "engine size exceeds database length"; return E_INVALID; }
+    if (rd8(r, rose::hasSom)) { why = "start-of-match databases are not supported"; return E_ARCH; }
+    if (rd32(r, rose::ckeyCount) || rd32(r, rose::lkeyCount)) { why = "logical combinations are not supported"; return E_ARCH; }
+    const u8 impl = rd8(r, rose::runtimeImpl);
+    if (impl != rose::RUNTIME_PURE_LITERAL) {
+        why = impl == rose::RUNTIME_FULL_ROSE ? "full-Rose databases (NFA/DFA engines) are not supported yet"
+                                              : "single-outfix databases are not supported yet";
+        return E_ARCH;
+    }
+    const u8 *bd = r + rose::boundary;
+    if (rd32(bd, rose::bd::reportEodOffset) || rd32(bd, rose::bd::reportZeroOffset) ||
+        rd32(bd, rose::bd::reportZeroEodOffset)) {
+        why = "boundary (vacuous-pattern) report programs are not supported yet";
+        return E_ARCH;
+    }
+    d.min_width = rd32(r, rose::minWidth);
+    d.min_width_excl = rd32(r, rose::minWidthExcludingBoundaries);
+    d.max_bi_width = rd32(r, rose::maxBiAnchoredWidth);
+    d.ekey_count = rd32(r, rose::ekeyCount);
+    d.dkey_count = rd32(r, rose::dkeyCount);
+    d.groups = rd64(r, rose::initialGroups) & rd64(r, rose::floating_group_mask);
+    d.hwlm_off = rd32(r, rose::fmatcherOffset);
+    if (!d.hwlm_off || !in_range(d, d.hwlm_off, hwlm::BODY + 24)) { why = "no floating literal matcher"; return E_INVALID; }
+    const u8 type = rd8(r, d.hwlm_off + hwlm::type);
+    d.eng_off = d.hwlm_off + (u32)hwlm::BODY;
+    std::set<u32> progs;
+    if (type == hwlm::ENGINE_NOOD) {
+        if (!in_range(d, d.eng_off, nood::SIZE)) { why = "noodle table truncated"; return E_INVALID; }
+        d.kind = ENG_NOODLE;
+        d.nood_id = rd32(r, d.eng_off + nood::id);
+        d.nood_msk = rd64(r, d.eng_off + nood::msk);
+        d.nood_cmp = rd64(r, d.eng_off + nood::cmp);
+        d.nood_len = rd8(r, d.eng_off + nood::msk_len);
+        if (d.nood_len < 1 || d.nood_len > 8) { why = "noodle mask length out of range"; return E_INVALID; }
+        d.max_string_len = d.nood_len;
+        d.n_strings = 1;
+        progs.insert(d.nood_id);
+    } else if (type == hwlm::ENGINE_FDR) {
+        const u8 *e = r + d.eng_off;
+        d.engine_id = rd32(e, fdr::engineID);
+        const u32 esize = rd32(e, fdr::size);
+        if (!in_range(d, d.eng_off, esize) || esize < fdr::TABLE) { why = "literal matcher truncated"; return E_INVALID; }
+        d.max_string_len = rd32(e, fdr::maxStringLen);
+        d.n_strings = rd32(e, fdr::numStrings);
+        d.conf_base = d.eng_off + rd32(e, fdr::confOffset);
+        if (d.engine_id == 0) {
+            d.kind = ENG_FDR;
+            d.fdr_stride = rd8(e, fdr::stride);
+            d.fdr_domain = rd8(e, fdr::domain);
+            d.fdr_tab = d.eng_off + (u32)fdr::TABLE;
+            d.fdr_start = rd64(e, fdr::start);
+            if (d.fdr_domain < 9 || d.fdr_domain > 15 || (d.fdr_stride != 1 && d.fdr_stride != 2 && d.fdr_stride != 4) ||
+                rd32(e, fdr::tabSize) != (8u << d.fdr_domain) || !in_range(d, d.fdr_tab, (size_t)8 << d.fdr_domain)) {
+                why = "malformed FDR header";
+                return E_INVALID;
+            }
+        } else if (d.engine_id >= teddy::ENGINE_FIRST && d.engine_id <= teddy::ENGINE_LAST) {
+            d.kind = ENG_TEDDY;
+            d.teddy_masks = (d.engine_id - teddy::ENGINE_FIRST) / 2 + 1;
+            d.teddy_mask_off = d.eng_off + (u32)teddy::MASKS;
+            if (!in_range(d, d.teddy_mask_off, (size_t)d.teddy_masks * 32)) { why = "Teddy masks truncated"; return E_INVALID; }
+        } else if (d.engine_id >= teddy::FAT_FIRST && d.engine_id <= teddy::FAT_LAST) {
+            why = "16-bucket (AVX2 fat) Teddy tables are not supported; compile for a generic platform";
+            return E_ARCH;
+        } else {
+            why = "unknown literal matcher engine id";
+            return E_INVALID;
+        }
+        if (!in_range(d, d.conf_base, d.n_buckets * 4)) { why = "confirm base outside bytecode"; return E_INVALID; }
+        for (u32 b = 0; b < d.n_buckets; b++) {
+            const u32 cf = rd32(r, d.conf_base + 4 * b);
+            if (!cf) continue;
+            const size_t fc = (size_t)d.conf_base + cf;
+            if (!in_range(d, fc, conf::SIZE)) { why = "FDRConfirm outside bytecode"; return E_INVALID; }
+            const u32 nbits = rd32(r, fc + conf::nBits);
+            if (nbits > 24 || !in_range(d, fc + conf::SIZE, (size_t)4 << nbits)) { why = "confirm index outside bytecode"; return E_INVALID; }
+            for (u32 h = 0; h < (1u << nbits); h++) {
+                u32 start = rd32(r, fc + conf::SIZE + 4 * (size_t)h);
+                if (!start) continue;
+                size_t li = fc + start;
+                for (;;) {
+                    if (!in_range(d, li, lit::SIZE)) { why = "LitInfo outside bytecode"; return E_INVALID; }
+                    LitRec lr;
+                    lr.v = rd64(r, li + lit::v);
+                    lr.msk = rd64(r, li + lit::msk);
+                    lr.groups = rd64(r, li + lit::groups);
+                    lr.program = rd32(r, li + lit::id);
+                    lr.size = rd8(r, li + lit::size);
+                    lr.flags = rd8(r, li + lit::flags);
+                    lr.bucket = (u8)b;
+                    d.lits.push_back(lr);
+                    progs.insert(lr.program);
+                    if (!rd8(r, li + lit::next)) break;
+                    li += lit::SIZE;
+                }
+            }
+        }
+    } else {
+        why = "unknown HWLM engine type";
+        return E_INVALID;
+    }
+    d.max_lit_len = 8;
+    for (u32 p : progs) {
+        if (p < rose::SIZE || !in_range(d, p, 8)) { why = "literal program offset outside bytecode"; return E_INVALID; }
+        int rv = census_program(d, p, why, d.max_lit_len);
+        if (rv != E_SUCCESS) return rv;
+        d.programs.push_back(p);
+    }
+    return E_SUCCESS;
+}
+
+}  // namespace hsb
