@@ -1,0 +1,314 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark: block-mode literal-set scanning throughput (GB/s, Mmatches/s).
+
+  python bench.py --gpus N --steps K --warmup W [--config c2|c1] [--impl reference]
+
+A "step" is one pass of the hot path over one batch of synthetic input.  Default workload (BASELINE.json
+configs[1]): 10 000 literals (FDR) over a 64 MiB batch of 1500-byte packets, scanned as independent block
+scans (hs_scan_vector shape).  Per rank, ROT batches (> L2 in total) are kept resident in HBM and scanned
+in rotation so no step finds its input in L2.
+
+  value        bytes scanned by all ranks / max-over-ranks device time, CUDA events around every step's
+               device work (front end + confirm + Rose programs + arena + sort/dedupe), inputs resident in HBM
+  e2e          the same metric through the reference-facing call hs_gpu_scan_vector_ex() with HOST buffers
+               (pinned), wall clock around the call: H2D of the batch, scan, D2H of the sorted matches
+  roofline     dominant kernel k_scan: algorithmic bytes per launch / its CUDA-event time, vs MEASURED_PEAKS hbm
+  cpu_baseline the unmodified reference runtime (oracle/_ref) on host cores, bounded sample
+  --impl reference   the same workload on the reference's CPU hs_scan with all host threads
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import numpy as np  # noqa: E402
+
+from vectorscan_b200 import litdb, workloads as W  # noqa: E402
+
+ROT = 4  # resident batches per rank: 4 x 64 MiB = 256 MiB > 126 MB of L2
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def make_workload(config, rank, nbytes):
+    if config == "c1":
+        lits, flags, ids = W.c1_patterns()
+        batches = []
+        for r in range(ROT):
+            t = W.c1_text(nbytes, lits, seed=20260101 + 100 * rank + r)
+            batches.append((t, np.array([0, len(t)], dtype=np.uint64)))
+        name = f"c1: 1000 literals (len 4-16, a-z, 20% caseless) over one {nbytes >> 20} MiB text buffer per step"
+    else:
+        lits, flags, ids = W.c2_patterns()
+        batches = [W.c2_batch(nbytes, lits, seed=20260102 + 100 * rank + r) for r in range(ROT)]
+        name = f"c2: 10000 literals (len 3-12, printable) over a {nbytes >> 20} MiB batch of 1500-byte packets per step"
+    return lits, flags, ids, batches, name
+
+
+class ClockSampler:
+    def __init__(self, dev):
+        self.dev, self.samples, self.reasons, self.maxmhz = dev, [], set(), None
+        self._stop = threading.Event()
+        self._t = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.dev), f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip().split(",")
+                self.samples.append(float(out[0]))
+                self.maxmhz = float(out[1])
+                for n, v in zip(names, out[2:]):
+                    if v.strip().lower().startswith("active"):
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def start(self):
+        self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        self._t.join(timeout=6)
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.maxmhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def cpu_reference_run(ser, flat, off, threads, repeats, budget_bytes=None):
+    """Times the unmodified reference runtime over (a prefix of) the batch; returns (GB/s, Mmatch/s, desc)."""
+    import refrt
+    isa = refrt.pick_isa()
+    lib = os.path.join(ROOT, "oracle", "_ref", f"libhs_ref_{isa}.so")
+    bl = C.CDLL(os.path.join(ROOT, "oracle", "liboracle_bench.so"))
+    bl.cpu_bench_run.restype = C.c_double
+    bl.cpu_bench_run.argtypes = [C.c_char_p, C.c_char_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int,
+                                 C.c_int, C.POINTER(C.c_uint64)]
+    count = len(off) - 1
+    if budget_bytes is not None and int(off[-1]) > budget_bytes:
+        count = max(1, int(np.searchsorted(off, budget_bytes, side="right")) - 1)
+    nbytes = int(off[count])
+    m = C.c_uint64()
+    secs = bl.cpu_bench_run(lib.encode(), ser, len(ser), flat.ctypes.data, off.ctypes.data, count, threads, repeats,
+                            C.byref(m))
+    if secs <= 0:
+        raise RuntimeError(f"cpu_bench_run failed: {secs}")
+    gbs = nbytes * repeats / secs / 1e9
+    return gbs, m.value / secs / 1e6, secs, nbytes, isa
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's own CPU hs_scan loop on all host threads (rank 0 only)."""
+    if rank != 0:
+        return
+    nbytes = args.bytes
+    lits, flags, ids, batches, name = make_workload(args.config, 0, nbytes)
+    ser = litdb.compile_lit_multi(lits, flags, ids).serialize()
+    threads = os.cpu_count() or 1
+    # bounded sample per step so that the whole run ends within minutes
+    sample = min(nbytes, args.ref_sample_bytes)
+    for w in range(args.warmup):
+        cpu_reference_run(ser, batches[w % ROT][0], batches[w % ROT][1], threads, 1, sample)
+    tot_s, tot_b, tot_m = 0.0, 0, 0
+    for k in range(args.steps):
+        flat, off = batches[k % ROT]
+        gbs, mms, secs, nb, isa = cpu_reference_run(ser, flat, off, threads, 1, sample)
+        tot_s += secs
+        tot_b += nb
+        tot_m += mms * secs
+    value = tot_b / tot_s / 1e9
+    line = {
+        "impl": "reference", "metric": "scan throughput", "value": round(value, 4), "unit": "GB/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * tot_s / args.steps, 3),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "mmatches_per_s": round(tot_m / tot_s, 4),
+        "config": {"workload": name, "l2": "inputs larger than L2 (rotation)"},
+        "cpu_baseline": {"value": round(value, 4), "unit": "GB/s", "cores": threads, "kind": "reference",
+                         "sample": f"first {sample >> 20} MiB of each step's batch, hs_scan per buffer, {isa} build, "
+                                   f"{threads} pinned threads"},
+        "e2e": {"value": round(value, 4), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--config", default="c2", choices=["c1", "c2"])
+    ap.add_argument("--bytes", type=int, default=64 << 20)
+    ap.add_argument("--ref-sample-bytes", type=int, default=64 << 20)
+    ap.add_argument("--cpu-sample-bytes", type=int, default=64 << 20)
+    ap.add_argument("--frontend", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from vectorscan_b200 import gpu
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the scanning runtime has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    gpu.lib().hs_gpu_set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    nbytes = args.bytes
+    lits, flags, ids, batches, name = make_workload(args.config, rank, nbytes)
+    db = litdb.compile_lit_multi(lits, flags, ids)
+    sc = gpu.alloc_scratch(db)
+    if args.frontend:
+        sc.set_option("frontend", args.frontend)
+    corpora = [gpu.Corpus(flat, off) for flat, off in batches]
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput ("value") -------------------------------------------------------
+    for w in range(max(args.warmup, 3)):
+        gpu.scan_corpus(db, corpora[w % ROT], sc)
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    dev_ms = kern_ms = 0.0
+    nmatch = raw = launches = nbytes_scanned = 0
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        c = corpora[k % ROT]
+        nmatch += gpu.scan_corpus(db, c, sc)
+        st = sc.stats()
+        dev_ms += st["scan_ms"] + st["sort_ms"]
+        kern_ms += st["kernel_ms"]
+        raw += st["raw_matches"]
+        launches += st["kernel_launches"]
+        nbytes_scanned += c.total
+    barrier()
+    wall_s = time.perf_counter() - t0
+    clocks = sampler.stop()
+
+    # the only collective of the path: match counts (+ per-pattern histogram) over NCCL
+    hist = torch.zeros(len(lits), dtype=torch.int64, device="cuda")
+    gpu.lib().hs_gpu_histogram(sc.ptr, C.c_void_p(hist.data_ptr()), len(lits))
+    agg = torch.tensor([dev_ms, float(nbytes_scanned), float(nmatch), kern_ms, wall_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        mx = agg.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(agg, op=dist.ReduceOp.SUM)
+        dist.all_reduce(hist, op=dist.ReduceOp.SUM)
+        max_dev_ms, max_wall = float(mx[0]), float(mx[4])
+    else:
+        max_dev_ms, max_wall = dev_ms, wall_s
+    tot_bytes, tot_matches = float(agg[1]), float(agg[2])
+    value = tot_bytes / (max_dev_ms * 1e-3) / 1e9
+
+    # ---- end to end through the C ABI with host buffers -----------------------------------------------
+    L = gpu.lib()
+    flat0, off0 = batches[0]
+    hp = L.hs_gpu_host_alloc(int(flat0.nbytes))
+    C.memmove(hp, flat0.ctypes.data, flat0.nbytes)
+    count0 = len(off0) - 1
+    ptrs = (C.c_char_p * count0)()
+    base = hp
+    ptr_arr = (np.uint64(base) + off0[:-1]).astype(np.uint64)
+    C.memmove(ptrs, ptr_arr.ctypes.data, count0 * 8)
+    lens = (C.c_uint * count0)(*np.diff(off0).astype(np.uint32).tolist())
+    mp, cnt = C.POINTER(gpu.Match)(), C.c_uint64()
+
+    def e2e_once():
+        rv = L.hs_gpu_scan_vector_ex(db.ptr, ptrs, lens, count0, 0, sc.ptr, C.byref(mp), C.byref(cnt))
+        if rv != 0:
+            raise RuntimeError(f"hs_gpu_scan_vector_ex -> {rv}")
+        return cnt.value
+
+    for _ in range(3):
+        e2e_once()
+    barrier()
+    e2e_steps = max(3, min(args.steps, 20))
+    t0 = time.perf_counter()
+    e2e_matches = 0
+    for _ in range(e2e_steps):
+        e2e_matches += e2e_once()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    e2e_value = world * e2e_steps * float(flat0.nbytes) / float(e2e_t[0]) / 1e9
+    d2h_per_step = int(e2e_matches / e2e_steps) * 16
+    L.hs_gpu_host_free(hp)
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        n_launch = args.steps
+        alg_bytes = (nbytes_scanned + 16 * raw + 12 * sum(c.count for c in corpora) * (args.steps / ROT)) / n_launch
+        achieved = alg_bytes / (kern_ms / n_launch * 1e-3) / 1e9
+        line = {
+            "metric": "scan throughput", "value": round(value, 2), "unit": "GB/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": round(max_dev_ms / args.steps, 4), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "mmatches_per_s": round(tot_matches / (max_dev_ms * 1e-3) / 1e6, 2),
+            "matches_per_step": int(tot_matches / args.steps / world),
+            "wall_ms_per_step": round(1e3 * max_wall / args.steps, 4),
+            "config": {"workload": name, "l2": f"inputs larger than L2: {ROT} resident batches scanned in rotation",
+                       "frontend": args.frontend, "hist_nonzero_ids": int((hist > 0).sum())},
+            "clocks": clocks,
+            "e2e": {"value": round(e2e_value, 3), "unit": "GB/s", "h2d_bytes_per_step": int(flat0.nbytes + off0.nbytes),
+                    "d2h_bytes_per_step": d2h_per_step, "steps": e2e_steps,
+                    "call": "hs_gpu_scan_vector_ex(host pinned buffers)"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "k_scan", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
+                         "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                         "alg_bytes_per_launch": int(alg_bytes), "kernel_ms": round(kern_ms / n_launch, 4)},
+        }
+        if not args.no_cpu_baseline:
+            try:
+                ser = db.serialize()
+                g1, m1, s1, nb1, isa = cpu_reference_run(ser, flat0, off0, 1, 1, args.cpu_sample_bytes)
+                threads = os.cpu_count() or 1
+                gN, mN, sN, nbN, _ = cpu_reference_run(ser, flat0, off0, threads, 4, args.cpu_sample_bytes)
+                line["cpu_baseline"] = {"value": round(gN, 4), "unit": "GB/s", "cores": threads, "kind": "reference",
+                                        "single_core_value": round(g1, 4),
+                                        "sample": f"{nb1 >> 20} MiB of the step's batch, unmodified reference hs_scan per "
+                                                  f"buffer ({isa} build): 1 pass on 1 thread, 4 passes on {threads} threads"}
+            except Exception as e:  # the oracle is test infrastructure: report, do not fail the bench
+                line["cpu_baseline"] = {"value": None, "unit": "GB/s", "cores": 0, "kind": "reference", "sample": f"failed: {e}"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

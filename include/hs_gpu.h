@@ -64,8 +64,10 @@ typedef struct hs_gpu_stats {
     float scan_ms;         /* front end + confirm + program + arena write */
     float sort_ms;         /* device sort / compaction of the arena */
     float d2h_ms;          /* device->host copy of the matches */
-    uint32_t scan_launches; /* kernels of this library launched by the call */
+    uint32_t scan_launches; /* k_scan launches (1 + arena_retries) */
     uint32_t arena_retries; /* re-runs forced by match arena growth */
+    float kernel_ms;        /* the (last) k_scan launch alone, CUDA events tight around it */
+    uint32_t kernel_launches; /* kernels of this library launched by the call (CUB's are not counted) */
 } hs_gpu_stats_t;
 
 /* hs_alloc_scratch(db, &scratch)                       src/hs_runtime.h:555-556, src/scratch.c:244-389
@@ -112,6 +114,10 @@ hs_error_t hs_gpu_scan_corpus(const hs_database_t *db, const hs_gpu_corpus_t *co
 hs_error_t hs_gpu_fetch_matches(hs_gpu_scratch_t *scratch, const hs_gpu_match_t **matches, uint64_t *n_matches);
 
 hs_error_t hs_gpu_last_stats(const hs_gpu_scratch_t *scratch, hs_gpu_stats_t *stats);
+/* Adds, for every match of the last device scan, 1 to device_hist_u64[id] (ids >= n_ids are skipped).
+ * device_hist_u64 is a DEVICE pointer to n_ids uint64 counters owned by the caller -- the vector the
+ * multi-GPU driver all-reduces over NCCL. */
+hs_error_t hs_gpu_histogram(hs_gpu_scratch_t *scratch, void *device_hist_u64, uint32_t n_ids);
 
 /* Host memory the library can DMA from without a staging copy (cudaHostAlloc). */
 void *hs_gpu_host_alloc(size_t bytes);

@@ -1,2 +1,309 @@
-/* placeholder, replaced below */
-int oracle_port_placeholder(void) { return 0; }
+/* oracle/oracle_port.c -- TEST INFRASTRUCTURE ONLY.  Never imported, linked or executed by the product
+ * path (vectorscan_b200/): only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may use it.
+ *
+ * Plain-C, sequential restatement of the reference's block-mode pure-literal scan path over the reference's
+ * own bytecode.  PARITY PINNED: tests/test_oracle.py checks it against (a) the known-answer vectors of the
+ * reference's unit tests (tests/golden/ref_unit_vectors.json, transcribed from unit/internal/fdr.cpp) and
+ * (b) outputs of the unmodified reference runtime compiled from /root/reference (oracle/_ref) on seeded
+ * random databases/inputs (tests/golden/ref_runtime_cases.json and live comparison where _ref exists).
+ *
+ * Each function cites the reference code it follows (paths under /root/reference/src):
+ *   op_scan            hs_scan                      runtime.c:316-475  (gates, engine switch)
+ *   hwlm_exec          hwlmExec / fdrExec           hwlm/hwlm.c:178-205, fdr/fdr.c:801-825
+ *   fdr_candidates     get_conf_stride_{1,2,4}      fdr/fdr.c:144-296 (+ getInitState :128-142, zones :624-659)
+ *   teddy_candidates   fdr_exec_teddy_msksN         fdr/teddy.c:920-1066
+ *   nood_match         noodExec / final             hwlm/noodle_engine.cpp:75-133
+ *   confirm            do_confirm_fdr / confWithBit fdr/fdr.c:298-333, fdr/fdr_confirm_runtime.h:43-102
+ *   run_program        roseCallback_i + roseRunProgram_l   rose/match.c:479-523, rose/program_runtime.c:3083-3504
+ *   report             dedupeCatchup / roseDeliverReport   report.h:54-117,300-340
+ * The walk is in increasing end offset, buckets low to high, chain order -- the order in which the reference
+ * invokes its callbacks when no flood/acceleration shortcut is taken (those are result-neutral).
+ */
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+typedef uint8_t u8;
+typedef uint16_t u16;
+typedef uint32_t u32;
+typedef uint64_t u64;
+
+/* ---- byte layout (same facts as vectorscan_b200/csrc/hsb_layout.h; pinned by tests/test_layout.py) ---- */
+enum {
+    DB_MAGIC_OFF = 0, DB_VERSION_OFF = 4, DB_LENGTH_OFF = 8, DB_BYTECODE_OFF = 36,
+    R_RUNTIME_IMPL = 4, R_HAS_SOM = 7, R_MODE = 12, R_EKEY_COUNT = 20, R_CKEY_COUNT = 32, R_DKEY_COUNT = 44,
+    R_FMATCHER = 96, R_MIN_WIDTH = 200, R_MIN_WIDTH_EXCL = 204, R_MAX_BI = 208, R_INIT_GROUPS = 240,
+    R_FLOAT_MASK = 248, R_SIZE = 256, R_BOUNDARY = 376,
+    HWLM_BODY = 192, F_ENGINE_ID = 0, F_CONF_OFF = 16, F_STRIDE = 24, F_DOMAIN = 25, F_DOMAIN_MASK = 26, F_START = 32,
+    F_TABLE = 64, C_ANDMSK = 0, C_MULT = 8, C_NBITS = 16, C_GROUPS = 24, C_SIZE = 32,
+    L_V = 0, L_MSK = 8, L_GROUPS = 16, L_ID = 24, L_SIZE = 28, L_FLAGS = 29, L_NEXT = 30, L_STRUCT = 32,
+    N_ID = 0, N_MSK = 8, N_CMP = 16, N_MSK_LEN = 24
+};
+enum { /* Rose opcodes, rose/rose_program.h:44-216 */
+    OP_END = 0, OP_CHECK_GROUPS = 3, OP_CHECK_MASK = 9, OP_CHECK_BYTE = 11, OP_CATCH_UP = 20, OP_DEDUPE = 28,
+    OP_REPORT = 33, OP_REPORT_EXHAUST = 34, OP_DEDUPE_AND_REPORT = 37, OP_FINAL_REPORT = 38, OP_CHECK_EXHAUSTED = 39,
+    OP_SQUASH_GROUPS = 43, OP_CHECK_LONG_LIT = 51, OP_CHECK_LONG_LIT_NOCASE = 52, OP_CHECK_MED_LIT = 53,
+    OP_CHECK_MED_LIT_NOCASE = 54, OP_CLEAR_WORK_DONE = 55, OP_INCLUDED_JUMP = 61, OP_SET_EXHAUST = 65
+};
+#define HS_SUCCESS 0
+#define HS_INVALID (-1)
+#define HS_SCAN_TERMINATED (-3)
+#define HS_DB_VERSION_ERROR (-5)
+#define HS_DB_MODE_ERROR (-7)
+#define HS_ARCH_ERROR (-11)
+#define HS_UNKNOWN_ERROR (-13)
+
+static u32 rd32(const u8 *p) { u32 v; memcpy(&v, p, 4); return v; }
+static u64 rd64(const u8 *p) { u64 v; memcpy(&v, p, 8); return v; }
+static u16 rd16(const u8 *p) { u16 v; memcpy(&v, p, 2); return v; }
+
+typedef int (*op_match_cb)(unsigned id, unsigned long long from, unsigned long long to, unsigned flags, void *ctx);
+
+struct scan_state {
+    const u8 *rose; const u8 *buf; u32 len;
+    u64 groups;
+    u8 *exhausted; u32 ekeys;          /* exhaustion vector (report.h:121-153) */
+    u8 *dedupe; u32 dkeys; u64 dedupe_offset; /* dedupe log for the current report offset */
+    op_match_cb cb; void *ctx;
+    int terminated, error;
+};
+
+/* roseDeliverReport + the dedupe test of dedupeCatchup for external reports without SOM */
+static int report(struct scan_state *s, u32 id, u64 to, u32 ekey, u32 dkey) {
+    if (dkey != 0xffffffffu) {
+        if (s->dedupe_offset != to) { memset(s->dedupe, 0, (s->dkeys + 7) / 8 + 1); s->dedupe_offset = to; }
+        if (s->dedupe[dkey >> 3] & (1u << (dkey & 7))) return 0; /* DEDUPE_SKIP */
+        s->dedupe[dkey >> 3] |= (u8)(1u << (dkey & 7));
+    }
+    if (s->cb && s->cb(id, 0, to, 0, s->ctx)) { s->terminated = 1; return -1; }
+    if (ekey != 0xffffffffu) s->exhausted[ekey >> 3] |= (u8)(1u << (ekey & 7));
+    return 1;
+}
+
+static u8 upc(u8 c) { return (c >= 'a' && c <= 'z') ? (u8)(c - 32) : c; }
+
+/* roseCheckMediumLiteral, rose/program_runtime.c:1954-2013 (block mode: no history) */
+static int check_lit(const struct scan_state *s, u32 lit_off, u32 lit_len, int nocase, u64 end) {
+    if (end < lit_len) return 0;
+    const u8 *t = s->buf + (end - lit_len), *l = s->rose + lit_off;
+    for (u32 i = 0; i < lit_len; i++)
+        if ((nocase ? upc(t[i]) : t[i]) != l[i]) return 0;
+    return 1;
+}
+
+/* roseCheckMask, rose/program_runtime.c:644-727 + validateMask, rose/validate_mask.h:80-104 */
+static int check_mask(const struct scan_state *s, u64 and_m, u64 cmp_m, u64 neg_m, int32_t off, u64 end) {
+    if (off < 0 && (u64)(-(int64_t)off) > end) return 0;
+    int64_t base = (int64_t)end + off;
+    for (int k = 0; k < 8; k++) {
+        int64_t o = base + k;
+        if (o < 0 || o >= (int64_t)s->len) continue;
+        u8 r = (u8)((s->buf[o] & (u8)(and_m >> (8 * k))) ^ (u8)(cmp_m >> (8 * k)));
+        if ((u8)(neg_m >> (8 * k)) ? r == 0 : r != 0) return 0;
+    }
+    return 1;
+}
+
+/* roseCheckByte, rose/program_runtime.c:600-641 */
+static int check_byte(const struct scan_state *s, u8 and_m, u8 cmp_m, u8 neg, int32_t off, u64 end) {
+    if (off < 0 && (u64)(-(int64_t)off) > end) return 0;
+    int64_t o = (int64_t)end + off;
+    if (o < 0 || o >= (int64_t)s->len) return 1;
+    int differ = (s->buf[o] & and_m) != cmp_m;
+    return !(differ ^ (neg != 0));
+}
+
+/* roseRunProgram_l.  `end` = offset one past the literal's last byte (lit_offset_adjust = 1).
+ * Returns 0 to continue, -1 to stop the scan. */
+static int run_program(struct scan_state *s, u32 prog, u64 end) {
+    const u8 *pc = s->rose + prog;
+    int work_done = 0;
+    for (;;) {
+        switch (pc[0]) {
+        case OP_END: return 0;
+        case OP_CHECK_GROUPS: if (!(rd64(pc + 8) & s->groups)) return 0; pc += 16; break;
+        case OP_CHECK_MASK:
+            if (!check_mask(s, rd64(pc + 8), rd64(pc + 16), rd64(pc + 24), (int32_t)rd32(pc + 32), end)) pc += rd32(pc + 36);
+            else pc += 40;
+            break;
+        case OP_CHECK_BYTE:
+            if (!check_byte(s, pc[1], pc[2], pc[3], (int32_t)rd32(pc + 4), end)) pc += rd32(pc + 8); else pc += 16;
+            break;
+        case OP_CATCH_UP: pc += 8; break; /* no engines in a pure-literal database */
+        case OP_CLEAR_WORK_DONE: work_done = 0; pc += 8; break;
+        case OP_CHECK_LONG_LIT: case OP_CHECK_MED_LIT: case OP_CHECK_LONG_LIT_NOCASE: case OP_CHECK_MED_LIT_NOCASE: {
+            int nocase = pc[0] == OP_CHECK_LONG_LIT_NOCASE || pc[0] == OP_CHECK_MED_LIT_NOCASE;
+            if (!check_lit(s, rd32(pc + 4), rd32(pc + 8), nocase, end)) pc += rd32(pc + 12); else pc += 16;
+            break;
+        }
+        case OP_CHECK_EXHAUSTED: {
+            u32 ek = rd32(pc + 4);
+            if (s->exhausted[ek >> 3] & (1u << (ek & 7))) pc += rd32(pc + 8); else pc += 16;
+            break;
+        }
+        case OP_DEDUPE: {
+            u32 dk = rd32(pc + 4);
+            u64 to = end + (int32_t)rd32(pc + 8);
+            if (s->dedupe_offset != to) { memset(s->dedupe, 0, (s->dkeys + 7) / 8 + 1); s->dedupe_offset = to; }
+            if (s->dedupe[dk >> 3] & (1u << (dk & 7))) pc += rd32(pc + 12);
+            else { s->dedupe[dk >> 3] |= (u8)(1u << (dk & 7)); pc += 16; }
+            break;
+        }
+        case OP_REPORT:
+            if (report(s, rd32(pc + 4), end + (int32_t)rd32(pc + 8), 0xffffffffu, 0xffffffffu) < 0) return -1;
+            work_done = 1; pc += 16; break;
+        case OP_FINAL_REPORT:
+            return report(s, rd32(pc + 4), end + (int32_t)rd32(pc + 8), 0xffffffffu, 0xffffffffu) < 0 ? -1 : 0;
+        case OP_REPORT_EXHAUST:
+            if (report(s, rd32(pc + 4), end + (int32_t)rd32(pc + 8), rd32(pc + 12), 0xffffffffu) < 0) return -1;
+            work_done = 1; pc += 16; break;
+        case OP_DEDUPE_AND_REPORT: {
+            int rv = report(s, rd32(pc + 8), end + (int32_t)rd32(pc + 12), 0xffffffffu, rd32(pc + 4));
+            if (rv < 0) return -1;
+            if (rv == 0) { pc += rd32(pc + 16); break; }
+            work_done = 1; pc += 24; break;
+        }
+        case OP_SET_EXHAUST: { u32 ek = rd32(pc + 4); s->exhausted[ek >> 3] |= (u8)(1u << (ek & 7)); work_done = 1; pc += 8; break; }
+        case OP_SQUASH_GROUPS: if (work_done) s->groups &= rd64(pc + 8); pc += 16; break;
+        case OP_INCLUDED_JUMP: pc += 8; break; /* scratch->fdr_conf == NULL fall-through: every bit is confirmed on its own */
+        default: s->error = 1; return -1;
+        }
+    }
+}
+
+/* do_confirm_fdr + confWithBit for one (end index i, bucket) pair */
+static int confirm(struct scan_state *s, const u8 *conf_base, u32 bucket, u32 i) {
+    u32 cf = rd32(conf_base + 4 * bucket);
+    if (!cf) return 0;
+    const u8 *fdrc = conf_base + cf;
+    if (!(rd64(fdrc + C_GROUPS) & s->groups)) return 0;
+    u64 v = 0; /* 8 bytes ending at i, zero before the buffer (block mode: fake zero history) */
+    for (int k = 0; k < 8; k++) { int64_t o = (int64_t)i - 7 + k; if (o >= 0) v |= (u64)s->buf[o] << (8 * k); }
+    u32 nbits = rd32(fdrc + C_NBITS);
+    u32 h = (u32)(((v & rd64(fdrc + C_ANDMSK)) * rd64(fdrc + C_MULT)) >> (64 - nbits));
+    u32 start = rd32(fdrc + C_SIZE + 4 * (size_t)h);
+    if (!start) return 0;
+    const u8 *li = fdrc + start;
+    for (;;) {
+        if ((v & rd64(li + L_MSK)) == rd64(li + L_V) && li[L_SIZE] <= i + 1 && (rd64(li + L_GROUPS) & s->groups)) {
+            if (run_program(s, rd32(li + L_ID), (u64)i + 1) < 0) return -1;
+        }
+        if (!li[L_NEXT]) break;
+        li += L_STRUCT;
+    }
+    return 0;
+}
+
+/* FDR: bucket mask of candidates at end index e (position-local form of the shift-or recurrence) */
+static u32 fdr_candidates(const u8 *fdr, const struct scan_state *s, u32 e) {
+    const u64 *ft = (const u64 *)(fdr + F_TABLE);
+    u32 stride = fdr[F_STRIDE], dmask = rd16(fdr + F_DOMAIN_MASK);
+    u8 st = e < 8 ? fdr[F_START + e] : 0; /* initial state: bit b set = bucket b cannot end here yet */
+    for (u32 p = 0; p < 8 && p <= e; p++) {
+        u32 x = e - p;
+        if (x % stride) continue;
+        u32 key = s->buf[x] | ((x + 1 < s->len ? s->buf[x + 1] : 0u) << 8);
+        st |= (u8)(ft[key & dmask] >> (8 * p));
+    }
+    return (u8)~st;
+}
+
+/* Teddy: r_j[i] = lo_j[c & 15] | hi_j[c >> 4]; candidate buckets at e = ~(OR_j r_j[e - j]) */
+static u32 teddy_candidates(const u8 *teddy, u32 masks, const struct scan_state *s, u32 e) {
+    const u8 *mb = teddy + 64;
+    u8 r = 0;
+    for (u32 j = 0; j < masks && j <= e; j++) {
+        u8 c = s->buf[e - j];
+        r |= (u8)(mb[(2 * j) * 16 + (c & 15)] | mb[(2 * j + 1) * 16 + (c >> 4)]);
+    }
+    return (u8)~r;
+}
+
+static int hwlm_exec(struct scan_state *s, const u8 *hwlm) {
+    if (!s->groups) return 0;
+    const u8 *eng = hwlm + HWLM_BODY;
+    if (hwlm[0] == 16) { /* noodle */
+        u32 n = eng[N_MSK_LEN];
+        u64 msk = rd64(eng + N_MSK), cmp = rd64(eng + N_CMP);
+        if (s->len < n) return 0;
+        for (u32 e = n - 1; e < s->len; e++) {
+            u64 v = 0;
+            for (u32 k = 0; k < n; k++) v |= (u64)s->buf[e + 1 - n + k] << (8 * k);
+            if ((v & msk) == cmp && run_program(s, rd32(eng + N_ID), (u64)e + 1) < 0) return -1;
+        }
+        return 0;
+    }
+    u32 id = rd32(eng + F_ENGINE_ID);
+    const u8 *conf_base = eng + rd32(eng + F_CONF_OFF);
+    for (u32 e = 0; e < s->len; e++) {
+        u32 cand;
+        if (id == 0) cand = fdr_candidates(eng, s, e);
+        else if (id >= 11 && id <= 18) cand = teddy_candidates(eng, (id - 11) / 2 + 1, s, e);
+        else { s->error = 1; return -1; }
+        for (u32 b = 0; cand; b++, cand >>= 1)
+            if ((cand & 1) && confirm(s, conf_base, b, e) < 0) return -1;
+    }
+    return 0;
+}
+
+/* hs_scan for block-mode pure-literal databases.  `db` = in-memory hs_database_t. */
+int op_scan(const void *db, const char *data, unsigned length, op_match_cb cb, void *ctx) {
+    const u8 *d = (const u8 *)db;
+    if (!d || !data || rd32(d + DB_MAGIC_OFF) != 0xdbdbdbdbu) return HS_INVALID;
+    if (rd32(d + DB_VERSION_OFF) != ((5u << 24) | (4u << 16) | (11u << 8))) return HS_DB_VERSION_ERROR;
+    const u8 *rose = d + rd32(d + DB_BYTECODE_OFF);
+    if (rd32(rose + R_MODE) != 1) return HS_DB_MODE_ERROR;
+    if (rose[R_RUNTIME_IMPL] != 1 || rose[R_HAS_SOM] || rd32(rose + R_CKEY_COUNT) || rd32(rose + R_BOUNDARY) ||
+        rd32(rose + R_BOUNDARY + 4) || rd32(rose + R_BOUNDARY + 8))
+        return HS_ARCH_ERROR; /* outside the restated path */
+    if (rd32(rose + R_MIN_WIDTH) > length) return HS_SUCCESS;
+    if (!length) return HS_SUCCESS;
+    if (rd32(rose + R_MIN_WIDTH_EXCL) > length) return HS_SUCCESS;
+    if (rd32(rose + R_MAX_BI) != 0xffffffffu && length > rd32(rose + R_MAX_BI)) return HS_SUCCESS;
+    struct scan_state s;
+    memset(&s, 0, sizeof(s));
+    s.rose = rose; s.buf = (const u8 *)data; s.len = length; s.cb = cb; s.ctx = ctx;
+    s.groups = rd64(rose + R_INIT_GROUPS) & rd64(rose + R_FLOAT_MASK);
+    s.ekeys = rd32(rose + R_EKEY_COUNT); s.dkeys = rd32(rose + R_DKEY_COUNT);
+    s.exhausted = calloc(s.ekeys / 8 + 2, 1);
+    s.dedupe = calloc(s.dkeys / 8 + 2, 1);
+    s.dedupe_offset = ~0ull;
+    hwlm_exec(&s, rose + rd32(rose + R_FMATCHER));
+    free(s.exhausted); free(s.dedupe);
+    if (s.error) return HS_UNKNOWN_ERROR;
+    return s.terminated ? HS_SCAN_TERMINATED : HS_SUCCESS;
+}
+
+/* Convenience for tests: collect (id, to) pairs; returns the hs_error_t, *n = pairs wanted (may exceed cap). */
+struct collect { u32 *ids; u64 *tos; size_t cap, n, stop_after; };
+static int collect_cb(unsigned id, unsigned long long from, unsigned long long to, unsigned flags, void *ctx) {
+    (void)from; (void)flags;
+    struct collect *c = (struct collect *)ctx;
+    if (c->n < c->cap) { c->ids[c->n] = id; c->tos[c->n] = to; }
+    c->n++;
+    return c->stop_after && c->n >= c->stop_after;
+}
+int op_scan_collect(const void *db, const char *data, unsigned length, u32 *ids, u64 *tos, size_t cap, size_t stop_after,
+                    size_t *n) {
+    struct collect c = {ids, tos, cap, 0, stop_after};
+    int rv = op_scan(db, data, length, collect_cb, &c);
+    if (n) *n = c.n;
+    return rv;
+}
+
+/* Independent ground truth (no bytecode involved): every occurrence of every literal, `to` one past the
+ * last byte, caseless = ASCII fold.  out_id/out_to receive up to cap pairs in (to, literal index) order. */
+size_t op_brute_force(const char *const *lits, const size_t *lens, const unsigned *flags, const unsigned *ids, unsigned n,
+                      const char *data, size_t length, u32 *out_id, u64 *out_to, size_t cap) {
+    size_t m = 0;
+    for (size_t e = 0; e < length; e++)
+        for (unsigned k = 0; k < n; k++) {
+            size_t L = lens[k];
+            if (L > e + 1) continue;
+            const u8 *t = (const u8 *)data + (e + 1 - L), *l = (const u8 *)lits[k];
+            int nocase = flags && (flags[k] & 1), ok = 1;
+            for (size_t i = 0; i < L && ok; i++) ok = nocase ? upc(t[i]) == upc(l[i]) : t[i] == l[i];
+            if (ok) { if (m < cap) { out_id[m] = ids ? ids[k] : k; out_to[m] = e + 1; } m++; }
+        }
+    return m;
+}

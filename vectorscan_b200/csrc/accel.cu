@@ -1,0 +1,167 @@
+// accel.cu -- shufti / truffle / vermicelli byte-class searches as warp-level tests (part of libhs_gpu.so).
+//
+// The reference's acceleration primitives (/root/reference/src/nfa) answer "where is the first (last) byte
+// of [buf, end) that belongs to a class":
+//   shufti     lo[c & 15] & hi[c >> 4] != 0                         shufti.cpp:44-70, shufti_simd.hpp:89-138
+//   truffle    (c & 0x80 ? highset : highclear)[c & 15] bit ((c >> 4) & 7)   x86/truffle.hpp:37-62, trufflecompile.cpp:59-73
+//   vermicelli (c & casemask) == ch ; double: adjacent pair, a trailing c1 counts   vermicelli_simd.cpp:82-622
+// with the return convention: forward -> pointer to the hit or buf_end; reverse -> pointer to the hit or buf - 1.
+// On the CPU these are one SIMD compare chain per 16..64 bytes.  Here every lane classifies 16 bytes
+// (one LDG.128), the warp votes with a ballot, and the grid keeps the minimum (maximum) hit offset with one
+// atomic per warp that saw a hit; blocks whose range lies behind an already-published hit exit early.
+#include "hs_gpu.h"
+
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstring>
+
+namespace {
+
+enum Kind { SHUFTI = 0, TRUFFLE = 1, VERM = 2, NVERM = 3, DVERM = 4 };
+
+struct ClassParams {
+    uint8_t a[16];  // shufti lo / truffle highclear
+    uint8_t b[16];  // shufti hi / truffle highset
+    uint8_t c1, c2, casemask, kind;
+};
+
+__device__ __forceinline__ bool in_class(const ClassParams &p, const uint8_t *sa, const uint8_t *sb, uint8_t c) {
+    switch (p.kind) {
+    case SHUFTI: return (sa[c & 15] & sb[c >> 4]) != 0;
+    case TRUFFLE: return ((((c & 0x80) ? sb : sa)[c & 15] >> ((c >> 4) & 7)) & 1) != 0;
+    case VERM: return (uint8_t)(c & p.casemask) == p.c1;
+    default: return (uint8_t)(c & p.casemask) != p.c1;  // NVERM
+    }
+}
+
+// result[0]: forward = smallest hit offset (init len), reverse = largest hit offset + 1 (init 0)
+template <bool REVERSE>
+__global__ void k_class_search(const uint8_t *buf, unsigned long long len, ClassParams p, unsigned long long *result) {
+    __shared__ uint8_t sa[16], sb[16];
+    if (threadIdx.x < 16) { sa[threadIdx.x] = p.a[threadIdx.x]; sb[threadIdx.x] = p.b[threadIdx.x]; }
+    __syncthreads();
+    const unsigned long long chunks = (len + 15) / 16;
+    const unsigned long long per_block = (chunks + gridDim.x - 1) / gridDim.x;
+    unsigned long long first = (unsigned long long)blockIdx.x * per_block, last = first + per_block;
+    if (last > chunks) last = chunks;
+    const unsigned lane = threadIdx.x & 31;
+    for (unsigned long long base = first + (threadIdx.x & ~31u); base < last; base += blockDim.x) {
+        // early exit: a better hit is already known
+        unsigned long long best = *(volatile unsigned long long *)result;
+        if (!REVERSE && best <= base * 16) return;
+        unsigned long long ch = REVERSE ? (first + last - 1 - (base - first) - lane) : base + lane;
+        // (reverse walks the block's range from its end; lanes keep ascending order inside the warp's 512 bytes)
+        if (REVERSE) {
+            const unsigned long long top = last - 1 - (base - first);  // highest chunk of this warp step
+            ch = top >= lane ? top - lane : ~0ull;
+            if (best > (top + 1) * 16) return;
+        }
+        unsigned hits = 0;
+        if (ch != ~0ull && ch >= first && ch < last) {
+            const unsigned long long off = ch * 16;
+            uint4 v = *reinterpret_cast<const uint4 *>(buf + off);  // buffer is padded to a multiple of 16 + 16
+            const unsigned w[5] = {v.x, v.y, v.z, v.w, *reinterpret_cast<const unsigned *>(buf + off + 16)};
+#pragma unroll
+            for (int i = 0; i < 16; i++) {
+                if (off + i >= len) break;
+                const uint8_t c = (uint8_t)(w[i >> 2] >> (8 * (i & 3)));
+                bool hit;
+                if (p.kind == DVERM) {
+                    const uint8_t n = (uint8_t)(w[(i + 1) >> 2] >> (8 * ((i + 1) & 3)));
+                    const bool is1 = (uint8_t)(c & p.casemask) == p.c1;
+                    hit = is1 && (off + i + 1 >= len || (uint8_t)(n & p.casemask) == p.c2);
+                } else {
+                    hit = in_class(p, sa, sb, c);
+                }
+                hits |= (hit ? 1u : 0u) << i;
+            }
+        }
+        const unsigned vote = __ballot_sync(0xffffffffu, hits != 0);
+        if (vote) {
+            if (!REVERSE) {
+                const unsigned src = __ffs(vote) - 1;  // lowest chunk with a hit
+                const unsigned h = __shfl_sync(0xffffffffu, hits, src);
+                if (lane == 0) atomicMin(result, (base + src) * 16 + (__ffs(h) - 1));
+            } else {
+                const unsigned src = __ffs(vote) - 1;  // lane 0 holds the highest chunk
+                const unsigned h = __shfl_sync(0xffffffffu, hits, src);
+                const unsigned long long chs = __shfl_sync(0xffffffffu, ch, src);
+                if (lane == 0) atomicMax(result, chs * 16 + (31 - __clz(h)) + 1);
+            }
+            return;  // every later chunk of this warp is worse; other warps check `best`
+        }
+    }
+}
+
+struct Workspace {
+    uint8_t *d_buf = nullptr;
+    size_t cap = 0;
+    unsigned long long *d_res = nullptr;
+};
+
+long long run_search(const ClassParams &p, const uint8_t *buf, size_t len, bool reverse) {
+    static thread_local Workspace ws;
+    if (!buf && len) return -2;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { cudaGetLastError(); return -2; }
+    if (!len) return reverse ? -1 : 0;
+    const size_t padded = (len + 15) / 16 * 16 + 32;
+    if (padded > ws.cap) {
+        if (ws.d_buf) cudaFree(ws.d_buf);
+        if (cudaMalloc((void **)&ws.d_buf, padded + padded / 4) != cudaSuccess) { ws.d_buf = nullptr; ws.cap = 0; return -2; }
+        ws.cap = padded + padded / 4;
+    }
+    if (!ws.d_res && cudaMalloc((void **)&ws.d_res, 8) != cudaSuccess) return -2;
+    cudaMemcpy(ws.d_buf, buf, len, cudaMemcpyHostToDevice);
+    cudaMemset(ws.d_buf + len, 0, padded - len);
+    unsigned long long init = reverse ? 0ull : (unsigned long long)len;
+    cudaMemcpy(ws.d_res, &init, 8, cudaMemcpyHostToDevice);
+    const unsigned long long chunks = (len + 15) / 16;
+    unsigned grid = (unsigned)((chunks + 255) / 256);
+    if (grid > 148 * 8) grid = 148 * 8;
+    if (reverse) k_class_search<true><<<grid, 256>>>(ws.d_buf, len, p, ws.d_res);
+    else k_class_search<false><<<grid, 256>>>(ws.d_buf, len, p, ws.d_res);
+    unsigned long long res = 0;
+    if (cudaMemcpy(&res, ws.d_res, 8, cudaMemcpyDeviceToHost) != cudaSuccess) return -2;
+    return reverse ? (long long)res - 1 : (long long)res;
+}
+
+}  // namespace
+
+extern "C" {
+
+long long hs_gpu_shufti(const uint8_t lo[16], const uint8_t hi[16], const uint8_t *buf, size_t len, int reverse) {
+    ClassParams p{};
+    std::memcpy(p.a, lo, 16);
+    std::memcpy(p.b, hi, 16);
+    p.kind = SHUFTI;
+    return run_search(p, buf, len, reverse != 0);
+}
+
+long long hs_gpu_truffle(const uint8_t mask1[16], const uint8_t mask2[16], const uint8_t *buf, size_t len, int reverse) {
+    ClassParams p{};
+    std::memcpy(p.a, mask1, 16);
+    std::memcpy(p.b, mask2, 16);
+    p.kind = TRUFFLE;
+    return run_search(p, buf, len, reverse != 0);
+}
+
+long long hs_gpu_vermicelli(uint8_t c, int nocase, const uint8_t *buf, size_t len, int reverse, int negate) {
+    ClassParams p{};
+    p.casemask = nocase ? 0xdf : 0xff;
+    p.c1 = (uint8_t)(c & p.casemask);
+    p.kind = negate ? NVERM : VERM;
+    return run_search(p, buf, len, reverse != 0);
+}
+
+long long hs_gpu_vermicelli_double(uint8_t c1, uint8_t c2, int nocase, const uint8_t *buf, size_t len) {
+    ClassParams p{};
+    p.casemask = nocase ? 0xdf : 0xff;
+    p.c1 = (uint8_t)(c1 & p.casemask);
+    p.c2 = (uint8_t)(c2 & p.casemask);
+    p.kind = DVERM;
+    return run_search(p, buf, len, false);
+}
+
+}  // extern "C"

@@ -698,6 +698,11 @@ __global__ void k_flag_dups(const Rec *in, u8 *keep, u64 n) {
     if (i < n) keep[i] = (i && RecDup()(in[i - 1], in[i])) ? 0 : 1;
 }
 
+__global__ void k_histogram(const hs_gpu_match_t *m, u64 n, unsigned long long *hist, u32 n_ids) {
+    const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && m[i].id < n_ids) atomicAdd(&hist[m[i].id], 1ull);
+}
+
 __global__ void k_convert(const Rec *in, hs_gpu_match_t *out, u64 n) {
     const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) {
@@ -774,7 +779,7 @@ struct hs_gpu_scratch {
     std::atomic<int> in_use{0};
     int device = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     std::vector<DbImage *> dbs;
     hs_gpu_corpus staging;       // device staging for host-buffer scans
     u8 *h_stage = nullptr;       // pinned host staging
@@ -914,13 +919,15 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
     st.bytes = corpus.total;
     st.buffers = corpus.count;
     st.scan_launches = 0;
+    st.kernel_launches = 0;
+    st.kernel_ms = 0;
     st.arena_retries = 0;
     s->n_matches = 0;
     s->fetched = false;
     s->last_image = im;
     if (!corpus.total || !corpus.count) {
         st.matches = st.raw_matches = st.candidates = st.confirms = 0;
-        st.scan_ms = st.sort_ms = 0;
+        st.scan_ms = st.sort_ms = st.kernel_ms = 0;
         return HS_SUCCESS;
     }
     CU_OK(s->recs.reserve(s->arena_hint));
@@ -931,13 +938,16 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
         CU_OK(cudaMemsetAsync(s->d_ctl, 0, 8 * sizeof(unsigned long long), s->stream));
         DevArena ar{s->recs.p, s->d_ctl + 0, s->d_ctl + 1, reinterpret_cast<u32 *>(s->d_ctl + 3), s->recs.cap};
         hs_error_t rv;
+        CU_OK(cudaEventRecord(s->ev[6], s->stream));
         switch (im->view.kind) {
         case ENG_FDR: rv = launch_scan<FdrNative, false>(s, im->dev, cp, ar); break;
         case ENG_TEDDY: rv = launch_scan<TeddyNative, false>(s, im->dev, cp, ar); break;
         default: rv = launch_scan<Noodle, true>(s, im->dev, cp, ar); break;
         }
         if (rv != HS_SUCCESS) return rv;
+        CU_OK(cudaEventRecord(s->ev[7], s->stream));
         st.scan_launches++;
+        st.kernel_launches++;
         CU_OK(cudaMemcpyAsync(s->h_ctl, s->d_ctl, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
         CU_OK(cudaStreamSynchronize(s->stream));
         if ((u32)s->h_ctl[3]) return HS_UNKNOWN_ERROR;
@@ -974,10 +984,12 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
         n_out = s->h_ctl[4];
         k_convert<<<(unsigned)((n_out + 255) / 256), 256, 0, s->stream>>>(s->recs2.p, s->d_matches.p, n_out);
         CU_OK(cudaGetLastError());
+        st.kernel_launches += 2;  // k_flag_dups + k_convert (CUB's sort/select kernels are not counted)
     }
     CU_OK(cudaEventRecord(s->ev[3], s->stream));
     CU_OK(cudaEventSynchronize(s->ev[3]));
     cudaEventElapsedTime(&st.scan_ms, s->ev[1], s->ev[2]);
+    cudaEventElapsedTime(&st.kernel_ms, s->ev[6], s->ev[7]);  // the last (successful) k_scan launch alone
     cudaEventElapsedTime(&st.sort_ms, s->ev[2], s->ev[3]);
     s->n_matches = n_out;
     st.matches = n_out;
@@ -1381,6 +1393,22 @@ hs_error_t hs_gpu_fetch_matches(hs_gpu_scratch_t *scratch, const hs_gpu_match_t 
     if (rv != HS_SUCCESS) return rv;
     *matches = scratch->h_matches;
     *n_matches = scratch->n_matches;
+    return HS_SUCCESS;
+}
+
+hs_error_t hs_gpu_histogram(hs_gpu_scratch_t *scratch, void *device_hist_u64, uint32_t n_ids) {
+    if (!scratch || scratch->magic != 0x47505553 || !device_hist_u64) return HS_INVALID;
+    InUseGuard g(scratch);
+    if (!g.ok) return HS_SCRATCH_IN_USE;
+    if (scratch->fetched && scratch->last_image && static_cast<DbImage *>(scratch->last_image)->view.ekey_count)
+        return HS_INVALID;  // single-match sets are resolved on the host: histogram the fetched matches instead
+    const u64 n = scratch->n_matches;
+    if (n) {
+        k_histogram<<<(unsigned)((n + 255) / 256), 256, 0, scratch->stream>>>(
+            scratch->d_matches.p, n, static_cast<unsigned long long *>(device_hist_u64), n_ids);
+        CU_OK(cudaGetLastError());
+        CU_OK(cudaStreamSynchronize(scratch->stream));
+    }
     return HS_SUCCESS;
 }
 

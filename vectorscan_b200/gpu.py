@@ -25,7 +25,8 @@ class Stats(C.Structure):
     _fields_ = [("bytes", C.c_uint64), ("buffers", C.c_uint64), ("matches", C.c_uint64),
                 ("raw_matches", C.c_uint64), ("candidates", C.c_uint64), ("confirms", C.c_uint64),
                 ("h2d_ms", C.c_float), ("scan_ms", C.c_float), ("sort_ms", C.c_float), ("d2h_ms", C.c_float),
-                ("scan_launches", C.c_uint32), ("arena_retries", C.c_uint32)]
+                ("scan_launches", C.c_uint32), ("arena_retries", C.c_uint32), ("kernel_ms", C.c_float),
+                ("kernel_launches", C.c_uint32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -64,6 +65,7 @@ def lib():
         L.hs_gpu_scan_corpus.argtypes = [vp, vp, vp, C.POINTER(C.c_uint64)]
         L.hs_gpu_fetch_matches.argtypes = [vp, C.POINTER(C.POINTER(Match)), C.POINTER(C.c_uint64)]
         L.hs_gpu_last_stats.argtypes = [vp, C.POINTER(Stats)]
+        L.hs_gpu_histogram.argtypes = [vp, vp, C.c_uint32]
         L.hs_gpu_host_alloc.argtypes = [C.c_size_t]
         L.hs_gpu_host_alloc.restype = vp
         L.hs_gpu_host_free.argtypes = [vp]

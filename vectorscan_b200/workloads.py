@@ -1,0 +1,114 @@
+"""Seeded synthetic workloads for BASELINE.json's configs (definitions: SURVEY.md section 8d).
+
+  c1: 1000 literals, lengths 4..16 over [a-z], 20 % caseless; one buffer of space-separated pseudo-words
+      (Zipf over a 50k-word vocabulary) with literals planted about once per 4 KiB.      [hs_scan]
+  c2: 10 000 literals, lengths 3..12 over printable ASCII; batches of 1500-byte packets, payload = random
+      printable bytes with HTTP-ish tokens, one planted literal in 10 % of the packets.  [hs_scan_vector shape]
+Everything is numpy-vectorised so that 64 MiB .. 1 GiB corpora generate in seconds.
+"""
+import numpy as np
+
+PRINTABLE = np.arange(32, 127, dtype=np.uint8)
+LOWER = np.arange(97, 123, dtype=np.uint8)
+HTTP_TOKENS = [b"GET /index.html HTTP/1.1\r\n", b"POST /api/v1/items HTTP/1.1\r\n", b"Host: www.example.com\r\n",
+               b"User-Agent: Mozilla/5.0 (X11; Linux x86_64)\r\n", b"Accept: */*\r\n", b"Content-Length: 348\r\n",
+               b"Content-Type: application/json\r\n", b"Connection: keep-alive\r\n", b"HTTP/1.1 200 OK\r\n",
+               b"Cookie: session=", b"Accept-Encoding: gzip, deflate\r\n", b"\r\n\r\n"]
+
+
+def _unique_literals(rng, n, lo, hi, alphabet):
+    seen, out = set(), []
+    while len(out) < n:
+        ln = int(rng.integers(lo, hi + 1))
+        s = bytes(alphabet[rng.integers(0, len(alphabet), ln)])
+        if s not in seen:
+            seen.add(s)
+            out.append(s)
+    return out
+
+
+def c1_patterns(n=1000, seed=20260101):
+    rng = np.random.default_rng(seed)
+    lits = _unique_literals(rng, n, 4, 16, LOWER)
+    flags = [1 if rng.random() < 0.2 else 0 for _ in lits]
+    # caseless literals get a mixed-case spelling
+    lits = [bytes((c - 32) if f and rng.random() < 0.5 else c for c in l) for l, f in zip(lits, flags)]
+    return lits, flags, list(range(n))
+
+
+def c1_text(nbytes, lits, seed=20260101):
+    rng = np.random.default_rng(seed + 1)
+    vocab_n = 50000
+    wl = rng.integers(2, 11, vocab_n)
+    starts = np.concatenate([[0], np.cumsum(wl + 1)])  # word + trailing space
+    pool = LOWER[rng.integers(0, 26, int(starts[-1]))]
+    pool[starts[1:] - 1] = 32
+    ranks = np.arange(1, vocab_n + 1, dtype=np.float64)
+    p = 1.0 / ranks
+    p /= p.sum()
+    out = np.empty(nbytes + 64, dtype=np.uint8)
+    pos = 0
+    while pos < nbytes:
+        k = min(4_000_000, (nbytes - pos) // 4 + 16)
+        w = rng.choice(vocab_n, size=k, p=p)
+        lens = wl[w] + 1
+        ends = np.cumsum(lens)
+        total = int(ends[-1])
+        idx = np.arange(total) - np.repeat(ends - lens, lens) + np.repeat(starts[w], lens)
+        chunk = pool[idx]
+        take = min(total, nbytes + 64 - pos)
+        out[pos:pos + take] = chunk[:take]
+        pos += take
+    out = out[:nbytes]
+    nplant = max(1, nbytes // 4096)
+    where = rng.integers(0, max(1, nbytes - 32), nplant)
+    which = rng.integers(0, len(lits), nplant)
+    for w_, k_ in zip(where, which):
+        l = lits[k_]
+        if w_ + len(l) <= nbytes:
+            out[w_:w_ + len(l)] = np.frombuffer(l, dtype=np.uint8)
+    return out
+
+
+def c2_patterns(n=10000, seed=20260102):
+    rng = np.random.default_rng(seed)
+    lits = _unique_literals(rng, n, 3, 12, PRINTABLE)
+    return lits, [0] * n, list(range(n))
+
+
+def c2_batch(nbytes, lits, seed=20260102, packet=1500):
+    """Returns (flat uint8 array, uint64 offsets[count+1])."""
+    rng = np.random.default_rng(seed + 7)
+    count = (nbytes + packet - 1) // packet
+    flat = PRINTABLE[rng.integers(0, len(PRINTABLE), nbytes)]
+    offsets = np.minimum(np.arange(count + 1, dtype=np.uint64) * packet, nbytes).astype(np.uint64)
+    # HTTP-ish tokens: ~30 % of the payload, written at random packet-relative positions
+    ntok = int(nbytes * 0.3 / 24)
+    tok_idx = rng.integers(0, len(HTTP_TOKENS), ntok)
+    tok_pos = rng.integers(0, max(1, nbytes - 64), ntok)
+    for t, tok in enumerate(HTTP_TOKENS):
+        sel = tok_pos[tok_idx == t]
+        tb = np.frombuffer(tok, dtype=np.uint8)
+        idx = sel[:, None] + np.arange(len(tb))[None, :]
+        flat[idx] = tb[None, :]
+    # planted literals: one in 10 % of the packets
+    npl = count // 10
+    pk = rng.choice(count, size=npl, replace=False)
+    which = rng.integers(0, len(lits), npl)
+    inner = rng.integers(0, packet - 16, npl)
+    for p_, k_, o_ in zip(pk, which, inner):
+        l = lits[k_]
+        s = int(offsets[p_]) + int(o_)
+        if s + len(l) <= int(offsets[p_ + 1]):
+            flat[s:s + len(l)] = np.frombuffer(l, dtype=np.uint8)
+    return flat, offsets
+
+
+def sweep_patterns(n, seed):
+    rng = np.random.default_rng(seed)
+    return _unique_literals(rng, n, 4, 12, PRINTABLE), [0] * n, list(range(n))
+
+
+def sweep_batch(nbytes, bufsize, lits, seed):
+    flat, offsets = c2_batch(nbytes, lits, seed=seed, packet=bufsize)
+    return flat, offsets
