@@ -62,3 +62,34 @@ size_t ref_shim_fdr_exec(const void *fdr, const unsigned char *buf, size_t len, 
 unsigned int ref_shim_crc32c(const void *p, size_t n) { return Crc32c_ComputeBuf(0, p, n); }
 int ref_shim_db_is_valid(const void *db) { return (int)dbIsValid((const struct hs_database *)db); }
 unsigned long long ref_shim_current_platform(void) { return hs_current_platform; }
+
+/* Byte-class primitives: thin offset-returning wrappers over the reference's own routines
+ * (src/nfa/shufti.h, truffle.h, vermicelli.hpp).  Forward: offset of the hit or len; reverse: offset or -1. */
+#include "nfa/shufti.h"
+#include "nfa/truffle.h"
+#include "util/simd_utils.h"
+const u8 *vermicelliExec(char c, char noCase, const u8 *buf, const u8 *buf_end);
+const u8 *nvermicelliExec(char c, char noCase, const u8 *buf, const u8 *buf_end);
+const u8 *rvermicelliExec(char c, char nocase, const u8 *buf, const u8 *buf_end);
+const u8 *rnvermicelliExec(char c, char nocase, const u8 *buf, const u8 *buf_end);
+const u8 *vermicelliDoubleExec(char c1, char c2, char nocase, const u8 *buf, const u8 *buf_end);
+
+long long ref_shim_shufti(const u8 *lo, const u8 *hi, const u8 *buf, size_t len, int reverse) {
+    m128 l = loadu128(lo), h = loadu128(hi);
+    const u8 *r = reverse ? rshuftiExec(l, h, buf, buf + len) : shuftiExec(l, h, buf, buf + len);
+    return (long long)(r - buf);
+}
+long long ref_shim_truffle(const u8 *m1, const u8 *m2, const u8 *buf, size_t len, int reverse) {
+    m128 a = loadu128(m1), b = loadu128(m2);
+    const u8 *r = reverse ? rtruffleExec(a, b, buf, buf + len) : truffleExec(a, b, buf, buf + len);
+    return (long long)(r - buf);
+}
+long long ref_shim_verm(u8 c, int nocase, const u8 *buf, size_t len, int reverse, int negate) {
+    const u8 *r;
+    if (!reverse) r = negate ? nvermicelliExec((char)c, (char)nocase, buf, buf + len) : vermicelliExec((char)c, (char)nocase, buf, buf + len);
+    else r = negate ? rnvermicelliExec((char)c, (char)nocase, buf, buf + len) : rvermicelliExec((char)c, (char)nocase, buf, buf + len);
+    return (long long)(r - buf);
+}
+long long ref_shim_dverm(u8 c1, u8 c2, int nocase, const u8 *buf, size_t len) {
+    return (long long)(vermicelliDoubleExec((char)c1, (char)c2, (char)nocase, buf, buf + len) - buf);
+}

@@ -1,0 +1,116 @@
+"""GPU tests: shufti / truffle / vermicelli byte-class searches against the reference's own routines
+(oracle/_ref exports shuftiExec, rshuftiExec, truffleExec, rtruffleExec, vermicelliExec, ...) with the
+vectors' shape of unit/internal/shufti.cpp, truffle.cpp, vermicelli.cpp: every start alignment, hit / no hit."""
+import ctypes as C
+import random
+
+import pytest
+
+from vectorscan_b200 import gpu
+
+pytestmark = pytest.mark.gpu
+
+
+def shufti_masks(chars):
+    """One-bucket shufti masks for a small class (src/nfa/shufticompile.cpp:54-110 with a single bucket per
+    distinct high nibble)."""
+    lo, hi = bytearray(16), bytearray(16)
+    his = sorted({c >> 4 for c in chars})
+    assert len(his) <= 8
+    for c in chars:
+        bit = 1 << his.index(c >> 4)
+        lo[c & 15] |= bit
+        hi[c >> 4] |= bit
+    return bytes(lo), bytes(hi)
+
+
+def truffle_masks(chars):
+    m1, m2 = bytearray(16), bytearray(16)
+    for c in chars:
+        (m2 if c & 0x80 else m1)[c & 15] |= 1 << ((c >> 4) & 7)
+    return bytes(m1), bytes(m2)
+
+
+def in_shufti(lo, hi, c):
+    return (lo[c & 15] & hi[c >> 4]) != 0
+
+
+def first(pred, buf):
+    for i, c in enumerate(buf):
+        if pred(c):
+            return i
+    return len(buf)
+
+
+def last(pred, buf):
+    for i in range(len(buf) - 1, -1, -1):
+        if pred(buf[i]):
+            return i
+    return -1
+
+
+def test_shufti_truffle_vermicelli_all_alignments(ref):
+    L = gpu.lib()
+    L.hs_gpu_shufti.restype = L.hs_gpu_truffle.restype = L.hs_gpu_vermicelli.restype = C.c_longlong
+    L.hs_gpu_vermicelli_double.restype = C.c_longlong
+    rng = random.Random(3)
+    for trial in range(40):
+        chars = set(rng.sample(range(256), rng.randint(1, 6)))
+        while len({c >> 4 for c in chars}) > 8:
+            chars.pop()
+        lo, hi = shufti_masks(chars)
+        m1, m2 = truffle_masks(chars)
+        filler = [c for c in range(256) if not in_shufti(lo, hi, c) and c not in chars]
+        n = rng.choice([1, 15, 16, 17, 64, 100, 1000, 70000])
+        base = bytearray(rng.choice(filler) for _ in range(n + 40))
+        for _ in range(rng.choice([0, 1, 3])):
+            base[rng.randrange(len(base))] = rng.choice(sorted(chars))
+        for align in range(0, 33, rng.choice([1, 3, 7])):
+            buf = bytes(base[align:align + n])
+            assert L.hs_gpu_shufti(lo, hi, buf, len(buf), 0) == first(lambda c: in_shufti(lo, hi, c), buf)
+            assert L.hs_gpu_shufti(lo, hi, buf, len(buf), 1) == last(lambda c: in_shufti(lo, hi, c), buf)
+            assert L.hs_gpu_truffle(m1, m2, buf, len(buf), 0) == first(lambda c: c in chars, buf)
+            assert L.hs_gpu_truffle(m1, m2, buf, len(buf), 1) == last(lambda c: c in chars, buf)
+            ch = sorted(chars)[0]
+            assert L.hs_gpu_vermicelli(ch, 0, buf, len(buf), 0, 0) == first(lambda c: c == ch, buf)
+            assert L.hs_gpu_vermicelli(ch, 0, buf, len(buf), 1, 0) == last(lambda c: c == ch, buf)
+            assert L.hs_gpu_vermicelli(ch, 0, buf, len(buf), 0, 1) == first(lambda c: c != ch, buf)
+            # against the reference's own SIMD routines (need >= 1 byte)
+            b = C.create_string_buffer(buf, len(buf))
+            p0 = C.addressof(b)
+            lo_t, hi_t = (C.c_ubyte * 16)(*lo), (C.c_ubyte * 16)(*hi)
+            ref.L.ref_shim_shufti.restype = C.c_longlong
+            ref.L.ref_shim_shufti.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]
+            ref.L.ref_shim_truffle.restype = C.c_longlong
+            ref.L.ref_shim_truffle.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]
+            for rev in (0, 1):
+                assert L.hs_gpu_shufti(lo, hi, buf, len(buf), rev) == ref.L.ref_shim_shufti(lo_t, hi_t, p0, len(buf), rev)
+                m1_t, m2_t = (C.c_ubyte * 16)(*m1), (C.c_ubyte * 16)(*m2)
+                assert L.hs_gpu_truffle(m1, m2, buf, len(buf), rev) == ref.L.ref_shim_truffle(m1_t, m2_t, p0, len(buf), rev)
+
+
+def test_vermicelli_double_and_nocase(ref):
+    L = gpu.lib()
+    L.hs_gpu_vermicelli.restype = L.hs_gpu_vermicelli_double.restype = C.c_longlong
+    ref.L.ref_shim_verm.restype = C.c_longlong
+    ref.L.ref_shim_verm.argtypes = [C.c_ubyte, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_int]
+    ref.L.ref_shim_dverm.restype = C.c_longlong
+    ref.L.ref_shim_dverm.argtypes = [C.c_ubyte, C.c_ubyte, C.c_int, C.c_void_p, C.c_size_t]
+    rng = random.Random(9)
+    for trial in range(60):
+        n = rng.choice([1, 2, 16, 31, 33, 200, 5000])
+        buf = bytearray(rng.choice(b"xyzXYZ.") for _ in range(n))
+        if rng.random() < 0.7 and n >= 2:
+            p = rng.randrange(n - 1)
+            buf[p:p + 2] = rng.choice([b"ab", b"Ab", b"aB", b"AB"])
+        if rng.random() < 0.3:
+            buf[-1] = ord("a")
+        buf = bytes(buf)
+        b = C.create_string_buffer(buf, len(buf))
+        for nocase in (0, 1):
+            c1, c2 = (ord("A"), ord("B")) if nocase else (ord("a"), ord("b"))
+            for rev in (0, 1):
+                for neg in (0, 1):
+                    assert L.hs_gpu_vermicelli(c1, nocase, buf, n, rev, neg) == \
+                        ref.L.ref_shim_verm(c1, nocase, C.addressof(b), n, rev, neg), (buf, nocase, rev, neg)
+            assert L.hs_gpu_vermicelli_double(c1, c2, nocase, buf, n) == ref.L.ref_shim_dverm(c1, c2, nocase, C.addressof(b), n)
