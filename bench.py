@@ -203,7 +203,7 @@ def main():
     barrier()
     sampler.start()
     dev_ms = kern_ms = 0.0
-    nmatch = raw = launches = nbytes_scanned = 0
+    nmatch = raw = launches = nbytes_scanned = cands = probes = 0
     t0 = time.perf_counter()
     for k in range(args.steps):
         c = corpora[k % ROT]
@@ -212,6 +212,8 @@ def main():
         dev_ms += st["scan_ms"] + st["sort_ms"]
         kern_ms += st["kernel_ms"]
         raw += st["raw_matches"]
+        cands += st["candidates"]
+        probes += st["confirms"]
         launches += st["kernel_launches"]
         nbytes_scanned += c.total
     barrier()
@@ -282,7 +284,8 @@ def main():
             "matches_per_step": int(tot_matches / args.steps / world),
             "wall_ms_per_step": round(1e3 * max_wall / args.steps, 4),
             "config": {"workload": name, "l2": f"inputs larger than L2: {ROT} resident batches scanned in rotation",
-                       "frontend": args.frontend, "hist_nonzero_ids": int((hist > 0).sum())},
+                       "frontend": args.frontend, "candidates_per_kb": round(1024.0 * cands / max(1, nbytes_scanned), 3),
+                       "confirm_probes_per_kb": round(1024.0 * probes / max(1, nbytes_scanned), 3), "hist_nonzero_ids": int((hist > 0).sum())},
             "clocks": clocks,
             "e2e": {"value": round(e2e_value, 3), "unit": "GB/s", "h2d_bytes_per_step": int(flat0.nbytes + off0.nbytes),
                     "d2h_bytes_per_step": d2h_per_step, "steps": e2e_steps,

@@ -24,6 +24,7 @@
 // atomic per flush).  A finalize pass sorts the arena by (buffer, to, id) and applies dedupe keys.
 #include "hsb_layout.h"
 #include "hsb_dbview.h"
+#include "turbo_tables.h"
 #include "hs_gpu.h"
 
 #include <cuda_runtime.h>
@@ -82,6 +83,10 @@ struct DevDb {
     u32 nood_len, nood_id;
     u32 min_width, min_width_excl, max_bi_width;
     u32 bc_len;
+    // turbo front end (turbo_tables.h); tK == 0 when not built
+    const u64 *pair_tab;
+    const turbo::Slot *slots;
+    u32 tK, tH1, tH2;
 };
 
 struct DevCorpus {
@@ -132,15 +137,18 @@ struct Ctx {
     const DevDb &db;
     const DevCorpus &cp;
     const DevArena &ar;
-    WarpShared *ws;
+    u32 *q;         // per-warp candidate queue
+    Rec *stage;     // per-warp staged match records
+    u32 *stage_n;
+    u32 stage_cap;
     const ConfHdr *conf;
 };
 
 __device__ __forceinline__ void emit(const Ctx &c, u32 buf, u32 to, u32 id, u32 aux) {
     Rec r{buf, to, id, aux};
-    u32 slot = atomicAdd(&c.ws->stage_n, 1u);
-    if (slot < STAGE_CAP) {
-        c.ws->stage[slot] = r;
+    u32 slot = atomicAdd(c.stage_n, 1u);
+    if (slot < c.stage_cap) {
+        c.stage[slot] = r;
     } else {  // staging full: slow path straight to the arena
         unsigned long long idx = atomicAdd(c.ar.count, 1ull);
         if (idx < c.ar.cap) c.ar.recs[idx] = r;
@@ -150,17 +158,17 @@ __device__ __forceinline__ void emit(const Ctx &c, u32 buf, u32 to, u32 id, u32 
 // warp-synchronous: move staged records to the arena with one global atomic
 __device__ __forceinline__ void flush_stage(const Ctx &c) {
     __syncwarp();
-    u32 n = *(volatile u32 *)&c.ws->stage_n;
-    if (n > STAGE_CAP) n = STAGE_CAP;
+    u32 n = *(volatile u32 *)c.stage_n;
+    if (n > c.stage_cap) n = c.stage_cap;
     if (n) {
         unsigned long long base = 0;
         if (lane_id() == 0) base = atomicAdd(c.ar.count, (unsigned long long)n);
         base = __shfl_sync(0xffffffffu, base, 0);
         for (u32 i = lane_id(); i < n; i += 32)
-            if (base + i < c.ar.cap) c.ar.recs[base + i] = c.ws->stage[i];
+            if (base + i < c.ar.cap) c.ar.recs[base + i] = c.stage[i];
     }
     __syncwarp();
-    if (lane_id() == 0) c.ws->stage_n = 0;
+    if (lane_id() == 0) *c.stage_n = 0;
     __syncwarp();
 }
 
@@ -396,12 +404,12 @@ __device__ void drain_queue(const Ctx &c, u32 strip, u64 strip_base, u32 count, 
     for (u32 base = 0; base < count; base += 32) {
         const u32 idx = base + lane_id();
         if (idx < count) {
-            const u32 e = c.ws->q[idx];
+            const u32 e = c.q[idx];
             if (NOODLE) confirm_entry_noodle(c, strip, strip_base + (e >> 8));
             else confirm_entry(c, strip, strip_base + (e >> 8), e & 0xff, n_probe);
         }
         __syncwarp();
-        if (*(volatile u32 *)&c.ws->stage_n >= STAGE_CAP / 2) flush_stage(c);
+        if (*(volatile u32 *)c.stage_n >= c.stage_cap / 2) flush_stage(c);
     }
 }
 
@@ -429,7 +437,7 @@ __device__ __forceinline__ u32 push_candidates(const Ctx &c, const u32 cw[4], u3
         const u32 k = __ffs(nz) - 1;
         nz &= nz - 1;
         const u32 byte = (cw[k >> 2] >> (8 * (k & 3))) & 0xff;
-        c.ws->q[slot++] = ((pos_in_strip + k) << 8) | byte;
+        c.q[slot++] = ((pos_in_strip + k) << 8) | byte;
     }
     return qn + __shfl_sync(0xffffffffu, incl, 31);
 }
@@ -624,7 +632,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_scan(const DevDb db, const DevCo
     if (ln == 0) wsh[warp].stage_n = 0;
     __syncthreads();
 
-    const Ctx c{db, cp, ar, &wsh[warp], conf};
+    const Ctx c{db, cp, ar, wsh[warp].q, wsh[warp].stage, &wsh[warp].stage_n, STAGE_CAP, conf};
     u32 n_cand = 0, n_probe = 0;
     const u32 warps_total = gridDim.x * WARPS;
     for (u32 strip = blockIdx.x * WARPS + warp; strip < cp.nstrips; strip += warps_total) {
@@ -673,6 +681,8 @@ __global__ void __launch_bounds__(THREADS, 1) k_scan(const DevDb db, const DevCo
         if (n_probe) atomicAdd(&ar.stats[1], (unsigned long long)n_probe);
     }
 }
+
+#include "turbo.cuh"
 
 // ------------------------------------------------------------------------------------------------
 // finalize: Rec (sorted, deduped) -> hs_gpu_match_t
@@ -750,12 +760,17 @@ struct DbImage {  // one uploaded database
     u8 *d_bc = nullptr;
     u64 *d_fdr = nullptr;
     u32 *d_teddy = nullptr;
+    u64 *d_pair = nullptr;
+    turbo::Slot *d_slots = nullptr;
+    turbo::Tables turbo_tabs;
     size_t device_bytes = 0;
     void release() {
         if (d_bc) cudaFree(d_bc);
         if (d_fdr) cudaFree(d_fdr);
         if (d_teddy) cudaFree(d_teddy);
-        d_bc = nullptr; d_fdr = nullptr; d_teddy = nullptr;
+        if (d_pair) cudaFree(d_pair);
+        if (d_slots) cudaFree(d_slots);
+        d_bc = nullptr; d_fdr = nullptr; d_teddy = nullptr; d_pair = nullptr; d_slots = nullptr;
     }
 };
 
@@ -880,6 +895,20 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         d.nood_len = v.nood_len;
         d.nood_id = v.nood_id;
     }
+    d.tK = 0;
+    if (turbo::build(v, im->turbo_tabs)) {
+        const turbo::Tables &tt = im->turbo_tabs;
+        if (cudaMalloc((void **)&im->d_pair, tt.pair.size() * 8) != cudaSuccess ||
+            cudaMalloc((void **)&im->d_slots, tt.slots.size() * sizeof(turbo::Slot)) != cudaSuccess) {
+            im->release(); delete im; return HS_NOMEM;
+        }
+        cudaMemcpyAsync(im->d_pair, tt.pair.data(), tt.pair.size() * 8, cudaMemcpyHostToDevice, s->stream);
+        cudaMemcpyAsync(im->d_slots, tt.slots.data(), tt.slots.size() * sizeof(turbo::Slot), cudaMemcpyHostToDevice, s->stream);
+        im->device_bytes += tt.pair.size() * 8 + tt.slots.size() * sizeof(turbo::Slot);
+        d.pair_tab = im->d_pair;
+        d.slots = im->d_slots;
+        d.tK = tt.K; d.tH1 = tt.H1; d.tH2 = tt.H2;
+    }
     if (cudaStreamSynchronize(s->stream) != cudaSuccess) { im->release(); delete im; return HS_UNKNOWN_ERROR; }
     s->dbs.push_back(im);
     *out = im;
@@ -895,6 +924,22 @@ void build_strip_first(const u64 *off, u32 count, u64 total, std::vector<u32> &o
         while (b + 1 < count && off[b + 1] <= pos) b++;
         out[s] = b;
     }
+}
+
+template <int K>
+hs_error_t launch_turbo(hs_gpu_scratch *s, const DevDb &db, const DevCorpus &cp, const DevArena &ar) {
+    const size_t dyn = ((size_t)8 << db.tH1) + sizeof(TurboWarpShared) * TWARPS;
+    static size_t configured = 0;
+    if (dyn > configured) {
+        CU_OK(cudaFuncSetAttribute(k_turbo<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+        configured = dyn;
+    }
+    u32 grid = s->opt_grid > 0 ? (u32)s->opt_grid : (u32)s->sm_count;
+    const u32 need = (cp.nstrips + TWARPS - 1) / TWARPS;
+    if (grid > need) grid = need ? need : 1;
+    k_turbo<K><<<grid, TTHREADS, dyn, s->stream>>>(db, cp, ar);
+    CU_OK(cudaGetLastError());
+    return HS_SUCCESS;
 }
 
 template <class FE, bool NOODLE>
@@ -939,6 +984,15 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
         DevArena ar{s->recs.p, s->d_ctl + 0, s->d_ctl + 1, reinterpret_cast<u32 *>(s->d_ctl + 3), s->recs.cap};
         hs_error_t rv;
         CU_OK(cudaEventRecord(s->ev[6], s->stream));
+        const bool use_turbo = im->dev.tK && s->opt_frontend != 1;
+        if (use_turbo) {
+            switch (im->dev.tK) {
+            case 1: rv = launch_turbo<1>(s, im->dev, cp, ar); break;
+            case 2: rv = launch_turbo<2>(s, im->dev, cp, ar); break;
+            case 3: rv = launch_turbo<3>(s, im->dev, cp, ar); break;
+            default: rv = launch_turbo<4>(s, im->dev, cp, ar); break;
+            }
+        } else
         switch (im->view.kind) {
         case ENG_FDR: rv = launch_scan<FdrNative, false>(s, im->dev, cp, ar); break;
         case ENG_TEDDY: rv = launch_scan<TeddyNative, false>(s, im->dev, cp, ar); break;

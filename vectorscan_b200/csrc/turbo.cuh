@@ -1,0 +1,192 @@
+// turbo.cuh -- the "turbo" front end and its confirm (included by hs_gpu.cu; see turbo_tables.h for the
+// tables).  Same strip/row/chunk geometry as k_scan; differences:
+//   * one 8-byte shared-memory lookup filters TWO end positions (pair table), ~5 ALU ops per position;
+//   * 24 warps per SM share the one table, the next row's LDG.128 is issued before the current row is
+//     processed (software prefetch: ~24 x 2 x 512 B in flight per SM);
+//   * candidates are queued as bare positions; the drain step (one lane per candidate, all lanes busy) reloads
+//     the 8-byte window from L1/L2, probes the slot table (one 32-byte L2 read per probe) and compares
+//     (window & msk) == v exactly as confWithBit does; only then is the buffer looked up for the size check.
+#pragma once
+
+constexpr int TWARPS = 24;
+constexpr int TTHREADS = TWARPS * 32;
+constexpr int TQCAP = 192;   // queued candidate positions per warp
+constexpr int TSTAGE = 32;   // staged match records per warp
+
+struct TurboWarpShared {
+    u32 q[TQCAP];
+    Rec stage[TSTAGE];
+    u32 stage_n;
+    u32 pad[3];
+};
+
+__device__ __forceinline__ void turbo_hit(const Ctx &c, const uint4 &b, u64 g) {
+    const BufRef br = find_buffer(c.cp, (u32)(g / STRIP_BYTES), g);
+    if (!passes_gates(c.db, br.len)) return;
+    const u32 i = (u32)(g - br.start);
+    const u32 size = b.w & 0xff, kind = (b.w >> 8) & 0xf;
+    if (size > i + 1) return;  // the literal would start before its buffer (fdr_confirm_runtime.h:77-88)
+    const u8 *btext = c.cp.text + br.start;
+    if (kind == turbo::SLOT_REPORT) {
+        emit(c, br.idx, i + 1, b.y, 0);
+    } else if (kind == turbo::SLOT_PROGRAM) {
+        run_program(c, b.y, br.idx, btext, br.len, i + 1);
+    } else if (check_literal(c.db.bc, b.z, b.w >> 16, kind == turbo::SLOT_LIT_NOCASE_REPORT, btext, i + 1)) {
+        emit(c, br.idx, i + 1, b.y, 0);
+    }
+}
+
+__device__ __forceinline__ void turbo_confirm(const Ctx &c, u64 g, u32 &n_probe) {
+    if (g >= c.cp.total) return;
+    const u64 w = load_tail8(c.cp.text, g);
+    const u32 key = (u32)(w >> (64 - 8 * c.db.tK));
+    const u32 mask = (1u << c.db.tH2) - 1;
+    u32 h = turbo::slot_home(key, c.db.tH2);
+    const uint4 *slots = reinterpret_cast<const uint4 *>(c.db.slots);
+    for (;;) {
+        const uint4 b = __ldg(slots + 2 * (size_t)h + 1);  // key, target, lit_off, meta
+        if (!((b.w >> 8) & 0xf)) break;
+        n_probe++;
+        if (b.x == key) {
+            const uint4 a = __ldg(slots + 2 * (size_t)h);  // v, msk
+            const u64 v = ((u64)a.y << 32) | a.x, m = ((u64)a.w << 32) | a.z;
+            if ((w & m) == v) turbo_hit(c, b, g);
+        }
+        h = (h + 1) & mask;
+    }
+}
+
+__device__ void turbo_drain(const Ctx &c, u64 span_base, u32 count, u32 &n_probe) {
+    for (u32 base = 0; base < count; base += 32) {
+        const u32 idx = base + lane_id();
+        if (idx < count) turbo_confirm(c, span_base + c.q[idx], n_probe);
+        __syncwarp();
+        if (*(volatile u32 *)c.stage_n >= c.stage_cap / 2) flush_stage(c);
+    }
+}
+
+// register whose low byte is extended-chunk byte `e` (E = {8 bytes before the chunk, the chunk})
+template <int e>
+__device__ __forceinline__ u32 byte_reg(const u32 E[6]) {
+    if ((e & 3) == 0) return E[e >> 2];
+    return __funnelshift_r(E[e >> 2], (e >> 2) + 1 <= 5 ? E[(e >> 2) + 1] : 0u, 8 * (e & 3));
+}
+
+// K-1 shared bytes of the pair ending at chunk byte i, packed as turbo::pack_shared packs them.
+// The packing puts text[i-2] in the low byte, so x(i) doubles as the shift-amount register for the B test
+// of pair i-2 and (K == 4) the A test of pair i+2: a funnel shift only looks at the low 5 bits.
+template <int K, int i>
+__device__ __forceinline__ u32 shared_reg(const u32 E[6]) {
+    if (K < 2) return 0;
+    constexpr int eS = i - K + 1 + 8, wS = eS >> 2, o = eS & 3;
+    constexpr u32 sel = K == 4 ? (u32)((o + 1) | (o << 4) | ((o + 2) << 8) | ((o + 2) << 12))
+                      : K == 3 ? (u32)(o | ((o + 1) << 4) | (o << 8) | ((o + 1) << 12))
+                               : (u32)(o * 0x1111);
+    return __byte_perm(E[wS], wS + 1 <= 5 ? E[wS + 1] : 0u, sel);
+}
+
+template <int K, int i>
+__device__ __forceinline__ void turbo_pair(const u64 *tab, u32 H1shift, const u32 E[6], const u32 (&x)[10], u32 &acc) {
+    // x[j] = shared_reg<K, 2j - 1>
+    const u32 row = (x[(i + 1) / 2] * turbo::PAIR_MULT) >> H1shift;
+    const u64 ent = tab[row];
+    u32 yA, yB;
+    if (K == 4) yA = x[(i - 1) / 2]; else yA = byte_reg<i - K + 8>(E);       // low 5 bits of text[i-K]
+    if ((K == 4 || K == 3) && i < 15) yB = x[(i + 3) / 2]; else yB = byte_reg<i + 8>(E);  // text[i]
+    // the table stores each 32-bit set bit-reversed: shifting left by low5(byte) brings the flag to bit 31,
+    // and a funnel shift by one appends it to the candidate mask (first position ends up in the top bit)
+    const u32 ra = __funnelshift_l(0u, (u32)ent, yA);
+    acc = __funnelshift_l(ra, acc, 1);
+    const u32 rb = __funnelshift_l(0u, (u32)(ent >> 32), yB);
+    acc = __funnelshift_l(rb, acc, 1);
+}
+
+// 16 end positions of one chunk -> candidate mask, bit (15 - j) = end position j is a candidate
+template <int K>
+__device__ __forceinline__ u32 turbo_chunk(const u64 *tab, u32 H1shift, const u32 E[6]) {
+    u32 x[10];
+    x[0] = shared_reg<K, -1>(E); x[1] = shared_reg<K, 1>(E); x[2] = shared_reg<K, 3>(E); x[3] = shared_reg<K, 5>(E);
+    x[4] = shared_reg<K, 7>(E); x[5] = shared_reg<K, 9>(E); x[6] = shared_reg<K, 11>(E); x[7] = shared_reg<K, 13>(E);
+    x[8] = shared_reg<K, 15>(E); x[9] = 0;
+    u32 acc = 0;
+    turbo_pair<K, 1>(tab, H1shift, E, x, acc); turbo_pair<K, 3>(tab, H1shift, E, x, acc);
+    turbo_pair<K, 5>(tab, H1shift, E, x, acc); turbo_pair<K, 7>(tab, H1shift, E, x, acc);
+    turbo_pair<K, 9>(tab, H1shift, E, x, acc); turbo_pair<K, 11>(tab, H1shift, E, x, acc);
+    turbo_pair<K, 13>(tab, H1shift, E, x, acc); turbo_pair<K, 15>(tab, H1shift, E, x, acc);
+    return acc & 0xffffu;
+}
+
+template <int K>
+__global__ void __launch_bounds__(TTHREADS, 1) k_turbo(const DevDb db, const DevCorpus cp, const DevArena ar) {
+    extern __shared__ __align__(16) u8 smem[];
+    u64 *tab = reinterpret_cast<u64 *>(smem);
+    const u32 rows = 1u << db.tH1;
+    TurboWarpShared *wsh = reinterpret_cast<TurboWarpShared *>(smem + (size_t)rows * 8);
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(db.pair_tab);
+        uint4 *dst = reinterpret_cast<uint4 *>(tab);
+        for (u32 i = threadIdx.x; i < rows / 2; i += blockDim.x) dst[i] = src[i];
+    }
+    const u32 warp = threadIdx.x >> 5, ln = lane_id();
+    if (ln == 0) wsh[warp].stage_n = 0;
+    __syncthreads();
+
+    const Ctx c{db, cp, ar, wsh[warp].q, wsh[warp].stage, &wsh[warp].stage_n, TSTAGE, nullptr};
+    const u32 H1shift = 32 - db.tH1;
+    u32 n_cand = 0, n_probe = 0;
+    // every warp of the grid takes one contiguous span of 512-byte rows, balanced to within one row
+    const u64 rows_total = (cp.total + ROW_BYTES - 1) / ROW_BYTES;
+    const u64 W = (u64)gridDim.x * TWARPS, w = (u64)blockIdx.x * TWARPS + warp;
+    const u64 r0 = rows_total * w / W, r1 = rows_total * (w + 1) / W;
+    if (r0 < r1) {
+        const u64 span_base = r0 * ROW_BYTES;
+        u32 qn = 0;
+        const u8 *p = cp.text + span_base + ln * CHUNK;
+        // 8 bytes preceding the span (FRONT_PAD keeps this in bounds at offset 0)
+        const uint2 before = *reinterpret_cast<const uint2 *>(cp.text + span_base - 8);
+        u32 carry2 = before.x, carry3 = before.y;
+        const u32 nrows = (u32)(r1 - r0);
+        uint4 cur = *reinterpret_cast<const uint4 *>(p);
+        for (u32 row = 0; row < nrows; row++) {
+            uint4 nxt = make_uint4(0, 0, 0, 0);
+            if (row + 1 < nrows) nxt = *reinterpret_cast<const uint4 *>(p + (size_t)(row + 1) * ROW_BYTES);
+            u32 p2 = __shfl_up_sync(0xffffffffu, cur.z, 1), p3 = __shfl_up_sync(0xffffffffu, cur.w, 1);
+            if (ln == 0) { p2 = carry2; p3 = carry3; }
+            carry2 = __shfl_sync(0xffffffffu, cur.z, 31);
+            carry3 = __shfl_sync(0xffffffffu, cur.w, 31);
+            const u32 E[6] = {p2, p3, cur.x, cur.y, cur.z, cur.w};
+            u32 m = turbo_chunk<K>(tab, H1shift, E);
+            const u32 pos0 = row * ROW_BYTES + ln * CHUNK;
+            const u64 g0 = span_base + pos0;
+            if (g0 + CHUNK > cp.total) m &= g0 >= cp.total ? 0u : ~((0x10000u >> (int)(cp.total - g0)) - 1);
+            while (__any_sync(0xffffffffu, m != 0)) {
+                const bool has = m != 0;
+                const u32 bal = __ballot_sync(0xffffffffu, has);
+                if (has) {
+                    const u32 top = 31 - __clz(m);  // bit 15 - j
+                    c.q[qn + __popc(bal & ((1u << ln) - 1))] = pos0 + (15 - top);
+                    m ^= 1u << top;
+                }
+                qn += __popc(bal);
+                __syncwarp();
+                if (qn > TQCAP - 32) {
+                    n_cand += qn;
+                    turbo_drain(c, span_base, qn, n_probe);
+                    qn = 0;
+                }
+            }
+            cur = nxt;
+        }
+        if (qn) {
+            n_cand += qn;
+            turbo_drain(c, span_base, qn, n_probe);
+        }
+    }
+    flush_stage(c);
+#pragma unroll
+    for (int d = 16; d; d >>= 1) n_probe += __shfl_down_sync(0xffffffffu, n_probe, d);
+    if (ln == 0) {
+        if (n_cand) atomicAdd(&ar.stats[0], (unsigned long long)n_cand);
+        if (n_probe) atomicAdd(&ar.stats[1], (unsigned long long)n_probe);
+    }
+}

@@ -1,0 +1,157 @@
+// turbo_tables.h -- upload-time re-encoding of a database's literal matcher for the "turbo" front end.
+//
+// the FDR/Teddy front end is only a FILTER (it may over-approximate); exactness is decided
+// by the confirm step ((conf_key & msk) == v, size/history check, groups: src/fdr/fdr_confirm_runtime.h:43-102)
+// and the literal's Rose program.  So the GPU may use any SOUND filter derived from the database's own
+// LitInfo records.  Two structures are derived here from them (nothing else is consulted):
+//
+//  1. PAIR TABLE (shared memory, 2^H1 x 8 bytes).  Let K = min(4, shortest LitInfo.size) and call the last K
+//     bytes of a literal its tail.  Two neighbouring end positions e-1 and e share the K-1 text bytes
+//     S = text[e-K+1 .. e-1].  Row hash(S) holds two 32-bit sets:  A, indexed by the low 5 bits of
+//     text[e-K] (bit set = some tail is text[e-K] + S, i.e. a literal may end at e-1) and B, indexed by the
+//     low 5 bits of text[e] (some tail is S + text[e]: a literal may end at e).  One 8-byte lookup therefore
+//     filters two end positions.  Caseless/masked tail bytes are expanded into all byte values they admit.
+//  2. SLOT TABLE (global memory / L2, open addressing, 32-byte slots).  Keyed by the exact K-byte tail; each
+//     slot carries the LitInfo's v / msk / size and the literal's Rose program pre-decoded when it is one of
+//     the three shapes the compiler emits for plain reports (REPORT | FINAL_REPORT, optionally guarded by one
+//     CHECK_MED_LIT[_NOCASE]); anything else keeps its program offset and is interpreted.
+#pragma once
+#include "hsb_dbview.h"
+
+#include <vector>
+
+namespace hsb {
+namespace turbo {
+
+constexpr u32 PAIR_MULT = 0x9E3779B1u, SLOT_MULT = 0x85EBCA6Bu;
+enum SlotKind : u32 { SLOT_EMPTY = 0, SLOT_REPORT = 1, SLOT_LIT_REPORT = 2, SLOT_LIT_NOCASE_REPORT = 3, SLOT_PROGRAM = 4 };
+
+struct Slot {     // 32 bytes
+    u64 v, msk;   // LitInfo.v / LitInfo.msk (8-byte window ending at the candidate, last byte on top)
+    u32 key;      // the K tail bytes this slot was filed under (first tail byte lowest)
+    u32 target;   // report id (SLOT_*REPORT) or Rose program offset (SLOT_PROGRAM)
+    u32 lit_off;  // bytecode offset of the full literal text (SLOT_LIT_*)
+    u32 meta;     // size | kind << 8 | lit_len << 16
+};
+static_assert(sizeof(Slot) == 32, "slot layout");
+
+// K-1 shared bytes packed the way the kernel's PRMT selectors pack them
+HSB_HD u32 pack_shared(u32 K, u32 s0, u32 s1, u32 s2) {
+    switch (K) {
+    case 4: return s1 | (s0 << 8) | (s2 << 16) | (s2 << 24);
+    case 3: return s0 | (s1 << 8) | (s0 << 16) | (s1 << 24);
+    case 2: return s0 * 0x01010101u;
+    default: return 0;
+    }
+}
+HSB_HD u32 pair_row(u32 packed, u32 H1) { return (packed * PAIR_MULT) >> (32 - H1); }
+HSB_HD u32 slot_home(u32 key, u32 H2) { return (key * SLOT_MULT) >> (32 - H2); }
+
+struct Tables {
+    u32 K = 0, H1 = 0, H2 = 0;
+    std::vector<u64> pair;   // low 32 bits = A, high 32 bits = B
+    std::vector<Slot> slots;
+    u64 variants = 0;
+};
+
+// Decode the shapes  [CHECK_MED_LIT*] (REPORT|FINAL_REPORT) [END]  with offset_adjust 0.
+inline void predecode(const DbView &d, u32 prog, Slot &s, u32 size) {
+    u32 kind = SLOT_PROGRAM, target = prog, lit_off = 0, lit_len = 0;
+    size_t pc = prog;
+    u8 code = rd8(d.bc, pc);
+    bool has_lit = false, nocase = false, ok = true;
+    if (code == op::CHECK_MED_LIT || code == op::CHECK_MED_LIT_NOCASE) {
+        has_lit = true;
+        nocase = code == op::CHECK_MED_LIT_NOCASE;
+        lit_off = rd32(d.bc, pc + op::check_lit::lit_offset);
+        lit_len = rd32(d.bc, pc + op::check_lit::lit_length);
+        const u32 fail = rd32(d.bc, pc + op::check_lit::fail_jump);
+        // the failure target must be END (nothing else would run)
+        ok = lit_len < 65536 && in_range(d, pc + fail, 8) && rd8(d.bc, pc + fail) == op::END;
+        pc += op::check_lit::SIZE;
+        code = rd8(d.bc, pc);
+    }
+    if (ok && (code == op::REPORT || code == op::FINAL_REPORT) &&
+        rd32(d.bc, pc + op::report::offset_adjust) == 0 &&
+        (code == op::FINAL_REPORT || rd8(d.bc, pc + op::report::SIZE) == op::END)) {
+        kind = has_lit ? (nocase ? SLOT_LIT_NOCASE_REPORT : SLOT_LIT_REPORT) : SLOT_REPORT;
+        target = rd32(d.bc, pc + op::report::onmatch);
+    } else {
+        lit_off = lit_len = 0;
+    }
+    s.target = target;
+    s.lit_off = lit_off;
+    s.meta = size | (kind << 8) | (lit_len << 16);
+}
+
+inline bool build(const DbView &d, Tables &t) {
+    std::vector<LitRec> lits = d.lits;
+    if (d.kind == ENG_NOODLE) {  // the single literal, brought to LitInfo form
+        LitRec lr{};
+        const u32 sh = 8 * (8 - d.nood_len);
+        lr.v = d.nood_cmp << sh;
+        lr.msk = d.nood_msk << sh;
+        lr.groups = ~0ull;
+        lr.program = d.nood_id;
+        lr.size = (u8)d.nood_len;
+        lits.push_back(lr);
+    }
+    u32 K = 4;
+    std::vector<const LitRec *> live;
+    for (const LitRec &l : lits) {
+        if (!(l.groups & (d.kind == ENG_NOODLE ? ~0ull : d.groups))) continue;
+        if (l.size < 1 || l.size > 8) return false;
+        K = std::min<u32>(K, l.size);
+        live.push_back(&l);
+    }
+    if (live.empty()) return false;
+    t.K = K;
+    // enumerate tail variants
+    struct Var { u32 key; const LitRec *lit; };
+    std::vector<Var> vars;
+    for (const LitRec *l : live) {
+        std::vector<u32> keys{0};
+        for (u32 j = 0; j < K; j++) {
+            const u32 sh = 8 * (8 - K + j);
+            const u8 m = (u8)(l->msk >> sh), val = (u8)(l->v >> sh);
+            std::vector<u32> next;
+            for (u32 c = 0; c < 256; c++)
+                if ((c & m) == val)
+                    for (u32 k : keys) next.push_back(k | (c << (8 * j)));
+            if (next.empty() || next.size() > 4096) return false;
+            keys.swap(next);
+        }
+        for (u32 k : keys) vars.push_back({k, l});
+        if (vars.size() > (1u << 22)) return false;
+    }
+    t.variants = vars.size();
+    t.H1 = vars.size() >= 512 ? 14 : (vars.size() >= 64 ? 12 : 10);
+    t.pair.assign((size_t)1 << t.H1, 0);
+    for (const Var &v : vars) {
+        u32 b[4] = {0, 0, 0, 0};
+        for (u32 j = 0; j < K; j++) b[j] = (v.key >> (8 * j)) & 0xff;
+        // A: extra byte first (b[0]), shared = b[1..K-1];  B: shared = b[0..K-2], extra byte last (b[K-1])
+        const u32 sa = pack_shared(K, b[1], b[2], b[3]), sb = pack_shared(K, b[0], b[1], b[2]);
+        t.pair[pair_row(sa, t.H1)] |= 1ull << (31 - (b[0] & 31));  // sets are stored bit-reversed (turbo.cuh)
+        t.pair[pair_row(sb, t.H1)] |= 1ull << (63 - (b[K - 1] & 31));
+    }
+    u32 H2 = 4;
+    while (((size_t)1 << H2) < vars.size() * 4) H2++;
+    if (H2 > 26) return false;
+    t.H2 = H2;
+    t.slots.assign((size_t)1 << H2, Slot{0, 0, 0, 0, 0, 0});
+    const u32 mask = (1u << H2) - 1;
+    for (const Var &v : vars) {
+        u32 h = slot_home(v.key, H2);
+        while ((t.slots[h].meta >> 8) & 0xf) h = (h + 1) & mask;
+        Slot &s = t.slots[h];
+        s.v = v.lit->v;
+        s.msk = v.lit->msk;
+        s.key = v.key;
+        predecode(d, v.lit->program, s, v.lit->size);
+    }
+    return true;
+}
+
+}  // namespace turbo
+}  // namespace hsb
