@@ -104,6 +104,17 @@ struct DevArena {
     unsigned long long *stats;  // [0] candidates, [1] confirm probes
     u32 *error;                 // sticky device-side error flag
     u64 cap;
+    // ordered (segmented) mode: warp w of the grid owns recs[w * seg_cap, (w + 1) * seg_cap) and appends in
+    // position order; seg_count[w] = records it wanted
+    u32 *seg_count;
+    u32 seg_cap;
+};
+
+constexpr u32 ERR_BAD_OPCODE = 1, ERR_BAD_DEDUPE = 2, ERR_PROGRAM_LOOP = 4, ERR_COLLECTOR = 8, ERR_UNSORTED = 16;
+
+struct Collector {  // per-lane, per-candidate match buffer of the ordered mode
+    Rec r[4];
+    u32 n;
 };
 
 struct WarpShared {
@@ -142,10 +153,16 @@ struct Ctx {
     u32 *stage_n;
     u32 stage_cap;
     const ConfHdr *conf;
+    Collector *col;  // non-null: ordered mode, emit() collects instead of staging
 };
 
 __device__ __forceinline__ void emit(const Ctx &c, u32 buf, u32 to, u32 id, u32 aux) {
     Rec r{buf, to, id, aux};
+    if (c.col) {
+        if (c.col->n < 4) c.col->r[c.col->n] = r; else atomicOr(c.ar.error, ERR_COLLECTOR);
+        c.col->n++;
+        return;
+    }
     u32 slot = atomicAdd(c.stage_n, 1u);
     if (slot < c.stage_cap) {
         c.stage[slot] = r;
@@ -299,6 +316,7 @@ __device__ void run_program(const Ctx &c, u32 prog, u32 buf, const u8 *btext, u3
             break;
         }
         case op::REPORT:
+            if (c.col && ld32(bc, pc + op::report::offset_adjust)) atomicOr(c.ar.error, ERR_UNSORTED);
             emit(c, buf, (u32)((int)to + (int)ld32(bc, pc + op::report::offset_adjust)),
                  ld32(bc, pc + op::report::onmatch), 0);
             pc += op::report::SIZE;
@@ -632,7 +650,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_scan(const DevDb db, const DevCo
     if (ln == 0) wsh[warp].stage_n = 0;
     __syncthreads();
 
-    const Ctx c{db, cp, ar, wsh[warp].q, wsh[warp].stage, &wsh[warp].stage_n, STAGE_CAP, conf};
+    const Ctx c{db, cp, ar, wsh[warp].q, wsh[warp].stage, &wsh[warp].stage_n, STAGE_CAP, conf, nullptr};
     u32 n_cand = 0, n_probe = 0;
     const u32 warps_total = gridDim.x * WARPS;
     for (u32 strip = blockIdx.x * WARPS + warp; strip < cp.nstrips; strip += warps_total) {
@@ -763,6 +781,7 @@ struct DbImage {  // one uploaded database
     u64 *d_pair = nullptr;
     turbo::Slot *d_slots = nullptr;
     turbo::Tables turbo_tabs;
+    bool ordered_ok = true;
     size_t device_bytes = 0;
     void release() {
         if (d_bc) cudaFree(d_bc);
@@ -804,6 +823,9 @@ struct hs_gpu_scratch {
     DevBuf<Rec> recs, recs2;
     DevBuf<hs_gpu_match_t> d_matches;
     DevBuf<u8> cub_tmp, keep;
+    DevBuf<u32> seg_count;
+    u64 seg_cap_hint = 256;
+    long opt_ordered = 1;
     unsigned long long *d_ctl = nullptr;  // [0] arena count, [1] candidates, [2] probes, [3] error(u32), [4] n_selected
     unsigned long long *h_ctl = nullptr;  // pinned mirror
     hs_gpu_match_t *h_matches = nullptr;  // pinned
@@ -926,18 +948,23 @@ void build_strip_first(const u64 *off, u32 count, u64 total, std::vector<u32> &o
     }
 }
 
-template <int K>
+u32 turbo_grid(const hs_gpu_scratch *s, const DevCorpus &cp) {
+    u32 grid = s->opt_grid > 0 ? (u32)s->opt_grid : (u32)s->sm_count;
+    if (grid > 170) grid = 170;  // k_compact scans at most 4096 warp segments
+    const u32 need = (cp.nstrips + TWARPS - 1) / TWARPS;
+    if (grid > need) grid = need ? need : 1;
+    return grid;
+}
+
+template <int K, bool ORDERED>
 hs_error_t launch_turbo(hs_gpu_scratch *s, const DevDb &db, const DevCorpus &cp, const DevArena &ar) {
     const size_t dyn = ((size_t)8 << db.tH1) + sizeof(TurboWarpShared) * TWARPS;
     static size_t configured = 0;
     if (dyn > configured) {
-        CU_OK(cudaFuncSetAttribute(k_turbo<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+        CU_OK(cudaFuncSetAttribute(k_turbo<K, ORDERED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
         configured = dyn;
     }
-    u32 grid = s->opt_grid > 0 ? (u32)s->opt_grid : (u32)s->sm_count;
-    const u32 need = (cp.nstrips + TWARPS - 1) / TWARPS;
-    if (grid > need) grid = need ? need : 1;
-    k_turbo<K><<<grid, TTHREADS, dyn, s->stream>>>(db, cp, ar);
+    k_turbo<K, ORDERED><<<turbo_grid(s, cp), TTHREADS, dyn, s->stream>>>(db, cp, ar);
     CU_OK(cudaGetLastError());
     return HS_SUCCESS;
 }
@@ -958,6 +985,56 @@ hs_error_t launch_scan(hs_gpu_scratch *s, const DevDb &db, const DevCorpus &cp, 
     return HS_SUCCESS;
 }
 
+// Ordered mode: k_turbo<K, true> appends position-ordered records to per-warp segments, k_compact gathers
+// them; no sort.  Returns HS_INSUFFICIENT_SPACE when the general path must be used instead.
+hs_error_t scan_device_ordered(hs_gpu_scratch *s, DbImage *im, const DevCorpus &cp) {
+    hs_gpu_stats_t &st = s->stats;
+    const u32 grid = turbo_grid(s, cp), W = grid * TWARPS;
+    CU_OK(s->seg_count.reserve(W));
+    CU_OK(cudaEventRecord(s->ev[1], s->stream));
+    for (int attempt = 0;; attempt++) {
+        const u64 seg_cap = s->seg_cap_hint;
+        if (seg_cap * W > (1ull << 28)) return HS_INSUFFICIENT_SPACE;  // > 4 GiB of segments: not this mode
+        CU_OK(s->recs.reserve(seg_cap * W));
+        CU_OK(s->recs2.reserve(seg_cap * W));
+        CU_OK(s->d_matches.reserve(seg_cap * W));
+        CU_OK(cudaMemsetAsync(s->d_ctl, 0, 8 * sizeof(unsigned long long), s->stream));
+        DevArena ar{s->recs.p, s->d_ctl + 0, s->d_ctl + 1, reinterpret_cast<u32 *>(s->d_ctl + 3), 0, s->seg_count.p, (u32)seg_cap};
+        CU_OK(cudaEventRecord(s->ev[6], s->stream));
+        hs_error_t rv;
+        switch (im->dev.tK) {
+        case 1: rv = launch_turbo<1, true>(s, im->dev, cp, ar); break;
+        case 2: rv = launch_turbo<2, true>(s, im->dev, cp, ar); break;
+        case 3: rv = launch_turbo<3, true>(s, im->dev, cp, ar); break;
+        default: rv = launch_turbo<4, true>(s, im->dev, cp, ar); break;
+        }
+        if (rv != HS_SUCCESS) return rv;
+        CU_OK(cudaEventRecord(s->ev[7], s->stream));
+        CU_OK(cudaEventRecord(s->ev[2], s->stream));
+        k_compact<<<grid, 256, 0, s->stream>>>(s->recs.p, s->seg_count.p, (u32)seg_cap, W, s->recs2.p, s->d_matches.p, s->d_ctl);
+        CU_OK(cudaGetLastError());
+        st.scan_launches++;
+        st.kernel_launches += 2;
+        CU_OK(cudaMemcpyAsync(s->h_ctl, s->d_ctl, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
+        CU_OK(cudaEventRecord(s->ev[3], s->stream));
+        CU_OK(cudaEventSynchronize(s->ev[3]));
+        const u32 err = (u32)s->h_ctl[3];
+        if (err & ERR_COLLECTOR) { im->ordered_ok = false; return HS_INSUFFICIENT_SPACE; }
+        if (err) return HS_UNKNOWN_ERROR;
+        if (s->h_ctl[5] <= seg_cap) break;
+        if (attempt >= 3) return HS_INSUFFICIENT_SPACE;
+        st.arena_retries++;
+        s->seg_cap_hint = s->h_ctl[5] + s->h_ctl[5] / 2 + 16;
+    }
+    cudaEventElapsedTime(&st.scan_ms, s->ev[1], s->ev[2]);
+    cudaEventElapsedTime(&st.sort_ms, s->ev[2], s->ev[3]);
+    cudaEventElapsedTime(&st.kernel_ms, s->ev[6], s->ev[7]);
+    st.raw_matches = st.matches = s->n_matches = s->h_ctl[4];
+    st.candidates = s->h_ctl[1];
+    st.confirms = s->h_ctl[2];
+    return HS_SUCCESS;
+}
+
 // Device pass over a resident corpus: scan (+ retry on arena growth), sort, dedupe, convert.
 hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corpus) {
     hs_gpu_stats_t &st = s->stats;
@@ -975,22 +1052,29 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
         st.scan_ms = st.sort_ms = st.kernel_ms = 0;
         return HS_SUCCESS;
     }
-    CU_OK(s->recs.reserve(s->arena_hint));
     const DevCorpus cp = corpus.dev();
+    // ---- ordered fast path: turbo front end, every program pre-decoded, no dedupe / exhaustion keys ----
+    if (im->dev.tK && s->opt_frontend != 1 && im->ordered_ok && im->turbo_tabs.all_simple && !im->view.dkey_count &&
+        !im->view.ekey_count && s->opt_ordered) {
+        hs_error_t orv = scan_device_ordered(s, im, cp);
+        if (orv != HS_INSUFFICIENT_SPACE) return orv;
+        // fell out of the ordered mode's envelope (collector or segment bounds): use the general path below
+    }
+    CU_OK(s->recs.reserve(s->arena_hint));
     u64 raw = 0;
     CU_OK(cudaEventRecord(s->ev[1], s->stream));
     for (int attempt = 0;; attempt++) {
         CU_OK(cudaMemsetAsync(s->d_ctl, 0, 8 * sizeof(unsigned long long), s->stream));
-        DevArena ar{s->recs.p, s->d_ctl + 0, s->d_ctl + 1, reinterpret_cast<u32 *>(s->d_ctl + 3), s->recs.cap};
+        DevArena ar{s->recs.p, s->d_ctl + 0, s->d_ctl + 1, reinterpret_cast<u32 *>(s->d_ctl + 3), s->recs.cap, nullptr, 0};
         hs_error_t rv;
         CU_OK(cudaEventRecord(s->ev[6], s->stream));
         const bool use_turbo = im->dev.tK && s->opt_frontend != 1;
         if (use_turbo) {
             switch (im->dev.tK) {
-            case 1: rv = launch_turbo<1>(s, im->dev, cp, ar); break;
-            case 2: rv = launch_turbo<2>(s, im->dev, cp, ar); break;
-            case 3: rv = launch_turbo<3>(s, im->dev, cp, ar); break;
-            default: rv = launch_turbo<4>(s, im->dev, cp, ar); break;
+            case 1: rv = launch_turbo<1, false>(s, im->dev, cp, ar); break;
+            case 2: rv = launch_turbo<2, false>(s, im->dev, cp, ar); break;
+            case 3: rv = launch_turbo<3, false>(s, im->dev, cp, ar); break;
+            default: rv = launch_turbo<4, false>(s, im->dev, cp, ar); break;
             }
         } else
         switch (im->view.kind) {
@@ -1304,6 +1388,7 @@ hs_error_t hs_gpu_free_scratch(hs_gpu_scratch_t *s) {
     s->d_matches.release();
     s->cub_tmp.release();
     s->keep.release();
+    s->seg_count.release();
     if (s->h_stage) cudaFreeHost(s->h_stage);
     if (s->h_matches) cudaFreeHost(s->h_matches);
     if (s->h_ctl) cudaFreeHost(s->h_ctl);
@@ -1476,6 +1561,8 @@ hs_error_t hs_gpu_set_option(hs_gpu_scratch_t *scratch, const char *name, long v
     if (!scratch || scratch->magic != 0x47505553 || !name) return HS_INVALID;
     if (!strcmp(name, "frontend")) { scratch->opt_frontend = value; return HS_SUCCESS; }
     if (!strcmp(name, "grid")) { scratch->opt_grid = value; return HS_SUCCESS; }
+    if (!strcmp(name, "ordered")) { scratch->opt_ordered = value; return HS_SUCCESS; }
+    if (!strcmp(name, "segment")) { scratch->seg_cap_hint = value > 0 ? (u64)value : 1; return HS_SUCCESS; }
     if (!strcmp(name, "arena")) { scratch->arena_hint = value > 0 ? (u64)value : 1; return HS_SUCCESS; }
     return HS_INVALID;
 }

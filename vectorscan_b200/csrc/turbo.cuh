@@ -10,7 +10,7 @@
 
 constexpr int TWARPS = 24;
 constexpr int TTHREADS = TWARPS * 32;
-constexpr int TQCAP = 192;   // queued candidate positions per warp
+constexpr int TQCAP = 544;   // queued candidate positions per warp: a full row (512) after a < 32 remainder
 constexpr int TSTAGE = 32;   // staged match records per warp
 
 struct TurboWarpShared {
@@ -56,12 +56,34 @@ __device__ __forceinline__ void turbo_confirm(const Ctx &c, u64 g, u32 &n_probe)
     }
 }
 
-__device__ void turbo_drain(const Ctx &c, u64 span_base, u32 count, u32 &n_probe) {
+// Warp-synchronous drain of `count` queued positions (ascending), one lane per candidate.
+// ORDERED: every lane collects its candidate's records, a warp prefix sum keeps them in position order and
+// they are appended to the warp's own arena segment (no staging, no atomics).
+template <bool ORDERED>
+__device__ void turbo_drain(const Ctx &c, u64 span_base, u32 count, u32 &n_probe, Rec *seg, u32 &cursor) {
     for (u32 base = 0; base < count; base += 32) {
         const u32 idx = base + lane_id();
-        if (idx < count) turbo_confirm(c, span_base + c.q[idx], n_probe);
-        __syncwarp();
-        if (*(volatile u32 *)c.stage_n >= c.stage_cap / 2) flush_stage(c);
+        if (ORDERED) {
+            Collector col;
+            col.n = 0;
+            const Ctx cc{c.db, c.cp, c.ar, c.q, c.stage, c.stage_n, c.stage_cap, c.conf, &col};
+            if (idx < count) turbo_confirm(cc, span_base + c.q[idx], n_probe);
+            const u32 n = col.n < 4 ? col.n : 4;
+            u32 incl = n;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const u32 t = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane_id() >= (u32)d) incl += t;
+            }
+            const u32 at = cursor + incl - n;
+            for (u32 k = 0; k < n; k++)
+                if (at + k < c.ar.seg_cap) seg[at + k] = col.r[k];
+            cursor += __shfl_sync(0xffffffffu, incl, 31);
+        } else {
+            if (idx < count) turbo_confirm(c, span_base + c.q[idx], n_probe);
+            __syncwarp();
+            if (*(volatile u32 *)c.stage_n >= c.stage_cap / 2) flush_stage(c);
+        }
     }
 }
 
@@ -116,7 +138,7 @@ __device__ __forceinline__ u32 turbo_chunk(const u64 *tab, u32 H1shift, const u3
     return acc & 0xffffu;
 }
 
-template <int K>
+template <int K, bool ORDERED>
 __global__ void __launch_bounds__(TTHREADS, 1) k_turbo(const DevDb db, const DevCorpus cp, const DevArena ar) {
     extern __shared__ __align__(16) u8 smem[];
     u64 *tab = reinterpret_cast<u64 *>(smem);
@@ -131,13 +153,15 @@ __global__ void __launch_bounds__(TTHREADS, 1) k_turbo(const DevDb db, const Dev
     if (ln == 0) wsh[warp].stage_n = 0;
     __syncthreads();
 
-    const Ctx c{db, cp, ar, wsh[warp].q, wsh[warp].stage, &wsh[warp].stage_n, TSTAGE, nullptr};
+    const Ctx c{db, cp, ar, wsh[warp].q, wsh[warp].stage, &wsh[warp].stage_n, TSTAGE, nullptr, nullptr};
     const u32 H1shift = 32 - db.tH1;
     u32 n_cand = 0, n_probe = 0;
     // every warp of the grid takes one contiguous span of 512-byte rows, balanced to within one row
     const u64 rows_total = (cp.total + ROW_BYTES - 1) / ROW_BYTES;
     const u64 W = (u64)gridDim.x * TWARPS, w = (u64)blockIdx.x * TWARPS + warp;
     const u64 r0 = rows_total * w / W, r1 = rows_total * (w + 1) / W;
+    Rec *seg = ORDERED ? ar.recs + (size_t)w * ar.seg_cap : nullptr;
+    u32 cursor = 0;
     if (r0 < r1) {
         const u64 span_base = r0 * ROW_BYTES;
         u32 qn = 0;
@@ -159,34 +183,92 @@ __global__ void __launch_bounds__(TTHREADS, 1) k_turbo(const DevDb db, const Dev
             const u32 pos0 = row * ROW_BYTES + ln * CHUNK;
             const u64 g0 = span_base + pos0;
             if (g0 + CHUNK > cp.total) m &= g0 >= cp.total ? 0u : ~((0x10000u >> (int)(cp.total - g0)) - 1);
-            while (__any_sync(0xffffffffu, m != 0)) {
-                const bool has = m != 0;
-                const u32 bal = __ballot_sync(0xffffffffu, has);
-                if (has) {
-                    const u32 top = 31 - __clz(m);  // bit 15 - j
-                    c.q[qn + __popc(bal & ((1u << ln) - 1))] = pos0 + (15 - top);
+            if (__any_sync(0xffffffffu, m != 0)) {
+                // append this row's candidates in position order: lane order, then descending bit = ascending byte
+                const u32 n = __popc(m);
+                u32 incl = n;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const u32 t = __shfl_up_sync(0xffffffffu, incl, d);
+                    if (ln >= (u32)d) incl += t;
+                }
+                u32 slot = qn + incl - n;
+                while (m) {
+                    const u32 top = 31 - __clz(m);
+                    c.q[slot++] = pos0 + (15 - top);
                     m ^= 1u << top;
                 }
-                qn += __popc(bal);
+                qn += __shfl_sync(0xffffffffu, incl, 31);
                 __syncwarp();
-                if (qn > TQCAP - 32) {
-                    n_cand += qn;
-                    turbo_drain(c, span_base, qn, n_probe);
-                    qn = 0;
+                if (qn >= 32) {
+                    const u32 full = qn & ~31u;
+                    n_cand += full;
+                    turbo_drain<ORDERED>(c, span_base, full, n_probe, seg, cursor);
+                    const u32 rem = qn - full;
+                    const u32 keep = ln < rem ? c.q[full + ln] : 0;
+                    __syncwarp();
+                    if (ln < rem) c.q[ln] = keep;
+                    __syncwarp();
+                    qn = rem;
                 }
             }
             cur = nxt;
         }
         if (qn) {
             n_cand += qn;
-            turbo_drain(c, span_base, qn, n_probe);
+            turbo_drain<ORDERED>(c, span_base, qn, n_probe, seg, cursor);
         }
     }
-    flush_stage(c);
+    if (ORDERED) {
+        if (ln == 0) ar.seg_count[w] = cursor;
+    }
+    if (!ORDERED) flush_stage(c);
 #pragma unroll
     for (int d = 16; d; d >>= 1) n_probe += __shfl_down_sync(0xffffffffu, n_probe, d);
     if (ln == 0) {
         if (n_cand) atomicAdd(&ar.stats[0], (unsigned long long)n_cand);
         if (n_probe) atomicAdd(&ar.stats[1], (unsigned long long)n_probe);
+    }
+}
+
+// Ordered mode epilogue: exclusive scan of the per-warp segment counts, then gather the segments into one
+// contiguous, position-ordered array (as Rec and as hs_gpu_match_t).  ctl[4] = records kept, ctl[5] = largest
+// count any warp wanted (> seg_cap means the launch must be repeated with larger segments).
+__global__ void __launch_bounds__(256) k_compact(const Rec *recs, const u32 *seg_count, u32 seg_cap, u32 W, Rec *out_recs,
+                                                 hs_gpu_match_t *out, unsigned long long *ctl) {
+    __shared__ u32 pre[4097];
+    __shared__ u32 part[256];
+    __shared__ u32 mx[256];
+    const u32 per = (W + 255) / 256, t = threadIdx.x;
+    u32 sum = 0, big = 0;
+    for (u32 i = t * per; i < (t + 1) * per && i < W; i++) {
+        const u32 cnt = seg_count[i];
+        big = cnt > big ? cnt : big;
+        sum += cnt < seg_cap ? cnt : seg_cap;
+    }
+    part[t] = sum;
+    mx[t] = big;
+    __syncthreads();
+    if (t == 0) {
+        u32 run = 0, m = 0;
+        for (int i = 0; i < 256; i++) { const u32 v = part[i]; part[i] = run; run += v; m = mx[i] > m ? mx[i] : m; }
+        pre[4096] = run;
+        if (blockIdx.x == 0) { ctl[4] = run; ctl[5] = m; }
+    }
+    __syncthreads();
+    u32 run = part[t];
+    for (u32 i = t * per; i < (t + 1) * per && i < W; i++) {
+        pre[i] = run;
+        const u32 cnt = seg_count[i];
+        run += cnt < seg_cap ? cnt : seg_cap;
+    }
+    __syncthreads();
+    for (u32 w = blockIdx.x; w < W; w += gridDim.x) {
+        const u32 cnt = seg_count[w], n = cnt < seg_cap ? cnt : seg_cap, at = pre[w];
+        for (u32 i = t; i < n; i += 256) {
+            const Rec r = recs[(size_t)w * seg_cap + i];
+            out_recs[at + i] = r;
+            out[at + i] = hs_gpu_match_t{r.buf, r.id, (uint64_t)r.to};
+        }
     }
 }

@@ -18,6 +18,7 @@
 #pragma once
 #include "hsb_dbview.h"
 
+#include <algorithm>
 #include <vector>
 
 namespace hsb {
@@ -52,6 +53,7 @@ struct Tables {
     std::vector<u64> pair;   // low 32 bits = A, high 32 bits = B
     std::vector<Slot> slots;
     u64 variants = 0;
+    bool all_simple = true;  // every literal's program pre-decoded to a plain report (no interpreter needed)
 };
 
 // Decode the shapes  [CHECK_MED_LIT*] (REPORT|FINAL_REPORT) [END]  with offset_adjust 0.
@@ -141,14 +143,22 @@ inline bool build(const DbView &d, Tables &t) {
     t.H2 = H2;
     t.slots.assign((size_t)1 << H2, Slot{0, 0, 0, 0, 0, 0});
     const u32 mask = (1u << H2) - 1;
+    // slots of one key are filed in ascending report id, so a probe walk meets them in (id) order
+    std::vector<Slot> filed;
+    filed.reserve(vars.size());
     for (const Var &v : vars) {
-        u32 h = slot_home(v.key, H2);
-        while ((t.slots[h].meta >> 8) & 0xf) h = (h + 1) & mask;
-        Slot &s = t.slots[h];
-        s.v = v.lit->v;
-        s.msk = v.lit->msk;
-        s.key = v.key;
+        Slot s{v.lit->v, v.lit->msk, v.key, 0, 0, 0};
         predecode(d, v.lit->program, s, v.lit->size);
+        if (((s.meta >> 8) & 0xf) == SLOT_PROGRAM) t.all_simple = false;
+        filed.push_back(s);
+    }
+    std::stable_sort(filed.begin(), filed.end(), [](const Slot &a, const Slot &b) {
+        return a.key != b.key ? a.key < b.key : a.target < b.target;
+    });
+    for (const Slot &s : filed) {
+        u32 h = slot_home(s.key, H2);
+        while ((t.slots[h].meta >> 8) & 0xf) h = (h + 1) & mask;
+        t.slots[h] = s;
     }
     return true;
 }
