@@ -57,6 +57,7 @@ constexpr int STRIP_ROWS = 32;
 constexpr int STRIP_BYTES = STRIP_ROWS * ROW_BYTES;  // 16 KiB per warp strip
 constexpr int QCAP = 1024;                     // candidate queue entries per warp
 constexpr int STAGE_CAP = 96;                  // staged match records per warp
+constexpr int CELL_BYTES = 1024;               // granularity of the position -> buffer index
 constexpr size_t FRONT_PAD = 1024, BACK_PAD = 2048;  // zero bytes around the flat text in HBM
 
 struct __align__(16) Rec {  // device match record
@@ -86,13 +87,14 @@ struct DevDb {
     // turbo front end (turbo_tables.h); tK == 0 when not built
     const u64 *pair_tab;
     const turbo::Slot *slots;
-    u32 tK, tH1, tH2;
+    const u32 *bloom;     // second filter tier (turbo_tables.h, 3.)
+    u32 tK, tH1, tH2, tL, tBL;
 };
 
 struct DevCorpus {
     const u8 *text;          // FRONT_PAD zero bytes precede, BACK_PAD follow
     const u64 *off;          // count + 1 offsets
-    const u32 *strip_first;  // nstrips + 1: buffer containing the first byte of each strip
+    const u32 *cell_first;   // ncells + 1: buffer containing the first byte of each CELL_BYTES cell
     u64 total;
     u32 count;
     u32 nstrips;
@@ -357,8 +359,14 @@ struct BufRef {
     u32 len;
 };
 
-__device__ __forceinline__ BufRef find_buffer(const DevCorpus &cp, u32 strip, u64 g) {
-    u32 lo = cp.strip_first[strip], hi = cp.strip_first[strip + 1];
+__device__ __forceinline__ BufRef find_buffer(const DevCorpus &cp, u32 /*strip*/, u64 g) {
+    const u32 cell = (u32)(g / CELL_BYTES);
+    u32 lo = cp.cell_first[cell], hi = cp.cell_first[cell + 1];
+    if (hi - lo <= 1) {  // common case (buffers of a cell's size or more): three independent loads, no search
+        const u64 o0 = cp.off[lo], o1 = cp.off[lo + 1], o2 = cp.off[hi + 1];
+        if (hi != lo && o1 <= g) return BufRef{hi, o1, (u32)(o2 - o1)};
+        return BufRef{lo, o0, (u32)(o1 - o0)};
+    }
     // largest b in [lo, hi] with off[b] <= g
     while (lo < hi) {
         u32 mid = (lo + hi + 1) >> 1;
@@ -780,6 +788,7 @@ struct DbImage {  // one uploaded database
     u32 *d_teddy = nullptr;
     u64 *d_pair = nullptr;
     turbo::Slot *d_slots = nullptr;
+    u32 *d_bloom = nullptr;
     turbo::Tables turbo_tabs;
     bool ordered_ok = true;
     size_t device_bytes = 0;
@@ -789,6 +798,8 @@ struct DbImage {  // one uploaded database
         if (d_teddy) cudaFree(d_teddy);
         if (d_pair) cudaFree(d_pair);
         if (d_slots) cudaFree(d_slots);
+        if (d_bloom) cudaFree(d_bloom);
+        d_bloom = nullptr;
         d_bc = nullptr; d_fdr = nullptr; d_teddy = nullptr; d_pair = nullptr; d_slots = nullptr;
     }
 };
@@ -800,11 +811,11 @@ struct hs_gpu_corpus {
     int device = 0;
     DevBuf<u8> text;          // FRONT_PAD + total + BACK_PAD
     DevBuf<u64> off;
-    DevBuf<u32> strip_first;
+    DevBuf<u32> cell_first;
     u64 total = 0;
     u32 count = 0, nstrips = 0;
     DevCorpus dev() const {
-        return DevCorpus{text.p + FRONT_PAD, off.p, strip_first.p, total, count, nstrips};
+        return DevCorpus{text.p + FRONT_PAD, off.p, cell_first.p, total, count, nstrips};
     }
 };
 
@@ -819,7 +830,7 @@ struct hs_gpu_scratch {
     u8 *h_stage = nullptr;       // pinned host staging
     size_t h_stage_cap = 0;
     std::vector<u64> h_off;
-    std::vector<u32> h_strip_first;
+    std::vector<u32> h_cell_first;
     DevBuf<Rec> recs, recs2;
     DevBuf<hs_gpu_match_t> d_matches;
     DevBuf<u8> cub_tmp, keep;
@@ -921,15 +932,18 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
     if (turbo::build(v, im->turbo_tabs)) {
         const turbo::Tables &tt = im->turbo_tabs;
         if (cudaMalloc((void **)&im->d_pair, tt.pair.size() * 8) != cudaSuccess ||
-            cudaMalloc((void **)&im->d_slots, tt.slots.size() * sizeof(turbo::Slot)) != cudaSuccess) {
+            cudaMalloc((void **)&im->d_slots, tt.slots.size() * sizeof(turbo::Slot)) != cudaSuccess ||
+            cudaMalloc((void **)&im->d_bloom, tt.bloom.size() * 4) != cudaSuccess) {
             im->release(); delete im; return HS_NOMEM;
         }
         cudaMemcpyAsync(im->d_pair, tt.pair.data(), tt.pair.size() * 8, cudaMemcpyHostToDevice, s->stream);
         cudaMemcpyAsync(im->d_slots, tt.slots.data(), tt.slots.size() * sizeof(turbo::Slot), cudaMemcpyHostToDevice, s->stream);
-        im->device_bytes += tt.pair.size() * 8 + tt.slots.size() * sizeof(turbo::Slot);
+        cudaMemcpyAsync(im->d_bloom, tt.bloom.data(), tt.bloom.size() * 4, cudaMemcpyHostToDevice, s->stream);
+        im->device_bytes += tt.pair.size() * 8 + tt.slots.size() * sizeof(turbo::Slot) + tt.bloom.size() * 4;
         d.pair_tab = im->d_pair;
         d.slots = im->d_slots;
-        d.tK = tt.K; d.tH1 = tt.H1; d.tH2 = tt.H2;
+        d.bloom = im->d_bloom;
+        d.tK = tt.K; d.tH1 = tt.H1; d.tH2 = tt.H2; d.tL = tt.L; d.tBL = tt.BL;
     }
     if (cudaStreamSynchronize(s->stream) != cudaSuccess) { im->release(); delete im; return HS_UNKNOWN_ERROR; }
     s->dbs.push_back(im);
@@ -937,12 +951,14 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
     return HS_SUCCESS;
 }
 
-void build_strip_first(const u64 *off, u32 count, u64 total, std::vector<u32> &out, u32 &nstrips) {
+// out[c] = buffer holding the first byte of cell c (CELL_BYTES each), out[ncells] = buffer of the last byte
+void build_cell_first(const u64 *off, u32 count, u64 total, std::vector<u32> &out, u32 &nstrips) {
     nstrips = (u32)((total + STRIP_BYTES - 1) / STRIP_BYTES);
-    out.resize((size_t)nstrips + 1);
+    const u32 ncells = (u32)((total + CELL_BYTES - 1) / CELL_BYTES);
+    out.resize((size_t)ncells + 1);
     u32 b = 0;
-    for (u32 s = 0; s <= nstrips; s++) {
-        u64 pos = std::min<u64>((u64)s * STRIP_BYTES, total ? total - 1 : 0);
+    for (u32 s = 0; s <= ncells; s++) {
+        u64 pos = std::min<u64>((u64)s * CELL_BYTES, total ? total - 1 : 0);
         while (b + 1 < count && off[b + 1] <= pos) b++;
         out[s] = b;
     }
@@ -958,7 +974,7 @@ u32 turbo_grid(const hs_gpu_scratch *s, const DevCorpus &cp) {
 
 template <int K, bool ORDERED>
 hs_error_t launch_turbo(hs_gpu_scratch *s, const DevDb &db, const DevCorpus &cp, const DevArena &ar) {
-    const size_t dyn = ((size_t)8 << db.tH1) + sizeof(TurboWarpShared) * TWARPS;
+    const size_t dyn = turbo_smem_bytes(db);
     static size_t configured = 0;
     if (dyn > configured) {
         CU_OK(cudaFuncSetAttribute(k_turbo<K, ORDERED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
@@ -1215,10 +1231,10 @@ hs_error_t stage_host_buffers(hs_gpu_scratch *s, const char *const *data, const 
     s->h_off[count] = total;
     cp.total = total;
     cp.count = count;
-    build_strip_first(s->h_off.data(), count, total, s->h_strip_first, cp.nstrips);
+    build_cell_first(s->h_off.data(), count, total, s->h_cell_first, cp.nstrips);
     CU_OK(cp.text.reserve(FRONT_PAD + total + BACK_PAD));
     CU_OK(cp.off.reserve((size_t)count + 1));
-    CU_OK(cp.strip_first.reserve((size_t)cp.nstrips + 1));
+    CU_OK(cp.cell_first.reserve(s->h_cell_first.size()));
     const u8 *src = nullptr;
     if (contiguous && count && total) {
         // zero-copy source when the caller's buffers are one pinned region (hs_gpu_host_alloc)
@@ -1249,7 +1265,7 @@ hs_error_t stage_host_buffers(hs_gpu_scratch *s, const char *const *data, const 
     CU_OK(cudaMemsetAsync(cp.text.p + FRONT_PAD + total, 0, BACK_PAD, s->stream));
     if (total) CU_OK(cudaMemcpyAsync(cp.text.p + FRONT_PAD, src, total, cudaMemcpyHostToDevice, s->stream));
     CU_OK(cudaMemcpyAsync(cp.off.p, s->h_off.data(), ((size_t)count + 1) * 8, cudaMemcpyHostToDevice, s->stream));
-    CU_OK(cudaMemcpyAsync(cp.strip_first.p, s->h_strip_first.data(), ((size_t)cp.nstrips + 1) * 4,
+    CU_OK(cudaMemcpyAsync(cp.cell_first.p, s->h_cell_first.data(), s->h_cell_first.size() * 4,
                           cudaMemcpyHostToDevice, s->stream));
     return HS_SUCCESS;
 }
@@ -1367,7 +1383,7 @@ hs_error_t hs_gpu_scratch_size(const hs_gpu_scratch_t *s, size_t *host_bytes, si
     if (!s || s->magic != 0x47505553) return HS_INVALID;
     size_t dev = 8 * sizeof(unsigned long long);
     for (DbImage *im : s->dbs) dev += im->device_bytes;
-    dev += s->staging.text.bytes() + s->staging.off.bytes() + s->staging.strip_first.bytes();
+    dev += s->staging.text.bytes() + s->staging.off.bytes() + s->staging.cell_first.bytes();
     dev += s->recs.bytes() + s->recs2.bytes() + s->d_matches.bytes() + s->cub_tmp.bytes();
     if (host_bytes) *host_bytes = sizeof(*s) + s->h_stage_cap + s->h_matches_cap * sizeof(hs_gpu_match_t);
     if (device_bytes) *device_bytes = dev;
@@ -1382,7 +1398,7 @@ hs_error_t hs_gpu_free_scratch(hs_gpu_scratch_t *s) {
     s->dbs.clear();
     s->staging.text.release();
     s->staging.off.release();
-    s->staging.strip_first.release();
+    s->staging.cell_first.release();
     s->recs.release();
     s->recs2.release();
     s->d_matches.release();
@@ -1479,9 +1495,9 @@ hs_error_t hs_gpu_corpus_create(const char *flat, const uint64_t *offsets, unsig
     c->total = total;
     c->count = count;
     std::vector<u32> sf;
-    build_strip_first(offsets, count, total, sf, c->nstrips);
+    build_cell_first(offsets, count, total, sf, c->nstrips);
     if (c->text.reserve(FRONT_PAD + total + BACK_PAD) != cudaSuccess || c->off.reserve((size_t)count + 1) != cudaSuccess ||
-        c->strip_first.reserve(sf.size()) != cudaSuccess) {
+        c->cell_first.reserve(sf.size()) != cudaSuccess) {
         hs_gpu_corpus_free(c);
         return HS_NOMEM;
     }
@@ -1489,7 +1505,7 @@ hs_error_t hs_gpu_corpus_create(const char *flat, const uint64_t *offsets, unsig
     cudaMemset(c->text.p + FRONT_PAD + total, 0, BACK_PAD);
     if (total) cudaMemcpy(c->text.p + FRONT_PAD, flat, total, cudaMemcpyHostToDevice);
     cudaMemcpy(c->off.p, offsets, ((size_t)count + 1) * 8, cudaMemcpyHostToDevice);
-    cudaMemcpy(c->strip_first.p, sf.data(), sf.size() * 4, cudaMemcpyHostToDevice);
+    cudaMemcpy(c->cell_first.p, sf.data(), sf.size() * 4, cudaMemcpyHostToDevice);
     if (cudaDeviceSynchronize() != cudaSuccess) { hs_gpu_corpus_free(c); return HS_UNKNOWN_ERROR; }
     *out = c;
     return HS_SUCCESS;
@@ -1500,7 +1516,7 @@ hs_error_t hs_gpu_corpus_free(hs_gpu_corpus_t *c) {
     if (c->magic != 0x43525053) return HS_INVALID;
     c->text.release();
     c->off.release();
-    c->strip_first.release();
+    c->cell_first.release();
     c->magic = 0;
     delete c;
     return HS_SUCCESS;

@@ -3,25 +3,32 @@
 //   * one 8-byte shared-memory lookup filters TWO end positions (pair table), ~5 ALU ops per position;
 //   * 24 warps per SM share the one table, the next row's LDG.128 is issued before the current row is
 //     processed (software prefetch: ~24 x 2 x 512 B in flight per SM);
-//   * candidates are queued as bare positions; the drain step (one lane per candidate, all lanes busy) reloads
-//     the 8-byte window from L1/L2, probes the slot table (one 32-byte L2 read per probe) and compares
+//   * tier-1 survivors are queued as bare positions; in batches of 32 (one lane each, all lanes busy) they go
+//     through the tail bloom (tier 2, shared memory); its survivors, again in batches of 32, reload the 8-byte
+//     window from L1/L2, probe the slot table (one 32-byte L2 read pair per probe) and compare
 //     (window & msk) == v exactly as confWithBit does; only then is the buffer looked up for the size check.
 #pragma once
 
 constexpr int TWARPS = 24;
 constexpr int TTHREADS = TWARPS * 32;
-constexpr int TQCAP = 544;   // queued candidate positions per warp: a full row (512) after a < 32 remainder
-constexpr int TSTAGE = 32;   // staged match records per warp
+constexpr int TQ1CAP = 128;  // tier-1 survivors (positions) queued per warp; a fuller row is pushed in passes
+constexpr int TQ2CAP = 64;   // tier-2 survivors awaiting the slot-table confirm
+constexpr int TSTAGE = 32;   // staged match records per warp (general mode)
 
 struct TurboWarpShared {
-    u32 q[TQCAP];
+    u32 q1[TQ1CAP];
+    u32 q2[TQ2CAP];
     Rec stage[TSTAGE];
     u32 stage_n;
     u32 pad[3];
 };
 
+__host__ __device__ inline size_t turbo_smem_bytes(const DevDb &db) {
+    return ((size_t)8 << db.tH1) + ((size_t)4 << (db.tBL - 5)) + sizeof(TurboWarpShared) * TWARPS;
+}
+
 __device__ __forceinline__ void turbo_hit(const Ctx &c, const uint4 &b, u64 g) {
-    const BufRef br = find_buffer(c.cp, (u32)(g / STRIP_BYTES), g);
+    const BufRef br = find_buffer(c.cp, 0, g);
     if (!passes_gates(c.db, br.len)) return;
     const u32 i = (u32)(g - br.start);
     const u32 size = b.w & 0xff, kind = (b.w >> 8) & 0xf;
@@ -37,18 +44,17 @@ __device__ __forceinline__ void turbo_hit(const Ctx &c, const uint4 &b, u64 g) {
 }
 
 __device__ __forceinline__ void turbo_confirm(const Ctx &c, u64 g, u32 &n_probe) {
-    if (g >= c.cp.total) return;
     const u64 w = load_tail8(c.cp.text, g);
     const u32 key = (u32)(w >> (64 - 8 * c.db.tK));
     const u32 mask = (1u << c.db.tH2) - 1;
     u32 h = turbo::slot_home(key, c.db.tH2);
     const uint4 *slots = reinterpret_cast<const uint4 *>(c.db.slots);
     for (;;) {
-        const uint4 b = __ldg(slots + 2 * (size_t)h + 1);  // key, target, lit_off, meta
+        // both halves of the slot in one round trip (v, msk | key, target, lit_off, meta)
+        const uint4 a = __ldg(slots + 2 * (size_t)h), b = __ldg(slots + 2 * (size_t)h + 1);
         if (!((b.w >> 8) & 0xf)) break;
         n_probe++;
         if (b.x == key) {
-            const uint4 a = __ldg(slots + 2 * (size_t)h);  // v, msk
             const u64 v = ((u64)a.y << 32) | a.x, m = ((u64)a.w << 32) | a.z;
             if ((w & m) == v) turbo_hit(c, b, g);
         }
@@ -56,19 +62,33 @@ __device__ __forceinline__ void turbo_confirm(const Ctx &c, u64 g, u32 &n_probe)
     }
 }
 
-// Warp-synchronous drain of `count` queued positions (ascending), one lane per candidate.
+// Second tier: the tail bloom.  True when some literal's exact tail may end at the position whose 8-byte
+// window (last byte on top) is w.
+__device__ __forceinline__ bool turbo_bloom(const u32 *bloom, const DevDb &db, u64 w) {
+    const u32 ks = (u32)(w >> (64 - 8 * db.tK));
+    const u32 b1 = turbo::bloom_bit(ks, 0, db.tK, db.tBL);
+    bool hit = (bloom[b1 >> 5] >> (b1 & 31)) & 1;
+    if (db.tL) {
+        const u64 kl = w >> (64 - 8 * db.tL);
+        const u32 b2 = turbo::bloom_bit((u32)kl, (u32)(kl >> 32), db.tL, db.tBL);
+        hit |= (bool)((bloom[b2 >> 5] >> (b2 & 31)) & 1);
+    }
+    return hit;
+}
+
+// Warp-synchronous confirm of `count` (<= 32) tier-2 survivors c.q2[0..count) (ascending), one lane each.
 // ORDERED: every lane collects its candidate's records, a warp prefix sum keeps them in position order and
 // they are appended to the warp's own arena segment (no staging, no atomics).
 template <bool ORDERED>
-__device__ void turbo_drain(const Ctx &c, u64 span_base, u32 count, u32 &n_probe, Rec *seg, u32 &cursor) {
-    for (u32 base = 0; base < count; base += 32) {
-        const u32 idx = base + lane_id();
-        if (ORDERED) {
-            Collector col;
-            col.n = 0;
-            const Ctx cc{c.db, c.cp, c.ar, c.q, c.stage, c.stage_n, c.stage_cap, c.conf, &col};
-            if (idx < count) turbo_confirm(cc, span_base + c.q[idx], n_probe);
-            const u32 n = col.n < 4 ? col.n : 4;
+__device__ void turbo_drain(const Ctx &c, const u32 *q2, u64 span_base, u32 count, u32 &n_probe, Rec *seg, u32 &cursor) {
+    const u32 idx = lane_id();
+    if (ORDERED) {
+        Collector col;
+        col.n = 0;
+        const Ctx cc{c.db, c.cp, c.ar, c.q, c.stage, c.stage_n, c.stage_cap, c.conf, &col};
+        if (idx < count) turbo_confirm(cc, span_base + q2[idx], n_probe);
+        const u32 n = col.n < 4 ? col.n : 4;
+        if (__any_sync(0xffffffffu, n != 0)) {
             u32 incl = n;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
@@ -79,10 +99,40 @@ __device__ void turbo_drain(const Ctx &c, u64 span_base, u32 count, u32 &n_probe
             for (u32 k = 0; k < n; k++)
                 if (at + k < c.ar.seg_cap) seg[at + k] = col.r[k];
             cursor += __shfl_sync(0xffffffffu, incl, 31);
-        } else {
-            if (idx < count) turbo_confirm(c, span_base + c.q[idx], n_probe);
+        }
+    } else {
+        if (idx < count) turbo_confirm(c, span_base + q2[idx], n_probe);
+        __syncwarp();
+        if (*(volatile u32 *)c.stage_n >= c.stage_cap / 2) flush_stage(c);
+    }
+}
+
+// Warp-synchronous second tier over `count` (multiple of 32, or the final remainder) queued positions
+// q1[0..count): survivors are appended to q2 in order; q2 is confirmed whenever it holds 32.
+template <bool ORDERED>
+__device__ __forceinline__ void turbo_tier2(const Ctx &c, const u32 *bloom, const u32 *q1, u32 *q2, u32 &q2n, u64 span_base,
+                                            u32 count, u32 &n_probe, Rec *seg, u32 &cursor) {
+    const u32 ln = lane_id();
+    for (u32 base = 0; base < count; base += 32) {
+        const u32 idx = base + ln;
+        bool pass = false;
+        u32 pos = 0;
+        if (idx < count) {
+            pos = q1[idx];
+            pass = turbo_bloom(bloom, c.db, load_tail8(c.cp.text, span_base + pos));
+        }
+        const u32 bal = __ballot_sync(0xffffffffu, pass);
+        if (pass) q2[q2n + __popc(bal & ((1u << ln) - 1))] = pos;
+        q2n += __popc(bal);
+        __syncwarp();
+        if (q2n >= 32) {
+            turbo_drain<ORDERED>(c, q2, span_base, 32, n_probe, seg, cursor);
+            const u32 rem = q2n - 32;
+            const u32 keep = ln < rem ? q2[32 + ln] : 0;
             __syncwarp();
-            if (*(volatile u32 *)c.stage_n >= c.stage_cap / 2) flush_stage(c);
+            if (ln < rem) q2[ln] = keep;
+            __syncwarp();
+            q2n = rem;
         }
     }
 }
@@ -142,35 +192,46 @@ template <int K, bool ORDERED>
 __global__ void __launch_bounds__(TTHREADS, 1) k_turbo(const DevDb db, const DevCorpus cp, const DevArena ar) {
     extern __shared__ __align__(16) u8 smem[];
     u64 *tab = reinterpret_cast<u64 *>(smem);
-    const u32 rows = 1u << db.tH1;
-    TurboWarpShared *wsh = reinterpret_cast<TurboWarpShared *>(smem + (size_t)rows * 8);
-    {
-        const uint4 *src = reinterpret_cast<const uint4 *>(db.pair_tab);
-        uint4 *dst = reinterpret_cast<uint4 *>(tab);
-        for (u32 i = threadIdx.x; i < rows / 2; i += blockDim.x) dst[i] = src[i];
-    }
+    const u32 rows = 1u << db.tH1, bloom_words = 1u << (db.tBL - 5);
+    u32 *bloom = reinterpret_cast<u32 *>(smem + (size_t)rows * 8);
+    TurboWarpShared *wsh = reinterpret_cast<TurboWarpShared *>(smem + (size_t)rows * 8 + (size_t)bloom_words * 4);
     const u32 warp = threadIdx.x >> 5, ln = lane_id();
-    if (ln == 0) wsh[warp].stage_n = 0;
-    __syncthreads();
-
-    const Ctx c{db, cp, ar, wsh[warp].q, wsh[warp].stage, &wsh[warp].stage_n, TSTAGE, nullptr, nullptr};
-    const u32 H1shift = 32 - db.tH1;
-    u32 n_cand = 0, n_probe = 0;
     // every warp of the grid takes one contiguous span of 512-byte rows, balanced to within one row
     const u64 rows_total = (cp.total + ROW_BYTES - 1) / ROW_BYTES;
     const u64 W = (u64)gridDim.x * TWARPS, w = (u64)blockIdx.x * TWARPS + warp;
     const u64 r0 = rows_total * w / W, r1 = rows_total * (w + 1) / W;
+    const u64 span_base = r0 * ROW_BYTES;
+    const u8 *p = cp.text + span_base + ln * CHUNK;
+    // the first row's text is requested before the tables are copied in, so HBM latency overlaps the copy
+    uint4 cur = make_uint4(0, 0, 0, 0);
+    uint2 before = make_uint2(0, 0);
+    if (r0 < r1) {
+        cur = *reinterpret_cast<const uint4 *>(p);
+        before = *reinterpret_cast<const uint2 *>(cp.text + span_base - 8);  // FRONT_PAD keeps this in bounds
+    }
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(db.pair_tab);
+        uint4 *dst = reinterpret_cast<uint4 *>(tab);
+#pragma unroll 4
+        for (u32 i = threadIdx.x; i < rows / 2; i += TTHREADS) dst[i] = __ldg(src + i);
+        const uint4 *bsrc = reinterpret_cast<const uint4 *>(db.bloom);
+        uint4 *bdst = reinterpret_cast<uint4 *>(bloom);
+#pragma unroll 4
+        for (u32 i = threadIdx.x; i < bloom_words / 4; i += TTHREADS) bdst[i] = __ldg(bsrc + i);
+    }
+    if (ln == 0) wsh[warp].stage_n = 0;
+    __syncthreads();
+
+    const Ctx c{db, cp, ar, wsh[warp].q1, wsh[warp].stage, &wsh[warp].stage_n, TSTAGE, nullptr, nullptr};
+    u32 *q1 = wsh[warp].q1, *q2 = wsh[warp].q2;
+    const u32 H1shift = 32 - db.tH1;
+    u32 n_cand = 0, n_probe = 0;
     Rec *seg = ORDERED ? ar.recs + (size_t)w * ar.seg_cap : nullptr;
     u32 cursor = 0;
     if (r0 < r1) {
-        const u64 span_base = r0 * ROW_BYTES;
-        u32 qn = 0;
-        const u8 *p = cp.text + span_base + ln * CHUNK;
-        // 8 bytes preceding the span (FRONT_PAD keeps this in bounds at offset 0)
-        const uint2 before = *reinterpret_cast<const uint2 *>(cp.text + span_base - 8);
+        u32 qn = 0, q2n = 0;
         u32 carry2 = before.x, carry3 = before.y;
         const u32 nrows = (u32)(r1 - r0);
-        uint4 cur = *reinterpret_cast<const uint4 *>(p);
         for (u32 row = 0; row < nrows; row++) {
             uint4 nxt = make_uint4(0, 0, 0, 0);
             if (row + 1 < nrows) nxt = *reinterpret_cast<const uint4 *>(p + (size_t)(row + 1) * ROW_BYTES);
@@ -183,8 +244,9 @@ __global__ void __launch_bounds__(TTHREADS, 1) k_turbo(const DevDb db, const Dev
             const u32 pos0 = row * ROW_BYTES + ln * CHUNK;
             const u64 g0 = span_base + pos0;
             if (g0 + CHUNK > cp.total) m &= g0 >= cp.total ? 0u : ~((0x10000u >> (int)(cp.total - g0)) - 1);
-            if (__any_sync(0xffffffffu, m != 0)) {
-                // append this row's candidates in position order: lane order, then descending bit = ascending byte
+            while (__any_sync(0xffffffffu, m != 0)) {
+                // append this row's candidates in position order: lane order, then descending bit = ascending
+                // byte; whatever does not fit below TQ1CAP stays in m for the next pass
                 const u32 n = __popc(m);
                 u32 incl = n;
 #pragma unroll
@@ -193,21 +255,22 @@ __global__ void __launch_bounds__(TTHREADS, 1) k_turbo(const DevDb db, const Dev
                     if (ln >= (u32)d) incl += t;
                 }
                 u32 slot = qn + incl - n;
-                while (m) {
+                while (m && slot < TQ1CAP) {
                     const u32 top = 31 - __clz(m);
-                    c.q[slot++] = pos0 + (15 - top);
+                    q1[slot++] = pos0 + (15 - top);
                     m ^= 1u << top;
                 }
                 qn += __shfl_sync(0xffffffffu, incl, 31);
+                if (qn > TQ1CAP) qn = TQ1CAP;
                 __syncwarp();
                 if (qn >= 32) {
                     const u32 full = qn & ~31u;
                     n_cand += full;
-                    turbo_drain<ORDERED>(c, span_base, full, n_probe, seg, cursor);
+                    turbo_tier2<ORDERED>(c, bloom, q1, q2, q2n, span_base, full, n_probe, seg, cursor);
                     const u32 rem = qn - full;
-                    const u32 keep = ln < rem ? c.q[full + ln] : 0;
+                    const u32 keep = ln < rem ? q1[full + ln] : 0;
                     __syncwarp();
-                    if (ln < rem) c.q[ln] = keep;
+                    if (ln < rem) q1[ln] = keep;
                     __syncwarp();
                     qn = rem;
                 }
@@ -216,8 +279,9 @@ __global__ void __launch_bounds__(TTHREADS, 1) k_turbo(const DevDb db, const Dev
         }
         if (qn) {
             n_cand += qn;
-            turbo_drain<ORDERED>(c, span_base, qn, n_probe, seg, cursor);
+            turbo_tier2<ORDERED>(c, bloom, q1, q2, q2n, span_base, qn, n_probe, seg, cursor);
         }
+        if (q2n) turbo_drain<ORDERED>(c, q2, span_base, q2n, n_probe, seg, cursor);
     }
     if (ORDERED) {
         if (ln == 0) ar.seg_count[w] = cursor;

@@ -15,6 +15,12 @@
 //     slot carries the LitInfo's v / msk / size and the literal's Rose program pre-decoded when it is one of
 //     the three shapes the compiler emits for plain reports (REPORT | FINAL_REPORT, optionally guarded by one
 //     CHECK_MED_LIT[_NOCASE]); anything else keeps its program offset and is interpreted.
+//  3. TAIL BLOOM (shared memory, 2^BL bits, one hash).  Second filter tier, consulted only for the positions
+//     the pair table lets through.  A literal whose LitInfo.size >= L (L = K + 1) is filed under the hash of
+//     its exact L-byte tail, a shorter one under its K-byte tail; a position survives when either probe hits.
+//     The pair table alone passes every position whose K-tail LOOKS like some literal's (it indexes the extra
+//     byte by 5 bits only); the bloom cuts that to (nearly) the positions where a literal's full L-tail is
+//     present, so the L2-resident slot table is probed an order of magnitude less often.
 #pragma once
 #include "hsb_dbview.h"
 
@@ -47,11 +53,20 @@ HSB_HD u32 pack_shared(u32 K, u32 s0, u32 s1, u32 s2) {
 }
 HSB_HD u32 pair_row(u32 packed, u32 H1) { return (packed * PAIR_MULT) >> (32 - H1); }
 HSB_HD u32 slot_home(u32 key, u32 H2) { return (key * SLOT_MULT) >> (32 - H2); }
+// bloom bit index of an n-byte tail (first tail byte in the low byte of lo; hi = bytes 4.. of the tail)
+HSB_HD u32 bloom_bit(u32 lo, u32 hi, u32 n, u32 BL) {
+    u32 h = (lo * 0x9E3779B1u) ^ (hi * 0x85EBCA6Bu) ^ (n * 0xC2B2AE35u);
+    h ^= h >> 15;
+    h *= 0x2C1B3C6Du;
+    return h >> (32 - BL);
+}
 
 struct Tables {
     u32 K = 0, H1 = 0, H2 = 0;
     std::vector<u64> pair;   // low 32 bits = A, high 32 bits = B
     std::vector<Slot> slots;
+    u32 L = 0, BL = 0;       // long-tail length (0: every literal is K bytes long) and log2(bloom bits)
+    std::vector<u32> bloom;
     u64 variants = 0;
     bool all_simple = true;  // every literal's program pre-decoded to a plain report (no interpreter needed)
 };
@@ -84,6 +99,22 @@ inline void predecode(const DbView &d, u32 prog, Slot &s, u32 size) {
     s.target = target;
     s.lit_off = lit_off;
     s.meta = size | (kind << 8) | (lit_len << 16);
+}
+
+// every n-byte text tail the LitInfo admits (its last n bytes under msk), first tail byte lowest
+inline bool tail_variants(const LitRec &l, u32 n, size_t limit, std::vector<u64> &keys) {
+    keys.assign(1, 0);
+    for (u32 j = 0; j < n; j++) {
+        const u32 sh = 8 * (8 - n + j);
+        const u8 m = (u8)(l.msk >> sh), val = (u8)(l.v >> sh);
+        std::vector<u64> next;
+        for (u32 c = 0; c < 256; c++)
+            if ((c & m) == val)
+                for (u64 k : keys) next.push_back(k | ((u64)c << (8 * j)));
+        if (next.empty() || next.size() > limit) return false;
+        keys.swap(next);
+    }
+    return true;
 }
 
 inline bool build(const DbView &d, Tables &t) {
@@ -136,6 +167,30 @@ inline bool build(const DbView &d, Tables &t) {
         const u32 sa = pack_shared(K, b[1], b[2], b[3]), sb = pack_shared(K, b[0], b[1], b[2]);
         t.pair[pair_row(sa, t.H1)] |= 1ull << (31 - (b[0] & 31));  // sets are stored bit-reversed (turbo.cuh)
         t.pair[pair_row(sb, t.H1)] |= 1ull << (63 - (b[K - 1] & 31));
+    }
+    // tail bloom
+    {
+        u32 longest = 0;
+        for (const LitRec *l : live) longest = std::max<u32>(longest, l->size);
+        t.L = longest > K ? K + 1 : 0;
+        std::vector<std::pair<u64, u32>> entries;  // (tail, length)
+        std::vector<u64> keys;
+        for (const LitRec *l : live) {
+            if (t.L && l->size >= t.L && tail_variants(*l, t.L, 256, keys)) {
+                for (u64 k : keys) entries.push_back({k, t.L});
+            } else {
+                if (!tail_variants(*l, K, 4096, keys)) return false;
+                for (u64 k : keys) entries.push_back({k, K});
+            }
+        }
+        u32 BL = 13;
+        while (BL < 19 && ((size_t)1 << BL) < entries.size() * 64) BL++;
+        t.BL = BL;
+        t.bloom.assign((size_t)1 << (BL - 5), 0);
+        for (const auto &e : entries) {
+            const u32 bit = bloom_bit((u32)e.first, (u32)(e.first >> 32), e.second, BL);
+            t.bloom[bit >> 5] |= 1u << (bit & 31);
+        }
     }
     u32 H2 = 4;
     while (((size_t)1 << H2) < vars.size() * 4) H2++;
