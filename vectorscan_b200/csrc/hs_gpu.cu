@@ -966,7 +966,7 @@ void build_cell_first(const u64 *off, u32 count, u64 total, std::vector<u32> &ou
 
 u32 turbo_grid(const hs_gpu_scratch *s, const DevCorpus &cp) {
     u32 grid = s->opt_grid > 0 ? (u32)s->opt_grid : (u32)s->sm_count;
-    if (grid > 170) grid = 170;  // k_compact scans at most 4096 warp segments
+    if (grid > 8192 / TWARPS) grid = 8192 / TWARPS;  // k_compact scans at most 8192 warp segments
     const u32 need = (cp.nstrips + TWARPS - 1) / TWARPS;
     if (grid > need) grid = need ? need : 1;
     return grid;

@@ -11,12 +11,16 @@
 
 constexpr int TWARPS = 24;
 constexpr int TTHREADS = TWARPS * 32;
-constexpr int TQ1CAP = 128;  // tier-1 survivors (positions) queued per warp; a fuller row is pushed in passes
+constexpr int TQ1CAP = 128;  // tier-1 survivors (positions inside the step) queued per warp; a fuller step is pushed in passes
 constexpr int TQ2CAP = 64;   // tier-2 survivors awaiting the slot-table confirm
 constexpr int TSTAGE = 32;   // staged match records per warp (general mode)
+constexpr int TCHUNK = 32;               // bytes per lane per step (two LDG.128)
+constexpr int TSTEP_BYTES = 32 * TCHUNK;  // 1 KiB per warp step
+constexpr int TEW = 2 + TCHUNK / 4;       // extended chunk words: 8 bytes before the chunk, then the chunk
 
 struct TurboWarpShared {
-    u32 q1[TQ1CAP];
+    u32 text[4 + TSTEP_BYTES / 4];  // the step's text: bytes 8..15 = the 8 bytes before it, step byte j at 16 + j
+    u16 q1[TQ1CAP];
     u32 q2[TQ2CAP];
     Rec stage[TSTAGE];
     u32 stage_n;
@@ -62,14 +66,14 @@ __device__ __forceinline__ void turbo_confirm(const Ctx &c, u64 g, u32 &n_probe)
     }
 }
 
-// Second tier: the tail bloom.  True when some literal's exact tail may end at the position whose 8-byte
-// window (last byte on top) is w.
-__device__ __forceinline__ bool turbo_bloom(const u32 *bloom, const DevDb &db, u64 w) {
-    const u32 ks = (u32)(w >> (64 - 8 * db.tK));
+// Second tier: the tail bloom.  True when some literal's exact tail may end at the position whose last five
+// text bytes are w40 (byte 4 = the position's own byte).
+__device__ __forceinline__ bool turbo_bloom(const u32 *bloom, const DevDb &db, u64 w40) {
+    const u32 ks = (u32)(w40 >> (40 - 8 * db.tK));
     const u32 b1 = turbo::bloom_bit(ks, 0, db.tK, db.tBL);
     bool hit = (bloom[b1 >> 5] >> (b1 & 31)) & 1;
     if (db.tL) {
-        const u64 kl = w >> (64 - 8 * db.tL);
+        const u64 kl = w40 >> (40 - 8 * db.tL);
         const u32 b2 = turbo::bloom_bit((u32)kl, (u32)(kl >> 32), db.tL, db.tBL);
         hit |= (bool)((bloom[b2 >> 5] >> (b2 & 31)) & 1);
     }
@@ -107,11 +111,12 @@ __device__ void turbo_drain(const Ctx &c, const u32 *q2, u64 span_base, u32 coun
     }
 }
 
-// Warp-synchronous second tier over `count` (multiple of 32, or the final remainder) queued positions
-// q1[0..count): survivors are appended to q2 in order; q2 is confirmed whenever it holds 32.
+// Warp-synchronous second tier over the `count` queued step positions q1[0..count): each lane reads its
+// candidate's last five bytes from the warp's staged text (shared memory), survivors are appended to q2 in
+// order as span-relative positions; q2 is confirmed whenever it holds 32.
 template <bool ORDERED>
-__device__ __forceinline__ void turbo_tier2(const Ctx &c, const u32 *bloom, const u32 *q1, u32 *q2, u32 &q2n, u64 span_base,
-                                            u32 count, u32 &n_probe, Rec *seg, u32 &cursor) {
+__device__ __forceinline__ void turbo_tier2(const Ctx &c, const u32 *bloom, const u32 *wtext, const u16 *q1, u32 *q2, u32 &q2n,
+                                            u64 span_base, u32 step_pos, u32 count, u32 &n_probe, Rec *seg, u32 &cursor) {
     const u32 ln = lane_id();
     for (u32 base = 0; base < count; base += 32) {
         const u32 idx = base + ln;
@@ -119,10 +124,13 @@ __device__ __forceinline__ void turbo_tier2(const Ctx &c, const u32 *bloom, cons
         u32 pos = 0;
         if (idx < count) {
             pos = q1[idx];
-            pass = turbo_bloom(bloom, c.db, load_tail8(c.cp.text, span_base + pos));
+            const u32 first = 16 + pos - 4;  // byte index of text[pos - 4] in wtext
+            const u32 lo = wtext[first >> 2], hi = wtext[(first >> 2) + 1];
+            const u64 both = ((u64)hi << 32) | lo;
+            pass = turbo_bloom(bloom, c.db, (both >> (8 * (first & 3))) & 0xffffffffffull);
         }
         const u32 bal = __ballot_sync(0xffffffffu, pass);
-        if (pass) q2[q2n + __popc(bal & ((1u << ln) - 1))] = pos;
+        if (pass) q2[q2n + __popc(bal & ((1u << ln) - 1))] = step_pos + pos;
         q2n += __popc(bal);
         __syncwarp();
         if (q2n >= 32) {
@@ -139,53 +147,55 @@ __device__ __forceinline__ void turbo_tier2(const Ctx &c, const u32 *bloom, cons
 
 // register whose low byte is extended-chunk byte `e` (E = {8 bytes before the chunk, the chunk})
 template <int e>
-__device__ __forceinline__ u32 byte_reg(const u32 E[6]) {
+__device__ __forceinline__ u32 byte_reg(const u32 (&E)[TEW]) {
     if ((e & 3) == 0) return E[e >> 2];
-    return __funnelshift_r(E[e >> 2], (e >> 2) + 1 <= 5 ? E[(e >> 2) + 1] : 0u, 8 * (e & 3));
+    return __funnelshift_r(E[e >> 2], (e >> 2) + 1 < TEW ? E[(e >> 2) + 1] : 0u, 8 * (e & 3));
 }
 
 // K-1 shared bytes of the pair ending at chunk byte i, packed as turbo::pack_shared packs them.
 // The packing puts text[i-2] in the low byte, so x(i) doubles as the shift-amount register for the B test
 // of pair i-2 and (K == 4) the A test of pair i+2: a funnel shift only looks at the low 5 bits.
 template <int K, int i>
-__device__ __forceinline__ u32 shared_reg(const u32 E[6]) {
+__device__ __forceinline__ u32 shared_reg(const u32 (&E)[TEW]) {
     if (K < 2) return 0;
     constexpr int eS = i - K + 1 + 8, wS = eS >> 2, o = eS & 3;
     constexpr u32 sel = K == 4 ? (u32)((o + 1) | (o << 4) | ((o + 2) << 8) | ((o + 2) << 12))
                       : K == 3 ? (u32)(o | ((o + 1) << 4) | (o << 8) | ((o + 1) << 12))
                                : (u32)(o * 0x1111);
-    return __byte_perm(E[wS], wS + 1 <= 5 ? E[wS + 1] : 0u, sel);
+    return __byte_perm(E[wS], wS + 1 < TEW ? E[wS + 1] : 0u, sel);
 }
 
+// Pairs (i-1, i) for i = 1, 3, ..., TCHUNK-1, unrolled by recursion.  xi = shared_reg<K, i>, xprev =
+// shared_reg<K, i-2>; the candidate mask is built first-position-on-top.
 template <int K, int i>
-__device__ __forceinline__ void turbo_pair(const u64 *tab, u32 H1shift, const u32 E[6], const u32 (&x)[10], u32 &acc) {
-    // x[j] = shared_reg<K, 2j - 1>
-    const u32 row = (x[(i + 1) / 2] * turbo::PAIR_MULT) >> H1shift;
-    const u64 ent = tab[row];
-    u32 yA, yB;
-    if (K == 4) yA = x[(i - 1) / 2]; else yA = byte_reg<i - K + 8>(E);       // low 5 bits of text[i-K]
-    if ((K == 4 || K == 3) && i < 15) yB = x[(i + 3) / 2]; else yB = byte_reg<i + 8>(E);  // text[i]
-    // the table stores each 32-bit set bit-reversed: shifting left by low5(byte) brings the flag to bit 31,
-    // and a funnel shift by one appends it to the candidate mask (first position ends up in the top bit)
-    const u32 ra = __funnelshift_l(0u, (u32)ent, yA);
-    acc = __funnelshift_l(ra, acc, 1);
-    const u32 rb = __funnelshift_l(0u, (u32)(ent >> 32), yB);
-    acc = __funnelshift_l(rb, acc, 1);
-}
-
-// 16 end positions of one chunk -> candidate mask, bit (15 - j) = end position j is a candidate
+struct TurboPairs {
+    static __device__ __forceinline__ void run(const u64 *tab, u32 H1shift, const u32 (&E)[TEW], u32 xprev, u32 xi, u32 &acc) {
+        const u32 row = (xi * turbo::PAIR_MULT) >> H1shift;
+        const u64 ent = tab[row];
+        const u32 xnext = i + 2 < TCHUNK ? shared_reg<K, (i + 2 < TCHUNK ? i + 2 : i)>(E) : 0u;
+        u32 yA, yB;
+        if (K == 4) yA = xprev; else yA = byte_reg<i - K + 8>(E);                         // low 5 bits of text[i-K]
+        if ((K == 4 || K == 3) && i + 2 < TCHUNK) yB = xnext; else yB = byte_reg<i + 8>(E);  // text[i]
+        // the table stores each 32-bit set bit-reversed: shifting left by low5(byte) brings the flag to bit 31,
+        // and a funnel shift by one appends it to the candidate mask (first position ends up in the top bit)
+        const u32 ra = __funnelshift_l(0u, (u32)ent, yA);
+        acc = __funnelshift_l(ra, acc, 1);
+        const u32 rb = __funnelshift_l(0u, (u32)(ent >> 32), yB);
+        acc = __funnelshift_l(rb, acc, 1);
+        TurboPairs<K, i + 2>::run(tab, H1shift, E, xi, xnext, acc);
+    }
+};
 template <int K>
-__device__ __forceinline__ u32 turbo_chunk(const u64 *tab, u32 H1shift, const u32 E[6]) {
-    u32 x[10];
-    x[0] = shared_reg<K, -1>(E); x[1] = shared_reg<K, 1>(E); x[2] = shared_reg<K, 3>(E); x[3] = shared_reg<K, 5>(E);
-    x[4] = shared_reg<K, 7>(E); x[5] = shared_reg<K, 9>(E); x[6] = shared_reg<K, 11>(E); x[7] = shared_reg<K, 13>(E);
-    x[8] = shared_reg<K, 15>(E); x[9] = 0;
+struct TurboPairs<K, TCHUNK + 1> {
+    static __device__ __forceinline__ void run(const u64 *, u32, const u32 (&)[TEW], u32, u32, u32 &) {}
+};
+
+// TCHUNK end positions of one chunk -> candidate mask, bit (TCHUNK - 1 - j) = end position j is a candidate
+template <int K>
+__device__ __forceinline__ u32 turbo_chunk(const u64 *tab, u32 H1shift, const u32 (&E)[TEW]) {
     u32 acc = 0;
-    turbo_pair<K, 1>(tab, H1shift, E, x, acc); turbo_pair<K, 3>(tab, H1shift, E, x, acc);
-    turbo_pair<K, 5>(tab, H1shift, E, x, acc); turbo_pair<K, 7>(tab, H1shift, E, x, acc);
-    turbo_pair<K, 9>(tab, H1shift, E, x, acc); turbo_pair<K, 11>(tab, H1shift, E, x, acc);
-    turbo_pair<K, 13>(tab, H1shift, E, x, acc); turbo_pair<K, 15>(tab, H1shift, E, x, acc);
-    return acc & 0xffffu;
+    TurboPairs<K, 1>::run(tab, H1shift, E, shared_reg<K, -1>(E), shared_reg<K, 1>(E), acc);
+    return acc;
 }
 
 template <int K, bool ORDERED>
@@ -196,56 +206,76 @@ __global__ void __launch_bounds__(TTHREADS, 1) k_turbo(const DevDb db, const Dev
     u32 *bloom = reinterpret_cast<u32 *>(smem + (size_t)rows * 8);
     TurboWarpShared *wsh = reinterpret_cast<TurboWarpShared *>(smem + (size_t)rows * 8 + (size_t)bloom_words * 4);
     const u32 warp = threadIdx.x >> 5, ln = lane_id();
-    // every warp of the grid takes one contiguous span of 512-byte rows, balanced to within one row
-    const u64 rows_total = (cp.total + ROW_BYTES - 1) / ROW_BYTES;
+    // every warp of the grid takes one contiguous span of 1 KiB steps, balanced to within one step
+    const u64 rows_total = (cp.total + TSTEP_BYTES - 1) / TSTEP_BYTES;
     const u64 W = (u64)gridDim.x * TWARPS, w = (u64)blockIdx.x * TWARPS + warp;
     const u64 r0 = rows_total * w / W, r1 = rows_total * (w + 1) / W;
-    const u64 span_base = r0 * ROW_BYTES;
-    const u8 *p = cp.text + span_base + ln * CHUNK;
-    // the first row's text is requested before the tables are copied in, so HBM latency overlaps the copy
-    uint4 cur = make_uint4(0, 0, 0, 0);
+    const u64 span_base = r0 * TSTEP_BYTES;
+    const u8 *p = cp.text + span_base + ln * TCHUNK;
+    // the first step's text is requested before the tables are copied in, so HBM latency overlaps the copy
+    uint4 cur0 = make_uint4(0, 0, 0, 0), cur1 = cur0;
     uint2 before = make_uint2(0, 0);
     if (r0 < r1) {
-        cur = *reinterpret_cast<const uint4 *>(p);
+        cur0 = *reinterpret_cast<const uint4 *>(p);
+        cur1 = *reinterpret_cast<const uint4 *>(p + 16);
         before = *reinterpret_cast<const uint2 *>(cp.text + span_base - 8);  // FRONT_PAD keeps this in bounds
     }
     {
+        // every CTA copies the same tables: each starts at a different offset so that the SMs do not all ask
+        // the same L2 slice for the same line at the same moment
         const uint4 *src = reinterpret_cast<const uint4 *>(db.pair_tab);
         uint4 *dst = reinterpret_cast<uint4 *>(tab);
+        const u32 n1 = rows / 2, rot1 = (u32)(((u64)blockIdx.x * n1) / gridDim.x) & ~31u;
 #pragma unroll 4
-        for (u32 i = threadIdx.x; i < rows / 2; i += TTHREADS) dst[i] = __ldg(src + i);
+        for (u32 i = threadIdx.x; i < n1; i += TTHREADS) {
+            const u32 j = (i + rot1) & (n1 - 1);
+            dst[j] = __ldg(src + j);
+        }
         const uint4 *bsrc = reinterpret_cast<const uint4 *>(db.bloom);
         uint4 *bdst = reinterpret_cast<uint4 *>(bloom);
+        const u32 n2 = bloom_words / 4, rot2 = (u32)(((u64)blockIdx.x * n2) / gridDim.x) & ~31u;
 #pragma unroll 4
-        for (u32 i = threadIdx.x; i < bloom_words / 4; i += TTHREADS) bdst[i] = __ldg(bsrc + i);
+        for (u32 i = threadIdx.x; i < n2; i += TTHREADS) {
+            const u32 j = (i + rot2) & (n2 - 1);
+            bdst[j] = __ldg(bsrc + j);
+        }
     }
     if (ln == 0) wsh[warp].stage_n = 0;
     __syncthreads();
 
-    const Ctx c{db, cp, ar, wsh[warp].q1, wsh[warp].stage, &wsh[warp].stage_n, TSTAGE, nullptr, nullptr};
-    u32 *q1 = wsh[warp].q1, *q2 = wsh[warp].q2;
+    const Ctx c{db, cp, ar, wsh[warp].q2, wsh[warp].stage, &wsh[warp].stage_n, TSTAGE, nullptr, nullptr};
+    u16 *q1 = wsh[warp].q1;
+    u32 *q2 = wsh[warp].q2, *wtext = wsh[warp].text;
     const u32 H1shift = 32 - db.tH1;
     u32 n_cand = 0, n_probe = 0;
     Rec *seg = ORDERED ? ar.recs + (size_t)w * ar.seg_cap : nullptr;
     u32 cursor = 0;
     if (r0 < r1) {
-        u32 qn = 0, q2n = 0;
+        u32 q2n = 0;
         u32 carry2 = before.x, carry3 = before.y;
         const u32 nrows = (u32)(r1 - r0);
+#pragma unroll 1
         for (u32 row = 0; row < nrows; row++) {
-            uint4 nxt = make_uint4(0, 0, 0, 0);
-            if (row + 1 < nrows) nxt = *reinterpret_cast<const uint4 *>(p + (size_t)(row + 1) * ROW_BYTES);
-            u32 p2 = __shfl_up_sync(0xffffffffu, cur.z, 1), p3 = __shfl_up_sync(0xffffffffu, cur.w, 1);
+            uint4 nxt0 = make_uint4(0, 0, 0, 0), nxt1 = nxt0;
+            if (row + 1 < nrows) {
+                nxt0 = *reinterpret_cast<const uint4 *>(p + (size_t)(row + 1) * TSTEP_BYTES);
+                nxt1 = *reinterpret_cast<const uint4 *>(p + (size_t)(row + 1) * TSTEP_BYTES + 16);
+            }
+            u32 p2 = __shfl_up_sync(0xffffffffu, cur1.z, 1), p3 = __shfl_up_sync(0xffffffffu, cur1.w, 1);
             if (ln == 0) { p2 = carry2; p3 = carry3; }
-            carry2 = __shfl_sync(0xffffffffu, cur.z, 31);
-            carry3 = __shfl_sync(0xffffffffu, cur.w, 31);
-            const u32 E[6] = {p2, p3, cur.x, cur.y, cur.z, cur.w};
+            carry2 = __shfl_sync(0xffffffffu, cur1.z, 31);
+            carry3 = __shfl_sync(0xffffffffu, cur1.w, 31);
+            // stage the step's text for the second tier (the previous step's candidates are all done)
+            *reinterpret_cast<uint4 *>(wtext + 4 + ln * 8) = cur0;
+            *reinterpret_cast<uint4 *>(wtext + 8 + ln * 8) = cur1;
+            if (ln == 0) { wtext[2] = p2; wtext[3] = p3; }
+            const u32 E[TEW] = {p2, p3, cur0.x, cur0.y, cur0.z, cur0.w, cur1.x, cur1.y, cur1.z, cur1.w};
             u32 m = turbo_chunk<K>(tab, H1shift, E);
-            const u32 pos0 = row * ROW_BYTES + ln * CHUNK;
-            const u64 g0 = span_base + pos0;
-            if (g0 + CHUNK > cp.total) m &= g0 >= cp.total ? 0u : ~((0x10000u >> (int)(cp.total - g0)) - 1);
+            const u32 pos0 = ln * TCHUNK, step_pos = row * TSTEP_BYTES;
+            const u64 g0 = span_base + step_pos + pos0;
+            if (g0 + TCHUNK > cp.total) m &= g0 >= cp.total ? 0u : ~(0xffffffffu >> (int)(cp.total - g0));
             while (__any_sync(0xffffffffu, m != 0)) {
-                // append this row's candidates in position order: lane order, then descending bit = ascending
+                // queue this step's candidates in position order: lane order, then descending bit = ascending
                 // byte; whatever does not fit below TQ1CAP stays in m for the next pass
                 const u32 n = __popc(m);
                 u32 incl = n;
@@ -254,32 +284,21 @@ __global__ void __launch_bounds__(TTHREADS, 1) k_turbo(const DevDb db, const Dev
                     const u32 t = __shfl_up_sync(0xffffffffu, incl, d);
                     if (ln >= (u32)d) incl += t;
                 }
-                u32 slot = qn + incl - n;
+                u32 slot = incl - n;
                 while (m && slot < TQ1CAP) {
-                    const u32 top = 31 - __clz(m);
-                    q1[slot++] = pos0 + (15 - top);
-                    m ^= 1u << top;
+                    const u32 lz = __clz(m);
+                    q1[slot++] = (u16)(pos0 + lz);
+                    m &= ~(0x80000000u >> lz);
                 }
-                qn += __shfl_sync(0xffffffffu, incl, 31);
+                u32 qn = __shfl_sync(0xffffffffu, incl, 31);
                 if (qn > TQ1CAP) qn = TQ1CAP;
                 __syncwarp();
-                if (qn >= 32) {
-                    const u32 full = qn & ~31u;
-                    n_cand += full;
-                    turbo_tier2<ORDERED>(c, bloom, q1, q2, q2n, span_base, full, n_probe, seg, cursor);
-                    const u32 rem = qn - full;
-                    const u32 keep = ln < rem ? q1[full + ln] : 0;
-                    __syncwarp();
-                    if (ln < rem) q1[ln] = keep;
-                    __syncwarp();
-                    qn = rem;
-                }
+                n_cand += qn;
+                turbo_tier2<ORDERED>(c, bloom, wtext, q1, q2, q2n, span_base, step_pos, qn, n_probe, seg, cursor);
+                __syncwarp();
             }
-            cur = nxt;
-        }
-        if (qn) {
-            n_cand += qn;
-            turbo_tier2<ORDERED>(c, bloom, q1, q2, q2n, span_base, qn, n_probe, seg, cursor);
+            cur0 = nxt0;
+            cur1 = nxt1;
         }
         if (q2n) turbo_drain<ORDERED>(c, q2, span_base, q2n, n_probe, seg, cursor);
     }
@@ -300,7 +319,7 @@ __global__ void __launch_bounds__(TTHREADS, 1) k_turbo(const DevDb db, const Dev
 // count any warp wanted (> seg_cap means the launch must be repeated with larger segments).
 __global__ void __launch_bounds__(256) k_compact(const Rec *recs, const u32 *seg_count, u32 seg_cap, u32 W, Rec *out_recs,
                                                  hs_gpu_match_t *out, unsigned long long *ctl) {
-    __shared__ u32 pre[4097];
+    __shared__ u32 pre[8193];
     __shared__ u32 part[256];
     __shared__ u32 mx[256];
     const u32 per = (W + 255) / 256, t = threadIdx.x;
@@ -316,7 +335,7 @@ __global__ void __launch_bounds__(256) k_compact(const Rec *recs, const u32 *seg
     if (t == 0) {
         u32 run = 0, m = 0;
         for (int i = 0; i < 256; i++) { const u32 v = part[i]; part[i] = run; run += v; m = mx[i] > m ? mx[i] : m; }
-        pre[4096] = run;
+        pre[8192] = run;
         if (blockIdx.x == 0) { ctl[4] = run; ctl[5] = m; }
     }
     __syncthreads();

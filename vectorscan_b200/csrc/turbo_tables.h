@@ -25,6 +25,7 @@
 #include "hsb_dbview.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <vector>
 
 namespace hsb {
@@ -55,9 +56,7 @@ HSB_HD u32 pair_row(u32 packed, u32 H1) { return (packed * PAIR_MULT) >> (32 - H
 HSB_HD u32 slot_home(u32 key, u32 H2) { return (key * SLOT_MULT) >> (32 - H2); }
 // bloom bit index of an n-byte tail (first tail byte in the low byte of lo; hi = bytes 4.. of the tail)
 HSB_HD u32 bloom_bit(u32 lo, u32 hi, u32 n, u32 BL) {
-    u32 h = (lo * 0x9E3779B1u) ^ (hi * 0x85EBCA6Bu) ^ (n * 0xC2B2AE35u);
-    h ^= h >> 15;
-    h *= 0x2C1B3C6Du;
+    const u32 h = (lo * 0x9E3779B1u) ^ (hi * 0x85EBCA6Bu) ^ (n * 0xC2B2AE35u);  // top bits: multiplicative hash
     return h >> (32 - BL);
 }
 
@@ -158,7 +157,7 @@ inline bool build(const DbView &d, Tables &t) {
         if (vars.size() > (1u << 22)) return false;
     }
     t.variants = vars.size();
-    t.H1 = vars.size() >= 512 ? 14 : (vars.size() >= 64 ? 12 : 10);
+    t.H1 = vars.size() >= 512 ? (getenv("HSB_H1") ? atoi(getenv("HSB_H1")) : 14) : (vars.size() >= 64 ? 12 : 10);
     t.pair.assign((size_t)1 << t.H1, 0);
     for (const Var &v : vars) {
         u32 b[4] = {0, 0, 0, 0};
@@ -183,8 +182,10 @@ inline bool build(const DbView &d, Tables &t) {
                 for (u64 k : keys) entries.push_back({k, K});
             }
         }
+        // 2^18 bits (32 KiB) at most: with the 128 KiB pair table, the per-warp text staging and queues it
+        // has to fit the 227 KiB of shared memory an SM offers
         u32 BL = 13;
-        while (BL < 19 && ((size_t)1 << BL) < entries.size() * 64) BL++;
+        while (BL < 18 && ((size_t)1 << BL) < entries.size() * 64) BL++;
         t.BL = BL;
         t.bloom.assign((size_t)1 << (BL - 5), 0);
         for (const auto &e : entries) {
