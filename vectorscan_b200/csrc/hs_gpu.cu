@@ -964,23 +964,23 @@ void build_cell_first(const u64 *off, u32 count, u64 total, std::vector<u32> &ou
     }
 }
 
-u32 turbo_grid(const hs_gpu_scratch *s, const DevCorpus &cp) {
+u32 turbo_grid(const hs_gpu_scratch *s, const DevCorpus &cp, u32 warps_per_cta) {
     u32 grid = s->opt_grid > 0 ? (u32)s->opt_grid : (u32)s->sm_count;
-    if (grid > 8192 / TWARPS) grid = 8192 / TWARPS;  // k_compact scans at most 8192 warp segments
-    const u32 need = (cp.nstrips + TWARPS - 1) / TWARPS;
+    if (grid > 8192 / warps_per_cta) grid = 8192 / warps_per_cta;  // k_compact scans at most 8192 warp segments
+    const u32 need = (cp.nstrips + warps_per_cta - 1) / warps_per_cta;
     if (grid > need) grid = need ? need : 1;
     return grid;
 }
 
 template <int K, bool ORDERED>
 hs_error_t launch_turbo(hs_gpu_scratch *s, const DevDb &db, const DevCorpus &cp, const DevArena &ar) {
-    const size_t dyn = turbo_smem_bytes(db);
+    const size_t dyn = turbo_smem_bytes<ORDERED>(db);
     static size_t configured = 0;
     if (dyn > configured) {
         CU_OK(cudaFuncSetAttribute(k_turbo<K, ORDERED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
         configured = dyn;
     }
-    k_turbo<K, ORDERED><<<turbo_grid(s, cp), TTHREADS, dyn, s->stream>>>(db, cp, ar);
+    k_turbo<K, ORDERED><<<turbo_grid(s, cp, turbo_warps<ORDERED>()), turbo_warps<ORDERED>() * 32, dyn, s->stream>>>(db, cp, ar);
     CU_OK(cudaGetLastError());
     return HS_SUCCESS;
 }
@@ -1005,7 +1005,7 @@ hs_error_t launch_scan(hs_gpu_scratch *s, const DevDb &db, const DevCorpus &cp, 
 // them; no sort.  Returns HS_INSUFFICIENT_SPACE when the general path must be used instead.
 hs_error_t scan_device_ordered(hs_gpu_scratch *s, DbImage *im, const DevCorpus &cp) {
     hs_gpu_stats_t &st = s->stats;
-    const u32 grid = turbo_grid(s, cp), W = grid * TWARPS;
+    const u32 grid = turbo_grid(s, cp, turbo_warps<true>()), W = grid * turbo_warps<true>();
     CU_OK(s->seg_count.reserve(W));
     CU_OK(cudaEventRecord(s->ev[1], s->stream));
     for (int attempt = 0;; attempt++) {

@@ -9,26 +9,54 @@
 //     (window & msk) == v exactly as confWithBit does; only then is the buffer looked up for the size check.
 #pragma once
 
-constexpr int TWARPS = 24;
-constexpr int TTHREADS = TWARPS * 32;
 constexpr int TQ1CAP = 128;  // tier-1 survivors (positions inside the step) queued per warp; a fuller step is pushed in passes
 constexpr int TQ2CAP = 64;   // tier-2 survivors awaiting the slot-table confirm
 constexpr int TSTAGE = 32;   // staged match records per warp (general mode)
-constexpr int TCHUNK = 32;               // bytes per lane per step (two LDG.128)
-constexpr int TSTEP_BYTES = 32 * TCHUNK;  // 1 KiB per warp step
-constexpr int TEW = 2 + TCHUNK / 4;       // extended chunk words: 8 bytes before the chunk, then the chunk
+constexpr int TCHUNK = 16;                 // bytes per lane per row (one LDS.128)
+constexpr int TROW_BYTES = 32 * TCHUNK;    // 512
+constexpr int TSTEP_BYTES = 2 * TROW_BYTES;  // a warp step = two rows = 1 KiB, fetched by one bulk copy
+constexpr int THALO = 16;                  // bytes before the step fetched with it (look-behind of tier 1 / tier 2)
+constexpr int TBUF_BYTES = THALO + TSTEP_BYTES;
+constexpr int TNBUF = 2;                   // step buffers per warp (one being scanned, one in flight)
+constexpr int TEW = 2 + TCHUNK / 4;        // extended chunk words: 8 bytes before the chunk, then the chunk
 
+// Per-warp shared memory.  ORDERED mode needs no record staging, so it affords 24 warps per SM; the general
+// mode runs 20.
+template <bool ORDERED>
 struct TurboWarpShared {
-    u32 text[4 + TSTEP_BYTES / 4];  // the step's text: bytes 8..15 = the 8 bytes before it, step byte j at 16 + j
+    __align__(16) u8 text[TNBUF][TBUF_BYTES];  // [THALO bytes before the step][the step], filled by cp.async.bulk
+    unsigned long long mbar[TNBUF];            // one mbarrier per buffer (transaction-count completion)
     u16 q1[TQ1CAP];
     u32 q2[TQ2CAP];
-    Rec stage[TSTAGE];
+    Rec stage[ORDERED ? 1 : TSTAGE];
     u32 stage_n;
     u32 pad[3];
 };
+template <bool ORDERED> __host__ __device__ constexpr int turbo_warps() { return ORDERED ? 24 : 20; }
 
+template <bool ORDERED>
 __host__ __device__ inline size_t turbo_smem_bytes(const DevDb &db) {
-    return ((size_t)8 << db.tH1) + ((size_t)4 << (db.tBL - 5)) + sizeof(TurboWarpShared) * TWARPS;
+    return ((size_t)8 << db.tH1) + ((size_t)4 << (db.tBL - 5)) + sizeof(TurboWarpShared<ORDERED>) * turbo_warps<ORDERED>();
+}
+
+// ---- bulk asynchronous copy (TMA, non-tensor form) + mbarrier, sm_90+/sm_100a PTX -------------------------
+__device__ __forceinline__ u32 smem_u32(const void *p) { return (u32)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, u32 count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+// one thread: expect `bytes` on the barrier and start the copy global -> shared that will deliver them
+__device__ __forceinline__ void bulk_load(void *dst, const void *src, u32 bytes, unsigned long long *bar) {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // earlier generic-proxy accesses to dst are done
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, u32 parity) {
+    u32 done;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    } while (!done);
 }
 
 __device__ __forceinline__ void turbo_hit(const Ctx &c, const uint4 &b, u64 g) {
@@ -199,26 +227,32 @@ __device__ __forceinline__ u32 turbo_chunk(const u64 *tab, u32 H1shift, const u3
 }
 
 template <int K, bool ORDERED>
-__global__ void __launch_bounds__(TTHREADS, 1) k_turbo(const DevDb db, const DevCorpus cp, const DevArena ar) {
+__global__ void __launch_bounds__(turbo_warps<ORDERED>() * 32, 1) k_turbo(const DevDb db, const DevCorpus cp, const DevArena ar) {
+    constexpr int TW = turbo_warps<ORDERED>(), NT = TW * 32;
+    using WS = TurboWarpShared<ORDERED>;
     extern __shared__ __align__(16) u8 smem[];
     u64 *tab = reinterpret_cast<u64 *>(smem);
     const u32 rows = 1u << db.tH1, bloom_words = 1u << (db.tBL - 5);
     u32 *bloom = reinterpret_cast<u32 *>(smem + (size_t)rows * 8);
-    TurboWarpShared *wsh = reinterpret_cast<TurboWarpShared *>(smem + (size_t)rows * 8 + (size_t)bloom_words * 4);
+    WS *wsh = reinterpret_cast<WS *>(smem + (size_t)rows * 8 + (size_t)bloom_words * 4);
     const u32 warp = threadIdx.x >> 5, ln = lane_id();
+    WS &ws = wsh[warp];
     // every warp of the grid takes one contiguous span of 1 KiB steps, balanced to within one step
-    const u64 rows_total = (cp.total + TSTEP_BYTES - 1) / TSTEP_BYTES;
-    const u64 W = (u64)gridDim.x * TWARPS, w = (u64)blockIdx.x * TWARPS + warp;
-    const u64 r0 = rows_total * w / W, r1 = rows_total * (w + 1) / W;
+    const u64 steps_total = (cp.total + TSTEP_BYTES - 1) / TSTEP_BYTES;
+    const u64 W = (u64)gridDim.x * TW, w = (u64)blockIdx.x * TW + warp;
+    const u64 r0 = steps_total * w / W, r1 = steps_total * (w + 1) / W;
     const u64 span_base = r0 * TSTEP_BYTES;
-    const u8 *p = cp.text + span_base + ln * TCHUNK;
-    // the first step's text is requested before the tables are copied in, so HBM latency overlaps the copy
-    uint4 cur0 = make_uint4(0, 0, 0, 0), cur1 = cur0;
-    uint2 before = make_uint2(0, 0);
-    if (r0 < r1) {
-        cur0 = *reinterpret_cast<const uint4 *>(p);
-        cur1 = *reinterpret_cast<const uint4 *>(p + 16);
-        before = *reinterpret_cast<const uint2 *>(cp.text + span_base - 8);  // FRONT_PAD keeps this in bounds
+    const u32 nsteps = (u32)(r1 - r0);
+    const u8 *gsrc = cp.text + span_base - THALO;  // FRONT_PAD keeps the first halo in bounds, BACK_PAD the last step
+    // the warp's first steps are requested before the tables are copied in, so HBM latency overlaps the copy
+    if (ln == 0) {
+#pragma unroll
+        for (int b = 0; b < TNBUF; b++) mbar_init(&ws.mbar[b], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+#pragma unroll
+        for (int b = 0; b < TNBUF; b++)
+            if ((u32)b < nsteps) bulk_load(ws.text[b], gsrc + (size_t)b * TSTEP_BYTES, TBUF_BYTES, &ws.mbar[b]);
+        ws.stage_n = 0;
     }
     {
         // every CTA copies the same tables: each starts at a different offset so that the SMs do not all ask
@@ -227,7 +261,7 @@ __global__ void __launch_bounds__(TTHREADS, 1) k_turbo(const DevDb db, const Dev
         uint4 *dst = reinterpret_cast<uint4 *>(tab);
         const u32 n1 = rows / 2, rot1 = (u32)(((u64)blockIdx.x * n1) / gridDim.x) & ~31u;
 #pragma unroll 4
-        for (u32 i = threadIdx.x; i < n1; i += TTHREADS) {
+        for (u32 i = threadIdx.x; i < n1; i += NT) {
             const u32 j = (i + rot1) & (n1 - 1);
             dst[j] = __ldg(src + j);
         }
@@ -235,73 +269,88 @@ __global__ void __launch_bounds__(TTHREADS, 1) k_turbo(const DevDb db, const Dev
         uint4 *bdst = reinterpret_cast<uint4 *>(bloom);
         const u32 n2 = bloom_words / 4, rot2 = (u32)(((u64)blockIdx.x * n2) / gridDim.x) & ~31u;
 #pragma unroll 4
-        for (u32 i = threadIdx.x; i < n2; i += TTHREADS) {
+        for (u32 i = threadIdx.x; i < n2; i += NT) {
             const u32 j = (i + rot2) & (n2 - 1);
             bdst[j] = __ldg(bsrc + j);
         }
     }
-    if (ln == 0) wsh[warp].stage_n = 0;
     __syncthreads();
 
-    const Ctx c{db, cp, ar, wsh[warp].q2, wsh[warp].stage, &wsh[warp].stage_n, TSTAGE, nullptr, nullptr};
-    u16 *q1 = wsh[warp].q1;
-    u32 *q2 = wsh[warp].q2, *wtext = wsh[warp].text;
+    const Ctx c{db, cp, ar, ws.q2, ws.stage, &ws.stage_n, ORDERED ? 0u : (u32)TSTAGE, nullptr, nullptr};
+    u16 *q1 = ws.q1;
+    u32 *q2 = ws.q2;
     const u32 H1shift = 32 - db.tH1;
     u32 n_cand = 0, n_probe = 0;
     Rec *seg = ORDERED ? ar.recs + (size_t)w * ar.seg_cap : nullptr;
-    u32 cursor = 0;
-    if (r0 < r1) {
-        u32 q2n = 0;
-        u32 carry2 = before.x, carry3 = before.y;
-        const u32 nrows = (u32)(r1 - r0);
+    u32 cursor = 0, q2n = 0;
 #pragma unroll 1
-        for (u32 row = 0; row < nrows; row++) {
-            uint4 nxt0 = make_uint4(0, 0, 0, 0), nxt1 = nxt0;
-            if (row + 1 < nrows) {
-                nxt0 = *reinterpret_cast<const uint4 *>(p + (size_t)(row + 1) * TSTEP_BYTES);
-                nxt1 = *reinterpret_cast<const uint4 *>(p + (size_t)(row + 1) * TSTEP_BYTES + 16);
-            }
-            u32 p2 = __shfl_up_sync(0xffffffffu, cur1.z, 1), p3 = __shfl_up_sync(0xffffffffu, cur1.w, 1);
-            if (ln == 0) { p2 = carry2; p3 = carry3; }
-            carry2 = __shfl_sync(0xffffffffu, cur1.z, 31);
-            carry3 = __shfl_sync(0xffffffffu, cur1.w, 31);
-            // stage the step's text for the second tier (the previous step's candidates are all done)
-            *reinterpret_cast<uint4 *>(wtext + 4 + ln * 8) = cur0;
-            *reinterpret_cast<uint4 *>(wtext + 8 + ln * 8) = cur1;
-            if (ln == 0) { wtext[2] = p2; wtext[3] = p3; }
-            const u32 E[TEW] = {p2, p3, cur0.x, cur0.y, cur0.z, cur0.w, cur1.x, cur1.y, cur1.z, cur1.w};
-            u32 m = turbo_chunk<K>(tab, H1shift, E);
-            const u32 pos0 = ln * TCHUNK, step_pos = row * TSTEP_BYTES;
-            const u64 g0 = span_base + step_pos + pos0;
-            if (g0 + TCHUNK > cp.total) m &= g0 >= cp.total ? 0u : ~(0xffffffffu >> (int)(cp.total - g0));
-            while (__any_sync(0xffffffffu, m != 0)) {
-                // queue this step's candidates in position order: lane order, then descending bit = ascending
-                // byte; whatever does not fit below TQ1CAP stays in m for the next pass
-                const u32 n = __popc(m);
-                u32 incl = n;
+    for (u32 step = 0; step < nsteps; step++) {
+        const u32 b = step % TNBUF;
+        mbar_wait(&ws.mbar[b], (step / TNBUF) & 1);
+        const u8 *buf = ws.text[b];
+        // lane chunk of row r: buffer bytes [THALO + r * 512 + ln * 16, +16); the 8 bytes before it come from
+        // the neighbouring chunk (or the halo) in the same buffer
+        u32 m = 0;
 #pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    const u32 t = __shfl_up_sync(0xffffffffu, incl, d);
-                    if (ln >= (u32)d) incl += t;
-                }
-                u32 slot = incl - n;
-                while (m && slot < TQ1CAP) {
-                    const u32 lz = __clz(m);
-                    q1[slot++] = (u16)(pos0 + lz);
-                    m &= ~(0x80000000u >> lz);
-                }
-                u32 qn = __shfl_sync(0xffffffffu, incl, 31);
-                if (qn > TQ1CAP) qn = TQ1CAP;
-                __syncwarp();
-                n_cand += qn;
-                turbo_tier2<ORDERED>(c, bloom, wtext, q1, q2, q2n, span_base, step_pos, qn, n_probe, seg, cursor);
-                __syncwarp();
-            }
-            cur0 = nxt0;
-            cur1 = nxt1;
+        for (int r = 0; r < 2; r++) {
+            const u8 *cb = buf + THALO + r * TROW_BYTES + ln * TCHUNK;
+            const uint4 cur = *reinterpret_cast<const uint4 *>(cb);
+            const uint2 prev = *reinterpret_cast<const uint2 *>(cb - 8);
+            const u32 E[TEW] = {prev.x, prev.y, cur.x, cur.y, cur.z, cur.w};
+            m = (m << 16) | turbo_chunk<K>(tab, H1shift, E);
         }
-        if (q2n) turbo_drain<ORDERED>(c, q2, span_base, q2n, n_probe, seg, cursor);
+        // m: bit 31 - j = position j of the lane's row-0 chunk, bit 15 - j = position j of its row-1 chunk
+        const u32 step_pos = step * TSTEP_BYTES;
+        {
+            const u64 g0 = span_base + step_pos + ln * TCHUNK;  // first byte of the row-0 chunk
+            if (g0 + TROW_BYTES + TCHUNK > cp.total) {  // clip end positions beyond the corpus
+                const long long left0 = (long long)cp.total - (long long)g0, left1 = left0 - TROW_BYTES;
+                const u32 k0 = left0 >= 16 ? 0xffffu : left0 <= 0 ? 0u : (0xffffu << (16 - (int)left0)) & 0xffffu;
+                const u32 k1 = left1 >= 16 ? 0xffffu : left1 <= 0 ? 0u : (0xffffu << (16 - (int)left1)) & 0xffffu;
+                m &= (k0 << 16) | k1;
+            }
+        }
+        while (__any_sync(0xffffffffu, m != 0)) {
+            // queue the step's candidates in position order (row 0 lane-major, then row 1); whatever does not
+            // fit below TQ1CAP stays in m for the next pass.  One scan serves both rows (16-bit fields).
+            const u32 n01 = __popc(m >> 16) | (__popc(m & 0xffffu) << 16);
+            u32 incl = n01;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const u32 t = __shfl_up_sync(0xffffffffu, incl, d);
+                if (ln >= (u32)d) incl += t;
+            }
+            const u32 tot = __shfl_sync(0xffffffffu, incl, 31);
+            const u32 tot0 = tot & 0xffffu;
+            u32 slot0 = (incl & 0xffffu) - (n01 & 0xffffu), slot1 = tot0 + (incl >> 16) - (n01 >> 16);
+            u32 mm = m;
+            while (mm) {
+                const u32 lz = __clz(mm);
+                const bool second = lz >= 16;
+                const u32 slot = second ? slot1 : slot0;
+                if (slot >= TQ1CAP) {
+                    if (second) break;         // row 1 is full from here on
+                    mm &= 0xffffu;             // row 0 is full from here on: skip to row 1 (kept in m below)
+                    continue;
+                }
+                q1[slot] = (u16)(ln * TCHUNK + lz + (second ? TROW_BYTES - 16 : 0));
+                if (second) slot1++; else slot0++;
+                mm &= ~(0x80000000u >> lz);
+                m &= ~(0x80000000u >> lz);
+            }
+            u32 qn = tot0 + (tot >> 16);
+            if (qn > TQ1CAP) qn = TQ1CAP;
+            __syncwarp();
+            n_cand += qn;
+            turbo_tier2<ORDERED>(c, bloom, reinterpret_cast<const u32 *>(buf), q1, q2, q2n, span_base, step_pos, qn, n_probe, seg,
+                                 cursor);
+            __syncwarp();
+        }
+        // the buffer is free: fetch the step TNBUF ahead into it
+        if (ln == 0 && step + TNBUF < nsteps)
+            bulk_load(ws.text[b], gsrc + (size_t)(step + TNBUF) * TSTEP_BYTES, TBUF_BYTES, &ws.mbar[b]);
     }
+    if (q2n) turbo_drain<ORDERED>(c, q2, span_base, q2n, n_probe, seg, cursor);
     if (ORDERED) {
         if (ln == 0) ar.seg_count[w] = cursor;
     }
