@@ -89,6 +89,7 @@ struct DevDb {
     const turbo::Slot *slots;
     const u32 *bloom;     // second filter tier (turbo_tables.h, 3.)
     u32 tK, tH1, tH2, tL, tBL;
+    u32 dbg;              // experiment switches (HSB_DBG), 0 in production
 };
 
 struct DevCorpus {
@@ -837,7 +838,12 @@ struct hs_gpu_scratch {
     DevBuf<u32> seg_count;
     u64 seg_cap_hint = 256;
     long opt_ordered = 1;
-    unsigned long long *d_ctl = nullptr;  // [0] arena count, [1] candidates, [2] probes, [3] error(u32), [4] n_selected
+    // control blocks of 8 words: [0] arena count, [1] candidates, [2] probes, [3] error(u32), [4] n_selected,
+    // [5] largest segment.  Block 0 serves the general path; blocks 1 and 2 alternate between ordered scans
+    // (k_compact clears the block of the next scan, so no memset sits in front of the kernel).
+    unsigned long long *d_ctl = nullptr;
+    u32 ctl_flip = 0;
+    bool ctl_dirty = true;
     unsigned long long *h_ctl = nullptr;  // pinned mirror
     hs_gpu_match_t *h_matches = nullptr;  // pinned
     size_t h_matches_cap = 0;
@@ -944,6 +950,7 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         d.slots = im->d_slots;
         d.bloom = im->d_bloom;
         d.tK = tt.K; d.tH1 = tt.H1; d.tH2 = tt.H2; d.tL = tt.L; d.tBL = tt.BL;
+        d.dbg = getenv("HSB_DBG") ? (u32)atoi(getenv("HSB_DBG")) : 0;
     }
     if (cudaStreamSynchronize(s->stream) != cudaSuccess) { im->release(); delete im; return HS_UNKNOWN_ERROR; }
     s->dbs.push_back(im);
@@ -1007,16 +1014,21 @@ hs_error_t scan_device_ordered(hs_gpu_scratch *s, DbImage *im, const DevCorpus &
     hs_gpu_stats_t &st = s->stats;
     const u32 grid = turbo_grid(s, cp, turbo_warps<true>()), W = grid * turbo_warps<true>();
     CU_OK(s->seg_count.reserve(W));
-    CU_OK(cudaEventRecord(s->ev[1], s->stream));
     for (int attempt = 0;; attempt++) {
         const u64 seg_cap = s->seg_cap_hint;
         if (seg_cap * W > (1ull << 28)) return HS_INSUFFICIENT_SPACE;  // > 4 GiB of segments: not this mode
         CU_OK(s->recs.reserve(seg_cap * W));
         CU_OK(s->recs2.reserve(seg_cap * W));
         CU_OK(s->d_matches.reserve(seg_cap * W));
-        CU_OK(cudaMemsetAsync(s->d_ctl, 0, 8 * sizeof(unsigned long long), s->stream));
-        DevArena ar{s->recs.p, s->d_ctl + 0, s->d_ctl + 1, reinterpret_cast<u32 *>(s->d_ctl + 3), 0, s->seg_count.p, (u32)seg_cap};
-        CU_OK(cudaEventRecord(s->ev[6], s->stream));
+        if (s->ctl_dirty) {
+            CU_OK(cudaMemsetAsync(s->d_ctl + 8, 0, 16 * sizeof(unsigned long long), s->stream));
+            s->ctl_dirty = false;
+        }
+        unsigned long long *ctl = s->d_ctl + 8 + 8 * s->ctl_flip, *ctl_next = s->d_ctl + 8 + 8 * (s->ctl_flip ^ 1);
+        s->ctl_flip ^= 1;
+        s->ctl_dirty = true;  // until this scan's k_compact is known to have run
+        DevArena ar{s->recs.p, ctl + 0, ctl + 1, reinterpret_cast<u32 *>(ctl + 3), 0, s->seg_count.p, (u32)seg_cap};
+        CU_OK(cudaEventRecord(s->ev[1], s->stream));
         hs_error_t rv;
         switch (im->dev.tK) {
         case 1: rv = launch_turbo<1, true>(s, im->dev, cp, ar); break;
@@ -1025,15 +1037,16 @@ hs_error_t scan_device_ordered(hs_gpu_scratch *s, DbImage *im, const DevCorpus &
         default: rv = launch_turbo<4, true>(s, im->dev, cp, ar); break;
         }
         if (rv != HS_SUCCESS) return rv;
-        CU_OK(cudaEventRecord(s->ev[7], s->stream));
         CU_OK(cudaEventRecord(s->ev[2], s->stream));
-        k_compact<<<grid, 256, 0, s->stream>>>(s->recs.p, s->seg_count.p, (u32)seg_cap, W, s->recs2.p, s->d_matches.p, s->d_ctl);
+        k_compact<<<grid, 256, 0, s->stream>>>(s->recs.p, s->seg_count.p, (u32)seg_cap, W, s->recs2.p, s->d_matches.p, ctl, ctl_next);
         CU_OK(cudaGetLastError());
         st.scan_launches++;
         st.kernel_launches += 2;
-        CU_OK(cudaMemcpyAsync(s->h_ctl, s->d_ctl, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
+        // device work ends here; the 64-byte control block read-back that follows is host synchronisation
         CU_OK(cudaEventRecord(s->ev[3], s->stream));
-        CU_OK(cudaEventSynchronize(s->ev[3]));
+        CU_OK(cudaMemcpyAsync(s->h_ctl, ctl, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
+        CU_OK(cudaStreamSynchronize(s->stream));
+        s->ctl_dirty = false;
         const u32 err = (u32)s->h_ctl[3];
         if (err & ERR_COLLECTOR) { im->ordered_ok = false; return HS_INSUFFICIENT_SPACE; }
         if (err) return HS_UNKNOWN_ERROR;
@@ -1044,7 +1057,7 @@ hs_error_t scan_device_ordered(hs_gpu_scratch *s, DbImage *im, const DevCorpus &
     }
     cudaEventElapsedTime(&st.scan_ms, s->ev[1], s->ev[2]);
     cudaEventElapsedTime(&st.sort_ms, s->ev[2], s->ev[3]);
-    cudaEventElapsedTime(&st.kernel_ms, s->ev[6], s->ev[7]);
+    st.kernel_ms = st.scan_ms;  // the last (successful) k_turbo launch alone
     st.raw_matches = st.matches = s->n_matches = s->h_ctl[4];
     st.candidates = s->h_ctl[1];
     st.confirms = s->h_ctl[2];
@@ -1346,7 +1359,7 @@ hs_error_t hs_gpu_alloc_scratch(const hs_database_t *db, hs_gpu_scratch_t **scra
         if (cudaGetDeviceProperties(&prop, s->device) == cudaSuccess) s->sm_count = prop.multiProcessorCount;
         if (cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) != cudaSuccess) { delete s; return HS_UNKNOWN_ERROR; }
         for (auto &e : s->ev) cudaEventCreate(&e);
-        if (cudaMalloc((void **)&s->d_ctl, 8 * sizeof(unsigned long long)) != cudaSuccess ||
+        if (cudaMalloc((void **)&s->d_ctl, 24 * sizeof(unsigned long long)) != cudaSuccess ||
             cudaHostAlloc((void **)&s->h_ctl, 8 * sizeof(unsigned long long), cudaHostAllocDefault) != cudaSuccess) {
             hs_gpu_free_scratch(s);
             return HS_NOMEM;

@@ -9,8 +9,7 @@
 //     (window & msk) == v exactly as confWithBit does; only then is the buffer looked up for the size check.
 #pragma once
 
-constexpr int TQ1CAP = 128;  // tier-1 survivors (positions inside the step) queued per warp; a fuller step is pushed in passes
-constexpr int TQ2CAP = 64;   // tier-2 survivors awaiting the slot-table confirm
+constexpr int TQ2CAP = 96;   // tier-2 survivors awaiting the slot-table confirm (drained 32 at a time)
 constexpr int TSTAGE = 32;   // staged match records per warp (general mode)
 constexpr int TCHUNK = 16;                 // bytes per lane per row (one LDS.128)
 constexpr int TROW_BYTES = 32 * TCHUNK;    // 512
@@ -26,7 +25,6 @@ template <bool ORDERED>
 struct TurboWarpShared {
     __align__(16) u8 text[TNBUF][TBUF_BYTES];  // [THALO bytes before the step][the step], filled by cp.async.bulk
     unsigned long long mbar[TNBUF];            // one mbarrier per buffer (transaction-count completion)
-    u16 q1[TQ1CAP];
     u32 q2[TQ2CAP];
     Rec stage[ORDERED ? 1 : TSTAGE];
     u32 stage_n;
@@ -94,18 +92,16 @@ __device__ __forceinline__ void turbo_confirm(const Ctx &c, u64 g, u32 &n_probe)
     }
 }
 
-// Second tier: the tail bloom.  True when some literal's exact tail may end at the position whose last five
-// text bytes are w40 (byte 4 = the position's own byte).
-__device__ __forceinline__ bool turbo_bloom(const u32 *bloom, const DevDb &db, u64 w40) {
-    const u32 ks = (u32)(w40 >> (40 - 8 * db.tK));
-    const u32 b1 = turbo::bloom_bit(ks, 0, db.tK, db.tBL);
-    bool hit = (bloom[b1 >> 5] >> (b1 & 31)) & 1;
-    if (db.tL) {
-        const u64 kl = w40 >> (40 - 8 * db.tL);
-        const u32 b2 = turbo::bloom_bit((u32)kl, (u32)(kl >> 32), db.tL, db.tBL);
-        hit |= (bool)((bloom[b2 >> 5] >> (b2 & 31)) & 1);
-    }
-    return hit;
+// Second tier: the tail table (turbo_tables.h, 3.).  One shared-memory word per position: true when some
+// literal's (K+1)-byte tail -- or K-byte tail, for a literal that short -- may end at the position.
+// ktail = the position's K-byte tail (first byte lowest); extra = a register whose low byte is the byte before it.
+__device__ __forceinline__ bool turbo_tail_hit(const u32 *tail_tab, u32 word_shift, bool has_long, u32 ktail, u32 extra) {
+    const u32 h = turbo::tail_hash(ktail);
+    const u32 w = tail_tab[h >> word_shift];
+    // funnel shifts look at the low 5 bits of the shift register only (turbo::tail_short_mask / tail_long_mask)
+    u32 r = __funnelshift_r(w, 0u, h);
+    if (has_long) r |= __funnelshift_r(w, 0u, extra);
+    return r & 1;
 }
 
 // Warp-synchronous confirm of `count` (<= 32) tier-2 survivors c.q2[0..count) (ascending), one lane each.
@@ -139,34 +135,100 @@ __device__ void turbo_drain(const Ctx &c, const u32 *q2, u64 span_base, u32 coun
     }
 }
 
-// Warp-synchronous second tier over the `count` queued step positions q1[0..count): each lane reads its
-// candidate's last five bytes from the warp's staged text (shared memory), survivors are appended to q2 in
-// order as span-relative positions; q2 is confirmed whenever it holds 32.
+// Second tier, lane-local: every lane walks the set bits of its own tier-1 mask -- two per round, from both
+// ends, so two independent lookups are in flight -- reads the candidate's tail from the warp's staged text
+// (shared memory) and keeps the bit when the tail table hits.
+// m: bit 31 - j = position j of the lane's row-0 chunk, bit 15 - j = position j of its row-1 chunk.
+template <int K>
+__device__ __forceinline__ bool turbo_tier2_one(const u32 *tail_tab, u32 word_shift, bool has_long, const u8 *wtext, u32 ln, u32 lz) {
+    const u32 pos = ln * TCHUNK + (lz & 15) + (lz >= 16 ? TROW_BYTES : 0);
+    if (K <= 3) {
+        // the four bytes ending at the position: K-tail on top, the byte before it right below
+        const u32 first = THALO + pos - 3;
+        const u32 *wp = reinterpret_cast<const u32 *>(wtext + (first & ~3u));
+        const u32 w4 = __funnelshift_r(wp[0], wp[1], first << 3);
+        return turbo_tail_hit(tail_tab, word_shift, has_long, w4 >> (8 * (4 - K)), w4 >> (8 * (3 - K)));
+    } else {
+        const u32 first = THALO + pos - 4;
+        const u32 *wp = reinterpret_cast<const u32 *>(wtext + (first & ~3u));
+        const u32 a = wp[0], b = wp[1];
+        const u32 extra = __funnelshift_r(a, b, first << 3);          // low byte = text[pos - 4]
+        const u32 ktail = __funnelshift_r(a, b, (first << 3) + 8);    // wrong when first & 3 == 3 (shift 32): fixed below
+        return turbo_tail_hit(tail_tab, word_shift, has_long, (first & 3) == 3 ? b : ktail, extra);
+    }
+}
+template <int K>
+__device__ __forceinline__ u32 turbo_tier2(const u32 *tail_tab, const DevDb &db, const u8 *wtext, u32 m) {
+    const u32 ln = lane_id(), word_shift = 37 - db.tBL;
+    const bool has_long = db.tL != 0;
+    u32 keep = 0;
+    while (m) {
+        const u32 lzA = __clz(m), bitA = 0x80000000u >> lzA;
+        m ^= bitA;
+        const u32 bitB = m & (0u - m);  // lowest remaining bit (0 when none)
+        m ^= bitB;
+        const u32 lzB = __clz(bitB | 1u);  // bitB == 0 probes the lane's last position; the result is dropped
+        const bool hitA = turbo_tier2_one<K>(tail_tab, word_shift, has_long, wtext, ln, lzA);
+        const bool hitB = turbo_tier2_one<K>(tail_tab, word_shift, has_long, wtext, ln, lzB);
+        if (hitA) keep |= bitA;
+        if (hitB) keep |= bitB;
+    }
+    return keep;
+}
+
+// Warp-synchronous: append the step's tier-2 survivors (mask layout as above) to q2 in position order -- row 0
+// lane-major, then row 1 -- as span-relative positions; q2 is confirmed whenever it holds 32.
 template <bool ORDERED>
-__device__ __forceinline__ void turbo_tier2(const Ctx &c, const u32 *bloom, const u32 *wtext, const u16 *q1, u32 *q2, u32 &q2n,
-                                            u64 span_base, u32 step_pos, u32 count, u32 &n_probe, Rec *seg, u32 &cursor) {
-    const u32 ln = lane_id();
-    for (u32 base = 0; base < count; base += 32) {
-        const u32 idx = base + ln;
-        bool pass = false;
-        u32 pos = 0;
-        if (idx < count) {
-            pos = q1[idx];
-            const u32 first = 16 + pos - 4;  // byte index of text[pos - 4] in wtext
-            const u32 lo = wtext[first >> 2], hi = wtext[(first >> 2) + 1];
-            const u64 both = ((u64)hi << 32) | lo;
-            pass = turbo_bloom(bloom, c.db, (both >> (8 * (first & 3))) & 0xffffffffffull);
+__device__ __forceinline__ void turbo_push(const Ctx &c, u32 m, u32 *q2, u32 &q2n, u64 span_base, u32 step_pos, u32 &n_probe,
+                                           Rec *seg, u32 &cursor) {
+    const u32 ln = lane_id(), lt = (1u << ln) - 1;
+    const u32 n0 = __popc(m >> 16), n1 = __popc(m & 0xffffu);
+    u32 slot0, slot1, total;
+    if (!__any_sync(0xffffffffu, (n0 | n1) > 1)) {
+        // common case: at most one survivor per lane and row -- two ballots rank them
+        const u32 b0 = __ballot_sync(0xffffffffu, n0 != 0), b1 = __ballot_sync(0xffffffffu, n1 != 0);
+        slot0 = __popc(b0 & lt);
+        slot1 = __popc(b0) + __popc(b1 & lt);
+        total = __popc(b0) + __popc(b1);
+    } else {
+        // one inclusive scan serves both rows (16-bit fields)
+        const u32 n01 = n0 | (n1 << 16);
+        u32 incl = n01;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const u32 t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (ln >= (u32)d) incl += t;
         }
-        const u32 bal = __ballot_sync(0xffffffffu, pass);
-        if (pass) q2[q2n + __popc(bal & ((1u << ln) - 1))] = step_pos + pos;
-        q2n += __popc(bal);
+        const u32 tot = __shfl_sync(0xffffffffu, incl, 31);
+        slot0 = (incl & 0xffffu) - n0;
+        slot1 = (tot & 0xffffu) + (incl >> 16) - n1;
+        total = (tot & 0xffffu) + (tot >> 16);
+    }
+    // q2 holds fewer than 32 entries on entry; a step adds at most TQ2CAP - 32 per pass
+    u32 done = 0;  // survivors of this step already moved to q2 (warp-uniform)
+    while (done < total) {
+        const u32 room = TQ2CAP - q2n, lim = done + room;  // this pass takes ranks [done, lim)
+        u32 mm = m, s0 = slot0, s1 = slot1;
+        while (mm) {
+            const u32 lz = __clz(mm);
+            mm &= ~(0x80000000u >> lz);
+            const bool second = lz >= 16;
+            const u32 rank = second ? s1++ : s0++;
+            if (rank >= done && rank < lim)
+                q2[q2n + rank - done] = step_pos + ln * TCHUNK + (lz & 15) + (second ? TROW_BYTES : 0);
+        }
+        const u32 took = total - done < room ? total - done : room;
+        q2n += took;
+        done += took;
         __syncwarp();
-        if (q2n >= 32) {
+        while (q2n >= 32) {
             turbo_drain<ORDERED>(c, q2, span_base, 32, n_probe, seg, cursor);
             const u32 rem = q2n - 32;
-            const u32 keep = ln < rem ? q2[32 + ln] : 0;
+            // slide the remainder (< TQ2CAP - 32 = 64 entries) down
+            const u32 k0 = ln < rem ? q2[32 + ln] : 0, k1 = 32 + ln < rem ? q2[64 + ln] : 0;
             __syncwarp();
-            if (ln < rem) q2[ln] = keep;
+            if (ln < rem) q2[ln] = k0;
+            if (32 + ln < rem) q2[32 + ln] = k1;
             __syncwarp();
             q2n = rem;
         }
@@ -198,8 +260,13 @@ __device__ __forceinline__ u32 shared_reg(const u32 (&E)[TEW]) {
 template <int K, int i>
 struct TurboPairs {
     static __device__ __forceinline__ void run(const u64 *tab, u32 H1shift, const u32 (&E)[TEW], u32 xprev, u32 xi, u32 &acc) {
-        const u32 row = (xi * turbo::PAIR_MULT) >> H1shift;
-        const u64 ent = tab[row];
+        u64 ent;
+        if (K == 3) {  // direct 7 + 7 bit index (turbo::pair_row), as a byte offset: two shifts and one LOP3
+            const u32 off = ((xi << 3) & 0x3f8u) | ((xi << 2) & 0x1fc00u);
+            ent = *reinterpret_cast<const u64 *>(reinterpret_cast<const u8 *>(tab) + off);
+        } else {
+            ent = tab[(xi * turbo::PAIR_MULT) >> H1shift];
+        }
         const u32 xnext = i + 2 < TCHUNK ? shared_reg<K, (i + 2 < TCHUNK ? i + 2 : i)>(E) : 0u;
         u32 yA, yB;
         if (K == 4) yA = xprev; else yA = byte_reg<i - K + 8>(E);                         // low 5 bits of text[i-K]
@@ -277,7 +344,6 @@ __global__ void __launch_bounds__(turbo_warps<ORDERED>() * 32, 1) k_turbo(const 
     __syncthreads();
 
     const Ctx c{db, cp, ar, ws.q2, ws.stage, &ws.stage_n, ORDERED ? 0u : (u32)TSTAGE, nullptr, nullptr};
-    u16 *q1 = ws.q1;
     u32 *q2 = ws.q2;
     const u32 H1shift = 32 - db.tH1;
     u32 n_cand = 0, n_probe = 0;
@@ -300,6 +366,7 @@ __global__ void __launch_bounds__(turbo_warps<ORDERED>() * 32, 1) k_turbo(const 
             m = (m << 16) | turbo_chunk<K>(tab, H1shift, E);
         }
         // m: bit 31 - j = position j of the lane's row-0 chunk, bit 15 - j = position j of its row-1 chunk
+        if (db.dbg & 1) { if (m == 0x12345678u) n_probe++; m = 0; }
         const u32 step_pos = step * TSTEP_BYTES;
         {
             const u64 g0 = span_base + step_pos + ln * TCHUNK;  // first byte of the row-0 chunk
@@ -310,42 +377,11 @@ __global__ void __launch_bounds__(turbo_warps<ORDERED>() * 32, 1) k_turbo(const 
                 m &= (k0 << 16) | k1;
             }
         }
-        while (__any_sync(0xffffffffu, m != 0)) {
-            // queue the step's candidates in position order (row 0 lane-major, then row 1); whatever does not
-            // fit below TQ1CAP stays in m for the next pass.  One scan serves both rows (16-bit fields).
-            const u32 n01 = __popc(m >> 16) | (__popc(m & 0xffffu) << 16);
-            u32 incl = n01;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const u32 t = __shfl_up_sync(0xffffffffu, incl, d);
-                if (ln >= (u32)d) incl += t;
-            }
-            const u32 tot = __shfl_sync(0xffffffffu, incl, 31);
-            const u32 tot0 = tot & 0xffffu;
-            u32 slot0 = (incl & 0xffffu) - (n01 & 0xffffu), slot1 = tot0 + (incl >> 16) - (n01 >> 16);
-            u32 mm = m;
-            while (mm) {
-                const u32 lz = __clz(mm);
-                const bool second = lz >= 16;
-                const u32 slot = second ? slot1 : slot0;
-                if (slot >= TQ1CAP) {
-                    if (second) break;         // row 1 is full from here on
-                    mm &= 0xffffu;             // row 0 is full from here on: skip to row 1 (kept in m below)
-                    continue;
-                }
-                q1[slot] = (u16)(ln * TCHUNK + lz + (second ? TROW_BYTES - 16 : 0));
-                if (second) slot1++; else slot0++;
-                mm &= ~(0x80000000u >> lz);
-                m &= ~(0x80000000u >> lz);
-            }
-            u32 qn = tot0 + (tot >> 16);
-            if (qn > TQ1CAP) qn = TQ1CAP;
-            __syncwarp();
-            n_cand += qn;
-            turbo_tier2<ORDERED>(c, bloom, reinterpret_cast<const u32 *>(buf), q1, q2, q2n, span_base, step_pos, qn, n_probe, seg,
-                                 cursor);
-            __syncwarp();
-        }
+        n_cand += __popc(m);
+        m = turbo_tier2<K>(bloom, db, buf, m);
+        if (db.dbg & 2) { if (m == 0x12345678u) n_probe++; m = 0; }
+        if (__any_sync(0xffffffffu, m != 0)) turbo_push<ORDERED>(c, m, q2, q2n, span_base, step_pos, n_probe, seg, cursor);
+        __syncwarp();
         // the buffer is free: fetch the step TNBUF ahead into it
         if (ln == 0 && step + TNBUF < nsteps)
             bulk_load(ws.text[b], gsrc + (size_t)(step + TNBUF) * TSTEP_BYTES, TBUF_BYTES, &ws.mbar[b]);
@@ -356,7 +392,10 @@ __global__ void __launch_bounds__(turbo_warps<ORDERED>() * 32, 1) k_turbo(const 
     }
     if (!ORDERED) flush_stage(c);
 #pragma unroll
-    for (int d = 16; d; d >>= 1) n_probe += __shfl_down_sync(0xffffffffu, n_probe, d);
+    for (int d = 16; d; d >>= 1) {
+        n_probe += __shfl_down_sync(0xffffffffu, n_probe, d);
+        n_cand += __shfl_down_sync(0xffffffffu, n_cand, d);
+    }
     if (ln == 0) {
         if (n_cand) atomicAdd(&ar.stats[0], (unsigned long long)n_cand);
         if (n_probe) atomicAdd(&ar.stats[1], (unsigned long long)n_probe);
@@ -364,28 +403,47 @@ __global__ void __launch_bounds__(turbo_warps<ORDERED>() * 32, 1) k_turbo(const 
 }
 
 // Ordered mode epilogue: exclusive scan of the per-warp segment counts, then gather the segments into one
-// contiguous, position-ordered array (as Rec and as hs_gpu_match_t).  ctl[4] = records kept, ctl[5] = largest
-// count any warp wanted (> seg_cap means the launch must be repeated with larger segments).
+// contiguous, position-ordered array (as Rec and as hs_gpu_match_t), one warp per segment.  ctl[4] = records
+// kept, ctl[5] = largest count any warp wanted (> seg_cap means the launch must be repeated with larger
+// segments).  Block 0 also clears `ctl_next`, the control block of the next scan.
 __global__ void __launch_bounds__(256) k_compact(const Rec *recs, const u32 *seg_count, u32 seg_cap, u32 W, Rec *out_recs,
-                                                 hs_gpu_match_t *out, unsigned long long *ctl) {
+                                                 hs_gpu_match_t *out, unsigned long long *ctl, unsigned long long *ctl_next) {
     __shared__ u32 pre[8193];
     __shared__ u32 part[256];
-    __shared__ u32 mx[256];
-    const u32 per = (W + 255) / 256, t = threadIdx.x;
+    __shared__ u32 wsum[8], wmax[8];
+    const u32 per = (W + 255) / 256, t = threadIdx.x, ln = t & 31, wid = t >> 5;
     u32 sum = 0, big = 0;
     for (u32 i = t * per; i < (t + 1) * per && i < W; i++) {
         const u32 cnt = seg_count[i];
         big = cnt > big ? cnt : big;
         sum += cnt < seg_cap ? cnt : seg_cap;
     }
-    part[t] = sum;
-    mx[t] = big;
+    // block-wide exclusive scan of the 256 partial sums (warp scans + scan of the 8 warp totals)
+    u32 incl = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const u32 v = __shfl_up_sync(0xffffffffu, incl, d);
+        if (ln >= (u32)d) incl += v;
+    }
+#pragma unroll
+    for (int d = 16; d; d >>= 1) {
+        const u32 v = __shfl_down_sync(0xffffffffu, big, d);
+        big = v > big ? v : big;
+    }
+    if (ln == 31) wsum[wid] = incl;
+    if (ln == 0) wmax[wid] = big;
     __syncthreads();
-    if (t == 0) {
-        u32 run = 0, m = 0;
-        for (int i = 0; i < 256; i++) { const u32 v = part[i]; part[i] = run; run += v; m = mx[i] > m ? mx[i] : m; }
-        pre[8192] = run;
-        if (blockIdx.x == 0) { ctl[4] = run; ctl[5] = m; }
+    u32 base = 0, total = 0, m = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        if ((u32)k < wid) base += wsum[k];
+        total += wsum[k];
+        m = wmax[k] > m ? wmax[k] : m;
+    }
+    part[t] = base + incl - sum;
+    if (blockIdx.x == 0) {
+        if (t == 0) { ctl[4] = total; ctl[5] = m; }
+        if (t < 8) ctl_next[t] = 0;
     }
     __syncthreads();
     u32 run = part[t];
@@ -395,9 +453,9 @@ __global__ void __launch_bounds__(256) k_compact(const Rec *recs, const u32 *seg
         run += cnt < seg_cap ? cnt : seg_cap;
     }
     __syncthreads();
-    for (u32 w = blockIdx.x; w < W; w += gridDim.x) {
+    for (u32 w = blockIdx.x * 8 + wid; w < W; w += gridDim.x * 8) {
         const u32 cnt = seg_count[w], n = cnt < seg_cap ? cnt : seg_cap, at = pre[w];
-        for (u32 i = t; i < n; i += 256) {
+        for (u32 i = ln; i < n; i += 32) {
             const Rec r = recs[(size_t)w * seg_cap + i];
             out_recs[at + i] = r;
             out[at + i] = hs_gpu_match_t{r.buf, r.id, (uint64_t)r.to};

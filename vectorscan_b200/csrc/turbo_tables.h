@@ -15,12 +15,14 @@
 //     slot carries the LitInfo's v / msk / size and the literal's Rose program pre-decoded when it is one of
 //     the three shapes the compiler emits for plain reports (REPORT | FINAL_REPORT, optionally guarded by one
 //     CHECK_MED_LIT[_NOCASE]); anything else keeps its program offset and is interpreted.
-//  3. TAIL BLOOM (shared memory, 2^BL bits, one hash).  Second filter tier, consulted only for the positions
-//     the pair table lets through.  A literal whose LitInfo.size >= L (L = K + 1) is filed under the hash of
-//     its exact L-byte tail, a shorter one under its K-byte tail; a position survives when either probe hits.
-//     The pair table alone passes every position whose K-tail LOOKS like some literal's (it indexes the extra
-//     byte by 5 bits only); the bloom cuts that to (nearly) the positions where a literal's full L-tail is
-//     present, so the L2-resident slot table is probed an order of magnitude less often.
+//  3. TAIL TABLE (shared memory, 2^(BL-5) words of 32 bits).  Second filter tier, consulted only for the
+//     positions the pair table lets through, ONE lookup per position: the word is chosen by a hash of the K-byte
+//     tail.  A literal of exactly K bytes -- or one whose longer tail cannot be enumerated -- sets the bit
+//     picked by the low 5 bits of that hash; a literal of more than K bytes sets the bit picked by the low 5
+//     bits of the byte BEFORE its K-tail.  A position survives when either of its two bits is set.  The pair table alone passes every position whose K-tail
+//     LOOKS like some literal's (it indexes the extra byte by 5 bits only); this cuts that to (nearly) the
+//     positions where a literal's (K+1)-byte tail is present, so the L2-resident slot table is probed an order
+//     of magnitude less often.
 #pragma once
 #include "hsb_dbview.h"
 
@@ -52,19 +54,27 @@ HSB_HD u32 pack_shared(u32 K, u32 s0, u32 s1, u32 s2) {
     default: return 0;
     }
 }
-HSB_HD u32 pair_row(u32 packed, u32 H1) { return (packed * PAIR_MULT) >> (32 - H1); }
-HSB_HD u32 slot_home(u32 key, u32 H2) { return (key * SLOT_MULT) >> (32 - H2); }
-// bloom bit index of an n-byte tail (first tail byte in the low byte of lo; hi = bytes 4.. of the tail)
-HSB_HD u32 bloom_bit(u32 lo, u32 hi, u32 n, u32 BL) {
-    const u32 h = (lo * 0x9E3779B1u) ^ (hi * 0x85EBCA6Bu) ^ (n * 0xC2B2AE35u);  // top bits: multiplicative hash
-    return h >> (32 - BL);
+// Row of the pair table.  K == 3 (two shared bytes): the low 7 bits of each byte index a 2^14-row table
+// directly -- no collisions at all on ASCII text, 4-to-1 aliasing on binary data (what a hash would give too).
+// Other K: multiplicative hash of the packed shared bytes.
+HSB_HD u32 pair_row(u32 K, u32 packed, u32 H1) {
+    if (K == 3) return (packed & 0x7f) | ((packed >> 1) & 0x3f80);
+    return (packed * PAIR_MULT) >> (32 - H1);
 }
+HSB_HD u32 slot_home(u32 key, u32 H2) { return (key * SLOT_MULT) >> (32 - H2); }
+// tail table addressing: h = tail_hash(K-tail, first tail byte lowest); the word comes from the top bits of h,
+// a short literal's bit from the low 5 bits of h, a long literal's bit from the low 5 bits of the byte before
+// its K-tail (both are what a funnel shift by that register looks at: no masking in the kernel)
+HSB_HD u32 tail_hash(u32 ktail) { return ktail * 0x9E3779B1u; }
+HSB_HD u32 tail_word(u32 h, u32 BL) { return h >> (37 - BL); }            // top BL - 5 bits
+HSB_HD u32 tail_short_mask(u32 h) { return 1u << (h & 31); }
+HSB_HD u32 tail_long_mask(u32 extra) { return 1u << (extra & 31); }
 
 struct Tables {
     u32 K = 0, H1 = 0, H2 = 0;
     std::vector<u64> pair;   // low 32 bits = A, high 32 bits = B
     std::vector<Slot> slots;
-    u32 L = 0, BL = 0;       // long-tail length (0: every literal is K bytes long) and log2(bloom bits)
+    u32 L = 0, BL = 0;       // long-tail length K + 1 (0: every literal is K bytes long) and log2(tail table bits)
     std::vector<u32> bloom;
     u64 variants = 0;
     bool all_simple = true;  // every literal's program pre-decoded to a plain report (no interpreter needed)
@@ -157,40 +167,41 @@ inline bool build(const DbView &d, Tables &t) {
         if (vars.size() > (1u << 22)) return false;
     }
     t.variants = vars.size();
-    t.H1 = vars.size() >= 512 ? (getenv("HSB_H1") ? atoi(getenv("HSB_H1")) : 14) : (vars.size() >= 64 ? 12 : 10);
+    t.H1 = (K == 3 || vars.size() >= 512) ? 14 : (vars.size() >= 64 ? 12 : 10);
     t.pair.assign((size_t)1 << t.H1, 0);
     for (const Var &v : vars) {
         u32 b[4] = {0, 0, 0, 0};
         for (u32 j = 0; j < K; j++) b[j] = (v.key >> (8 * j)) & 0xff;
         // A: extra byte first (b[0]), shared = b[1..K-1];  B: shared = b[0..K-2], extra byte last (b[K-1])
         const u32 sa = pack_shared(K, b[1], b[2], b[3]), sb = pack_shared(K, b[0], b[1], b[2]);
-        t.pair[pair_row(sa, t.H1)] |= 1ull << (31 - (b[0] & 31));  // sets are stored bit-reversed (turbo.cuh)
-        t.pair[pair_row(sb, t.H1)] |= 1ull << (63 - (b[K - 1] & 31));
+        t.pair[pair_row(K, sa, t.H1)] |= 1ull << (31 - (b[0] & 31));  // sets are stored bit-reversed (turbo.cuh)
+        t.pair[pair_row(K, sb, t.H1)] |= 1ull << (63 - (b[K - 1] & 31));
     }
-    // tail bloom
+    // tail table
     {
         u32 longest = 0;
         for (const LitRec *l : live) longest = std::max<u32>(longest, l->size);
         t.L = longest > K ? K + 1 : 0;
-        std::vector<std::pair<u64, u32>> entries;  // (tail, length)
+        struct Entry { u32 ktail; u32 extra; bool is_long; };
+        std::vector<Entry> entries;
         std::vector<u64> keys;
         for (const LitRec *l : live) {
             if (t.L && l->size >= t.L && tail_variants(*l, t.L, 256, keys)) {
-                for (u64 k : keys) entries.push_back({k, t.L});
+                for (u64 k : keys) entries.push_back({(u32)(k >> 8), (u32)(k & 0xff), true});
             } else {
                 if (!tail_variants(*l, K, 4096, keys)) return false;
-                for (u64 k : keys) entries.push_back({k, K});
+                for (u64 k : keys) entries.push_back({(u32)k, 0, false});
             }
         }
-        // 2^18 bits (32 KiB) at most: with the 128 KiB pair table, the per-warp text staging and queues it
+        // 2^18 bits (32 KiB) at most: with the 128 KiB pair table and the per-warp text buffers and queues it
         // has to fit the 227 KiB of shared memory an SM offers
         u32 BL = 13;
-        while (BL < 18 && ((size_t)1 << BL) < entries.size() * 64) BL++;
+        while (BL < 18 && ((size_t)1 << BL) < entries.size() * 32) BL++;
         t.BL = BL;
         t.bloom.assign((size_t)1 << (BL - 5), 0);
-        for (const auto &e : entries) {
-            const u32 bit = bloom_bit((u32)e.first, (u32)(e.first >> 32), e.second, BL);
-            t.bloom[bit >> 5] |= 1u << (bit & 31);
+        for (const Entry &e : entries) {
+            const u32 h = tail_hash(e.ktail);
+            t.bloom[tail_word(h, BL)] |= e.is_long ? tail_long_mask(e.extra) : tail_short_mask(h);
         }
     }
     u32 H2 = 4;
