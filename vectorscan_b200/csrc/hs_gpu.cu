@@ -89,7 +89,6 @@ struct DevDb {
     const turbo::Slot *slots;
     const u32 *bloom;     // second filter tier (turbo_tables.h, 3.)
     u32 tK, tH1, tH2, tL, tBL;
-    u32 dbg;              // experiment switches (HSB_DBG), 0 in production
 };
 
 struct DevCorpus {
@@ -200,18 +199,44 @@ __device__ __forceinline__ void flush_stage(const Ctx &c) {
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ u8 upcase(u8 c) { return (c >= 'a' && c <= 'z') ? (u8)(c - 0x20) : c; }
 
+// 8 bytes starting at p (first byte lowest), from 8-byte aligned loads; may touch up to 7 bytes either side
+__device__ __forceinline__ u64 load_u64_unaligned(const u8 *p) {
+    const uintptr_t ap = reinterpret_cast<uintptr_t>(p);
+    const u64 *q = reinterpret_cast<const u64 *>(ap & ~(uintptr_t)7);
+    const unsigned sh = (unsigned)(ap & 7) * 8;
+    const u64 lo = q[0];
+    if (!sh) return lo;
+    return (lo >> sh) | (q[1] << (64 - sh));
+}
+
+// clear bit 5 of every byte that is an ASCII lower-case letter (8 bytes at a time)
+__device__ __forceinline__ u64 upcase8(u64 x) {
+    const u64 k7f = 0x7f7f7f7f7f7f7f7full, low = x & k7f;
+    // per byte, bit 7 set iff 'a' <= low byte <= 'z' and the original byte was below 0x80
+    const u64 ge_a = low + (0x80 - 'a') * 0x0101010101010101ull;
+    const u64 le_z = low + (0x7f - 'z') * 0x0101010101010101ull;
+    const u64 is_lower = ge_a & ~le_z & ~x & 0x8080808080808080ull;
+    return x ^ (is_lower >> 2);
+}
+
+// roseCheckMediumLiteral / roseCheckLongLiteral in block mode (src/rose/program_runtime.c:1954-2013): the
+// lit_len bytes ending at `to` equal the literal (stored upper-cased when nocase).  Compared 8 bytes at a
+// time; the bytecode copy is padded (upload_database) and the text has pads either side.
 __device__ bool check_literal(const u8 *bc, u32 lit_off, u32 lit_len, bool nocase, const u8 *btext, u32 to) {
-    if (to < lit_len) return false;  // roseCheckMediumLiteral: "too short"
+    if (to < lit_len) return false;  // "too short"
     const u8 *t = btext + (to - lit_len);
     const u8 *l = bc + lit_off;
-    if (nocase) {
-        for (u32 i = 0; i < lit_len; i++)
-            if (upcase(t[i]) != l[i]) return false;  // literal text is stored upper-cased
-    } else {
-        for (u32 i = 0; i < lit_len; i++)
-            if (t[i] != l[i]) return false;
+    u64 diff = 0;
+    for (u32 i = 0; i < lit_len; i += 8) {
+        u64 a = load_u64_unaligned(t + i);
+        const u64 b = load_u64_unaligned(l + i);
+        if (nocase) a = upcase8(a);
+        u64 d = a ^ b;
+        const u32 left = lit_len - i;
+        if (left < 8) d &= (1ull << (8 * left)) - 1;
+        diff |= d;
     }
-    return true;
+    return diff == 0;
 }
 
 // roseCheckMask (src/rose/program_runtime.c:644-727) in block mode: bytes outside the buffer are don't-care
@@ -950,7 +975,6 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         d.slots = im->d_slots;
         d.bloom = im->d_bloom;
         d.tK = tt.K; d.tH1 = tt.H1; d.tH2 = tt.H2; d.tL = tt.L; d.tBL = tt.BL;
-        d.dbg = getenv("HSB_DBG") ? (u32)atoi(getenv("HSB_DBG")) : 0;
     }
     if (cudaStreamSynchronize(s->stream) != cudaSuccess) { im->release(); delete im; return HS_UNKNOWN_ERROR; }
     s->dbs.push_back(im);

@@ -9,7 +9,7 @@
 //     (window & msk) == v exactly as confWithBit does; only then is the buffer looked up for the size check.
 #pragma once
 
-constexpr int TQ2CAP = 96;   // tier-2 survivors awaiting the slot-table confirm (drained 32 at a time)
+constexpr int TQ2CAP = 64;   // tier-2 survivors awaiting the slot-table confirm (drained 32 at a time)
 constexpr int TSTAGE = 32;   // staged match records per warp (general mode)
 constexpr int TCHUNK = 16;                 // bytes per lane per row (one LDS.128)
 constexpr int TROW_BYTES = 32 * TCHUNK;    // 512
@@ -25,7 +25,7 @@ template <bool ORDERED>
 struct TurboWarpShared {
     __align__(16) u8 text[TNBUF][TBUF_BYTES];  // [THALO bytes before the step][the step], filled by cp.async.bulk
     unsigned long long mbar[TNBUF];            // one mbarrier per buffer (transaction-count completion)
-    u32 q2[TQ2CAP];
+    uint2 q2[TQ2CAP];                          // {span-relative position, K-byte tail}
     Rec stage[ORDERED ? 1 : TSTAGE];
     u32 stage_n;
     u32 pad[3];
@@ -73,22 +73,28 @@ __device__ __forceinline__ void turbo_hit(const Ctx &c, const uint4 &b, u64 g) {
     }
 }
 
-__device__ __forceinline__ void turbo_confirm(const Ctx &c, u64 g, u32 &n_probe) {
-    const u64 w = load_tail8(c.cp.text, g);
-    const u32 key = (u32)(w >> (64 - 8 * c.db.tK));
+// One tier-2 survivor: global end position g, key = its K-byte tail (so the slot probe does not wait for the
+// window).  Slots h and h + 1 are fetched together: with the table a quarter full most chains end there.
+__device__ __forceinline__ void turbo_confirm(const Ctx &c, u64 g, u32 key, u32 &n_probe) {
     const u32 mask = (1u << c.db.tH2) - 1;
     u32 h = turbo::slot_home(key, c.db.tH2);
     const uint4 *slots = reinterpret_cast<const uint4 *>(c.db.slots);
+    uint4 a0 = __ldg(slots + 2 * (size_t)h), b0 = __ldg(slots + 2 * (size_t)h + 1);
+    uint4 a1 = __ldg(slots + 2 * (size_t)((h + 1) & mask)), b1 = __ldg(slots + 2 * (size_t)((h + 1) & mask) + 1);
+    const u64 w = load_tail8(c.cp.text, g);
     for (;;) {
-        // both halves of the slot in one round trip (v, msk | key, target, lit_off, meta)
-        const uint4 a = __ldg(slots + 2 * (size_t)h), b = __ldg(slots + 2 * (size_t)h + 1);
-        if (!((b.w >> 8) & 0xf)) break;
+        // slot = (v, msk | key, target, lit_off, meta)
+        if (!((b0.w >> 8) & 0xf)) break;
         n_probe++;
-        if (b.x == key) {
-            const u64 v = ((u64)a.y << 32) | a.x, m = ((u64)a.w << 32) | a.z;
-            if ((w & m) == v) turbo_hit(c, b, g);
+        if (b0.x == key) {
+            const u64 v = ((u64)a0.y << 32) | a0.x, m = ((u64)a0.w << 32) | a0.z;
+            if ((w & m) == v) turbo_hit(c, b0, g);
         }
         h = (h + 1) & mask;
+        a0 = a1; b0 = b1;
+        if (!((b0.w >> 8) & 0xf)) break;
+        a1 = __ldg(slots + 2 * (size_t)((h + 1) & mask));
+        b1 = __ldg(slots + 2 * (size_t)((h + 1) & mask) + 1);
     }
 }
 
@@ -108,13 +114,13 @@ __device__ __forceinline__ bool turbo_tail_hit(const u32 *tail_tab, u32 word_shi
 // ORDERED: every lane collects its candidate's records, a warp prefix sum keeps them in position order and
 // they are appended to the warp's own arena segment (no staging, no atomics).
 template <bool ORDERED>
-__device__ void turbo_drain(const Ctx &c, const u32 *q2, u64 span_base, u32 count, u32 &n_probe, Rec *seg, u32 &cursor) {
+__device__ void turbo_drain(const Ctx &c, const uint2 *q2, u64 span_base, u32 count, u32 &n_probe, Rec *seg, u32 &cursor) {
     const u32 idx = lane_id();
     if (ORDERED) {
         Collector col;
         col.n = 0;
         const Ctx cc{c.db, c.cp, c.ar, c.q, c.stage, c.stage_n, c.stage_cap, c.conf, &col};
-        if (idx < count) turbo_confirm(cc, span_base + q2[idx], n_probe);
+        if (idx < count) { const uint2 e = q2[idx]; turbo_confirm(cc, span_base + e.x, e.y, n_probe); }
         const u32 n = col.n < 4 ? col.n : 4;
         if (__any_sync(0xffffffffu, n != 0)) {
             u32 incl = n;
@@ -129,7 +135,7 @@ __device__ void turbo_drain(const Ctx &c, const u32 *q2, u64 span_base, u32 coun
             cursor += __shfl_sync(0xffffffffu, incl, 31);
         }
     } else {
-        if (idx < count) turbo_confirm(c, span_base + q2[idx], n_probe);
+        if (idx < count) { const uint2 e = q2[idx]; turbo_confirm(c, span_base + e.x, e.y, n_probe); }
         __syncwarp();
         if (*(volatile u32 *)c.stage_n >= c.stage_cap / 2) flush_stage(c);
     }
@@ -178,9 +184,9 @@ __device__ __forceinline__ u32 turbo_tier2(const u32 *tail_tab, const DevDb &db,
 
 // Warp-synchronous: append the step's tier-2 survivors (mask layout as above) to q2 in position order -- row 0
 // lane-major, then row 1 -- as span-relative positions; q2 is confirmed whenever it holds 32.
-template <bool ORDERED>
-__device__ __forceinline__ void turbo_push(const Ctx &c, u32 m, u32 *q2, u32 &q2n, u64 span_base, u32 step_pos, u32 &n_probe,
-                                           Rec *seg, u32 &cursor) {
+template <int K, bool ORDERED>
+__device__ __forceinline__ void turbo_push(const Ctx &c, u32 m, const u8 *wtext, uint2 *q2, u32 &q2n, u64 span_base, u32 step_pos,
+                                           u32 &n_probe, Rec *seg, u32 &cursor) {
     const u32 ln = lane_id(), lt = (1u << ln) - 1;
     const u32 n0 = __popc(m >> 16), n1 = __popc(m & 0xffffu);
     u32 slot0, slot1, total;
@@ -204,7 +210,7 @@ __device__ __forceinline__ void turbo_push(const Ctx &c, u32 m, u32 *q2, u32 &q2
         slot1 = (tot & 0xffffu) + (incl >> 16) - n1;
         total = (tot & 0xffffu) + (tot >> 16);
     }
-    // q2 holds fewer than 32 entries on entry; a step adds at most TQ2CAP - 32 per pass
+    // q2 holds fewer than 32 entries on entry; a pass adds at most what fits below TQ2CAP
     u32 done = 0;  // survivors of this step already moved to q2 (warp-uniform)
     while (done < total) {
         const u32 room = TQ2CAP - q2n, lim = done + room;  // this pass takes ranks [done, lim)
@@ -214,8 +220,13 @@ __device__ __forceinline__ void turbo_push(const Ctx &c, u32 m, u32 *q2, u32 &q2
             mm &= ~(0x80000000u >> lz);
             const bool second = lz >= 16;
             const u32 rank = second ? s1++ : s0++;
-            if (rank >= done && rank < lim)
-                q2[q2n + rank - done] = step_pos + ln * TCHUNK + (lz & 15) + (second ? TROW_BYTES : 0);
+            if (rank >= done && rank < lim) {
+                const u32 pos = ln * TCHUNK + (lz & 15) + (second ? TROW_BYTES : 0);
+                const u32 first = THALO + pos - 3;  // the four bytes ending at the position, K-tail on top
+                const u32 *wp = reinterpret_cast<const u32 *>(wtext + (first & ~3u));
+                const u32 w4 = __funnelshift_r(wp[0], wp[1], first << 3);
+                q2[q2n + rank - done] = make_uint2(step_pos + pos, w4 >> (8 * (4 - K)));
+            }
         }
         const u32 took = total - done < room ? total - done : room;
         q2n += took;
@@ -224,11 +235,10 @@ __device__ __forceinline__ void turbo_push(const Ctx &c, u32 m, u32 *q2, u32 &q2
         while (q2n >= 32) {
             turbo_drain<ORDERED>(c, q2, span_base, 32, n_probe, seg, cursor);
             const u32 rem = q2n - 32;
-            // slide the remainder (< TQ2CAP - 32 = 64 entries) down
-            const u32 k0 = ln < rem ? q2[32 + ln] : 0, k1 = 32 + ln < rem ? q2[64 + ln] : 0;
+            // slide the remainder (at most TQ2CAP - 32 = 32 entries) down
+            const uint2 k0 = ln < rem ? q2[32 + ln] : make_uint2(0, 0);
             __syncwarp();
             if (ln < rem) q2[ln] = k0;
-            if (32 + ln < rem) q2[32 + ln] = k1;
             __syncwarp();
             q2n = rem;
         }
@@ -343,30 +353,46 @@ __global__ void __launch_bounds__(turbo_warps<ORDERED>() * 32, 1) k_turbo(const 
     }
     __syncthreads();
 
-    const Ctx c{db, cp, ar, ws.q2, ws.stage, &ws.stage_n, ORDERED ? 0u : (u32)TSTAGE, nullptr, nullptr};
-    u32 *q2 = ws.q2;
+    const Ctx c{db, cp, ar, nullptr, ws.stage, &ws.stage_n, ORDERED ? 0u : (u32)TSTAGE, nullptr, nullptr};
+    uint2 *q2 = ws.q2;
     const u32 H1shift = 32 - db.tH1;
     u32 n_cand = 0, n_probe = 0;
     Rec *seg = ORDERED ? ar.recs + (size_t)w * ar.seg_cap : nullptr;
     u32 cursor = 0, q2n = 0;
+    // lane chunk of row r: buffer bytes [THALO + r * 512 + ln * 16, +16); the 8 bytes before it come from the
+    // neighbouring chunk (or the halo) in the same buffer.  The registers of step s + 1 are loaded while step s
+    // is still in its second tier, so the next first tier starts without a shared-memory round trip.
+    uint4 cur0 = make_uint4(0, 0, 0, 0), cur1 = cur0;
+    uint2 prev0 = make_uint2(0, 0), prev1 = prev0;
+    if (nsteps) {
+        mbar_wait(&ws.mbar[0], 0);
+        const u8 *cb = ws.text[0] + THALO + ln * TCHUNK;
+        cur0 = *reinterpret_cast<const uint4 *>(cb);
+        prev0 = *reinterpret_cast<const uint2 *>(cb - 8);
+        cur1 = *reinterpret_cast<const uint4 *>(cb + TROW_BYTES);
+        prev1 = *reinterpret_cast<const uint2 *>(cb + TROW_BYTES - 8);
+    }
 #pragma unroll 1
     for (u32 step = 0; step < nsteps; step++) {
         const u32 b = step % TNBUF;
-        mbar_wait(&ws.mbar[b], (step / TNBUF) & 1);
         const u8 *buf = ws.text[b];
-        // lane chunk of row r: buffer bytes [THALO + r * 512 + ln * 16, +16); the 8 bytes before it come from
-        // the neighbouring chunk (or the halo) in the same buffer
-        u32 m = 0;
-#pragma unroll
-        for (int r = 0; r < 2; r++) {
-            const u8 *cb = buf + THALO + r * TROW_BYTES + ln * TCHUNK;
-            const uint4 cur = *reinterpret_cast<const uint4 *>(cb);
-            const uint2 prev = *reinterpret_cast<const uint2 *>(cb - 8);
-            const u32 E[TEW] = {prev.x, prev.y, cur.x, cur.y, cur.z, cur.w};
-            m = (m << 16) | turbo_chunk<K>(tab, H1shift, E);
+        u32 m;
+        {
+            const u32 E0[TEW] = {prev0.x, prev0.y, cur0.x, cur0.y, cur0.z, cur0.w};
+            m = turbo_chunk<K>(tab, H1shift, E0);
+            const u32 E1[TEW] = {prev1.x, prev1.y, cur1.x, cur1.y, cur1.z, cur1.w};
+            m = (m << 16) | turbo_chunk<K>(tab, H1shift, E1);
+        }
+        if (step + 1 < nsteps) {
+            const u32 nb = (step + 1) % TNBUF;
+            mbar_wait(&ws.mbar[nb], ((step + 1) / TNBUF) & 1);
+            const u8 *cb = ws.text[nb] + THALO + ln * TCHUNK;
+            cur0 = *reinterpret_cast<const uint4 *>(cb);
+            prev0 = *reinterpret_cast<const uint2 *>(cb - 8);
+            cur1 = *reinterpret_cast<const uint4 *>(cb + TROW_BYTES);
+            prev1 = *reinterpret_cast<const uint2 *>(cb + TROW_BYTES - 8);
         }
         // m: bit 31 - j = position j of the lane's row-0 chunk, bit 15 - j = position j of its row-1 chunk
-        if (db.dbg & 1) { if (m == 0x12345678u) n_probe++; m = 0; }
         const u32 step_pos = step * TSTEP_BYTES;
         {
             const u64 g0 = span_base + step_pos + ln * TCHUNK;  // first byte of the row-0 chunk
@@ -379,8 +405,7 @@ __global__ void __launch_bounds__(turbo_warps<ORDERED>() * 32, 1) k_turbo(const 
         }
         n_cand += __popc(m);
         m = turbo_tier2<K>(bloom, db, buf, m);
-        if (db.dbg & 2) { if (m == 0x12345678u) n_probe++; m = 0; }
-        if (__any_sync(0xffffffffu, m != 0)) turbo_push<ORDERED>(c, m, q2, q2n, span_base, step_pos, n_probe, seg, cursor);
+        if (__any_sync(0xffffffffu, m != 0)) turbo_push<K, ORDERED>(c, m, buf, q2, q2n, span_base, step_pos, n_probe, seg, cursor);
         __syncwarp();
         // the buffer is free: fetch the step TNBUF ahead into it
         if (ln == 0 && step + TNBUF < nsteps)
