@@ -12,7 +12,7 @@ in rotation so no step finds its input in L2.
                device work (front end + confirm + Rose programs + arena + sort/dedupe), inputs resident in HBM
   e2e          the same metric through the reference-facing call hs_gpu_scan_vector_ex() with HOST buffers
                (pinned), wall clock around the call: H2D of the batch, scan, D2H of the sorted matches
-  roofline     dominant kernel k_scan: algorithmic bytes per launch / its CUDA-event time, vs MEASURED_PEAKS hbm
+  roofline     dominant kernel k_turbo: algorithmic bytes per launch / its CUDA-event time, vs MEASURED_PEAKS hbm
   cpu_baseline the unmodified reference runtime (oracle/_ref) on host cores, bounded sample
   --impl reference   the same workload on the reference's CPU hs_scan with all host threads
 """
@@ -42,6 +42,19 @@ def peaks():
             return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     except Exception:
         return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic(config, nbytes, frontend):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch, from the committed ncu
+    --set full capture of this very workload (profiles/ncu_traffic.json); None when no capture matches."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            for e in json.load(f):
+                if e["config"] == config and e["bytes"] == nbytes and e["frontend"] == frontend:
+                    return e["dram_bytes_per_launch"]
+    except Exception:
+        pass
+    return None
 
 
 def make_workload(config, rank, nbytes):
@@ -260,10 +273,16 @@ def main():
     e2e_steps = max(3, min(args.steps, 20))
     t0 = time.perf_counter()
     e2e_matches = 0
+    brk = {"h2d_ms": 0.0, "scan_ms": 0.0, "sort_ms": 0.0, "d2h_ms": 0.0}
     for _ in range(e2e_steps):
         e2e_matches += e2e_once()
+        st = sc.stats()
+        for k in brk:
+            brk[k] += st[k]
     barrier()
     e2e_s = time.perf_counter() - t0
+    brk = {k: round(v / e2e_steps, 4) for k, v in brk.items()}
+    brk["wall_ms"] = round(1e3 * e2e_s / e2e_steps, 4)
     e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
@@ -289,10 +308,11 @@ def main():
             "clocks": clocks,
             "e2e": {"value": round(e2e_value, 3), "unit": "GB/s", "h2d_bytes_per_step": int(flat0.nbytes + off0.nbytes),
                     "d2h_bytes_per_step": d2h_per_step, "steps": e2e_steps,
-                    "call": "hs_gpu_scan_vector_ex(host pinned buffers)"},
+                    "call": "hs_gpu_scan_vector_ex(host pinned buffers)", "per_step_ms": brk},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "k_scan", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
-                         "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+            "roofline": {"bound": "hbm", "kernel": "k_scan" if args.frontend == 1 else "k_turbo", "achieved": round(achieved, 2),
+                         "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
+                         "traffic": ncu_traffic(args.config, nbytes, args.frontend), "peak_source": peak_src,
                          "alg_bytes_per_launch": int(alg_bytes), "kernel_ms": round(kern_ms / n_launch, 4)},
         }
         if not args.no_cpu_baseline:

@@ -804,6 +804,28 @@ struct DevBuf {  // grow-only device allocation
     size_t bytes() const { return cap * sizeof(T); }
 };
 
+template <class T>
+struct PinnedBuf {  // grow-only page-locked host array (so cudaMemcpyAsync from it really is asynchronous)
+    T *p = nullptr;
+    size_t cap = 0, n = 0;
+    bool resize(size_t want) {
+        if (want > cap) {
+            if (p) cudaFreeHost(p);
+            p = nullptr;
+            cap = 0;
+            const size_t c = want + want / 4 + 64;
+            if (cudaHostAlloc((void **)&p, c * sizeof(T), cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); n = 0; return false; }
+            cap = c;
+        }
+        n = want;
+        return true;
+    }
+    T *data() { return p; }
+    size_t size() const { return n; }
+    T &operator[](size_t i) { return p[i]; }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = n = 0; }
+};
+
 struct DbImage {  // one uploaded database
     const void *host_db = nullptr;
     u32 crc = 0, bc_len = 0;
@@ -855,8 +877,8 @@ struct hs_gpu_scratch {
     hs_gpu_corpus staging;       // device staging for host-buffer scans
     u8 *h_stage = nullptr;       // pinned host staging
     size_t h_stage_cap = 0;
-    std::vector<u64> h_off;
-    std::vector<u32> h_cell_first;
+    PinnedBuf<u64> h_off;
+    PinnedBuf<u32> h_cell_first;
     DevBuf<Rec> recs, recs2;
     DevBuf<hs_gpu_match_t> d_matches;
     DevBuf<u8> cub_tmp, keep;
@@ -982,17 +1004,22 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
     return HS_SUCCESS;
 }
 
+inline bool resize_ok(std::vector<u32> &v, size_t n) { v.resize(n); return true; }
+inline bool resize_ok(PinnedBuf<u32> &v, size_t n) { return v.resize(n); }
+
 // out[c] = buffer holding the first byte of cell c (CELL_BYTES each), out[ncells] = buffer of the last byte
-void build_cell_first(const u64 *off, u32 count, u64 total, std::vector<u32> &out, u32 &nstrips) {
+template <class Vec>
+bool build_cell_first(const u64 *off, u32 count, u64 total, Vec &out, u32 &nstrips) {
     nstrips = (u32)((total + STRIP_BYTES - 1) / STRIP_BYTES);
     const u32 ncells = (u32)((total + CELL_BYTES - 1) / CELL_BYTES);
-    out.resize((size_t)ncells + 1);
+    if (!resize_ok(out, (size_t)ncells + 1)) return false;
     u32 b = 0;
     for (u32 s = 0; s <= ncells; s++) {
         u64 pos = std::min<u64>((u64)s * CELL_BYTES, total ? total - 1 : 0);
         while (b + 1 < count && off[b + 1] <= pos) b++;
         out[s] = b;
     }
+    return true;
 }
 
 u32 turbo_grid(const hs_gpu_scratch *s, const DevCorpus &cp, u32 warps_per_cta) {
@@ -1256,7 +1283,7 @@ struct InUseGuard {
 
 hs_error_t stage_host_buffers(hs_gpu_scratch *s, const char *const *data, const unsigned int *length, unsigned count) {
     hs_gpu_corpus &cp = s->staging;
-    s->h_off.resize((size_t)count + 1);
+    if (!s->h_off.resize((size_t)count + 1)) return HS_NOMEM;
     u64 total = 0;
     bool contiguous = true;
     for (unsigned i = 0; i < count; i++) {
@@ -1268,10 +1295,8 @@ hs_error_t stage_host_buffers(hs_gpu_scratch *s, const char *const *data, const 
     s->h_off[count] = total;
     cp.total = total;
     cp.count = count;
-    build_cell_first(s->h_off.data(), count, total, s->h_cell_first, cp.nstrips);
     CU_OK(cp.text.reserve(FRONT_PAD + total + BACK_PAD));
     CU_OK(cp.off.reserve((size_t)count + 1));
-    CU_OK(cp.cell_first.reserve(s->h_cell_first.size()));
     const u8 *src = nullptr;
     if (contiguous && count && total) {
         // zero-copy source when the caller's buffers are one pinned region (hs_gpu_host_alloc)
@@ -1302,6 +1327,9 @@ hs_error_t stage_host_buffers(hs_gpu_scratch *s, const char *const *data, const 
     CU_OK(cudaMemsetAsync(cp.text.p + FRONT_PAD + total, 0, BACK_PAD, s->stream));
     if (total) CU_OK(cudaMemcpyAsync(cp.text.p + FRONT_PAD, src, total, cudaMemcpyHostToDevice, s->stream));
     CU_OK(cudaMemcpyAsync(cp.off.p, s->h_off.data(), ((size_t)count + 1) * 8, cudaMemcpyHostToDevice, s->stream));
+    // the position -> buffer index is built while the text is on its way
+    if (!build_cell_first(s->h_off.data(), count, total, s->h_cell_first, cp.nstrips)) return HS_NOMEM;
+    CU_OK(cp.cell_first.reserve(s->h_cell_first.size()));
     CU_OK(cudaMemcpyAsync(cp.cell_first.p, s->h_cell_first.data(), s->h_cell_first.size() * 4,
                           cudaMemcpyHostToDevice, s->stream));
     return HS_SUCCESS;
@@ -1442,6 +1470,8 @@ hs_error_t hs_gpu_free_scratch(hs_gpu_scratch_t *s) {
     s->cub_tmp.release();
     s->keep.release();
     s->seg_count.release();
+    s->h_off.release();
+    s->h_cell_first.release();
     if (s->h_stage) cudaFreeHost(s->h_stage);
     if (s->h_matches) cudaFreeHost(s->h_matches);
     if (s->h_ctl) cudaFreeHost(s->h_ctl);
