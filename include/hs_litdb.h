@@ -24,6 +24,7 @@ typedef struct hs_database hs_database_t; /* same opaque type as src/hs_common.h
 
 /* per-literal flags: same values as HS_FLAG_CASELESS / HS_FLAG_SINGLEMATCH (src/hs_compile.h:869,911) */
 #define HSB_FLAG_CASELESS 1u
+#define HSB_FLAG_DOTALL 2u /* HS_FLAG_DOTALL, src/hs_compile.h:877 (regex writer only) */
 #define HSB_FLAG_SINGLEMATCH 8u
 
 #define HSB_MODE_BLOCK 1u /* HS_MODE_BLOCK, src/hs_compile.h:1156 */
@@ -51,6 +52,14 @@ typedef struct hsb_lit_options {
 int hsb_compile_lit_multi(const char *const *expressions, const unsigned *flags, const unsigned *ids,
                           const size_t *lens, unsigned elements, unsigned mode,
                           const hsb_lit_options *options, hs_database_t **db, char **error);
+/* Stand-in for hs_compile_multi() (/root/reference/src/hs_compile.h:450-456) for SMALL pattern sets in a
+ * restricted dialect (vectorscan_b200/csrc/nfadb_writer.cpp): the whole set becomes ONE LimEx NFA inside a
+ * single-outfix block-mode database -- the shape the reference compiler gives a pattern set that has no
+ * useful literals -- which the unmodified reference runtime scans with hs_scan.  Flags: HSB_FLAG_CASELESS,
+ * HSB_FLAG_DOTALL.  Fails (HSB_LIT_COMPILER_ERROR + message) on unsupported syntax, on patterns that match
+ * the empty string and when the set needs more than 512 NFA states. */
+int hsb_compile_regex_multi(const char *const *expressions, const unsigned *flags, const unsigned *ids,
+                            unsigned elements, unsigned mode, hs_database_t **db, char **error);
 void hsb_free_database(hs_database_t *db);
 void hsb_free_error(char *error);
 

@@ -24,6 +24,19 @@
 #define SZ(t) printf("sizeof." #t " %zu\n", sizeof(t))
 #define OF(t, f) printf(#t "." #f " %zu\n", offsetof(t, f))
 #define VAL(v) printf(#v " %lld\n", (long long)(v))
+#define LIMEX(n) \
+ SZ(struct LimExNFA##n); OF(struct LimExNFA##n, reachMap); OF(struct LimExNFA##n, reachSize); OF(struct LimExNFA##n, accelCount); \
+ OF(struct LimExNFA##n, accelTableOffset); OF(struct LimExNFA##n, accelAuxCount); OF(struct LimExNFA##n, accelAuxOffset); \
+ OF(struct LimExNFA##n, acceptCount); OF(struct LimExNFA##n, acceptOffset); OF(struct LimExNFA##n, acceptEodCount); OF(struct LimExNFA##n, acceptEodOffset); \
+ OF(struct LimExNFA##n, exceptionCount); OF(struct LimExNFA##n, exceptionOffset); OF(struct LimExNFA##n, repeatCount); OF(struct LimExNFA##n, repeatOffset); \
+ OF(struct LimExNFA##n, squashOffset); OF(struct LimExNFA##n, squashCount); OF(struct LimExNFA##n, topCount); OF(struct LimExNFA##n, topOffset); \
+ OF(struct LimExNFA##n, stateSize); OF(struct LimExNFA##n, flags); OF(struct LimExNFA##n, init); OF(struct LimExNFA##n, initDS); OF(struct LimExNFA##n, accept); \
+ OF(struct LimExNFA##n, acceptAtEOD); OF(struct LimExNFA##n, accel); OF(struct LimExNFA##n, accelPermute); OF(struct LimExNFA##n, accelCompare); \
+ OF(struct LimExNFA##n, accel_and_friends); OF(struct LimExNFA##n, compressMask); OF(struct LimExNFA##n, exceptionMask); OF(struct LimExNFA##n, repeatCyclicMask); \
+ OF(struct LimExNFA##n, zombieMask); OF(struct LimExNFA##n, shift); OF(struct LimExNFA##n, shiftCount); OF(struct LimExNFA##n, shiftAmount); \
+ OF(struct LimExNFA##n, exceptionShufMask); OF(struct LimExNFA##n, exceptionBitMask); OF(struct LimExNFA##n, exceptionAndMask); \
+ SZ(struct NFAException##n); OF(struct NFAException##n, squash); OF(struct NFAException##n, successors); OF(struct NFAException##n, reports); \
+ OF(struct NFAException##n, repeatOffset); OF(struct NFAException##n, hasSquash); OF(struct NFAException##n, trigger);
 
 int main(void) {
     SZ(struct hs_database);
@@ -206,5 +219,18 @@ int main(void) {
     OF(struct hs_database, reserved0); OF(struct hs_database, reserved1); OF(struct hs_database, padding);
     VAL(HS_MODE_BLOCK); VAL(HS_MODE_STREAM); VAL(HS_MODE_VECTORED);
     VAL(FDR_FLOOD_MAX_IDS); VAL(FDR_LIT_FLAG_NOREPEAT);
+    /* NFA engines */
+
+ SZ(struct NFA); OF(struct NFA, flags); OF(struct NFA, length); OF(struct NFA, type); OF(struct NFA, rAccelType); OF(struct NFA, rAccelOffset);
+ OF(struct NFA, maxBiAnchoredWidth); OF(struct NFA, rAccelData); OF(struct NFA, queueIndex); OF(struct NFA, nPositions); OF(struct NFA, scratchStateSize);
+ OF(struct NFA, streamStateSize); OF(struct NFA, maxWidth); OF(struct NFA, minWidth); OF(struct NFA, maxOffset);
+ VAL(LIMEX_NFA_32); VAL(LIMEX_NFA_64); VAL(LIMEX_NFA_128); VAL(LIMEX_NFA_256); VAL(LIMEX_NFA_384); VAL(LIMEX_NFA_512);
+ VAL(NFA_ACCEPTS_EOD); VAL(NFA_ZOMBIE); VAL(MO_INVALID_IDX);
+ LIMEX(32) LIMEX(64) LIMEX(128) LIMEX(256) LIMEX(384) LIMEX(512)
+ SZ(struct NFAAccept); OF(struct NFAAccept, single_report); OF(struct NFAAccept, reports); OF(struct NFAAccept, squash);
+ SZ(struct NfaInfo); OF(struct NfaInfo, nfaOffset); OF(struct NfaInfo, stateOffset); OF(struct NfaInfo, fullStateOffset); 
+ OF(struct NfaInfo, no_retrigger); OF(struct NfaInfo, in_sbmatcher); OF(struct NfaInfo, eod);
+
+
     return 0;
 }

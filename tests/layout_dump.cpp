@@ -115,5 +115,45 @@ int main() {
     P("ROSE_INSTR_INCLUDED_JUMP", op::INCLUDED_JUMP); P("ROSE_INSTR_SET_EXHAUST", op::SET_EXHAUST);
     P("ROSE_INSTR_CHECK_SHUFTI_64x8", op::CHECK_SHUFTI_64x8); P("ROSE_INSTR_CHECK_MASK_64", op::CHECK_MASK_64);
     P("LAST_ROSE_INSTRUCTION", op::LAST);
+    // NFA engines
+    P("sizeof.struct NFA", nfa::SIZE); P("struct NFA.flags", nfa::flags); P("struct NFA.length", nfa::length);
+    P("struct NFA.type", nfa::type); P("struct NFA.rAccelType", nfa::rAccelType); P("struct NFA.rAccelOffset", nfa::rAccelOffset);
+    P("struct NFA.maxBiAnchoredWidth", nfa::maxBiAnchoredWidth); P("struct NFA.rAccelData", nfa::rAccelData);
+    P("struct NFA.queueIndex", nfa::queueIndex); P("struct NFA.nPositions", nfa::nPositions);
+    P("struct NFA.scratchStateSize", nfa::scratchStateSize); P("struct NFA.streamStateSize", nfa::streamStateSize);
+    P("struct NFA.maxWidth", nfa::maxWidth); P("struct NFA.minWidth", nfa::minWidth); P("struct NFA.maxOffset", nfa::maxOffset);
+    P("LIMEX_NFA_32", nfa::LIMEX_32); P("LIMEX_NFA_64", nfa::LIMEX_64); P("LIMEX_NFA_128", nfa::LIMEX_128);
+    P("LIMEX_NFA_256", nfa::LIMEX_256); P("LIMEX_NFA_384", nfa::LIMEX_384); P("LIMEX_NFA_512", nfa::LIMEX_512);
+    P("NFA_ACCEPTS_EOD", nfa::ACCEPTS_EOD); P("NFA_ZOMBIE", nfa::ZOMBIE); P("MO_INVALID_IDX", INVALID_DKEY);
+    for (u32 t = 0; t < 6; t++) {
+        const limex::Layout l = limex::layout(t);
+        char k[96];
+#define LK(f, v) std::snprintf(k, sizeof k, "struct LimExNFA%u." #f, l.bits); P(k, v)
+#define EK(f, v) std::snprintf(k, sizeof k, "struct NFAException%u." #f, l.bits); P(k, v)
+        std::snprintf(k, sizeof k, "sizeof.struct LimExNFA%u", l.bits); P(k, l.SIZE);
+        LK(reachMap, limex::reachMap); LK(reachSize, limex::reachSize); LK(accelCount, limex::accelCount);
+        LK(accelTableOffset, limex::accelTableOffset); LK(accelAuxCount, limex::accelAuxCount);
+        LK(accelAuxOffset, limex::accelAuxOffset); LK(acceptCount, limex::acceptCount); LK(acceptOffset, limex::acceptOffset);
+        LK(acceptEodCount, limex::acceptEodCount); LK(acceptEodOffset, limex::acceptEodOffset);
+        LK(exceptionCount, limex::exceptionCount); LK(exceptionOffset, limex::exceptionOffset);
+        LK(repeatCount, limex::repeatCount); LK(repeatOffset, limex::repeatOffset); LK(squashOffset, limex::squashOffset);
+        LK(squashCount, limex::squashCount); LK(topCount, limex::topCount); LK(topOffset, limex::topOffset);
+        LK(stateSize, limex::stateSize); LK(flags, limex::flags);
+        LK(init, l.init); LK(initDS, l.initDS); LK(accept, l.accept); LK(acceptAtEOD, l.acceptAtEOD); LK(accel, l.accel);
+        LK(accelPermute, l.accelPermute); LK(accelCompare, l.accelCompare); LK(accel_and_friends, l.accel_and_friends);
+        LK(compressMask, l.compressMask); LK(exceptionMask, l.exceptionMask); LK(repeatCyclicMask, l.repeatCyclicMask);
+        LK(zombieMask, l.zombieMask); LK(shift, l.shift); LK(shiftCount, l.shiftCount); LK(shiftAmount, l.shiftAmount);
+        LK(exceptionShufMask, l.exceptionShufMask); LK(exceptionBitMask, l.exceptionBitMask);
+        LK(exceptionAndMask, l.exceptionAndMask);
+        std::snprintf(k, sizeof k, "sizeof.struct NFAException%u", l.bits); P(k, l.E_SIZE);
+        EK(squash, l.e_squash); EK(successors, l.e_successors); EK(reports, l.e_reports); EK(repeatOffset, l.e_repeatOffset);
+        EK(hasSquash, l.e_hasSquash); EK(trigger, l.e_trigger);
+    }
+    P("sizeof.struct NFAAccept", nfaaccept::SIZE); P("struct NFAAccept.single_report", nfaaccept::single_report);
+    P("struct NFAAccept.reports", nfaaccept::reports); P("struct NFAAccept.squash", nfaaccept::squash);
+    P("sizeof.struct NfaInfo", nfainfo::SIZE); P("struct NfaInfo.nfaOffset", nfainfo::nfaOffset);
+    P("struct NfaInfo.stateOffset", nfainfo::stateOffset); P("struct NfaInfo.fullStateOffset", nfainfo::fullStateOffset);
+    P("struct NfaInfo.no_retrigger", nfainfo::no_retrigger); P("struct NfaInfo.in_sbmatcher", nfainfo::in_sbmatcher);
+    P("struct NfaInfo.eod", nfainfo::eod);
     return 0;
 }

@@ -14,6 +14,8 @@
 //   FDRFlood                  /root/reference/src/fdr/fdr_internal.h:50-62
 //   noodTable                 /root/reference/src/hwlm/noodle_internal.h:38-49
 //   Rose program opcodes      /root/reference/src/rose/rose_program.h:44-724
+//   NFA header / NfaInfo      /root/reference/src/nfa/nfa_internal.h:89-128, src/rose/rose_internal.h:153-164
+//   LimExNFA{32..512}         /root/reference/src/nfa/limex_internal.h:114-201
 #pragma once
 #include <cstddef>
 #include <cstdint>
@@ -216,6 +218,66 @@ namespace included_jump { constexpr size_t squash = 1, child_offset = 4, SIZE = 
 namespace set_exhaust { constexpr size_t ekey = 4, SIZE = 8; }
 constexpr size_t SIZE_1 = 8;  // END, CATCH_UP, CLEAR_WORK_DONE, ... (code byte only)
 }  // namespace op
+
+// ---- NFA engines --------------------------------------------------------------------------------
+namespace nfa {  // struct NFA (64 bytes, cache-line aligned); the implementation struct follows it
+constexpr size_t flags = 0, length = 4, type = 8, rAccelType = 9, rAccelOffset = 10, maxBiAnchoredWidth = 11,
+                 rAccelData = 12, queueIndex = 16, nPositions = 20, scratchStateSize = 24, streamStateSize = 28,
+                 maxWidth = 32, minWidth = 36, maxOffset = 40, SIZE = 64;
+constexpr u8 LIMEX_32 = 0, LIMEX_64 = 1, LIMEX_128 = 2, LIMEX_256 = 3, LIMEX_384 = 4, LIMEX_512 = 5;
+constexpr u32 ACCEPTS_EOD = 1, ZOMBIE = 2;
+}
+namespace nfainfo {  // struct NfaInfo
+constexpr size_t nfaOffset = 0, stateOffset = 4, fullStateOffset = 8, ekeyListOffset = 12, no_retrigger = 16,
+                 in_sbmatcher = 17, eod = 18, SIZE = 20;
+}
+namespace nfaaccept {  // struct NFAAccept
+constexpr size_t single_report = 0, reports = 4, squash = 8, SIZE = 12;
+}
+// LimExNFA<bits>: a fixed head, then twelve state-sized masks, shift[8], the shift bookkeeping and three m512
+// exception-extraction masks.  State masks are stored as `bytes`-byte little-endian bit vectors aligned to
+// `align` (u32, u64, m128, m256, m384 = 3 x m128, m512).
+namespace limex {
+constexpr size_t reachMap = 0, reachSize = 256, accelCount = 260, accelTableOffset = 264, accelAuxCount = 268,
+                 accelAuxOffset = 272, acceptCount = 276, acceptOffset = 280, acceptEodCount = 284,
+                 acceptEodOffset = 288, exceptionCount = 292, exceptionOffset = 296, repeatCount = 300,
+                 repeatOffset = 304, squashOffset = 308, squashCount = 312, topCount = 316, topOffset = 320,
+                 stateSize = 324, flags = 328, HEAD = 332;
+constexpr u32 FLAG_COMPRESS_STATE = 1, FLAG_COMPRESS_MASKED = 2, FLAG_CANNOT_DIE = 4, FLAG_EXTRACT_EXP = 8;
+constexpr u32 MAX_SHIFT_COUNT = 8, MAX_SHIFT_AMOUNT = 16;
+constexpr u8 SQUASH_NONE = 0, SQUASH_CYCLIC = 1, SQUASH_TUG = 2, SQUASH_REPORT = 3;
+struct Layout {
+    u32 bits, bytes, align;
+    size_t init, initDS, accept, acceptAtEOD, accel, accelPermute, accelCompare, accel_and_friends, compressMask,
+        exceptionMask, repeatCyclicMask, zombieMask, shift, shiftCount, shiftAmount, exceptionShufMask,
+        exceptionBitMask, exceptionAndMask, SIZE;
+    // struct NFAException<bits>
+    size_t e_squash, e_successors, e_reports, e_repeatOffset, e_hasSquash, e_trigger, E_SIZE;
+};
+HSB_HD Layout layout(u32 type) {
+    const u32 bits_of[6] = {32, 64, 128, 256, 384, 512}, align_of[6] = {4, 8, 16, 32, 16, 64};
+    Layout l{};
+    l.bits = bits_of[type];
+    l.bytes = l.bits / 8;
+    l.align = align_of[type];
+    const size_t S = l.bytes;
+    l.init = (HEAD + l.align - 1) / l.align * l.align;
+    l.initDS = l.init + S; l.accept = l.init + 2 * S; l.acceptAtEOD = l.init + 3 * S; l.accel = l.init + 4 * S;
+    l.accelPermute = l.init + 5 * S; l.accelCompare = l.init + 6 * S; l.accel_and_friends = l.init + 7 * S;
+    l.compressMask = l.init + 8 * S; l.exceptionMask = l.init + 9 * S; l.repeatCyclicMask = l.init + 10 * S;
+    l.zombieMask = l.init + 11 * S; l.shift = l.init + 12 * S;
+    l.shiftCount = l.shift + MAX_SHIFT_COUNT * S;
+    l.shiftAmount = l.shiftCount + 4;
+    l.exceptionShufMask = (l.shiftAmount + MAX_SHIFT_COUNT + 63) / 64 * 64;
+    l.exceptionBitMask = l.exceptionShufMask + 64;
+    l.exceptionAndMask = l.exceptionShufMask + 128;
+    l.SIZE = l.exceptionShufMask + 192;
+    l.e_squash = 0; l.e_successors = S; l.e_reports = 2 * S; l.e_repeatOffset = 2 * S + 4; l.e_hasSquash = 2 * S + 8;
+    l.e_trigger = 2 * S + 9;
+    l.E_SIZE = (2 * S + 10 + l.align - 1) / l.align * l.align;
+    return l;
+}
+}  // namespace limex
 
 constexpr u32 INVALID_EKEY = 0xffffffffu;
 constexpr u32 INVALID_DKEY = 0xffffffffu;  // MO_INVALID_IDX

@@ -1,0 +1,732 @@
+// nfadb_writer.cpp -- host-side writer of SINGLE-OUTFIX block-mode databases whose one engine is a LimEx NFA,
+// in the Vectorscan 5.4.11 bytecode format (part of libhs_litdb.so).
+//
+// Why this exists: the reference's pattern compiler (hs_compile_multi) cannot be built in this image
+// (SURVEY.md section 0.5), so there is no source of databases that contain an NFA.  This file compiles a small
+// regular-expression dialect into ONE Glushkov automaton and lays it out as the reference does for a pattern
+// set that becomes a single outfix: hs_database header, RoseEngine with runtimeImpl = SINGLE_OUTFIX
+// (src/runtime.c:246-279 runs it), one NfaInfo, one report program per pattern and a LimExNFA{32..512}
+// (src/nfa/limex_internal.h) behind a struct NFA header.  The unmodified reference runtime accepts the blob
+// and scans it with hs_scan; the GPU runtime steps the very same bytes.
+//
+// Dialect (bytes, no UTF-8): literals, escapes \n \r \t \f \v \a \e \0 \xHH \d \D \w \W \s \S and escaped
+// punctuation, '.', classes [a-z0-9_] [^...] (escapes allowed inside), groups ( ) and (?: ), alternation |,
+// quantifiers * + ? {m} {m,} {m,n} (greedy/lazy makes no difference to the set of end offsets), a leading ^.
+// Flags: HS_FLAG_CASELESS, HS_FLAG_DOTALL.  Semantics = Hyperscan's: every end offset of every non-empty match
+// is reported once per pattern.  Patterns that match the empty string are refused (they would need the
+// boundary programs), as is anything that does not fit 510 positions.
+//
+// Encoding choices (any LimEx that follows the format is valid input for the runtime): state 0 is the
+// unanchored start (self loop), the next state the anchored start, then the Glushkov positions of each pattern
+// in order; the <= 8 most frequent forward distances (0..16) between a state and its successors become the
+// shift masks, every other edge and every reporting state becomes an exception; no acceleration, no bounded
+// repeats, no squashing.
+//
+// Format sources followed (restated, nothing copied): src/nfa/limex_internal.h:33-201, nfa_internal.h:89-128,
+// src/nfa/limex_runtime_impl.h:209-367,620-730 (what the runtime reads), src/rose/rose_internal.h:153-164,330-483,
+// src/rose/rose_build_bytecode.cpp:3608-3890 (engine header of a single-outfix build).
+#include "hsb_layout.h"
+#include "hs_litdb.h"
+
+#include <algorithm>
+#include <bitset>
+#include <cstdlib>
+#include <map>
+#include <string>
+#include <vector>
+
+namespace {
+using namespace hsb;
+
+constexpr u32 MAX_STATES = 512;
+using StateSet = std::bitset<MAX_STATES>;
+
+struct CharSet {
+    u64 w[4] = {0, 0, 0, 0};
+    void set(u32 c) { w[c >> 6] |= 1ull << (c & 63); }
+    bool test(u32 c) const { return (w[c >> 6] >> (c & 63)) & 1; }
+    void set_range(u32 a, u32 b) { for (u32 c = a; c <= b; c++) set(c); }
+    void invert() { for (auto &x : w) x = ~x; }
+    void merge(const CharSet &o) { for (int i = 0; i < 4; i++) w[i] |= o.w[i]; }
+    bool empty() const { return !(w[0] | w[1] | w[2] | w[3]); }
+    void add_caseless() {
+        for (u32 c = 'a'; c <= 'z'; c++) {
+            if (test(c)) set(c - 32);
+            if (test(c - 32)) set(c);
+        }
+    }
+};
+
+struct Buf {
+    std::vector<u8> b;
+    size_t size() const { return b.size(); }
+    void align(size_t a) { b.resize(round_up(b.size(), a), 0); }
+    size_t grow(size_t n) { size_t o = b.size(); b.resize(o + n, 0); return o; }
+    u8 *at(size_t off) { return b.data() + off; }
+};
+
+// ---- regular expression -> syntax tree --------------------------------------------------------------------
+enum NodeType { N_EMPTY, N_CHAR, N_CAT, N_ALT, N_STAR, N_PLUS, N_OPT };
+struct Node {
+    NodeType type = N_EMPTY;
+    CharSet cs;
+    std::vector<int> kids;
+};
+
+struct Parser {
+    const std::string &src;
+    bool caseless, dotall;
+    size_t pos = 0;
+    std::vector<Node> nodes;
+    std::string err;
+    size_t n_char_nodes = 0;
+
+    Parser(const std::string &s, bool cl, bool da) : src(s), caseless(cl), dotall(da) {}
+    bool eof() const { return pos >= src.size(); }
+    u8 peek() const { return (u8)src[pos]; }
+    int add(NodeType t) { nodes.push_back(Node()); nodes.back().type = t; return (int)nodes.size() - 1; }
+    bool fail(const std::string &m) { if (err.empty()) err = m + " at offset " + std::to_string(pos); return false; }
+
+    int make_char(CharSet cs) {
+        if (caseless) cs.add_caseless();
+        int n = add(N_CHAR);
+        nodes[n].cs = cs;
+        n_char_nodes++;
+        return n;
+    }
+    int clone(int n) {
+        Node copy = nodes[n];
+        if (copy.type == N_CHAR) n_char_nodes++;
+        for (int &k : copy.kids) k = clone(k);
+        nodes.push_back(copy);
+        return (int)nodes.size() - 1;
+    }
+
+    static int hexval(u8 c) {
+        if (c >= '0' && c <= '9') return c - '0';
+        if (c >= 'a' && c <= 'f') return c - 'a' + 10;
+        if (c >= 'A' && c <= 'F') return c - 'A' + 10;
+        return -1;
+    }
+    // escape after the backslash; fills cs (single byte or a class)
+    bool parse_escape(CharSet &cs) {
+        if (eof()) return fail("trailing backslash");
+        const u8 c = (u8)src[pos++];
+        switch (c) {
+        case 'n': cs.set('\n'); return true;
+        case 'r': cs.set('\r'); return true;
+        case 't': cs.set('\t'); return true;
+        case 'f': cs.set('\f'); return true;
+        case 'v': cs.set('\v'); return true;
+        case 'a': cs.set(7); return true;
+        case 'e': cs.set(27); return true;
+        case '0': cs.set(0); return true;
+        case 'x': {
+            if (pos + 2 > src.size() || hexval((u8)src[pos]) < 0 || hexval((u8)src[pos + 1]) < 0) return fail("bad \\x escape");
+            cs.set((u32)(hexval((u8)src[pos]) * 16 + hexval((u8)src[pos + 1])));
+            pos += 2;
+            return true;
+        }
+        case 'd': cs.set_range('0', '9'); return true;
+        case 'D': cs.set_range('0', '9'); cs.invert(); return true;
+        case 'w': cs.set_range('0', '9'); cs.set_range('a', 'z'); cs.set_range('A', 'Z'); cs.set('_'); return true;
+        case 'W': cs.set_range('0', '9'); cs.set_range('a', 'z'); cs.set_range('A', 'Z'); cs.set('_'); cs.invert(); return true;
+        case 's': cs.set(' '); cs.set_range(9, 13); return true;
+        case 'S': cs.set(' '); cs.set_range(9, 13); cs.invert(); return true;
+        default:
+            if ((c >= 'a' && c <= 'z') || (c >= 'A' && c <= 'Z') || (c >= '1' && c <= '9'))
+                return fail("unsupported escape");
+            cs.set(c);
+            return true;
+        }
+    }
+    bool parse_class(CharSet &cs) {  // after '['
+        bool negate = false;
+        if (!eof() && peek() == '^') { negate = true; pos++; }
+        bool first = true;
+        for (;;) {
+            if (eof()) return fail("unterminated class");
+            u8 c = (u8)src[pos++];
+            if (c == ']' && !first) break;
+            first = false;
+            CharSet item;
+            bool single = true;
+            u32 lo = c;
+            if (c == '\\') {
+                const size_t before = pos;
+                if (!parse_escape(item)) return false;
+                const u8 e = (u8)src[before];
+                single = !(e == 'd' || e == 'D' || e == 'w' || e == 'W' || e == 's' || e == 'S');
+                if (single) for (u32 k = 0; k < 256; k++) if (item.test(k)) lo = k;
+            } else {
+                item.set(c);
+            }
+            if (single && pos + 1 < src.size() && src[pos] == '-' && src[pos + 1] != ']') {
+                pos++;
+                u8 h = (u8)src[pos++];
+                u32 hi = h;
+                if (h == '\\') {
+                    CharSet hs;
+                    if (!parse_escape(hs)) return false;
+                    int cnt = 0;
+                    for (u32 k = 0; k < 256; k++) if (hs.test(k)) { hi = k; cnt++; }
+                    if (cnt != 1) return fail("bad range end");
+                }
+                if (hi < lo) return fail("reversed range");
+                item = CharSet();
+                item.set_range(lo, hi);
+            }
+            cs.merge(item);
+        }
+        if (caseless) cs.add_caseless();
+        if (negate) cs.invert();
+        if (cs.empty()) return fail("empty class");
+        return true;
+    }
+
+    int parse_alt() {
+        std::vector<int> alts;
+        int c = parse_cat();
+        if (c < 0) return -1;
+        alts.push_back(c);
+        while (!eof() && peek() == '|') {
+            pos++;
+            c = parse_cat();
+            if (c < 0) return -1;
+            alts.push_back(c);
+        }
+        if (alts.size() == 1) return alts[0];
+        int n = add(N_ALT);
+        nodes[n].kids = alts;
+        return n;
+    }
+    int parse_cat() {
+        std::vector<int> items;
+        while (!eof() && peek() != '|' && peek() != ')') {
+            int r = parse_repeat();
+            if (r < 0) return -1;
+            items.push_back(r);
+        }
+        if (items.empty()) return add(N_EMPTY);
+        if (items.size() == 1) return items[0];
+        int n = add(N_CAT);
+        nodes[n].kids = items;
+        return n;
+    }
+    int wrap(NodeType t, int kid) { int n = add(t); nodes[n].kids = {kid}; return n; }
+    int parse_repeat() {
+        int a = parse_atom();
+        if (a < 0) return -1;
+        for (;;) {
+            if (eof()) break;
+            const u8 c = peek();
+            if (c == '*') { pos++; a = wrap(N_STAR, a); }
+            else if (c == '+') { pos++; a = wrap(N_PLUS, a); }
+            else if (c == '?') { pos++; a = wrap(N_OPT, a); }
+            else if (c == '{') {
+                size_t p = pos + 1;
+                auto number = [&](u32 &v) { size_t s0 = p; v = 0; while (p < src.size() && src[p] >= '0' && src[p] <= '9') { v = v * 10 + (u32)(src[p] - '0'); p++; if (v > 1000) return false; } return p > s0; };
+                u32 lo = 0, hi = 0;
+                bool open_ended = false;
+                if (!number(lo)) { fail("bad repeat"); return -1; }
+                if (p < src.size() && src[p] == ',') {
+                    p++;
+                    if (p < src.size() && src[p] == '}') open_ended = true;
+                    else if (!number(hi)) { fail("bad repeat"); return -1; }
+                } else {
+                    hi = lo;
+                }
+                if (p >= src.size() || src[p] != '}') { fail("bad repeat"); return -1; }
+                pos = p + 1;
+                if (!open_ended && hi < lo) { fail("reversed repeat bounds"); return -1; }
+                if (!open_ended && hi == 0) { a = add(N_EMPTY); continue; }
+                // expand: lo copies, then (hi - lo) nested optionals, or a star for {lo,}
+                std::vector<int> seq;
+                for (u32 i = 0; i < lo; i++) seq.push_back(i == 0 ? a : clone(a));
+                if (open_ended) {
+                    seq.push_back(wrap(N_STAR, lo == 0 ? a : clone(a)));
+                } else if (hi > lo) {
+                    int tail = -1;  // (a (a (a)?)?)?
+                    for (u32 i = 0; i < hi - lo; i++) {
+                        int copy = (lo == 0 && i == 0) ? a : clone(a);
+                        if (tail < 0) tail = wrap(N_OPT, copy);
+                        else { int cat = add(N_CAT); nodes[cat].kids = {copy, tail}; tail = wrap(N_OPT, cat); }
+                    }
+                    seq.push_back(tail);
+                }
+                if (n_char_nodes > MAX_STATES) { fail("pattern too large"); return -1; }
+                if (seq.size() == 1) a = seq[0];
+                else { int cat = add(N_CAT); nodes[cat].kids = seq; a = cat; }
+            } else break;
+            if (!eof() && (peek() == '?' || peek() == '+') && (c == '*' || c == '+' || c == '?' || c == '{')) pos++;  // lazy / possessive marker
+        }
+        return a;
+    }
+    int parse_atom() {
+        if (eof()) { fail("unexpected end"); return -1; }
+        const u8 c = (u8)src[pos++];
+        CharSet cs;
+        switch (c) {
+        case '(': {
+            if (pos + 1 < src.size() && src[pos] == '?' && src[pos + 1] == ':') pos += 2;
+            else if (!eof() && peek() == '?') { fail("unsupported group syntax"); return -1; }
+            int n = parse_alt();
+            if (n < 0) return -1;
+            if (eof() || peek() != ')') { fail("missing )"); return -1; }
+            pos++;
+            return n;
+        }
+        case '[':
+            if (!parse_class(cs)) return -1;
+            { int n = add(N_CHAR); nodes[n].cs = cs; n_char_nodes++; return n; }
+        case '.':
+            cs.invert();
+            if (!dotall) { CharSet nl; nl.set('\n'); for (int i = 0; i < 4; i++) cs.w[i] &= ~nl.w[i]; }
+            { int n = add(N_CHAR); nodes[n].cs = cs; n_char_nodes++; return n; }
+        case '\\':
+            if (!parse_escape(cs)) return -1;
+            return make_char(cs);
+        case '*': case '+': case '?': case '{':
+            fail("nothing to repeat");
+            return -1;
+        case '^': case '$':
+            fail("anchors are only supported as a leading ^");
+            return -1;
+        default:
+            cs.set(c);
+            return make_char(cs);
+        }
+    }
+};
+
+// ---- Glushkov construction ----------------------------------------------------------------------------------
+struct Glushkov {
+    std::vector<CharSet> cls;        // per position
+    std::vector<StateSet> follow;    // per position
+    struct Info { bool nullable; StateSet first, last; u32 min_len; };
+
+    Info build(const std::vector<Node> &nodes, int n) {
+        const Node &nd = nodes[n];
+        Info r{true, {}, {}, 0};
+        switch (nd.type) {
+        case N_EMPTY:
+            return r;
+        case N_CHAR: {
+            const u32 p = (u32)cls.size();
+            cls.push_back(nd.cs);
+            follow.push_back(StateSet());
+            r.nullable = false;
+            r.first.set(p);
+            r.last.set(p);
+            r.min_len = 1;
+            return r;
+        }
+        case N_CAT: {
+            bool have = false;
+            for (int k : nd.kids) {
+                Info ki = build(nodes, k);
+                if (!have) { r = ki; have = true; continue; }
+                for (u32 p = 0; p < cls.size(); p++) if (r.last.test(p)) follow[p] |= ki.first;
+                if (r.nullable) r.first |= ki.first;
+                if (ki.nullable) r.last |= ki.last; else r.last = ki.last;
+                r.nullable = r.nullable && ki.nullable;
+                r.min_len += ki.min_len;
+            }
+            return r;
+        }
+        case N_ALT: {
+            bool have = false;
+            for (int k : nd.kids) {
+                Info ki = build(nodes, k);
+                if (!have) { r = ki; have = true; continue; }
+                r.nullable = r.nullable || ki.nullable;
+                r.first |= ki.first;
+                r.last |= ki.last;
+                r.min_len = std::min(r.min_len, ki.min_len);
+            }
+            return r;
+        }
+        case N_STAR: case N_PLUS: case N_OPT: {
+            Info ki = build(nodes, nd.kids[0]);
+            r = ki;
+            if (nd.type != N_OPT)
+                for (u32 p = 0; p < cls.size(); p++) if (ki.last.test(p)) follow[p] |= ki.first;
+            if (nd.type != N_PLUS) { r.nullable = true; r.min_len = 0; }
+            return r;
+        }
+        }
+        return r;
+    }
+};
+
+}  // namespace
+
+namespace hsb_nfadb {
+struct Pattern { std::string expr; unsigned flags; unsigned id; };
+int build(const std::vector<Pattern> &pats, std::vector<hsb::u8> &image, std::string &err);
+}
+
+namespace {
+
+// little-endian bit vector of `bytes` bytes
+void put_state(u8 *dst, const StateSet &s, u32 bytes) {
+    std::memset(dst, 0, bytes);
+    for (u32 i = 0; i < bytes * 8 && i < MAX_STATES; i++)
+        if (s.test(i)) dst[i >> 3] |= (u8)(1u << (i & 7));
+}
+
+struct Automaton {
+    u32 n_states = 0;
+    std::vector<CharSet> reach_of;     // bytes on which a state may be entered
+    std::vector<StateSet> succ;        // successors of each state
+    std::vector<u32> report_of;        // pattern index + 1 a state reports, 0 = none
+    StateSet init, init_ds;
+    u32 min_width = ~0u;
+};
+
+}  // namespace
+
+namespace hsb_nfadb {
+
+int build(const std::vector<Pattern> &pats, std::vector<u8> &image, std::string &err) {
+    if (pats.empty()) { err = "no expressions"; return HSB_LIT_COMPILER_ERROR; }
+    // ---- 1. parse every pattern, build one automaton -------------------------------------------------
+    Automaton am;
+    bool any_unanch = false, any_anch = false;
+    struct Parsed { Glushkov g; Glushkov::Info info; bool anchored; };
+    std::vector<Parsed> parsed;
+    for (size_t pi = 0; pi < pats.size(); pi++) {
+        const Pattern &p = pats[pi];
+        if (p.flags & ~(HSB_FLAG_CASELESS | HSB_FLAG_DOTALL)) {
+            err = "expression " + std::to_string(pi) + ": unsupported flag";
+            return HSB_LIT_COMPILER_ERROR;
+        }
+        std::string body = p.expr;
+        bool anchored = false;
+        if (!body.empty() && body[0] == '^') { anchored = true; body.erase(0, 1); }
+        Parser ps(body, (p.flags & HSB_FLAG_CASELESS) != 0, (p.flags & HSB_FLAG_DOTALL) != 0);
+        const int root = ps.parse_alt();
+        if (root < 0 || !ps.eof()) {
+            if (ps.err.empty()) ps.fail("unbalanced )");
+            err = "expression " + std::to_string(pi) + ": " + ps.err;
+            return HSB_LIT_COMPILER_ERROR;
+        }
+        if (ps.n_char_nodes > MAX_STATES) { err = "pattern set too large for one LimEx NFA"; return HSB_LIT_COMPILER_ERROR; }
+        Parsed pr;
+        pr.anchored = anchored;
+        pr.info = pr.g.build(ps.nodes, root);
+        if (pr.info.nullable) {
+            err = "expression " + std::to_string(pi) + ": matches the empty string (not supported)";
+            return HSB_LIT_COMPILER_ERROR;
+        }
+        (anchored ? any_anch : any_unanch) = true;
+        parsed.push_back(std::move(pr));
+    }
+    size_t total = (any_unanch ? 1 : 0) + (any_anch ? 1 : 0);
+    for (auto &pr : parsed) total += pr.g.cls.size();
+    if (total > MAX_STATES) { err = "pattern set too large for one LimEx NFA (" + std::to_string(total) + " states)"; return HSB_LIT_COMPILER_ERROR; }
+    am.n_states = (u32)total;
+    am.reach_of.assign(total, CharSet());
+    am.succ.assign(total, StateSet());
+    am.report_of.assign(total, 0);
+    u32 next = 0;
+    const u32 st_ds = any_unanch ? next++ : ~0u, st_anch = any_anch ? next++ : ~0u;
+    if (any_unanch) {
+        am.reach_of[st_ds].invert();  // entered on every byte
+        am.succ[st_ds].set(st_ds);
+        am.init.set(st_ds);
+        am.init_ds.set(st_ds);
+    }
+    if (any_anch) am.init.set(st_anch);
+    for (size_t pi = 0; pi < parsed.size(); pi++) {
+        const Parsed &pr = parsed[pi];
+        const u32 base = next;
+        const u32 n = (u32)pr.g.cls.size();
+        for (u32 p = 0; p < n; p++) {
+            am.reach_of[base + p] = pr.g.cls[p];
+            for (u32 q = 0; q < n; q++) if (pr.g.follow[p].test(q)) am.succ[base + p].set(base + q);
+            if (pr.info.last.test(p)) am.report_of[base + p] = (u32)pi + 1;
+            if (pr.info.first.test(p)) am.succ[pr.anchored ? st_anch : st_ds].set(base + p);
+        }
+        am.min_width = std::min(am.min_width, pr.info.min_len);
+        next += n;
+    }
+
+    // ---- 2. LimEx model: shifts + exceptions ----------------------------------------------------------
+    u32 type = nfa::LIMEX_512;
+    for (u32 t = 0; t < 6; t++) if (limex::layout(t).bits >= am.n_states) { type = t; break; }
+    const limex::Layout L = limex::layout(type);
+    // most frequent forward distances become shifts
+    std::map<u32, u32> dist_count;
+    for (u32 s = 0; s < am.n_states; s++)
+        for (u32 d = 0; d <= limex::MAX_SHIFT_AMOUNT && s + d < am.n_states; d++)
+            if (am.succ[s].test(s + d)) dist_count[d]++;
+    std::vector<std::pair<u32, u32>> by_count;  // (count, distance)
+    for (auto &dc : dist_count) by_count.push_back({dc.second, dc.first});
+    std::sort(by_count.begin(), by_count.end(), [](auto &a, auto &b) { return a.first != b.first ? a.first > b.first : a.second < b.second; });
+    std::vector<u32> shifts;
+    for (auto &c : by_count) if (shifts.size() < limex::MAX_SHIFT_COUNT) shifts.push_back(c.second);
+    if (shifts.empty()) shifts.push_back(1);  // "number of shifts should always be >= 1"
+    std::sort(shifts.begin(), shifts.end());
+    std::vector<StateSet> shift_mask(shifts.size());
+    std::vector<StateSet> exc_succ(am.n_states);
+    StateSet exception_mask, accept_mask;
+    for (u32 s = 0; s < am.n_states; s++) {
+        for (u32 t = 0; t < am.n_states; t++) {
+            if (!am.succ[s].test(t)) continue;
+            bool shifted = false;
+            if (t >= s)
+                for (size_t k = 0; k < shifts.size(); k++)
+                    if (shifts[k] == t - s) { shift_mask[k].set(s); shifted = true; }
+            if (!shifted) { exc_succ[s].set(t); exception_mask.set(s); }
+        }
+        if (am.report_of[s]) { exception_mask.set(s); accept_mask.set(s); }
+    }
+    // reach table: distinct per-byte masks
+    std::vector<StateSet> reach_rows;
+    u8 reach_map[256];
+    {
+        std::map<std::string, u32> seen;
+        for (u32 c = 0; c < 256; c++) {
+            StateSet row;
+            for (u32 s = 0; s < am.n_states; s++) if (am.reach_of[s].test(c)) row.set(s);
+            const std::string key = row.to_string();
+            auto it = seen.find(key);
+            if (it == seen.end()) { it = seen.emplace(key, (u32)reach_rows.size()).first; reach_rows.push_back(row); }
+            reach_map[c] = (u8)it->second;
+        }
+        if (reach_rows.size() > 256) { err = "internal: reach table overflow"; return HSB_LIT_COMPILER_ERROR; }
+    }
+
+    // ---- 3. Rose blob: header, dedupe keys, report programs, NfaInfo, NFA ------------------------------
+    Buf rose;
+    rose.grow(rose::SIZE);
+    rose.align(CACHELINE);
+    // one dedupe key per distinct report id: two positions of a pattern may accept at the same offset
+    std::map<u32, u32> dkeys;
+    for (auto &p : pats) if (!dkeys.count(p.id)) { u32 k = (u32)dkeys.size(); dkeys[p.id] = k; }
+    const u32 inv_dkey_off = (u32)rose.grow(4 * dkeys.size());
+    for (auto &d : dkeys) wr32(rose.at(inv_dkey_off), 4 * d.second, d.first);
+    rose.align(op::ALIGN);
+    std::vector<u32> program_of(pats.size());
+    for (size_t pi = 0; pi < pats.size(); pi++) {
+        rose.align(op::ALIGN);
+        const u32 o = (u32)rose.grow(op::dedupe_and_report::SIZE + op::SIZE_1);
+        program_of[pi] = o;
+        wr8(rose.at(o), 0, op::DEDUPE_AND_REPORT);
+        wr8(rose.at(o), op::dedupe_and_report::quash_som, 0);
+        wr32(rose.at(o), op::dedupe_and_report::dkey, dkeys[pats[pi].id]);
+        wr32(rose.at(o), op::dedupe_and_report::onmatch, pats[pi].id);
+        wr32(rose.at(o), op::dedupe_and_report::offset_adjust, 0);
+        wr32(rose.at(o), op::dedupe_and_report::fail_jump, (u32)op::dedupe_and_report::SIZE);
+        wr8(rose.at(o + op::dedupe_and_report::SIZE), 0, op::END);
+    }
+    rose.align(4);
+    const u32 nfa_info_off = (u32)rose.grow(nfainfo::SIZE);
+    rose.align(CACHELINE);
+    const u32 nfa_off = (u32)rose.size();
+
+    // the engine, relative to its own start
+    Buf eng;
+    eng.grow(nfa::SIZE + L.SIZE);
+    const size_t lx = nfa::SIZE;  // LimExNFA base inside eng
+    // reach table right behind the struct (get_reach_table)
+    const size_t reach_off = eng.grow(reach_rows.size() * L.bytes);
+    for (size_t i = 0; i < reach_rows.size(); i++) put_state(eng.at(reach_off + i * L.bytes), reach_rows[i], L.bytes);
+    eng.align(L.align);
+    const size_t top_off = eng.grow(L.bytes);
+    put_state(eng.at(top_off), am.init, L.bytes);
+    const size_t accel_tab_off = eng.grow(1);  // one entry: state pattern 0 -> aux 0
+    eng.align(16);
+    const size_t accel_aux_off = eng.grow(hwlm::ACCEL_AUX_SIZE);  // aux[0] = ACCEL_NONE
+    eng.align(4);
+    std::vector<u32> accept_states, exc_states;
+    for (u32 s = 0; s < am.n_states; s++) {
+        if (accept_mask.test(s)) accept_states.push_back(s);
+        if (exception_mask.test(s)) exc_states.push_back(s);
+    }
+    const size_t accept_off = eng.grow(accept_states.size() * nfaaccept::SIZE);
+    for (size_t i = 0; i < accept_states.size(); i++) {
+        u8 *a = eng.at(accept_off + i * nfaaccept::SIZE);
+        wr8(a, nfaaccept::single_report, 1);
+        wr32(a, nfaaccept::reports, program_of[am.report_of[accept_states[i]] - 1]);
+        wr32(a, nfaaccept::squash, 0xffffffffu);
+    }
+    // report lists for the exceptions: {program offset, MO_INVALID_IDX} per pattern
+    eng.align(4);
+    std::vector<u32> report_list_of(pats.size());
+    for (size_t pi = 0; pi < pats.size(); pi++) {
+        const size_t o = eng.grow(8);
+        wr32(eng.at(o), 0, program_of[pi]);
+        wr32(eng.at(o), 4, 0xffffffffu);
+        report_list_of[pi] = (u32)(o - lx);
+    }
+    eng.align(L.align < 16 ? 16 : L.align);
+    const size_t exc_off = eng.grow(exc_states.size() * L.E_SIZE);
+    for (size_t i = 0; i < exc_states.size(); i++) {
+        u8 *e = eng.at(exc_off + i * L.E_SIZE);
+        const u32 s = exc_states[i];
+        StateSet ones;
+        ones.set();
+        put_state(e + L.e_squash, ones, L.bytes);
+        put_state(e + L.e_successors, exc_succ[s], L.bytes);
+        wr32(e, L.e_reports, am.report_of[s] ? report_list_of[am.report_of[s] - 1] : 0xffffffffu);
+        wr32(e, L.e_repeatOffset, 0xffffffffu);
+        wr8(e, L.e_hasSquash, limex::SQUASH_NONE);
+        wr8(e, L.e_trigger, 0);
+    }
+    eng.align(CACHELINE);
+    // struct NFA
+    u8 *nh = eng.at(0);
+    wr32(nh, nfa::flags, 0);
+    wr32(nh, nfa::length, (u32)eng.size());
+    wr8(nh, nfa::type, (u8)type);
+    wr32(nh, nfa::queueIndex, 0);
+    wr32(nh, nfa::nPositions, am.n_states);
+    wr32(nh, nfa::scratchStateSize, L.bytes);
+    const u32 stream_state = (am.n_states + 7) / 8;
+    wr32(nh, nfa::streamStateSize, stream_state);
+    wr32(nh, nfa::maxWidth, 0);
+    wr32(nh, nfa::minWidth, am.min_width);
+    // struct LimExNFA
+    u8 *lp = eng.at(lx);
+    std::memcpy(lp + limex::reachMap, reach_map, 256);
+    wr32(lp, limex::reachSize, (u32)reach_rows.size());
+    wr32(lp, limex::accelCount, 0);
+    wr32(lp, limex::accelTableOffset, (u32)(accel_tab_off - lx));
+    wr32(lp, limex::accelAuxCount, 1);
+    wr32(lp, limex::accelAuxOffset, (u32)(accel_aux_off - lx));
+    wr32(lp, limex::acceptCount, (u32)accept_states.size());
+    wr32(lp, limex::acceptOffset, (u32)(accept_off - lx));
+    wr32(lp, limex::acceptEodCount, 0);
+    wr32(lp, limex::acceptEodOffset, (u32)(accept_off - lx));
+    wr32(lp, limex::exceptionCount, (u32)exc_states.size());
+    wr32(lp, limex::exceptionOffset, (u32)(exc_off - lx));
+    wr32(lp, limex::repeatCount, 0);
+    wr32(lp, limex::repeatOffset, 0);
+    wr32(lp, limex::squashOffset, 0);
+    wr32(lp, limex::squashCount, 0);
+    wr32(lp, limex::topCount, 1);
+    wr32(lp, limex::topOffset, (u32)(top_off - lx));
+    wr32(lp, limex::stateSize, stream_state);
+    wr32(lp, limex::flags, 0);
+    StateSet all;
+    for (u32 s = 0; s < am.n_states; s++) all.set(s);
+    put_state(lp + L.init, am.init, L.bytes);
+    put_state(lp + L.initDS, am.init_ds, L.bytes);
+    put_state(lp + L.accept, accept_mask, L.bytes);
+    put_state(lp + L.compressMask, all, L.bytes);
+    put_state(lp + L.exceptionMask, exception_mask, L.bytes);
+    for (size_t k = 0; k < shifts.size(); k++) {
+        put_state(lp + L.shift + k * L.bytes, shift_mask[k], L.bytes);
+        wr8(lp, L.shiftAmount + k, (u8)shifts[k]);
+    }
+    wr32(lp, L.shiftCount, (u32)shifts.size());
+
+    const size_t nfa_at = rose.grow(eng.size());
+    std::memcpy(rose.at(nfa_at), eng.b.data(), eng.size());
+    rose.align(CACHELINE);
+
+    // NfaInfo of queue 0
+    u8 *r = rose.at(0);
+    // stream-state layout (fillStateOffsets): status byte, leaf multibit of one engine, no groups / history /
+    // exhaustion, then the NFA's stream state
+    u32 cur = 1;
+    u8 *so = r + rose::stateOffsets;
+    wr32(so, rose::so::activeLeafArray, cur);
+    wr32(so, rose::so::activeLeafArray_size, mmbit_size(1));
+    cur += mmbit_size(1);
+    wr32(so, rose::so::activeLeftArray, cur);
+    wr32(so, rose::so::longLitState, cur);
+    wr32(so, rose::so::leftfixLagTable, cur);
+    wr32(so, rose::so::anchorState, cur);
+    wr32(so, rose::so::groups, cur);
+    wr32(so, rose::so::groups_size, 0);
+    wr32(so, rose::so::history, cur);
+    wr32(so, rose::so::exhausted, cur);
+    wr32(so, rose::so::exhausted_size, mmbit_size(0));
+    wr32(so, rose::so::logicalVec, cur);
+    wr32(so, rose::so::combVec, cur);
+    wr32(so, rose::so::nfaStateBegin, cur);
+    const u32 nfa_stream_off = cur;
+    cur += stream_state;
+    wr32(so, rose::so::end, cur);
+    u8 *ni = rose.at(nfa_info_off);
+    wr32(ni, nfainfo::nfaOffset, nfa_off);
+    wr32(ni, nfainfo::stateOffset, nfa_stream_off);
+    wr32(ni, nfainfo::fullStateOffset, 0);
+
+    wr8(r, rose::pureLiteral, 0);
+    wr8(r, rose::runtimeImpl, rose::RUNTIME_SINGLE_OUTFIX);
+    wr8(r, rose::canExhaust, 0);
+    wr32(r, rose::mode, MODE_BLOCK);
+    wr32(r, rose::ekeyCount, 0);
+    wr32(r, rose::dkeyCount, (u32)dkeys.size());
+    wr32(r, rose::dkeyLogSize, fatbit_size((u32)dkeys.size()));
+    wr32(r, rose::invDkeyOffset, inv_dkey_off);
+    wr32(r, rose::somLocationFatbitSize, fatbit_size(0));
+    wr32(r, rose::stateSize, cur);
+    wr32(r, rose::scratchStateSize, (u32)round_up(L.bytes, 64));
+    wr32(r, rose::amatcherMaxBiAnchoredWidth, rose::BOUND_INF);
+    wr32(r, rose::fmatcherMaxBiAnchoredWidth, rose::BOUND_INF);
+    wr32(r, rose::activeArrayCount, 1);
+    wr32(r, rose::queueCount, 1);
+    wr32(r, rose::activeQueueArraySize, fatbit_size(1));
+    wr32(r, rose::handledKeyFatbitSize, fatbit_size(0));
+    wr32(r, rose::minWidth, am.min_width);
+    wr32(r, rose::minWidthExcludingBoundaries, am.min_width);
+    wr32(r, rose::maxBiAnchoredWidth, rose::BOUND_INF);
+    wr32(r, rose::nfaInfoOffset, nfa_info_off);
+    wr64(r, rose::initialGroups, 0);
+    wr64(r, rose::floating_group_mask, 0);
+    wr32(r, rose::size, (u32)rose.size());
+    wr32(r, rose::delay_fatbit_size, fatbit_size(0));
+    wr32(r, rose::anchored_fatbit_size, fatbit_size(0));
+    wr32(r, rose::outfixBeginQueue, 0);
+    wr32(r, rose::outfixEndQueue, 1);
+    wr32(r, rose::leftfixBeginQueue, 1);
+    wr32(r, rose::initMpvNfa, 0xffffffffu);
+
+    const size_t bc_off = db::IMAGE_BYTECODE;
+    image.assign(db::SIZE + rose.size(), 0);
+    std::memcpy(image.data() + bc_off, rose.b.data(), rose.size());
+    wr32(image.data(), db::magic, db::MAGIC);
+    wr32(image.data(), db::version, db::VERSION_5_4_11);
+    wr32(image.data(), db::length, (u32)rose.size());
+    wr64(image.data(), db::platform, db::PLATFORM_GENERIC);
+    wr32(image.data(), db::crc32, hsb_crc32c(rose.b.data(), rose.size()));
+    wr32(image.data(), db::bytecode, (u32)bc_off);
+    return HSB_LIT_SUCCESS;
+}
+
+}  // namespace hsb_nfadb
+
+extern "C" int hsb_compile_regex_multi(const char *const *expressions, const unsigned *flags, const unsigned *ids,
+                                       unsigned elements, unsigned mode, hs_database_t **db, char **error) {
+    if (error) *error = nullptr;
+    if (!db) return HSB_LIT_COMPILER_ERROR;
+    *db = nullptr;
+    auto fail = [&](const std::string &m) {
+        if (error) {
+            char *p = (char *)std::malloc(m.size() + 1);
+            if (p) std::memcpy(p, m.c_str(), m.size() + 1);
+            *error = p;
+        }
+        return HSB_LIT_COMPILER_ERROR;
+    };
+    if (!expressions || !elements) return fail("invalid parameter: no expressions");
+    if (mode != hsb::MODE_BLOCK) return fail("only HS_MODE_BLOCK databases are written");
+    std::vector<hsb_nfadb::Pattern> pats;
+    for (unsigned i = 0; i < elements; i++) {
+        if (!expressions[i]) return fail("null expression");
+        pats.push_back({expressions[i], flags ? flags[i] : 0, ids ? ids[i] : 0});
+    }
+    std::vector<hsb::u8> image;
+    std::string err;
+    if (hsb_nfadb::build(pats, image, err) != HSB_LIT_SUCCESS) return fail(err);
+    void *mem = nullptr;
+    if (posix_memalign(&mem, 64, image.size())) return fail("out of memory");
+    std::memcpy(mem, image.data(), image.size());
+    *db = (hs_database_t *)mem;
+    return HSB_LIT_SUCCESS;
+}

@@ -9,6 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 
 HS_FLAG_CASELESS = 1
+HS_FLAG_DOTALL = 2
 HS_FLAG_SINGLEMATCH = 8
 HS_MODE_BLOCK = 1
 
@@ -34,6 +35,9 @@ def lib():
                                             C.POINTER(C.c_size_t), C.c_uint, C.c_uint, C.POINTER(LitOptions),
                                             C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
         L.hsb_compile_lit_multi.restype = C.c_int
+        L.hsb_compile_regex_multi.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_uint), C.POINTER(C.c_uint), C.c_uint,
+                                              C.c_uint, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+        L.hsb_compile_regex_multi.restype = C.c_int
         L.hsb_free_database.argtypes = [C.c_void_p]
         L.hsb_free_error.argtypes = [C.c_void_p]
         L.hsb_database_size.argtypes = [C.c_void_p, C.POINTER(C.c_size_t)]
@@ -106,6 +110,26 @@ def compile_lit_multi(literals, flags=None, ids=None, mode=HS_MODE_BLOCK, engine
     opt = LitOptions(engine, fdr_domain, fdr_stride, teddy_masks, no_flood)
     db, err = C.c_void_p(), C.c_void_p()
     rv = lib().hsb_compile_lit_multi(arr, fl, idv, lens, n, mode, C.byref(opt), C.byref(db), C.byref(err))
+    if rv != 0:
+        msg = C.string_at(err).decode() if err else "error"
+        if err:
+            lib().hsb_free_error(err)
+        raise CompileError(msg)
+    return Database(db.value)
+
+
+def compile_regex_multi(expressions, flags=None, ids=None, mode=HS_MODE_BLOCK):
+    """expressions: list of bytes/str in the writer's dialect (csrc/nfadb_writer.cpp).  Returns a single-outfix
+    Database holding one LimEx NFA.  Same argument meaning as hs_compile_multi."""
+    n = len(expressions)
+    ex = [e.encode("latin-1") if isinstance(e, str) else bytes(e) for e in expressions]
+    if any(b"\0" in e for e in ex):
+        raise CompileError("NUL byte in expression: write it as \\x00")
+    arr = (C.c_char_p * n)(*ex)
+    fl = (C.c_uint * n)(*(flags if flags is not None else [0] * n))
+    idv = (C.c_uint * n)(*(ids if ids is not None else list(range(n))))
+    db, err = C.c_void_p(), C.c_void_p()
+    rv = lib().hsb_compile_regex_multi(arr, fl, idv, n, mode, C.byref(db), C.byref(err))
     if rv != 0:
         msg = C.string_at(err).decode() if err else "error"
         if err:
