@@ -460,7 +460,7 @@ int build(const std::vector<Pattern> &pats, std::vector<u8> &image, std::string 
     std::map<u32, u32> dist_count;
     for (u32 s = 0; s < am.n_states; s++)
         for (u32 d = 0; d <= limex::MAX_SHIFT_AMOUNT && s + d < am.n_states; d++)
-            if (am.succ[s].test(s + d)) dist_count[d]++;
+            if (am.succ[s].test(s + d) && (s >> 6) == ((s + d) >> 6)) dist_count[d]++;
     std::vector<std::pair<u32, u32>> by_count;  // (count, distance)
     for (auto &dc : dist_count) by_count.push_back({dc.second, dc.first});
     std::sort(by_count.begin(), by_count.end(), [](auto &a, auto &b) { return a.first != b.first ? a.first > b.first : a.second < b.second; });
@@ -475,7 +475,8 @@ int build(const std::vector<Pattern> &pats, std::vector<u8> &image, std::string 
         for (u32 t = 0; t < am.n_states; t++) {
             if (!am.succ[s].test(t)) continue;
             bool shifted = false;
-            if (t >= s)
+            // a shift never crosses a 64-bit lane of the state vector (limex_compile.cpp:245-255)
+            if (t >= s && (s >> 6) == (t >> 6))
                 for (size_t k = 0; k < shifts.size(); k++)
                     if (shifts[k] == t - s) { shift_mask[k].set(s); shifted = true; }
             if (!shifted) { exc_succ[s].set(t); exception_mask.set(s); }
