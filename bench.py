@@ -58,6 +58,14 @@ def ncu_traffic(config, nbytes, frontend):
 
 
 def make_workload(config, rank, nbytes):
+    """-> (database, number of pattern ids, [(flat, offsets)] x ROT, description)"""
+    if config == "c3":
+        ex, fl, ids = W.c3_patterns()
+        batches = [W.c3_corpus(nbytes, seed=20260103 + 100 * rank + r) for r in range(ROT)]
+        name = (f"c3: {len(ex)} Snort-like regexes with character classes in one LimEx512 NFA (single-outfix database; "
+                f"as many of the C3 templates as 512 states hold -- no pattern compiler in this image) over a "
+                f"{nbytes >> 20} MiB batch of 200-1400-byte synthetic HTTP payloads per step")
+        return litdb.compile_regex_multi(ex, fl, ids), len(ex), batches, name
     if config == "c1":
         lits, flags, ids = W.c1_patterns()
         batches = []
@@ -69,7 +77,7 @@ def make_workload(config, rank, nbytes):
         lits, flags, ids = W.c2_patterns()
         batches = [W.c2_batch(nbytes, lits, seed=20260102 + 100 * rank + r) for r in range(ROT)]
         name = f"c2: 10000 literals (len 3-12, printable) over a {nbytes >> 20} MiB batch of 1500-byte packets per step"
-    return lits, flags, ids, batches, name
+    return litdb.compile_lit_multi(lits, flags, ids), len(lits), batches, name
 
 
 class ClockSampler:
@@ -133,8 +141,8 @@ def run_reference(args, rank, world):
     if rank != 0:
         return
     nbytes = args.bytes
-    lits, flags, ids, batches, name = make_workload(args.config, 0, nbytes)
-    ser = litdb.compile_lit_multi(lits, flags, ids).serialize()
+    db, n_ids, batches, name = make_workload(args.config, 0, nbytes)
+    ser = db.serialize()
     threads = os.cpu_count() or 1
     # bounded sample per step so that the whole run ends within minutes
     sample = min(nbytes, args.ref_sample_bytes)
@@ -168,13 +176,18 @@ def main():
     ap.add_argument("--steps", type=int, default=40)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours")
-    ap.add_argument("--config", default="c2", choices=["c1", "c2"])
+    ap.add_argument("--config", default="c2", choices=["c1", "c2", "c3"])
     ap.add_argument("--bytes", type=int, default=64 << 20)
-    ap.add_argument("--ref-sample-bytes", type=int, default=64 << 20)
-    ap.add_argument("--cpu-sample-bytes", type=int, default=64 << 20)
+    ap.add_argument("--ref-sample-bytes", type=int, default=0)
+    ap.add_argument("--cpu-sample-bytes", type=int, default=0)
     ap.add_argument("--frontend", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    # bounded CPU samples (the NFA path is ~100x slower per byte on the CPU than the literal path)
+    if not args.ref_sample_bytes:
+        args.ref_sample_bytes = (8 << 20) if args.config == "c3" else (64 << 20)
+    if not args.cpu_sample_bytes:
+        args.cpu_sample_bytes = (4 << 20) if args.config == "c3" else (64 << 20)
 
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -196,8 +209,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     nbytes = args.bytes
-    lits, flags, ids, batches, name = make_workload(args.config, rank, nbytes)
-    db = litdb.compile_lit_multi(lits, flags, ids)
+    db, n_ids, batches, name = make_workload(args.config, rank, nbytes)
     sc = gpu.alloc_scratch(db)
     if args.frontend:
         sc.set_option("frontend", args.frontend)
@@ -234,8 +246,8 @@ def main():
     clocks = sampler.stop()
 
     # the only collective of the path: match counts (+ per-pattern histogram) over NCCL
-    hist = torch.zeros(len(lits), dtype=torch.int64, device="cuda")
-    gpu.lib().hs_gpu_histogram(sc.ptr, C.c_void_p(hist.data_ptr()), len(lits))
+    hist = torch.zeros(n_ids, dtype=torch.int64, device="cuda")
+    gpu.lib().hs_gpu_histogram(sc.ptr, C.c_void_p(hist.data_ptr()), n_ids)
     agg = torch.tensor([dev_ms, float(nbytes_scanned), float(nmatch), kern_ms, wall_s], dtype=torch.float64, device="cuda")
     if world > 1:
         mx = agg.clone()
@@ -310,7 +322,7 @@ def main():
                     "d2h_bytes_per_step": d2h_per_step, "steps": e2e_steps,
                     "call": "hs_gpu_scan_vector_ex(host pinned buffers)", "per_step_ms": brk},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "k_scan" if args.frontend == 1 else "k_turbo", "achieved": round(achieved, 2),
+            "roofline": {"bound": "hbm", "kernel": "k_limex" if args.config == "c3" else "k_scan" if args.frontend == 1 else "k_turbo", "achieved": round(achieved, 2),
                          "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
                          "traffic": ncu_traffic(args.config, nbytes, args.frontend), "peak_source": peak_src,
                          "alg_bytes_per_launch": int(alg_bytes), "kernel_ms": round(kern_ms / n_launch, 4)},

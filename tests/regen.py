@@ -8,70 +8,88 @@ HS_FLAG_DOTALL = 2
 
 _WORDS = [b"GET", b"POST", b"HTTP", b"host", b"php", b"admin", b"select", b"union", b"passwd", b"cmd", b"exe",
           b"login", b"user", b"id", b"script", b"alert", b"eval", b"base64", b"etc", b"bin", b"sh", b"www"]
-_CLASSES = [rb"[a-z]", rb"[A-Za-z0-9_]", rb"\d", rb"\w", rb"\s", rb"[^\r\n]", rb"[^ ]", rb".", rb"[0-9a-f]",
-            rb"[\x00-\x1f]", rb"\S", rb"[^a-z]"]
+_CLASSES = [(rb"[a-z]", b"qz"), (rb"[A-Za-z0-9_]", b"Q7_"), (rb"\d", b"07"), (rb"\w", b"k_"), (rb"\s", b" \t"),
+            (rb"[^\r\n]", b"x;"), (rb"[^ ]", b"y-"), (rb".", b"./"), (rb"[0-9a-f]", b"3e"), (rb"[\x00-\x1f]", b"\x01\x1f"),
+            (rb"\S", b"#s"), (rb"[^a-z]", b"Z5")]
 
 
 def _lit(rng, lo=1, hi=6):
     if rng.random() < 0.5:
-        return re.escape(rng.choice(_WORDS))
-    n = rng.randint(lo, hi)
-    return re.escape(bytes(rng.choice(b"abcdefgh/=?&. ") for _ in range(n)))
+        w = rng.choice(_WORDS)
+    else:
+        w = bytes(rng.choice(b"abcdefgh/=?&. ") for _ in range(rng.randint(lo, hi)))
+    return re.escape(w), w
 
 
 def _quant(rng):
+    """(quantifier, a repeat count it allows)"""
     r = rng.random()
     if r < 0.25:
-        return b"*"
+        return b"*", rng.randint(0, 3)
     if r < 0.5:
-        return b"+"
+        return b"+", rng.randint(1, 3)
     if r < 0.6:
-        return b"?"
+        return b"?", rng.randint(0, 1)
     m = rng.randint(0, 4)
     if r < 0.75:
-        return b"{%d}" % (m + 1)
+        return b"{%d}" % (m + 1), m + 1
     if r < 0.85:
-        return b"{%d,}" % m
-    return b"{%d,%d}" % (m, m + rng.randint(0, 5))
+        return b"{%d,}" % m, m + rng.randint(0, 2)
+    k = rng.randint(0, 5)
+    return b"{%d,%d}" % (m, m + k), m + rng.randint(0, k)
 
 
 def random_expr(rng, depth=0):
-    """One expression that cannot match the empty string (it always starts with a literal)."""
-    parts = [_lit(rng)]
+    """(expression, a string it matches).  Never matches the empty string (it starts with a literal)."""
+    e, x = _lit(rng)
+    parts, sample = [e], [x]
     for _ in range(rng.randint(1, 3)):
         r = rng.random()
         if r < 0.4:
-            parts.append(rng.choice(_CLASSES) + _quant(rng))
+            cls, chars = rng.choice(_CLASSES)
+            q, n = _quant(rng)
+            parts.append(cls + q)
+            sample.append(bytes(rng.choice(chars) for _ in range(n)))
         elif r < 0.6 and depth < 2:
             alts = [random_expr(rng, depth + 1) for _ in range(rng.randint(2, 3))]
-            g = b"(" + b"|".join(alts) + b")"
+            g = b"(" + b"|".join(a[0] for a in alts) + b")"
+            reps = 1
             if rng.random() < 0.3:
-                g += rng.choice([b"?", b"*", b"+", b"{1,2}"])
+                q, reps = rng.choice([(b"?", 0), (b"?", 1), (b"*", 2), (b"+", 1), (b"{1,2}", 2)])
+                g += q
             parts.append(g)
+            sample.append(b"".join(rng.choice(alts)[1] for _ in range(reps)))
         else:
-            parts.append(_lit(rng))
-    parts.append(_lit(rng, 1, 3))
-    e = b"".join(parts)
-    if depth == 0 and rng.random() < 0.15:
-        e = b"^" + e
-    return e
+            e, x = _lit(rng)
+            parts.append(e)
+            sample.append(x)
+    e, x = _lit(rng, 1, 3)
+    parts.append(e)
+    sample.append(x)
+    return b"".join(parts), b"".join(sample)
 
 
-def random_set(rng, n):
-    exprs, flags = [], []
+def random_set(rng, n, with_samples=False):
+    exprs, flags, samples = [], [], []
     for _ in range(n):
-        exprs.append(random_expr(rng))
+        e, x = random_expr(rng)
+        if rng.random() < 0.15:
+            e = b"^" + e
+        exprs.append(e)
+        samples.append(x)
         f = 0
         if rng.random() < 0.3:
             f |= HS_FLAG_CASELESS
         if rng.random() < 0.3:
             f |= HS_FLAG_DOTALL
         flags.append(f)
-    return exprs, flags, list(range(100, 100 + n))
+    ids = list(range(100, 100 + n))
+    return (exprs, flags, ids, samples) if with_samples else (exprs, flags, ids)
 
 
-def random_text(rng, exprs, n):
-    """Text over a small alphabet with fragments of the expressions' literal words planted."""
+def random_text(rng, exprs, n, samples=None):
+    """Text over a small alphabet with fragments of the expressions' literal words planted, and -- when given --
+    strings known to match (an anchored pattern's sample goes to the front)."""
     alpha = b"abcdefgh/=?&. \r\n0123456789_AZ"
     t = bytearray(rng.choice(alpha) for _ in range(n))
     i = 0
@@ -81,6 +99,19 @@ def random_text(rng, exprs, n):
             w = w.swapcase()
         t[i:i + len(w)] = w
         i += len(w) + rng.randint(0, 12)
+    if samples:
+        i = 0
+        for e, x in zip(exprs, samples):
+            if e.startswith(b"^") and rng.random() < 0.5 and x:
+                t[0:len(x)] = x
+                i = len(x)
+                break
+        while i < n:
+            x = rng.choice(samples)
+            if rng.random() < 0.2:
+                x = x.swapcase()
+            t[i:i + len(x)] = x
+            i += len(x) + rng.randint(0, 40)
     return bytes(t[:n])
 
 

@@ -24,13 +24,13 @@ def _scan_ref(ref, db, texts):
 @pytest.mark.parametrize("seed", range(24))
 def test_random_sets_match_brute_force(ref, seed):
     rng = random.Random(seed)
-    ex, fl, ids = regen.random_set(rng, rng.randint(1, 6))
+    ex, fl, ids, smp = regen.random_set(rng, rng.randint(1, 6), True)
     try:
         db = litdb.compile_regex_multi(ex, fl, ids)
     except litdb.CompileError as e:
         assert "too large" in str(e)
         return
-    texts = [regen.random_text(rng, ex, 140) for _ in range(3)]
+    texts = [regen.random_text(rng, ex, 140, smp) for _ in range(3)]
     got = _scan_ref(ref, db, texts)
     for t, g in zip(texts, got):
         assert g == regen.brute_force(ex, fl, ids, t), (ex, fl, t)

@@ -25,6 +25,7 @@
 #include "hsb_layout.h"
 #include "hsb_dbview.h"
 #include "turbo_tables.h"
+#include "limex_tables.h"
 #include "hs_gpu.h"
 
 #include <cuda_runtime.h>
@@ -89,6 +90,7 @@ struct DevDb {
     const turbo::Slot *slots;
     const u32 *bloom;     // second filter tier (turbo_tables.h, 3.)
     u32 tK, tH1, tH2, tL, tBL;
+    u32 lx_abs;           // absolute bytecode offset of the LimExNFA (single-outfix databases)
 };
 
 struct DevCorpus {
@@ -735,6 +737,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_scan(const DevDb db, const DevCo
 }
 
 #include "turbo.cuh"
+#include "limex.cuh"
 
 // ------------------------------------------------------------------------------------------------
 // finalize: Rec (sorted, deduped) -> hs_gpu_match_t
@@ -838,6 +841,9 @@ struct DbImage {  // one uploaded database
     turbo::Slot *d_slots = nullptr;
     u32 *d_bloom = nullptr;
     turbo::Tables turbo_tabs;
+    u64 *d_lx = nullptr;
+    limex_dev::Tables lx_tabs;
+    DevLimex lx{};
     bool ordered_ok = true;
     size_t device_bytes = 0;
     void release() {
@@ -847,6 +853,8 @@ struct DbImage {  // one uploaded database
         if (d_pair) cudaFree(d_pair);
         if (d_slots) cudaFree(d_slots);
         if (d_bloom) cudaFree(d_bloom);
+        if (d_lx) cudaFree(d_lx);
+        d_lx = nullptr;
         d_bloom = nullptr;
         d_bc = nullptr; d_fdr = nullptr; d_teddy = nullptr; d_pair = nullptr; d_slots = nullptr;
     }
@@ -975,6 +983,16 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         im->device_bytes += 1024;
         d.teddy_tab = im->d_teddy;
         d.teddy_masks = v.teddy_masks;
+    } else if (v.kind == ENG_LIMEX) {
+        limex_dev::Tables &t = im->lx_tabs;
+        if (!limex_dev::build(v, t)) { im->release(); delete im; return HS_UNKNOWN_ERROR; }
+        if (cudaMalloc((void **)&im->d_lx, t.blob.size() * 8) != cudaSuccess) { im->release(); delete im; return HS_NOMEM; }
+        cudaMemcpyAsync(im->d_lx, t.blob.data(), t.blob.size() * 8, cudaMemcpyHostToDevice, s->stream);
+        im->device_bytes += t.blob.size() * 8;
+        d.lx_abs = t.limex_abs;
+        im->lx = DevLimex{im->d_lx, t.G, t.n_exc, t.shift_count, t.any_squash ? 1u : 0u, t.shift_amounts, t.o_reach,
+                          t.o_shift, t.o_succ, t.o_squash, t.o_meta, t.o_masks, t.o_base, t.total_words,
+                          t.accept_abs, t.accept_eod_abs, t.nfa_flags};
     } else {
         d.nood_msk = v.nood_msk;
         d.nood_cmp = v.nood_cmp;
@@ -982,7 +1000,7 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         d.nood_id = v.nood_id;
     }
     d.tK = 0;
-    if (turbo::build(v, im->turbo_tabs)) {
+    if (v.kind != ENG_LIMEX && turbo::build(v, im->turbo_tabs)) {
         const turbo::Tables &tt = im->turbo_tabs;
         if (cudaMalloc((void **)&im->d_pair, tt.pair.size() * 8) != cudaSuccess ||
             cudaMalloc((void **)&im->d_slots, tt.slots.size() * sizeof(turbo::Slot)) != cudaSuccess ||
@@ -1057,6 +1075,33 @@ hs_error_t launch_scan(hs_gpu_scratch *s, const DevDb &db, const DevCorpus &cp, 
     k_scan<FE, NOODLE><<<grid, THREADS, dyn, s->stream>>>(db, cp, ar);
     CU_OK(cudaGetLastError());
     return HS_SUCCESS;
+}
+
+template <int G>
+hs_error_t launch_limex_g(hs_gpu_scratch *s, const DbImage *im, const DevCorpus &cp, const DevArena &ar) {
+    const size_t dyn = limex_smem_bytes(im->lx);
+    static size_t configured = 0;
+    if (dyn > configured) {
+        CU_OK(cudaFuncSetAttribute(k_limex<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+        configured = dyn;
+    }
+    // persistent groups of G lanes; no more CTAs than there are buffers to hand out
+    const u32 groups_per_cta = LX_THREADS / G;
+    u32 grid = s->opt_grid > 0 ? (u32)s->opt_grid : 3u * (u32)s->sm_count;
+    const u32 need = (cp.count + groups_per_cta - 1) / groups_per_cta;
+    if (grid > need) grid = need ? need : 1;
+    k_limex<G><<<grid, LX_THREADS, dyn, s->stream>>>(im->dev, im->lx, cp, ar, s->d_ctl + 6);
+    CU_OK(cudaGetLastError());
+    return HS_SUCCESS;
+}
+
+hs_error_t launch_limex(hs_gpu_scratch *s, const DbImage *im, const DevCorpus &cp, const DevArena &ar) {
+    switch (im->lx.G) {
+    case 1: return launch_limex_g<1>(s, im, cp, ar);
+    case 2: return launch_limex_g<2>(s, im, cp, ar);
+    case 4: return launch_limex_g<4>(s, im, cp, ar);
+    default: return launch_limex_g<8>(s, im, cp, ar);
+    }
 }
 
 // Ordered mode: k_turbo<K, true> appends position-ordered records to per-warp segments, k_compact gathers
@@ -1160,6 +1205,7 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
         switch (im->view.kind) {
         case ENG_FDR: rv = launch_scan<FdrNative, false>(s, im->dev, cp, ar); break;
         case ENG_TEDDY: rv = launch_scan<TeddyNative, false>(s, im->dev, cp, ar); break;
+        case ENG_LIMEX: rv = launch_limex(s, im, cp, ar); break;
         default: rv = launch_scan<Noodle, true>(s, im->dev, cp, ar); break;
         }
         if (rv != HS_SUCCESS) return rv;
@@ -1168,7 +1214,10 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
         st.kernel_launches++;
         CU_OK(cudaMemcpyAsync(s->h_ctl, s->d_ctl, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
         CU_OK(cudaStreamSynchronize(s->stream));
-        if ((u32)s->h_ctl[3]) return HS_UNKNOWN_ERROR;
+        if ((u32)s->h_ctl[3]) {
+            if (getenv("HS_GPU_DEBUG")) fprintf(stderr, "hs_gpu: device error flags 0x%x\n", (u32)s->h_ctl[3]);
+            return HS_UNKNOWN_ERROR;
+        }
         raw = s->h_ctl[0];
         if (raw <= s->recs.cap) break;
         if (attempt >= 3) return HS_NOMEM;

@@ -14,7 +14,7 @@ namespace hsb {
 constexpr int E_SUCCESS = 0, E_INVALID = -1, E_NOMEM = -2, E_DB_VERSION = -5, E_DB_PLATFORM = -6,
               E_DB_MODE = -7, E_BAD_ALIGN = -8, E_ARCH = -11, E_UNKNOWN = -13;
 
-enum EngineKind : u32 { ENG_FDR = 0, ENG_TEDDY = 1, ENG_NOODLE = 2 };
+enum EngineKind : u32 { ENG_FDR = 0, ENG_TEDDY = 1, ENG_NOODLE = 2, ENG_LIMEX = 3 };
 
 struct LitRec {  // one LitInfo, flattened
     u64 v, msk, groups;
@@ -43,6 +43,8 @@ struct DbView {
     std::vector<LitRec> lits;  // every literal of every bucket (empty for noodle)
     std::vector<u32> programs; // distinct program offsets reachable from the literal matcher
     u32 max_lit_len = 0;       // longest CHECK_*_LIT length seen (bounds look-behind)
+    // single-outfix LimEx NFA (kind == ENG_LIMEX): offsets are absolute bytecode offsets
+    u32 nfa_off = 0, limex_off = 0, limex_type = 0, nfa_flags = 0, nfa_len = 0;
 };
 
 inline bool in_range(const DbView &d, size_t off, size_t n) { return off <= d.bc_len && n <= d.bc_len - off; }
@@ -88,6 +90,86 @@ inline int census_program(const DbView &d, u32 prog, std::string &why, u32 &max_
     return E_INVALID;
 }
 
+// Single-outfix database (src/runtime.c:246-279): queue 0 holds the only engine.  Accepted when that engine is a
+// LimEx NFA without bounded repeats and without reverse acceleration; every report list and accept entry must
+// lead to a Rose report program the device interpreter implements.
+inline int parse_single_outfix(DbView &d, std::string &why) {
+    const u8 *r = d.bc;
+    if (rd32(r, rose::fmatcherOffset) || rd32(r, rose::amatcherOffset) || rd32(r, rose::ematcherOffset)) {
+        why = "single-outfix database with a literal matcher"; return E_INVALID;
+    }
+    if (rd32(r, rose::outfixEndQueue) != 1 || rd32(r, rose::queueCount) != 1) { why = "single-outfix database with more than one queue"; return E_INVALID; }
+    const u32 info_off = rd32(r, rose::nfaInfoOffset);
+    if (!in_range(d, info_off, nfainfo::SIZE)) { why = "NfaInfo outside bytecode"; return E_INVALID; }
+    d.nfa_off = rd32(r, info_off + nfainfo::nfaOffset);
+    if ((d.nfa_off & 63) || !in_range(d, d.nfa_off, nfa::SIZE)) { why = "NFA header outside bytecode or misaligned"; return E_INVALID; }
+    const u8 *n = r + d.nfa_off;
+    d.nfa_len = rd32(n, nfa::length);
+    d.nfa_flags = rd32(n, nfa::flags);
+    d.limex_type = rd8(n, nfa::type);
+    if (!in_range(d, d.nfa_off, d.nfa_len)) { why = "NFA runs past the bytecode"; return E_INVALID; }
+    if (d.limex_type > nfa::LIMEX_512) { why = "outfix engine type " + std::to_string(d.limex_type) + " (not LimEx) is not supported yet"; return E_ARCH; }
+    if (rd8(n, nfa::rAccelType)) { why = "reverse acceleration is not supported"; return E_ARCH; }
+    const limex::Layout L = limex::layout(d.limex_type);
+    if (d.nfa_len < nfa::SIZE + L.SIZE) { why = "LimEx truncated"; return E_INVALID; }
+    d.limex_off = d.nfa_off + (u32)nfa::SIZE;
+    d.kind = ENG_LIMEX;
+    const u8 *lx = r + d.limex_off;
+    const u32 lx_len = d.nfa_len - (u32)nfa::SIZE;
+    auto lx_range = [&](size_t off, size_t len) { return off <= lx_len && len <= lx_len - off; };
+    if (rd32(lx, limex::repeatCount)) { why = "LimEx bounded repeats are not supported yet"; return E_ARCH; }
+    if (rd32(lx, L.shiftCount) > limex::MAX_SHIFT_COUNT) { why = "LimEx shift count out of range"; return E_INVALID; }
+    for (u32 k = 0; k < rd32(lx, L.shiftCount); k++)
+        if (rd8(lx, L.shiftAmount + k) > 63) { why = "LimEx shift amount out of range"; return E_INVALID; }
+    if (!lx_range(L.SIZE, (size_t)rd32(lx, limex::reachSize) * L.bytes) || rd32(lx, limex::reachSize) > 256) { why = "LimEx reach table truncated"; return E_INVALID; }
+    for (u32 c = 0; c < 256; c++)
+        if (rd8(lx, limex::reachMap + c) >= rd32(lx, limex::reachSize)) { why = "LimEx reach map out of range"; return E_INVALID; }
+    std::set<u32> progs;
+    auto add_list = [&](u32 off) -> bool {  // ReportID list relative to the LimEx, MO_INVALID_IDX-terminated
+        for (u32 k = 0;; k++) {
+            if (k > 65536 || !lx_range((size_t)off + 4 * (size_t)k, 4)) return false;
+            const u32 id = rd32(lx, (size_t)off + 4 * (size_t)k);
+            if (id == 0xffffffffu) return true;
+            progs.insert(id);
+        }
+    };
+    // exception table: one entry per bit of exceptionMask
+    u32 n_exc = 0;
+    for (u32 b = 0; b < L.bytes; b++) n_exc += (u32)__builtin_popcount(rd8(lx, L.exceptionMask + b));
+    const u32 exc_off = rd32(lx, limex::exceptionOffset);
+    if (n_exc != rd32(lx, limex::exceptionCount) || !lx_range(exc_off, (size_t)n_exc * L.E_SIZE)) { why = "LimEx exception table inconsistent"; return E_INVALID; }
+    for (u32 i = 0; i < n_exc; i++) {
+        const u8 *e = lx + exc_off + (size_t)i * L.E_SIZE;
+        if (rd8(e, L.e_trigger)) { why = "LimEx repeat triggers are not supported yet"; return E_ARCH; }
+        const u8 sq = rd8(e, L.e_hasSquash);
+        if (sq != limex::SQUASH_NONE && sq != limex::SQUASH_CYCLIC && sq != limex::SQUASH_REPORT) { why = "LimEx tug squash without repeats"; return E_INVALID; }
+        const u32 rep = rd32(e, L.e_reports);
+        if (rep != 0xffffffffu && !add_list(rep)) { why = "LimEx report list outside the engine"; return E_INVALID; }
+    }
+    // accept tables: one NFAAccept per bit of accept / acceptAtEOD
+    const size_t masks[2] = {L.accept, L.acceptAtEOD}, cnt[2] = {limex::acceptCount, limex::acceptEodCount},
+                 offs[2] = {limex::acceptOffset, limex::acceptEodOffset};
+    for (int t = 0; t < 2; t++) {
+        u32 na = 0;
+        for (u32 b = 0; b < L.bytes; b++) na += (u32)__builtin_popcount(rd8(lx, masks[t] + b));
+        const u32 ao = rd32(lx, offs[t]);
+        if (na != rd32(lx, cnt[t]) || !lx_range(ao, (size_t)na * nfaaccept::SIZE)) { why = "LimEx accept table inconsistent"; return E_INVALID; }
+        for (u32 i = 0; i < na; i++) {
+            const u8 *a = lx + ao + (size_t)i * nfaaccept::SIZE;
+            if (rd8(a, nfaaccept::single_report)) progs.insert(rd32(a, nfaaccept::reports));
+            else if (!add_list(rd32(a, nfaaccept::reports))) { why = "LimEx accept report list outside the engine"; return E_INVALID; }
+        }
+    }
+    d.max_lit_len = 8;
+    for (u32 p : progs) {
+        if (p < rose::SIZE || !in_range(d, p, 8)) { why = "report program offset outside bytecode"; return E_INVALID; }
+        int rv = census_program(d, p, why, d.max_lit_len);
+        if (rv != E_SUCCESS) return rv;
+        d.programs.push_back(p);
+    }
+    return E_SUCCESS;
+}
+
 // `db` is the caller's in-memory hs_database_t.
 inline int parse_database(const void *db, DbView &d, std::string &why) {
     if (!db) return E_INVALID;
@@ -105,11 +187,11 @@ inline int parse_database(const void *db, DbView &d, std::string &why) {
     if (rd8(r, rose::hasSom)) { why = "start-of-match databases are not supported"; return E_ARCH; }
     if (rd32(r, rose::ckeyCount) || rd32(r, rose::lkeyCount)) { why = "logical combinations are not supported"; return E_ARCH; }
     const u8 impl = rd8(r, rose::runtimeImpl);
-    if (impl != rose::RUNTIME_PURE_LITERAL) {
-        why = impl == rose::RUNTIME_FULL_ROSE ? "full-Rose databases (NFA/DFA engines) are not supported yet"
-                                              : "single-outfix databases are not supported yet";
+    if (impl == rose::RUNTIME_FULL_ROSE) {
+        why = "full-Rose databases (several engines interleaved by Rose) are not supported yet";
         return E_ARCH;
     }
+    if (impl != rose::RUNTIME_PURE_LITERAL && impl != rose::RUNTIME_SINGLE_OUTFIX) { why = "unknown runtimeImpl"; return E_INVALID; }
     const u8 *bd = r + rose::boundary;
     if (rd32(bd, rose::bd::reportEodOffset) || rd32(bd, rose::bd::reportZeroOffset) ||
         rd32(bd, rose::bd::reportZeroEodOffset)) {
@@ -122,6 +204,7 @@ inline int parse_database(const void *db, DbView &d, std::string &why) {
     d.ekey_count = rd32(r, rose::ekeyCount);
     d.dkey_count = rd32(r, rose::dkeyCount);
     d.groups = rd64(r, rose::initialGroups) & rd64(r, rose::floating_group_mask);
+    if (impl == rose::RUNTIME_SINGLE_OUTFIX) return parse_single_outfix(d, why);
     d.hwlm_off = rd32(r, rose::fmatcherOffset);
     if (!d.hwlm_off || !in_range(d, d.hwlm_off, hwlm::BODY + 24)) { why = "no floating literal matcher"; return E_INVALID; }
     const u8 type = rd8(r, d.hwlm_off + hwlm::type);

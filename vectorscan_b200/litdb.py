@@ -82,6 +82,17 @@ class Database:
         off = int.from_bytes(raw[36:40], "little")
         return raw[off:]
 
+    def limex_bits(self):
+        """State width of the LimEx NFA of a single-outfix database (0 for any other database):
+        RoseEngine.nfaInfoOffset -> NfaInfo.nfaOffset -> NFA.type (nfa_internal.h:89-128)."""
+        bc = self.bytecode()
+        if bc[4] != 2:  # RoseEngine.runtimeImpl == ROSE_RUNTIME_SINGLE_OUTFIX
+            return 0
+        info = int.from_bytes(bc[236:240], "little")
+        nfa = int.from_bytes(bc[info:info + 4], "little")
+        t = bc[nfa + 8]
+        return [32, 64, 128, 256, 384, 512][t] if t < 6 else 0
+
     def serialize(self):
         out, n = C.c_void_p(), C.c_size_t()
         if lib().hsb_serialize_database(self.ptr, C.byref(out), C.byref(n)) != 0:

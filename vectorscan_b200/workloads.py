@@ -112,3 +112,90 @@ def sweep_patterns(n, seed):
 def sweep_batch(nbytes, bufsize, lits, seed):
     flat, offsets = c2_batch(nbytes, lits, seed=seed, packet=bufsize)
     return flat, offsets
+
+
+# ---- c3: Snort-like regex set over synthetic HTTP payloads (SURVEY.md 8d "C3 concrete input") ------------------
+# No pattern compiler exists in this image, so the set is what ONE LimEx NFA can hold:
+# templates of the C3 description are drawn until the next one would not fit 512 states (csrc/nfadb_writer.cpp).
+_C3_WORDS = [b"admin", b"login", b"passwd", b"select", b"union", b"script", b"eval", b"cmd", b"shell", b"upload",
+             b"config", b"backup", b"token", b"session", b"debug", b"root", b"etc", b"proc", b"wp-", b"cgi-bin"]
+_C3_EXT = [b"php", b"asp", b"jsp", b"cgi", b"exe", b"dll", b"sh"]
+
+
+def c3_patterns(seed=20260103, max_patterns=2000, state_budget=500):
+    """(expressions, flags, ids): expressions in the LimEx writer's dialect."""
+    rng = np.random.default_rng(seed)
+    ex, fl = [], []
+    used = 2
+    while len(ex) < max_patterns:
+        k = int(rng.integers(0, 6))
+        w = _C3_WORDS[int(rng.integers(0, len(_C3_WORDS)))]
+        w2 = _C3_WORDS[int(rng.integers(0, len(_C3_WORDS)))]
+        if k == 0:
+            m, n = int(rng.integers(1, 4)), int(rng.integers(4, 9))
+            e = w + b"[0-9a-f]{%d,%d}" % (m, n) + w2
+            cost = len(w) + n + len(w2)
+        elif k == 1:
+            n = int(rng.integers(4, 13))
+            e = w + b"\\s+[A-Za-z0-9_]{4,%d}=" % n
+            cost = len(w) + 1 + n + 1
+        elif k == 2:
+            e = b"^(GET|POST) /[^ ]*\\." + _C3_EXT[int(rng.integers(0, len(_C3_EXT)))] + b"\\?"
+            cost = 7 + 2 + 1 + 1 + 3 + 1
+        elif k == 3:
+            g = int(rng.integers(2, 9))
+            e = w + b"=[^\\r\\n]{%d}" % g + w2
+            cost = len(w) + 1 + g + len(w2)
+        elif k == 4:
+            e = b"/" + w + b"/[^ ?]*\\.\\./"
+            cost = len(w) + 7
+        else:
+            e = b"(" + w + b"|" + w2 + b")[^&]*&" + _C3_WORDS[int(rng.integers(0, len(_C3_WORDS)))] + b"="
+            cost = len(w) + len(w2) + 12
+        if used + cost > state_budget:
+            break
+        used += cost
+        ex.append(e)
+        fl.append(1 if rng.random() < 0.3 else 0)  # HS_FLAG_CASELESS
+    return ex, fl, list(range(len(ex)))
+
+
+def c3_corpus(nbytes, seed=20260103):
+    """Synthetic HTTP requests / responses, 200..1400 bytes each: (flat uint8 array, uint64 offsets)."""
+    rng = np.random.default_rng(seed + 11)
+    lens = []
+    tot = 0
+    while tot < nbytes:
+        chunk = rng.integers(200, 1401, 65536)
+        lens.append(chunk)
+        tot += int(chunk.sum())
+    lens = np.concatenate(lens)
+    ends = np.cumsum(lens)
+    count = int(np.searchsorted(ends, nbytes, side="left")) + 1
+    offsets = np.concatenate([[0], np.minimum(ends[:count], nbytes)]).astype(np.uint64)
+    # body: URL-ish / header-ish bytes
+    alpha = np.frombuffer(b"abcdefghijklmnopqrstuvwxyz0123456789/=&?._-%+ :;", dtype=np.uint8)
+    flat = alpha[rng.integers(0, len(alpha), nbytes)]
+    # line structure: CRLF about every 60 bytes
+    nl = rng.integers(0, max(1, nbytes - 2), nbytes // 60)
+    flat[nl] = 13
+    flat[nl + 1] = 10
+    # request lines at the start of 60 % of the buffers, status lines on the rest
+    starts = offsets[:-1].astype(np.int64)
+    heads = [b"GET /", b"POST /", b"HTTP/1.1 200 OK\r\n"]
+    pick = rng.choice(3, size=len(starts), p=[0.4, 0.2, 0.4])
+    for t, h in enumerate(heads):
+        sel = starts[(pick == t) & (np.diff(offsets).astype(np.int64) > 64)]
+        hb = np.frombuffer(h, dtype=np.uint8)
+        flat[sel[:, None] + np.arange(len(hb))[None, :]] = hb[None, :]
+    # header tokens and attack-ish words sprinkled through the payload (~25 % of the bytes)
+    toks = HTTP_TOKENS + [b"/" + w + b"/" for w in _C3_WORDS] + [w + b"=" for w in _C3_WORDS] + \
+           [b"." + e + b"?" for e in _C3_EXT] + [b"/../"]
+    ntok = int(nbytes * 0.25 / 14)
+    tok_idx = rng.integers(0, len(toks), ntok)
+    tok_pos = rng.integers(8, max(9, nbytes - 64), ntok)
+    for t, tok in enumerate(toks):
+        sel = tok_pos[tok_idx == t]
+        tb = np.frombuffer(tok, dtype=np.uint8)
+        flat[sel[:, None] + np.arange(len(tb))[None, :]] = tb[None, :]
+    return flat, offsets
