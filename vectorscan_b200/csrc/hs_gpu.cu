@@ -910,6 +910,7 @@ struct hs_gpu_scratch {
     long opt_frontend = 0;
     long opt_grid = 0;
     u64 arena_hint = 1 << 16;
+    u64 lx_event_hint = 1 << 16;
 };
 
 namespace {
@@ -991,7 +992,7 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         im->device_bytes += t.blob.size() * 8;
         d.lx_abs = t.limex_abs;
         im->lx = DevLimex{im->d_lx, t.G, t.n_exc, t.shift_count, t.any_squash ? 1u : 0u, t.shift_amounts, t.o_reach,
-                          t.o_shift, t.o_succ, t.o_squash, t.o_meta, t.o_masks, t.o_base, t.total_words,
+                          t.o_shift, t.o_shamt, t.o_csucc, t.o_succ, t.o_squash, t.o_meta, t.o_masks, t.o_base, t.total_words,
                           t.accept_abs, t.accept_eod_abs, t.nfa_flags};
     } else {
         d.nood_msk = v.nood_msk;
@@ -1087,11 +1088,17 @@ hs_error_t launch_limex_g(hs_gpu_scratch *s, const DbImage *im, const DevCorpus 
     }
     // persistent groups of G lanes; no more CTAs than there are buffers to hand out
     const u32 groups_per_cta = LX_THREADS / G;
-    u32 grid = s->opt_grid > 0 ? (u32)s->opt_grid : 3u * (u32)s->sm_count;
+    u32 grid = s->opt_grid > 0 ? (u32)s->opt_grid : 4u * (u32)s->sm_count;
     const u32 need = (cp.count + groups_per_cta - 1) / groups_per_cta;
     if (grid > need) grid = need ? need : 1;
-    k_limex<G><<<grid, LX_THREADS, dyn, s->stream>>>(im->dev, im->lx, cp, ar, s->d_ctl + 6);
+    // events (what the NFA raised) go to recs2, then one thread per event runs the report programs into the arena
+    CU_OK(s->recs2.reserve(s->lx_event_hint));
+    const DevLxEvents evq{reinterpret_cast<LxEvent *>(s->recs2.p), s->d_ctl + 7, s->recs2.cap};
+    k_limex<G><<<grid, LX_THREADS, dyn, s->stream>>>(im->dev, im->lx, cp, evq, s->d_ctl + 6);
     CU_OK(cudaGetLastError());
+    k_limex_report<<<(u32)s->sm_count, LX_THREADS, 0, s->stream>>>(im->dev, cp, ar, evq);
+    CU_OK(cudaGetLastError());
+    s->stats.kernel_launches++;
     return HS_SUCCESS;
 }
 
@@ -1219,6 +1226,12 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
             return HS_UNKNOWN_ERROR;
         }
         raw = s->h_ctl[0];
+        if (im->view.kind == ENG_LIMEX && s->h_ctl[7] > s->recs2.cap) {  // event queue overflow: grow, scan again
+            if (attempt >= 3) return HS_NOMEM;
+            st.arena_retries++;
+            s->lx_event_hint = s->h_ctl[7] + s->h_ctl[7] / 8 + 1024;
+            continue;
+        }
         if (raw <= s->recs.cap) break;
         if (attempt >= 3) return HS_NOMEM;
         st.arena_retries++;

@@ -19,14 +19,25 @@
 
 constexpr int LX_WARPS = 8;
 constexpr int LX_THREADS = LX_WARPS * 32;
-constexpr int LX_STAGE = 64;  // staged match records per warp
+constexpr int LX_STAGE = 64;  // staged match records per warp (report kernel)
 
 struct DevLimex {
     const u64 *tab;       // limex_dev::Tables blob in HBM
     u32 G, n_exc, shift_count, any_squash;
     u64 shift_amounts;
-    u32 o_reach, o_shift, o_succ, o_squash, o_meta, o_masks, o_base, total_words;
+    u32 o_reach, o_shift, o_shamt, o_csucc, o_succ, o_squash, o_meta, o_masks, o_base, total_words;
     u32 accept_abs, accept_eod_abs, nfa_flags;
+};
+
+// What the stepping kernel hands to the report kernel: "the NFA raised report list / report program `what` at
+// offset `to` of buffer `buf`" -- the arguments of the NfaCallback (roseReportAdaptor, src/rose/match.c:611-633).
+struct __align__(16) LxEvent {
+    u32 buf, to, what, single;  // single != 0: `what` is one program offset; else the absolute offset of a list
+};
+struct DevLxEvents {
+    LxEvent *ev;
+    unsigned long long *count;  // events wanted (may exceed cap)
+    u64 cap;
 };
 
 struct LxWarpShared {
@@ -35,78 +46,61 @@ struct LxWarpShared {
     u32 pad[3];
 };
 
-__host__ __device__ inline size_t limex_smem_bytes(const DevLimex &lx) {
-    return (size_t)lx.total_words * 8 + sizeof(LxWarpShared) * LX_WARPS;
+__host__ __device__ inline size_t limex_smem_bytes(const DevLimex &lx) { return (size_t)lx.total_words * 8; }
+
+__device__ __forceinline__ void lx_event(const DevLxEvents &q, u32 buf, u32 to, u32 what, u32 single) {
+    const unsigned long long slot = atomicAdd(q.count, 1ull);
+    if (slot < q.cap) q.ev[slot] = LxEvent{buf, to, what, single};
 }
 
-__device__ __noinline__ void lx_run_program(const Ctx &c, u32 prog, u32 buf, const u8 *btext, u32 blen, u32 to) {
-    run_program(c, prog, buf, btext, blen, to);
-}
-
-// fire a MO_INVALID_IDX-terminated list of report programs (limexRunReports -> roseReportAdaptor)
-__device__ __noinline__ void lx_run_reports(const Ctx &c, u32 list_abs, u32 buf, const u8 *btext, u32 blen, u32 to) {
-    for (u32 k = 0; k < 65536; k++) {
-        const u32 prog = ld32(c.db.bc, list_abs + 4 * k);
-        if (prog == 0xffffffffu) return;
-        lx_run_program(c, prog, buf, btext, blen, to);
-    }
-}
-
-// accepts of state word `a` (already AND-ed with the accept mask) -- moProcessAccepts
-template <int G>
-__device__ __noinline__ void lx_accepts(const Ctx &c, u64 a, u64 amask, const u32 *sh_base, u32 w, u32 table_abs,
-                                           u32 buf, const u8 *btext, u32 blen, u32 to) {
-    // every lane walks its own word: accept entries are independent of one another
-    const u32 base = sh_base[w];
+// accepts of state word `a` (already AND-ed with the accept mask) -- moProcessAccepts; every lane walks its own
+// word: accept entries are independent of one another
+__device__ __forceinline__ void lx_accepts(const DevLxEvents &q, const u8 *bc, u32 lx_abs, u64 a, u64 amask, u32 base,
+                                           u32 table_abs, u32 buf, u32 to) {
     while (a) {
         const u32 bit = (u32)__ffsll((long long)a) - 1;
         a &= a - 1;
         const u32 idx = base + (u32)__popcll(amask & ((1ull << bit) - 1));
         const u32 at = table_abs + idx * (u32)nfaaccept::SIZE;
-        const u32 rep = ld32(c.db.bc, at + (u32)nfaaccept::reports);
-        if (c.db.bc[at + nfaaccept::single_report]) lx_run_program(c, rep, buf, btext, blen, to);
-        else lx_run_reports(c, c.db.lx_abs + rep, buf, btext, blen, to);
+        const u32 rep = ld32(bc, at + (u32)nfaaccept::reports);
+        const u32 single = bc[at + nfaaccept::single_report];
+        lx_event(q, buf, to, single ? rep : lx_abs + rep, single);
     }
 }
 
 template <int G>
-__global__ void __launch_bounds__(LX_THREADS, 3) k_limex(const DevDb db, const DevLimex lx, const DevCorpus cp,
-                                                         const DevArena ar, unsigned long long *next_buf) {
+__global__ void __launch_bounds__(LX_THREADS, 4) k_limex(const DevDb db_, const DevLimex lx, const DevCorpus cp_,
+                                                         const DevLxEvents evq, unsigned long long *next_buf) {
     extern __shared__ __align__(16) u8 smem[];
     u64 *tab = reinterpret_cast<u64 *>(smem);
-    LxWarpShared *wsh = reinterpret_cast<LxWarpShared *>(smem + (size_t)lx.total_words * 8);
     for (u32 i = threadIdx.x; i < lx.total_words; i += LX_THREADS) tab[i] = lx.tab[i];
-    const u32 warp = threadIdx.x >> 5, ln = lane_id();
-    if (ln == 0) wsh[warp].stage_n = 0;
+    const u32 ln = lane_id();
     __syncthreads();
 
     const u64 *sh_reach = tab + lx.o_reach, *sh_succ = tab + lx.o_succ, *sh_squash = tab + lx.o_squash,
-              *sh_meta = tab + lx.o_meta, *sh_masks = tab + lx.o_masks;
+              *sh_meta = tab + lx.o_meta, *sh_masks = tab + lx.o_masks, *sh_shift = tab + lx.o_shift;
     const u32 *sh_base = reinterpret_cast<const u32 *>(tab + lx.o_base);
-    const Ctx c{db, cp, ar, nullptr, wsh[warp].stage, &wsh[warp].stage_n, LX_STAGE, nullptr, nullptr};
 
     const u32 w = ln & (G - 1), gbase = ln & ~(u32)(G - 1);
     const u32 gmask = (G == 32 ? 0xffffffffu : ((1u << G) - 1u)) << gbase;
-    const u64 initm = sh_masks[0 * G + w], excm = sh_masks[1 * G + w], accm = sh_masks[2 * G + w],
-              eodm = sh_masks[3 * G + w];
-    u64 shm[8];
-#pragma unroll
-    for (int k = 0; k < 8; k++) shm[k] = tab[lx.o_shift + k * G + w];
-    const u64 amts = lx.shift_amounts;
-    const u32 nshift = lx.shift_count;
+    const u64 excm = sh_masks[1 * G + w];        // exception states the device still has to look at
+    const u64 csucc = tab[lx.o_csucc + w];       // successors switched on at every step (limex_tables.h)
+    const u64 amts = tab[lx.o_shamt + w];
+    const u32 nshift = sh_base[3 * G + w];
     const bool any_squash = lx.any_squash != 0;
+    const u64 *my_shift = sh_shift + w, *my_reach = sh_reach + w;
+    const u32 count = cp_.count;
 
-    // per-buffer state
+    // per-buffer state.  The exception cache starts as "no exception state on -> nothing": the common step costs
+    // one group vote.
     u64 s = 0, c_est = 0, c_succ = 0;
     u32 c_rep = 0xffffffffu;
-    bool c_valid = false;
     u32 buf = 0, len = 0, i = 0;
-    const u8 *btext = nullptr;
     const uint4 *chunk = nullptr;
     u64 lo = 0, hi = 0;
+    uint4 nxt = make_uint4(0, 0, 0, 0);
     u32 in_chunk = 0;  // bytes left in (lo, hi)
     bool have = false;
-    unsigned long long n_steps = 0;
 
     for (;;) {
         if (!have || i == len) {
@@ -115,9 +109,12 @@ __global__ void __launch_bounds__(LX_THREADS, 3) k_limex(const DevDb db, const D
                 bool live = s != 0;
                 if (G > 1) live = __ballot_sync(gmask, live) != 0;
                 if (live) {
-                    lx_accepts<G>(c, s & accm, accm, sh_base + 1 * G, w, lx.accept_abs, buf, btext, len, len);
-                    if (lx.nfa_flags & nfa::ACCEPTS_EOD)
-                        lx_accepts<G>(c, s & eodm, eodm, sh_base + 2 * G, w, lx.accept_eod_abs, buf, btext, len, len);
+                    const u64 accm = sh_masks[2 * G + w];
+                    lx_accepts(evq, db_.bc, db_.lx_abs, s & accm, accm, sh_base[1 * G + w], lx.accept_abs, buf, len);
+                    if (lx.nfa_flags & nfa::ACCEPTS_EOD) {
+                        const u64 eodm = sh_masks[3 * G + w];
+                        lx_accepts(evq, db_.bc, db_.lx_abs, s & eodm, eodm, sh_base[2 * G + w], lx.accept_eod_abs, buf, len);
+                    }
                 }
                 have = false;
             }
@@ -125,93 +122,118 @@ __global__ void __launch_bounds__(LX_THREADS, 3) k_limex(const DevDb db, const D
             unsigned long long nb = 0;
             if (w == 0) nb = atomicAdd(next_buf, 1ull);
             if (G > 1) nb = __shfl_sync(gmask, nb, gbase);
-            if (nb >= cp.count) break;
+            if (nb >= count) break;
             buf = (u32)nb;
-            const u64 o0 = cp.off[buf], o1 = cp.off[buf + 1];
+            const u64 o0 = cp_.off[buf], o1 = cp_.off[buf + 1];
             len = (u32)(o1 - o0);
-            if (!len || !passes_gates(db, len)) continue;
-            btext = cp.text + o0;
-            const uintptr_t ap = reinterpret_cast<uintptr_t>(btext);
+            if (!len || !passes_gates(db_, len)) continue;
+            const uintptr_t ap = reinterpret_cast<uintptr_t>(cp_.text + o0);
             chunk = reinterpret_cast<const uint4 *>(ap & ~(uintptr_t)15);
             const u32 skip = (u32)(ap & 15);
-            const uint4 v = *chunk++;
+            const uint4 v = chunk[0];
+            nxt = chunk[1];  // always inside the padded text (BACK_PAD)
+            chunk += 2;
             lo = (u64)v.x | ((u64)v.y << 32);
             hi = (u64)v.z | ((u64)v.w << 32);
             if (skip >= 8) { lo = hi >> (8 * (skip - 8)); hi = 0; }
             else if (skip) { lo = (lo >> (8 * skip)) | (hi << (64 - 8 * skip)); hi >>= 8 * skip; }
             in_chunk = 16 - skip;
             i = 0;
-            s = initm;
-            c_valid = false;
+            s = sh_masks[0 * G + w];
+            c_est = 0; c_succ = 0; c_rep = 0xffffffffu;
             have = true;
         }
         // ---- one byte ----
         if (!in_chunk) {
-            const uint4 v = *chunk++;
-            lo = (u64)v.x | ((u64)v.y << 32);
-            hi = (u64)v.z | ((u64)v.w << 32);
+            lo = (u64)nxt.x | ((u64)nxt.y << 32);
+            hi = (u64)nxt.z | ((u64)nxt.w << 32);
             in_chunk = 16;
+            // once per 16 bytes: a state vector with nothing on stays that way (no TOP arrives mid-buffer)
+            bool dead = s == 0;
+            if (G > 1) dead = __ballot_sync(gmask, !dead) == 0;
+            if (dead) { i = len; continue; }
+            if (i + 16 < len) nxt = *chunk;  // the chunk after this one, if the buffer reaches it
+            chunk++;
         }
         const u32 ch = (u32)lo & 0xffu;
         lo = (lo >> 8) | (hi << 56);
         hi >>= 8;
         in_chunk--;
-        n_steps++;
 
-        u64 succ = 0;
-#pragma unroll
-        for (int k = 0; k < 8; k++)
-            if (k < (int)nshift) succ |= (s & shm[k]) << ((u32)(amts >> (8 * k)) & 63u);
+        u64 succ = csucc;
+        for (u32 k = 0; k < nshift; k++)
+            succ |= (s & my_shift[k * G]) << ((u32)(amts >> (8 * k)) & 63u);
 
         const u64 e = s & excm;
-        u32 eb;
-        if (G > 1) eb = __ballot_sync(gmask, e != 0); else eb = e != 0 ? (1u << ln) : 0u;
-        if (eb) {
-            bool hit = c_valid && e == c_est;
-            if (G > 1) hit = __ballot_sync(gmask, !hit) == 0;
-            if (hit) {
-                succ |= c_succ;
-                if (c_rep != 0xffffffffu && w == 0) lx_run_reports(c, c_rep, buf, btext, len, i);
-            } else {
-                u64 ls = 0;
-                u32 rep_seen = 0xffffffffu;
-                bool cacheable = true;
-                while (eb) {
-                    const u32 src = (u32)__ffs((int)eb) - 1;
-                    eb &= eb - 1;
-                    const u32 ws = src - gbase;
-                    u64 ew = G > 1 ? __shfl_sync(gmask, e, src) : e;
-                    const u64 xm = sh_masks[1 * G + ws];
-                    const u32 base = sh_base[ws];
-                    while (ew) {
-                        const u32 bit = (u32)__ffsll((long long)ew) - 1;
-                        ew &= ew - 1;
-                        const u32 idx = base + (u32)__popcll(xm & ((1ull << bit) - 1));
-                        ls |= sh_succ[idx * G + w];
-                        const u64 meta = sh_meta[idx];
-                        if (any_squash && (meta >> 32)) { succ &= sh_squash[idx * G + w]; cacheable = false; }
-                        const u32 rep = (u32)meta;
-                        if (rep != 0xffffffffu) {
-                            if (w == 0) lx_run_reports(c, rep, buf, btext, len, i);
-                            if (rep_seen == 0xffffffffu || rep_seen == rep) rep_seen = rep; else cacheable = false;
-                        }
+        bool miss = e != c_est;
+        if (G > 1) miss = __ballot_sync(gmask, miss) != 0;
+        if (!miss) {
+            succ |= c_succ;
+            if (c_rep != 0xffffffffu && w == 0) lx_event(evq, buf, i, c_rep, 0);
+        } else {
+            u32 eb;
+            if (G > 1) eb = __ballot_sync(gmask, e != 0); else eb = e != 0 ? (1u << ln) : 0u;
+            u64 ls = 0;
+            u32 rep_seen = 0xffffffffu;
+            bool cacheable = true;
+            while (eb) {
+                const u32 src = (u32)__ffs((int)eb) - 1;
+                eb &= eb - 1;
+                const u32 ws = src - gbase;
+                u64 ew = G > 1 ? __shfl_sync(gmask, e, src) : e;
+                const u64 xm = sh_masks[4 * G + ws];
+                const u32 base = sh_base[ws];
+                while (ew) {
+                    const u32 bit = (u32)__ffsll((long long)ew) - 1;
+                    ew &= ew - 1;
+                    const u32 idx = base + (u32)__popcll(xm & ((1ull << bit) - 1));
+                    ls |= sh_succ[idx * G + w];
+                    const u64 meta = sh_meta[idx];
+                    if (any_squash && (meta >> 32)) { succ &= sh_squash[idx * G + w]; cacheable = false; }
+                    const u32 rep = (u32)meta;
+                    if (rep != 0xffffffffu) {
+                        if (w == 0) lx_event(evq, buf, i, rep, 0);
+                        if (rep_seen == 0xffffffffu || rep_seen == rep) rep_seen = rep; else cacheable = false;
                     }
                 }
-                succ |= ls;
-                if (cacheable) { c_est = e; c_succ = ls; c_rep = rep_seen; c_valid = true; }
             }
-        } else {
-            // no exception state is on: if no state at all is on, the automaton is dead for good
-            bool dead = s == 0;
-            if (G > 1) dead = __ballot_sync(gmask, !dead) == 0;
-            if (dead) { i = len; s = 0; continue; }
+            succ |= ls;
+            if (cacheable) { c_est = e; c_succ = ls; c_rep = rep_seen; }
         }
-        s = succ & sh_reach[ch * G + w];
+        s = succ & my_reach[ch * G];
         i++;
     }
+}
+
+// The report half: one thread per event runs the Rose report program(s) the NFA named (limexRunReports ->
+// roseReportAdaptor -> roseRunProgram) and stages the resulting match records.
+__global__ void __launch_bounds__(LX_THREADS) k_limex_report(const DevDb db, const DevCorpus cp, const DevArena ar,
+                                                             const DevLxEvents evq) {
+    __shared__ LxWarpShared wsh[LX_WARPS];
+    const u32 warp = threadIdx.x >> 5, ln = lane_id();
+    if (ln == 0) wsh[warp].stage_n = 0;
     __syncwarp();
-    flush_stage(c);
-#pragma unroll
-    for (int d = 16; d; d >>= 1) n_steps += __shfl_down_sync(0xffffffffu, n_steps, d);
-    if (ln == 0 && n_steps) atomicAdd(&ar.stats[0], n_steps / G);
+    const Ctx c{db, cp, ar, nullptr, wsh[warp].stage, &wsh[warp].stage_n, LX_STAGE, nullptr, nullptr};
+    unsigned long long n = *evq.count;
+    if (n > evq.cap) n = evq.cap;  // overflow: the host grows the queue and repeats the scan
+    const unsigned long long stride = (unsigned long long)gridDim.x * LX_THREADS;
+    for (unsigned long long base = (unsigned long long)blockIdx.x * LX_THREADS + warp * 32; base < n; base += stride) {
+        const unsigned long long k = base + ln;
+        if (k < n) {
+            const LxEvent ev = evq.ev[k];
+            const u64 o0 = cp.off[ev.buf];
+            const u32 blen = (u32)(cp.off[ev.buf + 1] - o0);
+            const u8 *btext = cp.text + o0;
+            if (ev.single) {
+                run_program(c, ev.what, ev.buf, btext, blen, ev.to);
+            } else {
+                for (u32 j = 0; j < 65536; j++) {
+                    const u32 prog = ld32(db.bc, ev.what + 4 * j);
+                    if (prog == 0xffffffffu) break;
+                    run_program(c, prog, ev.buf, btext, blen, ev.to);
+                }
+            }
+        }
+        flush_stage(c);
+    }
 }

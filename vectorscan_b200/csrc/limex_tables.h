@@ -9,12 +9,18 @@
 //
 // Blob layout (u64 words; offsets in DevLimex):
 //   reach[256][G]      reach set of each input byte, reachMap already applied (limex_state_impl.h:64-67)
-//   shift[8][G]        shift masks (unused ones zero)
+//   shift[8][G]        per word w: its NON-ZERO shift masks, compacted to the front (count in base[3][w]);
+//   shamt[G]           byte k of word w = shift amount that goes with shift[k][w]
+//   csucc[G]           successors switched on at EVERY step: the exception successors of states that are on for
+//                      the whole scan (in init, self-loop by a 0-shift, in every byte's reach set, never squashed)
+//                      and that neither report nor squash; such states are dropped from masks[1] (the device's
+//                      exception mask) but keep their slot in the exception table (ranks use masks[4])
 //   exc_succ[n][G]     successors of exception i          (NFAException.successors)
 //   exc_squash[n][G]   squash mask of exception i, all-ones when it has none (only present if any squash)
 //   exc_meta[n]        lo32 = absolute bytecode offset of the report list or 0xffffffff, hi32 = 1 if it squashes
-//   masks[4][G]        init, exceptionMask, accept, acceptAtEOD
-//   base[3][G] (u32)   exceptions / accepts / EOD accepts that precede word w (rank base of its first bit)
+//   masks[5][G]        init, device exception mask, accept, acceptAtEOD, exceptionMask as in the database
+//   base[4][G] (u32)   exceptions / accepts / EOD accepts that precede word w (rank base of its first bit);
+//                      [3][w] = number of shift masks of word w
 #pragma once
 #include "hsb_dbview.h"
 
@@ -29,7 +35,7 @@ struct Tables {
     u32 n_exc = 0, shift_count = 0;
     u64 shift_amounts = 0;  // byte k = shiftAmount[k]
     bool any_squash = false;
-    u32 o_reach = 0, o_shift = 0, o_succ = 0, o_squash = 0, o_meta = 0, o_masks = 0, o_base = 0, total_words = 0;
+    u32 o_reach = 0, o_shift = 0, o_shamt = 0, o_csucc = 0, o_succ = 0, o_squash = 0, o_meta = 0, o_masks = 0, o_base = 0, total_words = 0;
     u32 accept_abs = 0, accept_eod_abs = 0, limex_abs = 0;  // absolute bytecode offsets
     u32 nfa_flags = 0;
     std::vector<u64> blob;
@@ -68,11 +74,13 @@ inline bool build(const DbView &d, Tables &t) {
     u32 at = 0;
     t.o_reach = at; at += 256 * G;
     t.o_shift = at; at += 8 * G;
+    t.o_shamt = at; at += G;
+    t.o_csucc = at; at += G;
     t.o_succ = at; at += t.n_exc * G;
     t.o_squash = at; at += t.any_squash ? t.n_exc * G : 0;
     t.o_meta = at; at += t.n_exc;
-    t.o_masks = at; at += 4 * G;
-    t.o_base = at; at += (3 * G + 1) / 2;
+    t.o_masks = at; at += 5 * G;
+    t.o_base = at; at += (4 * G + 1) / 2;
     t.total_words = (at + 1) & ~1u;  // the per-warp staging that follows in shared memory is 16-byte aligned
     t.blob.assign(t.total_words, 0);
     u64 *B = t.blob.data();
@@ -82,8 +90,21 @@ inline bool build(const DbView &d, Tables &t) {
         const u8 *row = reach + (size_t)rd8(lx, limex::reachMap + c) * L.bytes;
         for (u32 w = 0; w < t.words; w++) B[t.o_reach + c * G + w] = state_word(row, L.bytes, w);
     }
-    for (u32 k = 0; k < t.shift_count; k++)
-        for (u32 w = 0; w < t.words; w++) B[t.o_shift + k * G + w] = state_word(lx + L.shift + (size_t)k * L.bytes, L.bytes, w);
+    u32 *base = reinterpret_cast<u32 *>(B + t.o_base);
+    std::vector<u64> loop0(G, 0);  // states with a self loop through a 0-shift
+    for (u32 w = 0; w < t.words; w++) {
+        u32 n = 0;
+        for (u32 k = 0; k < t.shift_count; k++) {
+            const u64 m = state_word(lx + L.shift + (size_t)k * L.bytes, L.bytes, w);
+            const u32 amt = rd8(lx, L.shiftAmount + k);
+            if (!m) continue;
+            if (!amt) loop0[w] |= m;
+            B[t.o_shift + n * G + w] = m;
+            B[t.o_shamt + w] |= (u64)amt << (8 * n);
+            n++;
+        }
+        base[3 * G + w] = n;
+    }
     for (u32 i = 0; i < t.n_exc; i++) {
         const u8 *e = exc + (size_t)i * L.E_SIZE;
         const bool sq = rd8(e, L.e_hasSquash) != limex::SQUASH_NONE;
@@ -94,15 +115,30 @@ inline bool build(const DbView &d, Tables &t) {
         const u32 rep = rd32(e, L.e_reports);
         B[t.o_meta + i] = (u64)(rep == 0xffffffffu ? rep : d.limex_off + rep) | ((u64)(sq ? 1 : 0) << 32);
     }
-    const size_t mask_at[4] = {L.init, L.exceptionMask, L.accept, L.acceptAtEOD};
-    for (u32 m = 0; m < 4; m++)
+    const size_t mask_at[5] = {L.init, L.exceptionMask, L.accept, L.acceptAtEOD, L.exceptionMask};
+    for (u32 m = 0; m < 5; m++)
         for (u32 w = 0; w < t.words; w++) B[t.o_masks + m * G + w] = state_word(lx + mask_at[m], L.bytes, w);
-    u32 *base = reinterpret_cast<u32 *>(B + t.o_base);
     for (u32 m = 0; m < 3; m++) {
         u32 run = 0;
         for (u32 w = 0; w < G; w++) {
             base[m * G + w] = run;
-            run += (u32)__builtin_popcountll(B[t.o_masks + (m + 1) * G + w]);
+            run += (u32)__builtin_popcountll(B[t.o_masks + (m == 0 ? 4 : m + 1) * G + w]);
+        }
+    }
+    // states that are on from the first step to the last: fold their plain exception successors into csucc
+    for (u32 w = 0; w < t.words; w++) {
+        u64 on = B[t.o_masks + 0 * G + w] & loop0[w];
+        for (u32 c = 0; c < 256; c++) on &= B[t.o_reach + c * G + w];
+        if (t.any_squash)
+            for (u32 i = 0; i < t.n_exc; i++) on &= B[t.o_squash + i * G + w];
+        const u64 xm = B[t.o_masks + 4 * G + w];
+        for (u64 x = on & xm; x; x &= x - 1) {
+            const u32 bit = (u32)__builtin_ctzll(x);
+            const u32 idx = base[0 * G + w] + (u32)__builtin_popcountll(xm & ((1ull << bit) - 1));
+            const u64 meta = B[t.o_meta + idx];
+            if ((u32)meta != 0xffffffffu || (meta >> 32)) continue;  // reports or squashes: stays an exception
+            for (u32 v = 0; v < t.words; v++) B[t.o_csucc + v] |= B[t.o_succ + idx * G + v];
+            B[t.o_masks + 1 * G + w] &= ~(1ull << bit);
         }
     }
     return true;
