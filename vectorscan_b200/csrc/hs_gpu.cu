@@ -991,7 +991,7 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         cudaMemcpyAsync(im->d_lx, t.blob.data(), t.blob.size() * 8, cudaMemcpyHostToDevice, s->stream);
         im->device_bytes += t.blob.size() * 8;
         d.lx_abs = t.limex_abs;
-        im->lx = DevLimex{im->d_lx, t.G, t.n_exc, t.shift_count, t.any_squash ? 1u : 0u, t.shift_amounts, t.o_reach,
+        im->lx = DevLimex{im->d_lx, t.G, t.n_exc, t.shift_count, t.any_squash ? 1u : 0u, t.can_die ? 1u : 0u, t.shift_amounts, t.o_reach,
                           t.o_shift, t.o_shamt, t.o_csucc, t.o_succ, t.o_squash, t.o_meta, t.o_masks, t.o_base, t.total_words,
                           t.accept_abs, t.accept_eod_abs, t.nfa_flags};
     } else {

@@ -23,7 +23,7 @@ constexpr int LX_STAGE = 64;  // staged match records per warp (report kernel)
 
 struct DevLimex {
     const u64 *tab;       // limex_dev::Tables blob in HBM
-    u32 G, n_exc, shift_count, any_squash;
+    u32 G, n_exc, shift_count, any_squash, can_die;
     u64 shift_amounts;
     u32 o_reach, o_shift, o_shamt, o_csucc, o_succ, o_squash, o_meta, o_masks, o_base, total_words;
     u32 accept_abs, accept_eod_abs, nfa_flags;
@@ -68,6 +68,9 @@ __device__ __forceinline__ void lx_accepts(const DevLxEvents &q, const u8 *bc, u
     }
 }
 
+// One shift of the limited model, amount uniform over the launch: (s & shift[k]) << shiftAmount[k]
+#define LX_SHIFT(k) succ |= (s & my_shift[(k) * G]) << ((u32)(amts >> (8 * (k))) & 63u)
+
 template <int G>
 __global__ void __launch_bounds__(LX_THREADS, 4) k_limex(const DevDb db_, const DevLimex lx, const DevCorpus cp_,
                                                          const DevLxEvents evq, unsigned long long *next_buf) {
@@ -77,38 +80,38 @@ __global__ void __launch_bounds__(LX_THREADS, 4) k_limex(const DevDb db_, const 
     const u32 ln = lane_id();
     __syncthreads();
 
-    const u64 *sh_reach = tab + lx.o_reach, *sh_succ = tab + lx.o_succ, *sh_squash = tab + lx.o_squash,
-              *sh_meta = tab + lx.o_meta, *sh_masks = tab + lx.o_masks, *sh_shift = tab + lx.o_shift;
+    const u64 *sh_succ = tab + lx.o_succ, *sh_squash = tab + lx.o_squash, *sh_meta = tab + lx.o_meta,
+              *sh_masks = tab + lx.o_masks;
     const u32 *sh_base = reinterpret_cast<const u32 *>(tab + lx.o_base);
-
+    constexpr u32 FULL = 0xffffffffu;
     const u32 w = ln & (G - 1), gbase = ln & ~(u32)(G - 1);
-    const u32 gmask = (G == 32 ? 0xffffffffu : ((1u << G) - 1u)) << gbase;
+    const u32 gmask = (G == 32 ? FULL : ((1u << G) - 1u)) << gbase;
     const u64 excm = sh_masks[1 * G + w];        // exception states the device still has to look at
-    const u64 csucc = tab[lx.o_csucc + w];       // successors switched on at every step (limex_tables.h)
-    const u64 amts = tab[lx.o_shamt + w];
-    const u32 nshift = sh_base[3 * G + w];
-    const bool any_squash = lx.any_squash != 0;
-    const u64 *my_shift = sh_shift + w, *my_reach = sh_reach + w;
+    u64 csucc = tab[lx.o_csucc + w];             // successors switched on at every step (limex_tables.h)
+    const u64 amts = lx.shift_amounts;           // uniform
+    const u32 nshift = lx.shift_count;
+    const bool any_squash = lx.any_squash != 0, can_die = lx.can_die != 0;
+    const u64 *my_shift = tab + lx.o_shift + w, *my_reach = tab + lx.o_reach + w;
     const u32 count = cp_.count;
 
-    // per-buffer state.  The exception cache starts as "no exception state on -> nothing": the common step costs
-    // one group vote.
+    // Per-buffer state.  The exception cache starts as "no exception state on -> nothing".
+    // For G > 1 every vote and shuffle below is a FULL-WARP operation at a point all 32 lanes pass once per trip
+    // of the loop (groups that ran out of buffers idle along with an empty state until the whole warp is done),
+    // so the hardware takes the converged path; each group reads its own bits of the result.
     u64 s = 0, c_est = 0, c_succ = 0;
     u32 c_rep = 0xffffffffu;
     u32 buf = 0, len = 0, i = 0;
-    const uint4 *chunk = nullptr;
+    const uint4 *chunk = reinterpret_cast<const uint4 *>(cp_.text);
     u64 lo = 0, hi = 0;
     uint4 nxt = make_uint4(0, 0, 0, 0);
     u32 in_chunk = 0;  // bytes left in (lo, hi)
-    bool have = false;
+    bool have = false, done = false;
 
     for (;;) {
-        if (!have || i == len) {
+        if (!done && i == len) {
             if (have) {
                 // ---- end of buffer: accepts at offset len, then EOD accepts (runtime.c:273-278) ----
-                bool live = s != 0;
-                if (G > 1) live = __ballot_sync(gmask, live) != 0;
-                if (live) {
+                if (s) {
                     const u64 accm = sh_masks[2 * G + w];
                     lx_accepts(evq, db_.bc, db_.lx_abs, s & accm, accm, sh_base[1 * G + w], lx.accept_abs, buf, len);
                     if (lx.nfa_flags & nfa::ACCEPTS_EOD) {
@@ -118,40 +121,42 @@ __global__ void __launch_bounds__(LX_THREADS, 4) k_limex(const DevDb db_, const 
                 }
                 have = false;
             }
-            // ---- next buffer of this group ----
-            unsigned long long nb = 0;
-            if (w == 0) nb = atomicAdd(next_buf, 1ull);
-            if (G > 1) nb = __shfl_sync(gmask, nb, gbase);
-            if (nb >= count) break;
-            buf = (u32)nb;
-            const u64 o0 = cp_.off[buf], o1 = cp_.off[buf + 1];
-            len = (u32)(o1 - o0);
-            if (!len || !passes_gates(db_, len)) continue;
-            const uintptr_t ap = reinterpret_cast<uintptr_t>(cp_.text + o0);
-            chunk = reinterpret_cast<const uint4 *>(ap & ~(uintptr_t)15);
-            const u32 skip = (u32)(ap & 15);
-            const uint4 v = chunk[0];
-            nxt = chunk[1];  // always inside the padded text (BACK_PAD)
-            chunk += 2;
-            lo = (u64)v.x | ((u64)v.y << 32);
-            hi = (u64)v.z | ((u64)v.w << 32);
-            if (skip >= 8) { lo = hi >> (8 * (skip - 8)); hi = 0; }
-            else if (skip) { lo = (lo >> (8 * skip)) | (hi << (64 - 8 * skip)); hi >>= 8 * skip; }
-            in_chunk = 16 - skip;
-            i = 0;
-            s = sh_masks[0 * G + w];
-            c_est = 0; c_succ = 0; c_rep = 0xffffffffu;
-            have = true;
+            // ---- next buffer of this group (empty and gated-out buffers are skipped here) ----
+            s = 0; len = 0; i = 0;
+            c_est = 0; c_succ = 0; c_rep = 0xffffffffu;  // an idle group must never look like a cache miss
+            for (;;) {
+                unsigned long long nb = 0;
+                if (w == 0) nb = atomicAdd(next_buf, 1ull);
+                if (G > 1) nb = __shfl_sync(gmask, nb, gbase);
+                if (nb >= count) { done = true; csucc = 0; break; }  // idle from here on: nothing may switch on
+                buf = (u32)nb;
+                const u64 o0 = cp_.off[buf], o1 = cp_.off[buf + 1];
+                const u32 l = (u32)(o1 - o0);
+                if (!l || !passes_gates(db_, l)) continue;
+                len = l;
+                const uintptr_t ap = reinterpret_cast<uintptr_t>(cp_.text + o0);
+                chunk = reinterpret_cast<const uint4 *>(ap & ~(uintptr_t)15);
+                const u32 skip = (u32)(ap & 15);
+                const uint4 v = chunk[0];
+                nxt = chunk[1];  // always inside the padded text (BACK_PAD)
+                chunk += 2;
+                lo = (u64)v.x | ((u64)v.y << 32);
+                hi = (u64)v.z | ((u64)v.w << 32);
+                if (skip >= 8) { lo = hi >> (8 * (skip - 8)); hi = 0; }
+                else if (skip) { lo = (lo >> (8 * skip)) | (hi << (64 - 8 * skip)); hi >>= 8 * skip; }
+                in_chunk = 16 - skip;
+                s = sh_masks[0 * G + w];
+                have = true;
+                break;
+            }
         }
+        if (G > 1) { if (__all_sync(FULL, done)) break; } else if (done) break;
+
         // ---- one byte ----
         if (!in_chunk) {
             lo = (u64)nxt.x | ((u64)nxt.y << 32);
             hi = (u64)nxt.z | ((u64)nxt.w << 32);
             in_chunk = 16;
-            // once per 16 bytes: a state vector with nothing on stays that way (no TOP arrives mid-buffer)
-            bool dead = s == 0;
-            if (G > 1) dead = __ballot_sync(gmask, !dead) == 0;
-            if (dead) { i = len; continue; }
             if (i + 16 < len) nxt = *chunk;  // the chunk after this one, if the buffer reaches it
             chunk++;
         }
@@ -161,26 +166,34 @@ __global__ void __launch_bounds__(LX_THREADS, 4) k_limex(const DevDb db_, const 
         in_chunk--;
 
         u64 succ = csucc;
-        for (u32 k = 0; k < nshift; k++)
-            succ |= (s & my_shift[k * G]) << ((u32)(amts >> (8 * k)) & 63u);
+        switch (nshift) {
+        case 8: LX_SHIFT(7);  // fallthrough
+        case 7: LX_SHIFT(6);  // fallthrough
+        case 6: LX_SHIFT(5);  // fallthrough
+        case 5: LX_SHIFT(4);  // fallthrough
+        case 4: LX_SHIFT(3);  // fallthrough
+        case 3: LX_SHIFT(2);  // fallthrough
+        case 2: LX_SHIFT(1);  // fallthrough
+        case 1: LX_SHIFT(0);  // fallthrough
+        default: break;
+        }
 
         const u64 e = s & excm;
-        bool miss = e != c_est;
-        if (G > 1) miss = __ballot_sync(gmask, miss) != 0;
-        if (!miss) {
-            succ |= c_succ;
-            if (c_rep != 0xffffffffu && w == 0) lx_event(evq, buf, i, c_rep, 0);
-        } else {
-            u32 eb;
-            if (G > 1) eb = __ballot_sync(gmask, e != 0); else eb = e != 0 ? (1u << ln) : 0u;
+        u32 missw;  // lanes (of the whole warp) whose exception word differs from the cached one
+        if (G > 1) missw = __ballot_sync(FULL, e != c_est); else missw = e != c_est ? gmask : 0u;
+        if (missw) {
+            const bool mine = (missw & gmask) != 0;  // my group missed
+            u32 ebw;
+            if (G > 1) ebw = __ballot_sync(FULL, mine && e != 0); else ebw = e != 0 ? gmask : 0u;
+            u32 eb = ebw & gmask;
             u64 ls = 0;
             u32 rep_seen = 0xffffffffu;
             bool cacheable = true;
-            while (eb) {
-                const u32 src = (u32)__ffs((int)eb) - 1;
-                eb &= eb - 1;
+            while (ebw) {  // one exception word per group and round
+                const u32 src = eb ? (u32)__ffs((int)eb) - 1 : ln;
+                u64 ew = G > 1 ? __shfl_sync(FULL, e, src) : e;
+                if (!eb) ew = 0;
                 const u32 ws = src - gbase;
-                u64 ew = G > 1 ? __shfl_sync(gmask, e, src) : e;
                 const u64 xm = sh_masks[4 * G + ws];
                 const u32 base = sh_base[ws];
                 while (ew) {
@@ -196,14 +209,31 @@ __global__ void __launch_bounds__(LX_THREADS, 4) k_limex(const DevDb db_, const 
                         if (rep_seen == 0xffffffffu || rep_seen == rep) rep_seen = rep; else cacheable = false;
                     }
                 }
+                eb &= eb - 1;
+                if (G > 1) ebw = __ballot_sync(FULL, eb != 0); else ebw = 0;
             }
-            succ |= ls;
-            if (cacheable) { c_est = e; c_succ = ls; c_rep = rep_seen; }
+            if (mine) {
+                succ |= ls;
+                if (cacheable) { c_est = e; c_succ = ls; c_rep = rep_seen; }
+            } else {
+                succ |= c_succ;
+                if (c_rep != 0xffffffffu && w == 0) lx_event(evq, buf, i, c_rep, 0);
+            }
+        } else {
+            succ |= c_succ;
+            if (c_rep != 0xffffffffu && w == 0) lx_event(evq, buf, i, c_rep, 0);
         }
         s = succ & my_reach[ch * G];
         i++;
+        if (can_die) {
+            // a state vector with nothing on stays that way (no TOP arrives mid-buffer): skip to the end
+            bool nz = s != 0;
+            if (G > 1) nz = (__ballot_sync(FULL, nz) & gmask) != 0;
+            if (!nz && i < len) i = len;
+        }
     }
 }
+#undef LX_SHIFT
 
 // The report half: one thread per event runs the Rose report program(s) the NFA named (limexRunReports ->
 // roseReportAdaptor -> roseRunProgram) and stages the resulting match records.

@@ -9,8 +9,8 @@
 //
 // Blob layout (u64 words; offsets in DevLimex):
 //   reach[256][G]      reach set of each input byte, reachMap already applied (limex_state_impl.h:64-67)
-//   shift[8][G]        per word w: its NON-ZERO shift masks, compacted to the front (count in base[3][w]);
-//   shamt[G]           byte k of word w = shift amount that goes with shift[k][w]
+//   shift[8][G]        shift masks, in the database's order (amounts: Tables::shift_amounts, uniform per launch)
+//   shamt[G]           unused
 //   csucc[G]           successors switched on at EVERY step: the exception successors of states that are on for
 //                      the whole scan (in init, self-loop by a 0-shift, in every byte's reach set, never squashed)
 //                      and that neither report nor squash; such states are dropped from masks[1] (the device's
@@ -20,7 +20,7 @@
 //   exc_meta[n]        lo32 = absolute bytecode offset of the report list or 0xffffffff, hi32 = 1 if it squashes
 //   masks[5][G]        init, device exception mask, accept, acceptAtEOD, exceptionMask as in the database
 //   base[4][G] (u32)   exceptions / accepts / EOD accepts that precede word w (rank base of its first bit);
-//                      [3][w] = number of shift masks of word w
+//                      [3][w] = number of non-zero shift masks of word w (statistics)
 #pragma once
 #include "hsb_dbview.h"
 
@@ -35,6 +35,7 @@ struct Tables {
     u32 n_exc = 0, shift_count = 0;
     u64 shift_amounts = 0;  // byte k = shiftAmount[k]
     bool any_squash = false;
+    bool can_die = true;    // false when some state is on for the whole scan (then the state vector never empties)
     u32 o_reach = 0, o_shift = 0, o_shamt = 0, o_csucc = 0, o_succ = 0, o_squash = 0, o_meta = 0, o_masks = 0, o_base = 0, total_words = 0;
     u32 accept_abs = 0, accept_eod_abs = 0, limex_abs = 0;  // absolute bytecode offsets
     u32 nfa_flags = 0;
@@ -99,8 +100,7 @@ inline bool build(const DbView &d, Tables &t) {
             const u32 amt = rd8(lx, L.shiftAmount + k);
             if (!m) continue;
             if (!amt) loop0[w] |= m;
-            B[t.o_shift + n * G + w] = m;
-            B[t.o_shamt + w] |= (u64)amt << (8 * n);
+            B[t.o_shift + k * G + w] = m;
             n++;
         }
         base[3 * G + w] = n;
@@ -131,6 +131,7 @@ inline bool build(const DbView &d, Tables &t) {
         for (u32 c = 0; c < 256; c++) on &= B[t.o_reach + c * G + w];
         if (t.any_squash)
             for (u32 i = 0; i < t.n_exc; i++) on &= B[t.o_squash + i * G + w];
+        if (on) t.can_die = false;
         const u64 xm = B[t.o_masks + 4 * G + w];
         for (u64 x = on & xm; x; x &= x - 1) {
             const u32 bit = (u32)__builtin_ctzll(x);
