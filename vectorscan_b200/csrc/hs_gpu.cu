@@ -991,9 +991,15 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         cudaMemcpyAsync(im->d_lx, t.blob.data(), t.blob.size() * 8, cudaMemcpyHostToDevice, s->stream);
         im->device_bytes += t.blob.size() * 8;
         d.lx_abs = t.limex_abs;
-        im->lx = DevLimex{im->d_lx, t.G, t.n_exc, t.shift_count, t.any_squash ? 1u : 0u, t.can_die ? 1u : 0u, t.shift_amounts, t.o_reach,
-                          t.o_shift, t.o_shamt, t.o_csucc, t.o_succ, t.o_squash, t.o_meta, t.o_masks, t.o_base, t.total_words,
-                          t.accept_abs, t.accept_eod_abs, t.nfa_flags};
+        DevLimex &L = im->lx;
+        L = DevLimex{};
+        L.tab = im->d_lx; L.G = t.G; L.n_exc = t.n_exc; L.shift_count = t.shift_count;
+        L.any_squash = t.any_squash ? 1u : 0u; L.can_die = t.can_die ? 1u : 0u;
+        for (u32 k = 0; k < 8; k++) L.shmul[k] = 1u << ((u32)(t.shift_amounts >> (8 * k)) & 31u);
+        L.o_reach = t.o_reach; L.o_shift = t.o_shift; L.o_shamt = t.o_shamt; L.o_csucc = t.o_csucc; L.o_succ = t.o_succ;
+        L.o_squash = t.o_squash; L.o_meta = t.o_meta; L.o_masks = t.o_masks; L.o_base = t.o_base;
+        L.total_words = t.total_words; L.accept_abs = t.accept_abs; L.accept_eod_abs = t.accept_eod_abs;
+        L.nfa_flags = t.nfa_flags;
     } else {
         d.nood_msk = v.nood_msk;
         d.nood_cmp = v.nood_cmp;

@@ -120,7 +120,7 @@ inline int parse_single_outfix(DbView &d, std::string &why) {
     if (rd32(lx, limex::repeatCount)) { why = "LimEx bounded repeats are not supported yet"; return E_ARCH; }
     if (rd32(lx, L.shiftCount) > limex::MAX_SHIFT_COUNT) { why = "LimEx shift count out of range"; return E_INVALID; }
     for (u32 k = 0; k < rd32(lx, L.shiftCount); k++)
-        if (rd8(lx, L.shiftAmount + k) > 63) { why = "LimEx shift amount out of range"; return E_INVALID; }
+        if (rd8(lx, L.shiftAmount + k) > limex::MAX_SHIFT_AMOUNT) { why = "LimEx shift amount out of range"; return E_INVALID; }
     if (!lx_range(L.SIZE, (size_t)rd32(lx, limex::reachSize) * L.bytes) || rd32(lx, limex::reachSize) > 256) { why = "LimEx reach table truncated"; return E_INVALID; }
     for (u32 c = 0; c < 256; c++)
         if (rd8(lx, limex::reachMap + c) >= rd32(lx, limex::reachSize)) { why = "LimEx reach map out of range"; return E_INVALID; }

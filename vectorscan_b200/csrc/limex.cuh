@@ -24,7 +24,7 @@ constexpr int LX_STAGE = 64;  // staged match records per warp (report kernel)
 struct DevLimex {
     const u64 *tab;       // limex_dev::Tables blob in HBM
     u32 G, n_exc, shift_count, any_squash, can_die;
-    u64 shift_amounts;
+    u32 shmul[8];         // 1 << shiftAmount[k] (amounts <= MAX_SHIFT_AMOUNT = 16), constant-bank operands
     u32 o_reach, o_shift, o_shamt, o_csucc, o_succ, o_squash, o_meta, o_masks, o_base, total_words;
     u32 accept_abs, accept_eod_abs, nfa_flags;
 };
@@ -69,7 +69,9 @@ __device__ __forceinline__ void lx_accepts(const DevLxEvents &q, const u8 *bc, u
 }
 
 // One shift of the limited model, amount uniform over the launch: (s & shift[k]) << shiftAmount[k]
-#define LX_SHIFT(k) succ |= (s & my_shift[(k) * G]) << ((u32)(amts >> (8 * (k))) & 63u)
+// written as a multiplication by 2^amount (amounts are < 32): the two IMADs go to the fma pipe, which this loop
+// leaves idle, instead of two more SHFs on the alu pipe that bounds it
+#define LX_SHIFT(k) succ |= (s & my_shift[(k) * G]) * (u64)lx.shmul[k]
 
 template <int G>
 __global__ void __launch_bounds__(LX_THREADS, 4) k_limex(const DevDb db_, const DevLimex lx, const DevCorpus cp_,
@@ -88,7 +90,6 @@ __global__ void __launch_bounds__(LX_THREADS, 4) k_limex(const DevDb db_, const 
     const u32 gmask = (G == 32 ? FULL : ((1u << G) - 1u)) << gbase;
     const u64 excm = sh_masks[1 * G + w];        // exception states the device still has to look at
     u64 csucc = tab[lx.o_csucc + w];             // successors switched on at every step (limex_tables.h)
-    const u64 amts = lx.shift_amounts;           // uniform
     const u32 nshift = lx.shift_count;
     const bool any_squash = lx.any_squash != 0, can_die = lx.can_die != 0;
     const u64 *my_shift = tab + lx.o_shift + w, *my_reach = tab + lx.o_reach + w;
