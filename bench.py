@@ -31,7 +31,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 import numpy as np  # noqa: E402
 
-from vectorscan_b200 import litdb, workloads as W  # noqa: E402
+from vectorscan_b200 import litdb, shard, workloads as W  # noqa: E402
 
 ROT = 4  # resident batches per rank: 4 x 64 MiB = 256 MiB > 126 MB of L2
 
@@ -248,16 +248,14 @@ def main():
     # the only collective of the path: match counts (+ per-pattern histogram) over NCCL
     hist = torch.zeros(n_ids, dtype=torch.int64, device="cuda")
     gpu.lib().hs_gpu_histogram(sc.ptr, C.c_void_p(hist.data_ptr()), n_ids)
-    agg = torch.tensor([dev_ms, float(nbytes_scanned), float(nmatch), kern_ms, wall_s], dtype=torch.float64, device="cuda")
+    tot_matches, tot_bytes, hist = shard.reduce_counts(nmatch, nbytes_scanned, hist, device="cuda")
     if world > 1:
-        mx = agg.clone()
+        mx = torch.tensor([dev_ms, wall_s], dtype=torch.float64, device="cuda")
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-        dist.all_reduce(agg, op=dist.ReduceOp.SUM)
-        dist.all_reduce(hist, op=dist.ReduceOp.SUM)
-        max_dev_ms, max_wall = float(mx[0]), float(mx[4])
+        max_dev_ms, max_wall = float(mx[0]), float(mx[1])
     else:
         max_dev_ms, max_wall = dev_ms, wall_s
-    tot_bytes, tot_matches = float(agg[1]), float(agg[2])
+    tot_bytes, tot_matches = float(tot_bytes), float(tot_matches)
     value = tot_bytes / (max_dev_ms * 1e-3) / 1e9
 
     # ---- end to end through the C ABI with host buffers -----------------------------------------------

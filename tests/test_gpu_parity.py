@@ -244,3 +244,46 @@ def test_full_size_properties(ref, config):
         exp = ref_scan(ref, db, [bytes(flat[:8 << 20])])
         got = [(int(a), int(b), int(c)) for a, b, c in zip(m["buffer"], m["id"], m["to"]) if c <= (8 << 20)]
         assert got == exp
+
+
+def test_host_staging_paths_agree(ref):
+    """hs_gpu_scan_vector_ex takes buffers (a) scattered in pageable memory (gathered block by block into the
+    scratch's pinned staging), (b) back to back in one page-locked region (copied straight from it), (c) a mix of
+    both with empty buffers in between; more than one staging block (> 4096 buffers) in every case."""
+    rng = random.Random(77)
+    lits, flags, ids, _ = litgen.random_case(rng, None, 200, bytes(range(97, 107)), 8)
+    db = litdb.compile_lit_multi(lits, flags, ids)
+    bufs = []
+    for k in range(9000):
+        n = rng.choice([0, 1, 9, 60, 300, 1500])
+        bufs.append(bytes(rng.choice(b"abcdefghij") for _ in range(n)))
+    exp = ref_scan(ref, db, bufs)
+    sc = gpu.alloc_scratch(db)
+    as_list = lambda m: [(int(b), int(i), int(t)) for b, i, t in m]
+    assert as_list(gpu.scan_vector_ex(db, bufs, sc)) == exp                         # (a)
+    L = gpu.lib()
+    total = sum(len(b) for b in bufs)
+    hp = L.hs_gpu_host_alloc(total + 16)
+    assert hp
+    C.memmove(hp, b"".join(bufs), total)
+    n = len(bufs)
+    lens = (C.c_uint * n)(*[len(b) for b in bufs])
+    offs = np.concatenate([[0], np.cumsum([len(b) for b in bufs])]).astype(np.uint64)
+    mp, cnt = C.POINTER(gpu.Match)(), C.c_uint64()
+
+    def run(ptr_values):
+        ptrs = (C.c_char_p * n)()
+        C.memmove(ptrs, np.asarray(ptr_values, dtype=np.uint64).ctypes.data, n * 8)
+        assert L.hs_gpu_scan_vector_ex(db.ptr, ptrs, lens, n, 0, sc.ptr, C.byref(mp), C.byref(cnt)) == 0
+        return [(int(mp[k].buffer), int(mp[k].id), int(mp[k].to)) for k in range(cnt.value)]
+
+    pinned = np.uint64(hp) + offs[:-1]
+    assert run(pinned) == exp                                                       # (b)
+    keep = [C.create_string_buffer(b, len(b)) if len(b) else None for b in bufs]
+    mixed = pinned.copy()
+    for k in range(n):
+        if (k // 1000) % 2 and keep[k] is not None:
+            mixed[k] = C.addressof(keep[k])
+    assert run(mixed) == exp                                                        # (c)
+    L.hs_gpu_host_free(hp)
+    sc.close()

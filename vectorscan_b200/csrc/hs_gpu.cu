@@ -33,6 +33,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -1349,51 +1350,74 @@ struct InUseGuard {
     ~InUseGuard() { if (ok) s->in_use.store(0); }
 };
 
+// Host buffers -> the staging corpus in HBM.  The buffer list is walked in blocks (<= 4096 buffers or about
+// 8 MiB): a block whose buffers sit back to back in page-locked memory (hs_gpu_host_alloc) is copied straight
+// from the caller's memory, any other block is gathered into the scratch's pinned staging area first; either
+// way its cudaMemcpyAsync is queued as soon as the block has been walked, so the PCIe copy starts after a few
+// microseconds of host work and the rest of the walk (and any gathering) runs underneath it.
 hs_error_t stage_host_buffers(hs_gpu_scratch *s, const char *const *data, const unsigned int *length, unsigned count) {
     hs_gpu_corpus &cp = s->staging;
     if (!s->h_off.resize((size_t)count + 1)) return HS_NOMEM;
     u64 total = 0;
-    bool contiguous = true;
-    for (unsigned i = 0; i < count; i++) {
-        if (!data[i] && length[i]) return HS_INVALID;
-        s->h_off[i] = total;
-        if (i && length[i] && data[i] != data[i - 1] + length[i - 1]) contiguous = false;
-        total += length[i];
-    }
-    s->h_off[count] = total;
+    for (unsigned i = 0; i < count; i++) total += length[i];
     cp.total = total;
     cp.count = count;
     CU_OK(cp.text.reserve(FRONT_PAD + total + BACK_PAD));
     CU_OK(cp.off.reserve((size_t)count + 1));
-    const u8 *src = nullptr;
-    if (contiguous && count && total) {
-        // zero-copy source when the caller's buffers are one pinned region (hs_gpu_host_alloc)
-        const char *first = nullptr;
-        for (unsigned i = 0; i < count && !first; i++) if (length[i]) first = data[i];
-        cudaPointerAttributes at{};
-        if (first && cudaPointerGetAttributes(&at, first) == cudaSuccess && at.type == cudaMemoryTypeHost)
-            src = reinterpret_cast<const u8 *>(first);
-        else
-            cudaGetLastError();
-    }
-    if (!src && total) {
-        if (total > s->h_stage_cap) {
-            if (s->h_stage) cudaFreeHost(s->h_stage);
-            s->h_stage = nullptr;
-            s->h_stage_cap = 0;
-            const size_t want = total + total / 4 + 4096;
-            CU_OK(cudaHostAlloc((void **)&s->h_stage, want, cudaHostAllocDefault));
-            s->h_stage_cap = want;
-        }
-        for (unsigned i = 0; i < count; i++)
-            if (length[i]) std::memcpy(s->h_stage + s->h_off[i], data[i], length[i]);
-        src = s->h_stage;
-    }
     CU_OK(cudaEventRecord(s->ev[0], s->stream));
     // zero the pads (the front pad is read by look-behind, the back pad by the last rows)
     CU_OK(cudaMemsetAsync(cp.text.p, 0, FRONT_PAD, s->stream));
     CU_OK(cudaMemsetAsync(cp.text.p + FRONT_PAD + total, 0, BACK_PAD, s->stream));
-    if (total) CU_OK(cudaMemcpyAsync(cp.text.p + FRONT_PAD, src, total, cudaMemcpyHostToDevice, s->stream));
+    constexpr unsigned BLOCK_BUFS = 4096;
+    constexpr u64 BLOCK_BYTES = 8u << 20;
+    u64 pos = 0;
+    for (unsigned first = 0; first < count;) {
+        const u64 block_at = pos;
+        const char *run = nullptr;  // address the next non-empty buffer must have for the block to be one run
+        const char *run_begin = nullptr;
+        bool contiguous = true;
+        unsigned i = first;
+        for (; i < count && i - first < BLOCK_BUFS && pos - block_at < BLOCK_BYTES; i++) {
+            const unsigned len = length[i];
+            s->h_off[i] = pos;
+            if (len) {
+                const char *p = data[i];
+                if (!p) return HS_INVALID;
+                if (!run_begin) run_begin = p; else if (p != run) contiguous = false;
+                run = p + len;
+                pos += len;
+            }
+        }
+        const u64 bytes = pos - block_at;
+        if (bytes) {
+            const u8 *src = nullptr;
+            if (contiguous) {
+                cudaPointerAttributes at{};
+                if (cudaPointerGetAttributes(&at, run_begin) == cudaSuccess && at.type == cudaMemoryTypeHost)
+                    src = reinterpret_cast<const u8 *>(run_begin);
+                else
+                    cudaGetLastError();
+            }
+            if (!src) {
+                if (total > s->h_stage_cap) {
+                    // earlier blocks of this call never used the staging area (it would have been sized then)
+                    CU_OK(cudaStreamSynchronize(s->stream));
+                    if (s->h_stage) cudaFreeHost(s->h_stage);
+                    s->h_stage = nullptr;
+                    s->h_stage_cap = 0;
+                    const size_t want = total + total / 4 + 4096;
+                    CU_OK(cudaHostAlloc((void **)&s->h_stage, want, cudaHostAllocDefault));
+                    s->h_stage_cap = want;
+                }
+                for (unsigned k = first; k < i; k++)
+                    if (length[k]) std::memcpy(s->h_stage + s->h_off[k], data[k], length[k]);
+                src = s->h_stage + block_at;
+            }
+            CU_OK(cudaMemcpyAsync(cp.text.p + FRONT_PAD + block_at, src, bytes, cudaMemcpyHostToDevice, s->stream));
+        }
+        first = i;
+    }
+    s->h_off[count] = total;
     CU_OK(cudaMemcpyAsync(cp.off.p, s->h_off.data(), ((size_t)count + 1) * 8, cudaMemcpyHostToDevice, s->stream));
     // the position -> buffer index is built while the text is on its way
     if (!build_cell_first(s->h_off.data(), count, total, s->h_cell_first, cp.nstrips)) return HS_NOMEM;
@@ -1411,14 +1435,26 @@ hs_error_t scan_host_batch(const hs_database_t *db, const char *const *data, con
     rv = upload_database(s, db, &im);
     if (rv != HS_SUCCESS) return rv;
     *im_out = im;
+    static const bool trace = getenv("HS_GPU_TRACE") != nullptr;
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto us = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+        return std::chrono::duration<double, std::micro>(b - a).count();
+    };
+    const auto t0 = now();
     rv = stage_host_buffers(s, data, length, count);
     if (rv != HS_SUCCESS) return rv;
+    const auto t1 = now();
     cudaEvent_t h2d_begin = s->ev[0];
     rv = scan_device(s, im, s->staging);
     if (rv != HS_SUCCESS) return rv;
+    const auto t2 = now();
     // ev[1] was re-recorded by scan_device right after the copies were queued: h2d = ev0 -> ev1
     cudaEventElapsedTime(&s->stats.h2d_ms, h2d_begin, s->ev[1]);
-    return fetch_matches(s, im);
+    rv = fetch_matches(s, im);
+    if (trace)
+        fprintf(stderr, "hs_gpu trace: stage %.1f us, scan_device (incl. wait for H2D) %.1f us, fetch %.1f us\n",
+                us(t0, t1), us(t1, t2), us(t2, now()));
+    return rv;
 }
 
 hs_error_t validate_scan_args(const hs_database_t *db, hs_gpu_scratch *s) {
