@@ -1,11 +1,12 @@
 /* oracle/oracle_port.c -- TEST INFRASTRUCTURE ONLY.  Never imported, linked or executed by the product
  * path (vectorscan_b200/): only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may use it.
  *
- * Plain-C, sequential restatement of the reference's block-mode pure-literal scan path over the reference's
- * own bytecode.  PARITY PINNED: tests/test_oracle.py checks it against (a) the known-answer vectors of the
+ * Plain-C, sequential restatement of the reference's block-mode scan path -- pure-literal databases and
+ * single-outfix databases holding a LimEx NFA (see limex_scan below) -- over the reference's own bytecode.  PARITY PINNED: tests/test_oracle.py checks it against (a) the known-answer vectors of the
  * reference's unit tests (tests/golden/ref_unit_vectors.json, transcribed from unit/internal/fdr.cpp) and
  * (b) outputs of the unmodified reference runtime compiled from /root/reference (oracle/_ref) on seeded
- * random databases/inputs (tests/golden/ref_runtime_cases.json and live comparison where _ref exists).
+ * random databases/inputs (tests/golden/ref_runtime_cases.json, tests/golden/ref_limex_cases.json and live
+ * comparison where _ref exists).
  *
  * Each function cites the reference code it follows (paths under /root/reference/src):
  *   op_scan            hs_scan                      runtime.c:316-475  (gates, engine switch)
@@ -246,14 +247,120 @@ static int hwlm_exec(struct scan_state *s, const u8 *hwlm) {
     return 0;
 }
 
-/* hs_scan for block-mode pure-literal databases.  `db` = in-memory hs_database_t. */
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Single-outfix databases whose engine is a LimEx NFA.
+ *   limex_scan         soleOutfixBlockExec          runtime.c:246-279   (START, TOP at 0, END at len; EOD accepts)
+ *                      nfaExecLimEx*_Q / STREAM_FN  nfa/limex_runtime_impl.h:620-714, 246-367
+ *   limex_step         NFA_EXEC_GET_LIM_SUCC        nfa/limex_runtime_impl.h:164-199 (shifts, per 64-bit lane)
+ *                      processExceptional           nfa/limex_exceptional.h:92-204,212-368 (reports at offset i,
+ *                                                   squash on succ, successors OR-ed in afterwards)
+ *   limex_accepts      moProcessAccepts / TESTEOD   nfa/limex_common_impl.h:116-213
+ *   reports            limexRunReports -> roseReportAdaptor -> roseRunProgram    nfa/limex_runtime.h:90-117,
+ *                                                   rose/match.c:611-633
+ * State vectors are handled as arrays of 64-bit words (LimEx32: one word whose upper half stays clear because
+ * every reach row has it clear).  Acceleration and the exception cache are shortcuts without effect on results. */
+enum {
+    R_NFA_INFO = 236, NI_NFA_OFF = 0, NFA_FLAGS = 0, NFA_TYPE = 8, NFA_RACCEL = 9, NFA_SIZE = 64, NFA_ACCEPTS_EOD = 1,
+    LX_REACH_SIZE = 256, LX_ACCEPT_COUNT = 276, LX_ACCEPT_OFF = 280, LX_ACCEPT_EOD_COUNT = 284, LX_ACCEPT_EOD_OFF = 288,
+    LX_EXC_COUNT = 292, LX_EXC_OFF = 296, LX_REPEAT_COUNT = 300, LX_HEAD = 332
+};
+struct lx_layout { u32 bytes, words, init, accept, accept_eod, exc_mask, shift, shift_count, shift_amount, size, e_size; };
+static struct lx_layout lx_layout_of(u32 type) {
+    static const u32 bits_of[6] = {32, 64, 128, 256, 384, 512}, align_of[6] = {4, 8, 16, 32, 16, 64};
+    struct lx_layout l;
+    u32 S = bits_of[type] / 8, A = align_of[type];
+    l.bytes = S; l.words = (S + 7) / 8;
+    l.init = (LX_HEAD + A - 1) / A * A;            /* twelve state-sized masks follow the head, then shift[8] */
+    l.accept = l.init + 2 * S; l.accept_eod = l.init + 3 * S; l.exc_mask = l.init + 9 * S;
+    l.shift = l.init + 12 * S; l.shift_count = l.shift + 8 * S; l.shift_amount = l.shift_count + 4;
+    l.size = (l.shift_amount + 8 + 63) / 64 * 64 + 192;  /* three m512 exception-extraction masks close the struct */
+    l.e_size = (2 * S + 10 + A - 1) / A * A;       /* NFAException: squash, successors, reports, repeatOffset, 2 x u8 */
+    return l;
+}
+static void lx_load(u64 *dst, const u8 *src, const struct lx_layout *l) {
+    memset(dst, 0, 64);
+    memcpy(dst, src, l->bytes);
+}
+static u32 lx_rank(const u64 *mask, u32 bit) { /* number of mask bits below `bit` */
+    u32 n = 0;
+    for (u32 w = 0; w < bit / 64; w++) n += (u32)__builtin_popcountll(mask[w]);
+    return n + (u32)__builtin_popcountll(mask[bit / 64] & ((1ull << (bit % 64)) - 1));
+}
+static int lx_reports(struct scan_state *s, const u8 *limex, u32 list, u64 offset) {
+    for (const u8 *p = limex + list; rd32(p) != 0xffffffffu; p += 4)
+        if (run_program(s, rd32(p), offset) < 0) return -1;
+    return 0;
+}
+static int lx_accepts(struct scan_state *s, const u8 *limex, const struct lx_layout *l, const u64 *state, u32 mask_at,
+                      u32 table_off, u64 offset) {
+    u64 mask[8];
+    lx_load(mask, limex + mask_at, l);
+    for (u32 b = 0; b < l->bytes * 8; b++) {
+        if (!((state[b / 64] & mask[b / 64]) >> (b % 64) & 1)) continue;
+        const u8 *a = limex + table_off + 12 * (size_t)lx_rank(mask, b); /* struct NFAAccept {u8 single; u32 reports; u32 squash} */
+        if (a[0]) { if (run_program(s, rd32(a + 4), offset) < 0) return -1; }
+        else if (lx_reports(s, limex, rd32(a + 4), offset) < 0) return -1;
+    }
+    return 0;
+}
+
+static int limex_scan(struct scan_state *s, const u8 *nfa) {
+    u32 type = nfa[NFA_TYPE];
+    if (type > 5 || nfa[NFA_RACCEL]) { s->error = 1; return -1; }
+    const u8 *limex = nfa + NFA_SIZE;
+    if (rd32(limex + LX_REPEAT_COUNT)) { s->error = 1; return -1; } /* bounded repeats: outside the restated path */
+    const struct lx_layout l = lx_layout_of(type);
+    const u8 *reach = limex + l.size, *exc = limex + rd32(limex + LX_EXC_OFF);
+    u32 nshift = rd32(limex + l.shift_count);
+    u64 st[8], excm[8], shm[8][8];
+    lx_load(st, limex + l.init, &l);                       /* MQE_TOP at offset 0: s = init */
+    lx_load(excm, limex + l.exc_mask, &l);
+    for (u32 k = 0; k < nshift; k++) lx_load(shm[k], limex + l.shift + (size_t)k * l.bytes, &l);
+    const u64 lane_mask = l.bytes == 4 ? 0xffffffffull : ~0ull;
+    for (u32 i = 0; i < s->len; i++) {
+        u64 succ[8] = {0}, local[8] = {0}, any = 0;
+        for (u32 w = 0; w < l.words; w++) any |= st[w];
+        if (!any) return 0;                                  /* nothing on: stays that way */
+        for (u32 k = 0; k < nshift; k++)
+            for (u32 w = 0; w < l.words; w++)
+                succ[w] |= ((st[w] & shm[k][w]) << limex[l.shift_amount + k]) & lane_mask;
+        for (u32 b = 0; b < l.bytes * 8; b++) {              /* exceptions, lowest state first */
+            if (!((st[b / 64] & excm[b / 64]) >> (b % 64) & 1)) continue;
+            const u8 *e = exc + (size_t)lx_rank(excm, b) * l.e_size;
+            if (e[2 * l.bytes + 9]) { s->error = 1; return -1; }       /* trigger: repeats only */
+            u32 reports = rd32(e + 2 * l.bytes);
+            if (reports != 0xffffffffu && lx_reports(s, limex, reports, i) < 0) return -1;
+            u64 t[8];
+            lx_load(t, e + l.bytes, &l);
+            for (u32 w = 0; w < l.words; w++) local[w] |= t[w];
+            u8 sq = e[2 * l.bytes + 8];
+            if (sq == 1 || sq == 3) {                        /* LIMEX_SQUASH_CYCLIC / _REPORT: on succ, not local */
+                lx_load(t, e, &l);
+                for (u32 w = 0; w < l.words; w++) succ[w] &= t[w];
+            }
+        }
+        u64 r[8];
+        lx_load(r, reach + (size_t)limex[s->buf[i]] * l.bytes, &l);  /* reach[reachMap[c]] */
+        for (u32 w = 0; w < l.words; w++) st[w] = (succ[w] | local[w]) & r[w];
+    }
+    if (rd32(limex + LX_ACCEPT_COUNT) &&
+        lx_accepts(s, limex, &l, st, l.accept, rd32(limex + LX_ACCEPT_OFF), s->len) < 0) return -1;
+    u64 any = 0;
+    for (u32 w = 0; w < l.words; w++) any |= st[w];
+    if (any && (rd32(nfa + NFA_FLAGS) & NFA_ACCEPTS_EOD) && rd32(limex + LX_ACCEPT_EOD_COUNT) &&
+        lx_accepts(s, limex, &l, st, l.accept_eod, rd32(limex + LX_ACCEPT_EOD_OFF), s->len) < 0) return -1;
+    return 0;
+}
+
+/* hs_scan for block-mode pure-literal and single-outfix (LimEx) databases.  `db` = in-memory hs_database_t. */
 int op_scan(const void *db, const char *data, unsigned length, op_match_cb cb, void *ctx) {
     const u8 *d = (const u8 *)db;
     if (!d || !data || rd32(d + DB_MAGIC_OFF) != 0xdbdbdbdbu) return HS_INVALID;
     if (rd32(d + DB_VERSION_OFF) != ((5u << 24) | (4u << 16) | (11u << 8))) return HS_DB_VERSION_ERROR;
     const u8 *rose = d + rd32(d + DB_BYTECODE_OFF);
     if (rd32(rose + R_MODE) != 1) return HS_DB_MODE_ERROR;
-    if (rose[R_RUNTIME_IMPL] != 1 || rose[R_HAS_SOM] || rd32(rose + R_CKEY_COUNT) || rd32(rose + R_BOUNDARY) ||
+    if ((rose[R_RUNTIME_IMPL] != 1 && rose[R_RUNTIME_IMPL] != 2) || rose[R_HAS_SOM] || rd32(rose + R_CKEY_COUNT) || rd32(rose + R_BOUNDARY) ||
         rd32(rose + R_BOUNDARY + 4) || rd32(rose + R_BOUNDARY + 8))
         return HS_ARCH_ERROR; /* outside the restated path */
     if (rd32(rose + R_MIN_WIDTH) > length) return HS_SUCCESS;
@@ -268,7 +375,8 @@ int op_scan(const void *db, const char *data, unsigned length, op_match_cb cb, v
     s.exhausted = calloc(s.ekeys / 8 + 2, 1);
     s.dedupe = calloc(s.dkeys / 8 + 2, 1);
     s.dedupe_offset = ~0ull;
-    hwlm_exec(&s, rose + rd32(rose + R_FMATCHER));
+    if (rose[R_RUNTIME_IMPL] == 2) limex_scan(&s, rose + rd32(rose + rd32(rose + R_NFA_INFO) + NI_NFA_OFF));
+    else hwlm_exec(&s, rose + rd32(rose + R_FMATCHER));
     free(s.exhausted); free(s.dedupe);
     if (s.error) return HS_UNKNOWN_ERROR;
     return s.terminated ? HS_SCAN_TERMINATED : HS_SUCCESS;

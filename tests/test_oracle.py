@@ -133,3 +133,43 @@ def test_c_brute_force_agrees_with_python():
     flags = [f & 1 for f in flags]
     got = sorted(set(oracle_port.brute_force(lits, flags, ids, text)))
     assert got == litgen.brute_force(lits, flags, ids, text)
+
+
+# ---- LimEx (single-outfix databases): the C restatement's limex_scan ---------------------------------------------
+def test_limex_port_vs_recorded_reference_cases():
+    import json
+    import os
+    from vectorscan_b200 import litdb
+    with open(os.path.join(os.path.dirname(__file__), "golden", "ref_limex_cases.json")) as f:
+        cases = json.load(f)
+    n = 0
+    for c in cases:
+        db = litdb.compile_regex_multi([e.encode("latin-1") for e in c["exprs"]], c["flags"], c["ids"])
+        for t, exp in zip(c["texts"], c["expect"]):
+            rv, got = oracle_port.scan(db, bytes.fromhex(t))
+            assert rv == 0 and sorted(got, key=lambda x: (x[1], x[0])) == [tuple(x) for x in exp], c["seed"]
+            n += len(exp)
+    assert n > 500
+
+
+def test_limex_port_vs_live_reference_runtime(ref):
+    import random
+    import regen
+    from vectorscan_b200 import litdb
+    done = 0
+    for seed in range(60):
+        rng = random.Random(9000 + seed)
+        ex, fl, ids, smp = regen.random_set(rng, rng.randint(1, 16), True)
+        try:
+            db = litdb.compile_regex_multi(ex, fl, ids)
+        except litdb.CompileError:
+            continue
+        rdb = ref.deserialize(db.serialize())
+        rs = ref.alloc_scratch(rdb)
+        for n in (0, 1, 33, 500, 3000):
+            t = regen.random_text(rng, ex, n, smp)
+            rv, exp = ref.scan(rdb, rs, t)
+            rv2, got = oracle_port.scan(db, t)
+            assert rv == rv2 == 0 and got == exp, (seed, n)   # same callback ORDER too (ascending state index)
+        done += 1
+    assert done > 20
