@@ -60,6 +60,17 @@ int hsb_compile_lit_multi(const char *const *expressions, const unsigned *flags,
  * the empty string and when the set needs more than 512 NFA states. */
 int hsb_compile_regex_multi(const char *const *expressions, const unsigned *flags, const unsigned *ids,
                             unsigned elements, unsigned mode, hs_database_t **db, char **error);
+/* Same front end, engine chosen by the caller.  HSB_REGEX_ENGINE_MCCLELLAN determinises the automaton (subset
+ * construction + minimisation) and lays it out as the reference's McClellan DFA (src/nfa/mcclellan_internal.h;
+ * 8-bit table for <= 256 states, 16-bit otherwise, at most 16 383 states) -- the engine the reference compiler
+ * prefers for outfixes (src/grey.cpp:119).  ..._SHERMAN additionally stores states close to the start state or
+ * to their parent as 32-byte Sherman states (mcclellancompile.cpp:1020-1200), 16-bit engines only. */
+#define HSB_REGEX_ENGINE_LIMEX 0u
+#define HSB_REGEX_ENGINE_MCCLELLAN 1u
+#define HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN 2u
+int hsb_compile_regex_multi_ex(const char *const *expressions, const unsigned *flags, const unsigned *ids,
+                               unsigned elements, unsigned mode, unsigned engine, hs_database_t **db,
+                               char **error);
 void hsb_free_database(hs_database_t *db);
 void hsb_free_error(char *error);
 

@@ -18,6 +18,7 @@
 #include "nfa/nfa_internal.h"
 #include "nfa/limex_internal.h"
 #include "nfa/accel.h"
+#include "nfa/mcclellan_internal.h"
 #include "util/multibit_internal.h"
 #include "hs_compile.h"
 
@@ -230,6 +231,18 @@ int main(void) {
  SZ(struct NFAAccept); OF(struct NFAAccept, single_report); OF(struct NFAAccept, reports); OF(struct NFAAccept, squash);
  SZ(struct NfaInfo); OF(struct NfaInfo, nfaOffset); OF(struct NfaInfo, stateOffset); OF(struct NfaInfo, fullStateOffset); 
  OF(struct NfaInfo, no_retrigger); OF(struct NfaInfo, in_sbmatcher); OF(struct NfaInfo, eod);
+ /* McClellan DFA */
+ VAL(MCCLELLAN_NFA_8); VAL(MCCLELLAN_NFA_16); VAL(ACCEPT_FLAG); VAL(ACCEL_FLAG); VAL(STATE_MASK); VAL(MCCLELLAN_FLAG_SINGLE);
+ VAL(SHERMAN_STATE); VAL(SHERMAN_FIXED_SIZE); VAL(SHERMAN_LEN_OFFSET); VAL(SHERMAN_DADDY_OFFSET); VAL(SHERMAN_CHARS_OFFSET);
+ SZ(struct mcclellan); OF(struct mcclellan, state_count); OF(struct mcclellan, length); OF(struct mcclellan, start_anchored);
+ OF(struct mcclellan, start_floating); OF(struct mcclellan, aux_offset); OF(struct mcclellan, sherman_offset);
+ OF(struct mcclellan, sherman_end); OF(struct mcclellan, accel_limit_8); OF(struct mcclellan, accept_limit_8);
+ OF(struct mcclellan, sherman_limit); OF(struct mcclellan, wide_limit); OF(struct mcclellan, alphaShift);
+ OF(struct mcclellan, flags); OF(struct mcclellan, has_accel); OF(struct mcclellan, has_wide); OF(struct mcclellan, remap);
+ OF(struct mcclellan, arb_report); OF(struct mcclellan, accel_offset); OF(struct mcclellan, haig_offset);
+ OF(struct mcclellan, wide_offset);
+ SZ(struct mstate_aux); OF(struct mstate_aux, accept); OF(struct mstate_aux, accept_eod); OF(struct mstate_aux, top);
+ OF(struct mstate_aux, accel_offset);
 
 
     return 0;

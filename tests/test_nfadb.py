@@ -56,3 +56,39 @@ def test_refusals():
             litdb.compile_regex_multi([bad])
     with pytest.raises(litdb.CompileError):
         litdb.compile_regex_multi([b"a[b-z]{600}c"])
+
+
+# ---- McClellan DFA engine (mcclellan_internal.h), same acceptance: the unmodified runtime must scan it ----------
+@pytest.mark.parametrize("engine", [litdb.ENGINE_MCCLELLAN, litdb.ENGINE_MCCLELLAN_SHERMAN])
+@pytest.mark.parametrize("seed", range(16))
+def test_mcclellan_random_sets_match_brute_force(ref, seed, engine):
+    rng = random.Random(1000 + seed)
+    ex, fl, ids, smp = regen.random_set(rng, rng.randint(1, 6), True)
+    try:
+        db = litdb.compile_regex_multi(ex, fl, ids, engine=engine)
+    except litdb.CompileError as e:
+        assert "too large" in str(e)
+        return
+    assert db.outfix_engine_type() in (6, 7)
+    texts = [regen.random_text(rng, ex, 140, smp) for _ in range(3)] + [b""]
+    got = _scan_ref(ref, db, texts)
+    for t, g in zip(texts, got):
+        assert g == regen.brute_force(ex, fl, ids, t), (ex, fl, t)
+
+
+@pytest.mark.parametrize("engine", [litdb.ENGINE_MCCLELLAN, litdb.ENGINE_MCCLELLAN_SHERMAN])
+def test_mcclellan_8_and_16_bit(ref, engine):
+    """<= 256 states -> McClellan8 (NFA.type 6), more -> McClellan16 (type 7); both accepted by nfa_api_dispatch.c."""
+    small = [b"abc", b"^GET /[^ ]*\\.php", b"x[0-9]{3}y"]
+    big = [b"passwd\\s+[A-Za-z0-9_]{4,9}=", b"(login|admin)[^&]*&id=", b"User-Agent: [^\\r\\n]{8}", b"select.{1,12}from"]
+    for ex, want in ((small, 6), (big, 7)):
+        fl = [1 if k % 2 else 0 for k in range(len(ex))]
+        ids = [10 + k for k in range(len(ex))]
+        db = litdb.compile_regex_multi(ex, fl, ids, engine=engine)
+        assert db.outfix_engine_type() == want
+        rng = random.Random(want)
+        texts = [b"GET /a/b.php x123y abc PASSWD  user_1= login=1&id= select a,b from User-Agent: abcdefghij"] + \
+                [regen.random_text(rng, ex, 200) for _ in range(4)]
+        got = _scan_ref(ref, db, texts)
+        for t, g in zip(texts, got):
+            assert g == regen.brute_force(ex, fl, ids, t), (ex, t)

@@ -225,11 +225,26 @@ constexpr size_t flags = 0, length = 4, type = 8, rAccelType = 9, rAccelOffset =
                  rAccelData = 12, queueIndex = 16, nPositions = 20, scratchStateSize = 24, streamStateSize = 28,
                  maxWidth = 32, minWidth = 36, maxOffset = 40, SIZE = 64;
 constexpr u8 LIMEX_32 = 0, LIMEX_64 = 1, LIMEX_128 = 2, LIMEX_256 = 3, LIMEX_384 = 4, LIMEX_512 = 5;
+constexpr u8 MCCLELLAN_8 = 6, MCCLELLAN_16 = 7;
 constexpr u32 ACCEPTS_EOD = 1, ZOMBIE = 2;
 }
 namespace nfainfo {  // struct NfaInfo
 constexpr size_t nfaOffset = 0, stateOffset = 4, fullStateOffset = 8, ekeyListOffset = 12, no_retrigger = 16,
                  in_sbmatcher = 17, eod = 18, SIZE = 20;
+}
+// struct mcclellan (src/nfa/mcclellan_internal.h:77-101) follows struct NFA; the successor table follows it
+// (u8 or u16 per entry, row = state << alphaShift, column = remap[byte]); then mstate_aux[state], report lists
+// {u32 count, ReportID[]}, accel structures and (16-bit only) 32-byte Sherman states.
+namespace mcclellan {
+constexpr size_t state_count = 0, length = 4, start_anchored = 8, start_floating = 10, aux_offset = 12,
+                 sherman_offset = 16, sherman_end = 20, accel_limit_8 = 24, accept_limit_8 = 26, sherman_limit = 28,
+                 wide_limit = 30, alphaShift = 32, flags = 33, has_accel = 34, has_wide = 35, remap = 36,
+                 arb_report = 292, accel_offset = 296, haig_offset = 300, wide_offset = 304, SIZE = 308;
+constexpr u32 FLAG_SINGLE = 1;
+constexpr u32 ACCEPT_FLAG = 0x8000, ACCEL_FLAG = 0x4000, STATE_MASK = 0x3fff;
+constexpr u32 SHERMAN_STATE = 1, SHERMAN_FIXED_SIZE = 32, SHERMAN_LEN_OFFSET = 1, SHERMAN_DADDY_OFFSET = 2,
+              SHERMAN_CHARS_OFFSET = 4, MAX_SHERMAN_LIST_LEN = 9;
+namespace aux { constexpr size_t accept = 0, accept_eod = 4, top = 8, accel_offset = 12, SIZE = 16; }
 }
 namespace nfaaccept {  // struct NFAAccept
 constexpr size_t single_report = 0, reports = 4, squash = 8, SIZE = 12;

@@ -32,7 +32,9 @@
 #include <bitset>
 #include <cstdlib>
 #include <map>
+#include <set>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 namespace {
@@ -363,7 +365,7 @@ struct Glushkov {
 
 namespace hsb_nfadb {
 struct Pattern { std::string expr; unsigned flags; unsigned id; };
-int build(const std::vector<Pattern> &pats, std::vector<hsb::u8> &image, std::string &err);
+int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<hsb::u8> &image, std::string &err);
 }
 
 namespace {
@@ -384,11 +386,279 @@ struct Automaton {
     u32 min_width = ~0u;
 };
 
+
+// ---- determinisation: Automaton -> DFA (the McClellan engine, src/nfa/mcclellan_internal.h) -----------------
+// Symbols are the byte classes of the reach table (bytes no state tells apart share a column).  State 0 is the
+// dead state (empty subset), as in the reference (mcclellancompile.cpp:558 "dead is always 0").
+struct Dfa {
+    u32 n_sym = 0;
+    std::vector<std::vector<u32>> next;        // [state][symbol]
+    std::vector<std::vector<u32>> reports;     // [state] sorted pattern indices accepted on entering the state
+    u32 start_anchored = 0, start_floating = 0;
+};
+
+struct StateSetHash {
+    size_t operator()(const StateSet &s) const { return std::hash<StateSet>()(s); }
+};
+
+bool determinise(const Automaton &am, const std::vector<StateSet> &reach_rows, Dfa &d, u32 max_states) {
+    d.n_sym = (u32)reach_rows.size();
+    std::unordered_map<StateSet, u32, StateSetHash> id_of;
+    std::vector<StateSet> subset;
+    auto intern = [&](const StateSet &ss) -> u32 {
+        auto it = id_of.find(ss);
+        if (it != id_of.end()) return it->second;
+        const u32 id = (u32)subset.size();
+        id_of.emplace(ss, id);
+        subset.push_back(ss);
+        return id;
+    };
+    intern(StateSet());  // dead
+    d.start_anchored = intern(am.init);
+    d.start_floating = intern(am.init_ds);
+    for (u32 cur = 0; cur < subset.size(); cur++) {
+        if (subset.size() > max_states) return false;
+        const StateSet ss = subset[cur];
+        StateSet all_succ;
+        for (u32 s = 0; s < am.n_states; s++) if (ss.test(s)) all_succ |= am.succ[s];
+        std::vector<u32> row(d.n_sym, 0);
+        for (u32 k = 0; k < d.n_sym; k++) row[k] = intern(all_succ & reach_rows[k]);
+        d.next.push_back(std::move(row));
+    }
+    if (subset.size() > max_states) return false;
+    d.reports.assign(subset.size(), {});
+    for (u32 i = 0; i < subset.size(); i++) {
+        std::set<u32> r;
+        for (u32 s = 0; s < am.n_states; s++) if (subset[i].test(s) && am.report_of[s]) r.insert(am.report_of[s] - 1);
+        d.reports[i].assign(r.begin(), r.end());
+    }
+    return true;
+}
+
+// Moore partition refinement; keeps state 0 dead and renumbers in discovery order from the start states.
+void minimise(Dfa &d) {
+    const u32 n = (u32)d.next.size();
+    std::vector<u32> cls(n);
+    {
+        std::map<std::vector<u32>, u32> by_rep;
+        for (u32 i = 0; i < n; i++) {
+            auto it = by_rep.find(d.reports[i]);
+            if (it == by_rep.end()) it = by_rep.emplace(d.reports[i], (u32)by_rep.size()).first;
+            cls[i] = it->second;
+        }
+    }
+    for (;;) {
+        std::map<std::vector<u32>, u32> sig_id;
+        std::vector<u32> ncls(n);
+        std::vector<u32> sig(d.n_sym + 1);
+        for (u32 i = 0; i < n; i++) {
+            sig[0] = cls[i];
+            for (u32 k = 0; k < d.n_sym; k++) sig[k + 1] = cls[d.next[i][k]];
+            auto it = sig_id.find(sig);
+            if (it == sig_id.end()) it = sig_id.emplace(sig, (u32)sig_id.size()).first;
+            ncls[i] = it->second;
+        }
+        u32 before = 0, after = (u32)sig_id.size();
+        { std::set<u32> u(cls.begin(), cls.end()); before = (u32)u.size(); }
+        cls.swap(ncls);
+        if (after == before) break;
+    }
+    // renumber: dead class first, then breadth-first from the start states
+    std::vector<u32> rep_of_class, new_id;
+    {
+        u32 ncls = 0;
+        for (u32 c : cls) ncls = std::max(ncls, c + 1);
+        rep_of_class.assign(ncls, ~0u);
+        for (u32 i = 0; i < n; i++) if (rep_of_class[cls[i]] == ~0u) rep_of_class[cls[i]] = i;
+        new_id.assign(ncls, ~0u);
+    }
+    std::vector<u32> order;
+    auto visit = [&](u32 c) { if (new_id[c] == ~0u) { new_id[c] = (u32)order.size(); order.push_back(c); } };
+    visit(cls[0]);
+    visit(cls[d.start_anchored]);
+    visit(cls[d.start_floating]);
+    for (u32 q = 0; q < order.size(); q++) {
+        const u32 r = rep_of_class[order[q]];
+        for (u32 k = 0; k < d.n_sym; k++) visit(cls[d.next[r][k]]);
+    }
+    Dfa m;
+    m.n_sym = d.n_sym;
+    m.next.resize(order.size());
+    m.reports.resize(order.size());
+    for (u32 q = 0; q < order.size(); q++) {
+        const u32 r = rep_of_class[order[q]];
+        m.next[q].resize(d.n_sym);
+        for (u32 k = 0; k < d.n_sym; k++) m.next[q][k] = new_id[cls[d.next[r][k]]];
+        m.reports[q] = d.reports[r];
+    }
+    m.start_anchored = new_id[cls[d.start_anchored]];
+    m.start_floating = new_id[cls[d.start_floating]];
+    d = std::move(m);
+}
+
+
+// Lay the DFA out as the reference's McClellan engine (struct NFA + struct mcclellan + successor table +
+// mstate_aux[] + report lists [+ Sherman states]), following mcclellancompile.cpp:611-880 (16-bit) and :924-1000
+// (8-bit).  ReportIDs are Rose report-program offsets, as for every outfix engine (roseReportAdaptor).
+// `sherman`: compress states that differ from the start state or from their discovery parent in at most
+// MAX_SHERMAN_LIST_LEN symbols into 32-byte Sherman states (16-bit engines only).
+int emit_mcclellan(const Dfa &d, const u8 *reach_map, const std::vector<u32> &program_of, bool sherman,
+                   u32 min_width, Buf &eng, u32 &state_bytes, std::string &err) {
+    namespace mc = mcclellan;
+    const u32 n = (u32)d.next.size();
+    const u32 alpha = d.n_sym + 1;  // + TOP, the last symbol (never produced by remap)
+    u32 as = 0;
+    while ((1u << as) < alpha) as++;
+    const bool wide16 = n > 256;
+    if (n - 1 > mc::STATE_MASK) { err = "DFA too large for a McClellan engine (" + std::to_string(n) + " states)"; return HSB_LIT_COMPILER_ERROR; }
+    state_bytes = wide16 ? 2 : 1;
+    // ---- implementation ids ----
+    std::vector<u32> impl(n, 0);
+    std::vector<u32> daddy(n, 0);
+    std::vector<u8> is_sherman(n, 0);
+    u32 accel_limit_8 = 0, accept_limit_8 = 0, sherman_limit = 0, n_real = n;
+    if (!wide16) {
+        u32 j = 1;
+        for (u32 i = 1; i < n; i++) if (d.reports[i].empty()) impl[i] = j++;
+        accel_limit_8 = accept_limit_8 = j;  // no accel states
+        for (u32 i = 1; i < n; i++) if (!d.reports[i].empty()) impl[i] = j++;
+    } else {
+        if (sherman) {
+            std::vector<u32> parent(n, 0);
+            std::vector<u8> seen(n, 0);
+            seen[0] = 1;
+            for (u32 st : {d.start_anchored, d.start_floating}) seen[st] = 1;
+            for (u32 q = 0; q < n; q++)  // ids are already in discovery order (minimise)
+                for (u32 k = 0; k < d.n_sym; k++) { const u32 t = d.next[q][k]; if (!seen[t]) { seen[t] = 1; parent[t] = q; } }
+            for (u32 i = 1; i < n; i++) {
+                if (i == d.start_anchored || i == d.start_floating) continue;
+                for (u32 cand : {d.start_floating ? d.start_floating : d.start_anchored, parent[i]}) {
+                    if (!cand || cand == i || is_sherman[cand]) continue;
+                    u32 diff = 0;
+                    for (u32 k = 0; k < d.n_sym; k++) diff += d.next[i][k] != d.next[cand][k];
+                    if (diff <= mc::MAX_SHERMAN_LIST_LEN) { is_sherman[i] = 1; daddy[i] = cand; break; }
+                }
+            }
+            // a daddy must stay a normal state: candidates were checked against is_sherman at the time, and a later
+            // state may have turned its daddy's daddy... daddies are never Sherman by the check above, but a state
+            // chosen as daddy earlier may itself become Sherman later -- undo those
+            for (u32 i = 1; i < n; i++) if (is_sherman[i] && is_sherman[daddy[i]]) is_sherman[i] = 0;
+        }
+        u32 j = 1;
+        for (u32 i = 1; i < n; i++) if (!is_sherman[i]) impl[i] = j++;
+        sherman_limit = n_real = j;
+        for (u32 i = 1; i < n; i++) if (is_sherman[i]) impl[i] = j++;
+    }
+    // ---- report lists ----
+    std::map<std::vector<u32>, u32> list_id;  // sorted program offsets -> index
+    std::vector<std::vector<u32>> lists;
+    std::vector<u32> list_of(n, ~0u);
+    std::set<u32> all_reports;
+    for (u32 i = 0; i < n; i++) {
+        if (d.reports[i].empty()) continue;
+        std::set<u32> ps;
+        for (u32 pi : d.reports[i]) ps.insert(program_of[pi]);
+        std::vector<u32> l(ps.begin(), ps.end());
+        all_reports.insert(l.begin(), l.end());
+        auto it = list_id.find(l);
+        if (it == list_id.end()) { it = list_id.emplace(l, (u32)lists.size()).first; lists.push_back(l); }
+        list_of[i] = it->second;
+    }
+    const bool single = all_reports.size() == 1;
+    // ---- sizes (mcclellancompile.cpp:637-652 / :934-940) ----
+    const size_t ent = wide16 ? 2 : 1;
+    const size_t tran_size = ((size_t)1 << as) * ent * n_real;
+    const size_t aux_size = mc::aux::SIZE * (size_t)n;
+    const size_t aux_offset = round_up(nfa::SIZE + mc::SIZE + tran_size, 16);
+    size_t rl_size = 0;
+    for (auto &l : lists) rl_size += 4 + 4 * l.size();
+    const size_t accel_offset = round_up(aux_offset + aux_size + rl_size, 32);
+    const size_t sherman_offset = round_up(accel_offset, 16);
+    const size_t sherman_size = wide16 ? (size_t)mc::SHERMAN_FIXED_SIZE * (n - n_real) : 0;
+    const size_t total = round_up(sherman_offset + sherman_size, 16);
+    eng.grow(total);
+    eng.align(CACHELINE);
+    u8 *nh = eng.at(0), *m = eng.at(nfa::SIZE);
+    wr32(nh, nfa::flags, 0);
+    wr32(nh, nfa::length, (u32)eng.size());
+    wr8(nh, nfa::type, wide16 ? nfa::MCCLELLAN_16 : nfa::MCCLELLAN_8);
+    wr32(nh, nfa::queueIndex, 0);
+    wr32(nh, nfa::nPositions, n);
+    wr32(nh, nfa::scratchStateSize, state_bytes);
+    wr32(nh, nfa::streamStateSize, state_bytes);
+    wr32(nh, nfa::maxWidth, 0);
+    wr32(nh, nfa::minWidth, min_width);
+    wr16(m, mc::state_count, (u16)n);
+    wr32(m, mc::length, (u32)eng.size());
+    wr16(m, mc::start_anchored, (u16)impl[d.start_anchored]);
+    wr16(m, mc::start_floating, (u16)impl[d.start_floating]);
+    wr32(m, mc::aux_offset, (u32)aux_offset);
+    wr32(m, mc::sherman_offset, wide16 ? (u32)sherman_offset : 0);
+    wr32(m, mc::sherman_end, wide16 ? (u32)total : 0);
+    wr16(m, mc::accel_limit_8, (u16)accel_limit_8);
+    wr16(m, mc::accept_limit_8, (u16)accept_limit_8);
+    wr16(m, mc::sherman_limit, (u16)sherman_limit);
+    wr16(m, mc::wide_limit, wide16 ? (u16)n : 0);
+    wr8(m, mc::alphaShift, (u8)as);
+    wr8(m, mc::flags, single ? mc::FLAG_SINGLE : 0);
+    wr8(m, mc::has_accel, 0);
+    wr8(m, mc::has_wide, 0);
+    std::memcpy(m + mc::remap, reach_map, 256);
+    wr32(m, mc::arb_report, all_reports.empty() ? 0 : *all_reports.begin());
+    wr32(m, mc::accel_offset, (u32)(accel_offset - nfa::SIZE));
+    // report lists behind the aux array
+    std::vector<u32> list_off(lists.size());
+    {
+        size_t o = aux_offset + aux_size;
+        for (size_t i = 0; i < lists.size(); i++) {
+            list_off[i] = (u32)o;
+            wr32(eng.at(o), 0, (u32)lists[i].size());
+            for (size_t k = 0; k < lists[i].size(); k++) wr32(eng.at(o), 4 + 4 * k, lists[i][k]);
+            o += 4 + 4 * lists[i].size();
+        }
+    }
+    // aux + successor table
+    u8 *succ = m + mc::SIZE;
+    auto flagged = [&](u32 t) -> u32 {  // markEdges, mcclellancompile.cpp:188-214
+        u32 v = impl[t];
+        if (wide16 && !d.reports[t].empty()) v |= mc::ACCEPT_FLAG;
+        return v;
+    };
+    for (u32 i = 0; i < n; i++) {
+        const u32 id = impl[i];
+        u8 *a = eng.at(aux_offset + mc::aux::SIZE * (size_t)id);
+        wr32(a, mc::aux::accept, list_of[i] == ~0u ? 0 : list_off[list_of[i]]);
+        wr32(a, mc::aux::accept_eod, 0);
+        wr16(a, mc::aux::top, (u16)impl[i ? d.start_floating : d.start_floating]);
+        wr32(a, mc::aux::accel_offset, 0);
+        if (wide16 && is_sherman[i]) {
+            u8 *sh = eng.at(sherman_offset + (size_t)mc::SHERMAN_FIXED_SIZE * (id - sherman_limit));
+            std::vector<u32> ks;
+            for (u32 k = 0; k < d.n_sym; k++) if (d.next[i][k] != d.next[daddy[i]][k]) ks.push_back(k);
+            sh[0] = (u8)mc::SHERMAN_STATE;
+            sh[mc::SHERMAN_LEN_OFFSET] = (u8)ks.size();
+            wr16(sh, mc::SHERMAN_DADDY_OFFSET, (u16)impl[daddy[i]]);
+            for (size_t q = 0; q < ks.size(); q++) {
+                sh[mc::SHERMAN_CHARS_OFFSET + q] = (u8)ks[q];
+                wr16(sh, mc::SHERMAN_CHARS_OFFSET + ks.size() + 2 * q, (u16)flagged(d.next[i][ks[q]]));
+            }
+            continue;
+        }
+        for (u32 k = 0; k < d.n_sym; k++) {
+            const size_t at = ((size_t)id << as) + k;
+            if (wide16) wr16(succ, 2 * at, (u16)flagged(d.next[i][k]));
+            else succ[at] = (u8)impl[d.next[i][k]];
+        }
+    }
+    return HSB_LIT_SUCCESS;
+}
+
 }  // namespace
 
 namespace hsb_nfadb {
 
-int build(const std::vector<Pattern> &pats, std::vector<u8> &image, std::string &err) {
+int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &image, std::string &err) {
+    if (engine > HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN) { err = "unknown engine"; return HSB_LIT_COMPILER_ERROR; }
     if (pats.empty()) { err = "no expressions"; return HSB_LIT_COMPILER_ERROR; }
     // ---- 1. parse every pattern, build one automaton -------------------------------------------------
     Automaton am;
@@ -529,6 +799,15 @@ int build(const std::vector<Pattern> &pats, std::vector<u8> &image, std::string 
 
     // the engine, relative to its own start
     Buf eng;
+    u32 stream_state = 0, scratch_state = 0;
+    if (engine != HSB_REGEX_ENGINE_LIMEX) {
+        Dfa dfa;
+        if (!determinise(am, reach_rows, dfa, 4 * (mcclellan::STATE_MASK + 1))) { err = "DFA too large for a McClellan engine"; return HSB_LIT_COMPILER_ERROR; }
+        minimise(dfa);
+        const int rv = emit_mcclellan(dfa, reach_map, program_of, engine == HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN, am.min_width, eng, stream_state, err);
+        if (rv != HSB_LIT_SUCCESS) return rv;
+        scratch_state = stream_state;
+    } else {
     eng.grow(nfa::SIZE + L.SIZE);
     const size_t lx = nfa::SIZE;  // LimExNFA base inside eng
     // reach table right behind the struct (get_reach_table)
@@ -585,7 +864,8 @@ int build(const std::vector<Pattern> &pats, std::vector<u8> &image, std::string 
     wr32(nh, nfa::queueIndex, 0);
     wr32(nh, nfa::nPositions, am.n_states);
     wr32(nh, nfa::scratchStateSize, L.bytes);
-    const u32 stream_state = (am.n_states + 7) / 8;
+    stream_state = (am.n_states + 7) / 8;
+    scratch_state = L.bytes;
     wr32(nh, nfa::streamStateSize, stream_state);
     wr32(nh, nfa::maxWidth, 0);
     wr32(nh, nfa::minWidth, am.min_width);
@@ -623,6 +903,7 @@ int build(const std::vector<Pattern> &pats, std::vector<u8> &image, std::string 
         wr8(lp, L.shiftAmount + k, (u8)shifts[k]);
     }
     wr32(lp, L.shiftCount, (u32)shifts.size());
+    }
 
     const size_t nfa_at = rose.grow(eng.size());
     std::memcpy(rose.at(nfa_at), eng.b.data(), eng.size());
@@ -667,7 +948,7 @@ int build(const std::vector<Pattern> &pats, std::vector<u8> &image, std::string 
     wr32(r, rose::invDkeyOffset, inv_dkey_off);
     wr32(r, rose::somLocationFatbitSize, fatbit_size(0));
     wr32(r, rose::stateSize, cur);
-    wr32(r, rose::scratchStateSize, (u32)round_up(L.bytes, 64));
+    wr32(r, rose::scratchStateSize, (u32)round_up(scratch_state, 64));
     wr32(r, rose::amatcherMaxBiAnchoredWidth, rose::BOUND_INF);
     wr32(r, rose::fmatcherMaxBiAnchoredWidth, rose::BOUND_INF);
     wr32(r, rose::activeArrayCount, 1);
@@ -702,8 +983,9 @@ int build(const std::vector<Pattern> &pats, std::vector<u8> &image, std::string 
 
 }  // namespace hsb_nfadb
 
-extern "C" int hsb_compile_regex_multi(const char *const *expressions, const unsigned *flags, const unsigned *ids,
-                                       unsigned elements, unsigned mode, hs_database_t **db, char **error) {
+extern "C" int hsb_compile_regex_multi_ex(const char *const *expressions, const unsigned *flags, const unsigned *ids,
+                                          unsigned elements, unsigned mode, unsigned engine, hs_database_t **db,
+                                          char **error) {
     if (error) *error = nullptr;
     if (!db) return HSB_LIT_COMPILER_ERROR;
     *db = nullptr;
@@ -724,10 +1006,15 @@ extern "C" int hsb_compile_regex_multi(const char *const *expressions, const uns
     }
     std::vector<hsb::u8> image;
     std::string err;
-    if (hsb_nfadb::build(pats, image, err) != HSB_LIT_SUCCESS) return fail(err);
+    if (hsb_nfadb::build(pats, engine, image, err) != HSB_LIT_SUCCESS) return fail(err);
     void *mem = nullptr;
     if (posix_memalign(&mem, 64, image.size())) return fail("out of memory");
     std::memcpy(mem, image.data(), image.size());
     *db = (hs_database_t *)mem;
     return HSB_LIT_SUCCESS;
+}
+
+extern "C" int hsb_compile_regex_multi(const char *const *expressions, const unsigned *flags, const unsigned *ids,
+                                       unsigned elements, unsigned mode, hs_database_t **db, char **error) {
+    return hsb_compile_regex_multi_ex(expressions, flags, ids, elements, mode, HSB_REGEX_ENGINE_LIMEX, db, error);
 }

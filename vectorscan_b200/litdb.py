@@ -38,6 +38,9 @@ def lib():
         L.hsb_compile_regex_multi.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_uint), C.POINTER(C.c_uint), C.c_uint,
                                               C.c_uint, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
         L.hsb_compile_regex_multi.restype = C.c_int
+        L.hsb_compile_regex_multi_ex.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_uint), C.POINTER(C.c_uint), C.c_uint,
+                                                 C.c_uint, C.c_uint, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+        L.hsb_compile_regex_multi_ex.restype = C.c_int
         L.hsb_free_database.argtypes = [C.c_void_p]
         L.hsb_free_error.argtypes = [C.c_void_p]
         L.hsb_database_size.argtypes = [C.c_void_p, C.POINTER(C.c_size_t)]
@@ -93,6 +96,16 @@ class Database:
         t = bc[nfa + 8]
         return [32, 64, 128, 256, 384, 512][t] if t < 6 else 0
 
+    def outfix_engine_type(self):
+        """NFA.type of the sole outfix engine (nfa_internal.h:52-80: 0-5 LimEx32..512, 6/7 McClellan 8/16-bit), or
+        -1 when the database is not a single-outfix database."""
+        bc = self.bytecode()
+        if bc[4] != 2:
+            return -1
+        info = int.from_bytes(bc[236:240], "little")
+        nfa = int.from_bytes(bc[info:info + 4], "little")
+        return bc[nfa + 8]
+
     def serialize(self):
         out, n = C.c_void_p(), C.c_size_t()
         if lib().hsb_serialize_database(self.ptr, C.byref(out), C.byref(n)) != 0:
@@ -129,9 +142,12 @@ def compile_lit_multi(literals, flags=None, ids=None, mode=HS_MODE_BLOCK, engine
     return Database(db.value)
 
 
-def compile_regex_multi(expressions, flags=None, ids=None, mode=HS_MODE_BLOCK):
+ENGINE_LIMEX, ENGINE_MCCLELLAN, ENGINE_MCCLELLAN_SHERMAN = 0, 1, 2
+
+
+def compile_regex_multi(expressions, flags=None, ids=None, mode=HS_MODE_BLOCK, engine=ENGINE_LIMEX):
     """expressions: list of bytes/str in the writer's dialect (csrc/nfadb_writer.cpp).  Returns a single-outfix
-    Database holding one LimEx NFA.  Same argument meaning as hs_compile_multi."""
+    Database holding one LimEx NFA (default) or one McClellan DFA.  Same argument meaning as hs_compile_multi."""
     n = len(expressions)
     ex = [e.encode("latin-1") if isinstance(e, str) else bytes(e) for e in expressions]
     if any(b"\0" in e for e in ex):
@@ -140,7 +156,7 @@ def compile_regex_multi(expressions, flags=None, ids=None, mode=HS_MODE_BLOCK):
     fl = (C.c_uint * n)(*(flags if flags is not None else [0] * n))
     idv = (C.c_uint * n)(*(ids if ids is not None else list(range(n))))
     db, err = C.c_void_p(), C.c_void_p()
-    rv = lib().hsb_compile_regex_multi(arr, fl, idv, n, mode, C.byref(db), C.byref(err))
+    rv = lib().hsb_compile_regex_multi_ex(arr, fl, idv, n, mode, engine, C.byref(db), C.byref(err))
     if rv != 0:
         msg = C.string_at(err).decode() if err else "error"
         if err:
