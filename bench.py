@@ -57,8 +57,18 @@ def ncu_traffic(config, nbytes, frontend):
     return None
 
 
-def make_workload(config, rank, nbytes):
+def make_workload(config, rank, nbytes, npat=6):
     """-> (database, number of pattern ids, [(flat, offsets)] x ROT, description)"""
+    if config == "c3d":
+        # the C3 templates that determinise (no counted gaps), as ONE McClellan DFA: the engine the reference compiler
+        # prefers for outfixes; 6 patterns keep the 16-bit table in shared memory, 8 push it out to L2
+        ex, fl, ids = W.c3_patterns(max_patterns=npat, templates=(2, 4, 5))
+        batches = [W.c3_corpus(nbytes, seed=20260103 + 100 * rank + r) for r in range(ROT)]
+        db = litdb.compile_regex_multi(ex, fl, ids, engine=litdb.ENGINE_MCCLELLAN)
+        name = (f"c3d: {len(ex)} Snort-like regexes (C3 templates without counted gaps) as one McClellan"
+                f"{8 if db.outfix_engine_type() == 6 else 16} DFA (single-outfix database) over a "
+                f"{nbytes >> 20} MiB batch of 200-1400-byte synthetic HTTP payloads per step")
+        return db, len(ex), batches, name
     if config == "c3":
         ex, fl, ids = W.c3_patterns()
         batches = [W.c3_corpus(nbytes, seed=20260103 + 100 * rank + r) for r in range(ROT)]
@@ -141,7 +151,7 @@ def run_reference(args, rank, world):
     if rank != 0:
         return
     nbytes = args.bytes
-    db, n_ids, batches, name = make_workload(args.config, 0, nbytes)
+    db, n_ids, batches, name = make_workload(args.config, 0, nbytes, args.patterns)
     ser = db.serialize()
     threads = os.cpu_count() or 1
     # bounded sample per step so that the whole run ends within minutes
@@ -176,7 +186,8 @@ def main():
     ap.add_argument("--steps", type=int, default=40)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours")
-    ap.add_argument("--config", default="c2", choices=["c1", "c2", "c3"])
+    ap.add_argument("--config", default="c2", choices=["c1", "c2", "c3", "c3d"])
+    ap.add_argument("--patterns", type=int, default=6, help="c3d: number of patterns in the DFA")
     ap.add_argument("--bytes", type=int, default=64 << 20)
     ap.add_argument("--ref-sample-bytes", type=int, default=0)
     ap.add_argument("--cpu-sample-bytes", type=int, default=0)
@@ -185,9 +196,9 @@ def main():
     args = ap.parse_args()
     # bounded CPU samples (the NFA path is ~100x slower per byte on the CPU than the literal path)
     if not args.ref_sample_bytes:
-        args.ref_sample_bytes = (8 << 20) if args.config == "c3" else (64 << 20)
+        args.ref_sample_bytes = (8 << 20) if args.config in ("c3", "c3d") else (64 << 20)
     if not args.cpu_sample_bytes:
-        args.cpu_sample_bytes = (4 << 20) if args.config == "c3" else (64 << 20)
+        args.cpu_sample_bytes = (4 << 20) if args.config in ("c3", "c3d") else (64 << 20)
 
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -209,7 +220,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     nbytes = args.bytes
-    db, n_ids, batches, name = make_workload(args.config, rank, nbytes)
+    db, n_ids, batches, name = make_workload(args.config, rank, nbytes, args.patterns)
     sc = gpu.alloc_scratch(db)
     if args.frontend:
         sc.set_option("frontend", args.frontend)
@@ -320,7 +331,7 @@ def main():
                     "d2h_bytes_per_step": d2h_per_step, "steps": e2e_steps,
                     "call": "hs_gpu_scan_vector_ex(host pinned buffers)", "per_step_ms": brk},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "k_limex" if args.config == "c3" else "k_scan" if args.frontend == 1 else "k_turbo", "achieved": round(achieved, 2),
+            "roofline": {"bound": "hbm", "kernel": "k_limex" if args.config == "c3" else "k_mcclellan" if args.config == "c3d" else "k_scan" if args.frontend == 1 else "k_turbo", "achieved": round(achieved, 2),
                          "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
                          "traffic": ncu_traffic(args.config, nbytes, args.frontend), "peak_source": peak_src,
                          "alg_bytes_per_launch": int(alg_bytes), "kernel_ms": round(kern_ms / n_launch, 4)},

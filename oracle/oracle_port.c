@@ -353,7 +353,61 @@ static int limex_scan(struct scan_state *s, const u8 *nfa) {
     return 0;
 }
 
-/* hs_scan for block-mode pure-literal and single-outfix (LimEx) databases.  `db` = in-memory hs_database_t. */
+
+/* ------------------------------------------------------------------------------------------------------------
+ * McClellan DFA, sole-outfix block run: src/runtime.c:246-279 -> nfaExecMcClellan{8,16}_Q (mcclellan.c:961-999,
+ * Q2i :626-759 / :789-925: MQE_TOP at offset 0 sets s = start_anchored) -> mcclellanExec{16,8}_i (:227-366 /
+ * :445-565) with doNormal16 (:122-167), doNormal8 (:413-443), doSherman16 (mcclellan_common_impl.h:54-84),
+ * doComplexReport (mcclellan.c:43-89), then nfaCheckFinalState -> mcclellanCheckEOD (:609-623).
+ * struct mcclellan / mstate_aux offsets: mcclellan_internal.h:63-101 (pinned by tests/test_layout.py).
+ * Acceleration is a skip over bytes that cannot change the state; wide states are outside the restated path. */
+enum { MC_STATE_COUNT = 0, MC_START_ANCHORED = 8, MC_AUX_OFFSET = 12, MC_SHERMAN_OFFSET = 16, MC_ACCEPT_LIMIT_8 = 26,
+       MC_SHERMAN_LIMIT = 28, MC_ALPHA_SHIFT = 32, MC_FLAGS = 33, MC_HAS_WIDE = 35, MC_REMAP = 36, MC_ARB_REPORT = 292,
+       MC_SIZE = 308, MC_AUX_SIZE = 16, MC_AUX_ACCEPT = 0, MC_AUX_ACCEPT_EOD = 4 };
+
+static int mc_report(struct scan_state *s, const u8 *nfa, const u8 *m, u32 st, u64 loc, int eod) {
+    if (!eod && (m[MC_FLAGS] & 1)) return run_program(s, rd32(m + MC_ARB_REPORT), loc);   /* MCCLELLAN_FLAG_SINGLE */
+    const u8 *aux = nfa + rd32(m + MC_AUX_OFFSET) + (size_t)st * MC_AUX_SIZE;
+    u32 off = rd32(aux + (eod ? MC_AUX_ACCEPT_EOD : MC_AUX_ACCEPT));
+    if (!off) return 0;
+    const u8 *rl = nfa + off;                                  /* struct report_list {u32 count; ReportID report[]} */
+    for (u32 i = 0, n = rd32(rl); i < n; i++)
+        if (run_program(s, rd32(rl + 4 + 4 * (size_t)i), loc) < 0) return -1;
+    return 0;
+}
+
+static int mcclellan_scan(struct scan_state *s, const u8 *nfa) {
+    const int wide16 = nfa[NFA_TYPE] == 7;
+    const u8 *m = nfa + NFA_SIZE, *succ = m + MC_SIZE;
+    if (nfa[NFA_RACCEL] || m[MC_HAS_WIDE]) { s->error = 1; return -1; }
+    const u32 as = m[MC_ALPHA_SHIFT], accept_limit = rd16(m + MC_ACCEPT_LIMIT_8), sherman_limit = rd16(m + MC_SHERMAN_LIMIT);
+    u32 st = rd16(m + MC_START_ANCHORED);
+    for (u32 i = 0; i < s->len && st; i++) {
+        const u32 cp = m[MC_REMAP + s->buf[i]];
+        int accept;
+        if (wide16) {
+            u32 e;
+            if (st < sherman_limit) e = rd16(succ + 2 * (((size_t)st << as) + cp));
+            else {
+                const u8 *sh = nfa + rd32(m + MC_SHERMAN_OFFSET) + 32 * (size_t)(st - sherman_limit);
+                u32 len = sh[1], k;
+                for (k = 0; k < len && sh[4 + k] != cp; k++) {}
+                if (k < len) e = rd16(sh + 4 + len + 2 * k);
+                else e = rd16(succ + 2 * (((size_t)rd16(sh + 2) << as) + cp));
+            }
+            accept = (e & 0x8000u) != 0;
+            st = e & 0x3fffu;
+        } else {
+            st = succ[((size_t)st << as) + cp];
+            accept = st >= accept_limit;
+        }
+        if (accept && mc_report(s, nfa, m, st, (u64)i + 1, 0) < 0) return -1;
+    }
+    if (st && (rd32(nfa + NFA_FLAGS) & NFA_ACCEPTS_EOD) && mc_report(s, nfa, m, st, s->len, 1) < 0) return -1;
+    return 0;
+}
+
+/* hs_scan for block-mode pure-literal and single-outfix (LimEx or McClellan) databases.  `db` = in-memory hs_database_t. */
 int op_scan(const void *db, const char *data, unsigned length, op_match_cb cb, void *ctx) {
     const u8 *d = (const u8 *)db;
     if (!d || !data || rd32(d + DB_MAGIC_OFF) != 0xdbdbdbdbu) return HS_INVALID;
@@ -375,7 +429,11 @@ int op_scan(const void *db, const char *data, unsigned length, op_match_cb cb, v
     s.exhausted = calloc(s.ekeys / 8 + 2, 1);
     s.dedupe = calloc(s.dkeys / 8 + 2, 1);
     s.dedupe_offset = ~0ull;
-    if (rose[R_RUNTIME_IMPL] == 2) limex_scan(&s, rose + rd32(rose + rd32(rose + R_NFA_INFO) + NI_NFA_OFF));
+    if (rose[R_RUNTIME_IMPL] == 2) {
+        const u8 *nfa = rose + rd32(rose + rd32(rose + R_NFA_INFO) + NI_NFA_OFF);
+        if (nfa[NFA_TYPE] == 6 || nfa[NFA_TYPE] == 7) mcclellan_scan(&s, nfa);
+        else limex_scan(&s, nfa);
+    }
     else hwlm_exec(&s, rose + rd32(rose + R_FMATCHER));
     free(s.exhausted); free(s.dedupe);
     if (s.error) return HS_UNKNOWN_ERROR;

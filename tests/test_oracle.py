@@ -173,3 +173,45 @@ def test_limex_port_vs_live_reference_runtime(ref):
             assert rv == rv2 == 0 and got == exp, (seed, n)   # same callback ORDER too (ascending state index)
         done += 1
     assert done > 20
+
+
+# ---- McClellan DFA (single-outfix databases): the C restatement's mcclellan_scan ---------------------------------
+def test_mcclellan_port_vs_recorded_reference_cases():
+    import json
+    import os
+    from vectorscan_b200 import litdb
+    with open(os.path.join(os.path.dirname(__file__), "golden", "ref_mcclellan_cases.json")) as f:
+        cases = json.load(f)
+    n, kinds = 0, set()
+    for c in cases:
+        db = litdb.compile_regex_multi([e.encode("latin-1") for e in c["exprs"]], c["flags"], c["ids"], engine=c["engine"])
+        assert db.outfix_engine_type() == c["type"]
+        kinds.add((c["type"], c["engine"]))
+        for t, exp in zip(c["texts"], c["expect"]):
+            rv, got = oracle_port.scan(db, bytes.fromhex(t))
+            assert rv == 0 and sorted(got, key=lambda x: (x[1], x[0])) == [tuple(x) for x in exp], c["seed"]
+            n += len(exp)
+    assert n > 300 and {(6, 1), (7, 1), (7, 2)} <= kinds
+
+
+def test_mcclellan_port_vs_live_reference_runtime(ref):
+    import random
+    import regen
+    from vectorscan_b200 import litdb
+    done = 0
+    for seed in range(60):
+        rng = random.Random(9500 + seed)
+        ex, fl, ids, smp = regen.random_set(rng, rng.randint(1, 12), True)
+        try:
+            db = litdb.compile_regex_multi(ex, fl, ids, engine=1 + seed % 2)
+        except litdb.CompileError:
+            continue
+        rdb = ref.deserialize(db.serialize())
+        rs = ref.alloc_scratch(rdb)
+        for n in (0, 1, 33, 500, 3000):
+            t = regen.random_text(rng, ex, n, smp)
+            rv, exp = ref.scan(rdb, rs, t)
+            rv2, got = oracle_port.scan(db, t)
+            assert rv == rv2 == 0 and got == exp, (seed, n)   # same callback ORDER too (report-list order)
+        done += 1
+    assert done > 20

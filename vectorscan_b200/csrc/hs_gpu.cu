@@ -739,6 +739,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_scan(const DevDb db, const DevCo
 
 #include "turbo.cuh"
 #include "limex.cuh"
+#include "mcclellan.cuh"
 
 // ------------------------------------------------------------------------------------------------
 // finalize: Rec (sorted, deduped) -> hs_gpu_match_t
@@ -845,6 +846,7 @@ struct DbImage {  // one uploaded database
     u64 *d_lx = nullptr;
     limex_dev::Tables lx_tabs;
     DevLimex lx{};
+    DevMcc mcc{};
     bool ordered_ok = true;
     size_t device_bytes = 0;
     void release() {
@@ -1001,6 +1003,18 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         L.o_squash = t.o_squash; L.o_meta = t.o_meta; L.o_masks = t.o_masks; L.o_base = t.o_base;
         L.total_words = t.total_words; L.accept_abs = t.accept_abs; L.accept_eod_abs = t.accept_eod_abs;
         L.nfa_flags = t.nfa_flags;
+    } else if (v.kind == ENG_MCCLELLAN) {
+        // the engine is stepped straight from the uploaded bytecode (mcclellan.cuh copies the table to shared memory)
+        const DbView::Mcc &M = v.mcc;
+        DevMcc &D = im->mcc;
+        D = DevMcc{};
+        D.tab_abs = M.tab_off; D.tab_bytes = M.tab_bytes; D.remap_abs = M.m_off + (u32)mcclellan::remap;
+        D.nfa_abs = v.nfa_off; D.aux_abs = M.aux_off; D.sherman_abs = M.sherman_off;
+        D.wide16 = M.wide16; D.as = M.as; D.start = M.start; D.accept_limit_8 = M.accept_limit_8;
+        D.sherman_limit = M.sherman_limit; D.single = M.single; D.arb_report = M.arb_report;
+        D.accepts_eod = (v.nfa_flags & nfa::ACCEPTS_EOD) ? 1u : 0u;
+        D.in_smem = MCC_RM_BYTES + (size_t)M.tab_bytes + 8 <= MCC_SMEM_MAX ? 1u : 0u;
+        D.has_sherman = M.wide16 && M.sherman_limit < M.states ? 1u : 0u;
     } else {
         d.nood_msk = v.nood_msk;
         d.nood_cmp = v.nood_cmp;
@@ -1008,7 +1022,7 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         d.nood_id = v.nood_id;
     }
     d.tK = 0;
-    if (v.kind != ENG_LIMEX && turbo::build(v, im->turbo_tabs)) {
+    if (v.kind != ENG_LIMEX && v.kind != ENG_MCCLELLAN && turbo::build(v, im->turbo_tabs)) {
         const turbo::Tables &tt = im->turbo_tabs;
         if (cudaMalloc((void **)&im->d_pair, tt.pair.size() * 8) != cudaSuccess ||
             cudaMalloc((void **)&im->d_slots, tt.slots.size() * sizeof(turbo::Slot)) != cudaSuccess ||
@@ -1118,6 +1132,36 @@ hs_error_t launch_limex(hs_gpu_scratch *s, const DbImage *im, const DevCorpus &c
     }
 }
 
+template <bool WIDE16, bool SMEM, bool SHERMAN>
+hs_error_t launch_mcclellan_t(hs_gpu_scratch *s, const DbImage *im, const DevCorpus &cp, const DevArena &ar) {
+    const size_t dyn = mcc_smem_bytes(im->mcc);
+    static size_t configured = 0;
+    if (dyn > configured) {
+        CU_OK(cudaFuncSetAttribute(k_mcclellan<WIDE16, SMEM, SHERMAN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+        configured = dyn;
+    }
+    // persistent threads, one buffer each at a time, fed from a counter: every SM gets a CTA as soon as there is a
+    // warp's worth of buffers for it
+    u32 grid = s->opt_grid > 0 ? (u32)s->opt_grid : (u32)s->sm_count;
+    const u32 need = (cp.count + 31) / 32;
+    if (grid > need) grid = need ? need : 1;
+    CU_OK(s->recs2.reserve(s->lx_event_hint));
+    const DevLxEvents evq{reinterpret_cast<LxEvent *>(s->recs2.p), s->d_ctl + 7, s->recs2.cap};
+    k_mcclellan<WIDE16, SMEM, SHERMAN><<<grid, MCC_THREADS, dyn, s->stream>>>(im->dev, im->mcc, cp, evq, s->d_ctl + 6);
+    CU_OK(cudaGetLastError());
+    k_limex_report<<<(u32)s->sm_count, LX_THREADS, 0, s->stream>>>(im->dev, cp, ar, evq);
+    CU_OK(cudaGetLastError());
+    s->stats.kernel_launches++;
+    return HS_SUCCESS;
+}
+
+hs_error_t launch_mcclellan(hs_gpu_scratch *s, const DbImage *im, const DevCorpus &cp, const DevArena &ar) {
+    const DevMcc &m = im->mcc;
+    if (!m.wide16) return m.in_smem ? launch_mcclellan_t<false, true, false>(s, im, cp, ar) : launch_mcclellan_t<false, false, false>(s, im, cp, ar);
+    if (m.has_sherman) return m.in_smem ? launch_mcclellan_t<true, true, true>(s, im, cp, ar) : launch_mcclellan_t<true, false, true>(s, im, cp, ar);
+    return m.in_smem ? launch_mcclellan_t<true, true, false>(s, im, cp, ar) : launch_mcclellan_t<true, false, false>(s, im, cp, ar);
+}
+
 // Ordered mode: k_turbo<K, true> appends position-ordered records to per-warp segments, k_compact gathers
 // them; no sort.  Returns HS_INSUFFICIENT_SPACE when the general path must be used instead.
 hs_error_t scan_device_ordered(hs_gpu_scratch *s, DbImage *im, const DevCorpus &cp) {
@@ -1220,6 +1264,7 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
         case ENG_FDR: rv = launch_scan<FdrNative, false>(s, im->dev, cp, ar); break;
         case ENG_TEDDY: rv = launch_scan<TeddyNative, false>(s, im->dev, cp, ar); break;
         case ENG_LIMEX: rv = launch_limex(s, im, cp, ar); break;
+        case ENG_MCCLELLAN: rv = launch_mcclellan(s, im, cp, ar); break;
         default: rv = launch_scan<Noodle, true>(s, im->dev, cp, ar); break;
         }
         if (rv != HS_SUCCESS) return rv;
@@ -1233,7 +1278,7 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
             return HS_UNKNOWN_ERROR;
         }
         raw = s->h_ctl[0];
-        if (im->view.kind == ENG_LIMEX && s->h_ctl[7] > s->recs2.cap) {  // event queue overflow: grow, scan again
+        if ((im->view.kind == ENG_LIMEX || im->view.kind == ENG_MCCLELLAN) && s->h_ctl[7] > s->recs2.cap) {  // event queue overflow: grow, scan again
             if (attempt >= 3) return HS_NOMEM;
             st.arena_retries++;
             s->lx_event_hint = s->h_ctl[7] + s->h_ctl[7] / 8 + 1024;

@@ -14,7 +14,7 @@ namespace hsb {
 constexpr int E_SUCCESS = 0, E_INVALID = -1, E_NOMEM = -2, E_DB_VERSION = -5, E_DB_PLATFORM = -6,
               E_DB_MODE = -7, E_BAD_ALIGN = -8, E_ARCH = -11, E_UNKNOWN = -13;
 
-enum EngineKind : u32 { ENG_FDR = 0, ENG_TEDDY = 1, ENG_NOODLE = 2, ENG_LIMEX = 3 };
+enum EngineKind : u32 { ENG_FDR = 0, ENG_TEDDY = 1, ENG_NOODLE = 2, ENG_LIMEX = 3, ENG_MCCLELLAN = 4 };
 
 struct LitRec {  // one LitInfo, flattened
     u64 v, msk, groups;
@@ -45,6 +45,11 @@ struct DbView {
     u32 max_lit_len = 0;       // longest CHECK_*_LIT length seen (bounds look-behind)
     // single-outfix LimEx NFA (kind == ENG_LIMEX): offsets are absolute bytecode offsets
     u32 nfa_off = 0, limex_off = 0, limex_type = 0, nfa_flags = 0, nfa_len = 0;
+    // single-outfix McClellan DFA (kind == ENG_MCCLELLAN), absolute bytecode offsets
+    struct Mcc {
+        u32 m_off = 0, tab_off = 0, tab_bytes = 0, aux_off = 0, sherman_off = 0;
+        u32 wide16 = 0, as = 0, states = 0, start = 0, accept_limit_8 = 0, sherman_limit = 0, single = 0, arb_report = 0;
+    } mcc;
 };
 
 inline bool in_range(const DbView &d, size_t off, size_t n) { return off <= d.bc_len && n <= d.bc_len - off; }
@@ -90,6 +95,82 @@ inline int census_program(const DbView &d, u32 prog, std::string &why, u32 &max_
     return E_INVALID;
 }
 
+
+// Single-outfix McClellan DFA (mcclellan_internal.h:77-101).  Accepted: 8- and 16-bit tables, Sherman states,
+// per-state report lists, EOD accepts.  Refused: wide states (has_wide).  Accel structures are skip-ahead only.
+inline int parse_mcclellan(DbView &d, std::string &why) {
+    namespace mc = mcclellan;
+    const u8 *r = d.bc;
+    const u8 *n = r + d.nfa_off;
+    DbView::Mcc &M = d.mcc;
+    if (d.nfa_len < nfa::SIZE + mc::SIZE) { why = "McClellan truncated"; return E_INVALID; }
+    M.m_off = d.nfa_off + (u32)nfa::SIZE;
+    const u8 *m = r + M.m_off;
+    auto n_range = [&](size_t off, size_t len) { return off <= d.nfa_len && len <= d.nfa_len - off; };  // relative to NFA
+    M.wide16 = rd8(n, nfa::type) == nfa::MCCLELLAN_16;
+    if (rd8(m, mc::has_wide)) { why = "McClellan wide states are not supported yet"; return E_ARCH; }
+    M.as = rd8(m, mc::alphaShift);
+    M.states = rd16(m, mc::state_count);
+    M.start = rd16(m, mc::start_anchored);
+    M.accept_limit_8 = rd16(m, mc::accept_limit_8);
+    M.sherman_limit = M.wide16 ? rd16(m, mc::sherman_limit) : M.states;
+    M.single = (rd8(m, mc::flags) & mc::FLAG_SINGLE) ? 1 : 0;
+    M.arb_report = rd32(m, mc::arb_report);
+    if (M.as > 8 || !M.states || M.start >= M.states || M.sherman_limit > M.states) { why = "McClellan header inconsistent"; return E_INVALID; }
+    if (M.wide16 && M.states - 1 > mc::STATE_MASK) { why = "McClellan state count out of range"; return E_INVALID; }
+    if (!M.wide16 && (M.states > 256 || M.accept_limit_8 > M.states)) { why = "McClellan8 limits out of range"; return E_INVALID; }
+    const u32 rows = M.wide16 ? M.sherman_limit : M.states;
+    M.tab_off = M.m_off + (u32)mc::SIZE;
+    M.tab_bytes = (rows << M.as) * (M.wide16 ? 2u : 1u);
+    if (!n_range(nfa::SIZE + mc::SIZE, M.tab_bytes)) { why = "McClellan successor table truncated"; return E_INVALID; }
+    for (u32 c = 0; c < 256; c++)
+        if (rd8(m, mc::remap + c) >= (1u << M.as)) { why = "McClellan remap out of range"; return E_INVALID; }
+    const u32 aux_rel = rd32(m, mc::aux_offset);
+    if (!n_range(aux_rel, (size_t)M.states * mc::aux::SIZE)) { why = "McClellan aux array truncated"; return E_INVALID; }
+    M.aux_off = d.nfa_off + aux_rel;
+    // every table entry names a state
+    for (u32 i = 0; i < (rows << M.as); i++) {
+        const u32 e = M.wide16 ? (rd16(r, M.tab_off + 2 * (size_t)i) & mc::STATE_MASK) : rd8(r, M.tab_off + i);
+        if (e >= M.states) { why = "McClellan successor out of range"; return E_INVALID; }
+    }
+    if (M.wide16 && M.sherman_limit < M.states) {
+        const u32 sh_rel = rd32(m, mc::sherman_offset);
+        const size_t nsh = M.states - M.sherman_limit;
+        if ((sh_rel & 15) || !n_range(sh_rel, nsh * mc::SHERMAN_FIXED_SIZE)) { why = "McClellan Sherman region truncated"; return E_INVALID; }
+        M.sherman_off = d.nfa_off + sh_rel;
+        for (size_t k = 0; k < nsh; k++) {
+            const u8 *sh = r + M.sherman_off + k * mc::SHERMAN_FIXED_SIZE;
+            const u32 len = sh[mc::SHERMAN_LEN_OFFSET];
+            if (sh[0] != mc::SHERMAN_STATE || len > mc::MAX_SHERMAN_LIST_LEN || rd16(sh, mc::SHERMAN_DADDY_OFFSET) >= M.sherman_limit) {
+                why = "McClellan Sherman state malformed"; return E_INVALID;
+            }
+            for (u32 q = 0; q < len; q++)
+                if ((rd16(sh, mc::SHERMAN_CHARS_OFFSET + len + 2 * q) & mc::STATE_MASK) >= M.states) { why = "McClellan Sherman successor out of range"; return E_INVALID; }
+        }
+    }
+    std::set<u32> progs;
+    if (M.single) progs.insert(M.arb_report);
+    for (u32 st = 0; st < M.states; st++) {
+        for (size_t f : {mc::aux::accept, mc::aux::accept_eod}) {
+            const u32 rl = rd32(r, M.aux_off + st * mc::aux::SIZE + f);
+            if (!rl) continue;
+            if ((rl & 3) || !n_range(rl, 4)) { why = "McClellan report list outside the engine"; return E_INVALID; }
+            const u32 cnt = rd32(n, rl);
+            if (cnt > 65536 || !n_range((size_t)rl + 4, 4 * (size_t)cnt)) { why = "McClellan report list truncated"; return E_INVALID; }
+            for (u32 k = 0; k < cnt; k++) progs.insert(rd32(n, rl + 4 + 4 * k));
+        }
+    }
+    d.kind = ENG_MCCLELLAN;
+    d.max_lit_len = 8;
+    for (u32 p : progs) {
+        if (p < rose::SIZE || !in_range(d, p, 8)) { why = "report program offset outside bytecode"; return E_INVALID; }
+        int rv = census_program(d, p, why, d.max_lit_len);
+        if (rv != E_SUCCESS) return rv;
+        d.programs.push_back(p);
+    }
+    return E_SUCCESS;
+}
+
 // Single-outfix database (src/runtime.c:246-279): queue 0 holds the only engine.  Accepted when that engine is a
 // LimEx NFA without bounded repeats and without reverse acceleration; every report list and accept entry must
 // lead to a Rose report program the device interpreter implements.
@@ -108,8 +189,9 @@ inline int parse_single_outfix(DbView &d, std::string &why) {
     d.nfa_flags = rd32(n, nfa::flags);
     d.limex_type = rd8(n, nfa::type);
     if (!in_range(d, d.nfa_off, d.nfa_len)) { why = "NFA runs past the bytecode"; return E_INVALID; }
-    if (d.limex_type > nfa::LIMEX_512) { why = "outfix engine type " + std::to_string(d.limex_type) + " (not LimEx) is not supported yet"; return E_ARCH; }
     if (rd8(n, nfa::rAccelType)) { why = "reverse acceleration is not supported"; return E_ARCH; }
+    if (d.limex_type == nfa::MCCLELLAN_8 || d.limex_type == nfa::MCCLELLAN_16) return parse_mcclellan(d, why);
+    if (d.limex_type > nfa::LIMEX_512) { why = "outfix engine type " + std::to_string(d.limex_type) + " (neither LimEx nor McClellan) is not supported yet"; return E_ARCH; }
     const limex::Layout L = limex::layout(d.limex_type);
     if (d.nfa_len < nfa::SIZE + L.SIZE) { why = "LimEx truncated"; return E_INVALID; }
     d.limex_off = d.nfa_off + (u32)nfa::SIZE;

@@ -32,7 +32,8 @@ struct DevLimex {
 // What the stepping kernel hands to the report kernel: "the NFA raised report list / report program `what` at
 // offset `to` of buffer `buf`" -- the arguments of the NfaCallback (roseReportAdaptor, src/rose/match.c:611-633).
 struct __align__(16) LxEvent {
-    u32 buf, to, what, single;  // single != 0: `what` is one program offset; else the absolute offset of a list
+    u32 buf, to, what, single;  // single: 1 = `what` is one program offset; 0 = absolute offset of a MO_INVALID_IDX-
+                                // terminated list (LimEx); 2 = absolute offset of a counted report_list (McClellan)
 };
 struct DevLxEvents {
     LxEvent *ev;
@@ -255,8 +256,11 @@ __global__ void __launch_bounds__(LX_THREADS) k_limex_report(const DevDb db, con
             const u64 o0 = cp.off[ev.buf];
             const u32 blen = (u32)(cp.off[ev.buf + 1] - o0);
             const u8 *btext = cp.text + o0;
-            if (ev.single) {
+            if (ev.single == 1) {
                 run_program(c, ev.what, ev.buf, btext, blen, ev.to);
+            } else if (ev.single == 2) {  // counted list: struct report_list {u32 count; ReportID report[]} (McClellan)
+                const u32 cnt = ld32(db.bc, ev.what);
+                for (u32 j = 0; j < cnt; j++) run_program(c, ld32(db.bc, ev.what + 4 + 4 * j), ev.buf, btext, blen, ev.to);
             } else {
                 for (u32 j = 0; j < 65536; j++) {
                     const u32 prog = ld32(db.bc, ev.what + 4 * j);

@@ -1,0 +1,196 @@
+// mcclellan.cuh -- McClellan DFA stepping on the device (included by hs_gpu.cu; census: hsb_dbview.h).
+//
+// What it computes is the reference's block-mode run of a sole-outfix McClellan engine (src/runtime.c:246-279 ->
+// nfaExecMcClellan{8,16}_Q -> mcclellanExec{8,16}_i, src/nfa/mcclellan.c:227-366 / :445-565):
+//     s = start_anchored                                           (MQE_TOP at offset 0, mcclellan.c:740-745)
+//     for i in [0, len):  c' = remap[text[i]]
+//                         16-bit: e = s < sherman_limit ? succ[(s << alphaShift) + c'] : sherman(s, c')
+//                                 e & ACCEPT_FLAG -> reports of state e at offset i + 1;  s = e & STATE_MASK
+//                          8-bit: s = succ[(s << alphaShift) + c'];  s >= accept_limit_8 -> reports at offset i + 1
+//                         s == 0 (dead) ends the scan
+//     NFA_ACCEPTS_EOD: aux[s].accept_eod reports at offset len     (runtime.c:273-278, mcclellanCheckEOD)
+// Reports: MCCLELLAN_FLAG_SINGLE -> arb_report, else the counted report list at aux[s].accept (doComplexReport,
+// mcclellan.c:43-89; its one-entry cache is a CPU shortcut).  Acceleration (run_mcclellan_accel) skips bytes that
+// cannot change the state -- result-neutral, not used here; ACCEL_FLAG bits in table entries are masked off.
+//
+// Geometry: a DFA step is one dependent table read per byte, so the unit of parallelism is the BUFFER: one
+// thread per buffer, threads persistent and fed from a global counter (buffers of any length mix in a warp).
+// The successor table and remap[] sit in shared memory when they fit (<= MCC_SMEM_MAX), else they are read
+// through L1/L2.  Text is read one aligned 16-byte chunk per trip with the next chunk already in flight; bytes of
+// a chunk outside the buffer freeze the state (select), so all 32 lanes run the same 16 unrolled steps.
+// Hot loop = 16 branch-free steps that only remember whether an accept was passed; the rare chunk that passed one
+// is stepped again from its start state by the exact loop, which raises the events.
+#pragma once
+
+constexpr int MCC_THREADS = 1024;
+constexpr size_t MCC_SMEM_MAX = 226 * 1024;  // of the 227 KB a CTA may have
+constexpr size_t MCC_RM_BYTES = 256 * 32 * 4;  // symbol table, replicated per bank
+
+struct DevMcc {
+    u32 tab_abs;        // absolute bytecode offset of the successor table
+    u32 tab_bytes;      // its size (rows below sherman_limit only for 16-bit engines)
+    u32 remap_abs;      // absolute bytecode offset of remap[256]
+    u32 nfa_abs;        // absolute bytecode offset of struct NFA (report-list and aux offsets are relative to it)
+    u32 aux_abs;        // absolute bytecode offset of mstate_aux[0]
+    u32 sherman_abs;    // absolute bytecode offset of the first Sherman state
+    u32 wide16, as, start, accept_limit_8, sherman_limit, single, arb_report, accepts_eod, in_smem, has_sherman;
+};
+
+__host__ __device__ inline size_t mcc_smem_bytes(const DevMcc &m) { return MCC_RM_BYTES + (m.in_smem ? (size_t)m.tab_bytes + 8 : 0); }
+
+// doSherman16 (mcclellan_common_impl.h:54-84): a Sherman state lists up to 9 (symbol, successor) exceptions to
+// its daddy's row
+__device__ __noinline__ u32 mcc_sherman(const u8 *bc, const DevMcc &m, const u16 *tab16, u32 s, u32 cp) {
+    const u8 *sh = bc + m.sherman_abs + (size_t)mcclellan::SHERMAN_FIXED_SIZE * (s - m.sherman_limit);
+    const u32 len = sh[mcclellan::SHERMAN_LEN_OFFSET];
+    for (u32 k = 0; k < len; k++)
+        if (sh[mcclellan::SHERMAN_CHARS_OFFSET + k] == cp) {
+            const u8 *p = sh + mcclellan::SHERMAN_CHARS_OFFSET + len + 2 * k;
+            return (u32)p[0] | ((u32)p[1] << 8);
+        }
+    const u32 daddy = (u32)sh[mcclellan::SHERMAN_DADDY_OFFSET] | ((u32)sh[mcclellan::SHERMAN_DADDY_OFFSET + 1] << 8);
+    return tab16[(daddy << m.as) + cp];
+}
+
+// "state `st` accepts at offset `to`": hand the report (list) to the report kernel
+__device__ __noinline__ void mcc_accept(const DevLxEvents &q, const u8 *bc, const DevMcc &m, u32 st, u32 buf, u32 to, bool eod) {
+    if (m.single && !eod) { lx_event(q, buf, to, m.arb_report, 1); return; }
+    const u32 a = m.aux_abs + st * (u32)mcclellan::aux::SIZE;
+    const u32 rl = ld32(bc, a + (u32)(eod ? mcclellan::aux::accept_eod : mcclellan::aux::accept));
+    if (rl) lx_event(q, buf, to, m.nfa_abs + rl, 2);
+}
+
+// One step of the reference's loop, any engine flavour; returns the raw table entry (16-bit: flags included).
+template <bool WIDE16>
+__device__ __forceinline__ u32 mcc_step(const u8 *bc, const DevMcc &m, const u8 *tab, u32 rowbytes, u32 s, u32 sym) {
+    if (!WIDE16) return tab[s * rowbytes + sym];
+    if (s < m.sherman_limit) return *reinterpret_cast<const u16 *>(tab + s * rowbytes + sym);
+    return mcc_sherman(bc, m, reinterpret_cast<const u16 *>(tab), s, sym >> 1);
+}
+
+// SHERMAN = false: every state has a table row, so a chunk is 16 branch-free steps (extract, remap, multiply-add,
+// table read, select) that only OR the entries together; a chunk that saw an accept flag (rare) is then stepped
+// again from its saved start state by the exact loop below, which raises the events.  SHERMAN = true (16-bit
+// engines with Sherman states): the exact loop is the only loop.
+template <bool WIDE16, bool SMEM, bool SHERMAN>
+__global__ void __launch_bounds__(MCC_THREADS, 1) k_mcclellan(const DevDb db_, const DevMcc m, const DevCorpus cp_,
+                                                              const DevLxEvents evq, unsigned long long *next_buf) {
+    extern __shared__ __align__(16) u8 smem[];
+    // symbol table: rm[c] = remap[c] * (entry size), so that row offset + rm[c] is a byte offset;
+    // one copy per bank (word ch * 32 + lane): a warp's 32 lookups never conflict
+    u32 *rm_w = reinterpret_cast<u32 *>(smem);
+    for (u32 i = threadIdx.x; i < 256 * 32; i += MCC_THREADS) rm_w[i] = (u32)db_.bc[m.remap_abs + (i >> 5)] * (WIDE16 ? 2u : 1u);
+    if (SMEM) {
+        const u32 head = m.tab_abs & 3u;  // copy whole words; the table is only 2-aligned in the bytecode (372 = 64 + 308)
+        const u32 words = (m.tab_bytes + head + 3) / 4;
+        const u32 *src = reinterpret_cast<const u32 *>(db_.bc + (m.tab_abs - head));
+        u32 *dst = reinterpret_cast<u32 *>(smem + MCC_RM_BYTES);
+        for (u32 i = threadIdx.x; i < words; i += MCC_THREADS) dst[i] = src[i];
+    }
+    __syncthreads();
+    const u32 *rm = rm_w + (threadIdx.x & 31u);
+    const u8 *tab = SMEM ? smem + MCC_RM_BYTES + (m.tab_abs & 3u) : db_.bc + m.tab_abs;
+    const u32 rowbytes = (WIDE16 ? 2u : 1u) << m.as, count = cp_.count;
+    const u32 accept_limit = m.accept_limit_8;
+    const u32 tab_sh = SMEM ? (u32)__cvta_generic_to_shared(tab) : 0u;
+
+    u32 s = 0, buf = 0, len = 0;
+    long long i = 0;           // buffer offset of byte 0 of the current chunk (negative for the first chunk)
+    const uint4 *chunk = nullptr;
+    uint4 cur = make_uint4(0, 0, 0, 0), q1 = cur, q2 = cur, q3 = cur;  // this chunk and the three after it
+    bool have = false, first = true;
+
+    for (;;) {
+        if (!have) {
+            // ---- next buffer of this thread (empty and gated-out buffers report nothing: runtime.c:343-371) ----
+            unsigned long long nb;
+            u32 l = 0;
+            u64 o0 = 0;
+            for (;;) {
+                if (first) {
+                    // first buffer: by thread index, no counter traffic (one same-address atomic per thread would
+                    // serialise at the L2: ~1 per clock, i.e. longer than the scan itself for small buffers)
+                    // warps interleaved across the CTAs, so a batch smaller than the grid still uses every SM
+                    nb = ((unsigned long long)(threadIdx.x >> 5) * gridDim.x + blockIdx.x) * 32u + (threadIdx.x & 31u);
+                    first = false;
+                } else {
+                    // later buffers: one atomic per group of lanes that arrive here together
+                    const u32 act = __activemask(), ln = threadIdx.x & 31u, leader = (u32)__ffs((int)act) - 1u;
+                    unsigned long long base = 0;
+                    if (ln == leader) base = atomicAdd(next_buf, (unsigned long long)__popc(act));
+                    base = __shfl_sync(act, base, leader);
+                    nb = base + (unsigned long long)gridDim.x * MCC_THREADS + (u32)__popc(act & ((1u << ln) - 1u));
+                }
+                if (nb >= count) break;
+                o0 = cp_.off[nb];
+                l = (u32)(cp_.off[nb + 1] - o0);
+                if (l && passes_gates(db_, l)) break;
+            }
+            if (nb >= count) break;
+            buf = (u32)nb;
+            len = l;
+            const uintptr_t ap = reinterpret_cast<uintptr_t>(cp_.text + o0);
+            chunk = reinterpret_cast<const uint4 *>(ap & ~(uintptr_t)15);
+            i = -(long long)(ap & 15);
+            cur = chunk[0];              // over-reads stay inside the padded text (BACK_PAD)
+            q1 = chunk[1]; q2 = chunk[2]; q3 = chunk[3];
+            chunk += 4;
+            s = m.start;
+            have = true;
+        }
+        // ---- one aligned 16-byte chunk: bytes [j0, j1) of it belong to the buffer ----
+        const uint4 v = cur;
+        const long long rem = (long long)len - i;  // bytes from chunk byte 0 to the end of the buffer
+        // three chunks (48 steps) of loads in flight while this one is stepped: a step is ~40 cycles of dependent
+        // latency, a miss to HBM ~1000
+        cur = q1; q1 = q2; q2 = q3;
+        if (rem > 64) q3 = *chunk;
+        chunk++;
+        const u32 j0 = i < 0 ? (u32)(-i) : 0u;
+        const u32 j1 = rem < 16 ? (u32)rem : 16u;
+        const u32 valid = ((1u << j1) - 1u) & ~((1u << j0) - 1u);
+        const u32 wv[4] = {v.x, v.y, v.z, v.w};
+        const u32 s0 = s;
+        bool exact = SHERMAN;
+        if (!SHERMAN) {
+            u32 seen = 0;  // 16-bit: OR of the entries taken; 8-bit: highest state entered
+#pragma unroll
+            for (int j = 0; j < 16; j++) {
+                const u32 ch = (wv[j >> 2] >> (8 * (j & 3))) & 0xffu;
+                const u32 sym = rm[ch * 32];
+                u32 e;
+                if (SMEM) {
+                    // row offset + (symbol offset + table base): the second term is off the dependent chain, which is
+                    // then mask -> multiply-add -> shared-memory read
+                    u32 sa, addr;  // written as PTX so the compiler keeps the association
+                    asm("add.u32 %0, %1, %2;" : "=r"(sa) : "r"(sym), "r"(tab_sh));
+                    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(addr) : "r"(WIDE16 ? (s & mcclellan::STATE_MASK) : s), "r"(rowbytes), "r"(sa));
+                    if (WIDE16) { unsigned short t; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(t) : "r"(addr)); e = t; }
+                    else asm volatile("ld.shared.u8 %0, [%1];" : "=r"(e) : "r"(addr));
+                } else if (WIDE16) e = *reinterpret_cast<const u16 *>(tab + (s & mcclellan::STATE_MASK) * rowbytes + sym);
+                else e = tab[s * rowbytes + sym];
+                s = ((valid >> j) & 1u) ? e : s;   // bytes outside the buffer freeze the state (flags of s stay as they were)
+                if (WIDE16) seen |= s; else seen = max(seen, s);
+            }
+            if (WIDE16) { exact = (seen & mcclellan::ACCEPT_FLAG) != 0; s &= mcclellan::STATE_MASK; }
+            else exact = seen >= accept_limit;
+        }
+        if (exact) {
+            // the reference's loop, byte by byte, raising the accepts (mcclellan.c:267-289 / :482-506)
+            s = s0;
+            for (u32 j = j0; j < j1 && s; j++) {
+                const u32 w = j < 8 ? (j < 4 ? v.x : v.y) : (j < 12 ? v.z : v.w);
+                const u32 e = mcc_step<WIDE16>(db_.bc, m, tab, rowbytes, s, rm[((w >> (8 * (j & 3))) & 0xffu) * 32]);
+                s = WIDE16 ? (e & mcclellan::STATE_MASK) : e;
+                if (WIDE16 ? (e & mcclellan::ACCEPT_FLAG) != 0 : e >= accept_limit)
+                    mcc_accept(evq, db_.bc, m, s, buf, (u32)(i + j + 1), false);
+            }
+        }
+        i += 16;
+        if (i >= (long long)len || !s) {
+            // ---- end of buffer (or dead: nothing can switch on again, mcclellan.c:240-243) ----
+            if (s && m.accepts_eod) mcc_accept(evq, db_.bc, m, s, buf, len, true);
+            have = false;
+        }
+    }
+}
