@@ -1145,9 +1145,14 @@ hs_error_t launch_mcclellan_t(hs_gpu_scratch *s, const DbImage *im, const DevCor
     u32 grid = s->opt_grid > 0 ? (u32)s->opt_grid : (u32)s->sm_count;
     const u32 need = (cp.count + 31) / 32;
     if (grid > need) grid = need ? need : 1;
+    // 1024 threads per SM even when that leaves a thread with one buffer or none: the step is a dependent
+    // shared-memory read, and chains in flight are what hides it (measured: 128/256/512/1024 threads -> 0.36/0.20/
+    // 0.12/0.115 ms on 64 MiB of 200-1400-byte buffers)
+    u32 block = MCC_THREADS;
+    if (const char *e = getenv("HS_GPU_MCC_BLOCK")) { const int b = atoi(e); if (b >= 32 && b <= MCC_THREADS && !(b & 31)) block = (u32)b; }
     CU_OK(s->recs2.reserve(s->lx_event_hint));
     const DevLxEvents evq{reinterpret_cast<LxEvent *>(s->recs2.p), s->d_ctl + 7, s->recs2.cap};
-    k_mcclellan<WIDE16, SMEM, SHERMAN><<<grid, MCC_THREADS, dyn, s->stream>>>(im->dev, im->mcc, cp, evq, s->d_ctl + 6);
+    k_mcclellan<WIDE16, SMEM, SHERMAN><<<grid, block, dyn, s->stream>>>(im->dev, im->mcc, cp, evq, s->d_ctl + 6);
     CU_OK(cudaGetLastError());
     k_limex_report<<<(u32)s->sm_count, LX_THREADS, 0, s->stream>>>(im->dev, cp, ar, evq);
     CU_OK(cudaGetLastError());

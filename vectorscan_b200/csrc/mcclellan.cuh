@@ -78,21 +78,24 @@ __global__ void __launch_bounds__(MCC_THREADS, 1) k_mcclellan(const DevDb db_, c
     extern __shared__ __align__(16) u8 smem[];
     // symbol table: rm[c] = remap[c] * (entry size), so that row offset + rm[c] is a byte offset;
     // one copy per bank (word ch * 32 + lane): a warp's 32 lookups never conflict
+    // the shared-memory address of the table is folded in, so row offset + rm[c] is the address of the entry
     u32 *rm_w = reinterpret_cast<u32 *>(smem);
-    for (u32 i = threadIdx.x; i < 256 * 32; i += MCC_THREADS) rm_w[i] = (u32)db_.bc[m.remap_abs + (i >> 5)] * (WIDE16 ? 2u : 1u);
+    const u32 tab_sh = SMEM ? (u32)__cvta_generic_to_shared(smem + MCC_RM_BYTES + (m.tab_abs & 3u)) : 0u;
+    for (u32 i = threadIdx.x; i < 256 * 32; i += blockDim.x)
+        rm_w[i] = (u32)db_.bc[m.remap_abs + (i >> 5)] * (WIDE16 ? 2u : 1u) + tab_sh;
     if (SMEM) {
         const u32 head = m.tab_abs & 3u;  // copy whole words; the table is only 2-aligned in the bytecode (372 = 64 + 308)
         const u32 words = (m.tab_bytes + head + 3) / 4;
         const u32 *src = reinterpret_cast<const u32 *>(db_.bc + (m.tab_abs - head));
         u32 *dst = reinterpret_cast<u32 *>(smem + MCC_RM_BYTES);
-        for (u32 i = threadIdx.x; i < words; i += MCC_THREADS) dst[i] = src[i];
+        for (u32 i = threadIdx.x; i < words; i += blockDim.x) dst[i] = src[i];
     }
     __syncthreads();
     const u32 *rm = rm_w + (threadIdx.x & 31u);
     const u8 *tab = SMEM ? smem + MCC_RM_BYTES + (m.tab_abs & 3u) : db_.bc + m.tab_abs;
     const u32 rowbytes = (WIDE16 ? 2u : 1u) << m.as, count = cp_.count;
     const u32 accept_limit = m.accept_limit_8;
-    const u32 tab_sh = SMEM ? (u32)__cvta_generic_to_shared(tab) : 0u;
+    const u32 lane4 = (threadIdx.x & 31u) * 4u;
 
     u32 s = 0, buf = 0, len = 0;
     long long i = 0;           // buffer offset of byte 0 of the current chunk (negative for the first chunk)
@@ -119,7 +122,7 @@ __global__ void __launch_bounds__(MCC_THREADS, 1) k_mcclellan(const DevDb db_, c
                     unsigned long long base = 0;
                     if (ln == leader) base = atomicAdd(next_buf, (unsigned long long)__popc(act));
                     base = __shfl_sync(act, base, leader);
-                    nb = base + (unsigned long long)gridDim.x * MCC_THREADS + (u32)__popc(act & ((1u << ln) - 1u));
+                    nb = base + (unsigned long long)gridDim.x * blockDim.x + (u32)__popc(act & ((1u << ln) - 1u));
                 }
                 if (nb >= count) break;
                 o0 = cp_.off[nb];
@@ -156,15 +159,16 @@ __global__ void __launch_bounds__(MCC_THREADS, 1) k_mcclellan(const DevDb db_, c
             u32 seen = 0;  // 16-bit: OR of the entries taken; 8-bit: highest state entered
 #pragma unroll
             for (int j = 0; j < 16; j++) {
-                const u32 ch = (wv[j >> 2] >> (8 * (j & 3))) & 0xffu;
-                const u32 sym = rm[ch * 32];
+                // byte j of the chunk, times 128 (one 32-word row of the symbol table per byte value), plus my bank
+                const u32 w = wv[j >> 2], k = 8 * (j & 3);
+                const u32 ra = ((k >= 7 ? w >> (k - 7) : w << (7 - k)) & 0x7f80u) | lane4;
+                const u32 sym = *reinterpret_cast<const u32 *>(smem + ra);
                 u32 e;
                 if (SMEM) {
-                    // row offset + (symbol offset + table base): the second term is off the dependent chain, which is
-                    // then mask -> multiply-add -> shared-memory read
-                    u32 sa, addr;  // written as PTX so the compiler keeps the association
-                    asm("add.u32 %0, %1, %2;" : "=r"(sa) : "r"(sym), "r"(tab_sh));
-                    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(addr) : "r"(WIDE16 ? (s & mcclellan::STATE_MASK) : s), "r"(rowbytes), "r"(sa));
+                    // row offset + (symbol offset + table address): the second term is off the dependent chain, which
+                    // is then mask -> multiply-add -> shared-memory read
+                    u32 addr;  // written as PTX so the compiler keeps the association
+                    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(addr) : "r"(WIDE16 ? (s & mcclellan::STATE_MASK) : s), "r"(rowbytes), "r"(sym));
                     if (WIDE16) { unsigned short t; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(t) : "r"(addr)); e = t; }
                     else asm volatile("ld.shared.u8 %0, [%1];" : "=r"(e) : "r"(addr));
                 } else if (WIDE16) e = *reinterpret_cast<const u16 *>(tab + (s & mcclellan::STATE_MASK) * rowbytes + sym);
@@ -180,7 +184,7 @@ __global__ void __launch_bounds__(MCC_THREADS, 1) k_mcclellan(const DevDb db_, c
             s = s0;
             for (u32 j = j0; j < j1 && s; j++) {
                 const u32 w = j < 8 ? (j < 4 ? v.x : v.y) : (j < 12 ? v.z : v.w);
-                const u32 e = mcc_step<WIDE16>(db_.bc, m, tab, rowbytes, s, rm[((w >> (8 * (j & 3))) & 0xffu) * 32]);
+                const u32 e = mcc_step<WIDE16>(db_.bc, m, tab, rowbytes, s, rm[((w >> (8 * (j & 3))) & 0xffu) * 32] - tab_sh);
                 s = WIDE16 ? (e & mcclellan::STATE_MASK) : e;
                 if (WIDE16 ? (e & mcclellan::ACCEPT_FLAG) != 0 : e >= accept_limit)
                     mcc_accept(evq, db_.bc, m, s, buf, (u32)(i + j + 1), false);
