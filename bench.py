@@ -76,6 +76,13 @@ def make_workload(config, rank, nbytes, npat=6):
                 f"as many of the C3 templates as 512 states hold -- no pattern compiler in this image) over a "
                 f"{nbytes >> 20} MiB batch of 200-1400-byte synthetic HTTP payloads per step")
         return litdb.compile_regex_multi(ex, fl, ids), len(ex), batches, name
+    if config == "c4":
+        lits, flags, ids = W.c4_patterns()
+        batches = [W.c4_corpus(nbytes, lits, seed=20260104 + 100 * rank + r) for r in range(ROT)]
+        name = (f"c4 (literal part): 16000 literals of the 20000 mixed patterns over a {nbytes >> 20} MiB shard of "
+                f"pcap-shaped packets (64/576/1500 B = 40/20/40 %), one block scan per packet; the 4000 regexes need a "
+                f"full-Rose database (no compiler in this image)")
+        return litdb.compile_lit_multi(lits, flags, ids), len(lits), batches, name
     if config == "c1":
         lits, flags, ids = W.c1_patterns()
         batches = []
@@ -186,7 +193,7 @@ def main():
     ap.add_argument("--steps", type=int, default=40)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours")
-    ap.add_argument("--config", default="c2", choices=["c1", "c2", "c3", "c3d"])
+    ap.add_argument("--config", default="c2", choices=["c1", "c2", "c3", "c3d", "c4"])
     ap.add_argument("--patterns", type=int, default=6, help="c3d: number of patterns in the DFA")
     ap.add_argument("--bytes", type=int, default=64 << 20)
     ap.add_argument("--ref-sample-bytes", type=int, default=0)

@@ -203,3 +203,25 @@ def c3_corpus(nbytes, seed=20260103):
         tb = np.frombuffer(tok, dtype=np.uint8)
         flat[sel[:, None] + np.arange(len(tb))[None, :]] = tb[None, :]
     return flat, offsets
+
+
+# ---- c4: pcapscan-shaped packet corpus, literal part of the 20k mixed set (SURVEY.md 8d "C4 concrete input") ----
+def c4_patterns(n=16000, seed=20260104):
+    """The 16 000 literals of C4's 20 000 mixed patterns.  The 4 000 regexes need Rose's decomposition into many
+    small engines (full-Rose database), which no writer in this image produces: DESIGN.md section 6."""
+    rng = np.random.default_rng(seed)
+    return _unique_literals(rng, n, 4, 12, PRINTABLE), [0] * n, list(range(n))
+
+
+def c4_corpus(nbytes, lits, seed=20260104):
+    """Packets with the length mix {64 B: 40 %, 576 B: 20 %, 1500 B: 40 %} (by packet count), payload as c2;
+    one block-mode scan per packet, as tools/.. pcapscan.cc:305-316 does.  (flat uint8 array, uint64 offsets)."""
+    rng = np.random.default_rng(seed + 13)
+    mean = 0.4 * 64 + 0.2 * 576 + 0.4 * 1500
+    n_guess = int(nbytes / mean * 1.05) + 16
+    lens = rng.choice(np.array([64, 576, 1500]), size=n_guess, p=[0.4, 0.2, 0.4])
+    ends = np.cumsum(lens)
+    count = int(np.searchsorted(ends, nbytes, side="left")) + 1
+    offsets = np.concatenate([[0], np.minimum(ends[:count], nbytes)]).astype(np.uint64)
+    flat, _ = c2_batch(nbytes, lits, seed=seed, packet=1500)   # payload bytes + tokens + planted literals
+    return flat, offsets
