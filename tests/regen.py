@@ -127,14 +127,22 @@ def brute_force(exprs, flags, ids, text):
             fl |= re.DOTALL
         anchored = e.startswith(b"^")
         body = e[1:] if anchored else e
+        eod = body.endswith(b"\\z") and not body.endswith(b"\\\\z")   # writer dialect: match must end at end of data
+        if eod:
+            body = body[:-2]
         # all end offsets: reverse is awkward with re; instead test every (start) with a pattern that forces
         # each possible end via fullmatch on prefixes -- O(n^2) per pattern, so keep texts small.
         rx = re.compile(b"(?:" + body + b")", fl)
         starts = [0] if anchored else range(n)
         for s in starts:
-            for t in range(s + 1, n + 1):
-                if (i, t) in out:
+            for t in ([n] if eod else range(s + 1, n + 1)):
+                if t <= s or (i, t) in out:
                     continue
                 if rx.fullmatch(text, s, t):
                     out.add((i, t))
     return sorted(out, key=lambda x: (x[1], x[0]))
+
+
+def with_eod(rng, exprs, rate=0.5):
+    """Append \\z (end-of-data anchor of the writer's dialect) to a random subset of the expressions."""
+    return [e + b"\\z" if rng.random() < rate else e for e in exprs]

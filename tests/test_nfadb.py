@@ -92,3 +92,29 @@ def test_mcclellan_8_and_16_bit(ref, engine):
         got = _scan_ref(ref, db, texts)
         for t, g in zip(texts, got):
             assert g == regen.brute_force(ex, fl, ids, t), (ex, t)
+
+
+# ---- end-of-data accepts (\\z): LimEx acceptAtEOD / McClellan accept_eod, NFA_ACCEPTS_EOD (runtime.c:273-278) -----
+@pytest.mark.parametrize("engine", [litdb.ENGINE_LIMEX, litdb.ENGINE_MCCLELLAN, litdb.ENGINE_MCCLELLAN_SHERMAN])
+@pytest.mark.parametrize("seed", range(10))
+def test_eod_patterns_match_brute_force(ref, seed, engine):
+    rng = random.Random(3000 + seed)
+    ex, fl, ids, smp = regen.random_set(rng, rng.randint(2, 6), True)
+    ex = regen.with_eod(rng, ex)
+    try:
+        db = litdb.compile_regex_multi(ex, fl, ids, engine=engine)
+    except litdb.CompileError as e:
+        assert "too large" in str(e)
+        return
+    texts = []
+    for k in range(6):
+        t = regen.random_text(rng, ex, rng.choice([20, 60, 140]), smp)
+        if smp and k % 2 == 0:   # end the text with a sample of one of the patterns, so that \\z patterns fire
+            x = smp[k % len(smp)]
+            t = t[:max(0, len(t) - len(x))] + x
+        texts.append(t)
+    got = _scan_ref(ref, db, texts)
+    n = 0
+    for t, g in zip(texts, got):
+        assert g == regen.brute_force(ex, fl, ids, t), (ex, fl, t)
+        n += len(g)

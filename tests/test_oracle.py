@@ -215,3 +215,22 @@ def test_mcclellan_port_vs_live_reference_runtime(ref):
             assert rv == rv2 == 0 and got == exp, (seed, n)   # same callback ORDER too (report-list order)
         done += 1
     assert done > 20
+
+
+# ---- end-of-data accepts: LimEx acceptAtEOD and McClellan accept_eod through the C restatement --------------------
+def test_port_vs_recorded_eod_cases():
+    import json
+    import os
+    from vectorscan_b200 import litdb
+    with open(os.path.join(os.path.dirname(__file__), "golden", "ref_eod_cases.json")) as f:
+        cases = json.load(f)
+    n_eod, engines = 0, set()
+    for c in cases:
+        db = litdb.compile_regex_multi([e.encode("latin-1") for e in c["exprs"]], c["flags"], c["ids"], engine=c["engine"])
+        assert db.outfix_engine_type() == c["type"]
+        engines.add(c["engine"])
+        for t, exp in zip(c["texts"], c["expect"]):
+            rv, got = oracle_port.scan(db, bytes.fromhex(t))
+            assert rv == 0 and sorted(set(got), key=lambda x: (x[1], x[0])) == [tuple(x) for x in exp], c["seed"]
+        n_eod += c["eod_matches"]
+    assert engines == {0, 1, 2} and n_eod >= 20

@@ -382,6 +382,8 @@ struct Automaton {
     std::vector<CharSet> reach_of;     // bytes on which a state may be entered
     std::vector<StateSet> succ;        // successors of each state
     std::vector<u32> report_of;        // pattern index + 1 a state reports, 0 = none
+    std::vector<u32> report_eod_of;    // same, for patterns ending in \z: reported only at the end of the data
+    bool any_eod = false;
     StateSet init, init_ds;
     u32 min_width = ~0u;
 };
@@ -394,6 +396,7 @@ struct Dfa {
     u32 n_sym = 0;
     std::vector<std::vector<u32>> next;        // [state][symbol]
     std::vector<std::vector<u32>> reports;     // [state] sorted pattern indices accepted on entering the state
+    std::vector<std::vector<u32>> reports_eod; // [state] ... accepted only if the data ends in this state
     u32 start_anchored = 0, start_floating = 0;
 };
 
@@ -427,10 +430,14 @@ bool determinise(const Automaton &am, const std::vector<StateSet> &reach_rows, D
     }
     if (subset.size() > max_states) return false;
     d.reports.assign(subset.size(), {});
+    d.reports_eod.assign(subset.size(), {});
     for (u32 i = 0; i < subset.size(); i++) {
         std::set<u32> r;
         for (u32 s = 0; s < am.n_states; s++) if (subset[i].test(s) && am.report_of[s]) r.insert(am.report_of[s] - 1);
         d.reports[i].assign(r.begin(), r.end());
+        std::set<u32> re;
+        for (u32 s = 0; s < am.n_states; s++) if (subset[i].test(s) && am.report_eod_of[s]) re.insert(am.report_eod_of[s] - 1);
+        d.reports_eod[i].assign(re.begin(), re.end());
     }
     return true;
 }
@@ -440,10 +447,11 @@ void minimise(Dfa &d) {
     const u32 n = (u32)d.next.size();
     std::vector<u32> cls(n);
     {
-        std::map<std::vector<u32>, u32> by_rep;
+        std::map<std::pair<std::vector<u32>, std::vector<u32>>, u32> by_rep;
         for (u32 i = 0; i < n; i++) {
-            auto it = by_rep.find(d.reports[i]);
-            if (it == by_rep.end()) it = by_rep.emplace(d.reports[i], (u32)by_rep.size()).first;
+            const auto key = std::make_pair(d.reports[i], d.reports_eod[i]);
+            auto it = by_rep.find(key);
+            if (it == by_rep.end()) it = by_rep.emplace(key, (u32)by_rep.size()).first;
             cls[i] = it->second;
         }
     }
@@ -485,11 +493,13 @@ void minimise(Dfa &d) {
     m.n_sym = d.n_sym;
     m.next.resize(order.size());
     m.reports.resize(order.size());
+    m.reports_eod.resize(order.size());
     for (u32 q = 0; q < order.size(); q++) {
         const u32 r = rep_of_class[order[q]];
         m.next[q].resize(d.n_sym);
         for (u32 k = 0; k < d.n_sym; k++) m.next[q][k] = new_id[cls[d.next[r][k]]];
         m.reports[q] = d.reports[r];
+        m.reports_eod[q] = d.reports_eod[r];
     }
     m.start_anchored = new_id[cls[d.start_anchored]];
     m.start_floating = new_id[cls[d.start_floating]];
@@ -564,6 +574,19 @@ int emit_mcclellan(const Dfa &d, const u8 *reach_map, const std::vector<u32> &pr
         if (it == list_id.end()) { it = list_id.emplace(l, (u32)lists.size()).first; lists.push_back(l); }
         list_of[i] = it->second;
     }
+    std::vector<u32> list_eod_of(n, ~0u);
+    bool any_eod = false;
+    for (u32 i = 0; i < n; i++) {
+        if (d.reports_eod[i].empty()) continue;
+        any_eod = true;
+        std::set<u32> ps;
+        for (u32 pi : d.reports_eod[i]) ps.insert(program_of[pi]);
+        std::vector<u32> l(ps.begin(), ps.end());
+        all_reports.insert(l.begin(), l.end());
+        auto it = list_id.find(l);
+        if (it == list_id.end()) { it = list_id.emplace(l, (u32)lists.size()).first; lists.push_back(l); }
+        list_eod_of[i] = it->second;
+    }
     const bool single = all_reports.size() == 1;
     // ---- sizes (mcclellancompile.cpp:637-652 / :934-940) ----
     const size_t ent = wide16 ? 2 : 1;
@@ -579,7 +602,7 @@ int emit_mcclellan(const Dfa &d, const u8 *reach_map, const std::vector<u32> &pr
     eng.grow(total);
     eng.align(CACHELINE);
     u8 *nh = eng.at(0), *m = eng.at(nfa::SIZE);
-    wr32(nh, nfa::flags, 0);
+    wr32(nh, nfa::flags, any_eod ? nfa::ACCEPTS_EOD : 0);  // mcclellancompile.cpp:1513-1515
     wr32(nh, nfa::length, (u32)eng.size());
     wr8(nh, nfa::type, wide16 ? nfa::MCCLELLAN_16 : nfa::MCCLELLAN_8);
     wr32(nh, nfa::queueIndex, 0);
@@ -628,7 +651,7 @@ int emit_mcclellan(const Dfa &d, const u8 *reach_map, const std::vector<u32> &pr
         const u32 id = impl[i];
         u8 *a = eng.at(aux_offset + mc::aux::SIZE * (size_t)id);
         wr32(a, mc::aux::accept, list_of[i] == ~0u ? 0 : list_off[list_of[i]]);
-        wr32(a, mc::aux::accept_eod, 0);
+        wr32(a, mc::aux::accept_eod, list_eod_of[i] == ~0u ? 0 : list_off[list_eod_of[i]]);
         wr16(a, mc::aux::top, (u16)impl[i ? d.start_floating : d.start_floating]);
         wr32(a, mc::aux::accel_offset, 0);
         if (wide16 && is_sherman[i]) {
@@ -663,7 +686,7 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
     // ---- 1. parse every pattern, build one automaton -------------------------------------------------
     Automaton am;
     bool any_unanch = false, any_anch = false;
-    struct Parsed { Glushkov g; Glushkov::Info info; bool anchored; };
+    struct Parsed { Glushkov g; Glushkov::Info info; bool anchored, eod; };
     std::vector<Parsed> parsed;
     for (size_t pi = 0; pi < pats.size(); pi++) {
         const Pattern &p = pats[pi];
@@ -674,6 +697,10 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
         std::string body = p.expr;
         bool anchored = false;
         if (!body.empty() && body[0] == '^') { anchored = true; body.erase(0, 1); }
+        // a trailing \\z: the match must end where the data ends (reported by the engine's EOD accepts)
+        bool eod = false;
+        if (body.size() >= 2 && body.compare(body.size() - 2, 2, "\\z") == 0 &&
+            (body.size() < 3 || body[body.size() - 3] != '\\')) { eod = true; body.erase(body.size() - 2); }
         Parser ps(body, (p.flags & HSB_FLAG_CASELESS) != 0, (p.flags & HSB_FLAG_DOTALL) != 0);
         const int root = ps.parse_alt();
         if (root < 0 || !ps.eof()) {
@@ -684,6 +711,7 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
         if (ps.n_char_nodes > MAX_STATES) { err = "pattern set too large for one LimEx NFA"; return HSB_LIT_COMPILER_ERROR; }
         Parsed pr;
         pr.anchored = anchored;
+        pr.eod = eod;
         pr.info = pr.g.build(ps.nodes, root);
         if (pr.info.nullable) {
             err = "expression " + std::to_string(pi) + ": matches the empty string (not supported)";
@@ -699,6 +727,7 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
     am.reach_of.assign(total, CharSet());
     am.succ.assign(total, StateSet());
     am.report_of.assign(total, 0);
+    am.report_eod_of.assign(total, 0);
     u32 next = 0;
     const u32 st_ds = any_unanch ? next++ : ~0u, st_anch = any_anch ? next++ : ~0u;
     if (any_unanch) {
@@ -715,7 +744,8 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
         for (u32 p = 0; p < n; p++) {
             am.reach_of[base + p] = pr.g.cls[p];
             for (u32 q = 0; q < n; q++) if (pr.g.follow[p].test(q)) am.succ[base + p].set(base + q);
-            if (pr.info.last.test(p)) am.report_of[base + p] = (u32)pi + 1;
+            if (pr.info.last.test(p)) (pr.eod ? am.report_eod_of : am.report_of)[base + p] = (u32)pi + 1;
+            if (pr.eod) am.any_eod = true;
             if (pr.info.first.test(p)) am.succ[pr.anchored ? st_anch : st_ds].set(base + p);
         }
         am.min_width = std::min(am.min_width, pr.info.min_len);
@@ -740,7 +770,7 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
     std::sort(shifts.begin(), shifts.end());
     std::vector<StateSet> shift_mask(shifts.size());
     std::vector<StateSet> exc_succ(am.n_states);
-    StateSet exception_mask, accept_mask;
+    StateSet exception_mask, accept_mask, accept_eod_mask;
     for (u32 s = 0; s < am.n_states; s++) {
         for (u32 t = 0; t < am.n_states; t++) {
             if (!am.succ[s].test(t)) continue;
@@ -752,6 +782,7 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
             if (!shifted) { exc_succ[s].set(t); exception_mask.set(s); }
         }
         if (am.report_of[s]) { exception_mask.set(s); accept_mask.set(s); }
+        if (am.report_eod_of[s]) accept_eod_mask.set(s);  // EOD accepts fire from the accept table only
     }
     // reach table: distinct per-byte masks
     std::vector<StateSet> reach_rows;
@@ -820,9 +851,10 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
     eng.align(16);
     const size_t accel_aux_off = eng.grow(hwlm::ACCEL_AUX_SIZE);  // aux[0] = ACCEL_NONE
     eng.align(4);
-    std::vector<u32> accept_states, exc_states;
+    std::vector<u32> accept_states, accept_eod_states, exc_states;
     for (u32 s = 0; s < am.n_states; s++) {
         if (accept_mask.test(s)) accept_states.push_back(s);
+        if (accept_eod_mask.test(s)) accept_eod_states.push_back(s);
         if (exception_mask.test(s)) exc_states.push_back(s);
     }
     const size_t accept_off = eng.grow(accept_states.size() * nfaaccept::SIZE);
@@ -830,6 +862,13 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
         u8 *a = eng.at(accept_off + i * nfaaccept::SIZE);
         wr8(a, nfaaccept::single_report, 1);
         wr32(a, nfaaccept::reports, program_of[am.report_of[accept_states[i]] - 1]);
+        wr32(a, nfaaccept::squash, 0xffffffffu);
+    }
+    const size_t accept_eod_off = eng.grow(accept_eod_states.size() * nfaaccept::SIZE);
+    for (size_t i = 0; i < accept_eod_states.size(); i++) {
+        u8 *a = eng.at(accept_eod_off + i * nfaaccept::SIZE);
+        wr8(a, nfaaccept::single_report, 1);
+        wr32(a, nfaaccept::reports, program_of[am.report_eod_of[accept_eod_states[i]] - 1]);
         wr32(a, nfaaccept::squash, 0xffffffffu);
     }
     // report lists for the exceptions: {program offset, MO_INVALID_IDX} per pattern
@@ -858,7 +897,7 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
     eng.align(CACHELINE);
     // struct NFA
     u8 *nh = eng.at(0);
-    wr32(nh, nfa::flags, 0);
+    wr32(nh, nfa::flags, am.any_eod ? nfa::ACCEPTS_EOD : 0);
     wr32(nh, nfa::length, (u32)eng.size());
     wr8(nh, nfa::type, (u8)type);
     wr32(nh, nfa::queueIndex, 0);
@@ -879,8 +918,8 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
     wr32(lp, limex::accelAuxOffset, (u32)(accel_aux_off - lx));
     wr32(lp, limex::acceptCount, (u32)accept_states.size());
     wr32(lp, limex::acceptOffset, (u32)(accept_off - lx));
-    wr32(lp, limex::acceptEodCount, 0);
-    wr32(lp, limex::acceptEodOffset, (u32)(accept_off - lx));
+    wr32(lp, limex::acceptEodCount, (u32)accept_eod_states.size());
+    wr32(lp, limex::acceptEodOffset, (u32)(accept_eod_off - lx));
     wr32(lp, limex::exceptionCount, (u32)exc_states.size());
     wr32(lp, limex::exceptionOffset, (u32)(exc_off - lx));
     wr32(lp, limex::repeatCount, 0);
@@ -896,6 +935,7 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
     put_state(lp + L.init, am.init, L.bytes);
     put_state(lp + L.initDS, am.init_ds, L.bytes);
     put_state(lp + L.accept, accept_mask, L.bytes);
+    put_state(lp + L.acceptAtEOD, accept_eod_mask, L.bytes);
     put_state(lp + L.compressMask, all, L.bytes);
     put_state(lp + L.exceptionMask, exception_mask, L.bytes);
     for (size_t k = 0; k < shifts.size(); k++) {
