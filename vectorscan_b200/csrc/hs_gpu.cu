@@ -759,6 +759,74 @@ struct RecDup {  // equal = second is a dedupe-key duplicate of the first
     }
 };
 
+// Small batches of records (the usual case for regex databases: a few matches per MiB): sort, dedupe, compact and
+// convert in ONE single-CTA kernel -- a block merge sort with the records in registers -- instead of the device-wide
+// merge sort + select chain (five launches and a host round trip for the count: ~55 us for a thousand records).
+constexpr u32 SMALL_FIN_MAX = 4096, SMALL_FIN_ITEMS = 4;
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS) k_small_finalize(const Rec *in, Rec *out_recs, hs_gpu_match_t *out,
+                                                             unsigned long long *n_out,
+                                                             const unsigned long long *n_raw, u64 arena_cap) {
+    // launched right behind the scan, before the host knows the record count: do nothing when it is outside this
+    // kernel's envelope (the host then runs the general finalize) or when the arena overflowed (the scan is repeated)
+    const unsigned long long raw = *n_raw;
+    if (raw == 0 || raw > (unsigned long long)(THREADS * SMALL_FIN_ITEMS) || raw > arena_cap) {
+        if (threadIdx.x == 0) *n_out = raw ? ~0ull : 0ull;
+        return;
+    }
+    const u32 n = (u32)raw;
+    using Sort = cub::BlockMergeSort<Rec, THREADS, SMALL_FIN_ITEMS>;
+    using Scan = cub::BlockScan<u32, THREADS>;
+    extern __shared__ __align__(16) u8 fin_smem[];
+    typename Sort::TempStorage &sort_tmp = *reinterpret_cast<typename Sort::TempStorage *>(fin_smem);
+    __shared__ typename Scan::TempStorage scan_tmp;
+    __shared__ Rec last_of[THREADS];
+    const u32 tid = threadIdx.x;
+    Rec it[SMALL_FIN_ITEMS];
+#pragma unroll
+    for (u32 q = 0; q < SMALL_FIN_ITEMS; q++) {
+        const u32 i = tid * SMALL_FIN_ITEMS + q;
+        it[q] = i < n ? in[i] : Rec{0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};  // sorts behind every record
+    }
+    Sort(sort_tmp).Sort(it, RecLess());   // blocked arrangement: thread t holds sorted positions 4t .. 4t+3
+    last_of[tid] = it[SMALL_FIN_ITEMS - 1];
+    __syncthreads();
+    u32 keep = 0, cnt = 0;
+#pragma unroll
+    for (u32 q = 0; q < SMALL_FIN_ITEMS; q++) {
+        const u32 i = tid * SMALL_FIN_ITEMS + q;
+        bool dup = false;
+        if (q) dup = RecDup()(it[q - 1], it[q]);
+        else if (tid) dup = RecDup()(last_of[tid - 1], it[0]);
+        if (i < n && !dup) { keep |= 1u << q; cnt++; }
+    }
+    u32 base = 0, total = 0;
+    Scan(scan_tmp).ExclusiveSum(cnt, base, total);
+#pragma unroll
+    for (u32 q = 0; q < SMALL_FIN_ITEMS; q++)
+        if ((keep >> q) & 1u) {
+            out_recs[base] = it[q];
+            out[base] = hs_gpu_match_t{it[q].buf, it[q].id, (uint64_t)it[q].to};
+            base++;
+        }
+    if (tid == 0) *n_out = total;
+}
+
+template <int THREADS>
+cudaError_t launch_small_finalize(cudaStream_t st, const Rec *in, Rec *out_recs, hs_gpu_match_t *out, unsigned long long *n_out,
+                                  const unsigned long long *n_raw, u64 arena_cap) {
+    using Sort = cub::BlockMergeSort<Rec, THREADS, SMALL_FIN_ITEMS>;
+    const size_t dyn = sizeof(typename Sort::TempStorage);
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(k_small_finalize<THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+        if (e != cudaSuccess) return e;
+        configured = true;
+    }
+    k_small_finalize<THREADS><<<1, THREADS, dyn, st>>>(in, out_recs, out, n_out, n_raw, arena_cap);
+    return cudaGetLastError();
+}
+
 // keep[i] = 0 iff record i repeats record i-1 under a dedupe key (dedupeCatchup, src/report.h:83-93)
 __global__ void k_flag_dups(const Rec *in, u8 *keep, u64 n) {
     const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
@@ -913,6 +981,7 @@ struct hs_gpu_scratch {
     long opt_frontend = 0;
     long opt_grid = 0;
     u64 arena_hint = 1 << 16;
+    u64 last_raw = ~0ull;  // record count of the previous scan (picks the finalize kernel size)
     u64 lx_event_hint = 1 << 16;
 };
 
@@ -1249,7 +1318,10 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
         // fell out of the ordered mode's envelope (collector or segment bounds): use the general path below
     }
     CU_OK(s->recs.reserve(s->arena_hint));
+    CU_OK(s->recs2.reserve(SMALL_FIN_MAX));     // before the launch: the event queue of the NFA/DFA kernels lives here too
+    CU_OK(s->d_matches.reserve(SMALL_FIN_MAX));
     u64 raw = 0;
+    bool small_done = false;
     CU_OK(cudaEventRecord(s->ev[1], s->stream));
     for (int attempt = 0;; attempt++) {
         CU_OK(cudaMemsetAsync(s->d_ctl, 0, 8 * sizeof(unsigned long long), s->stream));
@@ -1276,6 +1348,14 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
         CU_OK(cudaEventRecord(s->ev[7], s->stream));
         st.scan_launches++;
         st.kernel_launches++;
+        // Few records are the rule for regex databases: the single-CTA finalize goes in right behind the scan and
+        // decides on the device whether it applies, so the whole scan costs ONE host round trip.
+        CU_OK(cudaEventRecord(s->ev[2], s->stream));
+        if (s->last_raw <= 256 * SMALL_FIN_ITEMS)
+            CU_OK(launch_small_finalize<256>(s->stream, s->recs.p, s->recs2.p, s->d_matches.p, s->d_ctl + 4, s->d_ctl + 0, s->recs.cap));
+        else
+            CU_OK(launch_small_finalize<1024>(s->stream, s->recs.p, s->recs2.p, s->d_matches.p, s->d_ctl + 4, s->d_ctl + 0, s->recs.cap));
+        CU_OK(cudaEventRecord(s->ev[3], s->stream));
         CU_OK(cudaMemcpyAsync(s->h_ctl, s->d_ctl, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
         CU_OK(cudaStreamSynchronize(s->stream));
         if ((u32)s->h_ctl[3]) {
@@ -1289,18 +1369,22 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
             s->lx_event_hint = s->h_ctl[7] + s->h_ctl[7] / 8 + 1024;
             continue;
         }
-        if (raw <= s->recs.cap) break;
+        s->last_raw = raw;
+        if (raw <= s->recs.cap) { small_done = s->h_ctl[4] != ~0ull; break; }
         if (attempt >= 3) return HS_NOMEM;
         st.arena_retries++;
         s->arena_hint = raw + raw / 8 + 1024;
         CU_OK(s->recs.reserve(s->arena_hint));
     }
-    CU_OK(cudaEventRecord(s->ev[2], s->stream));
+    if (!small_done) CU_OK(cudaEventRecord(s->ev[2], s->stream));
     st.raw_matches = raw;
     st.candidates = s->h_ctl[1];
     st.confirms = s->h_ctl[2];
     u64 n_out = 0;
-    if (raw) {
+    if (small_done) {
+        n_out = s->h_ctl[4];
+        st.kernel_launches += 1;
+    } else if (raw) {
         size_t tmp1 = 0, tmp2 = 0;
         CU_OK(s->recs2.reserve(raw));
         CU_OK(s->d_matches.reserve(raw));
@@ -1323,8 +1407,10 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
         CU_OK(cudaGetLastError());
         st.kernel_launches += 2;  // k_flag_dups + k_convert (CUB's sort/select kernels are not counted)
     }
-    CU_OK(cudaEventRecord(s->ev[3], s->stream));
-    CU_OK(cudaEventSynchronize(s->ev[3]));
+    if (!small_done) {
+        CU_OK(cudaEventRecord(s->ev[3], s->stream));
+        CU_OK(cudaEventSynchronize(s->ev[3]));
+    }
     cudaEventElapsedTime(&st.scan_ms, s->ev[1], s->ev[2]);
     cudaEventElapsedTime(&st.kernel_ms, s->ev[6], s->ev[7]);  // the last (successful) k_scan launch alone
     cudaEventElapsedTime(&st.sort_ms, s->ev[2], s->ev[3]);
