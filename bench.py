@@ -101,9 +101,32 @@ class ClockSampler:
     def __init__(self, dev):
         self.dev, self.samples, self.reasons, self.maxmhz = dev, [], set(), None
         self._stop = threading.Event()
+        self._ready = threading.Event()
+        self._go = threading.Event()
         self._t = threading.Thread(target=self._run, daemon=True)
 
     def _run(self):
+        # NVML in-process (one init, then ~20 us per sample): spawning nvidia-smi inside the timed region, once per rank,
+        # initialises the driver for every GPU and delays the launches being timed
+        try:
+            import pynvml as N
+            N.nvmlInit()
+            h = N.nvmlDeviceGetHandleByIndex(self.dev)
+            self.maxmhz = float(N.nvmlDeviceGetMaxClockInfo(h, N.NVML_CLOCK_SM))
+            get_reasons = getattr(N, "nvmlDeviceGetCurrentClocksEventReasons", None) or N.nvmlDeviceGetCurrentClocksThrottleReasons
+            bits = {"hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40, "sw_power_cap": 0x4}
+            self._ready.set()
+            self._go.wait()
+            while not self._stop.is_set():
+                self.samples.append(float(N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM)))
+                r = int(get_reasons(h))
+                for n, b in bits.items():
+                    if r & b:
+                        self.reasons.add(n)
+                self._stop.wait(0.001)
+            return
+        except Exception:
+            self._ready.set()
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
@@ -122,9 +145,14 @@ class ClockSampler:
 
     def start(self):
         self._t.start()
+        self._ready.wait(timeout=10)   # NVML initialised before the timed region begins
+
+    def go(self):
+        self._go.set()
 
     def stop(self):
         self._stop.set()
+        self._go.set()
         self._t.join(timeout=6)
         s = sorted(self.samples)
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.maxmhz, "reasons": sorted(self.reasons),
@@ -243,8 +271,9 @@ def main():
     for w in range(max(args.warmup, 3)):
         gpu.scan_corpus(db, corpora[w % ROT], sc)
     sampler = ClockSampler(local_rank)
-    barrier()
     sampler.start()
+    barrier()
+    sampler.go()
     dev_ms = kern_ms = 0.0
     nmatch = raw = launches = nbytes_scanned = cands = probes = 0
     t0 = time.perf_counter()

@@ -68,6 +68,7 @@ int hsb_compile_regex_multi(const char *const *expressions, const unsigned *flag
 #define HSB_REGEX_ENGINE_LIMEX 0u
 #define HSB_REGEX_ENGINE_MCCLELLAN 1u
 #define HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN 2u
+#define HSB_REGEX_ENGINE_SHENG 3u /* DFA of <= 16 states as byte-shuffle masks (src/nfa/sheng_internal.h) */
 int hsb_compile_regex_multi_ex(const char *const *expressions, const unsigned *flags, const unsigned *ids,
                                unsigned elements, unsigned mode, unsigned engine, hs_database_t **db,
                                char **error);

@@ -19,6 +19,9 @@
 #include "nfa/limex_internal.h"
 #include "nfa/accel.h"
 #include "nfa/mcclellan_internal.h"
+#define report_list report_list_sheng /* both engine headers define struct report_list */
+#include "nfa/sheng_internal.h"
+#undef report_list
 #include "util/multibit_internal.h"
 #include "hs_compile.h"
 
@@ -231,6 +234,14 @@ int main(void) {
  SZ(struct NFAAccept); OF(struct NFAAccept, single_report); OF(struct NFAAccept, reports); OF(struct NFAAccept, squash);
  SZ(struct NfaInfo); OF(struct NfaInfo, nfaOffset); OF(struct NfaInfo, stateOffset); OF(struct NfaInfo, fullStateOffset); 
  OF(struct NfaInfo, no_retrigger); OF(struct NfaInfo, in_sbmatcher); OF(struct NfaInfo, eod);
+ /* Sheng DFA */
+ VAL(SHENG_NFA); VAL(SHENG_STATE_ACCEPT); VAL(SHENG_STATE_DEAD); VAL(SHENG_STATE_ACCEL); VAL(SHENG_STATE_MASK);
+ VAL(SHENG_FLAG_SINGLE_REPORT); VAL(SHENG_FLAG_CAN_DIE); VAL(SHENG_FLAG_HAS_ACCEL);
+ SZ(struct sheng); OF(struct sheng, shuffle_masks); OF(struct sheng, length); OF(struct sheng, aux_offset);
+ OF(struct sheng, report_offset); OF(struct sheng, accel_offset); OF(struct sheng, n_states); OF(struct sheng, anchored);
+ OF(struct sheng, floating); OF(struct sheng, flags); OF(struct sheng, report);
+ SZ(struct sstate_aux); OF(struct sstate_aux, accept); OF(struct sstate_aux, accept_eod); OF(struct sstate_aux, accel);
+ OF(struct sstate_aux, top);
  /* McClellan DFA */
  VAL(MCCLELLAN_NFA_8); VAL(MCCLELLAN_NFA_16); VAL(ACCEPT_FLAG); VAL(ACCEL_FLAG); VAL(STATE_MASK); VAL(MCCLELLAN_FLAG_SINGLE);
  VAL(SHERMAN_STATE); VAL(SHERMAN_FIXED_SIZE); VAL(SHERMAN_LEN_OFFSET); VAL(SHERMAN_DADDY_OFFSET); VAL(SHERMAN_CHARS_OFFSET);

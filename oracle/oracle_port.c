@@ -407,7 +407,44 @@ static int mcclellan_scan(struct scan_state *s, const u8 *nfa) {
     return 0;
 }
 
-/* hs_scan for block-mode pure-literal and single-outfix (LimEx or McClellan) databases.  `db` = in-memory hs_database_t. */
+/* ------------------------------------------------------------------------------------------------------------
+ * Sheng DFA (<= 16 states), sole-outfix block run: src/runtime.c:246-279 -> nfaExecSheng_Q -> runSheng
+ * (sheng.c:510-700: MQE_TOP at offset 0 sets state = sh->anchored) -> runShengCb (:359-408) -> SHENG_IMPL
+ * (sheng_impl.h:40-97: state = shuffle_masks[c][state]; ACCEPT flag -> fireSingleReport / fireReports, sheng.c:106-157),
+ * MQE_END returns MO_DEAD for a dead state when SHENG_FLAG_CAN_DIE (:672-677), which skips the EOD check of
+ * runtime.c:273; otherwise nfaExecSheng_testEOD (:796-812).  Layout: sheng_internal.h:56-79. */
+enum { SH_MASKS = 0, SH_AUX_OFFSET = 4100, SH_ANCHORED = 4113, SH_FLAGS = 4115, SH_REPORT = 4116 };
+
+static int sh_report(struct scan_state *s, const u8 *nfa, const u8 *sh, u8 st, u64 loc, int eod) {
+    if (!eod && (sh[SH_FLAGS] & 1)) return run_program(s, rd32(sh + SH_REPORT), loc);      /* SHENG_FLAG_SINGLE_REPORT */
+    const u8 *aux = nfa + rd32(sh + SH_AUX_OFFSET) + (size_t)(st & 0xf) * 16;             /* struct sstate_aux */
+    u32 off = rd32(aux + (eod ? 4 : 0));
+    if (!off) return 0;
+    const u8 *rl = nfa + off;
+    for (u32 i = 0, n = rd32(rl); i < n; i++)
+        if (run_program(s, rd32(rl + 4 + 4 * (size_t)i), loc) < 0) return -1;
+    return 0;
+}
+
+static int sheng_scan(struct scan_state *s, const u8 *nfa) {
+    const u8 *sh = nfa + NFA_SIZE;
+    if (nfa[NFA_RACCEL]) { s->error = 1; return -1; }
+    const int can_die = (sh[SH_FLAGS] & 2) != 0;
+    u8 st = sh[SH_ANCHORED];
+    for (u32 i = 0; i < s->len; i++) {
+        if (st & 0x20) break;                                   /* SHENG_STATE_DEAD: every successor is the same state */
+        st = sh[SH_MASKS + 16 * (size_t)s->buf[i] + (st & 0xf)];
+        if ((st & 0x10) && sh_report(s, nfa, sh, st, (u64)i + 1, 0) < 0) return -1;
+    }
+    if (can_die && (st & 0x20)) return 0;                       /* MO_DEAD: no final-state check */
+    if (rd32(nfa + NFA_FLAGS) & NFA_ACCEPTS_EOD) {
+        const u8 *aux = nfa + rd32(sh + SH_AUX_OFFSET) + (size_t)(st & 0xf) * 16;
+        if (rd32(aux + 4) && sh_report(s, nfa, sh, st, s->len, 1) < 0) return -1;
+    }
+    return 0;
+}
+
+/* hs_scan for block-mode pure-literal and single-outfix (LimEx, McClellan or Sheng) databases.  `db` = in-memory hs_database_t. */
 int op_scan(const void *db, const char *data, unsigned length, op_match_cb cb, void *ctx) {
     const u8 *d = (const u8 *)db;
     if (!d || !data || rd32(d + DB_MAGIC_OFF) != 0xdbdbdbdbu) return HS_INVALID;
@@ -432,6 +469,7 @@ int op_scan(const void *db, const char *data, unsigned length, op_match_cb cb, v
     if (rose[R_RUNTIME_IMPL] == 2) {
         const u8 *nfa = rose + rd32(rose + rd32(rose + R_NFA_INFO) + NI_NFA_OFF);
         if (nfa[NFA_TYPE] == 6 || nfa[NFA_TYPE] == 7) mcclellan_scan(&s, nfa);
+        else if (nfa[NFA_TYPE] == 17) sheng_scan(&s, nfa);
         else limex_scan(&s, nfa);
     }
     else hwlm_exec(&s, rose + rd32(rose + R_FMATCHER));

@@ -1,0 +1,60 @@
+"""GPU tests (-m gpu): Sheng DFA engines (<= 16 states, sheng_internal.h) through the C ABI.  The device path re-lays
+the 256 shuffle masks as a state-major table at upload and steps it with k_mcclellan (csrc/hs_gpu.cu
+build_sheng_tables).  Against matches recorded from the unmodified reference runtime
+(tests/golden/ref_sheng_cases.json), the live reference runtime and the `re` brute force."""
+import json
+import os
+import random
+
+import pytest
+
+import regen
+from vectorscan_b200 import gpu, litdb
+from test_gpu_limex import gpu_batch, ref_batch
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def test_recorded_sheng_cases():
+    with open(os.path.join(GOLD, "ref_sheng_cases.json")) as f:
+        cases = json.load(f)
+    n = 0
+    for c in cases:
+        db = litdb.compile_regex_multi([e.encode("latin-1") for e in c["exprs"]], c["flags"], c["ids"], engine=c["engine"])
+        assert db.outfix_engine_type() == 17
+        bufs = [bytes.fromhex(t) for t in c["texts"]]
+        exp = [(bi, i, t) for bi, m in enumerate(c["expect"]) for (i, t) in m]
+        assert gpu_batch(db, bufs) == exp, c["seed"]
+        n += len(exp)
+    assert n > 300
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_sheng_batches_vs_live_reference(ref, seed):
+    rng = random.Random(7300 + seed)
+    for _ in range(400):
+        ex, fl, ids, smp = regen.random_set(rng, rng.randint(1, 3), True)
+        ex = regen.with_eod(rng, ex, 0.3)
+        try:
+            db = litdb.compile_regex_multi(ex, fl, ids, engine=litdb.ENGINE_SHENG)
+            break
+        except litdb.CompileError:
+            continue
+    bufs = []
+    for k in range(800):
+        t = regen.random_text(rng, ex, rng.choice([0, 1, 15, 16, 17, 64, 300, 1400]), smp)
+        if smp and k % 3 == 0:
+            x = smp[k % len(smp)]
+            t = t[:max(0, len(t) - len(x))] + x
+        bufs.append(t)
+    got = gpu_batch(db, bufs)
+    assert got == ref_batch(ref, db, bufs) and len(got) > 20
+
+
+def test_sheng_anchored_only_dies(ref):
+    ex = [b"^GET /a", b"^POST"]
+    db = litdb.compile_regex_multi(ex, [0, 0], [1, 2], engine=litdb.ENGINE_SHENG)
+    bufs = [b"GET /a/b", b"POST /x", b"xGET /a", b"", b"GET /" + b"a" * 5000]
+    got = gpu_batch(db, bufs)
+    assert got == ref_batch(ref, db, bufs) and len(got) == 3

@@ -118,3 +118,23 @@ def test_eod_patterns_match_brute_force(ref, seed, engine):
     for t, g in zip(texts, got):
         assert g == regen.brute_force(ex, fl, ids, t), (ex, fl, t)
         n += len(g)
+
+
+# ---- Sheng engine (sheng_internal.h): DFAs of at most 16 states as byte-shuffle masks ------------------------------
+@pytest.mark.parametrize("seed", range(40))
+def test_sheng_sets_match_brute_force(ref, seed):
+    rng = random.Random(6000 + seed)
+    ex, fl, ids, smp = regen.random_set(rng, rng.randint(1, 3), True)
+    ex = regen.with_eod(rng, ex, 0.3)
+    try:
+        db = litdb.compile_regex_multi(ex, fl, ids, engine=litdb.ENGINE_SHENG)
+    except litdb.CompileError as e:
+        assert "too large" in str(e)
+        return
+    assert db.outfix_engine_type() == 17
+    texts = [regen.random_text(rng, ex, 120, smp) for _ in range(3)] + [b""]
+    if smp:
+        texts.append(regen.random_text(rng, ex, 40, smp)[:20] + smp[0])
+    got = _scan_ref(ref, db, texts)
+    for t, g in zip(texts, got):
+        assert g == regen.brute_force(ex, fl, ids, t), (ex, fl, t)

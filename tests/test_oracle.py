@@ -234,3 +234,39 @@ def test_port_vs_recorded_eod_cases():
             assert rv == 0 and sorted(set(got), key=lambda x: (x[1], x[0])) == [tuple(x) for x in exp], c["seed"]
         n_eod += c["eod_matches"]
     assert engines == {0, 1, 2} and n_eod >= 20
+
+
+# ---- Sheng DFA through the C restatement (sheng_scan) ----------------------------------------------------------
+def test_sheng_port_vs_recorded_cases_and_live_reference(ref):
+    import json
+    import os
+    import random
+    import regen
+    from vectorscan_b200 import litdb
+    with open(os.path.join(os.path.dirname(__file__), "golden", "ref_sheng_cases.json")) as f:
+        cases = json.load(f)
+    n = 0
+    for c in cases:
+        db = litdb.compile_regex_multi([e.encode("latin-1") for e in c["exprs"]], c["flags"], c["ids"], engine=c["engine"])
+        assert db.outfix_engine_type() == c["type"] == 17
+        for t, exp in zip(c["texts"], c["expect"]):
+            rv, got = oracle_port.scan(db, bytes.fromhex(t))
+            assert rv == 0 and sorted(set(got), key=lambda x: (x[1], x[0])) == [tuple(x) for x in exp], c["seed"]
+            n += len(exp)
+    assert n > 300
+    done = 0
+    for seed in range(300):
+        rng = random.Random(52000 + seed)
+        ex, fl, ids, smp = regen.random_set(rng, rng.randint(1, 3), True)
+        ex = regen.with_eod(rng, ex, 0.3)
+        try:
+            db = litdb.compile_regex_multi(ex, fl, ids, engine=litdb.ENGINE_SHENG)
+        except litdb.CompileError:
+            continue
+        rdb = ref.deserialize(db.serialize())
+        rs = ref.alloc_scratch(rdb)
+        for ln in (0, 1, 33, 500):
+            t = regen.random_text(rng, ex, ln, smp)
+            assert ref.scan(rdb, rs, t) == oracle_port.scan(db, t), (seed, ln)   # callback order included
+        done += 1
+    assert done > 20

@@ -989,6 +989,39 @@ namespace {
 
 std::mutex g_init_mutex;
 
+// Sheng -> state-major table (see the upload).  Reference semantics kept: state byte = id | flags
+// (shengcompile.cpp:343-357); a DEAD-flagged state is a trap without reports (census), so it may become state 0.
+void build_sheng_tables(const DbView &v, u32 at, std::vector<u8> &out, DevMcc &D) {
+    namespace sh = sheng;
+    const DbView::Sheng &S = v.sheng;
+    const u8 *m = v.bc + S.sh_off;
+    const u32 n = S.n_states;
+    bool dead[16] = {false}, acc[16] = {false};
+    auto note = [&](u8 e) { if (e & sh::STATE_DEAD) dead[e & sh::STATE_MASK] = true; };
+    note((u8)S.anchored);
+    for (u32 c = 0; c < 256; c++) for (u32 st = 0; st < n; st++) note(m[sh::shuffle_masks + 16 * c + st]);
+    for (u32 st = 0; st < n; st++) acc[st] = rd32(v.bc, S.aux_off + st * sh::aux::SIZE + sh::aux::accept) != 0;
+    u32 new_of[16], old_of[17], next = 1;
+    for (u32 st = 0; st < n; st++) if (dead[st]) new_of[st] = 0;
+    for (u32 st = 0; st < n; st++) if (!dead[st] && !acc[st]) { old_of[next] = st; new_of[st] = next++; }
+    const u32 accept_limit = next;
+    for (u32 st = 0; st < n; st++) if (!dead[st] && acc[st]) { old_of[next] = st; new_of[st] = next++; }
+    const u32 rows = next, tab_bytes = rows * 256;
+    out.assign(256 + tab_bytes + rows * mcclellan::aux::SIZE, 0);
+    for (u32 c = 0; c < 256; c++) out[c] = (u8)c;  // remap: identity, alphaShift 8
+    for (u32 q = 1; q < rows; q++) {
+        for (u32 c = 0; c < 256; c++) out[256 + q * 256 + c] = (u8)new_of[m[sh::shuffle_masks + 16 * c + old_of[q]] & sh::STATE_MASK];
+        u8 *a = out.data() + 256 + tab_bytes + q * mcclellan::aux::SIZE;
+        wr32(a, mcclellan::aux::accept, rd32(v.bc, S.aux_off + old_of[q] * sh::aux::SIZE + sh::aux::accept));
+        wr32(a, mcclellan::aux::accept_eod, rd32(v.bc, S.aux_off + old_of[q] * sh::aux::SIZE + sh::aux::accept_eod));
+    }
+    D = DevMcc{};
+    D.remap_abs = at; D.tab_abs = at + 256; D.tab_bytes = tab_bytes; D.aux_abs = at + 256 + tab_bytes;
+    D.nfa_abs = v.nfa_off; D.sherman_abs = 0; D.wide16 = 0; D.as = 8; D.start = new_of[S.anchored & sh::STATE_MASK];
+    D.accept_limit_8 = accept_limit; D.sherman_limit = 0xffffffffu; D.single = (S.flags & sh::FLAG_SINGLE_REPORT) ? 1u : 0u;
+    D.arb_report = S.report; D.accepts_eod = (v.nfa_flags & nfa::ACCEPTS_EOD) ? 1u : 0u; D.in_smem = 1; D.has_sherman = 0;
+}
+
 hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage **out) {
     // cached by (pointer, crc)
     const u32 crc = rd32(db, db::crc32);
@@ -1006,10 +1039,20 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
     im->host_db = db;
     im->crc = crc;
     im->bc_len = v.bc_len;
-    cudaError_t e = cudaMalloc((void **)&im->d_bc, round_up(v.bc_len, 256) + 256);
+    // A Sheng engine (<= 16 states as 256 shuffle masks) is re-laid at upload as a state-major byte table with the
+    // McClellan8 conventions (dead = 0, accepting states numbered last) behind the bytecode, and stepped by k_mcclellan.
+    std::vector<u8> derived;
+    const u32 derived_at = (u32)round_up(v.bc_len, 256) + 256;
+    if (v.kind == ENG_SHENG) build_sheng_tables(v, derived_at, derived, im->mcc);
+    const size_t image_bytes = derived_at + (derived.empty() ? 0 : round_up(derived.size(), 256) + 256);
+    cudaError_t e = cudaMalloc((void **)&im->d_bc, image_bytes);
     if (e != cudaSuccess) { delete im; return HS_NOMEM; }
     cudaMemcpyAsync(im->d_bc, v.bc, v.bc_len, cudaMemcpyHostToDevice, s->stream);
-    im->device_bytes = round_up(v.bc_len, 256) + 256;
+    if (!derived.empty()) {
+        cudaMemcpyAsync(im->d_bc + derived_at, derived.data(), derived.size(), cudaMemcpyHostToDevice, s->stream);
+        cudaStreamSynchronize(s->stream);  // `derived` is a local
+    }
+    im->device_bytes = image_bytes;
     DevDb &d = im->dev;
     d.bc = im->d_bc;
     d.groups = v.groups;
@@ -1072,6 +1115,8 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         L.o_squash = t.o_squash; L.o_meta = t.o_meta; L.o_masks = t.o_masks; L.o_base = t.o_base;
         L.total_words = t.total_words; L.accept_abs = t.accept_abs; L.accept_eod_abs = t.accept_eod_abs;
         L.nfa_flags = t.nfa_flags;
+    } else if (v.kind == ENG_SHENG) {
+        // im->mcc was filled by build_sheng_tables above
     } else if (v.kind == ENG_MCCLELLAN) {
         // the engine is stepped straight from the uploaded bytecode (mcclellan.cuh copies the table to shared memory)
         const DbView::Mcc &M = v.mcc;
@@ -1091,7 +1136,7 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         d.nood_id = v.nood_id;
     }
     d.tK = 0;
-    if (v.kind != ENG_LIMEX && v.kind != ENG_MCCLELLAN && turbo::build(v, im->turbo_tabs)) {
+    if (v.kind != ENG_LIMEX && v.kind != ENG_MCCLELLAN && v.kind != ENG_SHENG && turbo::build(v, im->turbo_tabs)) {
         const turbo::Tables &tt = im->turbo_tabs;
         if (cudaMalloc((void **)&im->d_pair, tt.pair.size() * 8) != cudaSuccess ||
             cudaMalloc((void **)&im->d_slots, tt.slots.size() * sizeof(turbo::Slot)) != cudaSuccess ||
@@ -1341,7 +1386,7 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
         case ENG_FDR: rv = launch_scan<FdrNative, false>(s, im->dev, cp, ar); break;
         case ENG_TEDDY: rv = launch_scan<TeddyNative, false>(s, im->dev, cp, ar); break;
         case ENG_LIMEX: rv = launch_limex(s, im, cp, ar); break;
-        case ENG_MCCLELLAN: rv = launch_mcclellan(s, im, cp, ar); break;
+        case ENG_MCCLELLAN: case ENG_SHENG: rv = launch_mcclellan(s, im, cp, ar); break;
         default: rv = launch_scan<Noodle, true>(s, im->dev, cp, ar); break;
         }
         if (rv != HS_SUCCESS) return rv;
@@ -1363,7 +1408,7 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
             return HS_UNKNOWN_ERROR;
         }
         raw = s->h_ctl[0];
-        if ((im->view.kind == ENG_LIMEX || im->view.kind == ENG_MCCLELLAN) && s->h_ctl[7] > s->recs2.cap) {  // event queue overflow: grow, scan again
+        if ((im->view.kind == ENG_LIMEX || im->view.kind == ENG_MCCLELLAN || im->view.kind == ENG_SHENG) && s->h_ctl[7] > s->recs2.cap) {  // event queue overflow: grow, scan again
             if (attempt >= 3) return HS_NOMEM;
             st.arena_retries++;
             s->lx_event_hint = s->h_ctl[7] + s->h_ctl[7] / 8 + 1024;

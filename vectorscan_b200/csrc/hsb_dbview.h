@@ -14,7 +14,7 @@ namespace hsb {
 constexpr int E_SUCCESS = 0, E_INVALID = -1, E_NOMEM = -2, E_DB_VERSION = -5, E_DB_PLATFORM = -6,
               E_DB_MODE = -7, E_BAD_ALIGN = -8, E_ARCH = -11, E_UNKNOWN = -13;
 
-enum EngineKind : u32 { ENG_FDR = 0, ENG_TEDDY = 1, ENG_NOODLE = 2, ENG_LIMEX = 3, ENG_MCCLELLAN = 4 };
+enum EngineKind : u32 { ENG_FDR = 0, ENG_TEDDY = 1, ENG_NOODLE = 2, ENG_LIMEX = 3, ENG_MCCLELLAN = 4, ENG_SHENG = 5 };
 
 struct LitRec {  // one LitInfo, flattened
     u64 v, msk, groups;
@@ -50,6 +50,8 @@ struct DbView {
         u32 m_off = 0, tab_off = 0, tab_bytes = 0, aux_off = 0, sherman_off = 0;
         u32 wide16 = 0, as = 0, states = 0, start = 0, accept_limit_8 = 0, sherman_limit = 0, single = 0, arb_report = 0;
     } mcc;
+    // single-outfix Sheng DFA (kind == ENG_SHENG), absolute bytecode offsets
+    struct Sheng { u32 sh_off = 0, aux_off = 0, n_states = 0, anchored = 0, flags = 0, report = 0; } sheng;
 };
 
 inline bool in_range(const DbView &d, size_t off, size_t n) { return off <= d.bc_len && n <= d.bc_len - off; }
@@ -171,6 +173,65 @@ inline int parse_mcclellan(DbView &d, std::string &why) {
     return E_SUCCESS;
 }
 
+
+// Single-outfix Sheng DFA (sheng_internal.h:56-79): <= 16 states, 256 shuffle masks.  Accel structures are skip-ahead
+// only.  A state carrying the DEAD flag must be a trap without reports (that is what the flag means; the device path
+// stops there).
+inline int parse_sheng(DbView &d, std::string &why) {
+    namespace sh = sheng;
+    const u8 *r = d.bc;
+    const u8 *n = r + d.nfa_off;
+    if (d.nfa_len < nfa::SIZE + sh::SIZE) { why = "Sheng truncated"; return E_INVALID; }
+    DbView::Sheng &S = d.sheng;
+    S.sh_off = d.nfa_off + (u32)nfa::SIZE;
+    const u8 *m = r + S.sh_off;
+    auto n_range = [&](size_t off, size_t len) { return off <= d.nfa_len && len <= d.nfa_len - off; };
+    S.n_states = rd8(m, sh::n_states);
+    S.anchored = rd8(m, sh::anchored);
+    S.flags = rd8(m, sh::flags);
+    S.report = rd32(m, sh::report);
+    if (!S.n_states || S.n_states > 16 || (S.anchored & sh::STATE_MASK) >= S.n_states) { why = "Sheng header inconsistent"; return E_INVALID; }
+    const u32 aux_rel = rd32(m, sh::aux_offset);
+    if (!n_range(aux_rel, (size_t)S.n_states * sh::aux::SIZE)) { why = "Sheng aux array truncated"; return E_INVALID; }
+    S.aux_off = d.nfa_off + aux_rel;
+    std::set<u32> progs;
+    if (S.flags & sh::FLAG_SINGLE_REPORT) progs.insert(S.report);
+    bool has_reports[16] = {false};
+    for (u32 st = 0; st < S.n_states; st++)
+        for (size_t f : {sh::aux::accept, sh::aux::accept_eod}) {
+            const u32 rl = rd32(r, S.aux_off + st * sh::aux::SIZE + f);
+            if (!rl) continue;
+            has_reports[st] = true;
+            if ((rl & 3) || !n_range(rl, 4)) { why = "Sheng report list outside the engine"; return E_INVALID; }
+            const u32 cnt = rd32(n, rl);
+            if (cnt > 65536 || !n_range((size_t)rl + 4, 4 * (size_t)cnt)) { why = "Sheng report list truncated"; return E_INVALID; }
+            for (u32 k = 0; k < cnt; k++) progs.insert(rd32(n, rl + 4 + 4 * k));
+        }
+    for (u32 c = 0; c < 256; c++)
+        for (u32 st = 0; st < S.n_states; st++) {
+            const u8 e = rd8(m, sh::shuffle_masks + 16 * c + st);
+            const u32 t = e & sh::STATE_MASK;
+            if (t >= S.n_states) { why = "Sheng successor out of range"; return E_INVALID; }
+            if (((e & sh::STATE_ACCEPT) != 0) != (rd32(r, S.aux_off + t * sh::aux::SIZE + sh::aux::accept) != 0)) {
+                why = "Sheng accept flag disagrees with the state's report list"; return E_INVALID;
+            }
+            if (e & sh::STATE_DEAD) {
+                if (has_reports[t]) { why = "Sheng dead state with reports"; return E_INVALID; }
+                for (u32 c2 = 0; c2 < 256; c2++)
+                    if ((rd8(m, sh::shuffle_masks + 16 * c2 + t) & sh::STATE_MASK) != t) { why = "Sheng dead state is not a trap"; return E_INVALID; }
+            }
+        }
+    d.kind = ENG_SHENG;
+    d.max_lit_len = 8;
+    for (u32 p : progs) {
+        if (p < rose::SIZE || !in_range(d, p, 8)) { why = "report program offset outside bytecode"; return E_INVALID; }
+        int rv = census_program(d, p, why, d.max_lit_len);
+        if (rv != E_SUCCESS) return rv;
+        d.programs.push_back(p);
+    }
+    return E_SUCCESS;
+}
+
 // Single-outfix database (src/runtime.c:246-279): queue 0 holds the only engine.  Accepted when that engine is a
 // LimEx NFA without bounded repeats and without reverse acceleration; every report list and accept entry must
 // lead to a Rose report program the device interpreter implements.
@@ -191,7 +252,8 @@ inline int parse_single_outfix(DbView &d, std::string &why) {
     if (!in_range(d, d.nfa_off, d.nfa_len)) { why = "NFA runs past the bytecode"; return E_INVALID; }
     if (rd8(n, nfa::rAccelType)) { why = "reverse acceleration is not supported"; return E_ARCH; }
     if (d.limex_type == nfa::MCCLELLAN_8 || d.limex_type == nfa::MCCLELLAN_16) return parse_mcclellan(d, why);
-    if (d.limex_type > nfa::LIMEX_512) { why = "outfix engine type " + std::to_string(d.limex_type) + " (neither LimEx nor McClellan) is not supported yet"; return E_ARCH; }
+    if (d.limex_type == nfa::SHENG) return parse_sheng(d, why);
+    if (d.limex_type > nfa::LIMEX_512) { why = "outfix engine type " + std::to_string(d.limex_type) + " (not LimEx, McClellan or Sheng) is not supported yet"; return E_ARCH; }
     const limex::Layout L = limex::layout(d.limex_type);
     if (d.nfa_len < nfa::SIZE + L.SIZE) { why = "LimEx truncated"; return E_INVALID; }
     d.limex_off = d.nfa_off + (u32)nfa::SIZE;

@@ -225,7 +225,7 @@ constexpr size_t flags = 0, length = 4, type = 8, rAccelType = 9, rAccelOffset =
                  rAccelData = 12, queueIndex = 16, nPositions = 20, scratchStateSize = 24, streamStateSize = 28,
                  maxWidth = 32, minWidth = 36, maxOffset = 40, SIZE = 64;
 constexpr u8 LIMEX_32 = 0, LIMEX_64 = 1, LIMEX_128 = 2, LIMEX_256 = 3, LIMEX_384 = 4, LIMEX_512 = 5;
-constexpr u8 MCCLELLAN_8 = 6, MCCLELLAN_16 = 7;
+constexpr u8 MCCLELLAN_8 = 6, MCCLELLAN_16 = 7, SHENG = 17;
 constexpr u32 ACCEPTS_EOD = 1, ZOMBIE = 2;
 }
 namespace nfainfo {  // struct NfaInfo
@@ -245,6 +245,16 @@ constexpr u32 ACCEPT_FLAG = 0x8000, ACCEL_FLAG = 0x4000, STATE_MASK = 0x3fff;
 constexpr u32 SHERMAN_STATE = 1, SHERMAN_FIXED_SIZE = 32, SHERMAN_LEN_OFFSET = 1, SHERMAN_DADDY_OFFSET = 2,
               SHERMAN_CHARS_OFFSET = 4, MAX_SHERMAN_LIST_LEN = 9;
 namespace aux { constexpr size_t accept = 0, accept_eod = 4, top = 8, accel_offset = 12, SIZE = 16; }
+}
+// struct sheng (src/nfa/sheng_internal.h:68-79): a DFA of at most 16 states as 256 byte-shuffle masks; mask[c][s] is
+// the successor of state s on byte c with flag bits (accept / dead / accel) beside the 4-bit state id.  sstate_aux[]
+// and the report lists {u32 count, ReportID[]} follow; their offsets are relative to struct NFA.
+namespace sheng {
+constexpr size_t shuffle_masks = 0, length = 4096, aux_offset = 4100, report_offset = 4104, accel_offset = 4108,
+                 n_states = 4112, anchored = 4113, floating = 4114, flags = 4115, report = 4116, SIZE = 4128;
+constexpr u32 STATE_ACCEPT = 0x10, STATE_DEAD = 0x20, STATE_ACCEL = 0x40, STATE_MASK = 0xf;
+constexpr u32 FLAG_SINGLE_REPORT = 1, FLAG_CAN_DIE = 2, FLAG_HAS_ACCEL = 4;
+namespace aux { constexpr size_t accept = 0, accept_eod = 4, accel = 8, top = 12, SIZE = 16; }
 }
 namespace nfaaccept {  // struct NFAAccept
 constexpr size_t single_report = 0, reports = 4, squash = 8, SIZE = 12;

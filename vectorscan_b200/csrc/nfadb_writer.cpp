@@ -676,12 +676,97 @@ int emit_mcclellan(const Dfa &d, const u8 *reach_map, const std::vector<u32> &pr
     return HSB_LIT_SUCCESS;
 }
 
+
+// Lay a DFA of at most 16 states out as the reference's Sheng engine (struct NFA + struct sheng + sstate_aux[] +
+// report lists), following shengcompile.cpp:337-358 (state byte = id | flags), :420-444 (header), :560-578 (masks)
+// and :640-698 (region order and sizes).  State ids are the DFA's own (dead = 0).
+int emit_sheng(const Dfa &d, const u8 *reach_map, const std::vector<u32> &program_of, u32 min_width, Buf &eng,
+               u32 &state_bytes, std::string &err) {
+    namespace sh = sheng;
+    const u32 n = (u32)d.next.size();
+    if (n > 16) { err = "DFA too large for a Sheng engine (" + std::to_string(n) + " states)"; return HSB_LIT_COMPILER_ERROR; }
+    state_bytes = 1;
+    bool can_die = false, any_eod = false;
+    for (u32 i = 1; i < n; i++) for (u32 k = 0; k < d.n_sym; k++) if (d.next[i][k] == 0) can_die = true;
+    auto state_byte = [&](u32 t) -> u8 {
+        u8 v = (u8)t;
+        if (!d.reports[t].empty()) v |= sh::STATE_ACCEPT;
+        if (t == 0) v |= sh::STATE_DEAD;
+        return v;
+    };
+    // report lists (normal and EOD share one pool, as gatherReports does)
+    std::map<std::vector<u32>, u32> list_id;
+    std::vector<std::vector<u32>> lists;
+    std::set<u32> all_reports;
+    auto intern = [&](const std::vector<u32> &pis) -> u32 {
+        if (pis.empty()) return ~0u;
+        std::set<u32> ps;
+        for (u32 pi : pis) ps.insert(program_of[pi]);
+        std::vector<u32> l(ps.begin(), ps.end());
+        all_reports.insert(l.begin(), l.end());
+        auto it = list_id.find(l);
+        if (it == list_id.end()) { it = list_id.emplace(l, (u32)lists.size()).first; lists.push_back(l); }
+        return it->second;
+    };
+    std::vector<u32> list_of(n), list_eod_of(n);
+    for (u32 i = 0; i < n; i++) {
+        list_of[i] = intern(d.reports[i]);
+        list_eod_of[i] = intern(d.reports_eod[i]);
+        if (list_eod_of[i] != ~0u) any_eod = true;
+    }
+    const size_t nfa_size = round_up(nfa::SIZE + sh::SIZE, 16);
+    const size_t reports_offset = nfa_size + sh::aux::SIZE * (size_t)n;
+    size_t rl_size = 0;
+    for (auto &l : lists) rl_size += 4 + 4 * l.size();
+    const size_t accel_offset = round_up(reports_offset + rl_size, 16);
+    const size_t total = round_up(accel_offset, 64);
+    eng.grow(total);
+    u8 *nh = eng.at(0), *m = eng.at(nfa::SIZE);
+    wr32(nh, nfa::flags, any_eod ? nfa::ACCEPTS_EOD : 0);
+    wr32(nh, nfa::length, (u32)total);
+    wr8(nh, nfa::type, nfa::SHENG);
+    wr32(nh, nfa::queueIndex, 0);
+    wr32(nh, nfa::nPositions, n);
+    wr32(nh, nfa::scratchStateSize, 1);
+    wr32(nh, nfa::streamStateSize, 1);
+    wr32(nh, nfa::maxWidth, 0);
+    wr32(nh, nfa::minWidth, min_width);
+    for (u32 c = 0; c < 256; c++)
+        for (u32 i = 0; i < n; i++) m[sh::shuffle_masks + 16 * c + i] = state_byte(d.next[i][reach_map[c]]);
+    wr32(m, sh::length, (u32)(total - nfa::SIZE));
+    wr32(m, sh::aux_offset, (u32)nfa_size);
+    wr32(m, sh::report_offset, (u32)reports_offset);
+    wr32(m, sh::accel_offset, (u32)accel_offset);
+    wr8(m, sh::n_states, (u8)n);
+    wr8(m, sh::anchored, state_byte(d.start_anchored));
+    wr8(m, sh::floating, state_byte(d.start_floating));
+    const bool single = all_reports.size() == 1;
+    wr8(m, sh::flags, (u8)((single ? sh::FLAG_SINGLE_REPORT : 0) | (can_die ? sh::FLAG_CAN_DIE : 0)));
+    wr32(m, sh::report, single ? *all_reports.begin() : 0);
+    std::vector<u32> list_off(lists.size());
+    size_t o = reports_offset;
+    for (size_t i = 0; i < lists.size(); i++) {
+        list_off[i] = (u32)o;
+        wr32(eng.at(o), 0, (u32)lists[i].size());
+        for (size_t k = 0; k < lists[i].size(); k++) wr32(eng.at(o), 4 + 4 * k, lists[i][k]);
+        o += 4 + 4 * lists[i].size();
+    }
+    for (u32 i = 0; i < n; i++) {
+        u8 *a = eng.at(nfa_size + sh::aux::SIZE * (size_t)i);
+        wr32(a, sh::aux::accept, list_of[i] == ~0u ? 0 : list_off[list_of[i]]);
+        wr32(a, sh::aux::accept_eod, list_eod_of[i] == ~0u ? 0 : list_off[list_eod_of[i]]);
+        wr32(a, sh::aux::accel, 0);
+        wr32(a, sh::aux::top, state_byte(d.start_floating));
+    }
+    return HSB_LIT_SUCCESS;
+}
+
 }  // namespace
 
 namespace hsb_nfadb {
 
 int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &image, std::string &err) {
-    if (engine > HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN) { err = "unknown engine"; return HSB_LIT_COMPILER_ERROR; }
+    if (engine > HSB_REGEX_ENGINE_SHENG) { err = "unknown engine"; return HSB_LIT_COMPILER_ERROR; }
     if (pats.empty()) { err = "no expressions"; return HSB_LIT_COMPILER_ERROR; }
     // ---- 1. parse every pattern, build one automaton -------------------------------------------------
     Automaton am;
@@ -835,7 +920,9 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
         Dfa dfa;
         if (!determinise(am, reach_rows, dfa, 4 * (mcclellan::STATE_MASK + 1))) { err = "DFA too large for a McClellan engine"; return HSB_LIT_COMPILER_ERROR; }
         minimise(dfa);
-        const int rv = emit_mcclellan(dfa, reach_map, program_of, engine == HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN, am.min_width, eng, stream_state, err);
+        const int rv = engine == HSB_REGEX_ENGINE_SHENG
+                           ? emit_sheng(dfa, reach_map, program_of, am.min_width, eng, stream_state, err)
+                           : emit_mcclellan(dfa, reach_map, program_of, engine == HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN, am.min_width, eng, stream_state, err);
         if (rv != HSB_LIT_SUCCESS) return rv;
         scratch_state = stream_state;
     } else {

@@ -142,7 +142,7 @@ def compile_lit_multi(literals, flags=None, ids=None, mode=HS_MODE_BLOCK, engine
     return Database(db.value)
 
 
-ENGINE_LIMEX, ENGINE_MCCLELLAN, ENGINE_MCCLELLAN_SHERMAN = 0, 1, 2
+ENGINE_LIMEX, ENGINE_MCCLELLAN, ENGINE_MCCLELLAN_SHERMAN, ENGINE_SHENG = 0, 1, 2, 3
 
 
 def compile_regex_multi(expressions, flags=None, ids=None, mode=HS_MODE_BLOCK, engine=ENGINE_LIMEX):
