@@ -287,3 +287,41 @@ def test_host_staging_paths_agree(ref):
     assert run(mixed) == exp                                                        # (c)
     L.hs_gpu_host_free(hp)
     sc.close()
+
+
+@pytest.mark.parametrize("config", ["c3d", "c3", "c4"])
+def test_full_size_properties_engines_and_c4(ref, config):
+    """Bench-size batches of the other configs (bench.py make_workload): (1) the first 2 MiB of buffers equal the
+    unmodified reference runtime, (2) the batch scanned in two halves split at a buffer boundary gives the same
+    records, (3) a second scan of the same corpus gives the same records (no state leaks between scans), (4) output
+    is sorted by (buffer, to, id) and free of duplicates."""
+    import bench
+    nbytes = {"c3d": 64 << 20, "c3": 16 << 20, "c4": 64 << 20}[config]
+    db, n_ids, batches, name = bench.make_workload(config, 0, nbytes, 6)
+    flat, off = batches[0]
+    sc = gpu.alloc_scratch(db)
+    corpus = gpu.Corpus(flat, off)
+    n = gpu.scan_corpus(db, corpus, sc)
+    m = gpu.fetch_matches(sc).copy()
+    n_again = gpu.scan_corpus(db, corpus, sc)
+    assert n_again == n and np.array_equal(gpu.fetch_matches(sc), m)
+    corpus.close()
+    assert n == len(m) and n > 100
+    key = np.stack([m["buffer"].astype(np.uint64), m["to"], m["id"].astype(np.uint64)], axis=1)
+    order = np.lexsort((key[:, 2], key[:, 1], key[:, 0]))
+    assert np.array_equal(order, np.arange(len(m)))
+    assert len(np.unique(key, axis=0)) == len(m)
+    nb = int(np.searchsorted(off, 2 << 20))
+    bufs = [bytes(flat[int(off[k]):int(off[k + 1])]) for k in range(nb)]
+    exp = ref_scan(ref, db, bufs)
+    got = [(int(a), int(b), int(c)) for a, b, c in zip(m["buffer"], m["id"], m["to"]) if a < nb]
+    assert got == exp and len(exp) > 5
+    half = len(off) // 2
+    c1 = gpu.Corpus(flat[:int(off[half])], off[:half + 1])
+    c2 = gpu.Corpus(flat[int(off[half]):], off[half:] - off[half])
+    n1 = gpu.scan_corpus(db, c1, sc)
+    m1 = gpu.fetch_matches(sc).copy()
+    n2 = gpu.scan_corpus(db, c2, sc)
+    m2 = gpu.fetch_matches(sc).copy()
+    m2["buffer"] += half
+    assert n1 + n2 == len(m) and np.array_equal(np.concatenate([m1, m2]), m)
