@@ -100,7 +100,10 @@ __global__ void __launch_bounds__(MCC_THREADS, 1) k_mcclellan(const DevDb db_, c
     u32 s = 0, buf = 0, len = 0;
     long long i = 0;           // buffer offset of byte 0 of the current chunk (negative for the first chunk)
     const uint4 *chunk = nullptr;
-    uint4 cur = make_uint4(0, 0, 0, 0), q1 = cur, q2 = cur, q3 = cur;  // this chunk and the three after it
+    uint4 a[4];                // this chunk and the three after it; indexed statically (the trip below is unrolled
+                               // four times), so a chunk is loaded into the registers its predecessor just left and
+                               // is not touched again until it is stepped, 48 steps later
+    a[0] = a[1] = a[2] = a[3] = make_uint4(0, 0, 0, 0);
     bool have = false, first = true;
 
     for (;;) {
@@ -135,19 +138,22 @@ __global__ void __launch_bounds__(MCC_THREADS, 1) k_mcclellan(const DevDb db_, c
             const uintptr_t ap = reinterpret_cast<uintptr_t>(cp_.text + o0);
             chunk = reinterpret_cast<const uint4 *>(ap & ~(uintptr_t)15);
             i = -(long long)(ap & 15);
-            cur = chunk[0];              // over-reads stay inside the padded text (BACK_PAD)
-            q1 = chunk[1]; q2 = chunk[2]; q3 = chunk[3];
+            a[0] = chunk[0];             // over-reads stay inside the padded text (BACK_PAD)
+            a[1] = chunk[1]; a[2] = chunk[2]; a[3] = chunk[3];
             chunk += 4;
             s = m.start;
             have = true;
         }
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        if (!have) break;  // the buffer ended in an earlier quarter of this trip
         // ---- one aligned 16-byte chunk: bytes [j0, j1) of it belong to the buffer ----
-        const uint4 v = cur;
+        const uint4 v = a[q];
         const long long rem = (long long)len - i;  // bytes from chunk byte 0 to the end of the buffer
         // three chunks (48 steps) of loads in flight while this one is stepped: a step is ~40 cycles of dependent
-        // latency, a miss to HBM ~1000
-        cur = q1; q1 = q2; q2 = q3;
-        if (rem > 64) q3 = *chunk;
+        // latency, a miss to HBM ~1000.  (A rotating FIFO -- cur = q1; q1 = q2; q2 = q3 -- makes the move wait for
+        // the load issued one trip earlier: 20 % of the stall samples sat there.)
+        if (rem > 64) a[q] = *chunk;
         chunk++;
         const u32 j0 = i < 0 ? (u32)(-i) : 0u;
         const u32 j1 = rem < 16 ? (u32)rem : 16u;
@@ -196,5 +202,6 @@ __global__ void __launch_bounds__(MCC_THREADS, 1) k_mcclellan(const DevDb db_, c
             if (s && m.accepts_eod) mcc_accept(evq, db_.bc, m, s, buf, len, true);
             have = false;
         }
+      }
     }
 }
