@@ -14,10 +14,12 @@
 // cannot change the state -- result-neutral, not used here; ACCEL_FLAG bits in table entries are masked off.
 //
 // Geometry: a DFA step is one dependent table read per byte, so the unit of parallelism is the BUFFER: one
-// thread per buffer, threads persistent and fed from a global counter (buffers of any length mix in a warp).
-// The successor table and remap[] sit in shared memory when they fit (<= MCC_SMEM_MAX), else they are read
-// through L1/L2.  Text is read one aligned 16-byte chunk per trip with the next chunk already in flight; bytes of
-// a chunk outside the buffer freeze the state (select), so all 32 lanes run the same 16 unrolled steps.
+// thread per buffer, threads persistent (first buffer by thread index, later ones from a global counter; buffers of
+// any length mix in a warp).  The successor table and a bank-replicated symbol table sit in shared memory when
+// they fit (<= MCC_SMEM_MAX), else the successor table is read through L1/L2.  Text is read in aligned 16-byte
+// chunks, three chunks ahead; bytes of a chunk outside the buffer freeze the state (predicated read), so all 32
+// lanes run the same 16 unrolled steps.  A Sheng engine is re-laid at upload (hs_gpu.cu build_sheng_tables) into the
+// 8-bit form of this table and stepped by the same kernel.
 // Hot loop = 16 branch-free steps that only remember whether an accept was passed; the rare chunk that passed one
 // is stepped again from its start state by the exact loop, which raises the events.
 #pragma once
@@ -76,9 +78,8 @@ template <bool WIDE16, bool SMEM, bool SHERMAN>
 __global__ void __launch_bounds__(MCC_THREADS, 1) k_mcclellan(const DevDb db_, const DevMcc m, const DevCorpus cp_,
                                                               const DevLxEvents evq, unsigned long long *next_buf) {
     extern __shared__ __align__(16) u8 smem[];
-    // symbol table: rm[c] = remap[c] * (entry size), so that row offset + rm[c] is a byte offset;
-    // one copy per bank (word ch * 32 + lane): a warp's 32 lookups never conflict
-    // the shared-memory address of the table is folded in, so row offset + rm[c] is the address of the entry
+    // symbol table: rm[c] = remap[c] * (entry size) + (shared-memory address of the table), so that row offset + rm[c]
+    // is the address of the entry; one copy per bank (word c * 32 + lane): a warp's 32 lookups never conflict
     u32 *rm_w = reinterpret_cast<u32 *>(smem);
     const u32 tab_sh = SMEM ? (u32)__cvta_generic_to_shared(smem + MCC_RM_BYTES + (m.tab_abs & 3u)) : 0u;
     for (u32 i = threadIdx.x; i < 256 * 32; i += blockDim.x)

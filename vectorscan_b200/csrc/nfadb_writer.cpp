@@ -549,9 +549,8 @@ int emit_mcclellan(const Dfa &d, const u8 *reach_map, const std::vector<u32> &pr
                     if (diff <= mc::MAX_SHERMAN_LIST_LEN) { is_sherman[i] = 1; daddy[i] = cand; break; }
                 }
             }
-            // a daddy must stay a normal state: candidates were checked against is_sherman at the time, and a later
-            // state may have turned its daddy's daddy... daddies are never Sherman by the check above, but a state
-            // chosen as daddy earlier may itself become Sherman later -- undo those
+            // a daddy must be a normal state (doSherman16 reads its row): ids are in discovery order, so a parent is
+            // decided before its children; this pass only guards that invariant
             for (u32 i = 1; i < n; i++) if (is_sherman[i] && is_sherman[daddy[i]]) is_sherman[i] = 0;
         }
         u32 j = 1;
