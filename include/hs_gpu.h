@@ -18,7 +18,10 @@ extern "C" {
 #endif
 
 struct hs_database;
+#if !defined(HS_COMMON_H_) && !defined(HSB_HS_DATABASE_T) /* the reference's hs_common.h, or our other header, may have declared it */
+#define HSB_HS_DATABASE_T
 typedef struct hs_database hs_database_t; /* src/hs_common.h:56 */
+#endif
 struct hs_gpu_scratch;
 typedef struct hs_gpu_scratch hs_gpu_scratch_t; /* stands where hs_scratch_t stands, src/hs_common.h:466 */
 struct hs_gpu_corpus;

@@ -17,7 +17,10 @@ extern "C" {
 #endif
 
 struct hs_database;
+#if !defined(HS_COMMON_H_) && !defined(HSB_HS_DATABASE_T) /* the reference's hs_common.h, or our other header, may have declared it */
+#define HSB_HS_DATABASE_T
 typedef struct hs_database hs_database_t; /* same opaque type as src/hs_common.h:56 */
+#endif
 
 #define HSB_LIT_SUCCESS 0
 #define HSB_LIT_COMPILER_ERROR (-4) /* HS_COMPILER_ERROR, src/hs_common.h:503 */

@@ -73,3 +73,37 @@ def test_argument_errors_without_device():
         # a valid database but no device: loud failure, no CPU fallback
         assert L.hs_gpu_alloc_scratch(db.ptr, C.byref(s)) == gpu.HS_ARCH_ERROR
         assert L.hs_gpu_shufti(bytes(16), bytes(16), b"abc", 3, 0) == -2
+
+
+def test_headers_are_plain_c_and_a_c_caller_links(tmp_path):
+    """include/*.h must be usable from the reference's own language (C): compile a C caller with gcc -std=c99
+    -pedantic that references the entry points of the drop-in path with the reference's callback typedef, link it
+    against the two shared libraries, and run it far enough to get HS_INVALID for a NULL database (no device work)."""
+    import subprocess
+    src = tmp_path / "caller.c"
+    src.write_text(r'''
+#include "hs_gpu.h"
+#include "hs_litdb.h"
+#include <stdio.h>
+static int on_match(unsigned int id, unsigned long long from, unsigned long long to, unsigned int flags, void *ctx) {
+    (void)id; (void)from; (void)to; (void)flags; (void)ctx; return 0;
+}
+int main(void) {
+    hs_gpu_scratch_t *scratch = NULL;
+    int rv = hs_gpu_alloc_scratch(NULL, &scratch);               /* hs_alloc_scratch(NULL, ..) -> HS_INVALID */
+    int rv2 = hs_gpu_scan(NULL, "x", 1, 0, NULL, on_match, NULL); /* hs_scan(NULL, ..)         -> HS_INVALID */
+    const char *ex[1] = {"abc"};
+    hs_database_t *db = NULL;
+    char *err = NULL;
+    int rv3 = hsb_compile_regex_multi_ex(ex, NULL, NULL, 1, 1 /* HS_MODE_BLOCK */, HSB_REGEX_ENGINE_SHENG, &db, &err);
+    printf("%d %d %d %d\n", rv, rv2, rv3, db != NULL);
+    hsb_free_database(db);
+    return 0;
+}
+''')
+    exe = tmp_path / "caller"
+    pkg = os.path.join(ROOT, "vectorscan_b200")
+    subprocess.run(["gcc", "-std=c99", "-pedantic", "-Wall", "-Werror", "-I" + os.path.join(ROOT, "include"), str(src),
+                    "-L" + pkg, "-lhs_gpu", "-lhs_litdb", "-Wl,-rpath," + pkg, "-o", str(exe)], check=True)
+    out = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()
+    assert out == ["-1", "-1", "0", "1"]
