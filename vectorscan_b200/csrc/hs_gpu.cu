@@ -1396,8 +1396,11 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
         // Few records are the rule for regex databases: the single-CTA finalize goes in right behind the scan and
         // decides on the device whether it applies, so the whole scan costs ONE host round trip.
         CU_OK(cudaEventRecord(s->ev[2], s->stream));
+        // sized by the previous scan's count (fewer threads = fewer merge rounds and cheaper barriers)
         if (s->last_raw <= 256 * SMALL_FIN_ITEMS)
             CU_OK(launch_small_finalize<256>(s->stream, s->recs.p, s->recs2.p, s->d_matches.p, s->d_ctl + 4, s->d_ctl + 0, s->recs.cap));
+        else if (s->last_raw <= 512 * SMALL_FIN_ITEMS)
+            CU_OK(launch_small_finalize<512>(s->stream, s->recs.p, s->recs2.p, s->d_matches.p, s->d_ctl + 4, s->d_ctl + 0, s->recs.cap));
         else
             CU_OK(launch_small_finalize<1024>(s->stream, s->recs.p, s->recs2.p, s->d_matches.p, s->d_ctl + 4, s->d_ctl + 0, s->recs.cap));
         CU_OK(cudaEventRecord(s->ev[3], s->stream));
