@@ -1,9 +1,13 @@
 /* oracle/cpu_bench.c -- TEST / BASELINE INFRASTRUCTURE ONLY (never on the product path).
  *
- * hsbench-style block-mode timing loop over the UNMODIFIED reference runtime (oracle/_ref/libhs_ref_*.so,
- * loaded with dlopen): the loop tools/hsbench/main.cpp:486-512 runs -- every thread owns a cloned scratch
- * and calls hs_scan once per buffer with a counting callback (engine_hyperscan.cpp:89-96) -- timed with
- * CLOCK_MONOTONIC around the whole pass, threads pinned one per core (main.cpp:154).
+ * hsbench-shaped block-mode timing loop over the UNMODIFIED reference runtime (oracle/_ref/libhs_ref_*.so,
+ * loaded with dlopen).  Shape of tools/hsbench/main.cpp:
+ *   - one persistent worker per thread, pinned to one CPU of the process's affinity mask (main.cpp:154), each
+ *     with its own cloned scratch (engine_hyperscan.cpp:131-163) and a counting callback (:89-96);
+ *   - every worker scans the WHOLE corpus, `repeats` times, one hs_scan per buffer (benchBlock, main.cpp:486-512);
+ *   - workers are created, pinned and parked on a barrier BEFORE the clock starts; the clock (CLOCK_MONOTONIC)
+ *     brackets the passes only: release barrier -> passes -> completion barrier (main.cpp:560-590);
+ *   - throughput = threads x repeats x corpus bytes / seconds (main.cpp:704-708).
  * No matching logic lives here. */
 #define _GNU_SOURCE
 #include <dlfcn.h>
@@ -44,8 +48,10 @@ static int count_cb(unsigned id, unsigned long long from, unsigned long long to,
 
 struct job {
     const struct api *a; const void *db; void *scratch;
-    const char *flat; const uint64_t *off; uint32_t first, last; int repeats; int cpu;
+    const char *flat; const uint64_t *off; uint32_t count; int repeats; int cpu;
+    pthread_barrier_t *start, *done;
     uint64_t matches; int err;
+    char pad[64];
 };
 
 static void *worker(void *p) {
@@ -54,17 +60,24 @@ static void *worker(void *p) {
         cpu_set_t set; CPU_ZERO(&set); CPU_SET(j->cpu, &set);
         pthread_setaffinity_np(pthread_self(), sizeof(set), &set);
     }
+    /* one untimed pass over a little of the corpus: page in the runtime's code and this worker's scratch */
+    uint64_t warm = 0;
+    for (uint32_t b = 0; b < j->count && b < 64; b++)
+        j->a->scan(j->db, j->flat + j->off[b], (unsigned)(j->off[b + 1] - j->off[b]), 0, j->scratch, count_cb, &warm);
+    pthread_barrier_wait(j->start);
     for (int r = 0; r < j->repeats; r++)
-        for (uint32_t b = j->first; b < j->last; b++) {
+        for (uint32_t b = 0; b < j->count; b++) {
             int rv = j->a->scan(j->db, j->flat + j->off[b], (unsigned)(j->off[b + 1] - j->off[b]), 0, j->scratch,
                                 count_cb, &j->matches);
             if (rv) j->err = rv;
         }
+    pthread_barrier_wait(j->done);
     return NULL;
 }
 
-/* Scans buffers [0,count) `repeats` times with `threads` threads (buffers split in contiguous, byte-balanced
- * ranges).  Returns seconds for the whole pass (<0 on error); *matches = matches counted over all repeats. */
+/* Every one of `threads` pinned workers scans buffers [0,count) `repeats` times.  Returns the seconds between
+ * the release of the start barrier and the completion barrier (<0 on error); *matches = matches counted by all
+ * workers over all repeats.  Bytes scanned = threads x repeats x off[count]. */
 double cpu_bench_run(const char *ref_lib, const char *serialized, size_t ser_len, const char *flat,
                      const uint64_t *off, uint32_t count, int threads, int repeats, uint64_t *matches) {
     struct api a;
@@ -72,27 +85,34 @@ double cpu_bench_run(const char *ref_lib, const char *serialized, size_t ser_len
     void *db = NULL, *proto = NULL;
     if (a.deser(serialized, ser_len, &db) || a.alloc(db, &proto)) return -2.0;
     if (threads < 1) threads = 1;
+    if (repeats < 1) repeats = 1;
+    /* CPUs this process may run on (a container's mask need not start at 0) */
+    cpu_set_t avail; CPU_ZERO(&avail);
+    int ncpu = 0, cpus[1024];
+    if (sched_getaffinity(0, sizeof(avail), &avail) == 0)
+        for (int c = 0; c < CPU_SETSIZE && ncpu < 1024; c++) if (CPU_ISSET(c, &avail)) cpus[ncpu++] = c;
     struct job *jobs = calloc((size_t)threads, sizeof(*jobs));
     pthread_t *tids = calloc((size_t)threads, sizeof(*tids));
-    uint64_t total = off[count], per = total / (uint64_t)threads + 1;
-    uint32_t b = 0;
+    pthread_barrier_t start, done;
+    pthread_barrier_init(&start, NULL, (unsigned)threads + 1);
+    pthread_barrier_init(&done, NULL, (unsigned)threads + 1);
     for (int t = 0; t < threads; t++) {
-        jobs[t].a = &a; jobs[t].db = db; jobs[t].flat = flat; jobs[t].off = off; jobs[t].repeats = repeats;
-        jobs[t].cpu = t; jobs[t].first = b;
-        uint64_t limit = (uint64_t)(t + 1) * per;
-        while (b < count && off[b + 1] <= limit) b++;
-        if (t == threads - 1) b = count;
-        jobs[t].last = b;
+        jobs[t].a = &a; jobs[t].db = db; jobs[t].flat = flat; jobs[t].off = off; jobs[t].count = count;
+        jobs[t].repeats = repeats; jobs[t].cpu = ncpu ? cpus[t % ncpu] : -1;
+        jobs[t].start = &start; jobs[t].done = &done;
         if (a.clone(proto, &jobs[t].scratch)) return -3.0;
     }
-    struct timespec t0, t1;
-    clock_gettime(CLOCK_MONOTONIC, &t0);
     for (int t = 0; t < threads; t++) pthread_create(&tids[t], NULL, worker, &jobs[t]);
-    for (int t = 0; t < threads; t++) pthread_join(tids[t], NULL);
+    struct timespec t0, t1;
+    pthread_barrier_wait(&start);
+    clock_gettime(CLOCK_MONOTONIC, &t0);
+    pthread_barrier_wait(&done);
     clock_gettime(CLOCK_MONOTONIC, &t1);
+    for (int t = 0; t < threads; t++) pthread_join(tids[t], NULL);
     uint64_t m = 0; int err = 0;
     for (int t = 0; t < threads; t++) { m += jobs[t].matches; err |= jobs[t].err; a.free_scratch(jobs[t].scratch); }
     a.free_scratch(proto); a.free_db(db);
+    pthread_barrier_destroy(&start); pthread_barrier_destroy(&done);
     free(jobs); free(tids);
     if (matches) *matches = m;
     if (err) return -4.0;

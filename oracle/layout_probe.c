@@ -180,6 +180,18 @@ int main(void) {
     IOF("check_shufti_32x16", ROSE_STRUCT_CHECK_SHUFTI_32x16, bucket_select_mask_hi); IOF("check_shufti_32x16", ROSE_STRUCT_CHECK_SHUFTI_32x16, bucket_select_mask_lo);
     IOF("check_shufti_32x16", ROSE_STRUCT_CHECK_SHUFTI_32x16, neg_mask); IOF("check_shufti_32x16", ROSE_STRUCT_CHECK_SHUFTI_32x16, offset);
     IOF("check_shufti_32x16", ROSE_STRUCT_CHECK_SHUFTI_32x16, fail_jump); ISZ("check_shufti_32x16", ROSE_STRUCT_CHECK_SHUFTI_32x16);
+    IOF("check_mask64", ROSE_STRUCT_CHECK_MASK_64, and_mask); IOF("check_mask64", ROSE_STRUCT_CHECK_MASK_64, cmp_mask);
+    IOF("check_mask64", ROSE_STRUCT_CHECK_MASK_64, neg_mask); IOF("check_mask64", ROSE_STRUCT_CHECK_MASK_64, offset);
+    IOF("check_mask64", ROSE_STRUCT_CHECK_MASK_64, fail_jump); ISZ("check_mask64", ROSE_STRUCT_CHECK_MASK_64);
+    IOF("check_shufti_64x8", ROSE_STRUCT_CHECK_SHUFTI_64x8, hi_mask); IOF("check_shufti_64x8", ROSE_STRUCT_CHECK_SHUFTI_64x8, lo_mask);
+    IOF("check_shufti_64x8", ROSE_STRUCT_CHECK_SHUFTI_64x8, bucket_select_mask); IOF("check_shufti_64x8", ROSE_STRUCT_CHECK_SHUFTI_64x8, neg_mask);
+    IOF("check_shufti_64x8", ROSE_STRUCT_CHECK_SHUFTI_64x8, offset); IOF("check_shufti_64x8", ROSE_STRUCT_CHECK_SHUFTI_64x8, fail_jump);
+    ISZ("check_shufti_64x8", ROSE_STRUCT_CHECK_SHUFTI_64x8);
+    IOF("check_shufti_64x16", ROSE_STRUCT_CHECK_SHUFTI_64x16, hi_mask_1); IOF("check_shufti_64x16", ROSE_STRUCT_CHECK_SHUFTI_64x16, hi_mask_2);
+    IOF("check_shufti_64x16", ROSE_STRUCT_CHECK_SHUFTI_64x16, lo_mask_1); IOF("check_shufti_64x16", ROSE_STRUCT_CHECK_SHUFTI_64x16, lo_mask_2);
+    IOF("check_shufti_64x16", ROSE_STRUCT_CHECK_SHUFTI_64x16, bucket_select_mask_hi); IOF("check_shufti_64x16", ROSE_STRUCT_CHECK_SHUFTI_64x16, bucket_select_mask_lo);
+    IOF("check_shufti_64x16", ROSE_STRUCT_CHECK_SHUFTI_64x16, neg_mask); IOF("check_shufti_64x16", ROSE_STRUCT_CHECK_SHUFTI_64x16, offset);
+    IOF("check_shufti_64x16", ROSE_STRUCT_CHECK_SHUFTI_64x16, fail_jump); ISZ("check_shufti_64x16", ROSE_STRUCT_CHECK_SHUFTI_64x16);
     IOF("dedupe", ROSE_STRUCT_DEDUPE, quash_som); IOF("dedupe", ROSE_STRUCT_DEDUPE, dkey);
     IOF("dedupe", ROSE_STRUCT_DEDUPE, offset_adjust); IOF("dedupe", ROSE_STRUCT_DEDUPE, fail_jump); ISZ("dedupe", ROSE_STRUCT_DEDUPE);
     IOF("report", ROSE_STRUCT_REPORT, onmatch); IOF("report", ROSE_STRUCT_REPORT, offset_adjust); ISZ("report", ROSE_STRUCT_REPORT);

@@ -91,6 +91,8 @@ struct DevDb {
     const turbo::Slot *slots;
     const u32 *bloom;     // second filter tier (turbo_tables.h, 3.)
     u32 tK, tH1, tH2, tL, tBL;
+    const u32 *gram_tab;  // first tier of k_turbo2 (turbo_tables.h, "gram table")
+    u32 gG1, gmul, gS;
     u32 lx_abs;           // absolute bytecode offset of the LimExNFA (single-outfix databases)
 };
 
@@ -264,6 +266,86 @@ __device__ bool check_byte(u8 and_mask, u8 cmp_mask, u8 negation, int check_off,
     return !(differ ^ (negation != 0));
 }
 
+// roseCheckMask32 / roseCheckMask64 (src/rose/program_runtime.c:729-935) in block mode: n window bytes starting at
+// to + check_off; a byte outside the buffer is "don't care" (valid_data_mask), a byte inside must satisfy
+// ((c & and) != cmp) == its neg_mask bit (validateMask32, src/rose/validate_mask.h:106-127).
+__device__ bool check_mask_n(const u8 *andm, const u8 *cmpm, u64 neg, u32 n, int check_off, const u8 *btext, u32 blen, u32 to) {
+    if (check_off < 0 && (u32)(-check_off) > to) return false;
+    const long long base = (long long)to + check_off;
+    for (u32 k = 0; k < n; k++) {
+        const long long o = base + k;
+        if (o < 0 || o >= (long long)blen) continue;
+        const bool differ = (u8)(btext[o] & andm[k]) != cmpm[k];
+        if (differ != (((neg >> k) & 1) != 0)) return false;
+    }
+    return true;
+}
+
+// roseCheckShufti16x8 ... 64x16 (src/rose/program_runtime.c:992-1250, validateShuftiMask* src/rose/validate_shufti.h:
+// 46-372): window byte k is "in the class" when its nibble-mask product has a bit of bucket_select_mask[k]; every byte
+// inside the buffer must have (not in class) == its neg_mask bit.  `ins` = the instruction; one routine for the six
+// shapes (the 64-byte masks of the AVX512 shapes are four copies of a 16-byte mask, indexed per 16-byte lane as pshufb does).
+__device__ bool check_shufti(const u8 *ins, u8 code, const u8 *btext, u32 blen, u32 to) {
+    u32 n, wide;  // window bytes, 16 buckets?
+    const u8 *hi1, *lo1, *hi2 = nullptr, *lo2 = nullptr, *sel_lo, *sel_hi = nullptr;
+    u64 neg;
+    int check_off;
+    u32 lane_stride = 0;  // 16 for the 64-byte shapes: mask copy of the byte's 128-bit lane
+    switch (code) {
+    case op::CHECK_SHUFTI_16x8:
+        n = 16; wide = 0; lo1 = ins + op::check_shufti_16x8::nib_mask; hi1 = lo1 + 16;
+        sel_lo = ins + op::check_shufti_16x8::bucket_select_mask;
+        neg = *reinterpret_cast<const u32 *>(ins + op::check_shufti_16x8::neg_mask);
+        check_off = *reinterpret_cast<const int *>(ins + op::check_shufti_16x8::offset);
+        break;
+    case op::CHECK_SHUFTI_32x8:
+        n = 32; wide = 0; hi1 = ins + op::check_shufti_32x8::hi_mask; lo1 = ins + op::check_shufti_32x8::lo_mask;
+        sel_lo = ins + op::check_shufti_32x8::bucket_select_mask;
+        neg = *reinterpret_cast<const u32 *>(ins + op::check_shufti_32x8::neg_mask);
+        check_off = *reinterpret_cast<const int *>(ins + op::check_shufti_32x8::offset);
+        break;
+    case op::CHECK_SHUFTI_16x16:
+        n = 16; wide = 1; hi1 = ins + op::check_shufti_16x16::hi_mask; hi2 = hi1 + 16;
+        lo1 = ins + op::check_shufti_16x16::lo_mask; lo2 = lo1 + 16;
+        sel_lo = ins + op::check_shufti_16x16::bucket_select_mask; sel_hi = sel_lo + 16;
+        neg = *reinterpret_cast<const u32 *>(ins + op::check_shufti_16x16::neg_mask);
+        check_off = *reinterpret_cast<const int *>(ins + op::check_shufti_16x16::offset);
+        break;
+    case op::CHECK_SHUFTI_32x16:
+        n = 32; wide = 1; hi1 = ins + op::check_shufti_32x16::hi_mask; hi2 = hi1 + 16;
+        lo1 = ins + op::check_shufti_32x16::lo_mask; lo2 = lo1 + 16;
+        sel_hi = ins + op::check_shufti_32x16::bucket_select_mask_hi; sel_lo = ins + op::check_shufti_32x16::bucket_select_mask_lo;
+        neg = *reinterpret_cast<const u32 *>(ins + op::check_shufti_32x16::neg_mask);
+        check_off = *reinterpret_cast<const int *>(ins + op::check_shufti_32x16::offset);
+        break;
+    case op::CHECK_SHUFTI_64x8:
+        n = 64; wide = 0; lane_stride = 16; hi1 = ins + op::check_shufti_64x8::hi_mask; lo1 = ins + op::check_shufti_64x8::lo_mask;
+        sel_lo = ins + op::check_shufti_64x8::bucket_select_mask;
+        neg = *reinterpret_cast<const u64 *>(ins + op::check_shufti_64x8::neg_mask);
+        check_off = *reinterpret_cast<const int *>(ins + op::check_shufti_64x8::offset);
+        break;
+    default:  // CHECK_SHUFTI_64x16
+        n = 64; wide = 1; lane_stride = 16; hi1 = ins + op::check_shufti_64x16::hi_mask_1; hi2 = ins + op::check_shufti_64x16::hi_mask_2;
+        lo1 = ins + op::check_shufti_64x16::lo_mask_1; lo2 = ins + op::check_shufti_64x16::lo_mask_2;
+        sel_hi = ins + op::check_shufti_64x16::bucket_select_mask_hi; sel_lo = ins + op::check_shufti_64x16::bucket_select_mask_lo;
+        neg = *reinterpret_cast<const u64 *>(ins + op::check_shufti_64x16::neg_mask);
+        check_off = *reinterpret_cast<const int *>(ins + op::check_shufti_64x16::offset);
+        break;
+    }
+    if (check_off < 0 && (u32)(-check_off) > to) return false;
+    const long long base = (long long)to + check_off;
+    for (u32 k = 0; k < n; k++) {
+        const long long o = base + k;
+        if (o < 0 || o >= (long long)blen) continue;
+        const u8 ch = btext[o];
+        const u32 ln = lane_stride ? (k & ~15u) : 0u;
+        u8 hit = (u8)(lo1[ln + (ch & 15)] & hi1[ln + (ch >> 4)] & sel_lo[k]);
+        if (wide) hit |= (u8)(lo2[ln + (ch & 15)] & hi2[ln + (ch >> 4)] & sel_hi[k]);
+        if ((hit == 0) != (((neg >> k) & 1) != 0)) return false;
+    }
+    return true;
+}
+
 __device__ void run_program(const Ctx &c, u32 prog, u32 buf, const u8 *btext, u32 blen, u32 to) {
     const u8 *bc = c.db.bc;
     u32 pc = prog;
@@ -294,6 +376,36 @@ __device__ void run_program(const Ctx &c, u32 prog, u32 buf, const u8 *btext, u3
                 pc += op::check_byte::SIZE;
             }
             break;
+        case op::CHECK_MASK_32:
+            if (!check_mask_n(bc + pc + op::check_mask32::and_mask, bc + pc + op::check_mask32::cmp_mask,
+                              ld32(bc, pc + op::check_mask32::neg_mask), 32, (int)ld32(bc, pc + op::check_mask32::offset),
+                              btext, blen, to)) {
+                pc += ld32(bc, pc + op::check_mask32::fail_jump);
+            } else {
+                pc += op::check_mask32::SIZE;
+            }
+            break;
+        case op::CHECK_MASK_64:
+            if (!check_mask_n(bc + pc + op::check_mask64::and_mask, bc + pc + op::check_mask64::cmp_mask,
+                              ld64(bc, pc + op::check_mask64::neg_mask), 64, (int)ld32(bc, pc + op::check_mask64::offset),
+                              btext, blen, to)) {
+                pc += ld32(bc, pc + op::check_mask64::fail_jump);
+            } else {
+                pc += op::check_mask64::SIZE;
+            }
+            break;
+        case op::CHECK_SHUFTI_16x8: case op::CHECK_SHUFTI_32x8: case op::CHECK_SHUFTI_16x16:
+        case op::CHECK_SHUFTI_32x16: case op::CHECK_SHUFTI_64x8: case op::CHECK_SHUFTI_64x16: {
+            const u32 fj = code == op::CHECK_SHUFTI_16x8 ? op::check_shufti_16x8::fail_jump
+                         : code == op::CHECK_SHUFTI_32x8 ? op::check_shufti_32x8::fail_jump
+                         : code == op::CHECK_SHUFTI_16x16 ? op::check_shufti_16x16::fail_jump
+                         : code == op::CHECK_SHUFTI_32x16 ? op::check_shufti_32x16::fail_jump
+                         : code == op::CHECK_SHUFTI_64x8 ? op::check_shufti_64x8::fail_jump : op::check_shufti_64x16::fail_jump;
+            // every shape's fail_jump is its last operand: the instruction ends 4 bytes later (rounded to 8)
+            if (!check_shufti(bc + pc, code, btext, blen, to)) pc += ld32(bc, pc + fj);
+            else pc += (fj + 4 + 7) & ~7u;
+            break;
+        }
         case op::CATCH_UP:
         case op::CLEAR_WORK_DONE:
             pc += op::SIZE_1;
@@ -738,6 +850,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_scan(const DevDb db, const DevCo
 }
 
 #include "turbo.cuh"
+#include "turbo2.cuh"
 #include "limex.cuh"
 #include "mcclellan.cuh"
 
@@ -812,20 +925,6 @@ __global__ void __launch_bounds__(THREADS) k_small_finalize(const Rec *in, Rec *
     if (tid == 0) *n_out = total;
 }
 
-template <int THREADS>
-cudaError_t launch_small_finalize(cudaStream_t st, const Rec *in, Rec *out_recs, hs_gpu_match_t *out, unsigned long long *n_out,
-                                  const unsigned long long *n_raw, u64 arena_cap) {
-    using Sort = cub::BlockMergeSort<Rec, THREADS, SMALL_FIN_ITEMS>;
-    const size_t dyn = sizeof(typename Sort::TempStorage);
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(k_small_finalize<THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
-        if (e != cudaSuccess) return e;
-        configured = true;
-    }
-    k_small_finalize<THREADS><<<1, THREADS, dyn, st>>>(in, out_recs, out, n_out, n_raw, arena_cap);
-    return cudaGetLastError();
-}
 
 // keep[i] = 0 iff record i repeats record i-1 under a dedupe key (dedupeCatchup, src/report.h:83-93)
 __global__ void k_flag_dups(const Rec *in, u8 *keep, u64 n) {
@@ -910,6 +1009,7 @@ struct DbImage {  // one uploaded database
     u64 *d_pair = nullptr;
     turbo::Slot *d_slots = nullptr;
     u32 *d_bloom = nullptr;
+    u32 *d_gram = nullptr;
     turbo::Tables turbo_tabs;
     u64 *d_lx = nullptr;
     limex_dev::Tables lx_tabs;
@@ -924,6 +1024,8 @@ struct DbImage {  // one uploaded database
         if (d_pair) cudaFree(d_pair);
         if (d_slots) cudaFree(d_slots);
         if (d_bloom) cudaFree(d_bloom);
+        if (d_gram) cudaFree(d_gram);
+        d_gram = nullptr;
         if (d_lx) cudaFree(d_lx);
         d_lx = nullptr;
         d_bloom = nullptr;
@@ -978,16 +1080,34 @@ struct hs_gpu_scratch {
     void *last_image = nullptr;  // DbImage that produced the current matches
     hs_gpu_stats_t stats{};
     int sm_count = 148;
-    long opt_frontend = 0;
+    long opt_frontend = 0;   // 0: k_turbo2 (default), 1: the database's own FDR / Teddy / noodle tables (k_scan), 2: k_turbo
     long opt_grid = 0;
+    long opt_warps = 0;      // k_turbo2: cap on warps per CTA (0 = as many as fit)
+    size_t smem_optin_max = 227 * 1024;
     u64 arena_hint = 1 << 16;
     u64 last_raw = ~0ull;  // record count of the previous scan (picks the finalize kernel size)
     u64 lx_event_hint = 1 << 16;
+    // kernels whose > 48 KiB dynamic shared memory opt-in has been set ON THIS SCRATCH'S DEVICE (the attribute is per
+    // device; a scratch has one device and one user at a time, so this needs no lock)
+    std::vector<std::pair<const void *, size_t>> smem_optin;
 };
 
 namespace {
 
 std::mutex g_init_mutex;
+
+cudaError_t ensure_smem_optin(hs_gpu_scratch *s, const void *fn, size_t dyn) {
+    for (auto &e : s->smem_optin)
+        if (e.first == fn) {
+            if (dyn <= e.second) return cudaSuccess;
+            cudaError_t rv = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+            if (rv == cudaSuccess) e.second = dyn;
+            return rv;
+        }
+    cudaError_t rv = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+    if (rv == cudaSuccess) s->smem_optin.emplace_back(fn, dyn);
+    return rv;
+}
 
 // Sheng -> state-major table (see the upload).  Reference semantics kept: state byte = id | flags
 // (shengcompile.cpp:343-357); a DEAD-flagged state is a trap without reports (census), so it may become state 0.
@@ -1140,13 +1260,17 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         const turbo::Tables &tt = im->turbo_tabs;
         if (cudaMalloc((void **)&im->d_pair, tt.pair.size() * 8) != cudaSuccess ||
             cudaMalloc((void **)&im->d_slots, tt.slots.size() * sizeof(turbo::Slot)) != cudaSuccess ||
-            cudaMalloc((void **)&im->d_bloom, tt.bloom.size() * 4) != cudaSuccess) {
+            cudaMalloc((void **)&im->d_bloom, tt.bloom.size() * 4) != cudaSuccess ||
+            cudaMalloc((void **)&im->d_gram, tt.gram.size() * 4) != cudaSuccess) {
             im->release(); delete im; return HS_NOMEM;
         }
+        cudaMemcpyAsync(im->d_gram, tt.gram.data(), tt.gram.size() * 4, cudaMemcpyHostToDevice, s->stream);
+        d.gram_tab = im->d_gram;
+        d.gG1 = tt.G1; d.gmul = tt.gmul; d.gS = tt.S;
         cudaMemcpyAsync(im->d_pair, tt.pair.data(), tt.pair.size() * 8, cudaMemcpyHostToDevice, s->stream);
         cudaMemcpyAsync(im->d_slots, tt.slots.data(), tt.slots.size() * sizeof(turbo::Slot), cudaMemcpyHostToDevice, s->stream);
         cudaMemcpyAsync(im->d_bloom, tt.bloom.data(), tt.bloom.size() * 4, cudaMemcpyHostToDevice, s->stream);
-        im->device_bytes += tt.pair.size() * 8 + tt.slots.size() * sizeof(turbo::Slot) + tt.bloom.size() * 4;
+        im->device_bytes += tt.pair.size() * 8 + tt.slots.size() * sizeof(turbo::Slot) + tt.bloom.size() * 4 + tt.gram.size() * 4;
         d.pair_tab = im->d_pair;
         d.slots = im->d_slots;
         d.bloom = im->d_bloom;
@@ -1156,6 +1280,17 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
     s->dbs.push_back(im);
     *out = im;
     return HS_SUCCESS;
+}
+
+template <int THREADS>
+cudaError_t launch_small_finalize(hs_gpu_scratch *s, const Rec *in, Rec *out_recs, hs_gpu_match_t *out, unsigned long long *n_out,
+                                  const unsigned long long *n_raw, u64 arena_cap) {
+    using Sort = cub::BlockMergeSort<Rec, THREADS, SMALL_FIN_ITEMS>;
+    const size_t dyn = sizeof(typename Sort::TempStorage);
+    cudaError_t e = ensure_smem_optin(s, (const void *)k_small_finalize<THREADS>, dyn);
+    if (e != cudaSuccess) return e;
+    k_small_finalize<THREADS><<<1, THREADS, dyn, s->stream>>>(in, out_recs, out, n_out, n_raw, arena_cap);
+    return cudaGetLastError();
 }
 
 inline bool resize_ok(std::vector<u32> &v, size_t n) { v.resize(n); return true; }
@@ -1187,24 +1322,46 @@ u32 turbo_grid(const hs_gpu_scratch *s, const DevCorpus &cp, u32 warps_per_cta) 
 template <int K, bool ORDERED>
 hs_error_t launch_turbo(hs_gpu_scratch *s, const DevDb &db, const DevCorpus &cp, const DevArena &ar) {
     const size_t dyn = turbo_smem_bytes<ORDERED>(db);
-    static size_t configured = 0;
-    if (dyn > configured) {
-        CU_OK(cudaFuncSetAttribute(k_turbo<K, ORDERED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
-        configured = dyn;
-    }
+    CU_OK(ensure_smem_optin(s, (const void *)k_turbo<K, ORDERED>, dyn));
     k_turbo<K, ORDERED><<<turbo_grid(s, cp, turbo_warps<ORDERED>()), turbo_warps<ORDERED>() * 32, dyn, s->stream>>>(db, cp, ar);
     CU_OK(cudaGetLastError());
     return HS_SUCCESS;
 }
 
+// k_turbo2: as many warps per CTA (one CTA per SM) as the shared memory left by the tables holds, 32 at most
+template <bool ORDERED>
+u32 turbo2_warps(const hs_gpu_scratch *s, const DevDb &db) {
+    const size_t budget = s->smem_optin_max > 2048 ? s->smem_optin_max - 1024 : 0, tables = turbo2_smem_bytes<ORDERED>(db, 0);
+    u32 w = tables < budget ? (u32)((budget - tables) / sizeof(Turbo2WarpShared<ORDERED>)) : 0;
+    if (w > 32) w = 32;
+    if (s->opt_warps > 0 && (u32)s->opt_warps < w) w = (u32)s->opt_warps;
+    return w;
+}
+
+template <int K, int S, bool ORDERED>
+hs_error_t launch_turbo2(hs_gpu_scratch *s, const DevDb &db, const DevCorpus &cp, const DevArena &ar, u32 grid, u32 warps) {
+    const size_t dyn = turbo2_smem_bytes<ORDERED>(db, (int)warps);
+    CU_OK(ensure_smem_optin(s, (const void *)k_turbo2<K, S, ORDERED>, dyn));
+    k_turbo2<K, S, ORDERED><<<grid, warps * 32, dyn, s->stream>>>(db, cp, ar);
+    CU_OK(cudaGetLastError());
+    return HS_SUCCESS;
+}
+
+template <bool ORDERED>
+hs_error_t launch_turbo2_any(hs_gpu_scratch *s, const DevDb &db, const DevCorpus &cp, const DevArena &ar, u32 grid, u32 warps) {
+    if (db.gS == 2) return db.tK == 3 ? launch_turbo2<3, 2, ORDERED>(s, db, cp, ar, grid, warps) : launch_turbo2<4, 2, ORDERED>(s, db, cp, ar, grid, warps);
+    switch (db.tK) {
+    case 1: return launch_turbo2<1, 1, ORDERED>(s, db, cp, ar, grid, warps);
+    case 2: return launch_turbo2<2, 1, ORDERED>(s, db, cp, ar, grid, warps);
+    case 3: return launch_turbo2<3, 1, ORDERED>(s, db, cp, ar, grid, warps);
+    default: return launch_turbo2<4, 1, ORDERED>(s, db, cp, ar, grid, warps);
+    }
+}
+
 template <class FE, bool NOODLE>
 hs_error_t launch_scan(hs_gpu_scratch *s, const DevDb &db, const DevCorpus &cp, const DevArena &ar) {
     const size_t dyn = FE::smem_bytes(db);
-    static size_t configured = 0;
-    if (dyn > configured) {
-        CU_OK(cudaFuncSetAttribute(k_scan<FE, NOODLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
-        configured = dyn;
-    }
+    CU_OK(ensure_smem_optin(s, (const void *)k_scan<FE, NOODLE>, dyn));
     u32 grid = s->opt_grid > 0 ? (u32)s->opt_grid : (u32)s->sm_count;
     const u32 need = (cp.nstrips + WARPS - 1) / WARPS;
     if (grid > need) grid = need ? need : 1;
@@ -1216,11 +1373,7 @@ hs_error_t launch_scan(hs_gpu_scratch *s, const DevDb &db, const DevCorpus &cp, 
 template <int G>
 hs_error_t launch_limex_g(hs_gpu_scratch *s, const DbImage *im, const DevCorpus &cp, const DevArena &ar) {
     const size_t dyn = limex_smem_bytes(im->lx);
-    static size_t configured = 0;
-    if (dyn > configured) {
-        CU_OK(cudaFuncSetAttribute(k_limex<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
-        configured = dyn;
-    }
+    CU_OK(ensure_smem_optin(s, (const void *)k_limex<G>, dyn));
     // persistent groups of G lanes; no more CTAs than there are buffers to hand out
     const u32 groups_per_cta = LX_THREADS / G;
     u32 grid = s->opt_grid > 0 ? (u32)s->opt_grid : 4u * (u32)s->sm_count;
@@ -1249,11 +1402,7 @@ hs_error_t launch_limex(hs_gpu_scratch *s, const DbImage *im, const DevCorpus &c
 template <bool WIDE16, bool SMEM, bool SHERMAN>
 hs_error_t launch_mcclellan_t(hs_gpu_scratch *s, const DbImage *im, const DevCorpus &cp, const DevArena &ar) {
     const size_t dyn = mcc_smem_bytes(im->mcc);
-    static size_t configured = 0;
-    if (dyn > configured) {
-        CU_OK(cudaFuncSetAttribute(k_mcclellan<WIDE16, SMEM, SHERMAN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
-        configured = dyn;
-    }
+    CU_OK(ensure_smem_optin(s, (const void *)k_mcclellan<WIDE16, SMEM, SHERMAN>, dyn));
     // persistent threads, one buffer each at a time, fed from a counter: every SM gets a CTA as soon as there is a
     // warp's worth of buffers for it
     u32 grid = s->opt_grid > 0 ? (u32)s->opt_grid : (u32)s->sm_count;
@@ -1285,7 +1434,10 @@ hs_error_t launch_mcclellan(hs_gpu_scratch *s, const DbImage *im, const DevCorpu
 // them; no sort.  Returns HS_INSUFFICIENT_SPACE when the general path must be used instead.
 hs_error_t scan_device_ordered(hs_gpu_scratch *s, DbImage *im, const DevCorpus &cp) {
     hs_gpu_stats_t &st = s->stats;
-    const u32 grid = turbo_grid(s, cp, turbo_warps<true>()), W = grid * turbo_warps<true>();
+    const bool v2 = s->opt_frontend != 2;
+    const u32 cta_warps = v2 ? turbo2_warps<true>(s, im->dev) : (u32)turbo_warps<true>();
+    if (!cta_warps) return HS_INSUFFICIENT_SPACE;
+    const u32 grid = turbo_grid(s, cp, cta_warps), W = grid * cta_warps;
     CU_OK(s->seg_count.reserve(W));
     for (int attempt = 0;; attempt++) {
         const u64 seg_cap = s->seg_cap_hint;
@@ -1303,6 +1455,8 @@ hs_error_t scan_device_ordered(hs_gpu_scratch *s, DbImage *im, const DevCorpus &
         DevArena ar{s->recs.p, ctl + 0, ctl + 1, reinterpret_cast<u32 *>(ctl + 3), 0, s->seg_count.p, (u32)seg_cap};
         CU_OK(cudaEventRecord(s->ev[1], s->stream));
         hs_error_t rv;
+        if (v2) rv = launch_turbo2_any<true>(s, im->dev, cp, ar, grid, cta_warps);
+        else
         switch (im->dev.tK) {
         case 1: rv = launch_turbo<1, true>(s, im->dev, cp, ar); break;
         case 2: rv = launch_turbo<2, true>(s, im->dev, cp, ar); break;
@@ -1374,7 +1528,10 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
         hs_error_t rv;
         CU_OK(cudaEventRecord(s->ev[6], s->stream));
         const bool use_turbo = im->dev.tK && s->opt_frontend != 1;
-        if (use_turbo) {
+        const u32 t2w = use_turbo && s->opt_frontend != 2 ? turbo2_warps<false>(s, im->dev) : 0;
+        if (t2w) {
+            rv = launch_turbo2_any<false>(s, im->dev, cp, ar, turbo_grid(s, cp, t2w), t2w);
+        } else if (use_turbo) {
             switch (im->dev.tK) {
             case 1: rv = launch_turbo<1, false>(s, im->dev, cp, ar); break;
             case 2: rv = launch_turbo<2, false>(s, im->dev, cp, ar); break;
@@ -1398,11 +1555,11 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
         CU_OK(cudaEventRecord(s->ev[2], s->stream));
         // sized by the previous scan's count (fewer threads = fewer merge rounds and cheaper barriers)
         if (s->last_raw <= 256 * SMALL_FIN_ITEMS)
-            CU_OK(launch_small_finalize<256>(s->stream, s->recs.p, s->recs2.p, s->d_matches.p, s->d_ctl + 4, s->d_ctl + 0, s->recs.cap));
+            CU_OK(launch_small_finalize<256>(s, s->recs.p, s->recs2.p, s->d_matches.p, s->d_ctl + 4, s->d_ctl + 0, s->recs.cap));
         else if (s->last_raw <= 512 * SMALL_FIN_ITEMS)
-            CU_OK(launch_small_finalize<512>(s->stream, s->recs.p, s->recs2.p, s->d_matches.p, s->d_ctl + 4, s->d_ctl + 0, s->recs.cap));
+            CU_OK(launch_small_finalize<512>(s, s->recs.p, s->recs2.p, s->d_matches.p, s->d_ctl + 4, s->d_ctl + 0, s->recs.cap));
         else
-            CU_OK(launch_small_finalize<1024>(s->stream, s->recs.p, s->recs2.p, s->d_matches.p, s->d_ctl + 4, s->d_ctl + 0, s->recs.cap));
+            CU_OK(launch_small_finalize<1024>(s, s->recs.p, s->recs2.p, s->d_matches.p, s->d_ctl + 4, s->d_ctl + 0, s->recs.cap));
         CU_OK(cudaEventRecord(s->ev[3], s->stream));
         CU_OK(cudaMemcpyAsync(s->h_ctl, s->d_ctl, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
         CU_OK(cudaStreamSynchronize(s->stream));
@@ -1615,6 +1772,7 @@ hs_error_t scan_host_batch(const hs_database_t *db, const char *const *data, con
                            unsigned count, hs_gpu_scratch *s, DbImage **im_out) {
     hs_error_t rv = ensure_device(s);
     if (rv != HS_SUCCESS) return rv;
+    cudaGetLastError();  // a non-sticky error left behind by an earlier call must not fail this one's launch checks
     DbImage *im = nullptr;
     rv = upload_database(s, db, &im);
     if (rv != HS_SUCCESS) return rv;
@@ -1632,8 +1790,13 @@ hs_error_t scan_host_batch(const hs_database_t *db, const char *const *data, con
     rv = scan_device(s, im, s->staging);
     if (rv != HS_SUCCESS) return rv;
     const auto t2 = now();
-    // ev[1] was re-recorded by scan_device right after the copies were queued: h2d = ev0 -> ev1
-    cudaEventElapsedTime(&s->stats.h2d_ms, h2d_begin, s->ev[1]);
+    // ev[1] was re-recorded by scan_device right after the copies were queued: h2d = ev0 -> ev1.  An empty batch
+    // takes scan_device's early-out, which records nothing: no interval to read then.
+    s->stats.h2d_ms = 0;
+    if (s->staging.total && s->staging.count && cudaEventElapsedTime(&s->stats.h2d_ms, h2d_begin, s->ev[1]) != cudaSuccess) {
+        s->stats.h2d_ms = 0;
+        cudaGetLastError();
+    }
     rv = fetch_matches(s, im);
     if (trace)
         fprintf(stderr, "hs_gpu trace: stage %.1f us, scan_device (incl. wait for H2D) %.1f us, fetch %.1f us\n",
@@ -1696,7 +1859,10 @@ hs_error_t hs_gpu_alloc_scratch(const hs_database_t *db, hs_gpu_scratch_t **scra
         s->in_use.store(1);
         if (cudaGetDevice(&s->device) != cudaSuccess) { delete s; return HS_ARCH_ERROR; }
         cudaDeviceProp prop{};
-        if (cudaGetDeviceProperties(&prop, s->device) == cudaSuccess) s->sm_count = prop.multiProcessorCount;
+        if (cudaGetDeviceProperties(&prop, s->device) == cudaSuccess) {
+            s->sm_count = prop.multiProcessorCount;
+            s->smem_optin_max = prop.sharedMemPerBlockOptin;
+        }
         if (cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) != cudaSuccess) { delete s; return HS_UNKNOWN_ERROR; }
         for (auto &e : s->ev) cudaEventCreate(&e);
         if (cudaMalloc((void **)&s->d_ctl, 24 * sizeof(unsigned long long)) != cudaSuccess ||
@@ -1728,6 +1894,7 @@ hs_error_t hs_gpu_clone_scratch(const hs_gpu_scratch_t *src, hs_gpu_scratch_t **
     if (!d) return HS_INVALID;
     d->opt_frontend = src->opt_frontend;
     d->opt_grid = src->opt_grid;
+    d->opt_warps = src->opt_warps;
     *dest = d;
     return HS_SUCCESS;
 }
@@ -1910,8 +2077,9 @@ hs_error_t hs_gpu_histogram(hs_gpu_scratch_t *scratch, void *device_hist_u64, ui
     if (!scratch || scratch->magic != 0x47505553 || !device_hist_u64) return HS_INVALID;
     InUseGuard g(scratch);
     if (!g.ok) return HS_SCRATCH_IN_USE;
-    if (scratch->fetched && scratch->last_image && static_cast<DbImage *>(scratch->last_image)->view.ekey_count)
-        return HS_INVALID;  // single-match sets are resolved on the host: histogram the fetched matches instead
+    // d_matches of a single-match (exhaustion key) set still holds every repeat and the quiet records until the fetch
+    // resolves them on the host copy: refuse rather than count them
+    if (scratch->last_image && static_cast<DbImage *>(scratch->last_image)->view.ekey_count) return HS_INVALID;
     const u64 n = scratch->n_matches;
     if (n) {
         k_histogram<<<(unsigned)((n + 255) / 256), 256, 0, scratch->stream>>>(
@@ -1932,6 +2100,7 @@ hs_error_t hs_gpu_set_option(hs_gpu_scratch_t *scratch, const char *name, long v
     if (!scratch || scratch->magic != 0x47505553 || !name) return HS_INVALID;
     if (!strcmp(name, "frontend")) { scratch->opt_frontend = value; return HS_SUCCESS; }
     if (!strcmp(name, "grid")) { scratch->opt_grid = value; return HS_SUCCESS; }
+    if (!strcmp(name, "warps")) { scratch->opt_warps = value; return HS_SUCCESS; }
     if (!strcmp(name, "ordered")) { scratch->opt_ordered = value; return HS_SUCCESS; }
     if (!strcmp(name, "segment")) { scratch->seg_cap_hint = value > 0 ? (u64)value : 1; return HS_SUCCESS; }
     if (!strcmp(name, "arena")) { scratch->arena_hint = value > 0 ? (u64)value : 1; return HS_SUCCESS; }

@@ -56,40 +56,86 @@ struct DbView {
 
 inline bool in_range(const DbView &d, size_t off, size_t n) { return off <= d.bc_len && n <= d.bc_len - off; }
 
-// Walk one Rose program; collect opcodes; follow nothing outside it (INCLUDED_JUMP children are
-// programs of other literals and are walked on their own).
+// Padded size of an instruction the device interpreter implements (0 = not implemented) and the offset of its
+// fail_jump operand (0 = the instruction cannot fail).
+inline size_t op_size(u8 code, size_t &fail_jump_at) {
+    fail_jump_at = 0;
+    switch (code) {
+    case op::END: case op::CATCH_UP: case op::CLEAR_WORK_DONE: return op::SIZE_1;
+    case op::CHECK_GROUPS: return op::check_groups::SIZE;
+    case op::CHECK_MASK: fail_jump_at = op::check_mask::fail_jump; return op::check_mask::SIZE;
+    case op::CHECK_MASK_32: fail_jump_at = op::check_mask32::fail_jump; return op::check_mask32::SIZE;
+    case op::CHECK_BYTE: fail_jump_at = op::check_byte::fail_jump; return op::check_byte::SIZE;
+    case op::CHECK_SHUFTI_16x8: fail_jump_at = op::check_shufti_16x8::fail_jump; return op::check_shufti_16x8::SIZE;
+    case op::CHECK_SHUFTI_32x8: fail_jump_at = op::check_shufti_32x8::fail_jump; return op::check_shufti_32x8::SIZE;
+    case op::CHECK_SHUFTI_16x16: fail_jump_at = op::check_shufti_16x16::fail_jump; return op::check_shufti_16x16::SIZE;
+    case op::CHECK_SHUFTI_32x16: fail_jump_at = op::check_shufti_32x16::fail_jump; return op::check_shufti_32x16::SIZE;
+    case op::CHECK_MASK_64: fail_jump_at = op::check_mask64::fail_jump; return op::check_mask64::SIZE;
+    case op::CHECK_SHUFTI_64x8: fail_jump_at = op::check_shufti_64x8::fail_jump; return op::check_shufti_64x8::SIZE;
+    case op::CHECK_SHUFTI_64x16: fail_jump_at = op::check_shufti_64x16::fail_jump; return op::check_shufti_64x16::SIZE;
+    case op::DEDUPE: fail_jump_at = op::dedupe::fail_jump; return op::dedupe::SIZE;
+    case op::REPORT: case op::FINAL_REPORT: return op::report::SIZE;
+    case op::REPORT_EXHAUST: return op::report_exhaust::SIZE;
+    case op::DEDUPE_AND_REPORT: fail_jump_at = op::dedupe_and_report::fail_jump; return op::dedupe_and_report::SIZE;
+    case op::CHECK_EXHAUSTED: fail_jump_at = op::check_exhausted::fail_jump; return op::check_exhausted::SIZE;
+    case op::SQUASH_GROUPS: return op::squash_groups::SIZE;
+    case op::SET_EXHAUST: return op::set_exhaust::SIZE;
+    case op::INCLUDED_JUMP: return op::included_jump::SIZE;
+    case op::CHECK_LONG_LIT: case op::CHECK_LONG_LIT_NOCASE: case op::CHECK_MED_LIT: case op::CHECK_MED_LIT_NOCASE:
+        fail_jump_at = op::check_lit::fail_jump; return op::check_lit::SIZE;
+    default: return 0;
+    }
+}
+
+// Walk one Rose program to its END; this is the validation gate for caller-supplied blobs, so every instruction must lie
+// inside the bytecode with its full operand block, every fail_jump must land on an instruction of this same program at
+// or before its END (the device interpreter follows them unchecked), and a DEDUPE must be followed by one of the three
+// reports the interpreter fuses it with.  INCLUDED_JUMP children are programs of other literals, walked on their own.
 inline int census_program(const DbView &d, u32 prog, std::string &why, u32 &max_lit_len) {
     size_t pc = prog;
+    std::vector<size_t> starts, targets;
     for (int guard = 0; guard < 4096; guard++) {
-        if (!in_range(d, pc, 8)) { why = "program runs past the bytecode"; return E_INVALID; }
+        if (!in_range(d, pc, 8) || (pc & 7)) { why = "program runs past the bytecode"; return E_INVALID; }
         const u8 code = rd8(d.bc, pc);
-        size_t sz = 0;
-        switch (code) {
-        case op::END: return E_SUCCESS;
-        case op::CHECK_GROUPS: sz = op::check_groups::SIZE; break;
-        case op::CHECK_MASK: sz = op::check_mask::SIZE; break;
-        case op::CHECK_BYTE: sz = op::check_byte::SIZE; break;
-        case op::CATCH_UP: case op::CLEAR_WORK_DONE: sz = op::SIZE_1; break;
-        case op::DEDUPE: sz = op::dedupe::SIZE; break;
-        case op::REPORT: sz = op::report::SIZE; break;
-        case op::FINAL_REPORT: return E_SUCCESS;  // always terminates the program
-        case op::REPORT_EXHAUST: sz = op::report_exhaust::SIZE; break;
-        case op::DEDUPE_AND_REPORT: sz = op::dedupe_and_report::SIZE; break;
-        case op::CHECK_EXHAUSTED: sz = op::check_exhausted::SIZE; break;
-        case op::SQUASH_GROUPS: sz = op::squash_groups::SIZE; break;
-        case op::SET_EXHAUST: sz = op::set_exhaust::SIZE; break;
-        case op::INCLUDED_JUMP: sz = op::included_jump::SIZE; break;
-        case op::CHECK_LONG_LIT: case op::CHECK_LONG_LIT_NOCASE:
-        case op::CHECK_MED_LIT: case op::CHECK_MED_LIT_NOCASE: {
-            sz = op::check_lit::SIZE;
-            u32 lo = rd32(d.bc, pc + op::check_lit::lit_offset), ll = rd32(d.bc, pc + op::check_lit::lit_length);
-            if (!in_range(d, lo, ll)) { why = "literal text outside the bytecode"; return E_INVALID; }
-            if (ll > max_lit_len) max_lit_len = ll;
-            break;
-        }
-        default:
+        size_t fj = 0;
+        const size_t sz = op_size(code, fj);
+        if (!sz) {
             why = "Rose opcode " + std::to_string((int)code) + " is not implemented on the device path";
             return E_ARCH;
+        }
+        if (!in_range(d, pc, sz)) { why = "instruction operands run past the bytecode"; return E_INVALID; }
+        starts.push_back(pc);
+        if (fj) {
+            const u32 j = rd32(d.bc, pc + fj);
+            if (j < sz || (j & 7)) { why = "fail_jump does not move forward to an instruction boundary"; return E_INVALID; }
+            targets.push_back(pc + j);
+        }
+        if (code == op::CHECK_LONG_LIT || code == op::CHECK_LONG_LIT_NOCASE || code == op::CHECK_MED_LIT ||
+            code == op::CHECK_MED_LIT_NOCASE) {
+            const u32 lo = rd32(d.bc, pc + op::check_lit::lit_offset), ll = rd32(d.bc, pc + op::check_lit::lit_length);
+            if (!in_range(d, lo, ll)) { why = "literal text outside the bytecode"; return E_INVALID; }
+            if (ll > max_lit_len) max_lit_len = ll;
+        }
+        if (code == op::DEDUPE) {
+            const u8 nxt = in_range(d, pc + sz, 8) ? rd8(d.bc, pc + sz) : (u8)op::END;
+            if (nxt != op::REPORT && nxt != op::REPORT_EXHAUST && nxt != op::SET_EXHAUST) {
+                why = "DEDUPE followed by opcode " + std::to_string((int)nxt) + " is not implemented on the device path";
+                return E_ARCH;
+            }
+        }
+        if (code == op::END || code == op::FINAL_REPORT) {  // FINAL_REPORT always terminates the program
+            // a FINAL_REPORT in mid-program is followed by the blocks its predecessors' fail_jumps skip to: keep walking
+            // while some jump still points beyond this instruction
+            bool beyond = false;
+            for (size_t t : targets) if (t > pc) beyond = true;
+            if (code == op::END || !beyond) {
+                for (size_t t : targets) {
+                    bool found = false;
+                    for (size_t st : starts) if (st == t) found = true;
+                    if (!found) { why = "fail_jump target is not an instruction of its program"; return E_INVALID; }
+                }
+                return E_SUCCESS;
+            }
         }
         pc += sz;
     }

@@ -207,6 +207,9 @@ namespace check_shufti_16x8 { constexpr size_t nib_mask = 1, bucket_select_mask 
 namespace check_shufti_32x8 { constexpr size_t hi_mask = 1, lo_mask = 17, bucket_select_mask = 33, neg_mask = 68, offset = 72, fail_jump = 76, SIZE = 80; }
 namespace check_shufti_16x16 { constexpr size_t hi_mask = 1, lo_mask = 33, bucket_select_mask = 65, neg_mask = 100, offset = 104, fail_jump = 108, SIZE = 112; }
 namespace check_shufti_32x16 { constexpr size_t hi_mask = 1, lo_mask = 33, bucket_select_mask_hi = 65, bucket_select_mask_lo = 97, neg_mask = 132, offset = 136, fail_jump = 140, SIZE = 144; }
+namespace check_mask64 { constexpr size_t and_mask = 1, cmp_mask = 65, neg_mask = 136, offset = 144, fail_jump = 148, SIZE = 152; }
+namespace check_shufti_64x8 { constexpr size_t hi_mask = 1, lo_mask = 65, bucket_select_mask = 129, neg_mask = 200, offset = 208, fail_jump = 212, SIZE = 216; }
+namespace check_shufti_64x16 { constexpr size_t hi_mask_1 = 1, hi_mask_2 = 65, lo_mask_1 = 129, lo_mask_2 = 193, bucket_select_mask_hi = 257, bucket_select_mask_lo = 321, neg_mask = 392, offset = 400, fail_jump = 404, SIZE = 408; }
 namespace dedupe { constexpr size_t quash_som = 1, dkey = 4, offset_adjust = 8, fail_jump = 12, SIZE = 16; }
 namespace report { constexpr size_t onmatch = 4, offset_adjust = 8, SIZE = 16; }           // REPORT, FINAL_REPORT
 namespace report_exhaust { constexpr size_t onmatch = 4, offset_adjust = 8, ekey = 12, SIZE = 16; }
