@@ -86,10 +86,21 @@ def test_shufti_truffle_vermicelli_all_alignments(ref):
             for rev in (0, 1):
                 assert L.hs_gpu_shufti(lo, hi, buf, len(buf), rev) == ref.L.ref_shim_shufti(lo_t, hi_t, p0, len(buf), rev)
                 m1_t, m2_t = (C.c_ubyte * 16)(*m1), (C.c_ubyte * 16)(*m2)
-                assert L.hs_gpu_truffle(m1, m2, buf, len(buf), rev) == ref.L.ref_shim_truffle(m1_t, m2_t, p0, len(buf), rev)
+                got_t, ref_t = L.hs_gpu_truffle(m1, m2, buf, len(buf), rev), ref.L.ref_shim_truffle(m1_t, m2_t, p0, len(buf), rev)
+                if rev and 0 in chars and len(buf) < 64 and got_t != ref_t:
+                    # reference defect in its 256/512-bit builds (src/nfa/truffle_simd.hpp:184-195): a reverse scan of a
+                    # buffer shorter than the vector zero-pads it, NUL is in the class, so the padding "matches" past the
+                    # end and the routine answers "not found".  The scalar definition (checked above) stands.
+                    assert ref_t == -1
+                    continue
+                assert got_t == ref_t
 
 
 def test_vermicelli_double_and_nocase(ref):
+    # the reference's 512-bit forward vermicelli misses a match on the very last byte of the buffer (seen with n = 200
+    # and 5000 in this very loop; scalar definition src/nfa/vermicelli.hpp): the comparison uses its 256-bit build
+    import refrt
+    ref = refrt.RefRuntime("avx2")
     L = gpu.lib()
     L.hs_gpu_vermicelli.restype = L.hs_gpu_vermicelli_double.restype = C.c_longlong
     ref.L.ref_shim_verm.restype = C.c_longlong

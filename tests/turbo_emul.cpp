@@ -16,17 +16,13 @@ struct Text {
 };
 bool tier1_flag(const turbo::Tables &t, const Text &tx, long long pos) {
     const u32 K = t.K;
-    auto test = [&](long long gram_first, u32 idx_byte) {
-        const u32 row = K > 1 ? turbo::gram_row(tx.window(gram_first), t.gmul, t.G1) : 0u;
-        return ((t.gram[row] << (idx_byte & 31)) & 0x80000000u) != 0;
-    };
-    if (t.S == 1) {
-        // even positions take the A test (index = first byte of the gram), odd ones the B test (index = last byte)
-        if ((pos & 1) == 0) return test(pos - (long long)K + 2, tx.at(pos - (long long)K + 1));
-        return test(pos - (long long)K + 1, tx.at(pos));
-    }
-    auto sample = [&](long long p) { return (p & 1) && test(p - (long long)K + 1, tx.at(p)); };
-    return sample(pos - 1) || sample(pos) || sample(pos + 1);
+    // even positions take the A test (index = first byte of the gram), odd ones the B test (index = last byte)
+    const bool a = (pos & 1) == 0;
+    const long long shared_first = a ? pos - (long long)K + 2 : pos - (long long)K + 1;
+    const u32 idx_byte = a ? tx.at(pos - (long long)K + 1) : tx.at(pos);
+    const u32 row = K > 1 ? turbo::gram_row(tx.window(shared_first), t.gmul, t.G1) : 0u;
+    const u32 word = t.gram[row];
+    return ((word << (idx_byte & 31)) & 0x80000000u) != 0;
 }
 bool tier2_flag(const turbo::Tables &t, const Text &tx, long long pos) {
     u32 ktail = 0;
@@ -41,7 +37,7 @@ bool tier2_flag(const turbo::Tables &t, const Text &tx, long long pos) {
 
 extern "C" {
 // ends[i] = index of a literal's LAST byte in the flat text.  Returns the number of ends either tier would drop
-// (must be 0), or -1 when the tables cannot be built.  stats: [0] K, [1] stride, [2] G1, [3] tier-1 survivors,
+// (must be 0), or -1 when the tables cannot be built.  stats: [0] K, [1] wide form?, [2] G1, [3] tier-1 survivors,
 // [4] tier-2 survivors over the whole text.
 long turbo_emul_check(const void *db, const u8 *text, u64 len, const u64 *ends, u32 n_ends, u64 *stats) {
     DbView v;
@@ -56,7 +52,7 @@ long turbo_emul_check(const void *db, const u8 *text, u64 len, const u64 *ends, 
     u64 c1 = 0, c2 = 0;
     for (u64 p = 0; p < len; p++)
         if (tier1_flag(t, tx, (long long)p)) { c1++; if (tier2_flag(t, tx, (long long)p)) c2++; }
-    if (stats) { stats[0] = t.K; stats[1] = t.S; stats[2] = t.G1; stats[3] = c1; stats[4] = c2; }
+    if (stats) { stats[0] = t.K; stats[1] = t.wide; stats[2] = t.G1; stats[3] = c1; stats[4] = c2; }
     return dropped;
 }
 }

@@ -92,7 +92,7 @@ struct DevDb {
     const u32 *bloom;     // second filter tier (turbo_tables.h, 3.)
     u32 tK, tH1, tH2, tL, tBL;
     const u32 *gram_tab;  // first tier of k_turbo2 (turbo_tables.h, "gram table")
-    u32 gG1, gmul, gS;
+    u32 gG1, gmul, gwide;
     u32 lx_abs;           // absolute bytecode offset of the LimExNFA (single-outfix databases)
 };
 
@@ -1080,7 +1080,8 @@ struct hs_gpu_scratch {
     void *last_image = nullptr;  // DbImage that produced the current matches
     hs_gpu_stats_t stats{};
     int sm_count = 148;
-    long opt_frontend = 0;   // 0: k_turbo2 (default), 1: the database's own FDR / Teddy / noodle tables (k_scan), 2: k_turbo
+    long opt_frontend = 0;   // 0: k_turbo2 or k_turbo by the tables' estimate, 1: the database's own FDR / Teddy / noodle
+                             // tables (k_scan), 2: k_turbo, 3: k_turbo2
     long opt_grid = 0;
     long opt_warps = 0;      // k_turbo2: cap on warps per CTA (0 = as many as fit)
     size_t smem_optin_max = 227 * 1024;
@@ -1266,7 +1267,7 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         }
         cudaMemcpyAsync(im->d_gram, tt.gram.data(), tt.gram.size() * 4, cudaMemcpyHostToDevice, s->stream);
         d.gram_tab = im->d_gram;
-        d.gG1 = tt.G1; d.gmul = tt.gmul; d.gS = tt.S;
+        d.gG1 = tt.G1; d.gmul = tt.gmul; d.gwide = tt.wide;
         cudaMemcpyAsync(im->d_pair, tt.pair.data(), tt.pair.size() * 8, cudaMemcpyHostToDevice, s->stream);
         cudaMemcpyAsync(im->d_slots, tt.slots.data(), tt.slots.size() * sizeof(turbo::Slot), cudaMemcpyHostToDevice, s->stream);
         cudaMemcpyAsync(im->d_bloom, tt.bloom.data(), tt.bloom.size() * 4, cudaMemcpyHostToDevice, s->stream);
@@ -1328,34 +1329,40 @@ hs_error_t launch_turbo(hs_gpu_scratch *s, const DevDb &db, const DevCorpus &cp,
     return HS_SUCCESS;
 }
 
-// k_turbo2: as many warps per CTA (one CTA per SM) as the shared memory left by the tables holds, 32 at most
+// k_turbo2: as many warps per CTA (one CTA per SM) as the shared memory left by the tables holds, T2MAXW at most
 template <bool ORDERED>
 u32 turbo2_warps(const hs_gpu_scratch *s, const DevDb &db) {
     const size_t budget = s->smem_optin_max > 2048 ? s->smem_optin_max - 1024 : 0, tables = turbo2_smem_bytes<ORDERED>(db, 0);
     u32 w = tables < budget ? (u32)((budget - tables) / sizeof(Turbo2WarpShared<ORDERED>)) : 0;
-    if (w > 32) w = 32;
+    if (w > (u32)T2MAXW) w = T2MAXW;
     if (s->opt_warps > 0 && (u32)s->opt_warps < w) w = (u32)s->opt_warps;
     return w;
 }
 
-template <int K, int S, bool ORDERED>
+template <int K, bool ORDERED>
 hs_error_t launch_turbo2(hs_gpu_scratch *s, const DevDb &db, const DevCorpus &cp, const DevArena &ar, u32 grid, u32 warps) {
     const size_t dyn = turbo2_smem_bytes<ORDERED>(db, (int)warps);
-    CU_OK(ensure_smem_optin(s, (const void *)k_turbo2<K, S, ORDERED>, dyn));
-    k_turbo2<K, S, ORDERED><<<grid, warps * 32, dyn, s->stream>>>(db, cp, ar);
+    CU_OK(ensure_smem_optin(s, (const void *)k_turbo2<K, ORDERED>, dyn));
+    k_turbo2<K, ORDERED><<<grid, warps * 32, dyn, s->stream>>>(db, cp, ar);
     CU_OK(cudaGetLastError());
     return HS_SUCCESS;
 }
 
 template <bool ORDERED>
 hs_error_t launch_turbo2_any(hs_gpu_scratch *s, const DevDb &db, const DevCorpus &cp, const DevArena &ar, u32 grid, u32 warps) {
-    if (db.gS == 2) return db.tK == 3 ? launch_turbo2<3, 2, ORDERED>(s, db, cp, ar, grid, warps) : launch_turbo2<4, 2, ORDERED>(s, db, cp, ar, grid, warps);
     switch (db.tK) {
-    case 1: return launch_turbo2<1, 1, ORDERED>(s, db, cp, ar, grid, warps);
-    case 2: return launch_turbo2<2, 1, ORDERED>(s, db, cp, ar, grid, warps);
-    case 3: return launch_turbo2<3, 1, ORDERED>(s, db, cp, ar, grid, warps);
-    default: return launch_turbo2<4, 1, ORDERED>(s, db, cp, ar, grid, warps);
+    case 1: return launch_turbo2<1, ORDERED>(s, db, cp, ar, grid, warps);
+    case 2: return launch_turbo2<2, ORDERED>(s, db, cp, ar, grid, warps);
+    case 3: return launch_turbo2<3, ORDERED>(s, db, cp, ar, grid, warps);
+    default: return launch_turbo2<4, ORDERED>(s, db, cp, ar, grid, warps);
     }
+}
+
+// which literal front end serves this database: 0 option = by the tables' own estimate (turbo_tables.h `wide`)
+inline bool use_turbo2(const hs_gpu_scratch *s, const DevDb &db) {
+    if (s->opt_frontend == 2) return false;
+    if (s->opt_frontend == 3) return true;
+    return !db.gwide;
 }
 
 template <class FE, bool NOODLE>
@@ -1434,7 +1441,7 @@ hs_error_t launch_mcclellan(hs_gpu_scratch *s, const DbImage *im, const DevCorpu
 // them; no sort.  Returns HS_INSUFFICIENT_SPACE when the general path must be used instead.
 hs_error_t scan_device_ordered(hs_gpu_scratch *s, DbImage *im, const DevCorpus &cp) {
     hs_gpu_stats_t &st = s->stats;
-    const bool v2 = s->opt_frontend != 2;
+    const bool v2 = use_turbo2(s, im->dev);
     const u32 cta_warps = v2 ? turbo2_warps<true>(s, im->dev) : (u32)turbo_warps<true>();
     if (!cta_warps) return HS_INSUFFICIENT_SPACE;
     const u32 grid = turbo_grid(s, cp, cta_warps), W = grid * cta_warps;
@@ -1528,7 +1535,7 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
         hs_error_t rv;
         CU_OK(cudaEventRecord(s->ev[6], s->stream));
         const bool use_turbo = im->dev.tK && s->opt_frontend != 1;
-        const u32 t2w = use_turbo && s->opt_frontend != 2 ? turbo2_warps<false>(s, im->dev) : 0;
+        const u32 t2w = use_turbo && use_turbo2(s, im->dev) ? turbo2_warps<false>(s, im->dev) : 0;
         if (t2w) {
             rv = launch_turbo2_any<false>(s, im->dev, cp, ar, turbo_grid(s, cp, t2w), t2w);
         } else if (use_turbo) {

@@ -4,20 +4,24 @@
 // What changed against k_turbo, and why (profiles/r01_ncu_k_turbo_*: 12.6 / 19.9 thread-instructions per byte, 55-58 %
 // of the shared-memory wavefronts were bank-conflict replays of random 8-byte reads):
 //   * first tier = ONE 4-byte shared-memory read per two text bytes (a random LDS.32 costs ~3.5 wavefronts per warp, a
-//     random LDS.64 ~6.4): stride 1 tests two end positions against the union set of their shared row; stride 2 (literal
-//     sets without many shortest-possible literals) looks at every other position only;
+//     random LDS.64 ~6.4): two end positions are tested against the union set of their shared row.  Sets whose union
+//     form would pass too many positions stay with k_turbo's 8-byte rows (turbo_tables.h, `wide`).  A form that looks at
+//     every other position only was measured and dropped: it saves two shifts per lookup and triples the second tier's
+//     work;
 //   * the row hash is a multiply of the unmasked text window (turbo_tables.h), the shift-amount registers are the
 //     windows themselves (a funnel shift looks at 5 bits): ~8 instructions per lookup, no PRMT packing, no masks;
 //   * nothing after the first tier runs lane-local any more.  Survivors are compacted, in position order, into a
-//     per-warp ring of bare positions; whenever the ring holds 32, ONE full-warp pass (a lane per candidate) fetches the
-//     8-byte window from global memory (L2: the step just came through it), applies the tail table and queues what
+//     per-warp queue of bare positions; whenever it holds 32, ONE full-warp pass (a lane per candidate) fetches the
+//     K + 1 bytes ending there from global memory (L2: the step just came through it), applies the tail table and queues what
 //     is left for the slot-table confirm, again 32 at a time.  Rare work therefore costs instructions in proportion to
 //     the candidates, not one divergent trip per step;
 //   * the text registers are loaded at the top of a step and the step's buffer is handed back to the bulk-copy engine at
 //     once (the later tiers do not read it), so every warp keeps almost two steps of HBM latency covered.
 #pragma once
 
-constexpr int T2Q1 = 128;                  // ring of first-tier survivors (positions), power of two
+constexpr int T2Q1 = 128;                  // first-tier survivors (positions) waiting for the second tier
+constexpr int T2LANE = 2 * TCHUNK;         // every lane owns 32 consecutive bytes of a step
+constexpr int T2MAXW = 24;                 // warps per CTA at most (768 threads: 85 registers each)
 constexpr int T2E = 1 + TCHUNK / 4;        // extended chunk words: the 4 bytes before the chunk, then the chunk
 
 template <bool ORDERED>
@@ -30,7 +34,6 @@ struct Turbo2WarpShared {
     u32 stage_n;
     u32 pad[3];
 };
-template <bool ORDERED> __host__ __device__ constexpr int turbo2_max_warps() { return 32; }
 
 template <bool ORDERED>
 __host__ __device__ inline size_t turbo2_smem_bytes(const DevDb &db, int warps) {
@@ -46,7 +49,7 @@ __device__ __forceinline__ u32 t2_win(const u32 (&E)[T2E]) {
     return __funnelshift_r(E[w], w + 1 < T2E ? E[w + 1] : 0u, 8 * (e & 3));
 }
 
-// stride 1: pairs of end positions (i-1, i), i = 1, 3, ..., 15; the candidate mask is built first-position-on-top
+// pairs of end positions (i-1, i), i = 1, 3, ..., 15; the candidate mask is built first-position-on-top
 template <int K, int i>
 struct Turbo2Pairs {
     static __device__ __forceinline__ void run(const u32 *tab, u32 mul, u32 rshift, const u32 (&E)[T2E], u32 &acc) {
@@ -65,31 +68,18 @@ struct Turbo2Pairs<K, TCHUNK + 1> {
     static __device__ __forceinline__ void run(const u32 *, u32, u32, const u32 (&)[T2E], u32 &) {}
 };
 
-// stride 2: grams ending at the odd chunk positions i = 1, 3, ..., 15; one flag per sample, first sample on top
-template <int K, int i>
-struct Turbo2Samples {
-    static __device__ __forceinline__ void run(const u32 *tab, u32 mul, u32 rshift, const u32 (&E)[T2E], u32 &acc) {
-        const u32 ent = tab[(t2_win<i - K + 1>(E) * mul) >> rshift];
-        const u32 r = __funnelshift_l(0u, ent, t2_win<i>(E));
-        acc = __funnelshift_l(r, acc, 1);
-        Turbo2Samples<K, i + 2>::run(tab, mul, rshift, E, acc);
-    }
-};
-template <int K> struct Turbo2Samples<K, TCHUNK + 1> { static __device__ __forceinline__ void run(const u32 *, u32, u32, const u32 (&)[T2E], u32 &) {} };
-
-// first tier of one chunk.  S == 1: 16 flags, bit 15 - j = end position j.  S == 2: 8 flags, bit 7 - k = sample k
-// (chunk position 2k + 1).
-template <int K, int S>
+// first tier of one chunk: 16 flags, bit 15 - j = end position j
+template <int K>
 __device__ __forceinline__ u32 turbo2_chunk(const u32 *tab, u32 mul, u32 rshift, const u32 (&E)[T2E]) {
     u32 acc = 0;
-    if (S == 1) Turbo2Pairs<K, 1>::run(tab, mul, rshift, E, acc);
-    else Turbo2Samples<K, 1>::run(tab, mul, rshift, E, acc);
+    Turbo2Pairs<K, 1>::run(tab, mul, rshift, E, acc);
     return acc;
 }
 
-// Second tier + hand-over to the confirm queue for up to 32 ring entries (a lane each), warp-synchronous.
-// Ring entry = end position relative to qbase (= span start - THALO, so that it is never negative).  Survivors go to q2
-// in position order as {position, K-byte tail}; q2 is confirmed 32 at a time.
+// Second tier + hand-over to the confirm queue for up to 32 entries q1[head ...) (a lane each), warp-synchronous.
+// Queue entry = end position relative to qbase (= span start - THALO, so that it is never negative).  Survivors go to q2
+// in position order as {position, K-byte tail}; q2 is confirmed 32 at a time.  (Issuing a batch's window loads one batch
+// ahead of their use was measured: the extra live registers cost more than the L2 round trip they hid.)
 template <int K, bool ORDERED>
 __device__ __forceinline__ void turbo2_tier2(const Ctx &c, const u32 *tail_tab, const u32 *q1, u32 head, u32 count, uint2 *q2,
                                              u32 &q2n, u64 qbase, u32 &n_probe, Rec *seg, u32 &cursor) {
@@ -98,10 +88,16 @@ __device__ __forceinline__ void turbo2_tier2(const Ctx &c, const u32 *tail_tab, 
     bool keep = false;
     u32 pos = 0, ktail = 0;
     if (ln < count) {
-        pos = q1[(head + ln) & (T2Q1 - 1)];
-        const u64 w = load_tail8(c.cp.text, qbase + pos);
-        ktail = (u32)(w >> (64 - 8 * K));
-        keep = turbo_tail_hit(tail_tab, word_shift, has_long, ktail, (u32)(w >> (56 - 8 * K)));
+        pos = q1[head + ln];
+        // the K + 1 bytes ending at the position lie inside two aligned words (L2: the step just came through it)
+        const u8 *first = c.cp.text + (qbase + pos) - K;
+        const u32 o = (u32)(reinterpret_cast<uintptr_t>(first) & 3);
+        const u32 *wp = reinterpret_cast<const u32 *>(first - o);
+        const u32 w0 = __ldg(wp), w1 = __ldg(wp + 1);
+        const u32 extra = __funnelshift_r(w0, w1, 8 * o);   // low byte = the byte before the K-tail
+        if (K == 4) ktail = o == 3 ? w1 : __funnelshift_r(w0, w1, 8 * o + 8);
+        else ktail = (extra >> 8) & ((1u << (8 * K)) - 1);
+        keep = turbo_tail_hit(tail_tab, word_shift, has_long, ktail, extra);
     }
     const u32 b = __ballot_sync(0xffffffffu, keep);
     if (!b) return;
@@ -119,8 +115,8 @@ __device__ __forceinline__ void turbo2_tier2(const Ctx &c, const u32 *tail_tab, 
     }
 }
 
-template <int K, int S, bool ORDERED>
-__global__ void __launch_bounds__(1024, 1) k_turbo2(const DevDb db, const DevCorpus cp, const DevArena ar) {
+template <int K, bool ORDERED>
+__global__ void __launch_bounds__(T2MAXW * 32, 1) k_turbo2(const DevDb db, const DevCorpus cp, const DevArena ar) {
     using WS = Turbo2WarpShared<ORDERED>;
     extern __shared__ __align__(16) u8 smem[];
     u32 *tab = reinterpret_cast<u32 *>(smem);
@@ -174,104 +170,97 @@ __global__ void __launch_bounds__(1024, 1) k_turbo2(const DevDb db, const DevCor
     const u32 mul = db.gmul, rshift = 32 - db.gG1;
     u32 n_cand = 0, n_probe = 0;
     Rec *seg = ORDERED ? ar.recs + (size_t)w * ar.seg_cap : nullptr;
-    u32 cursor = 0, q1h = 0, q1n = 0, q2n = 0;
-    u32 s2_carry = 1;  // sampled form: "the sample just before this chunk hit"; unknown at the span's start, so assume it
+    u32 cursor = 0, q1n = 0, q2n = 0;
     const u32 lt = (1u << ln) - 1;
+    const u64 corpus_left = cp.total - span_base;   // text bytes from the span's start to the corpus end
 #pragma unroll 1
     for (u32 step = 0; step < nsteps; step++) {
         const u32 b = step % TNBUF;
         mbar_wait(&ws.mbar[b], (step / TNBUF) & 1);
+        // the lane's 32 consecutive bytes, and the 4 before them
         u32 m;
         {
-            const u8 *cb = ws.text[b] + THALO + ln * TCHUNK;
-            const uint4 c0 = *reinterpret_cast<const uint4 *>(cb), c1 = *reinterpret_cast<const uint4 *>(cb + TROW_BYTES);
-            const u32 p0 = *reinterpret_cast<const u32 *>(cb - 4), p1 = *reinterpret_cast<const u32 *>(cb + TROW_BYTES - 4);
+            const u8 *cb = ws.text[b] + THALO + ln * T2LANE;
+            const uint4 c0 = *reinterpret_cast<const uint4 *>(cb), c1 = *reinterpret_cast<const uint4 *>(cb + TCHUNK);
+            // the 4 bytes before the lane's: the previous lane's last word; lane 0 reads them from the halo
+            u32 p0 = __shfl_up_sync(0xffffffffu, c1.w, 1);
+            if (ln == 0) p0 = *reinterpret_cast<const u32 *>(cb - 4);
             __syncwarp();
             // the registers hold the step: its buffer can take the step TNBUF ahead already
             if (ln == 0 && step + TNBUF < nsteps)
                 bulk_load(ws.text[b], gsrc + (size_t)(step + TNBUF) * TSTEP_BYTES, TBUF_BYTES, &ws.mbar[b]);
             const u32 E0[T2E] = {p0, c0.x, c0.y, c0.z, c0.w};
-            m = turbo2_chunk<K, S>(tab, mul, rshift, E0);
-            const u32 E1[T2E] = {p1, c1.x, c1.y, c1.z, c1.w};
-            m = (m << 16) | turbo2_chunk<K, S>(tab, mul, rshift, E1);
+            m = turbo2_chunk<K>(tab, mul, rshift, E0);
+            const u32 E1[T2E] = {c0.w, c1.x, c1.y, c1.z, c1.w};
+            m = (m << 16) | turbo2_chunk<K>(tab, mul, rshift, E1);
         }
         const u32 step_pos = step * TSTEP_BYTES;
-        const bool last_step = span_base + step_pos + TSTEP_BYTES > cp.total;  // the corpus ends inside this step
-        const long long left0 = (long long)cp.total - (long long)(span_base + step_pos + ln * TCHUNK), left1 = left0 - TROW_BYTES;
-        if (S == 2) {
-            // m: bit 23 - k / bit 7 - k = sample k (chunk position 2k + 1) of row 0 / row 1.  A hit at p means "a
-            // literal may end at p - 1, p or p + 1": spread the 8 flags of each row over the odd positions, then let
-            // every flag also mark its two neighbours.  The flag that reaches over the chunk's end arrives at the next
-            // chunk (next lane, next row, next step) as `pin`.
-            if (last_step) {  // keep the samples up to and INCLUDING the position one past the corpus
-                const long long s0 = left0 < 1 ? 0 : (left0 + 1) / 2, s1 = left1 < 1 ? 0 : (left1 + 1) / 2;
-                const u32 k0 = s0 >= 8 ? 0xffu : (0xffu << (8 - (int)s0)) & 0xffu, k1 = s1 >= 8 ? 0xffu : (0xffu << (8 - (int)s1)) & 0xffu;
-                m &= (k0 << 16) | k1;
-            }
-            const u32 mu = __shfl_up_sync(0xffffffffu, m, 1), m31 = __shfl_sync(0xffffffffu, m, 31);
-            const u32 pin0 = ln ? (mu >> 16) & 1u : s2_carry, pin1 = ln ? mu & 1u : (m31 >> 16) & 1u;
-            s2_carry = m31 & 1u;
-            u32 x = m & 0x00ff00ffu;
-            x = (x | (x << 4)) & 0x0f0f0f0fu;
-            x = (x | (x << 2)) & 0x33333333u;
-            x = (x | (x << 1)) & 0x55555555u;   // sample k of row 0 at bit 30 - 2k, of row 1 at bit 14 - 2k
-            m = x | (x << 1) | ((x >> 1) & 0x7fff7fffu) | (pin0 << 31) | (pin1 << 15);
-        }
-        // m: bit 31 - j = position j of the lane's row-0 chunk, bit 15 - j = position j of its row-1 chunk
-        if (last_step) {  // clip end positions beyond the corpus
-            const u32 k0 = left0 >= 16 ? 0xffffu : left0 <= 0 ? 0u : (0xffffu << (16 - (int)left0)) & 0xffffu;
-            const u32 k1 = left1 >= 16 ? 0xffffu : left1 <= 0 ? 0u : (0xffffu << (16 - (int)left1)) & 0xffffu;
-            m &= (k0 << 16) | k1;
-        }
+        const bool last_step = (u64)step_pos + TSTEP_BYTES > corpus_left;  // the corpus ends inside this step
+        const long long left = (long long)corpus_left - (long long)(step_pos + ln * T2LANE);  // lane's bytes inside the corpus
+        // m: bit 31 - j = end position j of the lane's 32 bytes
+        if (last_step) m &= left >= 32 ? 0xffffffffu : left <= 0 ? 0u : 0xffffffffu << (32 - (int)left);
         if (!__any_sync(0xffffffffu, m != 0)) continue;
-        n_cand += __popc(m);
-        // ---- compaction into the ring, position order: row 0 lane-major, then row 1 ----
-        const u32 n0 = __popc(m >> 16), n1 = __popc(m & 0xffffu);
-        u32 slot0, slot1, total;
-        if (!__any_sync(0xffffffffu, (n0 | n1) > 1)) {
-            const u32 b0 = __ballot_sync(0xffffffffu, n0 != 0), b1 = __ballot_sync(0xffffffffu, n1 != 0);
-            slot0 = __popc(b0 & lt);
-            slot1 = __popc(b0) + __popc(b1 & lt);
-            total = __popc(b0) + __popc(b1);
+        // ---- compaction into q1, position order = lane order ----
+        const u32 n = __popc(m);
+        n_cand += n;
+        u32 excl, total;
+        if (!__any_sync(0xffffffffu, n >= 8)) {
+            // the usual case: three independent ballots (one per bit of n) instead of five dependent shuffles
+            const u32 b0 = __ballot_sync(0xffffffffu, n & 1u), b1 = __ballot_sync(0xffffffffu, n & 2u), b2 = __ballot_sync(0xffffffffu, n & 4u);
+            excl = __popc(b0 & lt) + 2 * __popc(b1 & lt) + 4 * __popc(b2 & lt);
+            total = __popc(b0) + 2 * __popc(b1) + 4 * __popc(b2);
         } else {
-            const u32 n01 = n0 | (n1 << 16);
-            u32 incl = n01;
+            u32 incl = n;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
                 const u32 t = __shfl_up_sync(0xffffffffu, incl, d);
                 if (ln >= (u32)d) incl += t;
             }
-            const u32 tot = __shfl_sync(0xffffffffu, incl, 31);
-            slot0 = (incl & 0xffffu) - n0;
-            slot1 = (tot & 0xffffu) + (incl >> 16) - n1;
-            total = (tot & 0xffffu) + (tot >> 16);
+            total = __shfl_sync(0xffffffffu, incl, 31);
+            excl = incl - n;
         }
-        u32 done = 0;  // survivors of this step already moved to the ring (warp-uniform)
-        while (done < total) {
-            const u32 room = T2Q1 - q1n, lim = done + room;  // this pass takes ranks [done, lim)
-            u32 mm = m, s0 = slot0, s1 = slot1;
+        const u32 pos_top = step_pos + ln * T2LANE + THALO + 31;  // queue position of the lane's byte j is pos_top - (31 - j)
+        if (q1n + total <= T2Q1) {
+            u32 *pf = q1 + q1n + excl;
+            u32 mm = m;
             while (mm) {
-                const u32 lz = __clz(mm);
-                mm &= ~(0x80000000u >> lz);
-                const bool second = lz >= 16;
-                const u32 rank = second ? s1++ : s0++;
-                if (rank >= done && rank < lim) {
-                    const u32 pos = ln * TCHUNK + (lz & 15) + (second ? TROW_BYTES : 0);
-                    q1[(q1h + q1n + rank - done) & (T2Q1 - 1)] = step_pos + pos + THALO;
-                }
+                const u32 f = 31 - __clz(mm);  // bit index of the first remaining position
+                *pf++ = pos_top - f;
+                mm &= ~(1u << f);
             }
-            const u32 took = total - done < room ? total - done : room;
-            q1n += took;
-            done += took;
+            q1n += total;
             __syncwarp();
-            while (q1n >= 32) {
-                turbo2_tier2<K, ORDERED>(c, bloom, q1, q1h, 32, q2, q2n, qbase, n_probe, seg, cursor);
-                q1h = (q1h + 32) & (T2Q1 - 1);
-                q1n -= 32;
+            u32 at = 0;
+            for (; at + 32 <= q1n; at += 32) turbo2_tier2<K, ORDERED>(c, bloom, q1, at, 32, q2, q2n, qbase, n_probe, seg, cursor);
+            if (at) {  // what is left (fewer than 32) moves to the front
+                const u32 rem = q1n - at, v = ln < rem ? q1[at + ln] : 0u;
+                __syncwarp();
+                if (ln < rem) q1[ln] = v;
+                q1n = rem;
+                __syncwarp();
+            }
+        } else {
+            // a step with more survivors than the queue holds (dense matches): empty the queue, then feed the step
+            // through it 96 ranks at a time
+            if (q1n) turbo2_tier2<K, ORDERED>(c, bloom, q1, 0, q1n, q2, q2n, qbase, n_probe, seg, cursor);
+            q1n = 0;
+            for (u32 lo = 0; lo < total; lo += 96) {
+                u32 mm = m, r = excl;
+                while (mm) {
+                    const u32 f = 31 - __clz(mm);
+                    if (r >= lo && r < lo + 96) q1[r - lo] = pos_top - f;
+                    r++;
+                    mm &= ~(1u << f);
+                }
+                __syncwarp();
+                const u32 have = total - lo < 96 ? total - lo : 96;
+                for (u32 at = 0; at < have; at += 32)
+                    turbo2_tier2<K, ORDERED>(c, bloom, q1, at, have - at < 32 ? have - at : 32, q2, q2n, qbase, n_probe, seg, cursor);
+                __syncwarp();
             }
         }
     }
-    if (q1n) turbo2_tier2<K, ORDERED>(c, bloom, q1, q1h, q1n, q2, q2n, qbase, n_probe, seg, cursor);
+    if (q1n) turbo2_tier2<K, ORDERED>(c, bloom, q1, 0, q1n, q2, q2n, qbase, n_probe, seg, cursor);
     if (q2n) turbo_drain<ORDERED>(c, q2, qbase, q2n, n_probe, seg, cursor);
     if (ORDERED) {
         if (ln == 0) ar.seg_count[w] = cursor;

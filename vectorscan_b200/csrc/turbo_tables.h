@@ -76,24 +76,19 @@ HSB_HD u32 tail_long_mask(u32 extra) { return 1u << (extra & 31); }
 // GRAM_MULT << 8*(5-K): the shift pushes the window bytes that are NOT among the K-1 hashed ones out of the product, so
 // the kernel needs no masking (one IMAD + one SHF per lookup), and the low 8*(K-1) bits of x * odd are a bijection of
 // the hashed bytes, so rows are used evenly.
-//   stride 1 ("pair" form): two neighbouring end positions e-1, e share the K-1 bytes S = text[e-K+1 .. e-1]; the row of
-//     S holds the union of  A = {low5(x) : x S is some literal's K-tail}  and  B = {low5(y) : S y is}; ONE 4-byte load
-//     filters both positions (position e-1 tests low5(text[e-K]), position e tests low5(text[e])).
-//   stride 2 ("sampled" form, every literal at least K bytes, few of exactly K): only grams ending at positions of one
-//     parity are looked up (row = hash of the gram's first K-1 bytes, bit = low5 of its last byte).  A literal of more
-//     than K bytes files its K-tail (it ends AT a sampled position) and the gram one byte further in (it ends one AFTER
-//     a sampled position); a literal of exactly K bytes files its K-tail and, for the other parity, the whole row of its
-//     last K-1 bytes (the sampled gram then ends one byte AFTER the literal: its last byte is not the literal's).  A hit
-//     at sampled position p therefore means "a literal may end at p-1, p or p+1"; the second tier decides which.
+//   Two neighbouring end positions e-1, e share the K-1 bytes S = text[e-K+1 .. e-1]; the row of S holds the union of
+//   A = {low5(x) : x S is some literal's K-tail}  and  B = {low5(y) : S y is}; ONE 4-byte load filters both positions
+//   (position e-1 tests low5(text[e-K]), position e tests low5(text[e])).
 constexpr u32 GRAM_MULT = 0x9E3779B1u;
 HSB_HD u32 gram_mul(u32 K) { return K >= 5 || K <= 1 ? (K <= 1 ? 0u : GRAM_MULT) : GRAM_MULT << (8 * (5 - K)); }
-HSB_HD u32 gram_row(u32 window, u32 mul, u32 G1) { return G1 ? (window * mul) >> (32 - G1) : 0u; }
+HSB_HD u32 gram_row(u32 window, u32 mul, u32 G1) { return (window * mul) >> (32 - G1); }  // G1 >= 10
 
 struct Tables {
     u32 K = 0, H1 = 0, H2 = 0;
     std::vector<u64> pair;   // low 32 bits = A, high 32 bits = B
     // k_turbo2
-    u32 S = 1, G1 = 0, gmul = 0, par = 1;
+    u32 G1 = 0, gmul = 0;
+    u32 wide = 0;            // 1: this set is better served by the pair table's 8-byte rows (k_turbo)
     std::vector<u32> gram;
     double est_tests_per_byte = 0;  // second-tier tests per text byte expected on uniformly random text
     std::vector<Slot> slots;
@@ -234,7 +229,6 @@ inline bool build(const DbView &d, Tables &t) {
         // rows: a few hundred cells per filed gram, at most 2^15 rows (128 KiB of shared memory)
         u32 G1 = 10;
         while (G1 < 15 && ((size_t)32 << G1) < vars.size() * 400) G1++;
-        if (K == 1) G1 = 0;
         t.G1 = G1;
         const double cells = 32.0 * (double)((size_t)1 << G1);
         auto window_of = [&](const u32 *b, u32 n) { u32 w = 0; for (u32 j = 0; j < n && j < 4; j++) w |= b[j] << (8 * j); return w; };
@@ -246,49 +240,28 @@ inline bool build(const DbView &d, Tables &t) {
             g1[gram_row(window_of(b + 1, K - 1), mul, G1)] |= 0x80000000u >> (b[0] & 31);      // A: shared = b[1..K-1]
             g1[gram_row(window_of(b, K - 1), mul, G1)] |= 0x80000000u >> (b[K - 1] & 31);      // B: shared = b[0..K-2]
         }
-        const double tests1 = 2.0 * (double)vars.size() / cells;
-        // stride 2
-        bool s2_ok = K >= 3;
-        std::vector<u32> g2;
-        double tests2 = 1e9;
-        if (s2_ok) {
-            g2.assign((size_t)1 << G1, 0);
-            double filed = 0;
-            std::vector<u64> keys;
-            for (const LitRec *l : live) {
-                if (!tail_variants(*l, K, 4096, keys)) { s2_ok = false; break; }
-                for (u64 k : keys) {  // ends at a sampled position: the K-tail
-                    u32 b[4]; for (u32 j = 0; j < 4; j++) b[j] = (u32)(k >> (8 * j)) & 0xff;
-                    g2[gram_row(window_of(b, K - 1), mul, G1)] |= 0x80000000u >> (b[K - 1] & 31);
-                }
-                filed += (double)keys.size();
-                if (l->size > K && tail_variants(*l, K + 1, 8192, keys)) {
-                    for (u64 k : keys) {  // ends one after a sampled position: the gram one byte further in
-                        u32 b[5]; for (u32 j = 0; j < 5; j++) b[j] = (u32)(k >> (8 * j)) & 0xff;
-                        g2[gram_row(window_of(b, K - 1), mul, G1)] |= 0x80000000u >> (b[K - 1] & 31);
-                    }
-                    filed += (double)keys.size();
-                } else {
-                    // exactly K bytes (or a longer tail that cannot be enumerated): the sampled gram that ends one
-                    // byte after the literal starts with its last K-1 bytes -- the whole row
-                    if (!tail_variants(*l, K - 1, 4096, keys)) { s2_ok = false; break; }
-                    for (u64 k : keys) {
-                        u32 b[4]; for (u32 j = 0; j < 4; j++) b[j] = (u32)(k >> (8 * j)) & 0xff;
-                        g2[gram_row(window_of(b, K - 1), mul, G1)] = 0xffffffffu;
-                    }
-                    filed += 32.0 * (double)keys.size();
-                }
-            }
-            if (s2_ok) tests2 = 3.0 * 0.5 * filed / cells;  // a hit asks the second tier about three positions
+        // Share of positions the union form lets through, estimated for text over the literals' own alphabet: the text's
+        // K-1 shared bytes reach at most alphabet^(K-1) rows however large the table is.
+        double tests1;
+        {
+            bool seen[256] = {false};
+            for (const Var &v : vars) for (u32 j = 0; j < K; j++) seen[(v.key >> (8 * j)) & 0xff] = true;
+            double alpha = 0, reach = 1, bits = 0, populated = 0;
+            for (bool b : seen) alpha += b ? 1 : 0;
+            for (u32 j = 1; j < K; j++) reach *= alpha;
+            for (u32 w : g1) { bits += __builtin_popcount(w); populated += w ? 1 : 0; }
+            reach = std::min(reach, cells / 32.0);
+            tests1 = bits / (32.0 * std::max(reach, populated));
         }
-        // sampled form when it keeps the second tier's work small (it halves the first tier's)
-        const char *force = getenv("HS_GPU_TURBO_STRIDE");
-        const int forced = force ? atoi(force) : 0;
-        const bool use2 = s2_ok && (forced == 2 || (forced != 1 && tests2 <= 0.025 && tests2 <= 4.0 * tests1 + 0.01));
-        t.S = use2 ? 2 : 1;
-        t.par = (use2 && K == 3) ? 0 : 1;
-        t.gram.swap(use2 ? g2 : g1);
-        t.est_tests_per_byte = use2 ? tests2 : tests1;
+        // When the union sets would pass more than a few percent of all positions (many literals behind a SHORT shared
+        // part: K = 3 hashes two bytes, so printable text reaches < 10^4 rows however large the table), the 8-byte rows
+        // of the pair table (separate A and B sets, k_turbo) halve the candidates the later tiers have to look at and
+        // win despite the costlier lookup (measured on C2: DESIGN.md section 4).
+        const char *force = getenv("HS_GPU_TURBO_WIDE");
+        const int forced = force ? atoi(force) : -1;
+        t.wide = (K >= 2 && K <= 3 && (forced == 1 || (forced != 0 && tests1 > 0.04))) ? 1 : 0;
+        t.gram.swap(g1);
+        t.est_tests_per_byte = tests1;
     }
     u32 H2 = 4;
     while (((size_t)1 << H2) < vars.size() * 4) H2++;
