@@ -44,13 +44,14 @@ def peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def ncu_traffic(config, nbytes, frontend):
-    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch, from the committed ncu
-    --set full capture of this very workload (profiles/ncu_traffic.json); None when no capture matches."""
+def ncu_traffic(config, nbytes, kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch, from the committed ncu --set full
+    capture of this workload (profiles/ncu_traffic.json, which names the kernel and the capture it came from); None when
+    no capture matches config, batch size AND kernel name -- a capture of another kernel says nothing about this one."""
     try:
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
             for e in json.load(f):
-                if e["config"] == config and e["bytes"] == nbytes and e["frontend"] == frontend:
+                if e["config"] == config and e["bytes"] == nbytes and e.get("kernel") == kernel:
                     return e["dram_bytes_per_launch"]
     except Exception:
         pass
@@ -241,6 +242,8 @@ def main():
     ap.add_argument("--ref-sample-bytes", type=int, default=0)
     ap.add_argument("--cpu-sample-bytes", type=int, default=0)
     ap.add_argument("--frontend", type=int, default=0)
+    ap.add_argument("--batches-per-step", type=int, default=0, help="batches queued back to back per step (0: about 1 GiB)")
+    ap.add_argument("--no-verify", action="store_true", help="skip the sharded-equals-single check")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     # bounded CPU samples (the NFA path is ~100x slower per byte on the CPU than the literal path)
@@ -282,89 +285,162 @@ def main():
         torch.cuda.synchronize()
 
     # ---- device-resident throughput ("value") -------------------------------------------------------
+    # A step = `per_step` batches queued back to back (hs_gpu_scan_corpora: one host round trip per step), so that a
+    # step is >= 1 ms of device work and a launch gap on one rank does not decide the max over ranks; consecutive
+    # members are different resident batches (ROT x bytes > L2).  Databases outside the sort-free path (regex engines)
+    # scan one batch per step.
+    per_step = args.batches_per_step or max(1, min(16, (1 << 30) // max(1, nbytes)))
+    try:
+        gpu.scan_corpora(db, [corpora[0], corpora[1 % ROT]], sc)
+        train_ok = True
+    except gpu.HsGpuError:
+        train_ok, per_step = False, 1
+
+    def step(k):
+        if train_ok:
+            members = [corpora[(k * per_step + j) % ROT] for j in range(per_step)]
+            n = gpu.scan_corpora(db, members, sc)
+            st = sc.stats()
+            return n, st, st["train_ms"], sum(c.total for c in members), sum(c.count for c in members)
+        c = corpora[k % ROT]
+        n = gpu.scan_corpus(db, c, sc)
+        st = sc.stats()
+        return n, st, st["scan_ms"] + st["sort_ms"], c.total, c.count
+
     for w in range(max(args.warmup, 3)):
-        gpu.scan_corpus(db, corpora[w % ROT], sc)
+        step(w)
     sampler = ClockSampler(local_rank)
     sampler.start()
     barrier()
     sampler.go()
     dev_ms = kern_ms = 0.0
-    nmatch = raw = launches = nbytes_scanned = cands = probes = 0
+    nmatch = raw = launches = nbytes_scanned = nbuffers = cands = probes = scans = 0
     t0 = time.perf_counter()
     for k in range(args.steps):
-        c = corpora[k % ROT]
-        nmatch += gpu.scan_corpus(db, c, sc)
-        st = sc.stats()
-        dev_ms += st["scan_ms"] + st["sort_ms"]
+        n, st, ms, nb, nbuf = step(k)
+        nmatch += n
+        dev_ms += ms
         kern_ms += st["kernel_ms"]
         raw += st["raw_matches"]
         cands += st["candidates"]
         probes += st["confirms"]
         launches += st["kernel_launches"]
-        nbytes_scanned += c.total
+        scans += st["scan_launches"]
+        nbytes_scanned += nb
+        nbuffers += nbuf
     barrier()
     wall_s = time.perf_counter() - t0
     clocks = sampler.stop()
 
-    # the only collective of the path: match counts (+ per-pattern histogram) over NCCL
+    # the only collective of the path: match counts (+ per-pattern histogram of the last step) over NCCL
     hist = torch.zeros(n_ids, dtype=torch.int64, device="cuda")
     gpu.lib().hs_gpu_histogram(sc.ptr, C.c_void_p(hist.data_ptr()), n_ids)
     tot_matches, tot_bytes, hist = shard.reduce_counts(nmatch, nbytes_scanned, hist, device="cuda")
+    rank_ms = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
     if world > 1:
-        mx = torch.tensor([dev_ms, wall_s], dtype=torch.float64, device="cuda")
+        allms = [torch.zeros_like(rank_ms) for _ in range(world)]
+        dist.all_gather(allms, rank_ms)
+        allms = sorted(float(x[0]) for x in allms)
+        mx = torch.tensor([wall_s], dtype=torch.float64, device="cuda")
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-        max_dev_ms, max_wall = float(mx[0]), float(mx[1])
+        max_wall = float(mx[0])
     else:
-        max_dev_ms, max_wall = dev_ms, wall_s
+        allms, max_wall = [dev_ms], wall_s
+    max_dev_ms = allms[-1]
     tot_bytes, tot_matches = float(tot_bytes), float(tot_matches)
     value = tot_bytes / (max_dev_ms * 1e-3) / 1e9
 
     # ---- end to end through the C ABI with host buffers -----------------------------------------------
+    # (a) the friendly shape: the batch back to back in page-locked memory (hs_gpu_host_alloc);
+    # (b) the pcapscan shape (examples/pcapscan.cc:305-316): every packet its own pageable allocation slot.
     L = gpu.lib()
     flat0, off0 = batches[0]
-    hp = L.hs_gpu_host_alloc(int(flat0.nbytes))
-    C.memmove(hp, flat0.ctypes.data, flat0.nbytes)
     count0 = len(off0) - 1
-    ptrs = (C.c_char_p * count0)()
-    base = hp
-    ptr_arr = (np.uint64(base) + off0[:-1]).astype(np.uint64)
-    C.memmove(ptrs, ptr_arr.ctypes.data, count0 * 8)
-    lens = (C.c_uint * count0)(*np.diff(off0).astype(np.uint32).tolist())
+    lens_np = np.diff(off0).astype(np.uint32)
+    lens = (C.c_uint * count0)(*lens_np.tolist())
     mp, cnt = C.POINTER(gpu.Match)(), C.c_uint64()
 
-    def e2e_once():
-        rv = L.hs_gpu_scan_vector_ex(db.ptr, ptrs, lens, count0, 0, sc.ptr, C.byref(mp), C.byref(cnt))
-        if rv != 0:
-            raise RuntimeError(f"hs_gpu_scan_vector_ex -> {rv}")
-        return cnt.value
+    def e2e_measure(ptrs, steps):
+        def once():
+            rv = L.hs_gpu_scan_vector_ex(db.ptr, ptrs, lens, count0, 0, sc.ptr, C.byref(mp), C.byref(cnt))
+            if rv != 0:
+                raise RuntimeError(f"hs_gpu_scan_vector_ex -> {rv}")
+            return cnt.value
+        for _ in range(3):
+            once()
+        barrier()
+        t0 = time.perf_counter()
+        matches = 0
+        brk = {"h2d_ms": 0.0, "scan_ms": 0.0, "sort_ms": 0.0, "d2h_ms": 0.0}
+        for _ in range(steps):
+            matches += once()
+            st = sc.stats()
+            for k in brk:
+                brk[k] += st[k]
+        barrier()
+        secs = time.perf_counter() - t0
+        brk = {k: round(v / steps, 4) for k, v in brk.items()}
+        brk["wall_ms"] = round(1e3 * secs / steps, 4)
+        t = torch.tensor([secs], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return world * steps * float(flat0.nbytes) / float(t[0]) / 1e9, matches, brk
 
-    for _ in range(3):
-        e2e_once()
-    barrier()
     e2e_steps = max(3, min(args.steps, 20))
-    t0 = time.perf_counter()
-    e2e_matches = 0
-    brk = {"h2d_ms": 0.0, "scan_ms": 0.0, "sort_ms": 0.0, "d2h_ms": 0.0}
-    for _ in range(e2e_steps):
-        e2e_matches += e2e_once()
-        st = sc.stats()
-        for k in brk:
-            brk[k] += st[k]
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    brk = {k: round(v / e2e_steps, 4) for k, v in brk.items()}
-    brk["wall_ms"] = round(1e3 * e2e_s / e2e_steps, 4)
-    e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
-    e2e_value = world * e2e_steps * float(flat0.nbytes) / float(e2e_t[0]) / 1e9
+    hp = L.hs_gpu_host_alloc(int(flat0.nbytes))
+    C.memmove(hp, flat0.ctypes.data, flat0.nbytes)
+    ptrs = (C.c_char_p * count0)()
+    ptr_arr = (np.uint64(hp) + off0[:-1]).astype(np.uint64)
+    C.memmove(ptrs, ptr_arr.ctypes.data, count0 * 8)
+    e2e_value, e2e_matches, brk = e2e_measure(ptrs, e2e_steps)
     d2h_per_step = int(e2e_matches / e2e_steps) * 16
     L.hs_gpu_host_free(hp)
+    # (b): packets at a stride of their length rounded up to 64 + 64 in ordinary (pageable) memory
+    slot = ((lens_np.astype(np.int64) + 63) // 64 + 1) * 64
+    starts = np.concatenate([[0], np.cumsum(slot)[:-1]]).astype(np.int64)
+    pageable = np.zeros(int(slot.sum()) + 64, dtype=np.uint8)
+    idx = np.repeat(starts - off0[:-1].astype(np.int64), lens_np) + np.arange(int(off0[-1]), dtype=np.int64)
+    pageable[idx] = flat0
+    ptrs2 = (C.c_char_p * count0)()
+    ptr_arr2 = (np.uint64(pageable.ctypes.data) + starts.astype(np.uint64)).astype(np.uint64)
+    C.memmove(ptrs2, ptr_arr2.ctypes.data, count0 * 8)
+    e2e2_value, e2e2_matches, brk2 = e2e_measure(ptrs2, max(3, e2e_steps // 2))
+    assert e2e2_matches // max(3, e2e_steps // 2) == e2e_matches // e2e_steps, "pageable and pinned inputs disagree"
+
+    # ---- N GPUs scanning a sharded corpus reproduce the 1-GPU match list and histogram -----------------
+    verify = None
+    if not args.no_verify:
+        vflat, voff = make_workload(args.config, 0, min(nbytes, 64 << 20), args.patterns)[2][0] if rank else batches[0]
+        if len(voff) - 1 >= world:
+            bounds = shard.shard_bounds(voff, world)
+            sflat, soff, first = shard.take_shard(vflat, voff, bounds, rank)
+            sbufs = [sflat[int(soff[i]):int(soff[i + 1])].tobytes() for i in range(len(soff) - 1)]
+            mine = gpu.scan_vector_ex(db, sbufs, sc)
+            myhist = torch.zeros(n_ids, dtype=torch.int64, device="cuda")
+            if len(mine):
+                myhist.index_add_(0, torch.as_tensor(mine["id"].astype(np.int64), device="cuda"),
+                                  torch.ones(len(mine), dtype=torch.int64, device="cuda"))
+            if world > 1:
+                dist.all_reduce(myhist, op=dist.ReduceOp.SUM)
+                gathered = [None] * world
+                dist.all_gather_object(gathered, [tuple(int(v) for v in m) for m in mine])
+            else:
+                gathered = [[tuple(int(v) for v in m) for m in mine]]
+            if rank == 0:
+                merged = shard.merge_shards(gathered, bounds)
+                vb = [vflat[int(voff[i]):int(voff[i + 1])].tobytes() for i in range(len(voff) - 1)]
+                single = gpu.scan_vector_ex(db, vb, sc)
+                single_l = [tuple(int(v) for v in m) for m in single]
+                shist = np.bincount(single["id"].astype(np.int64), minlength=n_ids)[:n_ids] if len(single) else np.zeros(n_ids, dtype=np.int64)
+                verify = {"sharded_equals_single": merged == single_l,
+                          "histogram_equals_single": bool((myhist.cpu().numpy() == shist).all()),
+                          "matches": len(single_l), "shards": world, "bytes": int(voff[-1])}
 
     if rank == 0:
         peak, peak_src = peaks()
-        n_launch = args.steps
-        alg_bytes = (nbytes_scanned + 16 * raw + 12 * sum(c.count for c in corpora) * (args.steps / ROT)) / n_launch
+        n_launch = max(1, scans)   # launches of the dominant kernel inside the timed region
+        kernel = gpu.KERNEL_NAMES.get(sc.stats()["front_end"], "?")
+        alg_bytes = (nbytes_scanned + 16 * raw + 12 * nbuffers) / n_launch
         achieved = alg_bytes / (kern_ms / n_launch * 1e-3) / 1e9
         line = {
             "metric": "scan throughput", "value": round(value, 2), "unit": "GB/s", "n_gpus": world, "steps": args.steps,
@@ -374,25 +450,32 @@ def main():
             "matches_per_step": int(tot_matches / args.steps / world),
             "wall_ms_per_step": round(1e3 * max_wall / args.steps, 4),
             "config": workload_config(name),
+            "step": (f"{per_step} batches of {nbytes >> 20} MiB queued back to back (hs_gpu_scan_corpora), CUDA events around the "
+                     f"whole train" if train_ok else f"one {nbytes >> 20} MiB batch (hs_gpu_scan_corpus)"),
+            "rank_ms_per_step": {"min": round(allms[0] / args.steps, 4), "median": round(allms[len(allms) // 2] / args.steps, 4),
+                                 "max": round(allms[-1] / args.steps, 4)},
             "diag": {"frontend": args.frontend, "candidates_per_kb": round(1024.0 * cands / max(1, nbytes_scanned), 3),
                      "confirm_probes_per_kb": round(1024.0 * probes / max(1, nbytes_scanned), 3), "hist_nonzero_ids": int((hist > 0).sum())},
             "clocks": clocks,
             "e2e": {"value": round(e2e_value, 3), "unit": "GB/s", "h2d_bytes_per_step": int(flat0.nbytes + off0.nbytes),
                     "d2h_bytes_per_step": d2h_per_step, "steps": e2e_steps,
-                    "call": "hs_gpu_scan_vector_ex(host pinned buffers)", "per_step_ms": brk},
+                    "call": "hs_gpu_scan_vector_ex(host pinned buffers)", "per_step_ms": brk,
+                    "pageable_scattered": {"value": round(e2e2_value, 3), "unit": "GB/s", "per_step_ms": brk2,
+                                           "shape": "every packet in its own slot of ordinary (pageable) memory, as pcapscan holds them"}},
+            "verify": verify,
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "k_limex" if args.config == "c3" else "k_mcclellan" if args.config == "c3d" else "k_scan" if args.frontend == 1 else "k_turbo" if args.frontend == 2 else "k_turbo2", "achieved": round(achieved, 2),
+            "roofline": {"bound": "hbm", "kernel": kernel, "achieved": round(achieved, 2),
                          "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-                         "traffic": ncu_traffic(args.config, nbytes, args.frontend), "peak_source": peak_src,
+                         "traffic": ncu_traffic(args.config, nbytes, kernel), "peak_source": peak_src, "launches": n_launch,
                          "alg_bytes_per_launch": int(alg_bytes), "kernel_ms": round(kern_ms / n_launch, 4)},
         }
         if not args.no_cpu_baseline:
             try:
                 ser = db.serialize()
                 threads = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
-                sample = min(args.cpu_sample_bytes, 8 << 20)
+                sample = args.cpu_sample_bytes  # same sizing as the --impl reference arm
                 g0, _, s0, nb1, isa = cpu_reference_run(ser, flat0, off0, threads, 1, sample)
-                reps = int(max(2, min(20, round(1.0 / max(s0, 1e-4)))))
+                reps = int(max(2, min(40, round(1.0 / max(s0, 1e-4)))))
                 gN, mN, sN, nbN, _ = cpu_reference_run(ser, flat0, off0, threads, reps, sample)
                 g1, m1, s1, _, _ = cpu_reference_run(ser, flat0, off0, 1, max(2, reps // 2), sample)
                 line["cpu_baseline"] = {"value": round(gN, 4), "unit": "GB/s", "cores": threads, "kind": "reference",

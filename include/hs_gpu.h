@@ -71,6 +71,8 @@ typedef struct hs_gpu_stats {
     uint32_t arena_retries; /* re-runs forced by match arena growth */
     float kernel_ms;        /* the (last) k_scan launch alone, CUDA events tight around it */
     uint32_t kernel_launches; /* kernels of this library launched by the call (CUB's are not counted) */
+    float train_ms;           /* ordered path: first kernel's start to last kernel's end, gaps between members included */
+    uint32_t front_end;       /* dominant kernel of the call: 1 k_scan, 2 k_turbo, 3 k_turbo2, 4 k_limex, 5 k_mcclellan, 6 several engines */
 } hs_gpu_stats_t;
 
 /* hs_alloc_scratch(db, &scratch)                       src/hs_runtime.h:555-556, src/scratch.c:244-389
@@ -114,6 +116,12 @@ hs_error_t hs_gpu_corpus_free(hs_gpu_corpus_t *corpus);
 /* Scan a resident corpus; matches stay on the device until fetched.  Only device work is done. */
 hs_error_t hs_gpu_scan_corpus(const hs_database_t *db, const hs_gpu_corpus_t *corpus, hs_gpu_scratch_t *scratch,
                               uint64_t *n_matches);
+/* Scan n resident corpora back to back as ONE logical batch (the hsbench loop over several in-memory blocks): the
+ * kernels of all members are queued on the scratch's stream before the host waits once; buffer indices of the matches
+ * continue from corpus to corpus.  Needs a database the sort-free path serves (plain-report literal sets; otherwise
+ * HS_ARCH_ERROR, scan the corpora one by one). */
+hs_error_t hs_gpu_scan_corpora(const hs_database_t *db, const hs_gpu_corpus_t *const *corpora, unsigned int n,
+                               hs_gpu_scratch_t *scratch, uint64_t *n_matches);
 hs_error_t hs_gpu_fetch_matches(hs_gpu_scratch_t *scratch, const hs_gpu_match_t **matches, uint64_t *n_matches);
 
 hs_error_t hs_gpu_last_stats(const hs_gpu_scratch_t *scratch, hs_gpu_stats_t *stats);

@@ -431,8 +431,13 @@ __global__ void __launch_bounds__(turbo_warps<ORDERED>() * 32, 1) k_turbo(const 
 // contiguous, position-ordered array (as Rec and as hs_gpu_match_t), one warp per segment.  ctl[4] = records
 // kept, ctl[5] = largest count any warp wanted (> seg_cap means the launch must be repeated with larger
 // segments).  Block 0 also clears `ctl_next`, the control block of the next scan.
+// A train of scans (several corpora, or the chunks of one host batch, scanned back to back) shares one output array:
+// `prev` is the control block of the member before this one (its word 6 = records written so far; nullptr for the
+// first), `buf_base` the number of buffers before this member; ctl[6] = records written including this member.  Writes
+// beyond `out_cap` are dropped and show as ctl[6] > out_cap (the host grows the array and repeats the train).
 __global__ void __launch_bounds__(256) k_compact(const Rec *recs, const u32 *seg_count, u32 seg_cap, u32 W, Rec *out_recs,
-                                                 hs_gpu_match_t *out, unsigned long long *ctl, unsigned long long *ctl_next) {
+                                                 hs_gpu_match_t *out, unsigned long long *ctl, unsigned long long *ctl_next,
+                                                 const unsigned long long *prev, u32 buf_base, u64 out_cap) {
     __shared__ u32 pre[8193];
     __shared__ u32 part[256];
     __shared__ u32 wsum[8], wmax[8];
@@ -466,9 +471,10 @@ __global__ void __launch_bounds__(256) k_compact(const Rec *recs, const u32 *seg
         m = wmax[k] > m ? wmax[k] : m;
     }
     part[t] = base + incl - sum;
+    const u64 out_base = prev ? prev[6] : 0ull;
     if (blockIdx.x == 0) {
-        if (t == 0) { ctl[4] = total; ctl[5] = m; }
-        if (t < 8) ctl_next[t] = 0;
+        if (t == 0) { ctl[4] = total; ctl[5] = m; ctl[6] = out_base + total; }
+        if (ctl_next && t < 8) ctl_next[t] = 0;
     }
     __syncthreads();
     u32 run = part[t];
@@ -479,9 +485,12 @@ __global__ void __launch_bounds__(256) k_compact(const Rec *recs, const u32 *seg
     }
     __syncthreads();
     for (u32 w = blockIdx.x * 8 + wid; w < W; w += gridDim.x * 8) {
-        const u32 cnt = seg_count[w], n = cnt < seg_cap ? cnt : seg_cap, at = pre[w];
+        const u32 cnt = seg_count[w], n = cnt < seg_cap ? cnt : seg_cap;
+        const u64 at = out_base + pre[w];
         for (u32 i = ln; i < n; i += 32) {
-            const Rec r = recs[(size_t)w * seg_cap + i];
+            if (at + i >= out_cap) break;
+            Rec r = recs[(size_t)w * seg_cap + i];
+            r.buf += buf_base;
             out_recs[at + i] = r;
             out[at + i] = hs_gpu_match_t{r.buf, r.id, (uint64_t)r.to};
         }

@@ -26,7 +26,7 @@ class Stats(C.Structure):
                 ("raw_matches", C.c_uint64), ("candidates", C.c_uint64), ("confirms", C.c_uint64),
                 ("h2d_ms", C.c_float), ("scan_ms", C.c_float), ("sort_ms", C.c_float), ("d2h_ms", C.c_float),
                 ("scan_launches", C.c_uint32), ("arena_retries", C.c_uint32), ("kernel_ms", C.c_float),
-                ("kernel_launches", C.c_uint32)]
+                ("kernel_launches", C.c_uint32), ("train_ms", C.c_float), ("front_end", C.c_uint32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -37,6 +37,8 @@ class HsGpuError(RuntimeError):
         super().__init__(f"{what} -> {code}")
         self.code = code
 
+
+KERNEL_NAMES = {1: "k_scan", 2: "k_turbo", 3: "k_turbo2", 4: "k_limex", 5: "k_mcclellan", 6: "k_mcclellan/k_limex (several engines)"}
 
 _lib = None
 
@@ -63,6 +65,7 @@ def lib():
         L.hs_gpu_corpus_create.argtypes = [vp, C.POINTER(C.c_uint64), C.c_uint, C.POINTER(vp)]
         L.hs_gpu_corpus_free.argtypes = [vp]
         L.hs_gpu_scan_corpus.argtypes = [vp, vp, vp, C.POINTER(C.c_uint64)]
+        L.hs_gpu_scan_corpora.argtypes = [vp, C.POINTER(vp), C.c_uint, vp, C.POINTER(C.c_uint64)]
         L.hs_gpu_fetch_matches.argtypes = [vp, C.POINTER(C.POINTER(Match)), C.POINTER(C.c_uint64)]
         L.hs_gpu_last_stats.argtypes = [vp, C.POINTER(Stats)]
         L.hs_gpu_histogram.argtypes = [vp, vp, C.c_uint32]
@@ -190,6 +193,17 @@ def scan_corpus(db, corpus, scratch):
     rv = lib().hs_gpu_scan_corpus(_dbptr(db), corpus.ptr, scratch.ptr, C.byref(n))
     if rv != HS_SUCCESS:
         raise HsGpuError(rv, "hs_gpu_scan_corpus")
+    return n.value
+
+
+def scan_corpora(db, corpora, scratch):
+    """hs_gpu_scan_corpora: the resident corpora scanned back to back as one logical batch (one host round trip);
+    buffer indices of the matches continue from corpus to corpus.  Returns the match count."""
+    arr = (C.c_void_p * len(corpora))(*[c.ptr for c in corpora])
+    n = C.c_uint64()
+    rv = lib().hs_gpu_scan_corpora(_dbptr(db), arr, len(corpora), scratch.ptr, C.byref(n))
+    if rv != HS_SUCCESS:
+        raise HsGpuError(rv, "hs_gpu_scan_corpora")
     return n.value
 
 
