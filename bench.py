@@ -243,6 +243,7 @@ def main():
     ap.add_argument("--cpu-sample-bytes", type=int, default=0)
     ap.add_argument("--frontend", type=int, default=0)
     ap.add_argument("--batches-per-step", type=int, default=0, help="batches queued back to back per step (0: about 1 GiB)")
+    ap.add_argument("--pipeline", type=int, default=-1, help="host path: 0 one copy then scan, 1 chunked for gathered input, 2 always chunked")
     ap.add_argument("--no-verify", action="store_true", help="skip the sharded-equals-single check")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -276,6 +277,8 @@ def main():
     sc = gpu.alloc_scratch(db)
     if args.frontend:
         sc.set_option("frontend", args.frontend)
+    if args.pipeline >= 0:
+        sc.set_option("pipeline", args.pipeline)
     corpora = [gpu.Corpus(flat, off) for flat, off in batches]
 
     def barrier():

@@ -246,19 +246,23 @@ def test_full_size_properties(ref, config):
         assert got == exp
 
 
-def test_host_staging_paths_agree(ref):
-    """hs_gpu_scan_vector_ex takes buffers (a) scattered in pageable memory (gathered block by block into the
+@pytest.mark.parametrize("pipeline", [0, 1, 2])
+def test_host_staging_paths_agree(ref, pipeline):
+    """Host staging: one copy then one scan (0), or chunks copied on a second stream with the scans of earlier chunks
+    running beside them (2; 1 = only for input that has to be gathered).  hs_gpu_scan_vector_ex takes buffers (a) scattered in pageable memory (gathered block by block into the
     scratch's pinned staging), (b) back to back in one page-locked region (copied straight from it), (c) a mix of
     both with empty buffers in between; more than one staging block (> 4096 buffers) in every case."""
     rng = random.Random(77)
     lits, flags, ids, _ = litgen.random_case(rng, None, 200, bytes(range(97, 107)), 8)
     db = litdb.compile_lit_multi(lits, flags, ids)
+    nrng = np.random.default_rng(77)
     bufs = []
-    for k in range(9000):
+    for k in range(30000):  # ~9.4 MB: above the 8 MiB floor of the chunked ("pipeline") staging
         n = rng.choice([0, 1, 9, 60, 300, 1500])
-        bufs.append(bytes(rng.choice(b"abcdefghij") for _ in range(n)))
+        bufs.append(nrng.integers(97, 107, size=n, dtype=np.uint8).tobytes())
     exp = ref_scan(ref, db, bufs)
     sc = gpu.alloc_scratch(db)
+    sc.set_option("pipeline", pipeline)
     as_list = lambda m: [(int(b), int(i), int(t)) for b, i, t in m]
     assert as_list(gpu.scan_vector_ex(db, bufs, sc)) == exp                         # (a)
     L = gpu.lib()

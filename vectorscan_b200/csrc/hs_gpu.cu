@@ -1092,7 +1092,7 @@ struct hs_gpu_scratch {
                              // tables (k_scan), 2: k_turbo, 3: k_turbo2
     long opt_grid = 0;
     long opt_warps = 0;      // k_turbo2: cap on warps per CTA (0 = as many as fit)
-    long opt_pipeline = 1;   // host batches: chunked H2D on the copy stream overlapped with the scans
+    long opt_pipeline = 0;   // host batches: 0 one copy then one scan (measured fastest), 1 chunk gathered input, 2 always chunk
     size_t smem_optin_max = 227 * 1024;
     u64 arena_hint = 1 << 16;
     u64 last_raw = ~0ull;  // record count of the previous scan (picks the finalize kernel size)
@@ -1324,7 +1324,9 @@ bool build_cell_first(const u64 *off, u32 count, u64 total, Vec &out, u32 &nstri
 u32 turbo_grid(const hs_gpu_scratch *s, const DevCorpus &cp, u32 warps_per_cta) {
     u32 grid = s->opt_grid > 0 ? (u32)s->opt_grid : (u32)s->sm_count;
     if (grid > 8192 / warps_per_cta) grid = 8192 / warps_per_cta;  // k_compact scans at most 8192 warp segments
-    const u32 need = (cp.nstrips + warps_per_cta - 1) / warps_per_cta;
+    // the kernels balance 1 KiB steps over all warps of the grid: shrink the grid only when a warp would see fewer than 4
+    const u64 steps = (cp.total + 1023) / 1024;
+    const u32 need = (u32)((steps + 4 * warps_per_cta - 1) / (4 * warps_per_cta));
     if (grid > need) grid = need ? need : 1;
     return grid;
 }
@@ -1765,6 +1767,24 @@ struct InUseGuard {
     ~InUseGuard() { if (ok) s->in_use.store(0); }
 };
 
+// Scattered buffers [first, last) -> one contiguous run at dst (buffer q lands at dst + off[q - base] - block_at).  A block
+// of several MiB made of packet-sized pieces is copied by a few threads: one core's memcpy of 1.5 KB pieces (~7 GB/s)
+// is far below what the PCIe copy behind it takes.
+void gather_block(u8 *dst, const char *const *data, const unsigned int *length, const u64 *off, unsigned base, unsigned first,
+                  unsigned last, u64 block_at) {
+    auto part = [&](unsigned a, unsigned b) {
+        for (unsigned q = a; q < b; q++)
+            if (length[q]) std::memcpy(dst + (off[q - base] - block_at), data[q], length[q]);
+    };
+    const unsigned n = last - first;
+    unsigned threads = std::min<unsigned>(8, std::max<unsigned>(1, std::thread::hardware_concurrency() / 2));
+    if (n < 512 || threads < 2) { part(first, last); return; }
+    std::vector<std::thread> pool;
+    for (unsigned t = 1; t < threads; t++) pool.emplace_back(part, first + (u64)n * t / threads, first + (u64)n * (t + 1) / threads);
+    part(first, first + n / threads);
+    for (std::thread &t : pool) t.join();
+}
+
 // Host buffers -> the staging corpus in HBM.  The buffer list is walked in blocks (<= 4096 buffers or about
 // 8 MiB): a block whose buffers sit back to back in page-locked memory (hs_gpu_host_alloc) is copied straight
 // from the caller's memory, any other block is gathered into the scratch's pinned staging area first; either
@@ -1824,8 +1844,8 @@ hs_error_t stage_host_buffers(hs_gpu_scratch *s, const char *const *data, const 
                     CU_OK(cudaHostAlloc((void **)&s->h_stage, want, cudaHostAllocDefault));
                     s->h_stage_cap = want;
                 }
-                for (unsigned k = first; k < i; k++)
-                    if (length[k]) std::memcpy(s->h_stage + s->h_off[k], data[k], length[k]);
+                s->h_off[i] = pos;
+                gather_block(s->h_stage + block_at, data, length, s->h_off.data(), 0, first, i, block_at);
                 src = s->h_stage + block_at;
             }
             CU_OK(cudaMemcpyAsync(cp.text.p + FRONT_PAD + block_at, src, bytes, cudaMemcpyHostToDevice, s->stream));
@@ -1840,24 +1860,6 @@ hs_error_t stage_host_buffers(hs_gpu_scratch *s, const char *const *data, const 
     CU_OK(cudaMemcpyAsync(cp.cell_first.p, s->h_cell_first.data(), s->h_cell_first.size() * 4,
                           cudaMemcpyHostToDevice, s->stream));
     return HS_SUCCESS;
-}
-
-// Scattered buffers [first, last) -> one contiguous run at dst (buffer q lands at dst + off[q - base] - block_at).  A block
-// of several MiB made of packet-sized pieces is copied by a few threads: one core's memcpy of 1.5 KB pieces (~7 GB/s)
-// is far below what the PCIe copy behind it takes.
-void gather_block(u8 *dst, const char *const *data, const unsigned int *length, const u64 *off, unsigned base, unsigned first,
-                  unsigned last, u64 block_at) {
-    auto part = [&](unsigned a, unsigned b) {
-        for (unsigned q = a; q < b; q++)
-            if (length[q]) std::memcpy(dst + (off[q - base] - block_at), data[q], length[q]);
-    };
-    const unsigned n = last - first;
-    unsigned threads = std::min<unsigned>(8, std::max<unsigned>(1, std::thread::hardware_concurrency() / 2));
-    if (n < 512 || threads < 2) { part(first, last); return; }
-    std::vector<std::thread> pool;
-    for (unsigned t = 1; t < threads; t++) pool.emplace_back(part, first + (u64)n * t / threads, first + (u64)n * (t + 1) / threads);
-    part(first, first + n / threads);
-    for (std::thread &t : pool) t.join();
 }
 
 // Pipelined form of the staging for databases the sort-free path serves: the batch is cut at buffer boundaries into a
@@ -1920,52 +1922,36 @@ hs_error_t stage_host_chunks(hs_gpu_scratch *s, const char *const *data, const u
     constexpr u64 BLOCK_BYTES = 8u << 20;
     u64 host_pos = 0;  // running position in the pinned staging area (gathered blocks only)
     mem.clear();
-    // Pass 1 -- everything that depends on the lengths alone, for all chunks, as a handful of operations at the head of
-    // the copy stream: the zero gaps (front pad, between chunks, back pad), the offsets and the position -> buffer tables.
+    // The zero gaps first (front pad, between chunks, back pad): they depend on the chunk bounds alone.  Then the text,
+    // block by block as the host walks the buffers, so the bus is busy from the first few microseconds on; a chunk's
+    // offsets and position -> buffer table follow its text, and the chunk is ready when they have landed.
+    for (unsigned k = 0; k <= nch; k++) {
+        const u64 gap_from = k ? ch[k - 1].text_at + ch[k - 1].bytes : 0;
+        const u64 gap_to = k < nch ? ch[k].text_at : gap_from + BACK_PAD;
+        CU_OK(cudaMemsetAsync(cp.text.p + gap_from, 0, gap_to - gap_from, s->copy_stream));
+    }
     for (unsigned k = 0; k < nch; k++) {
         Chunk &c = ch[k];
         u64 *off = s->h_off.data() + c.off_at;
         u64 pos = 0;
-        for (unsigned i = c.first; i < c.last; i++) {
-            if (length[i] && !data[i]) return HS_INVALID;
-            off[i - c.first] = pos;
-            pos += length[i];
-        }
-        off[c.last - c.first] = pos;
-        const u32 ncells = (u32)((c.bytes + CELL_BYTES - 1) / CELL_BYTES);
-        u32 *cf = s->h_cell_first.data() + c.cell_at;
-        const u32 cnt = c.last - c.first;
-        u32 b = 0;
-        for (u32 q = 0; q <= ncells; q++) {
-            const u64 p = std::min<u64>((u64)q * CELL_BYTES, c.bytes ? c.bytes - 1 : 0);
-            while (b + 1 < cnt && off[b + 1] <= p) b++;
-            cf[q] = b;
-        }
-        c.nstrips = (u32)((c.bytes + STRIP_BYTES - 1) / STRIP_BYTES);
-        const u64 gap_from = k ? ch[k - 1].text_at + ch[k - 1].bytes : 0;
-        CU_OK(cudaMemsetAsync(cp.text.p + gap_from, 0, c.text_at - gap_from, s->copy_stream));
-    }
-    CU_OK(cudaMemsetAsync(cp.text.p + ch[nch - 1].text_at + ch[nch - 1].bytes, 0, BACK_PAD, s->copy_stream));
-    CU_OK(cudaMemcpyAsync(cp.off.p, s->h_off.data(), off_n * 8, cudaMemcpyHostToDevice, s->copy_stream));
-    CU_OK(cudaMemcpyAsync(cp.cell_first.p, s->h_cell_first.data(), cell_n * 4, cudaMemcpyHostToDevice, s->copy_stream));
-    // Pass 2 -- the text, block by block; a chunk is ready when its last block has landed.
-    for (unsigned k = 0; k < nch; k++) {
-        const Chunk &c = ch[k];
-        const u64 *off = s->h_off.data() + c.off_at;
         for (unsigned first = c.first; first < c.last;) {
-            const u64 block_at = off[first - c.first];
+            const u64 block_at = pos;
             const char *run = nullptr, *run_begin = nullptr;
             bool contiguous = true;
             unsigned i = first;
-            for (; i < c.last && i - first < BLOCK_BUFS && off[i - c.first] - block_at < BLOCK_BYTES; i++) {
+            for (; i < c.last && i - first < BLOCK_BUFS && pos - block_at < BLOCK_BYTES; i++) {
                 const unsigned len = length[i];
+                off[i - c.first] = pos;
                 if (len) {
                     const char *p = data[i];
+                    if (!p) return HS_INVALID;
                     if (!run_begin) run_begin = p; else if (p != run) contiguous = false;
                     run = p + len;
+                    pos += len;
                 }
             }
-            const u64 bytes = off[i - c.first] - block_at;
+            off[i - c.first] = pos;  // gather_block reads one offset past its last buffer's
+            const u64 bytes = pos - block_at;
             if (bytes) {
                 const u8 *src = nullptr;
                 if (contiguous) {
@@ -1993,10 +1979,23 @@ hs_error_t stage_host_chunks(hs_gpu_scratch *s, const char *const *data, const u
             }
             first = i;
         }
+        off[c.last - c.first] = pos;
+        const u32 ncells = (u32)((c.bytes + CELL_BYTES - 1) / CELL_BYTES);
+        u32 *cf = s->h_cell_first.data() + c.cell_at;
+        const u32 cnt = c.last - c.first;
+        u32 b = 0;
+        for (u32 q = 0; q <= ncells; q++) {
+            const u64 p = std::min<u64>((u64)q * CELL_BYTES, c.bytes ? c.bytes - 1 : 0);
+            while (b + 1 < cnt && off[b + 1] <= p) b++;
+            cf[q] = b;
+        }
+        c.nstrips = (u32)((c.bytes + STRIP_BYTES - 1) / STRIP_BYTES);
+        CU_OK(cudaMemcpyAsync(cp.off.p + c.off_at, off, ((size_t)cnt + 1) * 8, cudaMemcpyHostToDevice, s->copy_stream));
+        CU_OK(cudaMemcpyAsync(cp.cell_first.p + c.cell_at, cf, ((size_t)ncells + 1) * 4, cudaMemcpyHostToDevice, s->copy_stream));
         CU_OK(cudaEventRecord(s->chunk_ready[k], s->copy_stream));
         if (c.bytes)
             mem.push_back(TrainMember{DevCorpus{cp.text.p + c.text_at, cp.off.p + c.off_at, cp.cell_first.p + c.cell_at, c.bytes,
-                                                c.last - c.first, c.nstrips},
+                                                cnt, c.nstrips},
                                       c.first, s->chunk_ready[k]});
     }
     CU_OK(cudaEventRecord(s->ev[6], s->copy_stream));  // end of the H2D work (h2d_ms = ev0 -> ev6)
@@ -2025,10 +2024,12 @@ hs_error_t scan_host_batch(const hs_database_t *db, const char *const *data, con
             if (i && length[i] && data[i] != data[i - 1] + length[i - 1]) one_run = false;
             total += length[i];
         }
-        // Measured (C2, 64 MiB): a batch that is one run of pinned memory goes over the bus at 52 GB/s as a plain copy
-        // and at 46 GB/s with chunk scans running beside it, which costs more than the hidden scans save; a batch
-        // that has to be gathered is bounded by the host's copying, and there the overlap is free.  1 = chunk only
-        // gathered input, 2 = always.
+        // Off by default.  Measured on C2 (64 MiB of packets, B200, PCIe 5): plain = one copy then one scan, wall 1.49 ms
+        // (h2d 1.29); chunked (1/2, 1/4, 1/8, 1/8) wall 1.60 ms (h2d 1.36).  The scan + compact being hidden is 0.08 ms
+        // of a 1.29 ms copy, kernels running beside the DMA take 2-3x longer and slow the DMA by 5 %, and the tail
+        // (last chunk + control read-back + match copy) stays ~0.1 ms either way.  Gathered (pageable, scattered)
+        // input: 14.8 GB/s plain, 13.4 GB/s chunked -- the host's gather is the bound.  "pipeline" = 1 chunks gathered
+        // input only, 2 always.
         bool chunked = total >= (8u << 20);
         if (chunked && s->opt_pipeline == 1 && one_run) {
             cudaPointerAttributes pa{};
@@ -2052,6 +2053,15 @@ hs_error_t scan_host_batch(const hs_database_t *db, const char *const *data, con
                 if (cudaEventElapsedTime(&st.h2d_ms, s->ev[0], s->ev[6]) != cudaSuccess) { st.h2d_ms = 0; cudaGetLastError(); }
                 const auto t2 = now();
                 rv = fetch_matches(s, im);
+                if (trace)
+                    for (size_t k = 0; k < mem.size(); k++) {
+                        float a = 0, b = 0, c = 0;
+                        cudaEventElapsedTime(&a, s->ev[0], s->tev[3 * k]);
+                        cudaEventElapsedTime(&b, s->tev[3 * k], s->tev[3 * k + 1]);
+                        cudaEventElapsedTime(&c, s->tev[3 * k + 1], s->tev[3 * k + 2]);
+                        fprintf(stderr, "hs_gpu trace: chunk %zu: %llu bytes, scan starts at %.3f ms, scan %.3f ms, compact %.3f ms\n", k,
+                                (unsigned long long)mem[k].cp.total, a, b, c);
+                    }
                 if (trace)
                     fprintf(stderr, "hs_gpu trace: stage (%zu chunks) %.1f us, scans (incl. wait for H2D) %.1f us, fetch %.1f us\n",
                             mem.size(), us(t0, t1), us(t1, t2), us(t2, now()));
