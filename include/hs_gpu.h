@@ -137,6 +137,13 @@ void hs_gpu_host_free(void *p);
 /* Runtime knobs.  front end: 0 = auto, 1 = "native" (the database's own FDR/Teddy tables and FDRConfirm
  * structures), 2 = "turbo" (tables re-encoded at upload for shared memory; identical results). */
 hs_error_t hs_gpu_set_option(hs_gpu_scratch_t *scratch, const char *name, long value);
+/* Test instrumentation: after hs_gpu_set_option(scratch, "count_ops", 1) the device interpreter of Rose programs
+ * (roseRunProgram_l, src/rose/program_runtime.c:3083-3504) counts every instruction it executes by opcode
+ * (enum RoseInstructionCode, src/rose/rose_program.h:48-212); this copies the first n (<= 128) counters out. */
+/* Host-only (no device needed): how often each Rose opcode occurs in the programs the database's literal matcher /
+ * engine can start -- the census hs_gpu_alloc_scratch runs, as a histogram. */
+hs_error_t hs_gpu_database_opcodes(const hs_database_t *db, unsigned long long *hist, unsigned int n);
+hs_error_t hs_gpu_opcode_counts(hs_gpu_scratch_t *scratch, unsigned long long *counts, unsigned int n);
 int hs_gpu_device_count(void);
 hs_error_t hs_gpu_set_device(int device);
 const char *hs_gpu_version(void);

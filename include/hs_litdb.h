@@ -55,6 +55,45 @@ typedef struct hsb_lit_options {
 int hsb_compile_lit_multi(const char *const *expressions, const unsigned *flags, const unsigned *ids,
                           const size_t *lens, unsigned elements, unsigned mode,
                           const hsb_lit_options *options, hs_database_t **db, char **error);
+/* ---- extended literal form: what the reference compiler attaches to a literal beyond its text -------------------
+ * Per-literal extras (all optional; a zeroed record = a plain literal):
+ *  - `look`: byte constraints at negative offsets from the literal's END (offset -1 = its last byte), the
+ *    "lookaround" the reference derives for mixed-case / masked literals (makeCheckLitMaskInstruction,
+ *    src/rose/rose_build_program.cpp:1526-1558).  An entry is either and/cmp form -- ((byte & and_mask) == cmp_mask)
+ *    != negate -- or a 256-bit class (cls != NULL: byte is in the class).  The writer picks the instruction the way
+ *    makeLookaroundInstruction does (:1343-1523): CHECK_BYTE (one and/cmp entry), CHECK_MASK (span <= 8),
+ *    CHECK_MASK_32 (<= 32), CHECK_MASK_64 (<= 64, AVX512 targets), and for classes CHECK_SHUFTI_16x8 / 32x8 / 16x16 /
+ *    32x16 / 64x8 / 64x16.  An entry that lies before the start of the buffer fails the literal (program_runtime.c:604,651).
+ *  - `group`: the literal's Rose group (0..62).  HSB_EXT_CHECK_GROUPS puts a CHECK_GROUPS at the head of its program,
+ *    HSB_EXT_SQUASH_GROUP a SQUASH_GROUPS behind its report (only honoured where it is result-neutral: a SINGLEMATCH
+ *    literal alone in its group, rose_build_groups.cpp isGroupSquasher), HSB_EXT_QUIET makes the report quiet
+ *    (HS_FLAG_QUIET: no callback; with SINGLEMATCH a SET_EXHAUST, makeReport rose_build_program.cpp:533-640). */
+typedef struct hsb_lit_look {
+    int offset;                   /* -64 .. -1 */
+    unsigned char and_mask, cmp_mask, negate, reserved;
+    const unsigned char *cls;     /* 32-byte bitmap (bit c of byte c/8), or NULL for the and/cmp form */
+} hsb_lit_look;
+#define HSB_EXT_CHECK_GROUPS 1u
+#define HSB_EXT_SQUASH_GROUP 2u
+#define HSB_EXT_QUIET 4u
+typedef struct hsb_lit_ext {
+    const hsb_lit_look *look;
+    unsigned look_count;
+    unsigned group;
+    unsigned flags; /* HSB_EXT_* */
+} hsb_lit_ext;
+/* database-level extras */
+typedef struct hsb_lit_build_ext {
+    int included_jump;                 /* FDR: INCLUDED_JUMP + bucket squash for suffix-included fragments
+                                          (src/fdr/fdr_compile.cpp:654-812, rose_build_bytecode.cpp:2877-2950) */
+    int target_avx512;                 /* allow the 64-byte instructions (only an AVX512 runtime build executes them) */
+    unsigned long long groups_off;     /* group bits left out of RoseEngine.initialGroups */
+    unsigned max_bi_anchored_width;    /* RoseEngine.maxBiAnchoredWidth; 0 = ROSE_BOUND_INF */
+} hsb_lit_build_ext;
+int hsb_compile_lit_multi_ext(const char *const *expressions, const unsigned *flags, const unsigned *ids,
+                              const size_t *lens, const hsb_lit_ext *ext, unsigned elements, unsigned mode,
+                              const hsb_lit_options *options, const hsb_lit_build_ext *build_ext,
+                              hs_database_t **db, char **error);
 /* Stand-in for hs_compile_multi() (/root/reference/src/hs_compile.h:450-456) for SMALL pattern sets in a
  * restricted dialect (vectorscan_b200/csrc/nfadb_writer.cpp): the whole set becomes ONE LimEx NFA inside a
  * single-outfix block-mode database -- the shape the reference compiler gives a pattern set that has no

@@ -41,7 +41,7 @@ enum {
     N_ID = 0, N_MSK = 8, N_CMP = 16, N_MSK_LEN = 24
 };
 enum { /* Rose opcodes, rose/rose_program.h:44-216 */
-    OP_END = 0, OP_CHECK_GROUPS = 3, OP_CHECK_MASK = 9, OP_CHECK_BYTE = 11, OP_CATCH_UP = 20, OP_DEDUPE = 28,
+    OP_END = 0, OP_CHECK_GROUPS = 3, OP_CHECK_MASK = 9, OP_CHECK_MASK_32 = 10, OP_CHECK_MASK_64 = 69, OP_CHECK_BYTE = 11, OP_CATCH_UP = 20, OP_DEDUPE = 28,
     OP_REPORT = 33, OP_REPORT_EXHAUST = 34, OP_DEDUPE_AND_REPORT = 37, OP_FINAL_REPORT = 38, OP_CHECK_EXHAUSTED = 39,
     OP_SQUASH_GROUPS = 43, OP_CHECK_LONG_LIT = 51, OP_CHECK_LONG_LIT_NOCASE = 52, OP_CHECK_MED_LIT = 53,
     OP_CHECK_MED_LIT_NOCASE = 54, OP_CLEAR_WORK_DONE = 55, OP_INCLUDED_JUMP = 61, OP_SET_EXHAUST = 65
@@ -114,6 +114,21 @@ static int check_byte(const struct scan_state *s, u8 and_m, u8 cmp_m, u8 neg, in
     return !(differ ^ (neg != 0));
 }
 
+/* roseCheckMask32 / roseCheckMask64, rose/program_runtime.c:729-935 + validateMask32, rose/validate_mask.h:106-127:
+ * n window bytes from end + off; a byte outside the buffer is don't-care, a byte inside passes when
+ * ((c & and) != cmp) equals its neg_mask bit. */
+static int check_mask_n(const struct scan_state *s, const u8 *and_m, const u8 *cmp_m, u64 neg, u32 n, int32_t off, u64 end) {
+    if (off < 0 && (u64)(-(int64_t)off) > end) return 0;
+    int64_t base = (int64_t)end + off;
+    for (u32 k = 0; k < n; k++) {
+        int64_t o = base + k;
+        if (o < 0 || o >= (int64_t)s->len) continue;
+        int differ = (u8)(s->buf[o] & and_m[k]) != cmp_m[k];
+        if (differ != (int)((neg >> k) & 1)) return 0;
+    }
+    return 1;
+}
+
 /* roseRunProgram_l.  `end` = offset one past the literal's last byte (lit_offset_adjust = 1).
  * Returns 0 to continue, -1 to stop the scan. */
 static int run_program(struct scan_state *s, u32 prog, u64 end) {
@@ -129,6 +144,14 @@ static int run_program(struct scan_state *s, u32 prog, u64 end) {
             break;
         case OP_CHECK_BYTE:
             if (!check_byte(s, pc[1], pc[2], pc[3], (int32_t)rd32(pc + 4), end)) pc += rd32(pc + 8); else pc += 16;
+            break;
+        case OP_CHECK_MASK_32: /* struct ROSE_STRUCT_CHECK_MASK_32, rose/rose_program.h: and 1, cmp 33, neg 68, offset 72, fail 76 */
+            if (!check_mask_n(s, pc + 1, pc + 33, rd32(pc + 68), 32, (int32_t)rd32(pc + 72), end)) pc += rd32(pc + 76);
+            else pc += 80;
+            break;
+        case OP_CHECK_MASK_64: /* and 1, cmp 65, neg 136, offset 144, fail 148 */
+            if (!check_mask_n(s, pc + 1, pc + 65, rd64(pc + 136), 64, (int32_t)rd32(pc + 144), end)) pc += rd32(pc + 148);
+            else pc += 152;
             break;
         case OP_CATCH_UP: pc += 8; break; /* no engines in a pure-literal database */
         case OP_CLEAR_WORK_DONE: work_done = 0; pc += 8; break;

@@ -1,0 +1,124 @@
+"""GPU tests (-m gpu) of the literal-program instructions beyond the plain report shapes: databases written with the
+extended literal form (tests/test_litdb_ext.py validates the same databases on the unmodified reference runtime) are
+scanned through the C ABI by every literal front end and compared with the reference runtime and the brute-force ground
+truth; device-side counters prove that every case of the program interpreter was executed."""
+import random
+
+import pytest
+
+import litgen
+from test_litdb_ext import KINDS, KINDS_512, OP, compile_case, ext_cases, included_case
+from vectorscan_b200 import gpu, litdb
+
+pytestmark = pytest.mark.gpu
+FRONTENDS = [0, 1, 2, 3]
+
+
+def split_buffers(rng, text):
+    """The text as one buffer plus the same text cut into ragged pieces (independent block scans)."""
+    bufs = [text]
+    p = 0
+    while p < len(text):
+        n = rng.choice([1, 7, 64, 300, 1500])
+        bufs.append(text[p:p + n])
+        p += n
+    bufs.append(b"")
+    return bufs
+
+
+def gpu_batch(db, bufs, frontend, counts):
+    sc = gpu.alloc_scratch(db)
+    sc.set_option("frontend", frontend)
+    sc.set_option("count_ops", 1)
+    got = [(int(b), int(i), int(t)) for b, i, t in gpu.scan_vector_ex(db, bufs, sc)]
+    for k, v in enumerate(sc.opcode_counts()):
+        counts[k] += v
+    sc.close()
+    return got
+
+
+def expected(lits, flags, ids, ext, bufs, goff):
+    out = []
+    for bi, b in enumerate(bufs):
+        out += [(bi, i, t) for (i, t) in litgen.brute_force_ext(lits, flags, ids, ext, b, goff)]
+    return sorted(out, key=lambda x: (x[0], x[2], x[1]))
+
+
+@pytest.mark.parametrize("frontend", FRONTENDS)
+def test_ext_programs_equal_reference_and_brute_force(ref, frontend):
+    rng = random.Random(77 + frontend)
+    counts = [0] * 128
+    kinds = KINDS + KINDS_512  # the device implements the 64-byte instructions whatever ISA the host has
+    ran = 0
+    for kind, lits, flags, ids, ext, text, goff in ext_cases(11 + frontend, kinds):
+        try:
+            db = compile_case(kind, lits, flags, ids, ext, goff)
+        except litdb.CompileError:
+            continue
+        bufs = split_buffers(rng, text)
+        got = gpu_batch(db, bufs, frontend, counts)
+        assert got == expected(lits, flags, ids, ext, bufs, goff), (kind, len(lits), len(text))
+        if kind not in KINDS_512 or ref.isa == "avx512":
+            rdb = ref.deserialize(db.serialize())
+            rs = ref.alloc_scratch(rdb)
+            rexp = []
+            for bi, b in enumerate(bufs):
+                rv, m = ref.scan(rdb, rs, b)
+                assert rv == 0
+                rexp += [(bi, i, t) for (i, t) in m]
+            ref.L.hs_free_scratch(rs)
+            ref.L.hs_free_database(rdb)
+            assert got == sorted(rexp, key=lambda x: (x[0], x[2], x[1])), kind
+        ran += 1
+    assert ran >= 60
+    for name in ("CHECK_GROUPS", "CHECK_MASK", "CHECK_MASK_32", "CHECK_MASK_64", "CHECK_BYTE", "SQUASH_GROUPS", "SET_EXHAUST"):
+        assert counts[OP[name]] > 0, f"{name} never executed on the device"
+    # and the everyday ones: END 0, DEDUPE 28, REPORT 33, REPORT_EXHAUST 34, CHECK_EXHAUSTED 39, CHECK_MED_LIT 53
+    for code in (0, 33, 34, 39, 53):
+        assert counts[code] > 0, code
+
+
+@pytest.mark.parametrize("frontend", FRONTENDS)
+def test_included_jump_programs(ref, frontend):
+    rng = random.Random(5)
+    counts = [0] * 128
+    for n in (20, 120, 600):
+        for alpha in (b"abcd", b"abcdefghijklmnop"):
+            lits, flags, ids, text = included_case(rng, n, alpha, rng.choice([500, 3000]))
+            db = litdb.compile_lit_multi(lits, flags, ids, engine=litdb.ENGINE_FDR, fdr_domain=rng.choice([9, 11, 13]),
+                                         fdr_stride=1, included_jump=1)
+            bufs = split_buffers(rng, text)
+            got = gpu_batch(db, bufs, frontend, counts)
+            exp = []
+            for bi, b in enumerate(bufs):
+                exp += [(bi, i, t) for (i, t) in litgen.brute_force(lits, flags, ids, b)]
+            assert got == sorted(exp, key=lambda x: (x[0], x[2], x[1])), (n, len(alpha))
+    assert counts[OP["INCLUDED_JUMP"]] > 0
+
+
+def test_every_interpreter_case_is_reached():
+    """One database per remaining case of run_program: DEDUPE (+REPORT_EXHAUST / +SET_EXHAUST), DEDUPE_AND_REPORT,
+    FINAL_REPORT, so that together with the tests above no case of the device interpreter is left unexecuted."""
+    counts = [0] * 128
+    # shared report id between two literals -> dkey; SINGLEMATCH -> DEDUPE + REPORT_EXHAUST; quiet -> DEDUPE + SET_EXHAUST
+    lits = [b"alpha", b"alphabet", b"beta", b"betamax", b"gamma", b"gammaray", b"delta"]
+    flags = [0, 0, 8, 8, 8, 8, 0]
+    ids = [1, 1, 2, 2, 3, 3, 4]
+    ext = [None, None, None, None, {"flags": 4}, {"flags": 4}, None]
+    db = litdb.compile_lit_multi(lits, flags, ids, ext=ext)
+    text = b"alphabet betamax gammaray delta alphabet betamax delta"
+    got = gpu_batch(db, [text, text[:20]], 1, counts)
+    exp = []
+    for bi, b in enumerate([text, text[:20]]):
+        exp += [(bi, i, t) for (i, t) in litgen.brute_force_ext(lits, flags, ids, ext, b)]
+    assert got == sorted(exp, key=lambda x: (x[0], x[2], x[1]))
+    for code in (28, 34, 37, 38, 65):  # DEDUPE, REPORT_EXHAUST, DEDUPE_AND_REPORT, FINAL_REPORT, SET_EXHAUST
+        assert counts[code] > 0, code
+
+
+def test_max_bi_anchored_width_gate_on_device():
+    db = litdb.compile_lit_multi([b"needle", b"pin"], [0, 0], [1, 2], max_bi_anchored_width=40)
+    short, long_ = b"x" * 10 + b"needle" + b"pin", b"x" * 60 + b"needle" + b"pin"
+    sc = gpu.alloc_scratch(db)
+    got = [(int(b), int(i), int(t)) for b, i, t in gpu.scan_vector_ex(db, [short, long_, short], sc)]
+    assert got == [(0, 1, 16), (0, 2, 19), (2, 1, 16), (2, 2, 19)]

@@ -116,6 +116,7 @@ struct DevArena {
     // position order; seg_count[w] = records it wanted
     u32 *seg_count;
     u32 seg_cap;
+    unsigned long long *op_counts;  // test instrumentation (option "count_ops"): executions per Rose opcode, else null
 };
 
 constexpr u32 ERR_BAD_OPCODE = 1, ERR_BAD_DEDUPE = 2, ERR_PROGRAM_LOOP = 4, ERR_COLLECTOR = 8, ERR_UNSORTED = 16;
@@ -352,6 +353,7 @@ __device__ void run_program(const Ctx &c, u32 prog, u32 buf, const u8 *btext, u3
     u32 pc = prog;
     for (int guard = 0; guard < 4096; guard++) {
         const u8 code = bc[pc];
+        if (c.ar.op_counts) atomicAdd(&c.ar.op_counts[code & 127], 1ull);
         switch (code) {
         case op::END:
             return;
@@ -1074,6 +1076,7 @@ struct hs_gpu_scratch {
     cudaStream_t copy_stream = nullptr;        // H2D of host batches, so that chunk k + 1 copies while chunk k is scanned
     std::vector<cudaEvent_t> chunk_ready;
     long opt_ordered = 1;
+    DevBuf<unsigned long long> op_counts;      // option "count_ops": 128 counters, one per Rose opcode (tests)
     // control blocks of 8 words: [0] arena count, [1] candidates, [2] probes, [3] error(u32), [4] n_selected,
     // [5] largest segment.  Block 0 serves the general path; blocks 1 and 2 alternate between ordered scans
     // (k_compact clears the block of the next scan, so no memset sits in front of the kernel).
@@ -1500,7 +1503,7 @@ hs_error_t scan_train_ordered(hs_gpu_scratch *s, DbImage *im, const TrainMember 
             if (mem[i].ready) CU_OK(cudaStreamWaitEvent(s->stream, mem[i].ready, 0));
             CU_OK(cudaEventRecord(s->tev[3 * i], s->stream));  // the kernel's interval starts after the wait
             const u32 grid = turbo_grid(s, cp, cta_warps), W = grid * cta_warps;
-            DevArena ar{s->recs.p, ctl + 0, ctl + 1, reinterpret_cast<u32 *>(ctl + 3), 0, s->seg_count.p, (u32)seg_cap};
+            DevArena ar{s->recs.p, ctl + 0, ctl + 1, reinterpret_cast<u32 *>(ctl + 3), 0, s->seg_count.p, (u32)seg_cap, s->op_counts.p};
             hs_error_t rv;
             if (v2) rv = launch_turbo2_any<true>(s, im->dev, cp, ar, grid, cta_warps);
             else
@@ -1598,7 +1601,7 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
     bool small_done = false;
     for (int attempt = 0;; attempt++) {
         CU_OK(cudaMemsetAsync(s->d_ctl, 0, 8 * sizeof(unsigned long long), s->stream));
-        DevArena ar{s->recs.p, s->d_ctl + 0, s->d_ctl + 1, reinterpret_cast<u32 *>(s->d_ctl + 3), s->recs.cap, nullptr, 0};
+        DevArena ar{s->recs.p, s->d_ctl + 0, s->d_ctl + 1, reinterpret_cast<u32 *>(s->d_ctl + 3), s->recs.cap, nullptr, 0, s->op_counts.p};
         hs_error_t rv;
         CU_OK(cudaEventRecord(s->ev[6], s->stream));
         const bool use_turbo = im->dev.tK && s->opt_frontend != 1;
@@ -2430,6 +2433,30 @@ hs_error_t hs_gpu_last_stats(const hs_gpu_scratch_t *scratch, hs_gpu_stats_t *st
     return HS_SUCCESS;
 }
 
+hs_error_t hs_gpu_database_opcodes(const hs_database_t *db, unsigned long long *hist, unsigned int n) {
+    if (!db || !hist) return HS_INVALID;
+    DbView v;
+    std::string why;
+    const int rv = parse_database(db, v, why);
+    if (rv != E_SUCCESS) return (hs_error_t)rv;
+    u64 h[128] = {0};
+    u32 dummy = 0;
+    for (u32 p : v.programs)
+        if (census_program(v, p, why, dummy, h) != E_SUCCESS) return HS_INVALID;
+    for (unsigned int i = 0; i < n && i < 128; i++) hist[i] = h[i];
+    return HS_SUCCESS;
+}
+
+hs_error_t hs_gpu_opcode_counts(hs_gpu_scratch_t *scratch, unsigned long long *counts, unsigned int n) {
+    if (!scratch || scratch->magic != 0x47505553 || !counts) return HS_INVALID;
+    if (!scratch->op_counts.p) return HS_INVALID;  // option "count_ops" not set
+    if (ensure_device(scratch) != HS_SUCCESS) return HS_UNKNOWN_ERROR;
+    if (cudaStreamSynchronize(scratch->stream) != cudaSuccess) return HS_UNKNOWN_ERROR;
+    if (n > 128) n = 128;
+    return cudaMemcpy(counts, scratch->op_counts.p, n * sizeof(unsigned long long), cudaMemcpyDeviceToHost) == cudaSuccess
+               ? HS_SUCCESS : HS_UNKNOWN_ERROR;
+}
+
 hs_error_t hs_gpu_set_option(hs_gpu_scratch_t *scratch, const char *name, long value) {
     if (!scratch || scratch->magic != 0x47505553 || !name) return HS_INVALID;
     if (!strcmp(name, "frontend")) { scratch->opt_frontend = value; return HS_SUCCESS; }
@@ -2437,6 +2464,11 @@ hs_error_t hs_gpu_set_option(hs_gpu_scratch_t *scratch, const char *name, long v
     if (!strcmp(name, "warps")) { scratch->opt_warps = value; return HS_SUCCESS; }
     if (!strcmp(name, "pipeline")) { scratch->opt_pipeline = value; return HS_SUCCESS; }
     if (!strcmp(name, "ordered")) { scratch->opt_ordered = value; return HS_SUCCESS; }
+    if (!strcmp(name, "count_ops")) {
+        if (!value) { scratch->op_counts.release(); return HS_SUCCESS; }
+        if (ensure_device(scratch) != HS_SUCCESS || scratch->op_counts.reserve(128) != cudaSuccess) return HS_NOMEM;
+        return cudaMemset(scratch->op_counts.p, 0, 128 * sizeof(unsigned long long)) == cudaSuccess ? HS_SUCCESS : HS_UNKNOWN_ERROR;
+    }
     if (!strcmp(name, "segment")) { scratch->seg_cap_hint = value > 0 ? (u64)value : 1; return HS_SUCCESS; }
     if (!strcmp(name, "arena")) { scratch->arena_hint = value > 0 ? (u64)value : 1; return HS_SUCCESS; }
     return HS_INVALID;

@@ -91,7 +91,7 @@ inline size_t op_size(u8 code, size_t &fail_jump_at) {
 // inside the bytecode with its full operand block, every fail_jump must land on an instruction of this same program at
 // or before its END (the device interpreter follows them unchecked), and a DEDUPE must be followed by one of the three
 // reports the interpreter fuses it with.  INCLUDED_JUMP children are programs of other literals, walked on their own.
-inline int census_program(const DbView &d, u32 prog, std::string &why, u32 &max_lit_len) {
+inline int census_program(const DbView &d, u32 prog, std::string &why, u32 &max_lit_len, u64 *hist = nullptr) {
     size_t pc = prog;
     std::vector<size_t> starts, targets;
     for (int guard = 0; guard < 4096; guard++) {
@@ -104,6 +104,7 @@ inline int census_program(const DbView &d, u32 prog, std::string &why, u32 &max_
             return E_ARCH;
         }
         if (!in_range(d, pc, sz)) { why = "instruction operands run past the bytecode"; return E_INVALID; }
+        if (hist) hist[code & 127]++;
         starts.push_back(pc);
         if (fj) {
             const u32 j = rd32(d.bc, pc + fj);

@@ -29,6 +29,7 @@
 #include <map>
 #include <set>
 #include <string>
+#include <tuple>
 #include <vector>
 
 namespace {
@@ -72,6 +73,18 @@ struct HwlmLit {
     u64 groups;
 };
 
+// one byte constraint of a literal's lookaround (offset relative to the literal's end, negative)
+struct Look {
+    int offset;
+    bool is_class;
+    u8 andm, cmpm, neg;
+    u8 cls[32];
+    bool admits(u8 c) const {
+        if (is_class) return (cls[c >> 3] >> (c & 7)) & 1;
+        return ((c & andm) == cmpm) != (neg != 0);
+    }
+};
+
 struct FullLit {
     std::string s;
     bool nocase;
@@ -79,6 +92,15 @@ struct FullLit {
     bool single;  // HS_FLAG_SINGLEMATCH
     u32 ekey = INVALID_EKEY;
     u32 dkey = INVALID_DKEY;
+    std::vector<Look> look;  // sorted by offset
+    u32 group = 0;
+    bool check_groups = false, want_squash = false, quiet = false;
+};
+
+struct BuildExt {
+    bool included_jump = false, avx512 = false;
+    u64 groups_off = 0;
+    u32 max_bi_anchored_width = 0;
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -614,14 +636,186 @@ std::vector<u8> build_noodle(const HwlmLit &l) {
 // ------------------------------------------------------------------------------------------------
 // Rose programs + engine header + database header
 // ------------------------------------------------------------------------------------------------
+// The instruction that checks a literal's lookaround `look` (sorted by offset), chosen as makeLookaroundInstruction
+// does (src/rose/rose_build_program.cpp:1343-1523): and/cmp entries -> CHECK_BYTE / CHECK_MASK / CHECK_MASK_32 /
+// CHECK_MASK_64 (makeRoleByte :969, makeRoleMask :989, makeRoleMask32 :1034, makeRoleMask64 :1074); class entries ->
+// the shufti family (makeRoleShufti :1380, mask layout getShuftiMasks :1190 / nibMaskUpdate :1175).  `fails` receives
+// (instruction offset, offset of its fail_jump operand) so the caller can aim it at the end of the block.
+bool emit_look(Buf &rose, const std::vector<Look> &look, bool avx512, std::vector<std::pair<size_t, size_t>> &fails,
+               std::string &err) {
+    if (look.empty()) return true;
+    const int base = look.front().offset, span = look.back().offset - base + 1;
+    bool any_class = false;
+    for (auto &e : look) any_class |= e.is_class;
+    if (!any_class) {
+        if (look.size() == 1) {
+            const Look &e = look[0];
+            size_t o = rose.grow(op::check_byte::SIZE);
+            wr8(rose.at(o), 0, op::CHECK_BYTE);
+            wr8(rose.at(o), op::check_byte::and_mask, e.andm);
+            wr8(rose.at(o), op::check_byte::cmp_mask, e.cmpm);
+            wr8(rose.at(o), op::check_byte::negation, e.neg ? 1 : 0);
+            wr32(rose.at(o), op::check_byte::offset, (u32)e.offset);
+            fails.push_back({o, op::check_byte::fail_jump});
+            return true;
+        }
+        if (span <= 8) {
+            u64 am = 0, cm = 0, nm = 0;
+            for (auto &e : look) {
+                const unsigned sh = 8u * (unsigned)(e.offset - base);
+                am |= (u64)e.andm << sh;
+                cm |= (u64)e.cmpm << sh;
+                if (e.neg) nm |= 0xffull << sh;
+            }
+            size_t o = rose.grow(op::check_mask::SIZE);
+            wr8(rose.at(o), 0, op::CHECK_MASK);
+            wr64(rose.at(o), op::check_mask::and_mask, am);
+            wr64(rose.at(o), op::check_mask::cmp_mask, cm);
+            wr64(rose.at(o), op::check_mask::neg_mask, nm);
+            wr32(rose.at(o), op::check_mask::offset, (u32)base);
+            fails.push_back({o, op::check_mask::fail_jump});
+            return true;
+        }
+        if (span <= 32 || (span <= 64 && avx512)) {
+            const bool wide = span > 32;
+            size_t o = rose.grow(wide ? op::check_mask64::SIZE : op::check_mask32::SIZE);
+            wr8(rose.at(o), 0, wide ? op::CHECK_MASK_64 : op::CHECK_MASK_32);
+            u64 nm = 0;
+            for (auto &e : look) {
+                const size_t k = (size_t)(e.offset - base);
+                wr8(rose.at(o), (wide ? op::check_mask64::and_mask : op::check_mask32::and_mask) + k, e.andm);
+                wr8(rose.at(o), (wide ? op::check_mask64::cmp_mask : op::check_mask32::cmp_mask) + k, e.cmpm);
+                if (e.neg) nm |= 1ull << k;
+            }
+            if (wide) {
+                wr64(rose.at(o), op::check_mask64::neg_mask, nm);
+                wr32(rose.at(o), op::check_mask64::offset, (u32)base);
+                fails.push_back({o, op::check_mask64::fail_jump});
+            } else {
+                wr32(rose.at(o), op::check_mask32::neg_mask, (u32)nm);
+                wr32(rose.at(o), op::check_mask32::offset, (u32)base);
+                fails.push_back({o, op::check_mask32::fail_jump});
+            }
+            return true;
+        }
+        err = "lookaround spans more bytes than any mask instruction of the target holds";
+        return false;
+    }
+    // shufti family: a bucket = one (high-nibble set) x (low-nibble set) product; a class is the union of its products
+    if (span > (avx512 ? 64 : 32)) { err = "class lookaround spans more bytes than a shufti instruction holds"; return false; }
+    std::map<u32, u32> bucket_of;  // (hi set << 16 | lo set) -> bucket index
+    u8 hi_mask[32] = {0}, lo_mask[32] = {0}, sel_lo[64] = {0}, sel_hi[64] = {0};
+    u64 neg = ~0ull;
+    for (auto &e : look) {
+        bool in[256];
+        u32 count = 0;
+        for (u32 c = 0; c < 256; c++) { in[c] = e.admits((u8)c); count += in[c]; }
+        const size_t k = (size_t)(e.offset - base);
+        if (count > 128) { for (u32 c = 0; c < 256; c++) in[c] = !in[c]; }  // heavy classes are stored complemented
+        else neg ^= 1ull << k;
+        std::map<u32, u32> lo2hi;
+        for (u32 h = 0; h < 16; h++) {
+            u32 lo = 0;
+            for (u32 l = 0; l < 16; l++) if (in[h * 16 + l]) lo |= 1u << l;
+            if (lo) lo2hi[lo] |= 1u << h;
+        }
+        for (auto &kv : lo2hi) {
+            const u32 key = (kv.second << 16) | kv.first;
+            auto it = bucket_of.find(key);
+            if (it == bucket_of.end()) {
+                const u32 b = (u32)bucket_of.size();
+                if (b >= 16) { err = "class lookaround needs more than 16 shufti buckets"; return false; }
+                it = bucket_of.emplace(key, b).first;
+                for (u32 n = 0; n < 16; n++) {
+                    if ((kv.second >> n) & 1) hi_mask[n + (b >= 8 ? 16 : 0)] |= (u8)(1u << (b & 7));
+                    if ((kv.first >> n) & 1) lo_mask[n + (b >= 8 ? 16 : 0)] |= (u8)(1u << (b & 7));
+                }
+            }
+            if (it->second >= 8) sel_hi[k] |= (u8)(1u << (it->second - 8)); else sel_lo[k] |= (u8)(1u << it->second);
+        }
+    }
+    const u32 nb = (u32)bucket_of.size();
+    auto rep4 = [&](size_t o, size_t field, const u8 *m16) { for (int r = 0; r < 4; r++) std::memcpy(rose.at(o) + field + 16 * r, m16, 16); };
+    if (span <= 16 && nb <= 8) {
+        namespace I = op::check_shufti_16x8;
+        size_t o = rose.grow(I::SIZE);
+        wr8(rose.at(o), 0, op::CHECK_SHUFTI_16x8);
+        std::memcpy(rose.at(o) + I::nib_mask, lo_mask, 16);
+        std::memcpy(rose.at(o) + I::nib_mask + 16, hi_mask, 16);
+        std::memcpy(rose.at(o) + I::bucket_select_mask, sel_lo, 16);
+        wr32(rose.at(o), I::neg_mask, (u32)(neg & 0xffff));
+        wr32(rose.at(o), I::offset, (u32)base);
+        fails.push_back({o, I::fail_jump});
+    } else if (span <= 32 && nb <= 8) {
+        namespace I = op::check_shufti_32x8;
+        size_t o = rose.grow(I::SIZE);
+        wr8(rose.at(o), 0, op::CHECK_SHUFTI_32x8);
+        std::memcpy(rose.at(o) + I::hi_mask, hi_mask, 16);
+        std::memcpy(rose.at(o) + I::lo_mask, lo_mask, 16);
+        std::memcpy(rose.at(o) + I::bucket_select_mask, sel_lo, 32);
+        wr32(rose.at(o), I::neg_mask, (u32)neg);
+        wr32(rose.at(o), I::offset, (u32)base);
+        fails.push_back({o, I::fail_jump});
+    } else if (avx512 && nb <= 8) {
+        namespace I = op::check_shufti_64x8;
+        size_t o = rose.grow(I::SIZE);
+        wr8(rose.at(o), 0, op::CHECK_SHUFTI_64x8);
+        rep4(o, I::hi_mask, hi_mask);
+        rep4(o, I::lo_mask, lo_mask);
+        std::memcpy(rose.at(o) + I::bucket_select_mask, sel_lo, 64);
+        wr64(rose.at(o), I::neg_mask, neg);
+        wr32(rose.at(o), I::offset, (u32)base);
+        fails.push_back({o, I::fail_jump});
+    } else if (span <= 16) {
+        namespace I = op::check_shufti_16x16;
+        size_t o = rose.grow(I::SIZE);
+        wr8(rose.at(o), 0, op::CHECK_SHUFTI_16x16);
+        std::memcpy(rose.at(o) + I::hi_mask, hi_mask, 32);
+        std::memcpy(rose.at(o) + I::lo_mask, lo_mask, 32);
+        std::memcpy(rose.at(o) + I::bucket_select_mask, sel_lo, 16);
+        std::memcpy(rose.at(o) + I::bucket_select_mask + 16, sel_hi, 16);
+        wr32(rose.at(o), I::neg_mask, (u32)(neg & 0xffff));
+        wr32(rose.at(o), I::offset, (u32)base);
+        fails.push_back({o, I::fail_jump});
+    } else if (span <= 32) {
+        namespace I = op::check_shufti_32x16;
+        size_t o = rose.grow(I::SIZE);
+        wr8(rose.at(o), 0, op::CHECK_SHUFTI_32x16);
+        std::memcpy(rose.at(o) + I::hi_mask, hi_mask, 32);
+        std::memcpy(rose.at(o) + I::lo_mask, lo_mask, 32);
+        std::memcpy(rose.at(o) + I::bucket_select_mask_hi, sel_hi, 32);
+        std::memcpy(rose.at(o) + I::bucket_select_mask_lo, sel_lo, 32);
+        wr32(rose.at(o), I::neg_mask, (u32)neg);
+        wr32(rose.at(o), I::offset, (u32)base);
+        fails.push_back({o, I::fail_jump});
+    } else {
+        namespace I = op::check_shufti_64x16;
+        size_t o = rose.grow(I::SIZE);
+        wr8(rose.at(o), 0, op::CHECK_SHUFTI_64x16);
+        rep4(o, I::hi_mask_1, hi_mask);
+        rep4(o, I::hi_mask_2, hi_mask + 16);
+        rep4(o, I::lo_mask_1, lo_mask);
+        rep4(o, I::lo_mask_2, lo_mask + 16);
+        std::memcpy(rose.at(o) + I::bucket_select_mask_hi, sel_hi, 64);
+        std::memcpy(rose.at(o) + I::bucket_select_mask_lo, sel_lo, 64);
+        wr64(rose.at(o), I::neg_mask, neg);
+        wr32(rose.at(o), I::offset, (u32)base);
+        fails.push_back({o, I::fail_jump});
+    }
+    return true;
+}
+
 struct Fragment {
     std::string suffix;  // <= 8 bytes handed to the literal matcher
     bool nocase;
     std::vector<u32> fulls;  // indices into the FullLit array
     u32 program = 0;
+    u32 group = 0;
+    int child = -1;          // fragment whose text is a suffix of this one's and whose program INCLUDED_JUMP enters
+    u8 squash = 0;           // FDR confirm bits (buckets) of that fragment
 };
 
-int build(const std::vector<FullLit> &fulls_in, const hsb_lit_options &opt, std::vector<u8> &image,
+int build(const std::vector<FullLit> &fulls_in, const hsb_lit_options &opt, const BuildExt &bx, std::vector<u8> &image,
           std::string &err) {
     std::vector<FullLit> fulls = fulls_in;
     if (fulls.empty()) { err = "no literals"; return HSB_LIT_COMPILER_ERROR; }
@@ -632,9 +826,18 @@ int build(const std::vector<FullLit> &fulls_in, const hsb_lit_options &opt, std:
     // than one distinct literal (the same (id, to) could otherwise be delivered twice)
     std::map<u32, u32> ekeys, dkeys;
     std::map<u32, std::set<std::pair<std::string, bool>>> lits_per_report;
+    std::map<u32, int> quiet_of;  // report id -> quiet? (one report = one behaviour)
     for (auto &f : fulls) {
         if (f.single) ekeys.emplace(f.report, 0);
         lits_per_report[f.report].insert({f.s, f.nocase});
+        auto q = quiet_of.emplace(f.report, f.quiet ? 1 : 0);
+        if (q.first->second != (f.quiet ? 1 : 0)) { err = "a report id is either quiet or not"; return HSB_LIT_COMPILER_ERROR; }
+        if (f.group > 62) { err = "group must be 0..62"; return HSB_LIT_COMPILER_ERROR; }
+        for (size_t k = 0; k < f.look.size(); k++)
+            if (f.look[k].offset < -64 || f.look[k].offset > -1 || (k && f.look[k].offset <= f.look[k - 1].offset)) {
+                err = "lookaround offsets must be distinct, ascending and within -64..-1";
+                return HSB_LIT_COMPILER_ERROR;
+            }
     }
     { u32 k = 0; for (auto &e : ekeys) e.second = k++; }
     for (auto &r : lits_per_report) if (r.second.size() > 1) { u32 k = (u32)dkeys.size(); dkeys[r.first] = k; }
@@ -646,23 +849,28 @@ int build(const std::vector<FullLit> &fulls_in, const hsb_lit_options &opt, std:
     }
 
     // fragments: full literals sharing the same (<=8-byte suffix, caselessness)
-    std::map<std::pair<std::string, bool>, u32> frag_index;
+    std::map<std::tuple<std::string, bool, u32>, u32> frag_index;
     std::vector<Fragment> frags;
     for (u32 i = 0; i < fulls.size(); i++) {
         const FullLit &f = fulls[i];
         std::string suf = f.s.size() > 8 ? f.s.substr(f.s.size() - 8) : f.s;
         bool any_alpha = false;
         for (char c : suf) any_alpha |= is_alpha((u8)c);
-        auto key = std::make_pair(suf, f.nocase && any_alpha);
+        auto key = std::make_tuple(suf, f.nocase && any_alpha, f.group);
         auto it = frag_index.find(key);
         if (it == frag_index.end()) {
             it = frag_index.emplace(key, (u32)frags.size()).first;
-            frags.push_back({suf, key.second, {}, 0});
+            Fragment fr;
+            fr.suffix = suf;
+            fr.nocase = f.nocase && any_alpha;
+            fr.group = f.group;
+            frags.push_back(fr);
         }
         // identical (text, case, report) duplicates add nothing
         bool dup = false;
         for (u32 o : frags[it->second].fulls)
-            dup |= fulls[o].s == f.s && fulls[o].nocase == f.nocase && fulls[o].report == f.report;
+            dup |= fulls[o].s == f.s && fulls[o].nocase == f.nocase && fulls[o].report == f.report &&
+                   fulls[o].look.empty() && f.look.empty();
         if (!dup) frags[it->second].fulls.push_back(i);
     }
 
@@ -693,69 +901,137 @@ int build(const std::vector<FullLit> &fulls_in, const hsb_lit_options &opt, std:
             }
     rose.align(8);
 
-    // programs: per full literal a block  [CHECK_MED_LIT*] [CHECK_EXHAUSTED] [DEDUPE] REPORT*  whose
-    // fail_jumps land on the next block; END closes the program
+    // Suffix inclusion (FDR only; findIncludedLits / buildSquashMask, src/fdr/fdr_compile.cpp:654-812): when fragment P
+    // confirms at some end position and fragment C -- a proper suffix of P with the same caselessness and group, alone
+    // among the fragments of its bucket that can end where P ends -- sits in a LATER bucket, P's program ends in an
+    // INCLUDED_JUMP that clears C's bucket bit for that position and runs C's program directly.  This writer only
+    // takes the clear-cut cases (one child per parent, one parent per child); leaving a squash out is always valid.
+    if (bx.included_jump) {
+        if (opt.engine != HSB_LIT_ENGINE_FDR) { err = "included_jump needs engine = FDR"; return HSB_LIT_COMPILER_ERROR; }
+        std::vector<HwlmLit> pre;
+        for (u32 i = 0; i < frags.size(); i++) pre.push_back({frags[i].suffix, frags[i].nocase, i, 1ull << frags[i].group});
+        std::vector<std::vector<u32>> pb = assign_fdr_buckets(pre);
+        std::vector<u32> bucket_of(frags.size(), 0);
+        for (u32 b = 0; b < pb.size(); b++) for (u32 li : pb[b]) bucket_of[pre[li].id] = b;
+        auto upper = [](const std::string &x) { std::string r = x; for (auto &c : r) c = (char)to_upper((u8)c); return r; };
+        auto ends_with = [](const std::string &a, const std::string &b) {
+            return b.size() <= a.size() && a.compare(a.size() - b.size(), b.size(), b) == 0;
+        };
+        std::vector<bool> has_parent(frags.size(), false);
+        for (u32 p = 0; p < frags.size(); p++) {
+            const std::string up = upper(frags[p].suffix);
+            bool same_bucket = false;
+            for (u32 x = 0; x < frags.size(); x++)
+                same_bucket |= x != p && bucket_of[x] == bucket_of[p] && ends_with(up, upper(frags[x].suffix));
+            if (same_bucket) continue;
+            for (u32 b2 = bucket_of[p] + 1; b2 < fdr::NUM_BUCKETS; b2++) {
+                std::vector<u32> related;
+                for (u32 x = 0; x < frags.size(); x++)
+                    if (bucket_of[x] == b2 && ends_with(up, upper(frags[x].suffix))) related.push_back(x);
+                if (related.empty()) continue;
+                if (related.size() == 1) {
+                    const u32 c = related[0];
+                    const Fragment &P = frags[p], &Cf = frags[c];
+                    const bool same_text = P.nocase ? true : ends_with(P.suffix, Cf.suffix);
+                    if (Cf.suffix.size() < P.suffix.size() && Cf.nocase == P.nocase && Cf.group == P.group && same_text &&
+                        !has_parent[c]) {
+                        frags[p].child = (int)c;
+                        frags[p].squash = (u8)(1u << b2);
+                        has_parent[c] = true;
+                    }
+                }
+                break;  // only the first later bucket holding a suffix is considered
+            }
+        }
+    }
+    std::map<u32, u32> group_users;
+    for (auto &fr : frags) group_users[fr.group]++;
+
+    // programs: [CHECK_GROUPS] then per full literal a block  [lookaround] [CHECK_MED_LIT*] [CHECK_EXHAUSTED] [DEDUPE]
+    // REPORT*  whose fail_jumps land on the next block, then [SQUASH_GROUPS] [INCLUDED_JUMP]; END closes the program
+    std::vector<std::pair<size_t, u32>> jump_patches;  // INCLUDED_JUMP instruction -> child fragment
     for (auto &fr : frags) {
         rose.align(op::ALIGN);
         fr.program = (u32)rose.size();
+        bool any_check_groups = false;
+        for (u32 i : fr.fulls) any_check_groups |= fulls[i].check_groups;
+        if (any_check_groups) {
+            size_t o = rose.grow(op::check_groups::SIZE);
+            wr8(rose.at(o), 0, op::CHECK_GROUPS);
+            wr64(rose.at(o), op::check_groups::groups, 1ull << fr.group);
+        }
+        const bool squash = fr.fulls.size() == 1 && fulls[fr.fulls[0]].want_squash && fulls[fr.fulls[0]].single &&
+                            group_users[fr.group] == 1;
+        const bool trailing = squash || fr.child >= 0;
         for (size_t bi = 0; bi < fr.fulls.size(); bi++) {
             const FullLit &f = fulls[fr.fulls[bi]];
-            size_t block_len = 0;
-            if (f.s.size() > 8) block_len += op::check_lit::SIZE;
-            if (f.ekey != INVALID_EKEY) {
-                block_len += op::check_exhausted::SIZE;
-                if (f.dkey != INVALID_DKEY) block_len += op::dedupe::SIZE;
-                block_len += op::report_exhaust::SIZE;
-            } else if (f.dkey != INVALID_DKEY) {
-                block_len += op::dedupe_and_report::SIZE;
-            } else {
-                block_len += op::report::SIZE;
-            }
-            const size_t block_start = rose.size(), block_end = block_start + block_len;
+            std::vector<std::pair<size_t, size_t>> fails;
+            if (!emit_look(rose, f.look, bx.avx512, fails, err)) return HSB_LIT_COMPILER_ERROR;
             if (f.s.size() > 8) {
                 size_t o = rose.grow(op::check_lit::SIZE);
                 wr8(rose.at(o), 0, f.nocase ? op::CHECK_MED_LIT_NOCASE : op::CHECK_MED_LIT);
                 wr32(rose.at(o), op::check_lit::lit_offset, lit_text_off[fr.fulls[bi]]);
                 wr32(rose.at(o), op::check_lit::lit_length, (u32)f.s.size());
-                wr32(rose.at(o), op::check_lit::fail_jump, (u32)(block_end - o));
+                fails.push_back({o, op::check_lit::fail_jump});
             }
             if (f.ekey != INVALID_EKEY) {
                 size_t o = rose.grow(op::check_exhausted::SIZE);
                 wr8(rose.at(o), 0, op::CHECK_EXHAUSTED);
                 wr32(rose.at(o), op::check_exhausted::ekey, f.ekey);
-                wr32(rose.at(o), op::check_exhausted::fail_jump, (u32)(block_end - o));
+                fails.push_back({o, op::check_exhausted::fail_jump});
                 if (f.dkey != INVALID_DKEY) {
                     o = rose.grow(op::dedupe::SIZE);
                     wr8(rose.at(o), 0, op::DEDUPE);
                     wr32(rose.at(o), op::dedupe::dkey, f.dkey);
-                    wr32(rose.at(o), op::dedupe::fail_jump, (u32)(block_end - o));
+                    fails.push_back({o, op::dedupe::fail_jump});
                 }
-                o = rose.grow(op::report_exhaust::SIZE);
-                wr8(rose.at(o), 0, op::REPORT_EXHAUST);
-                wr32(rose.at(o), op::report_exhaust::onmatch, f.report);
-                wr32(rose.at(o), op::report_exhaust::ekey, f.ekey);
+                if (f.quiet) {
+                    o = rose.grow(op::set_exhaust::SIZE);
+                    wr8(rose.at(o), 0, op::SET_EXHAUST);
+                    wr32(rose.at(o), op::set_exhaust::ekey, f.ekey);
+                } else {
+                    o = rose.grow(op::report_exhaust::SIZE);
+                    wr8(rose.at(o), 0, op::REPORT_EXHAUST);
+                    wr32(rose.at(o), op::report_exhaust::onmatch, f.report);
+                    wr32(rose.at(o), op::report_exhaust::ekey, f.ekey);
+                }
+            } else if (f.quiet) {
+                // a quiet report without an exhaustion key delivers nothing
             } else if (f.dkey != INVALID_DKEY) {
                 size_t o = rose.grow(op::dedupe_and_report::SIZE);
                 wr8(rose.at(o), 0, op::DEDUPE_AND_REPORT);
                 wr32(rose.at(o), op::dedupe_and_report::dkey, f.dkey);
                 wr32(rose.at(o), op::dedupe_and_report::onmatch, f.report);
-                wr32(rose.at(o), op::dedupe_and_report::fail_jump, (u32)(block_end - o));
+                fails.push_back({o, op::dedupe_and_report::fail_jump});
             } else {
                 size_t o = rose.grow(op::report::SIZE);
                 // a lone trailing REPORT is emitted in its one-shot FINAL_REPORT form
-                bool last = bi + 1 == fr.fulls.size();
+                bool last = bi + 1 == fr.fulls.size() && !trailing;
                 wr8(rose.at(o), 0, last ? op::FINAL_REPORT : op::REPORT);
                 wr32(rose.at(o), op::report::onmatch, f.report);
             }
-            (void)block_start;
+            const size_t block_end = rose.size();
+            for (auto &fj : fails) wr32(rose.at(fj.first), fj.second, (u32)(block_end - fj.first));
+        }
+        if (squash) {
+            size_t o = rose.grow(op::squash_groups::SIZE);
+            wr8(rose.at(o), 0, op::SQUASH_GROUPS);
+            wr64(rose.at(o), op::squash_groups::groups, ~(1ull << fr.group));
+        }
+        if (fr.child >= 0) {
+            size_t o = rose.grow(op::included_jump::SIZE);
+            wr8(rose.at(o), 0, op::INCLUDED_JUMP);
+            wr8(rose.at(o), op::included_jump::squash, fr.squash);
+            jump_patches.push_back({o, (u32)fr.child});
         }
         size_t o = rose.grow(op::SIZE_1);
         wr8(rose.at(o), 0, op::END);
     }
+    for (auto &jp : jump_patches) wr32(rose.at(jp.first), op::included_jump::child_offset, frags[jp.second].program);
 
     // literal matcher
     std::vector<HwlmLit> hl;
-    for (auto &fr : frags) hl.push_back({fr.suffix, fr.nocase, fr.program, 1ull});
+    for (auto &fr : frags) hl.push_back({fr.suffix, fr.nocase, fr.program, 1ull << fr.group});
     std::vector<u8> engine;
     u8 hwlm_type = hwlm::ENGINE_FDR;
     int engine_choice = opt.engine;
@@ -830,12 +1106,15 @@ int build(const std::vector<FullLit> &fulls_in, const hsb_lit_options &opt, std:
     wr32(r, rose::handledKeyFatbitSize, fatbit_size(0));
     wr32(r, rose::minWidth, min_width);
     wr32(r, rose::minWidthExcludingBoundaries, min_width);
-    wr32(r, rose::maxBiAnchoredWidth, rose::BOUND_INF);
+    wr32(r, rose::maxBiAnchoredWidth, bx.max_bi_anchored_width ? bx.max_bi_anchored_width : rose::BOUND_INF);
     wr32(r, rose::floatingDistance, rose::BOUND_INF);
     wr32(r, rose::smallBlockDistance, 0);
     wr32(r, rose::floatingMinLiteralMatchOffset, min_width);
-    wr64(r, rose::initialGroups, 1);
-    wr64(r, rose::floating_group_mask, 1);
+    u64 all_groups = 0;
+    u32 top_group = 0;
+    for (auto &fr : frags) { all_groups |= 1ull << fr.group; top_group = std::max(top_group, fr.group); }
+    wr64(r, rose::initialGroups, all_groups & ~bx.groups_off);
+    wr64(r, rose::floating_group_mask, all_groups);
     wr32(r, rose::size, (u32)rose.size());
     wr32(r, rose::delay_fatbit_size, fatbit_size(0));
     wr32(r, rose::anchored_fatbit_size, fatbit_size(0));
@@ -852,8 +1131,8 @@ int build(const std::vector<FullLit> &fulls_in, const hsb_lit_options &opt, std:
         wr32(so, rose::so::leftfixLagTable, cur);
         wr32(so, rose::so::anchorState, cur);
         wr32(so, rose::so::groups, cur);
-        wr32(so, rose::so::groups_size, 1);
-        cur += 1;
+        wr32(so, rose::so::groups_size, top_group / 8 + 1);
+        cur += top_group / 8 + 1;
         wr32(so, rose::so::history, cur);
         wr32(so, rose::so::exhausted, cur);
         wr32(so, rose::so::exhausted_size, mmbit_size((u32)ekeys.size()));
@@ -889,9 +1168,10 @@ char *dup_error(const std::string &s) {
 
 extern "C" {
 
-int hsb_compile_lit_multi(const char *const *expressions, const unsigned *flags, const unsigned *ids,
-                          const size_t *lens, unsigned elements, unsigned mode,
-                          const hsb_lit_options *options, hs_database_t **db, char **error) {
+int hsb_compile_lit_multi_ext(const char *const *expressions, const unsigned *flags, const unsigned *ids,
+                              const size_t *lens, const hsb_lit_ext *ext, unsigned elements, unsigned mode,
+                              const hsb_lit_options *options, const hsb_lit_build_ext *build_ext,
+                              hs_database_t **db, char **error) {
     if (error) *error = nullptr;
     if (!db) return HSB_LIT_COMPILER_ERROR;
     *db = nullptr;
@@ -901,6 +1181,13 @@ int hsb_compile_lit_multi(const char *const *expressions, const unsigned *flags,
     if (mode != hsb::MODE_BLOCK) return fail("only HS_MODE_BLOCK databases are written");
     hsb_lit_options opt{};
     if (options) opt = *options;
+    BuildExt bx;
+    if (build_ext) {
+        bx.included_jump = build_ext->included_jump != 0;
+        bx.avx512 = build_ext->target_avx512 != 0;
+        bx.groups_off = build_ext->groups_off;
+        bx.max_bi_anchored_width = build_ext->max_bi_anchored_width;
+    }
     std::vector<FullLit> fulls;
     for (unsigned i = 0; i < elements; i++) {
         unsigned f = flags ? flags[i] : 0;
@@ -911,16 +1198,39 @@ int hsb_compile_lit_multi(const char *const *expressions, const unsigned *flags,
         fl.nocase = (f & HSB_FLAG_CASELESS) != 0;
         fl.report = ids ? ids[i] : 0;
         fl.single = (f & HSB_FLAG_SINGLEMATCH) != 0;
+        if (ext) {
+            const hsb_lit_ext &e = ext[i];
+            fl.group = e.group;
+            fl.check_groups = (e.flags & HSB_EXT_CHECK_GROUPS) != 0;
+            fl.want_squash = (e.flags & HSB_EXT_SQUASH_GROUP) != 0;
+            fl.quiet = (e.flags & HSB_EXT_QUIET) != 0;
+            for (unsigned k = 0; k < e.look_count; k++) {
+                Look l{};
+                l.offset = e.look[k].offset;
+                l.is_class = e.look[k].cls != nullptr;
+                l.andm = e.look[k].and_mask;
+                l.cmpm = e.look[k].cmp_mask;
+                l.neg = e.look[k].negate;
+                if (l.is_class) std::memcpy(l.cls, e.look[k].cls, 32);
+                fl.look.push_back(l);
+            }
+        }
         fulls.push_back(fl);
     }
     std::vector<u8> image;
-    int rv = build(fulls, opt, image, err);
+    int rv = build(fulls, opt, bx, image, err);
     if (rv != HSB_LIT_SUCCESS) return fail(err);
     void *mem = nullptr;
     if (posix_memalign(&mem, 64, image.size())) return fail("out of memory");
     std::memcpy(mem, image.data(), image.size());
     *db = (hs_database_t *)mem;
     return HSB_LIT_SUCCESS;
+}
+
+int hsb_compile_lit_multi(const char *const *expressions, const unsigned *flags, const unsigned *ids,
+                          const size_t *lens, unsigned elements, unsigned mode,
+                          const hsb_lit_options *options, hs_database_t **db, char **error) {
+    return hsb_compile_lit_multi_ext(expressions, flags, ids, lens, nullptr, elements, mode, options, nullptr, db, error);
 }
 
 void hsb_free_database(hs_database_t *db) { std::free(db); }

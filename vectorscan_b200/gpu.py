@@ -73,6 +73,8 @@ def lib():
         L.hs_gpu_host_alloc.restype = vp
         L.hs_gpu_host_free.argtypes = [vp]
         L.hs_gpu_set_option.argtypes = [vp, C.c_char_p, C.c_long]
+        L.hs_gpu_opcode_counts.argtypes = [vp, C.POINTER(C.c_ulonglong), C.c_uint]
+        L.hs_gpu_database_opcodes.argtypes = [vp, C.POINTER(C.c_ulonglong), C.c_uint]
         L.hs_gpu_set_device.argtypes = [C.c_int]
         L.hs_gpu_version.restype = C.c_char_p
         _lib = L
@@ -121,10 +123,27 @@ class Scratch:
         if rv != HS_SUCCESS:
             raise HsGpuError(rv, "hs_gpu_set_option")
 
+    def opcode_counts(self):
+        """Executions per Rose opcode since set_option("count_ops", 1) (test instrumentation)."""
+        out = (C.c_ulonglong * 128)()
+        rv = lib().hs_gpu_opcode_counts(self.ptr, out, 128)
+        if rv != HS_SUCCESS:
+            raise HsGpuError(rv, "hs_gpu_opcode_counts")
+        return list(out)
+
     def stats(self):
         st = Stats()
         lib().hs_gpu_last_stats(self.ptr, C.byref(st))
         return st.as_dict()
+
+
+def database_opcodes(db):
+    """Static histogram of the Rose opcodes in the database's literal/report programs (host only)."""
+    out = (C.c_ulonglong * 128)()
+    rv = lib().hs_gpu_database_opcodes(db.ptr, out, 128)
+    if rv != HS_SUCCESS:
+        raise HsGpuError(rv, "hs_gpu_database_opcodes")
+    return list(out)
 
 
 def alloc_scratch(db):

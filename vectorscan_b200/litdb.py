@@ -21,6 +21,22 @@ class LitOptions(C.Structure):
                 ("teddy_masks", C.c_int), ("no_flood", C.c_int)]
 
 
+class LitLook(C.Structure):
+    _fields_ = [("offset", C.c_int), ("and_mask", C.c_ubyte), ("cmp_mask", C.c_ubyte), ("negate", C.c_ubyte),
+                ("reserved", C.c_ubyte), ("cls", C.c_void_p)]
+
+
+class LitExt(C.Structure):
+    _fields_ = [("look", C.POINTER(LitLook)), ("look_count", C.c_uint), ("group", C.c_uint), ("flags", C.c_uint)]
+
+
+class LitBuildExt(C.Structure):
+    _fields_ = [("included_jump", C.c_int), ("target_avx512", C.c_int), ("groups_off", C.c_ulonglong),
+                ("max_bi_anchored_width", C.c_uint)]
+
+
+EXT_CHECK_GROUPS, EXT_SQUASH_GROUP, EXT_QUIET = 1, 2, 4
+
 _lib = None
 
 
@@ -35,6 +51,11 @@ def lib():
                                             C.POINTER(C.c_size_t), C.c_uint, C.c_uint, C.POINTER(LitOptions),
                                             C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
         L.hsb_compile_lit_multi.restype = C.c_int
+        L.hsb_compile_lit_multi_ext.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_uint), C.POINTER(C.c_uint),
+                                                C.POINTER(C.c_size_t), C.POINTER(LitExt), C.c_uint, C.c_uint,
+                                                C.POINTER(LitOptions), C.POINTER(LitBuildExt),
+                                                C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+        L.hsb_compile_lit_multi_ext.restype = C.c_int
         L.hsb_compile_regex_multi.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_uint), C.POINTER(C.c_uint), C.c_uint,
                                               C.c_uint, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
         L.hsb_compile_regex_multi.restype = C.c_int
@@ -123,8 +144,11 @@ class Database:
 
 
 def compile_lit_multi(literals, flags=None, ids=None, mode=HS_MODE_BLOCK, engine=ENGINE_AUTO, fdr_domain=0,
-                      fdr_stride=0, teddy_masks=0, no_flood=0):
-    """literals: list of bytes. Returns Database. Same argument meaning as hs_compile_lit_multi."""
+                      fdr_stride=0, teddy_masks=0, no_flood=0, ext=None, included_jump=0, target_avx512=0,
+                      groups_off=0, max_bi_anchored_width=0):
+    """literals: list of bytes. Returns Database. Same argument meaning as hs_compile_lit_multi.
+    ext: optional per-literal dicts {"look": [(offset, and, cmp, negate) | (offset, class_bitmap32)], "group": g,
+    "flags": EXT_*} (include/hs_litdb.h, hsb_lit_ext); the remaining keywords are hsb_lit_build_ext."""
     n = len(literals)
     lits = [bytes(x) for x in literals]
     arr = (C.c_char_p * n)(*lits)
@@ -132,8 +156,32 @@ def compile_lit_multi(literals, flags=None, ids=None, mode=HS_MODE_BLOCK, engine
     fl = (C.c_uint * n)(*(flags if flags is not None else [0] * n))
     idv = (C.c_uint * n)(*(ids if ids is not None else list(range(n))))
     opt = LitOptions(engine, fdr_domain, fdr_stride, teddy_masks, no_flood)
+    keep = []
+    extv = None
+    if ext is not None:
+        extv = (LitExt * n)()
+        for i, e in enumerate(ext):
+            e = e or {}
+            look = e.get("look", [])
+            if look:
+                lv = (LitLook * len(look))()
+                for k, le in enumerate(look):
+                    lv[k].offset = le[0]
+                    if len(le) == 2:
+                        cb = C.create_string_buffer(bytes(le[1]), 32)
+                        keep.append(cb)
+                        lv[k].cls = C.cast(cb, C.c_void_p)
+                    else:
+                        lv[k].and_mask, lv[k].cmp_mask, lv[k].negate = le[1], le[2], 1 if le[3] else 0
+                keep.append(lv)
+                extv[i].look = lv
+                extv[i].look_count = len(look)
+            extv[i].group = e.get("group", 0)
+            extv[i].flags = e.get("flags", 0)
+    bx = LitBuildExt(included_jump, target_avx512, groups_off, max_bi_anchored_width)
     db, err = C.c_void_p(), C.c_void_p()
-    rv = lib().hsb_compile_lit_multi(arr, fl, idv, lens, n, mode, C.byref(opt), C.byref(db), C.byref(err))
+    rv = lib().hsb_compile_lit_multi_ext(arr, fl, idv, lens, extv, n, mode, C.byref(opt), C.byref(bx), C.byref(db),
+                                         C.byref(err))
     if rv != 0:
         msg = C.string_at(err).decode() if err else "error"
         if err:
