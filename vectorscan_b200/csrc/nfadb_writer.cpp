@@ -762,16 +762,12 @@ int emit_sheng(const Dfa &d, const u8 *reach_map, const std::vector<u32> &progra
 
 }  // namespace
 
-namespace hsb_nfadb {
+namespace {
+using hsb_nfadb::Pattern;
+struct Parsed { Glushkov g; Glushkov::Info info; bool anchored, eod; };
 
-int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &image, std::string &err) {
-    if (engine > HSB_REGEX_ENGINE_SHENG) { err = "unknown engine"; return HSB_LIT_COMPILER_ERROR; }
-    if (pats.empty()) { err = "no expressions"; return HSB_LIT_COMPILER_ERROR; }
-    // ---- 1. parse every pattern, build one automaton -------------------------------------------------
-    Automaton am;
-    bool any_unanch = false, any_anch = false;
-    struct Parsed { Glushkov g; Glushkov::Info info; bool anchored, eod; };
-    std::vector<Parsed> parsed;
+// parse every pattern of the set (the writer's dialect: classes, groups, alternation, * + ? {m,n}, ^, trailing \z)
+int parse_all(const std::vector<Pattern> &pats, std::vector<Parsed> &parsed, std::string &err) {
     for (size_t pi = 0; pi < pats.size(); pi++) {
         const Pattern &p = pats[pi];
         if (p.flags & ~(HSB_FLAG_CASELESS | HSB_FLAG_DOTALL)) {
@@ -801,12 +797,20 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
             err = "expression " + std::to_string(pi) + ": matches the empty string (not supported)";
             return HSB_LIT_COMPILER_ERROR;
         }
-        (anchored ? any_anch : any_unanch) = true;
         parsed.push_back(std::move(pr));
     }
-    size_t total = (any_unanch ? 1 : 0) + (any_anch ? 1 : 0);
-    for (auto &pr : parsed) total += pr.g.cls.size();
-    if (total > MAX_STATES) { err = "pattern set too large for one LimEx NFA (" + std::to_string(total) + " states)"; return HSB_LIT_COMPILER_ERROR; }
+    return HSB_LIT_SUCCESS;
+}
+
+// one Glushkov automaton for the patterns `members` (indices into parsed); report_of holds GLOBAL pattern index + 1.
+// Returns false when the automaton needs more than MAX_STATES states.
+bool make_automaton(const std::vector<Parsed> &parsed, const std::vector<u32> &members, Automaton &am, size_t &total) {
+    bool any_unanch = false, any_anch = false;
+    for (u32 pi : members) (parsed[pi].anchored ? any_anch : any_unanch) = true;
+    total = (any_unanch ? 1 : 0) + (any_anch ? 1 : 0);
+    for (u32 pi : members) total += parsed[pi].g.cls.size();
+    if (total > MAX_STATES) return false;
+    am = Automaton();
     am.n_states = (u32)total;
     am.reach_of.assign(total, CharSet());
     am.succ.assign(total, StateSet());
@@ -821,22 +825,44 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
         am.init_ds.set(st_ds);
     }
     if (any_anch) am.init.set(st_anch);
-    for (size_t pi = 0; pi < parsed.size(); pi++) {
+    for (u32 pi : members) {
         const Parsed &pr = parsed[pi];
         const u32 base = next;
         const u32 n = (u32)pr.g.cls.size();
         for (u32 p = 0; p < n; p++) {
             am.reach_of[base + p] = pr.g.cls[p];
             for (u32 q = 0; q < n; q++) if (pr.g.follow[p].test(q)) am.succ[base + p].set(base + q);
-            if (pr.info.last.test(p)) (pr.eod ? am.report_eod_of : am.report_of)[base + p] = (u32)pi + 1;
+            if (pr.info.last.test(p)) (pr.eod ? am.report_eod_of : am.report_of)[base + p] = pi + 1;
             if (pr.eod) am.any_eod = true;
             if (pr.info.first.test(p)) am.succ[pr.anchored ? st_anch : st_ds].set(base + p);
         }
         am.min_width = std::min(am.min_width, pr.info.min_len);
         next += n;
     }
+    return true;
+}
 
-    // ---- 2. LimEx model: shifts + exceptions ----------------------------------------------------------
+// reach table: distinct per-byte masks
+bool reach_table(const Automaton &am, std::vector<StateSet> &reach_rows, u8 *reach_map) {
+    reach_rows.clear();
+    std::map<std::string, u32> seen;
+    for (u32 c = 0; c < 256; c++) {
+        StateSet row;
+        for (u32 s = 0; s < am.n_states; s++) if (am.reach_of[s].test(c)) row.set(s);
+        const std::string key = row.to_string();
+        auto it = seen.find(key);
+        if (it == seen.end()) { it = seen.emplace(key, (u32)reach_rows.size()).first; reach_rows.push_back(row); }
+        reach_map[c] = (u8)it->second;
+    }
+    return reach_rows.size() <= 256;
+}
+
+// LimEx model (shifts + exceptions) and layout of one automaton: struct NFA + LimExNFA<bits> + tables, relative to the
+// engine's own start.  program_of[global pattern index] = Rose report program offset.
+int emit_limex(const Automaton &am, const std::vector<StateSet> &reach_rows, const u8 *reach_map,
+               const std::vector<u32> &program_of, Buf &eng, u32 &stream_state, u32 &scratch_state, std::string &err) {
+    (void)err;
+    const size_t n_pats = program_of.size();
     u32 type = nfa::LIMEX_512;
     for (u32 t = 0; t < 6; t++) if (limex::layout(t).bits >= am.n_states) { type = t; break; }
     const limex::Layout L = limex::layout(type);
@@ -868,63 +894,6 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
         if (am.report_of[s]) { exception_mask.set(s); accept_mask.set(s); }
         if (am.report_eod_of[s]) accept_eod_mask.set(s);  // EOD accepts fire from the accept table only
     }
-    // reach table: distinct per-byte masks
-    std::vector<StateSet> reach_rows;
-    u8 reach_map[256];
-    {
-        std::map<std::string, u32> seen;
-        for (u32 c = 0; c < 256; c++) {
-            StateSet row;
-            for (u32 s = 0; s < am.n_states; s++) if (am.reach_of[s].test(c)) row.set(s);
-            const std::string key = row.to_string();
-            auto it = seen.find(key);
-            if (it == seen.end()) { it = seen.emplace(key, (u32)reach_rows.size()).first; reach_rows.push_back(row); }
-            reach_map[c] = (u8)it->second;
-        }
-        if (reach_rows.size() > 256) { err = "internal: reach table overflow"; return HSB_LIT_COMPILER_ERROR; }
-    }
-
-    // ---- 3. Rose blob: header, dedupe keys, report programs, NfaInfo, NFA ------------------------------
-    Buf rose;
-    rose.grow(rose::SIZE);
-    rose.align(CACHELINE);
-    // one dedupe key per distinct report id: two positions of a pattern may accept at the same offset
-    std::map<u32, u32> dkeys;
-    for (auto &p : pats) if (!dkeys.count(p.id)) { u32 k = (u32)dkeys.size(); dkeys[p.id] = k; }
-    const u32 inv_dkey_off = (u32)rose.grow(4 * dkeys.size());
-    for (auto &d : dkeys) wr32(rose.at(inv_dkey_off), 4 * d.second, d.first);
-    rose.align(op::ALIGN);
-    std::vector<u32> program_of(pats.size());
-    for (size_t pi = 0; pi < pats.size(); pi++) {
-        rose.align(op::ALIGN);
-        const u32 o = (u32)rose.grow(op::dedupe_and_report::SIZE + op::SIZE_1);
-        program_of[pi] = o;
-        wr8(rose.at(o), 0, op::DEDUPE_AND_REPORT);
-        wr8(rose.at(o), op::dedupe_and_report::quash_som, 0);
-        wr32(rose.at(o), op::dedupe_and_report::dkey, dkeys[pats[pi].id]);
-        wr32(rose.at(o), op::dedupe_and_report::onmatch, pats[pi].id);
-        wr32(rose.at(o), op::dedupe_and_report::offset_adjust, 0);
-        wr32(rose.at(o), op::dedupe_and_report::fail_jump, (u32)op::dedupe_and_report::SIZE);
-        wr8(rose.at(o + op::dedupe_and_report::SIZE), 0, op::END);
-    }
-    rose.align(4);
-    const u32 nfa_info_off = (u32)rose.grow(nfainfo::SIZE);
-    rose.align(CACHELINE);
-    const u32 nfa_off = (u32)rose.size();
-
-    // the engine, relative to its own start
-    Buf eng;
-    u32 stream_state = 0, scratch_state = 0;
-    if (engine != HSB_REGEX_ENGINE_LIMEX) {
-        Dfa dfa;
-        if (!determinise(am, reach_rows, dfa, 4 * (mcclellan::STATE_MASK + 1))) { err = "DFA too large for a McClellan engine"; return HSB_LIT_COMPILER_ERROR; }
-        minimise(dfa);
-        const int rv = engine == HSB_REGEX_ENGINE_SHENG
-                           ? emit_sheng(dfa, reach_map, program_of, am.min_width, eng, stream_state, err)
-                           : emit_mcclellan(dfa, reach_map, program_of, engine == HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN, am.min_width, eng, stream_state, err);
-        if (rv != HSB_LIT_SUCCESS) return rv;
-        scratch_state = stream_state;
-    } else {
     eng.grow(nfa::SIZE + L.SIZE);
     const size_t lx = nfa::SIZE;  // LimExNFA base inside eng
     // reach table right behind the struct (get_reach_table)
@@ -959,8 +928,8 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
     }
     // report lists for the exceptions: {program offset, MO_INVALID_IDX} per pattern
     eng.align(4);
-    std::vector<u32> report_list_of(pats.size());
-    for (size_t pi = 0; pi < pats.size(); pi++) {
+    std::vector<u32> report_list_of(n_pats);
+    for (size_t pi = 0; pi < n_pats; pi++) {
         const size_t o = eng.grow(8);
         wr32(eng.at(o), 0, program_of[pi]);
         wr32(eng.at(o), 4, 0xffffffffu);
@@ -1029,7 +998,75 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
         wr8(lp, L.shiftAmount + k, (u8)shifts[k]);
     }
     wr32(lp, L.shiftCount, (u32)shifts.size());
+    return HSB_LIT_SUCCESS;
+}
+
+// one engine for one automaton: LimEx, or the determinised McClellan / Sheng form
+int emit_engine(const Automaton &am, unsigned engine, const std::vector<u32> &program_of, u32 dfa_state_limit, Buf &eng,
+                u32 &stream_state, u32 &scratch_state, std::string &err) {
+    std::vector<StateSet> reach_rows;
+    u8 reach_map[256];
+    if (!reach_table(am, reach_rows, reach_map)) { err = "internal: reach table overflow"; return HSB_LIT_COMPILER_ERROR; }
+    if (engine == HSB_REGEX_ENGINE_LIMEX) return emit_limex(am, reach_rows, reach_map, program_of, eng, stream_state, scratch_state, err);
+    Dfa dfa;
+    if (!determinise(am, reach_rows, dfa, dfa_state_limit)) { err = "DFA too large for a McClellan engine"; return HSB_LIT_COMPILER_ERROR; }
+    minimise(dfa);
+    const int rv = engine == HSB_REGEX_ENGINE_SHENG
+                       ? emit_sheng(dfa, reach_map, program_of, am.min_width, eng, stream_state, err)
+                       : emit_mcclellan(dfa, reach_map, program_of, engine == HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN, am.min_width, eng, stream_state, err);
+    scratch_state = stream_state;
+    return rv;
+}
+
+}  // namespace
+
+namespace hsb_nfadb {
+
+int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &image, std::string &err) {
+    if (engine > HSB_REGEX_ENGINE_SHENG) { err = "unknown engine"; return HSB_LIT_COMPILER_ERROR; }
+    if (pats.empty()) { err = "no expressions"; return HSB_LIT_COMPILER_ERROR; }
+    // ---- 1. parse every pattern, build one automaton -------------------------------------------------
+    std::vector<Parsed> parsed;
+    if (parse_all(pats, parsed, err) != HSB_LIT_SUCCESS) return HSB_LIT_COMPILER_ERROR;
+    Automaton am;
+    std::vector<u32> everyone(pats.size());
+    for (u32 i = 0; i < pats.size(); i++) everyone[i] = i;
+    size_t total = 0;
+    if (!make_automaton(parsed, everyone, am, total)) { err = "pattern set too large for one LimEx NFA (" + std::to_string(total) + " states)"; return HSB_LIT_COMPILER_ERROR; }
+
+    // ---- 3. Rose blob: header, dedupe keys, report programs, NfaInfo, NFA ------------------------------
+    Buf rose;
+    rose.grow(rose::SIZE);
+    rose.align(CACHELINE);
+    // one dedupe key per distinct report id: two positions of a pattern may accept at the same offset
+    std::map<u32, u32> dkeys;
+    for (auto &p : pats) if (!dkeys.count(p.id)) { u32 k = (u32)dkeys.size(); dkeys[p.id] = k; }
+    const u32 inv_dkey_off = (u32)rose.grow(4 * dkeys.size());
+    for (auto &d : dkeys) wr32(rose.at(inv_dkey_off), 4 * d.second, d.first);
+    rose.align(op::ALIGN);
+    std::vector<u32> program_of(pats.size());
+    for (size_t pi = 0; pi < pats.size(); pi++) {
+        rose.align(op::ALIGN);
+        const u32 o = (u32)rose.grow(op::dedupe_and_report::SIZE + op::SIZE_1);
+        program_of[pi] = o;
+        wr8(rose.at(o), 0, op::DEDUPE_AND_REPORT);
+        wr8(rose.at(o), op::dedupe_and_report::quash_som, 0);
+        wr32(rose.at(o), op::dedupe_and_report::dkey, dkeys[pats[pi].id]);
+        wr32(rose.at(o), op::dedupe_and_report::onmatch, pats[pi].id);
+        wr32(rose.at(o), op::dedupe_and_report::offset_adjust, 0);
+        wr32(rose.at(o), op::dedupe_and_report::fail_jump, (u32)op::dedupe_and_report::SIZE);
+        wr8(rose.at(o + op::dedupe_and_report::SIZE), 0, op::END);
     }
+    rose.align(4);
+    const u32 nfa_info_off = (u32)rose.grow(nfainfo::SIZE);
+    rose.align(CACHELINE);
+    const u32 nfa_off = (u32)rose.size();
+
+    // the engine, relative to its own start
+    Buf eng;
+    u32 stream_state = 0, scratch_state = 0;
+    if (emit_engine(am, engine, program_of, 4 * (mcclellan::STATE_MASK + 1), eng, stream_state, scratch_state, err) != HSB_LIT_SUCCESS)
+        return HSB_LIT_COMPILER_ERROR;
 
     const size_t nfa_at = rose.grow(eng.size());
     std::memcpy(rose.at(nfa_at), eng.b.data(), eng.size());
