@@ -114,6 +114,16 @@ int hsb_compile_regex_multi(const char *const *expressions, const unsigned *flag
 int hsb_compile_regex_multi_ex(const char *const *expressions, const unsigned *flags, const unsigned *ids,
                                unsigned elements, unsigned mode, unsigned engine, hs_database_t **db,
                                char **error);
+/* The same front end for LARGE regex sets: a full-Rose database (RoseEngine.runtimeImpl = ROSE_RUNTIME_FULL_ROSE) whose
+ * patterns are spread over many OUTFIX engines -- the shape hs_compile_multi gives patterns without usable literals
+ * (src/rose/rose_build_bytecode.cpp:3608-3890, outfix queues :2078-2116).  `engine` = HSB_REGEX_ENGINE_MCCLELLAN[_SHERMAN]:
+ * patterns join a group while its DFA stays within `dfa_states` states (0 = 1024); patterns whose own DFA is larger
+ * become LimEx engines, as the reference falls back when DFA construction hits its limit.  HSB_REGEX_ENGINE_LIMEX: every
+ * group is a LimEx NFA of <= 512 states.  At most 256 engines; no \z patterns.  Scanned by the unmodified reference
+ * runtime through roseBlockExec -> blockInitSufPQ -> roseCatchUpTo (src/rose/block.c:345-422, src/rose/catchup.c). */
+int hsb_compile_regex_rose(const char *const *expressions, const unsigned *flags, const unsigned *ids,
+                           unsigned elements, unsigned mode, unsigned engine, unsigned dfa_states,
+                           hs_database_t **db, char **error);
 void hsb_free_database(hs_database_t *db);
 void hsb_free_error(char *error);
 

@@ -67,6 +67,9 @@ struct scan_state {
     u8 *dedupe; u32 dkeys; u64 dedupe_offset; /* dedupe log for the current report offset */
     op_match_cb cb; void *ctx;
     int terminated, error;
+    /* multi-outfix catch-up (rose/catchup.c): engine reports are gathered, then replayed in offset order */
+    int defer; u32 cur_queue;
+    struct deferred { u64 to; u32 queue, prog, seq; } *ev; size_t n_ev, cap_ev;
 };
 
 /* roseDeliverReport + the dedupe test of dedupeCatchup for external reports without SOM */
@@ -132,6 +135,15 @@ static int check_mask_n(const struct scan_state *s, const u8 *and_m, const u8 *c
 /* roseRunProgram_l.  `end` = offset one past the literal's last byte (lit_offset_adjust = 1).
  * Returns 0 to continue, -1 to stop the scan. */
 static int run_program(struct scan_state *s, u32 prog, u64 end) {
+    if (s->defer) {
+        if (s->n_ev == s->cap_ev) {
+            s->cap_ev = s->cap_ev ? 2 * s->cap_ev : 256;
+            s->ev = realloc(s->ev, s->cap_ev * sizeof(*s->ev));
+        }
+        s->ev[s->n_ev] = (struct deferred){end, s->cur_queue, prog, (u32)s->n_ev};
+        s->n_ev++;
+        return 0;
+    }
     const u8 *pc = s->rose + prog;
     int work_done = 0;
     for (;;) {
@@ -467,16 +479,57 @@ static int sheng_scan(struct scan_state *s, const u8 *nfa) {
     return 0;
 }
 
-/* hs_scan for block-mode pure-literal and single-outfix (LimEx, McClellan or Sheng) databases.  `db` = in-memory hs_database_t. */
+static int deferred_cmp(const void *a, const void *b) {
+    const struct deferred *x = a, *y = b;
+    if (x->to != y->to) return x->to < y->to ? -1 : 1;
+    if (x->queue != y->queue) return x->queue < y->queue ? -1 : 1;
+    return x->seq < y->seq ? -1 : x->seq > y->seq;
+}
+
+static void engine_scan(struct scan_state *s, const u8 *nfa) {
+    if (nfa[NFA_TYPE] == 6 || nfa[NFA_TYPE] == 7) mcclellan_scan(s, nfa);
+    else if (nfa[NFA_TYPE] == 17) sheng_scan(s, nfa);
+    else limex_scan(s, nfa);
+}
+
+/* roseBlockExec for a database of outfix engines only (rose/block.c:345-422): blockInitSufPQ (rose/catchup.c:612-672)
+ * starts every outfix whose NFA.minWidth the block satisfies (nfaRevAccelCheck, nfa/nfa_rev_api.h:135-155) and
+ * roseCatchUpTo(length) delivers their reports in offset order (queue order inside one offset) through the report
+ * programs, which share one dedupe log per offset (dedupeCatchup). */
+static void outfixes_exec(struct scan_state *s, const u8 *rose) {
+    const u32 q0 = rd32(rose + 396), q1 = rd32(rose + 400); /* outfixBeginQueue, outfixEndQueue */
+    s->defer = 1;
+    for (u32 qi = q0; qi < q1 && !s->error; qi++) {
+        const u8 *nfa = rose + rd32(rose + rd32(rose + R_NFA_INFO) + 20 * qi + NI_NFA_OFF);
+        if (rd32(nfa + 36) > s->len) continue; /* NFA.minWidth */
+        s->cur_queue = qi;
+        engine_scan(s, nfa);
+    }
+    s->defer = 0;
+    qsort(s->ev, s->n_ev, sizeof(*s->ev), deferred_cmp);
+    for (size_t i = 0; i < s->n_ev && !s->error; i++)
+        if (run_program(s, s->ev[i].prog, s->ev[i].to) < 0) break;
+    free(s->ev);
+    s->ev = NULL;
+}
+
+/* hs_scan for block-mode pure-literal, single-outfix and outfix-only full-Rose (LimEx, McClellan or Sheng) databases.  `db` = in-memory hs_database_t. */
 int op_scan(const void *db, const char *data, unsigned length, op_match_cb cb, void *ctx) {
     const u8 *d = (const u8 *)db;
     if (!d || !data || rd32(d + DB_MAGIC_OFF) != 0xdbdbdbdbu) return HS_INVALID;
     if (rd32(d + DB_VERSION_OFF) != ((5u << 24) | (4u << 16) | (11u << 8))) return HS_DB_VERSION_ERROR;
     const u8 *rose = d + rd32(d + DB_BYTECODE_OFF);
     if (rd32(rose + R_MODE) != 1) return HS_DB_MODE_ERROR;
-    if ((rose[R_RUNTIME_IMPL] != 1 && rose[R_RUNTIME_IMPL] != 2) || rose[R_HAS_SOM] || rd32(rose + R_CKEY_COUNT) || rd32(rose + R_BOUNDARY) ||
+    if (rose[R_RUNTIME_IMPL] > 2 || rose[R_HAS_SOM] || rd32(rose + R_CKEY_COUNT) || rd32(rose + R_BOUNDARY) ||
         rd32(rose + R_BOUNDARY + 4) || rd32(rose + R_BOUNDARY + 8))
         return HS_ARCH_ERROR; /* outside the restated path */
+    if (rose[R_RUNTIME_IMPL] == 0) {
+        /* full Rose: only the outfix-only shape is restated (no literal matchers, roles, leftfixes, EOD program) */
+        if (rd32(rose + 88) || rd32(rose + 92) || rd32(rose + R_FMATCHER) || rd32(rose + 100) || rd32(rose + 104) ||
+            rd32(rose + 84) || rd32(rose + 184) || rd32(rose + 64) || rd32(rose + 152) ||
+            rd32(rose + 404) != rd32(rose + 156) || rd32(rose + 400) != rd32(rose + 156) || rd32(rose + 408) != 0xffffffffu)
+            return HS_ARCH_ERROR;
+    }
     if (rd32(rose + R_MIN_WIDTH) > length) return HS_SUCCESS;
     if (!length) return HS_SUCCESS;
     if (rd32(rose + R_MIN_WIDTH_EXCL) > length) return HS_SUCCESS;
@@ -489,12 +542,8 @@ int op_scan(const void *db, const char *data, unsigned length, op_match_cb cb, v
     s.exhausted = calloc(s.ekeys / 8 + 2, 1);
     s.dedupe = calloc(s.dkeys / 8 + 2, 1);
     s.dedupe_offset = ~0ull;
-    if (rose[R_RUNTIME_IMPL] == 2) {
-        const u8 *nfa = rose + rd32(rose + rd32(rose + R_NFA_INFO) + NI_NFA_OFF);
-        if (nfa[NFA_TYPE] == 6 || nfa[NFA_TYPE] == 7) mcclellan_scan(&s, nfa);
-        else if (nfa[NFA_TYPE] == 17) sheng_scan(&s, nfa);
-        else limex_scan(&s, nfa);
-    }
+    if (rose[R_RUNTIME_IMPL] == 0) outfixes_exec(&s, rose);
+    else if (rose[R_RUNTIME_IMPL] == 2) engine_scan(&s, rose + rd32(rose + rd32(rose + R_NFA_INFO) + NI_NFA_OFF));
     else hwlm_exec(&s, rose + rd32(rose + R_FMATCHER));
     free(s.exhausted); free(s.dedupe);
     if (s.error) return HS_UNKNOWN_ERROR;

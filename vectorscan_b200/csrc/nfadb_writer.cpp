@@ -366,6 +366,7 @@ struct Glushkov {
 namespace hsb_nfadb {
 struct Pattern { std::string expr; unsigned flags; unsigned id; };
 int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<hsb::u8> &image, std::string &err);
+int build_rose(const std::vector<Pattern> &pats, unsigned engine, hsb::u32 dfa_states, std::vector<hsb::u8> &image, std::string &err);
 }
 
 namespace {
@@ -1144,6 +1145,200 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
     return HSB_LIT_SUCCESS;
 }
 
+
+// ---- full-Rose database of outfix engines only ------------------------------------------------------------------
+// The shape the reference compiler gives a pattern set without usable literals: runtimeImpl = ROSE_RUNTIME_FULL_ROSE, no
+// literal matchers, no roles; every group of patterns is one OUTFIX engine on its own queue [outfixBeginQueue,
+// outfixEndQueue).  At scan time roseBlockExec (src/rose/block.c:345-422) starts every outfix (blockInitSufPQ,
+// src/rose/catchup.c:612-672: MQE_START, MQE_TOP, MQE_END), and roseCatchUpTo (catchup.h:128-167, roseCatchUpAll
+// catchup.c:560+) interleaves their matches by offset through the report programs.  Followed for the layout:
+// rose_build_bytecode.cpp:2078-2116 (state space per engine), :3608-3890 (header), rose_build_scatter.cpp:66-97
+// (state_init plan: the active leaf array is cleared before every block).
+// Grouping: patterns join the current group while its determinised automaton stays within `dfa_states` states; a pattern
+// whose own DFA is larger goes to a LimEx group (<= 512 NFA states) -- the reference's own fallback when McClellan
+// construction fails (src/nfagraph/ng_limex.cpp / ng_mcclellan.cpp state limits).
+int build_rose(const std::vector<Pattern> &pats, unsigned engine, u32 dfa_states, std::vector<u8> &image, std::string &err) {
+    if (engine != HSB_REGEX_ENGINE_LIMEX && engine != HSB_REGEX_ENGINE_MCCLELLAN && engine != HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN) {
+        err = "outfix engines are LimEx or McClellan";
+        return HSB_LIT_COMPILER_ERROR;
+    }
+    if (pats.empty()) { err = "no expressions"; return HSB_LIT_COMPILER_ERROR; }
+    if (!dfa_states) dfa_states = 1024;
+    if (dfa_states > mcclellan::STATE_MASK) dfa_states = mcclellan::STATE_MASK;
+    std::vector<Parsed> parsed;
+    if (parse_all(pats, parsed, err) != HSB_LIT_SUCCESS) return HSB_LIT_COMPILER_ERROR;
+    for (size_t i = 0; i < parsed.size(); i++)
+        if (parsed[i].eod) { err = "expression " + std::to_string(i) + ": \\z needs an EOD program (not written for multi-engine databases)"; return HSB_LIT_COMPILER_ERROR; }
+
+    struct Group { std::vector<u32> members; unsigned engine; };
+    std::vector<Group> groups;
+    auto dfa_fits = [&](const std::vector<u32> &members) {
+        Automaton am;
+        size_t total = 0;
+        if (!make_automaton(parsed, members, am, total)) return false;
+        std::vector<StateSet> rows;
+        u8 map[256];
+        if (!reach_table(am, rows, map)) return false;
+        Dfa d;
+        return determinise(am, rows, d, dfa_states);
+    };
+    std::vector<u32> for_limex;
+    if (engine == HSB_REGEX_ENGINE_LIMEX) {
+        for (u32 i = 0; i < pats.size(); i++) for_limex.push_back(i);
+    } else {
+        std::vector<u32> cur;
+        for (u32 i = 0; i < pats.size(); i++) {
+            cur.push_back(i);
+            if (dfa_fits(cur)) continue;
+            cur.pop_back();
+            if (!cur.empty()) { groups.push_back({cur, engine}); cur.clear(); }
+            cur.push_back(i);
+            if (!dfa_fits(cur)) { cur.clear(); for_limex.push_back(i); }
+        }
+        if (!cur.empty()) groups.push_back({cur, engine});
+    }
+    {
+        std::vector<u32> cur;
+        size_t states = 2;
+        for (u32 i : for_limex) {
+            const size_t n = parsed[i].g.cls.size();
+            if (n + 2 > MAX_STATES) { err = "expression " + std::to_string(i) + " needs more than 512 NFA states"; return HSB_LIT_COMPILER_ERROR; }
+            if (states + n > MAX_STATES) { groups.push_back({cur, HSB_REGEX_ENGINE_LIMEX}); cur.clear(); states = 2; }
+            cur.push_back(i);
+            states += n;
+        }
+        if (!cur.empty()) groups.push_back({cur, HSB_REGEX_ENGINE_LIMEX});
+    }
+    const u32 N = (u32)groups.size();
+    if (N > 256) { err = "more than 256 engines (the flat multibit model of the active array)"; return HSB_LIT_COMPILER_ERROR; }
+
+    Buf rose;
+    rose.grow(rose::SIZE);
+    rose.align(CACHELINE);
+    std::map<u32, u32> dkeys;
+    for (auto &p : pats) if (!dkeys.count(p.id)) { u32 k = (u32)dkeys.size(); dkeys[p.id] = k; }
+    const u32 inv_dkey_off = (u32)rose.grow(4 * dkeys.size());
+    for (auto &d : dkeys) wr32(rose.at(inv_dkey_off), 4 * d.second, d.first);
+    rose.align(op::ALIGN);
+    std::vector<u32> program_of(pats.size());
+    for (size_t pi = 0; pi < pats.size(); pi++) {
+        rose.align(op::ALIGN);
+        const u32 o = (u32)rose.grow(op::dedupe_and_report::SIZE + op::SIZE_1);
+        program_of[pi] = o;
+        wr8(rose.at(o), 0, op::DEDUPE_AND_REPORT);
+        wr32(rose.at(o), op::dedupe_and_report::dkey, dkeys[pats[pi].id]);
+        wr32(rose.at(o), op::dedupe_and_report::onmatch, pats[pi].id);
+        wr32(rose.at(o), op::dedupe_and_report::fail_jump, (u32)op::dedupe_and_report::SIZE);
+        wr8(rose.at(o + op::dedupe_and_report::SIZE), 0, op::END);
+    }
+    rose.align(4);
+    const u32 nfa_info_off = (u32)rose.grow((size_t)nfainfo::SIZE * N);
+    // state layout: status byte, active leaf multibit of N queues, then every engine's stream state
+    const u32 leaf_off = 1, leaf_bytes = mmbit_size(N);
+    u32 cur_state = leaf_off + leaf_bytes;
+    const u32 nfa_state_begin = cur_state;
+    u32 scratch_total = 0, min_width = ~0u;
+    for (u32 qi = 0; qi < N; qi++) {
+        Automaton am;
+        size_t total = 0;
+        if (!make_automaton(parsed, groups[qi].members, am, total)) { err = "internal: group too large"; return HSB_LIT_COMPILER_ERROR; }
+        Buf eng;
+        u32 stream_state = 0, scratch_state = 0;
+        if (emit_engine(am, groups[qi].engine, program_of, 4 * (mcclellan::STATE_MASK + 1), eng, stream_state, scratch_state, err) != HSB_LIT_SUCCESS)
+            return HSB_LIT_COMPILER_ERROR;
+        wr32(eng.at(0), nfa::queueIndex, qi);
+        rose.align(CACHELINE);
+        const u32 nfa_off = (u32)rose.grow(eng.size());
+        std::memcpy(rose.at(nfa_off), eng.b.data(), eng.size());
+        u8 *ni = rose.at(nfa_info_off + (size_t)nfainfo::SIZE * qi);
+        wr32(ni, nfainfo::nfaOffset, nfa_off);
+        wr32(ni, nfainfo::stateOffset, cur_state);
+        scratch_total = (u32)round_up(scratch_total, 64);
+        wr32(ni, nfainfo::fullStateOffset, scratch_total);
+        cur_state += stream_state;
+        scratch_total += scratch_state;
+        min_width = std::min(min_width, am.min_width);
+    }
+    rose.align(CACHELINE);
+    // state_init: clear the active leaf array (8-byte stores, then single bytes)
+    u32 plan_u64_off = 0, plan_u64_n = 0, plan_u8_off = 0, plan_u8_n = 0;
+    {
+        u32 b = 0;
+        if (leaf_bytes >= 8) {
+            plan_u64_off = (u32)rose.size();
+            for (; b + 8 <= leaf_bytes; b += 8) {
+                const size_t o = rose.grow(16);  // struct scatter_unit_u64a { u32 offset; u64a val; }
+                wr32(rose.at(o), 0, leaf_off + b);
+                plan_u64_n++;
+            }
+        }
+        if (b < leaf_bytes) {
+            plan_u8_off = (u32)rose.size();
+            for (; b < leaf_bytes; b++) {
+                const size_t o = rose.grow(8);   // struct scatter_unit_u8 { u32 offset; u8 val; }
+                wr32(rose.at(o), 0, leaf_off + b);
+                plan_u8_n++;
+            }
+        }
+    }
+    rose.align(CACHELINE);
+
+    u8 *r = rose.at(0);
+    u8 *so = r + rose::stateOffsets;
+    wr32(so, rose::so::activeLeafArray, leaf_off);
+    wr32(so, rose::so::activeLeafArray_size, leaf_bytes);
+    for (size_t f : {rose::so::activeLeftArray, rose::so::longLitState, rose::so::leftfixLagTable, rose::so::anchorState,
+                     rose::so::groups, rose::so::history, rose::so::exhausted, rose::so::logicalVec, rose::so::combVec,
+                     rose::so::nfaStateBegin})
+        wr32(so, f, nfa_state_begin);
+    wr32(so, rose::so::exhausted_size, mmbit_size(0));
+    wr32(so, rose::so::end, cur_state);
+    // struct scatter_full_plan (src/util/scatter.h:43-52)
+    u8 *sp = r + rose::state_init;
+    wr32(sp, 0, plan_u64_off); wr32(sp, 4, plan_u64_n);
+    wr32(sp, 24, plan_u8_n); wr32(sp, 28, plan_u8_off);
+
+    wr8(r, rose::pureLiteral, 0);
+    wr8(r, rose::runtimeImpl, rose::RUNTIME_FULL_ROSE);
+    wr8(r, rose::hasOutfixesInSmallBlock, 1);
+    wr32(r, rose::mode, MODE_BLOCK);
+    wr32(r, rose::dkeyCount, (u32)dkeys.size());
+    wr32(r, rose::dkeyLogSize, fatbit_size((u32)dkeys.size()));
+    wr32(r, rose::invDkeyOffset, inv_dkey_off);
+    wr32(r, rose::somLocationFatbitSize, fatbit_size(0));
+    wr32(r, rose::stateSize, cur_state);
+    wr32(r, rose::scratchStateSize, (u32)round_up(scratch_total, 64));
+    wr32(r, rose::amatcherMaxBiAnchoredWidth, rose::BOUND_INF);
+    wr32(r, rose::fmatcherMaxBiAnchoredWidth, rose::BOUND_INF);
+    wr32(r, rose::activeArrayCount, N);
+    wr32(r, rose::queueCount, N);
+    wr32(r, rose::activeQueueArraySize, fatbit_size(N));
+    wr32(r, rose::handledKeyFatbitSize, fatbit_size(0));
+    wr32(r, rose::minWidth, min_width);
+    wr32(r, rose::minWidthExcludingBoundaries, min_width);
+    wr32(r, rose::maxBiAnchoredWidth, rose::BOUND_INF);
+    wr32(r, rose::floatingDistance, rose::BOUND_INF);
+    wr32(r, rose::nfaInfoOffset, nfa_info_off);
+    wr32(r, rose::size, (u32)rose.size());
+    wr32(r, rose::delay_fatbit_size, fatbit_size(0));
+    wr32(r, rose::anchored_fatbit_size, fatbit_size(0));
+    wr32(r, rose::outfixBeginQueue, 0);
+    wr32(r, rose::outfixEndQueue, N);
+    wr32(r, rose::leftfixBeginQueue, N);
+    wr32(r, rose::initMpvNfa, 0xffffffffu);
+
+    const size_t bc_off = db::IMAGE_BYTECODE;
+    image.assign(db::SIZE + rose.size(), 0);
+    std::memcpy(image.data() + bc_off, rose.b.data(), rose.size());
+    wr32(image.data(), db::magic, db::MAGIC);
+    wr32(image.data(), db::version, db::VERSION_5_4_11);
+    wr32(image.data(), db::length, (u32)rose.size());
+    wr64(image.data(), db::platform, db::PLATFORM_GENERIC);
+    wr32(image.data(), db::crc32, hsb_crc32c(rose.b.data(), rose.size()));
+    wr32(image.data(), db::bytecode, (u32)bc_off);
+    return HSB_LIT_SUCCESS;
+}
+
 }  // namespace hsb_nfadb
 
 extern "C" int hsb_compile_regex_multi_ex(const char *const *expressions, const unsigned *flags, const unsigned *ids,
@@ -1170,6 +1365,37 @@ extern "C" int hsb_compile_regex_multi_ex(const char *const *expressions, const 
     std::vector<hsb::u8> image;
     std::string err;
     if (hsb_nfadb::build(pats, engine, image, err) != HSB_LIT_SUCCESS) return fail(err);
+    void *mem = nullptr;
+    if (posix_memalign(&mem, 64, image.size())) return fail("out of memory");
+    std::memcpy(mem, image.data(), image.size());
+    *db = (hs_database_t *)mem;
+    return HSB_LIT_SUCCESS;
+}
+
+extern "C" int hsb_compile_regex_rose(const char *const *expressions, const unsigned *flags, const unsigned *ids,
+                                      unsigned elements, unsigned mode, unsigned engine, unsigned dfa_states,
+                                      hs_database_t **db, char **error) {
+    if (error) *error = nullptr;
+    if (!db) return HSB_LIT_COMPILER_ERROR;
+    *db = nullptr;
+    auto fail = [&](const std::string &m) {
+        if (error) {
+            char *p = (char *)std::malloc(m.size() + 1);
+            if (p) std::memcpy(p, m.c_str(), m.size() + 1);
+            *error = p;
+        }
+        return HSB_LIT_COMPILER_ERROR;
+    };
+    if (!expressions || !elements) return fail("invalid parameter: no expressions");
+    if (mode != hsb::MODE_BLOCK) return fail("only HS_MODE_BLOCK databases are written");
+    std::vector<hsb_nfadb::Pattern> pats;
+    for (unsigned i = 0; i < elements; i++) {
+        if (!expressions[i]) return fail("null expression");
+        pats.push_back({expressions[i], flags ? flags[i] : 0, ids ? ids[i] : 0});
+    }
+    std::vector<hsb::u8> image;
+    std::string err;
+    if (hsb_nfadb::build_rose(pats, engine, dfa_states, image, err) != HSB_LIT_SUCCESS) return fail(err);
     void *mem = nullptr;
     if (posix_memalign(&mem, 64, image.size())) return fail("out of memory");
     std::memcpy(mem, image.data(), image.size());

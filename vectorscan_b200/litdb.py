@@ -62,6 +62,9 @@ def lib():
         L.hsb_compile_regex_multi_ex.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_uint), C.POINTER(C.c_uint), C.c_uint,
                                                  C.c_uint, C.c_uint, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
         L.hsb_compile_regex_multi_ex.restype = C.c_int
+        L.hsb_compile_regex_rose.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_uint), C.POINTER(C.c_uint), C.c_uint,
+                                             C.c_uint, C.c_uint, C.c_uint, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+        L.hsb_compile_regex_rose.restype = C.c_int
         L.hsb_free_database.argtypes = [C.c_void_p]
         L.hsb_free_error.argtypes = [C.c_void_p]
         L.hsb_database_size.argtypes = [C.c_void_p, C.POINTER(C.c_size_t)]
@@ -205,6 +208,26 @@ def compile_regex_multi(expressions, flags=None, ids=None, mode=HS_MODE_BLOCK, e
     idv = (C.c_uint * n)(*(ids if ids is not None else list(range(n))))
     db, err = C.c_void_p(), C.c_void_p()
     rv = lib().hsb_compile_regex_multi_ex(arr, fl, idv, n, mode, engine, C.byref(db), C.byref(err))
+    if rv != 0:
+        msg = C.string_at(err).decode() if err else "error"
+        if err:
+            lib().hsb_free_error(err)
+        raise CompileError(msg)
+    return Database(db.value)
+
+
+def compile_regex_rose(expressions, flags=None, ids=None, mode=HS_MODE_BLOCK, engine=ENGINE_MCCLELLAN, dfa_states=0):
+    """Large regex sets: a full-Rose Database whose patterns are spread over many outfix engines (McClellan DFAs of at
+    most dfa_states states, LimEx NFAs for what does not determinise).  include/hs_litdb.h hsb_compile_regex_rose."""
+    n = len(expressions)
+    ex = [e.encode("latin-1") if isinstance(e, str) else bytes(e) for e in expressions]
+    if any(b"\0" in e for e in ex):
+        raise CompileError("NUL byte in expression: write it as \\x00")
+    arr = (C.c_char_p * n)(*ex)
+    fl = (C.c_uint * n)(*(flags if flags is not None else [0] * n))
+    idv = (C.c_uint * n)(*(ids if ids is not None else list(range(n))))
+    db, err = C.c_void_p(), C.c_void_p()
+    rv = lib().hsb_compile_regex_rose(arr, fl, idv, n, mode, engine, dfa_states, C.byref(db), C.byref(err))
     if rv != 0:
         msg = C.string_at(err).decode() if err else "error"
         if err:
