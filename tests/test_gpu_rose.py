@@ -1,0 +1,59 @@
+"""GPU tests (-m gpu) of full-Rose databases of outfix engines (outfix slice): many McClellan / LimEx
+engines on their own queues, every one stepping the whole batch on the device, one report pass, one finalize.  Against
+the unmodified reference runtime (roseBlockExec -> blockInitSufPQ -> roseCatchUpTo), the C restatement and `re`."""
+import random
+
+import pytest
+
+import regen
+from test_gpu_limex import gpu_batch, ref_batch
+from test_gpu_mcclellan import port_batch
+from vectorscan_b200 import gpu, litdb, workloads as W
+
+pytestmark = pytest.mark.gpu
+
+
+def brute_batch(ex, fl, ids, bufs):
+    out = []
+    for bi, b in enumerate(bufs):
+        out += [(bi, i, t) for (i, t) in regen.brute_force(ex, fl, ids, b)]
+    return sorted(out, key=lambda x: (x[0], x[2], x[1]))
+
+
+@pytest.mark.parametrize("engine,dfa_states", [(litdb.ENGINE_MCCLELLAN, 24), (litdb.ENGINE_MCCLELLAN, 300),
+                                               (litdb.ENGINE_MCCLELLAN_SHERMAN, 600), (litdb.ENGINE_LIMEX, 0)])
+@pytest.mark.parametrize("seed", range(4))
+def test_multi_outfix_batches(ref, seed, engine, dfa_states):
+    rng = random.Random(9100 + seed)
+    ex, fl, ids, smp = regen.random_set(rng, rng.randint(2, 14), True)
+    db = litdb.compile_regex_rose(ex, fl, ids, engine=engine, dfa_states=dfa_states)
+    bufs = [regen.random_text(rng, ex, rng.choice([0, 1, 30, 200, 1400]), smp) for _ in range(60)]
+    got = gpu_batch(db, bufs)
+    assert got == ref_batch(ref, db, bufs)
+    assert got == port_batch(db, bufs)
+    assert got == brute_batch(ex, fl, ids, bufs)
+
+
+def test_c3_shaped_set_of_several_hundred_patterns(ref):
+    """The C3 templates (workloads.c3_patterns) at a few hundred patterns: dozens of engines, shared words, caseless."""
+    ex, fl, ids = W.c3_patterns(max_patterns=300, state_budget=1 << 30)
+    db = litdb.compile_regex_rose(ex, fl, ids, dfa_states=512)
+    nq = int.from_bytes(db.bytecode()[156:160], "little")
+    assert nq > 4
+    flat, offs = W.c3_corpus(1 << 20)
+    data = flat.tobytes()
+    bufs = [data[int(offs[k]):int(offs[k + 1])] for k in range(len(offs) - 1)]
+    got = gpu_batch(db, bufs)
+    assert len(got) > 100
+    assert got == ref_batch(ref, db, bufs)
+
+
+def test_scan_one_buffer_callback_order(ref):
+    ex = [b"abc[0-9]{2,5}x", b"foo.*bar", b"(login|admin)[^&]*&id=", b"^GET /[^ ]*\\.php"]
+    db = litdb.compile_regex_rose(ex, [0, 2, 0, 0], [5, 6, 7, 8], dfa_states=40)
+    text = b"GET /a.php login=1&id=2 abc123x foo abc12x bar admin&id="
+    sc = gpu.alloc_scratch(db)
+    got = []
+    assert gpu.scan(db, text, sc, lambda i, f, t, fl, c: got.append((i, t)) or 0) == 0
+    exp = sorted(regen.brute_force(ex, [0, 2, 0, 0], [5, 6, 7, 8], text), key=lambda x: (x[1], x[0]))
+    assert got == exp

@@ -1020,8 +1020,13 @@ struct DbImage {  // one uploaded database
     DevMcc mcc{};
     bool ordered_ok = true;
     size_t device_bytes = 0;
+    // full-Rose database of outfix engines (view.kind == ENG_MULTI): one image per queue, sharing this image's bytecode
+    std::vector<DbImage *> subs;
+    bool owns_bc = true;
     void release() {
-        if (d_bc) cudaFree(d_bc);
+        for (DbImage *sub : subs) { sub->release(); delete sub; }
+        subs.clear();
+        if (d_bc && owns_bc) cudaFree(d_bc);
         if (d_fdr) cudaFree(d_fdr);
         if (d_teddy) cudaFree(d_teddy);
         if (d_pair) cudaFree(d_pair);
@@ -1155,6 +1160,44 @@ void build_sheng_tables(const DbView &v, u32 at, std::vector<u8> &out, DevMcc &D
     D.arb_report = S.report; D.accepts_eod = (v.nfa_flags & nfa::ACCEPTS_EOD) ? 1u : 0u; D.in_smem = 1; D.has_sherman = 0;
 }
 
+// Device tables of ONE outfix engine (im->view describes it; im->dev.bc is the uploaded bytecode it lives in).
+hs_error_t build_engine_image(hs_gpu_scratch *s, DbImage *im) {
+    const DbView &v = im->view;
+    DevDb &d = im->dev;
+    if (v.kind == ENG_LIMEX) {
+        limex_dev::Tables &t = im->lx_tabs;
+        if (!limex_dev::build(v, t)) return HS_UNKNOWN_ERROR;
+        if (cudaMalloc((void **)&im->d_lx, t.blob.size() * 8) != cudaSuccess) return HS_NOMEM;
+        cudaMemcpyAsync(im->d_lx, t.blob.data(), t.blob.size() * 8, cudaMemcpyHostToDevice, s->stream);
+        im->device_bytes += t.blob.size() * 8;
+        d.lx_abs = t.limex_abs;
+        DevLimex &L = im->lx;
+        L = DevLimex{};
+        L.tab = im->d_lx; L.G = t.G; L.n_exc = t.n_exc; L.shift_count = t.shift_count;
+        L.any_squash = t.any_squash ? 1u : 0u; L.can_die = t.can_die ? 1u : 0u;
+        for (u32 k = 0; k < 8; k++) L.shmul[k] = 1u << ((u32)(t.shift_amounts >> (8 * k)) & 31u);
+        L.o_reach = t.o_reach; L.o_shift = t.o_shift; L.o_shamt = t.o_shamt; L.o_csucc = t.o_csucc; L.o_succ = t.o_succ;
+        L.o_squash = t.o_squash; L.o_meta = t.o_meta; L.o_masks = t.o_masks; L.o_base = t.o_base;
+        L.total_words = t.total_words; L.accept_abs = t.accept_abs; L.accept_eod_abs = t.accept_eod_abs;
+        L.nfa_flags = t.nfa_flags;
+    } else if (v.kind == ENG_SHENG) {
+        // im->mcc was filled by build_sheng_tables above
+    } else if (v.kind == ENG_MCCLELLAN) {
+        // the engine is stepped straight from the uploaded bytecode (mcclellan.cuh copies the table to shared memory)
+        const DbView::Mcc &M = v.mcc;
+        DevMcc &D = im->mcc;
+        D = DevMcc{};
+        D.tab_abs = M.tab_off; D.tab_bytes = M.tab_bytes; D.remap_abs = M.m_off + (u32)mcclellan::remap;
+        D.nfa_abs = v.nfa_off; D.aux_abs = M.aux_off; D.sherman_abs = M.sherman_off;
+        D.wide16 = M.wide16; D.as = M.as; D.start = M.start; D.accept_limit_8 = M.accept_limit_8;
+        D.sherman_limit = M.sherman_limit; D.single = M.single; D.arb_report = M.arb_report;
+        D.accepts_eod = (v.nfa_flags & nfa::ACCEPTS_EOD) ? 1u : 0u;
+        D.in_smem = MCC_RM_BYTES + (size_t)M.tab_bytes + 8 <= MCC_SMEM_MAX ? 1u : 0u;
+        D.has_sherman = M.wide16 && M.sherman_limit < M.states ? 1u : 0u;
+    }
+    return HS_SUCCESS;
+}
+
 hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage **out) {
     // cached by (pointer, crc)
     const u32 crc = rd32(db, db::crc32);
@@ -1232,36 +1275,24 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         im->device_bytes += 1024;
         d.teddy_tab = im->d_teddy;
         d.teddy_masks = v.teddy_masks;
-    } else if (v.kind == ENG_LIMEX) {
-        limex_dev::Tables &t = im->lx_tabs;
-        if (!limex_dev::build(v, t)) { im->release(); delete im; return HS_UNKNOWN_ERROR; }
-        if (cudaMalloc((void **)&im->d_lx, t.blob.size() * 8) != cudaSuccess) { im->release(); delete im; return HS_NOMEM; }
-        cudaMemcpyAsync(im->d_lx, t.blob.data(), t.blob.size() * 8, cudaMemcpyHostToDevice, s->stream);
-        im->device_bytes += t.blob.size() * 8;
-        d.lx_abs = t.limex_abs;
-        DevLimex &L = im->lx;
-        L = DevLimex{};
-        L.tab = im->d_lx; L.G = t.G; L.n_exc = t.n_exc; L.shift_count = t.shift_count;
-        L.any_squash = t.any_squash ? 1u : 0u; L.can_die = t.can_die ? 1u : 0u;
-        for (u32 k = 0; k < 8; k++) L.shmul[k] = 1u << ((u32)(t.shift_amounts >> (8 * k)) & 31u);
-        L.o_reach = t.o_reach; L.o_shift = t.o_shift; L.o_shamt = t.o_shamt; L.o_csucc = t.o_csucc; L.o_succ = t.o_succ;
-        L.o_squash = t.o_squash; L.o_meta = t.o_meta; L.o_masks = t.o_masks; L.o_base = t.o_base;
-        L.total_words = t.total_words; L.accept_abs = t.accept_abs; L.accept_eod_abs = t.accept_eod_abs;
-        L.nfa_flags = t.nfa_flags;
-    } else if (v.kind == ENG_SHENG) {
-        // im->mcc was filled by build_sheng_tables above
-    } else if (v.kind == ENG_MCCLELLAN) {
-        // the engine is stepped straight from the uploaded bytecode (mcclellan.cuh copies the table to shared memory)
-        const DbView::Mcc &M = v.mcc;
-        DevMcc &D = im->mcc;
-        D = DevMcc{};
-        D.tab_abs = M.tab_off; D.tab_bytes = M.tab_bytes; D.remap_abs = M.m_off + (u32)mcclellan::remap;
-        D.nfa_abs = v.nfa_off; D.aux_abs = M.aux_off; D.sherman_abs = M.sherman_off;
-        D.wide16 = M.wide16; D.as = M.as; D.start = M.start; D.accept_limit_8 = M.accept_limit_8;
-        D.sherman_limit = M.sherman_limit; D.single = M.single; D.arb_report = M.arb_report;
-        D.accepts_eod = (v.nfa_flags & nfa::ACCEPTS_EOD) ? 1u : 0u;
-        D.in_smem = MCC_RM_BYTES + (size_t)M.tab_bytes + 8 <= MCC_SMEM_MAX ? 1u : 0u;
-        D.has_sherman = M.wide16 && M.sherman_limit < M.states ? 1u : 0u;
+    } else if (v.kind == ENG_LIMEX || v.kind == ENG_SHENG || v.kind == ENG_MCCLELLAN) {
+        const hs_error_t erv = build_engine_image(s, im);
+        if (erv != HS_SUCCESS) { im->release(); delete im; return erv; }
+    } else if (v.kind == ENG_MULTI) {
+        for (const DbView &ev : v.engines) {
+            DbImage *sub = new DbImage();
+            sub->view = ev;
+            sub->host_db = db;
+            sub->crc = crc;
+            sub->bc_len = v.bc_len;
+            sub->d_bc = im->d_bc;
+            sub->owns_bc = false;
+            sub->dev = im->dev;
+            im->subs.push_back(sub);
+            const hs_error_t erv = build_engine_image(s, sub);
+            if (erv != HS_SUCCESS) { im->release(); delete im; return erv; }
+            im->device_bytes += sub->device_bytes;
+        }
     } else {
         d.nood_msk = v.nood_msk;
         d.nood_cmp = v.nood_cmp;
@@ -1269,7 +1300,7 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         d.nood_id = v.nood_id;
     }
     d.tK = 0;
-    if (v.kind != ENG_LIMEX && v.kind != ENG_MCCLELLAN && v.kind != ENG_SHENG && turbo::build(v, im->turbo_tabs)) {
+    if (v.kind != ENG_LIMEX && v.kind != ENG_MCCLELLAN && v.kind != ENG_SHENG && v.kind != ENG_MULTI && turbo::build(v, im->turbo_tabs)) {
         const turbo::Tables &tt = im->turbo_tabs;
         if (cudaMalloc((void **)&im->d_pair, tt.pair.size() * 8) != cudaSuccess ||
             cudaMalloc((void **)&im->d_slots, tt.slots.size() * sizeof(turbo::Slot)) != cudaSuccess ||
@@ -1392,7 +1423,7 @@ hs_error_t launch_scan(hs_gpu_scratch *s, const DevDb &db, const DevCorpus &cp, 
 }
 
 template <int G>
-hs_error_t launch_limex_g(hs_gpu_scratch *s, const DbImage *im, const DevCorpus &cp, const DevArena &ar) {
+hs_error_t launch_limex_g(hs_gpu_scratch *s, const DbImage *im, const DevCorpus &cp, const DevArena &ar, bool report) {
     const size_t dyn = limex_smem_bytes(im->lx);
     CU_OK(ensure_smem_optin(s, (const void *)k_limex<G>, dyn));
     // persistent groups of G lanes; no more CTAs than there are buffers to hand out
@@ -1405,23 +1436,25 @@ hs_error_t launch_limex_g(hs_gpu_scratch *s, const DbImage *im, const DevCorpus 
     const DevLxEvents evq{reinterpret_cast<LxEvent *>(s->recs2.p), s->d_ctl + 7, s->recs2.cap};
     k_limex<G><<<grid, LX_THREADS, dyn, s->stream>>>(im->dev, im->lx, cp, evq, s->d_ctl + 6);
     CU_OK(cudaGetLastError());
+    s->stats.kernel_launches++;
+    if (!report) return HS_SUCCESS;
     k_limex_report<<<(u32)s->sm_count, LX_THREADS, 0, s->stream>>>(im->dev, cp, ar, evq);
     CU_OK(cudaGetLastError());
     s->stats.kernel_launches++;
     return HS_SUCCESS;
 }
 
-hs_error_t launch_limex(hs_gpu_scratch *s, const DbImage *im, const DevCorpus &cp, const DevArena &ar) {
+hs_error_t launch_limex(hs_gpu_scratch *s, const DbImage *im, const DevCorpus &cp, const DevArena &ar, bool report = true) {
     switch (im->lx.G) {
-    case 1: return launch_limex_g<1>(s, im, cp, ar);
-    case 2: return launch_limex_g<2>(s, im, cp, ar);
-    case 4: return launch_limex_g<4>(s, im, cp, ar);
-    default: return launch_limex_g<8>(s, im, cp, ar);
+    case 1: return launch_limex_g<1>(s, im, cp, ar, report);
+    case 2: return launch_limex_g<2>(s, im, cp, ar, report);
+    case 4: return launch_limex_g<4>(s, im, cp, ar, report);
+    default: return launch_limex_g<8>(s, im, cp, ar, report);
     }
 }
 
 template <bool WIDE16, bool SMEM, bool SHERMAN>
-hs_error_t launch_mcclellan_t(hs_gpu_scratch *s, const DbImage *im, const DevCorpus &cp, const DevArena &ar) {
+hs_error_t launch_mcclellan_t(hs_gpu_scratch *s, const DbImage *im, const DevCorpus &cp, const DevArena &ar, bool report) {
     const size_t dyn = mcc_smem_bytes(im->mcc);
     CU_OK(ensure_smem_optin(s, (const void *)k_mcclellan<WIDE16, SMEM, SHERMAN>, dyn));
     // persistent threads, one buffer each at a time, fed from a counter: every SM gets a CTA as soon as there is a
@@ -1438,17 +1471,37 @@ hs_error_t launch_mcclellan_t(hs_gpu_scratch *s, const DbImage *im, const DevCor
     const DevLxEvents evq{reinterpret_cast<LxEvent *>(s->recs2.p), s->d_ctl + 7, s->recs2.cap};
     k_mcclellan<WIDE16, SMEM, SHERMAN><<<grid, block, dyn, s->stream>>>(im->dev, im->mcc, cp, evq, s->d_ctl + 6);
     CU_OK(cudaGetLastError());
+    s->stats.kernel_launches++;
+    if (!report) return HS_SUCCESS;
     k_limex_report<<<(u32)s->sm_count, LX_THREADS, 0, s->stream>>>(im->dev, cp, ar, evq);
     CU_OK(cudaGetLastError());
     s->stats.kernel_launches++;
     return HS_SUCCESS;
 }
 
-hs_error_t launch_mcclellan(hs_gpu_scratch *s, const DbImage *im, const DevCorpus &cp, const DevArena &ar) {
+hs_error_t launch_mcclellan(hs_gpu_scratch *s, const DbImage *im, const DevCorpus &cp, const DevArena &ar, bool report = true) {
     const DevMcc &m = im->mcc;
-    if (!m.wide16) return m.in_smem ? launch_mcclellan_t<false, true, false>(s, im, cp, ar) : launch_mcclellan_t<false, false, false>(s, im, cp, ar);
-    if (m.has_sherman) return m.in_smem ? launch_mcclellan_t<true, true, true>(s, im, cp, ar) : launch_mcclellan_t<true, false, true>(s, im, cp, ar);
-    return m.in_smem ? launch_mcclellan_t<true, true, false>(s, im, cp, ar) : launch_mcclellan_t<true, false, false>(s, im, cp, ar);
+    if (!m.wide16) return m.in_smem ? launch_mcclellan_t<false, true, false>(s, im, cp, ar, report) : launch_mcclellan_t<false, false, false>(s, im, cp, ar, report);
+    if (m.has_sherman) return m.in_smem ? launch_mcclellan_t<true, true, true>(s, im, cp, ar, report) : launch_mcclellan_t<true, false, true>(s, im, cp, ar, report);
+    return m.in_smem ? launch_mcclellan_t<true, true, false>(s, im, cp, ar, report) : launch_mcclellan_t<true, false, false>(s, im, cp, ar, report);
+}
+
+// Full-Rose database of outfix engines (roseBlockExec with outfixes only, src/rose/block.c:345-422, catchup.c:612-672):
+// every engine steps the whole batch (its own kernel launch; a block shorter than the engine's NFA.minWidth cannot
+// match it), all of them append to ONE event queue, and one report pass runs the Rose report programs; the finalize
+// sorts by (buffer, offset, id) and applies the dedupe keys, which is what the catch-up queue's offset order is for.
+hs_error_t launch_outfixes(hs_gpu_scratch *s, const DbImage *im, const DevCorpus &cp, const DevArena &ar) {
+    for (size_t qi = 0; qi < im->subs.size(); qi++) {
+        const DbImage *sub = im->subs[qi];
+        if (qi) CU_OK(cudaMemsetAsync(s->d_ctl + 6, 0, sizeof(unsigned long long), s->stream));  // the buffer counter
+        const hs_error_t rv = sub->view.kind == ENG_LIMEX ? launch_limex(s, sub, cp, ar, false) : launch_mcclellan(s, sub, cp, ar, false);
+        if (rv != HS_SUCCESS) return rv;
+    }
+    const DevLxEvents evq{reinterpret_cast<LxEvent *>(s->recs2.p), s->d_ctl + 7, s->recs2.cap};
+    k_limex_report<<<(u32)s->sm_count, LX_THREADS, 0, s->stream>>>(im->dev, cp, ar, evq);
+    CU_OK(cudaGetLastError());
+    s->stats.kernel_launches++;
+    return HS_SUCCESS;
 }
 
 // Ordered mode: k_turbo / k_turbo2 append position-ordered records to per-warp segments, k_compact gathers them; no
@@ -1621,11 +1674,12 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
         case ENG_TEDDY: rv = launch_scan<TeddyNative, false>(s, im->dev, cp, ar); break;
         case ENG_LIMEX: rv = launch_limex(s, im, cp, ar); break;
         case ENG_MCCLELLAN: case ENG_SHENG: rv = launch_mcclellan(s, im, cp, ar); break;
+        case ENG_MULTI: rv = launch_outfixes(s, im, cp, ar); break;
         default: rv = launch_scan<Noodle, true>(s, im->dev, cp, ar); break;
         }
         if (rv != HS_SUCCESS) return rv;
         st.front_end = t2w ? 3u : use_turbo ? 2u : im->view.kind == ENG_LIMEX ? 4u
-                     : (im->view.kind == ENG_MCCLELLAN || im->view.kind == ENG_SHENG) ? 5u : 1u;
+                     : (im->view.kind == ENG_MCCLELLAN || im->view.kind == ENG_SHENG) ? 5u : im->view.kind == ENG_MULTI ? 6u : 1u;
         CU_OK(cudaEventRecord(s->ev[7], s->stream));
         st.scan_launches++;
         st.kernel_launches++;
@@ -1647,7 +1701,7 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
             return HS_UNKNOWN_ERROR;
         }
         raw = s->h_ctl[0];
-        if ((im->view.kind == ENG_LIMEX || im->view.kind == ENG_MCCLELLAN || im->view.kind == ENG_SHENG) && s->h_ctl[7] > s->recs2.cap) {  // event queue overflow: grow, scan again
+        if ((im->view.kind == ENG_LIMEX || im->view.kind == ENG_MCCLELLAN || im->view.kind == ENG_SHENG || im->view.kind == ENG_MULTI) && s->h_ctl[7] > s->recs2.cap) {  // event queue overflow: grow, scan again
             if (attempt >= 3) return HS_NOMEM;
             st.arena_retries++;
             s->lx_event_hint = s->h_ctl[7] + s->h_ctl[7] / 8 + 1024;

@@ -14,7 +14,8 @@ namespace hsb {
 constexpr int E_SUCCESS = 0, E_INVALID = -1, E_NOMEM = -2, E_DB_VERSION = -5, E_DB_PLATFORM = -6,
               E_DB_MODE = -7, E_BAD_ALIGN = -8, E_ARCH = -11, E_UNKNOWN = -13;
 
-enum EngineKind : u32 { ENG_FDR = 0, ENG_TEDDY = 1, ENG_NOODLE = 2, ENG_LIMEX = 3, ENG_MCCLELLAN = 4, ENG_SHENG = 5 };
+enum EngineKind : u32 { ENG_FDR = 0, ENG_TEDDY = 1, ENG_NOODLE = 2, ENG_LIMEX = 3, ENG_MCCLELLAN = 4, ENG_SHENG = 5,
+                        ENG_MULTI = 6 /* full-Rose database of outfix engines: DbView::engines */ };
 
 struct LitRec {  // one LitInfo, flattened
     u64 v, msk, groups;
@@ -52,6 +53,9 @@ struct DbView {
     } mcc;
     // single-outfix Sheng DFA (kind == ENG_SHENG), absolute bytecode offsets
     struct Sheng { u32 sh_off = 0, aux_off = 0, n_states = 0, anchored = 0, flags = 0, report = 0; } sheng;
+    // full-Rose database of outfix engines (kind == ENG_MULTI): one view per queue, each of kind LIMEX / MCCLELLAN
+    std::vector<DbView> engines;
+    u32 nfa_min_width = 0;  // NFA.minWidth of an outfix engine: blocks shorter than this do not start it
 };
 
 inline bool in_range(const DbView &d, size_t off, size_t n) { return off <= d.bc_len && n <= d.bc_len - off; }
@@ -282,19 +286,67 @@ inline int parse_sheng(DbView &d, std::string &why) {
 // Single-outfix database (src/runtime.c:246-279): queue 0 holds the only engine.  Accepted when that engine is a
 // LimEx NFA without bounded repeats and without reverse acceleration; every report list and accept entry must
 // lead to a Rose report program the device interpreter implements.
+inline int parse_outfix_at(DbView &d, u32 info_off, std::string &why);
+
 inline int parse_single_outfix(DbView &d, std::string &why) {
     const u8 *r = d.bc;
     if (rd32(r, rose::fmatcherOffset) || rd32(r, rose::amatcherOffset) || rd32(r, rose::ematcherOffset)) {
         why = "single-outfix database with a literal matcher"; return E_INVALID;
     }
     if (rd32(r, rose::outfixEndQueue) != 1 || rd32(r, rose::queueCount) != 1) { why = "single-outfix database with more than one queue"; return E_INVALID; }
+    return parse_outfix_at(d, rd32(r, rose::nfaInfoOffset), why);
+}
+
+// Full-Rose database whose only engines are outfixes (src/rose/block.c:345-422 with no literal matcher: every outfix is
+// started by blockInitSufPQ and caught up to the end of the block, src/rose/catchup.c:560-672).  Accepted when there is
+// nothing else for Rose to orchestrate: no anchored / floating / EOD / delay-rebuild / small-block matcher, no roles, no
+// leftfixes, no MPV, no EOD program, no delayed or anchored literals.  Each queue's engine is censused like a sole outfix.
+inline int parse_outfix_rose(DbView &d, std::string &why) {
+    const u8 *r = d.bc;
+    if (rd32(r, rose::amatcherOffset) || rd32(r, rose::fmatcherOffset) || rd32(r, rose::ematcherOffset) ||
+        rd32(r, rose::drmatcherOffset) || rd32(r, rose::sbmatcherOffset) || rd32(r, rose::longLitTableOffset)) {
+        why = "full-Rose databases with literal matchers (roles, leftfixes, delayed literals) are not supported yet";
+        return E_ARCH;
+    }
+    const u32 nq = rd32(r, rose::queueCount);
+    if (rd32(r, rose::rolesWithStateCount) || rd32(r, rose::activeLeftCount) || rd32(r, rose::roseCount) ||
+        rd32(r, rose::eodProgramOffset) || rd8(r, rose::requiresEodCheck) || rd32(r, rose::delay_count) ||
+        rd32(r, rose::anchored_count) || rd32(r, rose::initMpvNfa) != 0xffffffffu || rd32(r, rose::outfixBeginQueue) ||
+        rd32(r, rose::outfixEndQueue) != nq || rd32(r, rose::leftfixBeginQueue) != nq || rd32(r, rose::somLocationCount)) {
+        why = "full-Rose database with more than outfix engines (roles, leftfixes, MPV, EOD program) is not supported yet";
+        return E_ARCH;
+    }
+    if (!nq || nq > 4096) { why = "outfix queue count out of range"; return E_INVALID; }
     const u32 info_off = rd32(r, rose::nfaInfoOffset);
+    if (!in_range(d, info_off, (size_t)nfainfo::SIZE * nq)) { why = "NfaInfo array outside bytecode"; return E_INVALID; }
+    std::set<u32> progs;
+    for (u32 qi = 0; qi < nq; qi++) {
+        DbView e;
+        e.bc = d.bc; e.bc_len = d.bc_len; e.crc = d.crc;
+        e.min_width = d.min_width; e.min_width_excl = d.min_width_excl; e.max_bi_width = d.max_bi_width;
+        e.ekey_count = d.ekey_count; e.dkey_count = d.dkey_count; e.groups = d.groups;
+        const int rv = parse_outfix_at(e, info_off + (u32)nfainfo::SIZE * qi, why);
+        if (rv != E_SUCCESS) { why = "queue " + std::to_string(qi) + ": " + why; return rv; }
+        if (e.kind == ENG_SHENG) { why = "Sheng outfixes inside a multi-engine database are not supported yet"; return E_ARCH; }
+        if (e.nfa_flags & nfa::ACCEPTS_EOD) { why = "outfix with end-of-data accepts needs the EOD program (not supported yet)"; return E_ARCH; }
+        for (u32 p : e.programs) progs.insert(p);
+        d.max_lit_len = std::max(d.max_lit_len, e.max_lit_len);
+        d.engines.push_back(std::move(e));
+    }
+    d.programs.assign(progs.begin(), progs.end());
+    d.kind = ENG_MULTI;
+    return E_SUCCESS;
+}
+
+inline int parse_outfix_at(DbView &d, u32 info_off, std::string &why) {
+    const u8 *r = d.bc;
     if (!in_range(d, info_off, nfainfo::SIZE)) { why = "NfaInfo outside bytecode"; return E_INVALID; }
     d.nfa_off = rd32(r, info_off + nfainfo::nfaOffset);
     if ((d.nfa_off & 63) || !in_range(d, d.nfa_off, nfa::SIZE)) { why = "NFA header outside bytecode or misaligned"; return E_INVALID; }
     const u8 *n = r + d.nfa_off;
     d.nfa_len = rd32(n, nfa::length);
     d.nfa_flags = rd32(n, nfa::flags);
+    d.nfa_min_width = rd32(n, nfa::minWidth);
     d.limex_type = rd8(n, nfa::type);
     if (!in_range(d, d.nfa_off, d.nfa_len)) { why = "NFA runs past the bytecode"; return E_INVALID; }
     if (rd8(n, nfa::rAccelType)) { why = "reverse acceleration is not supported"; return E_ARCH; }
@@ -378,11 +430,7 @@ inline int parse_database(const void *db, DbView &d, std::string &why) {
     if (rd8(r, rose::hasSom)) { why = "start-of-match databases are not supported"; return E_ARCH; }
     if (rd32(r, rose::ckeyCount) || rd32(r, rose::lkeyCount)) { why = "logical combinations are not supported"; return E_ARCH; }
     const u8 impl = rd8(r, rose::runtimeImpl);
-    if (impl == rose::RUNTIME_FULL_ROSE) {
-        why = "full-Rose databases (several engines interleaved by Rose) are not supported yet";
-        return E_ARCH;
-    }
-    if (impl != rose::RUNTIME_PURE_LITERAL && impl != rose::RUNTIME_SINGLE_OUTFIX) { why = "unknown runtimeImpl"; return E_INVALID; }
+    if (impl != rose::RUNTIME_FULL_ROSE && impl != rose::RUNTIME_PURE_LITERAL && impl != rose::RUNTIME_SINGLE_OUTFIX) { why = "unknown runtimeImpl"; return E_INVALID; }
     const u8 *bd = r + rose::boundary;
     if (rd32(bd, rose::bd::reportEodOffset) || rd32(bd, rose::bd::reportZeroOffset) ||
         rd32(bd, rose::bd::reportZeroEodOffset)) {
@@ -396,6 +444,7 @@ inline int parse_database(const void *db, DbView &d, std::string &why) {
     d.dkey_count = rd32(r, rose::dkeyCount);
     d.groups = rd64(r, rose::initialGroups) & rd64(r, rose::floating_group_mask);
     if (impl == rose::RUNTIME_SINGLE_OUTFIX) return parse_single_outfix(d, why);
+    if (impl == rose::RUNTIME_FULL_ROSE) return parse_outfix_rose(d, why);
     d.hwlm_off = rd32(r, rose::fmatcherOffset);
     if (!d.hwlm_off || !in_range(d, d.hwlm_off, hwlm::BODY + 24)) { why = "no floating literal matcher"; return E_INVALID; }
     const u8 type = rd8(r, d.hwlm_off + hwlm::type);

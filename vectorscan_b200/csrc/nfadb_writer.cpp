@@ -1186,8 +1186,16 @@ int build_rose(const std::vector<Pattern> &pats, unsigned engine, u32 dfa_states
     if (engine == HSB_REGEX_ENGINE_LIMEX) {
         for (u32 i = 0; i < pats.size(); i++) for_limex.push_back(i);
     } else {
+        // patterns are visited in the order of their text (anchored ones first), so that patterns sharing a head --
+        // which share DFA states -- are neighbours; identical expressions cost no states at all
+        std::vector<u32> order(pats.size());
+        for (u32 i = 0; i < pats.size(); i++) order[i] = i;
+        std::stable_sort(order.begin(), order.end(), [&](u32 a, u32 b) {
+            if (parsed[a].anchored != parsed[b].anchored) return parsed[a].anchored;
+            return pats[a].expr < pats[b].expr;
+        });
         std::vector<u32> cur;
-        for (u32 i = 0; i < pats.size(); i++) {
+        for (u32 i : order) {
             cur.push_back(i);
             if (dfa_fits(cur)) continue;
             cur.pop_back();
@@ -1210,7 +1218,7 @@ int build_rose(const std::vector<Pattern> &pats, unsigned engine, u32 dfa_states
         if (!cur.empty()) groups.push_back({cur, HSB_REGEX_ENGINE_LIMEX});
     }
     const u32 N = (u32)groups.size();
-    if (N > 256) { err = "more than 256 engines (the flat multibit model of the active array)"; return HSB_LIT_COMPILER_ERROR; }
+    if (N > 4096) { err = "more than 4096 engines"; return HSB_LIT_COMPILER_ERROR; }
 
     Buf rose;
     rose.grow(rose::SIZE);
@@ -1264,7 +1272,14 @@ int build_rose(const std::vector<Pattern> &pats, unsigned engine, u32 dfa_states
     u32 plan_u64_off = 0, plan_u64_n = 0, plan_u8_off = 0, plan_u8_n = 0;
     {
         u32 b = 0;
-        if (leaf_bytes >= 8) {
+        if (N > 256) {
+            // hierarchical multibit: clearing the root block empties it (mmbit_clear, src/util/multibit.h:332-343)
+            plan_u64_off = (u32)rose.size();
+            const size_t o = rose.grow(16);
+            wr32(rose.at(o), 0, leaf_off);
+            plan_u64_n = 1;
+            b = leaf_bytes;
+        } else if (leaf_bytes >= 8) {
             plan_u64_off = (u32)rose.size();
             for (; b + 8 <= leaf_bytes; b += 8) {
                 const size_t o = rose.grow(16);  // struct scatter_unit_u64a { u32 offset; u64a val; }
