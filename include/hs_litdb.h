@@ -89,11 +89,24 @@ typedef struct hsb_lit_build_ext {
     int target_avx512;                 /* allow the 64-byte instructions (only an AVX512 runtime build executes them) */
     unsigned long long groups_off;     /* group bits left out of RoseEngine.initialGroups */
     unsigned max_bi_anchored_width;    /* RoseEngine.maxBiAnchoredWidth; 0 = ROSE_BOUND_INF */
+    unsigned reserved_pure_literal;    /* set by hsb_compile_lit_multi_ext; leave 0 */
 } hsb_lit_build_ext;
 int hsb_compile_lit_multi_ext(const char *const *expressions, const unsigned *flags, const unsigned *ids,
                               const size_t *lens, const hsb_lit_ext *ext, unsigned elements, unsigned mode,
                               const hsb_lit_options *options, const hsb_lit_build_ext *build_ext,
                               hs_database_t **db, char **error);
+/* Mixed pattern sets -- literals AND regular expressions in ONE full-Rose database (RoseEngine.runtimeImpl =
+ * ROSE_RUNTIME_FULL_ROSE): the literals sit in the floating literal matcher (FDR / Teddy / noodle) and their programs run
+ * through the full interpreter roseRunProgram (src/rose/match.c:479-523, so class lookarounds -> CHECK_SHUFTI_* are
+ * available); the regular expressions become outfix engines on their own queues exactly as hsb_compile_regex_rose lays
+ * them out, and every literal program starts with CATCH_UP so that the engines' earlier matches are delivered first
+ * (src/rose/block.c:345-422, catchup.c).  n_regexes = 0 gives a literal-only full-Rose database.  Report ids of
+ * literals and of regexes must be disjoint. */
+int hsb_compile_mixed(const char *const *literals, const unsigned *flags, const unsigned *ids,
+                      const size_t *lens, const hsb_lit_ext *ext, unsigned n_literals,
+                      const char *const *regexes, const unsigned *regex_flags, const unsigned *regex_ids, unsigned n_regexes,
+                      unsigned mode, const hsb_lit_options *options, const hsb_lit_build_ext *build_ext,
+                      unsigned regex_engine, unsigned dfa_states, hs_database_t **db, char **error);
 /* Stand-in for hs_compile_multi() (/root/reference/src/hs_compile.h:450-456) for SMALL pattern sets in a
  * restricted dialect (vectorscan_b200/csrc/nfadb_writer.cpp): the whole set becomes ONE LimEx NFA inside a
  * single-outfix block-mode database -- the shape the reference compiler gives a pattern set that has no

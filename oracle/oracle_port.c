@@ -69,7 +69,7 @@ struct scan_state {
     int terminated, error;
     /* multi-outfix catch-up (rose/catchup.c): engine reports are gathered, then replayed in offset order */
     int defer; u32 cur_queue;
-    struct deferred { u64 to; u32 queue, prog, seq; } *ev; size_t n_ev, cap_ev;
+    struct deferred { u64 to; u32 queue, prog, seq; } *ev; size_t n_ev, cap_ev, ev_next;
 };
 
 /* roseDeliverReport + the dedupe test of dedupeCatchup for external reports without SOM */
@@ -132,6 +132,8 @@ static int check_mask_n(const struct scan_state *s, const u8 *and_m, const u8 *c
     return 1;
 }
 
+static int catch_up(struct scan_state *s, u64 end);
+
 /* roseRunProgram_l.  `end` = offset one past the literal's last byte (lit_offset_adjust = 1).
  * Returns 0 to continue, -1 to stop the scan. */
 static int run_program(struct scan_state *s, u32 prog, u64 end) {
@@ -165,7 +167,10 @@ static int run_program(struct scan_state *s, u32 prog, u64 end) {
             if (!check_mask_n(s, pc + 1, pc + 65, rd64(pc + 136), 64, (int32_t)rd32(pc + 144), end)) pc += rd32(pc + 148);
             else pc += 152;
             break;
-        case OP_CATCH_UP: pc += 8; break; /* no engines in a pure-literal database */
+        case OP_CATCH_UP: /* roseCatchUpTo(end), program_runtime.c:2499-2504: engine matches up to `end` come first */
+            if (catch_up(s, end) < 0) return -1;
+            pc += 8;
+            break;
         case OP_CLEAR_WORK_DONE: work_done = 0; pc += 8; break;
         case OP_CHECK_LONG_LIT: case OP_CHECK_MED_LIT: case OP_CHECK_LONG_LIT_NOCASE: case OP_CHECK_MED_LIT_NOCASE: {
             int nocase = pc[0] == OP_CHECK_LONG_LIT_NOCASE || pc[0] == OP_CHECK_MED_LIT_NOCASE;
@@ -492,11 +497,22 @@ static void engine_scan(struct scan_state *s, const u8 *nfa) {
     else limex_scan(s, nfa);
 }
 
-/* roseBlockExec for a database of outfix engines only (rose/block.c:345-422): blockInitSufPQ (rose/catchup.c:612-672)
- * starts every outfix whose NFA.minWidth the block satisfies (nfaRevAccelCheck, nfa/nfa_rev_api.h:135-155) and
- * roseCatchUpTo(length) delivers their reports in offset order (queue order inside one offset) through the report
- * programs, which share one dedupe log per offset (dedupeCatchup). */
-static void outfixes_exec(struct scan_state *s, const u8 *rose) {
+/* roseCatchUpTo (rose/catchup.h:128-167): deliver the outfix engines' pending reports with offset <= end, in offset
+ * order (queue order inside one offset), through their report programs. */
+static int catch_up(struct scan_state *s, u64 end) {
+    while (s->ev_next < s->n_ev && s->ev[s->ev_next].to <= end) {
+        const struct deferred e = s->ev[s->ev_next++];
+        if (run_program(s, e.prog, e.to) < 0) return -1;
+    }
+    return 0;
+}
+
+/* roseBlockExec (rose/block.c:345-422) for the restated full-Rose shapes: blockInitSufPQ (rose/catchup.c:612-672) starts
+ * every outfix whose NFA.minWidth the block satisfies (nfaRevAccelCheck, nfa/nfa_rev_api.h:135-155); the floating literal
+ * matcher runs with roseFloatingCallback, whose programs begin with CATCH_UP; roseCatchUpTo(length) delivers what is
+ * left.  The engines are stepped up front and their reports replayed at the catch-up points, which gives the same
+ * callback sequence as the reference's priority queue of engines. */
+static void full_rose_exec(struct scan_state *s, const u8 *rose) {
     const u32 q0 = rd32(rose + 396), q1 = rd32(rose + 400); /* outfixBeginQueue, outfixEndQueue */
     s->defer = 1;
     for (u32 qi = q0; qi < q1 && !s->error; qi++) {
@@ -507,8 +523,10 @@ static void outfixes_exec(struct scan_state *s, const u8 *rose) {
     }
     s->defer = 0;
     qsort(s->ev, s->n_ev, sizeof(*s->ev), deferred_cmp);
-    for (size_t i = 0; i < s->n_ev && !s->error; i++)
-        if (run_program(s, s->ev[i].prog, s->ev[i].to) < 0) break;
+    s->ev_next = 0;
+    if (rd32(rose + R_FMATCHER) && s->len >= rd32(rose + 116) /* fmatcherMinWidth */ && !s->error)
+        hwlm_exec(s, rose + rd32(rose + R_FMATCHER));
+    if (!s->terminated && !s->error) catch_up(s, s->len);
     free(s->ev);
     s->ev = NULL;
 }
@@ -524,8 +542,9 @@ int op_scan(const void *db, const char *data, unsigned length, op_match_cb cb, v
         rd32(rose + R_BOUNDARY + 4) || rd32(rose + R_BOUNDARY + 8))
         return HS_ARCH_ERROR; /* outside the restated path */
     if (rose[R_RUNTIME_IMPL] == 0) {
-        /* full Rose: only the outfix-only shape is restated (no literal matchers, roles, leftfixes, EOD program) */
-        if (rd32(rose + 88) || rd32(rose + 92) || rd32(rose + R_FMATCHER) || rd32(rose + 100) || rd32(rose + 104) ||
+        /* full Rose: a floating literal matcher and / or outfix engines; no roles, leftfixes, other matchers, EOD program */
+        if (rd32(rose + 88) || rd32(rose + 92) || rd32(rose + 100) || rd32(rose + 104) || rd32(rose + 108) ||
+            (rd32(rose + R_FMATCHER) && (rose[1] || rd32(rose + 224) || rd32(rose + 220) != 0xffffffffu || rd32(rose + 128) != 0xffffffffu)) ||
             rd32(rose + 84) || rd32(rose + 184) || rd32(rose + 64) || rd32(rose + 152) ||
             rd32(rose + 404) != rd32(rose + 156) || rd32(rose + 400) != rd32(rose + 156) || rd32(rose + 408) != 0xffffffffu)
             return HS_ARCH_ERROR;
@@ -542,7 +561,7 @@ int op_scan(const void *db, const char *data, unsigned length, op_match_cb cb, v
     s.exhausted = calloc(s.ekeys / 8 + 2, 1);
     s.dedupe = calloc(s.dkeys / 8 + 2, 1);
     s.dedupe_offset = ~0ull;
-    if (rose[R_RUNTIME_IMPL] == 0) outfixes_exec(&s, rose);
+    if (rose[R_RUNTIME_IMPL] == 0) full_rose_exec(&s, rose);
     else if (rose[R_RUNTIME_IMPL] == 2) engine_scan(&s, rose + rd32(rose + rd32(rose + R_NFA_INFO) + NI_NFA_OFF));
     else hwlm_exec(&s, rose + rd32(rose + R_FMATCHER));
     free(s.exhausted); free(s.dedupe);

@@ -123,3 +123,65 @@ def test_max_bi_anchored_width_gate_on_device():
     sc = gpu.alloc_scratch(db)
     got = [(int(b), int(i), int(t)) for b, i, t in gpu.scan_vector_ex(db, [short, long_, short], sc)]
     assert got == [(0, 1, 16), (0, 2, 19), (2, 1, 16), (2, 2, 19)]
+
+
+# ---- full-Rose databases: literal matcher (+ outfix engines) -------------------------------------------------------
+from test_litdb_ext import KINDS_SHUFTI, mixed_case, mixed_expected  # noqa: E402
+
+
+@pytest.mark.parametrize("frontend", FRONTENDS)
+def test_full_rose_literal_databases_with_class_lookarounds(ref, frontend):
+    """CHECK_SHUFTI_* (all six shapes) on the device against the reference's full interpreter and the ground truth."""
+    rng = random.Random(170 + frontend)
+    counts = [0] * 128
+    ran = 0
+    for kind, lits, flags, ids, ext, text, goff in ext_cases(31 + frontend, KINDS_SHUFTI + ["shufti64", "mask"]):
+        try:
+            db = litdb.compile_lit_multi(lits, flags, ids, ext=ext, groups_off=goff, full_rose=True,
+                                         target_avx512=1 if kind == "shufti64" else 0)
+        except litdb.CompileError:
+            continue
+        bufs = split_buffers(rng, text)
+        got = gpu_batch(db, bufs, frontend, counts)
+        assert got == expected(lits, flags, ids, ext, bufs, goff), (kind, len(lits), len(text))
+        if kind != "shufti64" or ref.isa == "avx512":
+            rdb = ref.deserialize(db.serialize())
+            rs = ref.alloc_scratch(rdb)
+            rexp = []
+            for bi, b in enumerate(bufs):
+                rv, m = ref.scan(rdb, rs, b)
+                assert rv == 0
+                rexp += [(bi, i, t) for (i, t) in m]
+            ref.L.hs_free_scratch(rs)
+            ref.L.hs_free_database(rdb)
+            assert got == sorted(rexp, key=lambda x: (x[0], x[2], x[1])), kind
+        ran += 1
+    assert ran >= 30
+    for name in ("CHECK_SHUFTI_16x8", "CHECK_SHUFTI_32x8", "CHECK_SHUFTI_64x8"):
+        assert counts[OP[name]] > 0, f"{name} never executed on the device"
+    assert counts[OP["CHECK_SHUFTI_16x16"]] + counts[OP["CHECK_SHUFTI_32x16"]] + counts[OP["CHECK_SHUFTI_64x16"]] > 0
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_mixed_literal_and_regex_databases(ref, seed):
+    """C4's shape: floating literal matcher + outfix engines in one full-Rose database; the literal kernel and every
+    engine add to one arena, the finalize merges by (buffer, offset, id)."""
+    rng = random.Random(800 + seed)
+    lits, flags, ids, ex, fl, rids, text = mixed_case(rng, rng.choice([1, 5, 40, 300]), rng.randint(1, 8), 4000)
+    db = litdb.compile_lit_multi(lits, flags, ids, regexes=ex, regex_flags=fl, regex_ids=rids, dfa_states=rng.choice([30, 300]))
+    bufs = split_buffers(rng, text)
+    counts = [0] * 128
+    got = gpu_batch(db, bufs, seed % 4, counts)
+    exp = []
+    for bi, b in enumerate(bufs):
+        exp += [(bi, i, t) for (i, t) in mixed_expected(lits, flags, ids, ex, fl, rids, b)]
+    assert got == sorted(exp, key=lambda x: (x[0], x[2], x[1]))
+    rdb = ref.deserialize(db.serialize())
+    rs = ref.alloc_scratch(rdb)
+    rexp = []
+    for bi, b in enumerate(bufs):
+        rv, m = ref.scan(rdb, rs, b)
+        assert rv == 0
+        rexp += [(bi, i, t) for (i, t) in set(m)]
+    assert got == sorted(rexp, key=lambda x: (x[0], x[2], x[1]))
+    assert counts[20] > 0 or seed % 4 != 1   # CATCH_UP is interpreted (native front end runs every program)

@@ -132,3 +132,78 @@ def test_max_bi_anchored_width_gate(ref):
     short, long_ = b"x" * 10 + b"needle" + b"pin", b"x" * 60 + b"needle" + b"pin"
     assert sorted(ref_scan(ref, db, short)) == [(1, 16), (2, 19)]
     assert ref_scan(ref, db, long_) == []
+
+
+# ---- full-Rose databases: literal programs run through the full roseRunProgram; regexes ride along as outfix engines ----
+@pytest.mark.parametrize("seed", [21, 22])
+def test_full_rose_literal_databases_with_class_lookarounds(ref, seed):
+    """CHECK_SHUFTI_16x8 / 32x8 / 16x16 / 32x16 exist only in the full interpreter (program_runtime.c:2379-2470): a
+    literal-only FULL_ROSE database reaches it through roseFloatingCallback (src/rose/match.c:479-523)."""
+    seen = [0] * 128
+    total = 0
+    for kind, lits, flags, ids, ext, text, goff in ext_cases(seed, KINDS_SHUFTI + ["mask", "groups", "quiet"]):
+        try:
+            db = litdb.compile_lit_multi(lits, flags, ids, ext=ext, groups_off=goff, full_rose=True)
+        except litdb.CompileError as e:
+            assert "bucket" in str(e) or "spans" in str(e), str(e)
+            continue
+        assert db.bytecode()[4] == 0   # ROSE_RUNTIME_FULL_ROSE
+        for k, v in enumerate(gpu.database_opcodes(db)):
+            seen[k] += v
+        exp = litgen.brute_force_ext(lits, flags, ids, ext, text, goff)
+        assert sorted(ref_scan(ref, db, text)) == exp, (kind, len(lits), len(text))
+        total += 1
+    assert total >= 40
+    assert seen[OP["CHECK_SHUFTI_16x8"]] > 0 and seen[OP["CHECK_SHUFTI_32x8"]] > 0
+    assert seen[OP["CHECK_SHUFTI_16x16"]] + seen[OP["CHECK_SHUFTI_32x16"]] > 0
+
+
+def test_avx512_shufti_shapes_in_full_rose(ref):
+    if ref.isa != "avx512":
+        pytest.skip("host CPU cannot run the AVX512 build of the reference runtime")
+    seen = [0] * 128
+    for kind, lits, flags, ids, ext, text, goff in ext_cases(23, ["shufti64"]):
+        try:
+            db = litdb.compile_lit_multi(lits, flags, ids, ext=ext, full_rose=True, target_avx512=1)
+        except litdb.CompileError:
+            continue
+        for k, v in enumerate(gpu.database_opcodes(db)):
+            seen[k] += v
+        assert sorted(ref_scan(ref, db, text)) == litgen.brute_force_ext(lits, flags, ids, ext, text, goff)
+    assert seen[OP["CHECK_SHUFTI_64x8"]] + seen[OP["CHECK_SHUFTI_64x16"]] > 0
+
+
+def mixed_case(rng, n_lits, n_rx, tl):
+    import regen
+    alpha = bytes(range(97, 123)) + b"0123456789 =&/."
+    lits, flags, ids, text = litgen.random_case(rng, None, n_lits, alpha, tl)
+    ids = [k + 1 for k in range(len(lits))]
+    ex, fl, rids, smp = regen.random_set(rng, n_rx, True)
+    rids = [100000 + k for k in range(len(ex))]
+    t = bytearray(text)
+    for s_ in smp[:8]:
+        if len(s_) < len(t):
+            p = rng.randrange(0, len(t) - len(s_))
+            t[p:p + len(s_)] = s_
+    return lits, flags, ids, ex, fl, rids, bytes(t)
+
+
+def mixed_expected(lits, flags, ids, ex, fl, rids, text):
+    import regen
+    return sorted(litgen.brute_force(lits, flags, ids, text) + [tuple(x) for x in regen.brute_force(ex, fl, rids, text)])
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_mixed_literal_and_regex_databases(ref, seed):
+    """Floating literal matcher + outfix engines in one FULL_ROSE database (C4's shape): reference hs_scan == literal brute
+    force + `re` brute force, delivered in offset order."""
+    rng = random.Random(700 + seed)
+    lits, flags, ids, ex, fl, rids, text = mixed_case(rng, rng.choice([1, 5, 40, 300]), rng.randint(1, 8), rng.choice([60, 400, 3000]))
+    db = litdb.compile_lit_multi(lits, flags, ids, regexes=ex, regex_flags=fl, regex_ids=rids, dfa_states=rng.choice([30, 300]))
+    assert db.bytecode()[4] == 0
+    for t in (text, text[:17], b""):
+        got = ref_scan(ref, db, t)
+        assert sorted(set(got)) == mixed_expected(lits, flags, ids, ex, fl, rids, t)
+        assert [x[1] for x in got] == sorted(x[1] for x in got)   # CATCH_UP keeps the callbacks in offset order
+        prv, pgot = oracle_port.scan(db, t)
+        assert prv == 0 and pgot == got   # the C restatement: same matches, same callback order

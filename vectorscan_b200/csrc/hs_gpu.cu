@@ -1279,26 +1279,29 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         const hs_error_t erv = build_engine_image(s, im);
         if (erv != HS_SUCCESS) { im->release(); delete im; return erv; }
     } else if (v.kind == ENG_MULTI) {
-        for (const DbView &ev : v.engines) {
-            DbImage *sub = new DbImage();
-            sub->view = ev;
-            sub->host_db = db;
-            sub->crc = crc;
-            sub->bc_len = v.bc_len;
-            sub->d_bc = im->d_bc;
-            sub->owns_bc = false;
-            sub->dev = im->dev;
-            im->subs.push_back(sub);
-            const hs_error_t erv = build_engine_image(s, sub);
-            if (erv != HS_SUCCESS) { im->release(); delete im; return erv; }
-            im->device_bytes += sub->device_bytes;
-        }
+        // engines only: images built below
     } else {
         d.nood_msk = v.nood_msk;
         d.nood_cmp = v.nood_cmp;
         d.nood_len = v.nood_len;
         d.nood_id = v.nood_id;
     }
+    // outfix engines of a full-Rose database (alone, or beside the literal matcher): one image per queue
+    for (const DbView &ev : v.engines) {
+        DbImage *sub = new DbImage();
+        sub->view = ev;
+        sub->host_db = db;
+        sub->crc = crc;
+        sub->bc_len = v.bc_len;
+        sub->d_bc = im->d_bc;
+        sub->owns_bc = false;
+        sub->dev = im->dev;
+        im->subs.push_back(sub);
+        const hs_error_t erv = build_engine_image(s, sub);
+        if (erv != HS_SUCCESS) { im->release(); delete im; return erv; }
+        im->device_bytes += sub->device_bytes;
+    }
+    if (!im->subs.empty()) im->ordered_ok = false;  // engine matches merge with the literal ones in the sorting finalize
     d.tK = 0;
     if (v.kind != ENG_LIMEX && v.kind != ENG_MCCLELLAN && v.kind != ENG_SHENG && v.kind != ENG_MULTI && turbo::build(v, im->turbo_tabs)) {
         const turbo::Tables &tt = im->turbo_tabs;
@@ -1678,6 +1681,10 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
         default: rv = launch_scan<Noodle, true>(s, im->dev, cp, ar); break;
         }
         if (rv != HS_SUCCESS) return rv;
+        if (im->view.kind != ENG_MULTI && !im->subs.empty()) {  // mixed database: the engines add their matches to the same arena
+            rv = launch_outfixes(s, im, cp, ar);
+            if (rv != HS_SUCCESS) return rv;
+        }
         st.front_end = t2w ? 3u : use_turbo ? 2u : im->view.kind == ENG_LIMEX ? 4u
                      : (im->view.kind == ENG_MCCLELLAN || im->view.kind == ENG_SHENG) ? 5u : im->view.kind == ENG_MULTI ? 6u : 1u;
         CU_OK(cudaEventRecord(s->ev[7], s->stream));
@@ -1701,7 +1708,7 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
             return HS_UNKNOWN_ERROR;
         }
         raw = s->h_ctl[0];
-        if ((im->view.kind == ENG_LIMEX || im->view.kind == ENG_MCCLELLAN || im->view.kind == ENG_SHENG || im->view.kind == ENG_MULTI) && s->h_ctl[7] > s->recs2.cap) {  // event queue overflow: grow, scan again
+        if ((im->view.kind == ENG_LIMEX || im->view.kind == ENG_MCCLELLAN || im->view.kind == ENG_SHENG || !im->subs.empty()) && s->h_ctl[7] > s->recs2.cap) {  // event queue overflow: grow, scan again
             if (attempt >= 3) return HS_NOMEM;
             st.arena_retries++;
             s->lx_event_hint = s->h_ctl[7] + s->h_ctl[7] / 8 + 1024;

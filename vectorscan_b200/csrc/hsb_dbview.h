@@ -301,11 +301,11 @@ inline int parse_single_outfix(DbView &d, std::string &why) {
 // started by blockInitSufPQ and caught up to the end of the block, src/rose/catchup.c:560-672).  Accepted when there is
 // nothing else for Rose to orchestrate: no anchored / floating / EOD / delay-rebuild / small-block matcher, no roles, no
 // leftfixes, no MPV, no EOD program, no delayed or anchored literals.  Each queue's engine is censused like a sole outfix.
-inline int parse_outfix_rose(DbView &d, std::string &why) {
+inline int full_rose_gates(const DbView &d, std::string &why) {
     const u8 *r = d.bc;
-    if (rd32(r, rose::amatcherOffset) || rd32(r, rose::fmatcherOffset) || rd32(r, rose::ematcherOffset) ||
-        rd32(r, rose::drmatcherOffset) || rd32(r, rose::sbmatcherOffset) || rd32(r, rose::longLitTableOffset)) {
-        why = "full-Rose databases with literal matchers (roles, leftfixes, delayed literals) are not supported yet";
+    if (rd32(r, rose::amatcherOffset) || rd32(r, rose::ematcherOffset) || rd32(r, rose::drmatcherOffset) ||
+        rd32(r, rose::sbmatcherOffset) || rd32(r, rose::longLitTableOffset)) {
+        why = "full-Rose databases with anchored / EOD / delay-rebuild / small-block matchers or long literals are not supported yet";
         return E_ARCH;
     }
     const u32 nq = rd32(r, rose::queueCount);
@@ -313,13 +313,27 @@ inline int parse_outfix_rose(DbView &d, std::string &why) {
         rd32(r, rose::eodProgramOffset) || rd8(r, rose::requiresEodCheck) || rd32(r, rose::delay_count) ||
         rd32(r, rose::anchored_count) || rd32(r, rose::initMpvNfa) != 0xffffffffu || rd32(r, rose::outfixBeginQueue) ||
         rd32(r, rose::outfixEndQueue) != nq || rd32(r, rose::leftfixBeginQueue) != nq || rd32(r, rose::somLocationCount)) {
-        why = "full-Rose database with more than outfix engines (roles, leftfixes, MPV, EOD program) is not supported yet";
+        why = "full-Rose database with roles, leftfixes, MPV, delayed literals or an EOD program is not supported yet";
         return E_ARCH;
     }
-    if (!nq || nq > 4096) { why = "outfix queue count out of range"; return E_INVALID; }
+    if (rd32(r, rose::fmatcherOffset) &&
+        (rd8(r, rose::noFloatingRoots) || rd32(r, rose::floatingMinDistance) || rd32(r, rose::floatingDistance) != rose::BOUND_INF ||
+         rd32(r, rose::fmatcherMaxBiAnchoredWidth) != rose::BOUND_INF)) {
+        why = "floating matcher with a distance window is not supported yet";
+        return E_ARCH;
+    }
+    if (nq > 4096) { why = "outfix queue count out of range"; return E_INVALID; }
+    return E_SUCCESS;
+}
+
+// The outfix engines of a full-Rose database (src/rose/block.c:345-422: every outfix is started by blockInitSufPQ and
+// caught up to the end of the block, src/rose/catchup.c:560-672), one view per queue, each censused like a sole outfix.
+inline int parse_outfix_queues(DbView &d, std::string &why) {
+    const u8 *r = d.bc;
+    const u32 nq = rd32(r, rose::queueCount);
     const u32 info_off = rd32(r, rose::nfaInfoOffset);
     if (!in_range(d, info_off, (size_t)nfainfo::SIZE * nq)) { why = "NfaInfo array outside bytecode"; return E_INVALID; }
-    std::set<u32> progs;
+    std::set<u32> progs(d.programs.begin(), d.programs.end());
     for (u32 qi = 0; qi < nq; qi++) {
         DbView e;
         e.bc = d.bc; e.bc_len = d.bc_len; e.crc = d.crc;
@@ -334,6 +348,14 @@ inline int parse_outfix_rose(DbView &d, std::string &why) {
         d.engines.push_back(std::move(e));
     }
     d.programs.assign(progs.begin(), progs.end());
+    return E_SUCCESS;
+}
+
+// Full-Rose database whose only engines are outfixes: nothing else for Rose to orchestrate.
+inline int parse_outfix_rose(DbView &d, std::string &why) {
+    if (!rd32(d.bc, rose::queueCount)) { why = "full-Rose database with neither a literal matcher nor engines"; return E_INVALID; }
+    const int rv = parse_outfix_queues(d, why);
+    if (rv != E_SUCCESS) return rv;
     d.kind = ENG_MULTI;
     return E_SUCCESS;
 }
@@ -444,7 +466,13 @@ inline int parse_database(const void *db, DbView &d, std::string &why) {
     d.dkey_count = rd32(r, rose::dkeyCount);
     d.groups = rd64(r, rose::initialGroups) & rd64(r, rose::floating_group_mask);
     if (impl == rose::RUNTIME_SINGLE_OUTFIX) return parse_single_outfix(d, why);
-    if (impl == rose::RUNTIME_FULL_ROSE) return parse_outfix_rose(d, why);
+    if (impl == rose::RUNTIME_FULL_ROSE) {
+        // supported shapes: outfix engines only; a floating literal matcher (programs through the full interpreter,
+        // roseFloatingCallback src/rose/match.c:479-523); both (literal matches and engine matches merge by offset)
+        const int grv = full_rose_gates(d, why);
+        if (grv != E_SUCCESS) return grv;
+        if (!rd32(r, rose::fmatcherOffset)) return parse_outfix_rose(d, why);
+    }
     d.hwlm_off = rd32(r, rose::fmatcherOffset);
     if (!d.hwlm_off || !in_range(d, d.hwlm_off, hwlm::BODY + 24)) { why = "no floating literal matcher"; return E_INVALID; }
     const u8 type = rd8(r, d.hwlm_off + hwlm::type);
@@ -532,6 +560,7 @@ inline int parse_database(const void *db, DbView &d, std::string &why) {
         if (rv != E_SUCCESS) return rv;
         d.programs.push_back(p);
     }
+    if (impl == rose::RUNTIME_FULL_ROSE && rd32(r, rose::queueCount)) return parse_outfix_queues(d, why);
     return E_SUCCESS;
 }
 

@@ -22,6 +22,7 @@
 //   database header   src/database.h:103-114, src/database.c:88-106,178-197
 #include "hsb_layout.h"
 #include "hs_litdb.h"
+#include "outfix_engines.h"
 
 #include <algorithm>
 #include <cmath>
@@ -99,6 +100,10 @@ struct FullLit {
 
 struct BuildExt {
     bool included_jump = false, avx512 = false;
+    bool full_rose = false;  // runtimeImpl = FULL_ROSE: literal matches run through the full roseRunProgram
+    std::vector<hsb_nfadb::Pattern> regexes;  // outfix engines beside the floating literal matcher (implies full_rose)
+    unsigned regex_engine = HSB_REGEX_ENGINE_MCCLELLAN;
+    u32 dfa_states = 0;
     u64 groups_off = 0;
     u32 max_bi_anchored_width = 0;
 };
@@ -641,8 +646,8 @@ std::vector<u8> build_noodle(const HwlmLit &l) {
 // CHECK_MASK_64 (makeRoleByte :969, makeRoleMask :989, makeRoleMask32 :1034, makeRoleMask64 :1074); class entries ->
 // the shufti family (makeRoleShufti :1380, mask layout getShuftiMasks :1190 / nibMaskUpdate :1175).  `fails` receives
 // (instruction offset, offset of its fail_jump operand) so the caller can aim it at the end of the block.
-bool emit_look(Buf &rose, const std::vector<Look> &look, bool avx512, std::vector<std::pair<size_t, size_t>> &fails,
-               std::string &err) {
+bool emit_look(Buf &rose, const std::vector<Look> &look, bool avx512, bool full_rose,
+               std::vector<std::pair<size_t, size_t>> &fails, std::string &err) {
     if (look.empty()) return true;
     const int base = look.front().offset, span = look.back().offset - base + 1;
     bool any_class = false;
@@ -701,6 +706,8 @@ bool emit_look(Buf &rose, const std::vector<Look> &look, bool avx512, std::vecto
         err = "lookaround spans more bytes than any mask instruction of the target holds";
         return false;
     }
+    // roseRunProgram_l, the interpreter of pure-literal databases, has no CHECK_SHUFTI_* case (program_runtime.c:3083-3504)
+    if (!full_rose) { err = "class lookaround needs a full-Rose database (the pure-literal interpreter has no CHECK_SHUFTI)"; return false; }
     // shufti family: a bucket = one (high-nibble set) x (low-nibble set) product; a class is the union of its products
     if (span > (avx512 ? 64 : 32)) { err = "class lookaround spans more bytes than a shufti instruction holds"; return false; }
     std::map<u32, u32> bucket_of;  // (hi set << 16 | lo set) -> bucket index
@@ -822,6 +829,10 @@ int build(const std::vector<FullLit> &fulls_in, const hsb_lit_options &opt, cons
     for (auto &f : fulls)
         if (f.s.empty()) { err = "empty literal"; return HSB_LIT_COMPILER_ERROR; }
 
+    const bool full_rose = bx.full_rose || !bx.regexes.empty();
+    for (auto &p : bx.regexes)
+        for (auto &f : fulls)
+            if (f.report == p.id) { err = "a report id belongs either to literals or to regexes"; return HSB_LIT_COMPILER_ERROR; }
     // exhaustion keys: one per SINGLEMATCH report id; dedupe keys: report ids reachable from more
     // than one distinct literal (the same (id, to) could otherwise be delivered twice)
     std::map<u32, u32> ekeys, dkeys;
@@ -953,6 +964,12 @@ int build(const std::vector<FullLit> &fulls_in, const hsb_lit_options &opt, cons
     for (auto &fr : frags) {
         rose.align(op::ALIGN);
         fr.program = (u32)rose.size();
+        if (!bx.regexes.empty()) {
+            // outfix engines must deliver their earlier matches first (makeCatchup, rose_build_program.cpp; CATCH_UP ->
+            // roseCatchUpTo, program_runtime.c:2499-2504)
+            size_t o = rose.grow(op::SIZE_1);
+            wr8(rose.at(o), 0, op::CATCH_UP);
+        }
         bool any_check_groups = false;
         for (u32 i : fr.fulls) any_check_groups |= fulls[i].check_groups;
         if (any_check_groups) {
@@ -962,11 +979,11 @@ int build(const std::vector<FullLit> &fulls_in, const hsb_lit_options &opt, cons
         }
         const bool squash = fr.fulls.size() == 1 && fulls[fr.fulls[0]].want_squash && fulls[fr.fulls[0]].single &&
                             group_users[fr.group] == 1;
-        const bool trailing = squash || fr.child >= 0;
+        const bool trailing = squash || fr.child >= 0;  // (FINAL_REPORT only closes a program that has nothing behind it)
         for (size_t bi = 0; bi < fr.fulls.size(); bi++) {
             const FullLit &f = fulls[fr.fulls[bi]];
             std::vector<std::pair<size_t, size_t>> fails;
-            if (!emit_look(rose, f.look, bx.avx512, fails, err)) return HSB_LIT_COMPILER_ERROR;
+            if (!emit_look(rose, f.look, bx.avx512, full_rose, fails, err)) return HSB_LIT_COMPILER_ERROR;
             if (f.s.size() > 8) {
                 size_t o = rose.grow(op::check_lit::SIZE);
                 wr8(rose.at(o), 0, f.nocase ? op::CHECK_MED_LIT_NOCASE : op::CHECK_MED_LIT);
@@ -1088,28 +1105,93 @@ int build(const std::vector<FullLit> &fulls_in, const hsb_lit_options &opt, cons
     // engine header
     u32 min_width = ~0u;
     for (auto &f : fulls) min_width = std::min<u32>(min_width, (u32)f.s.size());
+    const u32 fmatcher_min_width = min_width;
+
+    // Outfix engines beside the literal matcher (mixed literal + regex sets): report programs, one engine per queue,
+    // NfaInfo array, state_init plan -- the layout of nfadb_writer.cpp build_rose.
+    u32 n_queues = 0, nfa_info_off = 0, leaf_bytes = 0, scratch_total = 0, total_dkeys = (u32)dkeys.size();
+    u32 plan_u64_off = 0, plan_u64_n = 0, plan_u8_off = 0, plan_u8_n = 0;
+    std::vector<hsb_nfadb::EngineBlob> blobs;
+    std::vector<u32> nfa_at;
+    const u32 leaf_off = 1;
+    if (!bx.regexes.empty()) {
+        std::map<u32, u32> rdkeys;  // regex report id -> dedupe key, numbered behind the literal ones
+        for (auto &p : bx.regexes) if (!rdkeys.count(p.id)) { const u32 k = total_dkeys++; rdkeys[p.id] = k; }
+        rose.align(8);
+        inv_dkey_off = (u32)rose.grow(4 * (size_t)total_dkeys);
+        for (auto &d : dkeys) wr32(rose.at(inv_dkey_off), 4 * d.second, d.first);
+        for (auto &d : rdkeys) wr32(rose.at(inv_dkey_off), 4 * d.second, d.first);
+        std::vector<u32> program_of(bx.regexes.size());
+        for (size_t pi = 0; pi < bx.regexes.size(); pi++) {
+            rose.align(op::ALIGN);
+            const u32 o = (u32)rose.grow(op::dedupe_and_report::SIZE + op::SIZE_1);
+            program_of[pi] = o;
+            wr8(rose.at(o), 0, op::DEDUPE_AND_REPORT);
+            wr32(rose.at(o), op::dedupe_and_report::dkey, rdkeys[bx.regexes[pi].id]);
+            wr32(rose.at(o), op::dedupe_and_report::onmatch, bx.regexes[pi].id);
+            wr32(rose.at(o), op::dedupe_and_report::fail_jump, (u32)op::dedupe_and_report::SIZE);
+            wr8(rose.at(o + op::dedupe_and_report::SIZE), 0, op::END);
+        }
+        if (hsb_nfadb::build_outfix_engines(bx.regexes, bx.regex_engine, bx.dfa_states, program_of, blobs, err) != HSB_LIT_SUCCESS)
+            return HSB_LIT_COMPILER_ERROR;
+        n_queues = (u32)blobs.size();
+        leaf_bytes = mmbit_size(n_queues);
+        rose.align(4);
+        nfa_info_off = (u32)rose.grow((size_t)nfainfo::SIZE * n_queues);
+        for (u32 qi = 0; qi < n_queues; qi++) {
+            rose.align(CACHELINE);
+            const u32 at = (u32)rose.grow(blobs[qi].bytes.size());
+            std::memcpy(rose.at(at), blobs[qi].bytes.data(), blobs[qi].bytes.size());
+            nfa_at.push_back(at);
+            min_width = std::min(min_width, blobs[qi].min_width);
+        }
+        rose.align(CACHELINE);
+        u32 b = 0;
+        if (n_queues > 256) {  // hierarchical multibit: clearing the root block empties it (src/util/multibit.h:332-343)
+            plan_u64_off = (u32)rose.size();
+            wr32(rose.at(rose.grow(16)), 0, leaf_off);
+            plan_u64_n = 1;
+            b = leaf_bytes;
+        } else if (leaf_bytes >= 8) {
+            plan_u64_off = (u32)rose.size();
+            for (; b + 8 <= leaf_bytes; b += 8) { wr32(rose.at(rose.grow(16)), 0, leaf_off + b); plan_u64_n++; }
+        }
+        if (b < leaf_bytes) {
+            plan_u8_off = (u32)rose.size();
+            for (; b < leaf_bytes; b++) { wr32(rose.at(rose.grow(8)), 0, leaf_off + b); plan_u8_n++; }
+        }
+        rose.align(CACHELINE);
+    }
+
     u8 *r = rose.at(0);
-    wr8(r, rose::pureLiteral, 1);
-    wr8(r, rose::runtimeImpl, rose::RUNTIME_PURE_LITERAL);
-    wr8(r, rose::canExhaust, all_exhaustible ? 1 : 0);
+    wr8(r, rose::pureLiteral, full_rose ? 0 : 1);
+    wr8(r, rose::runtimeImpl, full_rose ? rose::RUNTIME_FULL_ROSE : rose::RUNTIME_PURE_LITERAL);
+    wr8(r, rose::hasOutfixesInSmallBlock, n_queues ? 1 : 0);
+    wr8(r, rose::canExhaust, all_exhaustible && bx.regexes.empty() ? 1 : 0);
     wr32(r, rose::mode, MODE_BLOCK);
     wr32(r, rose::ekeyCount, (u32)ekeys.size());
-    wr32(r, rose::dkeyCount, (u32)dkeys.size());
-    wr32(r, rose::dkeyLogSize, fatbit_size((u32)dkeys.size()));
+    wr32(r, rose::dkeyCount, total_dkeys);
+    wr32(r, rose::dkeyLogSize, fatbit_size(total_dkeys));
     wr32(r, rose::invDkeyOffset, inv_dkey_off);
     wr32(r, rose::somLocationFatbitSize, fatbit_size(0));
     wr32(r, rose::fmatcherOffset, fmatcher);
-    wr32(r, rose::fmatcherMinWidth, min_width);
+    wr32(r, rose::fmatcherMinWidth, fmatcher_min_width);
     wr32(r, rose::amatcherMaxBiAnchoredWidth, rose::BOUND_INF);
     wr32(r, rose::fmatcherMaxBiAnchoredWidth, rose::BOUND_INF);
-    wr32(r, rose::activeQueueArraySize, fatbit_size(0));
+    wr32(r, rose::activeArrayCount, n_queues);
+    wr32(r, rose::queueCount, n_queues);
+    wr32(r, rose::activeQueueArraySize, fatbit_size(n_queues));
+    wr32(r, rose::nfaInfoOffset, nfa_info_off);
+    wr32(r, rose::outfixBeginQueue, 0);
+    wr32(r, rose::outfixEndQueue, n_queues);
+    wr32(r, rose::leftfixBeginQueue, n_queues);
     wr32(r, rose::handledKeyFatbitSize, fatbit_size(0));
     wr32(r, rose::minWidth, min_width);
     wr32(r, rose::minWidthExcludingBoundaries, min_width);
     wr32(r, rose::maxBiAnchoredWidth, bx.max_bi_anchored_width ? bx.max_bi_anchored_width : rose::BOUND_INF);
     wr32(r, rose::floatingDistance, rose::BOUND_INF);
     wr32(r, rose::smallBlockDistance, 0);
-    wr32(r, rose::floatingMinLiteralMatchOffset, min_width);
+    wr32(r, rose::floatingMinLiteralMatchOffset, full_rose ? 0 : fmatcher_min_width);
     u64 all_groups = 0;
     u32 top_group = 0;
     for (auto &fr : frags) { all_groups |= 1ull << fr.group; top_group = std::max(top_group, fr.group); }
@@ -1126,6 +1208,8 @@ int build(const std::vector<FullLit> &fulls_in, const hsb_lit_options &opt, cons
         u8 *so = r + rose::stateOffsets;
         u32 cur = 1;
         wr32(so, rose::so::activeLeafArray, cur);
+        wr32(so, rose::so::activeLeafArray_size, leaf_bytes);
+        cur += leaf_bytes;
         wr32(so, rose::so::activeLeftArray, cur);
         wr32(so, rose::so::longLitState, cur);
         wr32(so, rose::so::leftfixLagTable, cur);
@@ -1140,7 +1224,21 @@ int build(const std::vector<FullLit> &fulls_in, const hsb_lit_options &opt, cons
         wr32(so, rose::so::logicalVec, cur);
         wr32(so, rose::so::combVec, cur);
         wr32(so, rose::so::nfaStateBegin, cur);
+        for (u32 qi = 0; qi < n_queues; qi++) {
+            u8 *ni = rose.at(nfa_info_off + (size_t)nfainfo::SIZE * qi);
+            wr32(ni, nfainfo::nfaOffset, nfa_at[qi]);
+            wr32(ni, nfainfo::stateOffset, cur);
+            scratch_total = (u32)round_up(scratch_total, 64);
+            wr32(ni, nfainfo::fullStateOffset, scratch_total);
+            cur += blobs[qi].stream_state;
+            scratch_total += blobs[qi].scratch_state;
+        }
         wr32(so, rose::so::end, cur);
+        wr32(r, rose::stateSize, cur);
+        wr32(r, rose::scratchStateSize, (u32)round_up(scratch_total, 64));
+        u8 *sp = r + rose::state_init;  // struct scatter_full_plan (src/util/scatter.h:43-52)
+        wr32(sp, 0, plan_u64_off); wr32(sp, 4, plan_u64_n);
+        wr32(sp, 24, plan_u8_n); wr32(sp, 28, plan_u8_off);
     }
 
     // database header; the image sits at a 64-byte aligned address with the bytecode at offset 64
@@ -1168,10 +1266,11 @@ char *dup_error(const std::string &s) {
 
 extern "C" {
 
-int hsb_compile_lit_multi_ext(const char *const *expressions, const unsigned *flags, const unsigned *ids,
-                              const size_t *lens, const hsb_lit_ext *ext, unsigned elements, unsigned mode,
-                              const hsb_lit_options *options, const hsb_lit_build_ext *build_ext,
-                              hs_database_t **db, char **error) {
+int hsb_compile_mixed(const char *const *expressions, const unsigned *flags, const unsigned *ids,
+                      const size_t *lens, const hsb_lit_ext *ext, unsigned elements,
+                      const char *const *regexes, const unsigned *regex_flags, const unsigned *regex_ids, unsigned n_regexes,
+                      unsigned mode, const hsb_lit_options *options, const hsb_lit_build_ext *build_ext,
+                      unsigned regex_engine, unsigned dfa_states, hs_database_t **db, char **error) {
     if (error) *error = nullptr;
     if (!db) return HSB_LIT_COMPILER_ERROR;
     *db = nullptr;
@@ -1188,6 +1287,14 @@ int hsb_compile_lit_multi_ext(const char *const *expressions, const unsigned *fl
         bx.groups_off = build_ext->groups_off;
         bx.max_bi_anchored_width = build_ext->max_bi_anchored_width;
     }
+    bx.full_rose = true;  // literal matches go through the full roseRunProgram (src/rose/match.c:479-523 -> program_runtime.c:2241)
+    bx.regex_engine = regex_engine;
+    bx.dfa_states = dfa_states;
+    for (unsigned i = 0; i < n_regexes; i++) {
+        if (!regexes || !regexes[i]) return fail("null regular expression");
+        bx.regexes.push_back({regexes[i], regex_flags ? regex_flags[i] : 0, regex_ids ? regex_ids[i] : 0});
+    }
+    if (build_ext && build_ext->reserved_pure_literal) bx.full_rose = !bx.regexes.empty();
     std::vector<FullLit> fulls;
     for (unsigned i = 0; i < elements; i++) {
         unsigned f = flags ? flags[i] : 0;
@@ -1225,6 +1332,17 @@ int hsb_compile_lit_multi_ext(const char *const *expressions, const unsigned *fl
     std::memcpy(mem, image.data(), image.size());
     *db = (hs_database_t *)mem;
     return HSB_LIT_SUCCESS;
+}
+
+int hsb_compile_lit_multi_ext(const char *const *expressions, const unsigned *flags, const unsigned *ids,
+                              const size_t *lens, const hsb_lit_ext *ext, unsigned elements, unsigned mode,
+                              const hsb_lit_options *options, const hsb_lit_build_ext *build_ext,
+                              hs_database_t **db, char **error) {
+    hsb_lit_build_ext bx{};
+    if (build_ext) bx = *build_ext;
+    bx.reserved_pure_literal = 1;
+    return hsb_compile_mixed(expressions, flags, ids, lens, ext, elements, nullptr, nullptr, nullptr, 0, mode, options, &bx,
+                             0, 0, db, error);
 }
 
 int hsb_compile_lit_multi(const char *const *expressions, const unsigned *flags, const unsigned *ids,

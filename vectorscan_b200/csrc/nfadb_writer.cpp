@@ -363,8 +363,8 @@ struct Glushkov {
 
 }  // namespace
 
+#include "outfix_engines.h"
 namespace hsb_nfadb {
-struct Pattern { std::string expr; unsigned flags; unsigned id; };
 int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<hsb::u8> &image, std::string &err);
 int build_rose(const std::vector<Pattern> &pats, unsigned engine, hsb::u32 dfa_states, std::vector<hsb::u8> &image, std::string &err);
 }
@@ -1157,7 +1157,8 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
 // Grouping: patterns join the current group while its determinised automaton stays within `dfa_states` states; a pattern
 // whose own DFA is larger goes to a LimEx group (<= 512 NFA states) -- the reference's own fallback when McClellan
 // construction fails (src/nfagraph/ng_limex.cpp / ng_mcclellan.cpp state limits).
-int build_rose(const std::vector<Pattern> &pats, unsigned engine, u32 dfa_states, std::vector<u8> &image, std::string &err) {
+int build_outfix_engines(const std::vector<Pattern> &pats, unsigned engine, u32 dfa_states,
+                         const std::vector<u32> &program_of, std::vector<EngineBlob> &out, std::string &err) {
     if (engine != HSB_REGEX_ENGINE_LIMEX && engine != HSB_REGEX_ENGINE_MCCLELLAN && engine != HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN) {
         err = "outfix engines are LimEx or McClellan";
         return HSB_LIT_COMPILER_ERROR;
@@ -1217,9 +1218,25 @@ int build_rose(const std::vector<Pattern> &pats, unsigned engine, u32 dfa_states
         }
         if (!cur.empty()) groups.push_back({cur, HSB_REGEX_ENGINE_LIMEX});
     }
-    const u32 N = (u32)groups.size();
-    if (N > 4096) { err = "more than 4096 engines"; return HSB_LIT_COMPILER_ERROR; }
+    if (groups.size() > 4096) { err = "more than 4096 engines"; return HSB_LIT_COMPILER_ERROR; }
+    for (u32 qi = 0; qi < groups.size(); qi++) {
+        Automaton am;
+        size_t total = 0;
+        if (!make_automaton(parsed, groups[qi].members, am, total)) { err = "internal: group too large"; return HSB_LIT_COMPILER_ERROR; }
+        Buf eng;
+        EngineBlob blob;
+        if (emit_engine(am, groups[qi].engine, program_of, 4 * (mcclellan::STATE_MASK + 1), eng, blob.stream_state, blob.scratch_state, err) != HSB_LIT_SUCCESS)
+            return HSB_LIT_COMPILER_ERROR;
+        wr32(eng.at(0), nfa::queueIndex, qi);
+        blob.bytes = eng.b;
+        blob.min_width = am.min_width;
+        out.push_back(std::move(blob));
+    }
+    return HSB_LIT_SUCCESS;
+}
 
+int build_rose(const std::vector<Pattern> &pats, unsigned engine, u32 dfa_states, std::vector<u8> &image, std::string &err) {
+    if (pats.empty()) { err = "no expressions"; return HSB_LIT_COMPILER_ERROR; }
     Buf rose;
     rose.grow(rose::SIZE);
     rose.align(CACHELINE);
@@ -1239,6 +1256,9 @@ int build_rose(const std::vector<Pattern> &pats, unsigned engine, u32 dfa_states
         wr32(rose.at(o), op::dedupe_and_report::fail_jump, (u32)op::dedupe_and_report::SIZE);
         wr8(rose.at(o + op::dedupe_and_report::SIZE), 0, op::END);
     }
+    std::vector<EngineBlob> blobs;
+    if (build_outfix_engines(pats, engine, dfa_states, program_of, blobs, err) != HSB_LIT_SUCCESS) return HSB_LIT_COMPILER_ERROR;
+    const u32 N = (u32)blobs.size();
     rose.align(4);
     const u32 nfa_info_off = (u32)rose.grow((size_t)nfainfo::SIZE * N);
     // state layout: status byte, active leaf multibit of N queues, then every engine's stream state
@@ -1247,25 +1267,18 @@ int build_rose(const std::vector<Pattern> &pats, unsigned engine, u32 dfa_states
     const u32 nfa_state_begin = cur_state;
     u32 scratch_total = 0, min_width = ~0u;
     for (u32 qi = 0; qi < N; qi++) {
-        Automaton am;
-        size_t total = 0;
-        if (!make_automaton(parsed, groups[qi].members, am, total)) { err = "internal: group too large"; return HSB_LIT_COMPILER_ERROR; }
-        Buf eng;
-        u32 stream_state = 0, scratch_state = 0;
-        if (emit_engine(am, groups[qi].engine, program_of, 4 * (mcclellan::STATE_MASK + 1), eng, stream_state, scratch_state, err) != HSB_LIT_SUCCESS)
-            return HSB_LIT_COMPILER_ERROR;
-        wr32(eng.at(0), nfa::queueIndex, qi);
+        const EngineBlob &blob = blobs[qi];
         rose.align(CACHELINE);
-        const u32 nfa_off = (u32)rose.grow(eng.size());
-        std::memcpy(rose.at(nfa_off), eng.b.data(), eng.size());
+        const u32 nfa_off = (u32)rose.grow(blob.bytes.size());
+        std::memcpy(rose.at(nfa_off), blob.bytes.data(), blob.bytes.size());
         u8 *ni = rose.at(nfa_info_off + (size_t)nfainfo::SIZE * qi);
         wr32(ni, nfainfo::nfaOffset, nfa_off);
         wr32(ni, nfainfo::stateOffset, cur_state);
         scratch_total = (u32)round_up(scratch_total, 64);
         wr32(ni, nfainfo::fullStateOffset, scratch_total);
-        cur_state += stream_state;
-        scratch_total += scratch_state;
-        min_width = std::min(min_width, am.min_width);
+        cur_state += blob.stream_state;
+        scratch_total += blob.scratch_state;
+        min_width = std::min(min_width, blob.min_width);
     }
     rose.align(CACHELINE);
     // state_init: clear the active leaf array (8-byte stores, then single bytes)

@@ -32,7 +32,7 @@ class LitExt(C.Structure):
 
 class LitBuildExt(C.Structure):
     _fields_ = [("included_jump", C.c_int), ("target_avx512", C.c_int), ("groups_off", C.c_ulonglong),
-                ("max_bi_anchored_width", C.c_uint)]
+                ("max_bi_anchored_width", C.c_uint), ("reserved_pure_literal", C.c_uint)]
 
 
 EXT_CHECK_GROUPS, EXT_SQUASH_GROUP, EXT_QUIET = 1, 2, 4
@@ -56,6 +56,12 @@ def lib():
                                                 C.POINTER(LitOptions), C.POINTER(LitBuildExt),
                                                 C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
         L.hsb_compile_lit_multi_ext.restype = C.c_int
+        L.hsb_compile_mixed.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_uint), C.POINTER(C.c_uint),
+                                        C.POINTER(C.c_size_t), C.POINTER(LitExt), C.c_uint,
+                                        C.POINTER(C.c_char_p), C.POINTER(C.c_uint), C.POINTER(C.c_uint), C.c_uint, C.c_uint,
+                                        C.POINTER(LitOptions), C.POINTER(LitBuildExt), C.c_uint, C.c_uint,
+                                        C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+        L.hsb_compile_mixed.restype = C.c_int
         L.hsb_compile_regex_multi.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_uint), C.POINTER(C.c_uint), C.c_uint,
                                               C.c_uint, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
         L.hsb_compile_regex_multi.restype = C.c_int
@@ -148,7 +154,8 @@ class Database:
 
 def compile_lit_multi(literals, flags=None, ids=None, mode=HS_MODE_BLOCK, engine=ENGINE_AUTO, fdr_domain=0,
                       fdr_stride=0, teddy_masks=0, no_flood=0, ext=None, included_jump=0, target_avx512=0,
-                      groups_off=0, max_bi_anchored_width=0):
+                      groups_off=0, max_bi_anchored_width=0, full_rose=False, regexes=None, regex_flags=None,
+                      regex_ids=None, regex_engine=1, dfa_states=0):
     """literals: list of bytes. Returns Database. Same argument meaning as hs_compile_lit_multi.
     ext: optional per-literal dicts {"look": [(offset, and, cmp, negate) | (offset, class_bitmap32)], "group": g,
     "flags": EXT_*} (include/hs_litdb.h, hsb_lit_ext); the remaining keywords are hsb_lit_build_ext."""
@@ -181,10 +188,20 @@ def compile_lit_multi(literals, flags=None, ids=None, mode=HS_MODE_BLOCK, engine
                 extv[i].look_count = len(look)
             extv[i].group = e.get("group", 0)
             extv[i].flags = e.get("flags", 0)
-    bx = LitBuildExt(included_jump, target_avx512, groups_off, max_bi_anchored_width)
+    bx = LitBuildExt(included_jump, target_avx512, groups_off, max_bi_anchored_width, 0)
     db, err = C.c_void_p(), C.c_void_p()
-    rv = lib().hsb_compile_lit_multi_ext(arr, fl, idv, lens, extv, n, mode, C.byref(opt), C.byref(bx), C.byref(db),
-                                         C.byref(err))
+    if full_rose or regexes:
+        # hsb_compile_mixed: a full-Rose database, the regexes (if any) as outfix engines beside the literal matcher
+        rx = [e.encode("latin-1") if isinstance(e, str) else bytes(e) for e in (regexes or [])]
+        m = len(rx)
+        rarr = (C.c_char_p * max(1, m))(*rx)
+        rfl = (C.c_uint * max(1, m))(*(regex_flags if regex_flags is not None else [0] * m))
+        rid = (C.c_uint * max(1, m))(*(regex_ids if regex_ids is not None else list(range(m))))
+        rv = lib().hsb_compile_mixed(arr, fl, idv, lens, extv, n, rarr, rfl, rid, m, mode, C.byref(opt), C.byref(bx),
+                                     regex_engine, dfa_states, C.byref(db), C.byref(err))
+    else:
+        rv = lib().hsb_compile_lit_multi_ext(arr, fl, idv, lens, extv, n, mode, C.byref(opt), C.byref(bx), C.byref(db),
+                                             C.byref(err))
     if rv != 0:
         msg = C.string_at(err).decode() if err else "error"
         if err:
