@@ -1685,7 +1685,7 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
             rv = launch_outfixes(s, im, cp, ar);
             if (rv != HS_SUCCESS) return rv;
         }
-        st.front_end = t2w ? 3u : use_turbo ? 2u : im->view.kind == ENG_LIMEX ? 4u
+        st.front_end = !im->subs.empty() ? 6u : t2w ? 3u : use_turbo ? 2u : im->view.kind == ENG_LIMEX ? 4u
                      : (im->view.kind == ENG_MCCLELLAN || im->view.kind == ENG_SHENG) ? 5u : im->view.kind == ENG_MULTI ? 6u : 1u;
         CU_OK(cudaEventRecord(s->ev[7], s->stream));
         st.scan_launches++;
