@@ -47,6 +47,8 @@ typedef struct hsb_lit_options {
     int fdr_stride;  /* 1, 2, 4, 0 = chooseEngine's pick */
     int teddy_masks; /* 1..4, 0 = chooseTeddyEngine's pick */
     int no_flood;    /* 1 = Grey::fdrAllowFlood off */
+    int teddy_fat;   /* with engine = TEDDY: 1 = the 16-bucket "fat" Teddy an AVX2 target gets (engines 3-10,
+                        src/fdr/teddy_engine_description.cpp:52-62; up to 96 fragments); needs an AVX2 runtime build */
 } hsb_lit_options;
 
 /* Same parameter meaning as hs_compile_lit_multi; `platform` is replaced by `options` (the blob is

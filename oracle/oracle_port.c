@@ -249,15 +249,20 @@ static u32 fdr_candidates(const u8 *fdr, const struct scan_state *s, u32 e) {
     return (u8)~st;
 }
 
-/* Teddy: r_j[i] = lo_j[c & 15] | hi_j[c >> 4]; candidate buckets at e = ~(OR_j r_j[e - j]) */
-static u32 teddy_candidates(const u8 *teddy, u32 masks, const struct scan_state *s, u32 e) {
+/* Teddy: r_j[i] = lo_j[c & 15] | hi_j[c >> 4]; candidate buckets at e = ~(OR_j r_j[e - j]).  width = 1: 8 buckets;
+ * width = 2 (fat Teddy, fdr/teddy_avx2.c): every mask twice, buckets 0-7 then 8-15 (fdr/teddy_compile.cpp:436-500) */
+static u32 teddy_candidates(const u8 *teddy, u32 masks, u32 width, const struct scan_state *s, u32 e) {
     const u8 *mb = teddy + 64;
-    u8 r = 0;
-    for (u32 j = 0; j < masks && j <= e; j++) {
-        u8 c = s->buf[e - j];
-        r |= (u8)(mb[(2 * j) * 16 + (c & 15)] | mb[(2 * j + 1) * 16 + (c >> 4)]);
+    u32 cand = 0;
+    for (u32 g = 0; g < width; g++) {
+        u8 r = 0;
+        for (u32 j = 0; j < masks && j <= e; j++) {
+            u8 c = s->buf[e - j];
+            r |= (u8)(mb[((2 * j) * width + g) * 16 + (c & 15)] | mb[((2 * j + 1) * width + g) * 16 + (c >> 4)]);
+        }
+        cand |= (u32)(u8)~r << (8 * g);
     }
-    return (u8)~r;
+    return cand;
 }
 
 static int hwlm_exec(struct scan_state *s, const u8 *hwlm) {
@@ -279,7 +284,8 @@ static int hwlm_exec(struct scan_state *s, const u8 *hwlm) {
     for (u32 e = 0; e < s->len; e++) {
         u32 cand;
         if (id == 0) cand = fdr_candidates(eng, s, e);
-        else if (id >= 11 && id <= 18) cand = teddy_candidates(eng, (id - 11) / 2 + 1, s, e);
+        else if (id >= 11 && id <= 18) cand = teddy_candidates(eng, (id - 11) / 2 + 1, 1, s, e);
+        else if (id >= 3 && id <= 10) cand = teddy_candidates(eng, (id - 3) / 2 + 1, 2, s, e);
         else { s->error = 1; return -1; }
         for (u32 b = 0; cand; b++, cand >>= 1)
             if ((cand & 1) && confirm(s, conf_base, b, e) < 0) return -1;

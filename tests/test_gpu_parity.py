@@ -329,3 +329,24 @@ def test_full_size_properties_engines_and_c4(ref, config):
     m2 = gpu.fetch_matches(sc).copy()
     m2["buffer"] += half
     assert n1 + n2 == len(m) and np.array_equal(np.concatenate([m1, m2]), m)
+
+
+@pytest.mark.parametrize("frontend", FRONTENDS)
+def test_fat_teddy_databases(ref, frontend):
+    """16-bucket (AVX2 "fat") Teddy databases: the native front end folds the 16 buckets onto 8 filter bits and confirms
+    both buckets of a bit; the turbo front ends re-encode the LitInfo records as for any other matcher."""
+    rng = random.Random(91 + frontend)
+    ran = 0
+    for trial in range(30):
+        nl = rng.choice([2, 9, 17, 30, 60, 96])
+        alpha = rng.choice([b"abcdefgh", bytes(range(32, 127)), bytes(range(256))])
+        lits, flags, ids, text = litgen.random_case(rng, None, nl, alpha, rng.choice([0, 5, 40, 600, 20000]))
+        try:
+            db = litdb.compile_lit_multi(lits, flags, ids, engine=litdb.ENGINE_TEDDY, teddy_masks=rng.randint(1, 4), teddy_fat=1)
+        except litdb.CompileError:
+            continue
+        got = sorted(gpu_scan(db, text, frontend))
+        assert got == litgen.brute_force(lits, flags, ids, text), (nl, len(text))
+        assert got == sorted((i, t) for (_, i, t) in ref_scan(ref, db, [text]))
+        ran += 1
+    assert ran > 15

@@ -76,3 +76,35 @@ def test_reference_runtime_on_emitted_databases_equals_brute_force(ref, seed):
                 assert rv == 0 and sorted(got) == exp, (n, len(alpha), tl, opts)
                 total += 1
     assert total > 40
+
+
+@pytest.mark.parametrize("seed", [3, 4])
+def test_fat_teddy_databases_on_reference_runtime(ref, seed):
+    """16-bucket "fat" Teddy (engines 3-10: what an AVX2 target gets for up to 96 fragments, teddy_engine_description.cpp:
+    52-62; masks teddy_compile.cpp:436-500, dup masks :355-435): accepted and scanned by the AVX2 / AVX512 builds of the
+    unmodified runtime (fdr_exec_fat_teddy_*, src/fdr/teddy_avx2.c / teddy.c) == brute force."""
+    rng = random.Random(seed)
+    ran, eids = 0, set()
+    for trial in range(60):
+        nl = rng.choice([2, 9, 17, 30, 60, 96])
+        alpha = rng.choice([b"abcdefgh", bytes(range(32, 127)), bytes(range(256))])
+        lits, flags, ids, text = litgen.random_case(rng, None, nl, alpha, rng.choice([0, 5, 40, 600, 5000]))
+        try:
+            db = litdb.compile_lit_multi(lits, flags, ids, engine=litdb.ENGINE_TEDDY, teddy_masks=rng.randint(1, 4), teddy_fat=1)
+        except litdb.CompileError:
+            continue
+        bc = db.bytecode()
+        f = int.from_bytes(bc[96:100], "little")
+        eid = int.from_bytes(bc[f + 192:f + 196], "little")
+        assert 3 <= eid <= 10
+        eids.add(eid)
+        rdb = ref.deserialize(db.serialize())
+        sc = ref.alloc_scratch(rdb)
+        rv, got = ref.scan(rdb, sc, text)
+        ref.L.hs_free_scratch(sc)
+        ref.L.hs_free_database(rdb)
+        assert rv == 0 and sorted(got) == litgen.brute_force(lits, flags, ids, text), (nl, len(text))
+        import oracle_port
+        assert oracle_port.scan(db, text) == (0, got)   # the C restatement: same matches, same callback order
+        ran += 1
+    assert ran > 30 and len(eids) >= 6

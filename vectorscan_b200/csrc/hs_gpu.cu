@@ -536,6 +536,7 @@ __device__ void confirm_entry(const Ctx &c, u32 strip, u64 g, u32 bucket_mask, u
     if (i < 7) v &= ~0ull << (8 * (7 - i));  // bytes before the buffer start read as zero (block mode has no history)
     const u8 *btext = c.cp.text + b.start;
     const u8 *bc = c.db.bc;
+    if (c.db.n_buckets == 16) bucket_mask |= bucket_mask << 8;  // fat Teddy: filter bit b stands for buckets b and b + 8
     while (bucket_mask) {
         const u32 bk = __ffs(bucket_mask) - 1;
         bucket_mask &= bucket_mask - 1;
@@ -1263,6 +1264,15 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         for (u32 cch = 0; cch < 256; cch++) {
             u32 t = 0;
             for (u32 j = 0; j < v.teddy_masks; j++) {
+                if (v.teddy_fat) {
+                    // 16 buckets folded onto 8 filter bits: bit b stays clear ("possible") when bucket b OR bucket b + 8
+                    // admits the byte; confirm_entry then walks both buckets' FDRConfirm (sound: over-approximation only)
+                    const size_t lo0 = v.teddy_mask_off + (size_t)(4 * j) * 16, hi0 = v.teddy_mask_off + (size_t)(4 * j + 2) * 16;
+                    const u8 a = rd8(v.bc, lo0 + (cch & 15)) | rd8(v.bc, hi0 + (cch >> 4));
+                    const u8 b = rd8(v.bc, lo0 + 16 + (cch & 15)) | rd8(v.bc, hi0 + 16 + (cch >> 4));
+                    t |= (u32)(a & b) << (8 * j);
+                    continue;
+                }
                 const u8 lo = rd8(v.bc, v.teddy_mask_off + (size_t)(2 * j) * 16 + (cch & 15));
                 const u8 hi = rd8(v.bc, v.teddy_mask_off + (size_t)(2 * j + 1) * 16 + (cch >> 4));
                 t |= (u32)(lo | hi) << (8 * j);

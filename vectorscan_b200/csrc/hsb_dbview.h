@@ -37,7 +37,7 @@ struct DbView {
     u32 fdr_tab = 0, fdr_domain = 0, fdr_stride = 0;
     u64 fdr_start = 0;
     // Teddy
-    u32 teddy_masks = 0, teddy_mask_off = 0;
+    u32 teddy_masks = 0, teddy_mask_off = 0, teddy_fat = 0;
     // noodle
     u64 nood_msk = 0, nood_cmp = 0;
     u32 nood_len = 0, nood_id = 0;
@@ -514,8 +514,14 @@ inline int parse_database(const void *db, DbView &d, std::string &why) {
             d.teddy_mask_off = d.eng_off + (u32)teddy::MASKS;
             if (!in_range(d, d.teddy_mask_off, (size_t)d.teddy_masks * 32)) { why = "Teddy masks truncated"; return E_INVALID; }
         } else if (d.engine_id >= teddy::FAT_FIRST && d.engine_id <= teddy::FAT_LAST) {
-            why = "16-bucket (AVX2 fat) Teddy tables are not supported; compile for a generic platform";
-            return E_ARCH;
+            // fat Teddy (AVX2 hosts, src/fdr/teddy_avx2.c:452-480): 16 buckets, every nibble mask twice -- buckets 0-7 then
+            // buckets 8-15 (teddy_compile.cpp:436-500, maskWidth = 2); confBase has 16 entries
+            d.kind = ENG_TEDDY;
+            d.teddy_fat = 1;
+            d.n_buckets = 16;
+            d.teddy_masks = (d.engine_id - teddy::FAT_FIRST) / 2 + 1;
+            d.teddy_mask_off = d.eng_off + (u32)teddy::MASKS;
+            if (!in_range(d, d.teddy_mask_off, (size_t)d.teddy_masks * 64)) { why = "fat Teddy masks truncated"; return E_INVALID; }
         } else {
             why = "unknown literal matcher engine id";
             return E_INVALID;

@@ -542,34 +542,43 @@ u32 choose_teddy_masks(const std::vector<HwlmLit> &lits) {
     return best;
 }
 
+// nbuckets = 8: Teddy (engines 11-18); nbuckets = 16: fat Teddy (engines 3-10, AVX2 hosts): every nibble mask is laid out
+// twice, buckets 0-7 then buckets 8-15 (maskWidth 2, teddy_compile.cpp:436-500), and the reinforcement table's place is
+// taken by the "dup" masks -- each 16-byte mask twice in a row (fillDupNibbleMasks :355-435; build :559-620).
 std::vector<u8> build_teddy(const std::vector<HwlmLit> &lits, u32 masks, bool packed, bool allow_flood,
-                            std::string &err) {
+                            std::string &err, u32 nbuckets = 8) {
     std::vector<std::vector<u32>> buckets;
-    if (!pack_teddy(lits, masks, 8, buckets)) { err = "literal set does not pack into 8 Teddy buckets"; return {}; }
-    const size_t mask_len = (size_t)masks * 32;
-    const size_t rtab_len = teddy::REINFORCE_ROWS * 8;
-    std::vector<u8> nib(mask_len, 0xff);
+    if (!pack_teddy(lits, masks, nbuckets, buckets)) { err = "literal set does not pack into the Teddy buckets"; return {}; }
+    const u32 width = nbuckets / 8;
+    const size_t mask_len = (size_t)masks * 32 * width;
+    const size_t rtab_len = width == 1 ? teddy::REINFORCE_ROWS * 8 : mask_len * 2;
+    std::vector<u8> nib(mask_len, 0xff), dup(width == 2 ? mask_len * 2 : 0, 0xff);
     std::vector<u64> reinforce(teddy::REINFORCE_ROWS, 0x00ffffffffffffffull);
-    for (u32 b = 0; b < 8; b++) {
-        const u8 bm = (u8)(1u << b);
+    for (u32 b = 0; b < nbuckets; b++) {
+        const u8 bm = (u8)(1u << (b % 8));
+        const u32 g = b / 8;
         for (u32 li : buckets[b]) {
             const HwlmLit &l = lits[li];
             const u32 sz = (u32)l.s.size();
             for (u32 j = 0; j < masks; j++) {
-                u8 *lo = nib.data() + (size_t)(2 * j) * 16, *hi = nib.data() + (size_t)(2 * j + 1) * 16;
+                const size_t lo_id = (size_t)(2 * j) * width + g, hi_id = (size_t)(2 * j + 1) * width + g;
+                u8 *lo = nib.data() + lo_id * 16, *hi = nib.data() + hi_id * 16;
+                auto clear_lo = [&](u32 n) { lo[n] &= (u8)~bm; if (width == 2) { dup[lo_id * 32 + n] &= (u8)~bm; dup[lo_id * 32 + 16 + n] &= (u8)~bm; } };
+                auto clear_hi = [&](u32 n) { hi[n] &= (u8)~bm; if (width == 2) { dup[hi_id * 32 + n] &= (u8)~bm; dup[hi_id * 32 + 16 + n] &= (u8)~bm; } };
                 if (j >= sz) {
-                    for (int n = 0; n < 16; n++) { lo[n] &= (u8)~bm; hi[n] &= (u8)~bm; }
+                    for (u32 n = 0; n < 16; n++) { clear_lo(n); clear_hi(n); }
                     continue;
                 }
                 u8 c = (u8)l.s[sz - 1 - j];
-                lo[c & 0xf] &= (u8)~bm;
+                clear_lo(c & 0xf);
                 if (l.nocase && is_alpha(c)) {
-                    hi[(c >> 4) & 0xd] &= (u8)~bm;
-                    hi[(c >> 4) | 0x2] &= (u8)~bm;
+                    clear_hi((c >> 4) & 0xd);
+                    clear_hi((c >> 4) | 0x2);
                 } else {
-                    hi[c >> 4] &= (u8)~bm;
+                    clear_hi(c >> 4);
                 }
             }
+            if (width != 1) continue;
             // reinforcement: byte j-1 of row[c] has bit b clear iff a bucket-b literal can have byte c
             // j positions before its end (row index = the byte preceding the vector being scanned)
             for (u32 j = 1; j < 8; j++) {
@@ -589,14 +598,15 @@ std::vector<u8> build_teddy(const std::vector<HwlmLit> &lits, u32 masks, bool pa
     std::vector<u8> out(total, 0);
     u32 max_len = 0;
     for (auto &l : lits) max_len = std::max<u32>(max_len, (u32)l.s.size());
-    wr32(out.data(), fdr::engineID, teddy::ENGINE_FIRST + 2 * (masks - 1) + (packed ? 1 : 0));
+    wr32(out.data(), fdr::engineID, (width == 2 ? teddy::FAT_FIRST : teddy::ENGINE_FIRST) + 2 * (masks - 1) + (packed ? 1 : 0));
     wr32(out.data(), fdr::size, (u32)total);
     wr32(out.data(), fdr::maxStringLen, max_len);
     wr32(out.data(), fdr::numStrings, (u32)lits.size());
     wr32(out.data(), fdr::confOffset, (u32)conf_off);
     wr32(out.data(), fdr::floodOffset, (u32)flood_off);
     std::memcpy(out.data() + teddy::MASKS, nib.data(), mask_len);
-    std::memcpy(out.data() + teddy::MASKS + round_up(mask_len, CACHELINE), reinforce.data(), rtab_len);
+    if (width == 1) std::memcpy(out.data() + teddy::MASKS + round_up(mask_len, CACHELINE), reinforce.data(), rtab_len);
+    else std::memcpy(out.data() + teddy::MASKS + round_up(mask_len, CACHELINE), dup.data(), rtab_len);
     std::memcpy(out.data() + conf_off, confirm.data(), confirm.size());
     std::memcpy(out.data() + flood_off, floodt.data(), floodt.size());
     return out;
@@ -1065,11 +1075,13 @@ int build(const std::vector<FullLit> &fulls_in, const hsb_lit_options &opt, cons
         hwlm_type = hwlm::ENGINE_NOOD;
     } else if (engine_choice == HSB_LIT_ENGINE_TEDDY) {
         u32 masks = opt.teddy_masks ? (u32)opt.teddy_masks : (teddy_sel & 0xff);
-        bool packed = opt.teddy_masks ? hl.size() > 8 : (teddy_sel >> 8) != 0;
+        bool packed = opt.teddy_masks ? hl.size() > (opt.teddy_fat ? 16u : 8u) : (teddy_sel >> 8) != 0;
         if (!masks) { masks = 1; for (auto &l : hl) masks = std::max<u32>(masks, std::min<u32>(3, (u32)l.s.size())); }
         if (masks < 1 || masks > 4) { err = "teddy_masks must be 1..4"; return HSB_LIT_COMPILER_ERROR; }
-        if (hl.size() > 48) { err = "too many literal fragments for Teddy (max 48)"; return HSB_LIT_COMPILER_ERROR; }
-        engine = build_teddy(hl, masks, packed, allow_flood, err);
+        const u32 tb = opt.teddy_fat ? 16u : 8u;
+        if (opt.teddy_fat && !opt.teddy_masks) packed = hl.size() > 16;
+        if (hl.size() > 6 * tb) { err = "too many literal fragments for Teddy (max 6 per bucket)"; return HSB_LIT_COMPILER_ERROR; }
+        engine = build_teddy(hl, masks, packed, allow_flood, err, tb);
         if (engine.empty()) {
             // as fdrBuildProtoInternal does: "build with teddy failed, will try with FDR"
             if (opt.engine != HSB_LIT_ENGINE_AUTO) return HSB_LIT_COMPILER_ERROR;

@@ -18,7 +18,7 @@ ENGINE_AUTO, ENGINE_FDR, ENGINE_TEDDY, ENGINE_NOODLE = 0, 1, 2, 3
 
 class LitOptions(C.Structure):
     _fields_ = [("engine", C.c_int), ("fdr_domain", C.c_int), ("fdr_stride", C.c_int),
-                ("teddy_masks", C.c_int), ("no_flood", C.c_int)]
+                ("teddy_masks", C.c_int), ("no_flood", C.c_int), ("teddy_fat", C.c_int)]
 
 
 class LitLook(C.Structure):
@@ -155,7 +155,7 @@ class Database:
 def compile_lit_multi(literals, flags=None, ids=None, mode=HS_MODE_BLOCK, engine=ENGINE_AUTO, fdr_domain=0,
                       fdr_stride=0, teddy_masks=0, no_flood=0, ext=None, included_jump=0, target_avx512=0,
                       groups_off=0, max_bi_anchored_width=0, full_rose=False, regexes=None, regex_flags=None,
-                      regex_ids=None, regex_engine=1, dfa_states=0):
+                      regex_ids=None, regex_engine=1, dfa_states=0, teddy_fat=0):
     """literals: list of bytes. Returns Database. Same argument meaning as hs_compile_lit_multi.
     ext: optional per-literal dicts {"look": [(offset, and, cmp, negate) | (offset, class_bitmap32)], "group": g,
     "flags": EXT_*} (include/hs_litdb.h, hsb_lit_ext); the remaining keywords are hsb_lit_build_ext."""
@@ -165,7 +165,7 @@ def compile_lit_multi(literals, flags=None, ids=None, mode=HS_MODE_BLOCK, engine
     lens = (C.c_size_t * n)(*[len(x) for x in lits])
     fl = (C.c_uint * n)(*(flags if flags is not None else [0] * n))
     idv = (C.c_uint * n)(*(ids if ids is not None else list(range(n))))
-    opt = LitOptions(engine, fdr_domain, fdr_stride, teddy_masks, no_flood)
+    opt = LitOptions(engine, fdr_domain, fdr_stride, teddy_masks, no_flood, teddy_fat)
     keep = []
     extv = None
     if ext is not None:
