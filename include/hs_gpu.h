@@ -156,6 +156,16 @@ long long hs_gpu_shufti(const uint8_t lo[16], const uint8_t hi[16], const uint8_
 long long hs_gpu_truffle(const uint8_t mask1[16], const uint8_t mask2[16], const uint8_t *buf, size_t len, int reverse);
 long long hs_gpu_vermicelli(uint8_t c, int nocase, const uint8_t *buf, size_t len, int reverse, int negate);
 long long hs_gpu_vermicelli_double(uint8_t c1, uint8_t c2, int nocase, const uint8_t *buf, size_t len);
+/* shuftiDoubleExec (src/nfa/shufti.h, shufti_simd.hpp:196-285): first i with a pair bucket admitting byte i under
+ * (lo1, hi1) and byte i + 1 under (lo2, hi2) -- masks with CLEAR bits for members; a trailing first byte counts. */
+long long hs_gpu_shufti_double(const uint8_t lo1[16], const uint8_t hi1[16], const uint8_t lo2[16], const uint8_t hi2[16],
+                               const uint8_t *buf, size_t len);
+/* Measurement: stage the data on the device once, then search it `repeats` times (kind 0 shufti, 1 truffle,
+ * 2 vermicelli, 3 negated vermicelli, 4 double vermicelli, 5 double shufti; masks = up to four 16-byte masks);
+ * *kernel_ms = mean kernel time (CUDA events).  The shape of /root/reference/benchmarks/benchmarks.cpp:112-250. */
+int hs_gpu_accel_stage(const uint8_t *buf, size_t len);
+long long hs_gpu_accel_search_staged(int kind, const uint8_t *masks, uint8_t c1, uint8_t c2, int nocase, int reverse,
+                                     int repeats, float *kernel_ms);
 
 #ifdef __cplusplus
 }

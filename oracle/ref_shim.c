@@ -93,3 +93,6 @@ long long ref_shim_verm(u8 c, int nocase, const u8 *buf, size_t len, int reverse
 long long ref_shim_dverm(u8 c1, u8 c2, int nocase, const u8 *buf, size_t len) {
     return (long long)(vermicelliDoubleExec((char)c1, (char)c2, (char)nocase, buf, buf + len) - buf);
 }
+long long ref_shim_dshufti(const u8 *lo1, const u8 *hi1, const u8 *lo2, const u8 *hi2, const u8 *buf, size_t len) {
+    return (long long)(shuftiDoubleExec(loadu128(lo1), loadu128(hi1), loadu128(lo2), loadu128(hi2), buf, buf + len) - buf);
+}

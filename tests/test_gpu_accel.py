@@ -125,3 +125,55 @@ def test_vermicelli_double_and_nocase(ref):
                     assert L.hs_gpu_vermicelli(c1, nocase, buf, n, rev, neg) == \
                         ref.L.ref_shim_verm(c1, nocase, C.addressof(b), n, rev, neg), (buf, nocase, rev, neg)
             assert L.hs_gpu_vermicelli_double(c1, c2, nocase, buf, n) == ref.L.ref_shim_dverm(c1, c2, nocase, C.addressof(b), n)
+
+
+def dshufti_masks(pairs):
+    """Double-shufti masks for up to 8 byte pairs, one bucket per pair (src/nfa/shufticompile.cpp:112-200): bit k of
+    lo1/hi1 (lo2/hi2) is CLEAR where pair k's first (second) byte has that nibble."""
+    lo1, hi1, lo2, hi2 = (bytearray([0xff] * 16) for _ in range(4))
+    for k, (a, b) in enumerate(pairs):
+        lo1[a & 15] &= ~(1 << k) & 0xff
+        hi1[a >> 4] &= ~(1 << k) & 0xff
+        lo2[b & 15] &= ~(1 << k) & 0xff
+        hi2[b >> 4] &= ~(1 << k) & 0xff
+    return bytes(lo1), bytes(hi1), bytes(lo2), bytes(hi2)
+
+
+def test_shufti_double(ref):
+    """shuftiDoubleExec: first position whose byte pair is one of the listed pairs (a trailing first byte counts).  The
+    filler never contains a first byte of any pair, so the reference's conservative answers at the ends of its vector
+    lanes (x86/shufti.hpp:69-70 shifts zeros in) cannot differ from the scalar definition."""
+    L = gpu.lib()
+    L.hs_gpu_shufti_double.restype = C.c_longlong
+    ref.L.ref_shim_dshufti.restype = C.c_longlong
+    ref.L.ref_shim_dshufti.argtypes = [C.c_void_p] * 5 + [C.c_size_t]
+    rng = random.Random(17)
+    for trial in range(60):
+        pairs = [(rng.randrange(97, 110), rng.randrange(32, 127)) for _ in range(rng.randint(1, 8))]
+        lo1, hi1, lo2, hi2 = dshufti_masks(pairs)
+
+        def m1(c):
+            return (lo1[c & 15] | hi1[c >> 4]) & 0xff
+
+        def m2(c):
+            return (lo2[c & 15] | hi2[c >> 4]) & 0xff
+        filler = [c for c in range(32, 127) if m1(c) == 0xff]
+        n = rng.choice([16, 17, 64, 100, 1000, 70000])
+        buf = bytearray(rng.choice(filler) for _ in range(n))
+        for _ in range(rng.choice([0, 1, 2])):
+            a, b = rng.choice(pairs)
+            p = rng.randrange(n - 1)
+            buf[p:p + 2] = bytes([a, b])
+        if rng.random() < 0.3:
+            buf[-1] = pairs[0][0]
+        buf = bytes(buf)
+        exp = n
+        for i in range(n):
+            if (m1(buf[i]) | (m2(buf[i + 1]) if i + 1 < n else 0)) != 0xff:
+                exp = i
+                break
+        got = L.hs_gpu_shufti_double(lo1, hi1, lo2, hi2, buf, n)
+        assert got == exp, (pairs, n)
+        b = C.create_string_buffer(buf, n)
+        t = [(C.c_ubyte * 16)(*m) for m in (lo1, hi1, lo2, hi2)]
+        assert ref.L.ref_shim_dshufti(t[0], t[1], t[2], t[3], C.addressof(b), n) == exp

@@ -18,11 +18,12 @@
 
 namespace {
 
-enum Kind { SHUFTI = 0, TRUFFLE = 1, VERM = 2, NVERM = 3, DVERM = 4 };
+enum Kind { SHUFTI = 0, TRUFFLE = 1, VERM = 2, NVERM = 3, DVERM = 4, DSHUFTI = 5 };
 
 struct ClassParams {
     uint8_t a[16];  // shufti lo / truffle highclear
     uint8_t b[16];  // shufti hi / truffle highset
+    uint8_t a2[16], b2[16];  // double shufti: lo / hi nibble masks of the second byte
     uint8_t c1, c2, casemask, kind;
 };
 
@@ -38,8 +39,11 @@ __device__ __forceinline__ bool in_class(const ClassParams &p, const uint8_t *sa
 // result[0]: forward = smallest hit offset (init len), reverse = largest hit offset + 1 (init 0)
 template <bool REVERSE>
 __global__ void k_class_search(const uint8_t *buf, unsigned long long len, ClassParams p, unsigned long long *result) {
-    __shared__ uint8_t sa[16], sb[16];
-    if (threadIdx.x < 16) { sa[threadIdx.x] = p.a[threadIdx.x]; sb[threadIdx.x] = p.b[threadIdx.x]; }
+    __shared__ uint8_t sa[16], sb[16], sa2[16], sb2[16];
+    if (threadIdx.x < 16) {
+        sa[threadIdx.x] = p.a[threadIdx.x]; sb[threadIdx.x] = p.b[threadIdx.x];
+        sa2[threadIdx.x] = p.a2[threadIdx.x]; sb2[threadIdx.x] = p.b2[threadIdx.x];
+    }
     __syncthreads();
     const unsigned long long chunks = (len + 15) / 16;
     const unsigned long long per_block = (chunks + gridDim.x - 1) / gridDim.x;
@@ -71,6 +75,14 @@ __global__ void k_class_search(const uint8_t *buf, unsigned long long len, Class
                     const uint8_t n = (uint8_t)(w[(i + 1) >> 2] >> (8 * ((i + 1) & 3)));
                     const bool is1 = (uint8_t)(c & p.casemask) == p.c1;
                     hit = is1 && (off + i + 1 >= len || (uint8_t)(n & p.casemask) == p.c2);
+                } else if (p.kind == DSHUFTI) {
+                    // blockDoubleMask (src/nfa/x86/shufti.hpp:49-74): the masks hold CLEAR bits for members; a pair
+                    // bucket k matches at i when bit k is clear for byte i under mask 1 and for byte i + 1 under mask 2;
+                    // past the end of the data the second byte admits everything (a trailing first byte counts)
+                    const uint8_t n = (uint8_t)(w[(i + 1) >> 2] >> (8 * ((i + 1) & 3)));
+                    const uint8_t m1 = (uint8_t)(sa[c & 15] | sb[c >> 4]);
+                    const uint8_t m2 = off + i + 1 >= len ? (uint8_t)0 : (uint8_t)(sa2[n & 15] | sb2[n >> 4]);
+                    hit = (uint8_t)(m1 | m2) != 0xff;
                 } else {
                     hit = in_class(p, sa, sb, c);
                 }
@@ -98,33 +110,81 @@ struct Workspace {
     uint8_t *d_buf = nullptr;
     size_t cap = 0;
     unsigned long long *d_res = nullptr;
+    size_t len = 0;
 };
 
-long long run_search(const ClassParams &p, const uint8_t *buf, size_t len, bool reverse) {
+Workspace &workspace() {
     static thread_local Workspace ws;
+    return ws;
+}
+
+// stage the data on the device (padded to a multiple of 16 + 32 zero bytes)
+bool stage(const uint8_t *buf, size_t len) {
+    Workspace &ws = workspace();
+    const size_t padded = (len + 15) / 16 * 16 + 32;
+    if (padded > ws.cap) {
+        if (ws.d_buf) cudaFree(ws.d_buf);
+        if (cudaMalloc((void **)&ws.d_buf, padded + padded / 4) != cudaSuccess) { ws.d_buf = nullptr; ws.cap = 0; return false; }
+        ws.cap = padded + padded / 4;
+    }
+    if (!ws.d_res && cudaMalloc((void **)&ws.d_res, 8) != cudaSuccess) return false;
+    if (cudaMemcpy(ws.d_buf, buf, len, cudaMemcpyHostToDevice) != cudaSuccess) return false;
+    cudaMemset(ws.d_buf + len, 0, padded - len);
+    ws.len = len;
+    return true;
+}
+
+// one search over the staged data; `repeats` > 1 re-runs it and reports the mean kernel time (CUDA events)
+long long search_staged(const ClassParams &p, bool reverse, int repeats, float *ms) {
+    Workspace &ws = workspace();
+    const size_t len = ws.len;
+    if (!len) return reverse ? -1 : 0;
+    const unsigned long long chunks = (len + 15) / 16;
+    unsigned grid = (unsigned)((chunks + 255) / 256);
+    if (grid > 148 * 8) grid = 148 * 8;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (ms) { cudaEventCreate(&e0); cudaEventCreate(&e1); }
+    float total = 0;
+    unsigned long long res = 0;
+    for (int r = 0; r < (repeats > 0 ? repeats : 1); r++) {
+        const unsigned long long init = reverse ? 0ull : (unsigned long long)len;
+        cudaMemcpy(ws.d_res, &init, 8, cudaMemcpyHostToDevice);
+        if (ms) cudaEventRecord(e0);
+        if (reverse) k_class_search<true><<<grid, 256>>>(ws.d_buf, len, p, ws.d_res);
+        else k_class_search<false><<<grid, 256>>>(ws.d_buf, len, p, ws.d_res);
+        if (ms) {
+            cudaEventRecord(e1);
+            cudaEventSynchronize(e1);
+            float t = 0;
+            cudaEventElapsedTime(&t, e0, e1);
+            total += t;
+        }
+    }
+    if (cudaMemcpy(&res, ws.d_res, 8, cudaMemcpyDeviceToHost) != cudaSuccess) return -2;
+    if (ms) { *ms = total / (float)(repeats > 0 ? repeats : 1); cudaEventDestroy(e0); cudaEventDestroy(e1); }
+    return reverse ? (long long)res - 1 : (long long)res;
+}
+
+long long run_search(const ClassParams &p, const uint8_t *buf, size_t len, bool reverse) {
     if (!buf && len) return -2;
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { cudaGetLastError(); return -2; }
     if (!len) return reverse ? -1 : 0;
-    const size_t padded = (len + 15) / 16 * 16 + 32;
-    if (padded > ws.cap) {
-        if (ws.d_buf) cudaFree(ws.d_buf);
-        if (cudaMalloc((void **)&ws.d_buf, padded + padded / 4) != cudaSuccess) { ws.d_buf = nullptr; ws.cap = 0; return -2; }
-        ws.cap = padded + padded / 4;
-    }
-    if (!ws.d_res && cudaMalloc((void **)&ws.d_res, 8) != cudaSuccess) return -2;
-    cudaMemcpy(ws.d_buf, buf, len, cudaMemcpyHostToDevice);
-    cudaMemset(ws.d_buf + len, 0, padded - len);
-    unsigned long long init = reverse ? 0ull : (unsigned long long)len;
-    cudaMemcpy(ws.d_res, &init, 8, cudaMemcpyHostToDevice);
-    const unsigned long long chunks = (len + 15) / 16;
-    unsigned grid = (unsigned)((chunks + 255) / 256);
-    if (grid > 148 * 8) grid = 148 * 8;
-    if (reverse) k_class_search<true><<<grid, 256>>>(ws.d_buf, len, p, ws.d_res);
-    else k_class_search<false><<<grid, 256>>>(ws.d_buf, len, p, ws.d_res);
-    unsigned long long res = 0;
-    if (cudaMemcpy(&res, ws.d_res, 8, cudaMemcpyDeviceToHost) != cudaSuccess) return -2;
-    return reverse ? (long long)res - 1 : (long long)res;
+    if (!stage(buf, len)) return -2;
+    return search_staged(p, reverse, 1, nullptr);
+}
+
+ClassParams make_params(int kind, const uint8_t *m1, const uint8_t *m2, const uint8_t *m3, const uint8_t *m4, uint8_t c1, uint8_t c2, int nocase) {
+    ClassParams p{};
+    if (m1) std::memcpy(p.a, m1, 16);
+    if (m2) std::memcpy(p.b, m2, 16);
+    if (m3) std::memcpy(p.a2, m3, 16);
+    if (m4) std::memcpy(p.b2, m4, 16);
+    p.casemask = nocase ? 0xdf : 0xff;
+    p.c1 = (uint8_t)(c1 & p.casemask);
+    p.c2 = (uint8_t)(c2 & p.casemask);
+    p.kind = (uint8_t)kind;
+    return p;
 }
 
 }  // namespace
@@ -162,6 +222,27 @@ long long hs_gpu_vermicelli_double(uint8_t c1, uint8_t c2, int nocase, const uin
     p.c2 = (uint8_t)(c2 & p.casemask);
     p.kind = DVERM;
     return run_search(p, buf, len, false);
+}
+
+long long hs_gpu_shufti_double(const uint8_t lo1[16], const uint8_t hi1[16], const uint8_t lo2[16], const uint8_t hi2[16],
+                               const uint8_t *buf, size_t len) {
+    return run_search(make_params(DSHUFTI, lo1, hi1, lo2, hi2, 0, 0, 0), buf, len, false);
+}
+
+// Measurement entry points (tools/accel_bench.py): the data is staged once, then searched `repeats` times with CUDA
+// events around each kernel.  kind: 0 shufti, 1 truffle, 2 vermicelli, 3 negated vermicelli, 4 double vermicelli,
+// 5 double shufti; masks = up to four 16-byte masks back to back.
+int hs_gpu_accel_stage(const uint8_t *buf, size_t len) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { cudaGetLastError(); return -11; }
+    return stage(buf, len) ? 0 : -2;
+}
+long long hs_gpu_accel_search_staged(int kind, const uint8_t *masks, uint8_t c1, uint8_t c2, int nocase, int reverse,
+                                     int repeats, float *kernel_ms) {
+    if (kind < 0 || kind > 5) return -2;
+    const ClassParams p = make_params(kind, masks, masks ? masks + 16 : nullptr, masks ? masks + 32 : nullptr,
+                                      masks ? masks + 48 : nullptr, c1, c2, nocase);
+    return search_staged(p, reverse != 0, repeats, kernel_ms);
 }
 
 }  // extern "C"
