@@ -49,7 +49,7 @@ def main():
         ("shufti_double", 5, b"".join(bytes(x) for x in d), 0, 0,
          lambda p, n: R.L.ref_shim_dshufti(bytes(d[0]), bytes(d[1]), bytes(d[2]), bytes(d[3]), p, n)),
     ]
-    sizes = [16 << 10, 256 << 10, 4 << 20, 64 << 20, 256 << 20]
+    sizes = [int(x) for x in sys.argv[1].split(",")] if len(sys.argv) > 1 else [16 << 10, 256 << 10, 4 << 20, 64 << 20, 256 << 20]
     rng = np.random.default_rng(5)
     for n in sizes:
         base = rng.integers(97, 123, n, dtype=np.uint8)       # a-z: no member of any class
@@ -69,11 +69,14 @@ def main():
                 for _ in range(creps):
                     exp = cpu(data.ctypes.data, n)
                 cpu_s = (time.perf_counter() - t0) / creps
-                assert got == exp == (n if shape == "no match" else n - 6), (name, n, shape, got, exp)
+                want = n if shape == "no match" else n - 6
+                assert got == want, (name, n, shape, got)
+                # (the reference's 512-bit vermicelli answers "not found" for some matches close to the end of the buffer --
+                # tests/test_gpu_accel.py notes the defect; its answer is recorded, not asserted)
                 print(json.dumps({"routine": name, "bytes": n, "shape": shape, "gpu_kernel_ms": round(ms.value, 4),
                                   "gpu_GBps": round(n / (ms.value * 1e-3) / 1e9, 1), "cpu_ms": round(cpu_s * 1e3, 4),
                                   "cpu_GBps": round(n / cpu_s / 1e9, 2), "cpu": f"reference routine, 1 core, {R.isa} build",
-                                  "result": int(got)}), flush=True)
+                                  "result": int(got), "cpu_result": int(exp)}), flush=True)
 
 
 if __name__ == "__main__":

@@ -106,10 +106,107 @@ __global__ void k_class_search(const uint8_t *buf, unsigned long long len, Class
     }
 }
 
+
+// ---- k_class_scan: the single-byte classes (shufti, truffle, vermicelli, negated vermicelli) and the double vermicelli ----
+// Every one of them is "byte c is in a set" (the double form: c in set 1 and the NEXT byte in set 2), so the class is
+// turned on the host into a 256-entry table -- bit 31 = member of set 1, bit 30 = member of set 2 -- and the kernel is
+// one conflict-free shared-memory read per byte: the table is replicated once per bank (word c * 32 + lane, 32 KiB), as
+// k_mcclellan's symbol table.  A warp step is 2 KiB: four coalesced LDG.128 per lane issued together, then 4 instructions
+// per byte (shift, and-or address, LDS, funnel-shift the flag into the mask) -- bound by HBM, not by issue.
+// Forward: the grid publishes the smallest hit offset (atomicMin); blocks own contiguous ranges and look at the published
+// value every few steps to stop early.  Reverse: the largest hit offset + 1 (atomicMax), ranges walked from their end.
+constexpr int CS_THREADS = 256;
+constexpr int CS_TILE_CHUNKS = 128;  // 16-byte chunks per warp step (4 per lane)
+
+template <bool REVERSE, bool DOUBLE>
+__global__ void __launch_bounds__(CS_THREADS) k_class_scan(const uint8_t *buf, unsigned long long len, const unsigned *table256,
+                                                           unsigned long long *result) {
+    extern __shared__ unsigned cs_tab[];  // [256][32]
+    for (unsigned i = threadIdx.x; i < 256 * 32; i += blockDim.x) cs_tab[i] = table256[i >> 5];
+    __syncthreads();
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
+    const unsigned lane4 = lane * 4;
+    const unsigned char *tab_b = reinterpret_cast<const unsigned char *>(cs_tab);
+    const unsigned long long chunks = (len + 15) / 16;
+    const unsigned long long tiles = (chunks + CS_TILE_CHUNKS - 1) / CS_TILE_CHUNKS;
+    const unsigned long long per_block = (tiles + gridDim.x - 1) / gridDim.x;
+    const unsigned long long t0 = (unsigned long long)blockIdx.x * per_block;
+    unsigned long long t1 = t0 + per_block;
+    if (t1 > tiles) t1 = tiles;
+    unsigned step = 0;
+    for (unsigned long long it = warp; t0 + it < t1; it += warps, step++) {
+        const unsigned long long tile = REVERSE ? t1 - 1 - it : t0 + it;
+        if ((step & 3) == 0) {  // a better hit is already known: nothing in this warp's remaining tiles can beat it
+            const unsigned long long best = *(volatile unsigned long long *)result;
+            if (!REVERSE && best <= tile * (CS_TILE_CHUNKS * 16ull)) return;
+            if (REVERSE && best >= (tile + 1) * (CS_TILE_CHUNKS * 16ull)) return;
+        }
+        uint4 v[4];
+        unsigned nxt[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const unsigned long long ch = tile * CS_TILE_CHUNKS + (unsigned)k * 32 + lane;
+            v[k] = ch < chunks ? *reinterpret_cast<const uint4 *>(buf + ch * 16) : make_uint4(0, 0, 0, 0);
+            if (DOUBLE) nxt[k] = ch < chunks ? buf[ch * 16 + 16] : 0u;  // the staged data is padded: always readable
+        }
+        unsigned hits[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const unsigned long long ch = tile * CS_TILE_CHUNKS + (unsigned)k * 32 + lane;
+            const unsigned w[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
+            unsigned a1 = 0, a2 = 0;  // bit 15 - i = byte i of the chunk
+#pragma unroll
+            for (int i = 0; i < 16; i++) {
+                const unsigned x = w[i >> 2], sh = 8 * (i & 3);
+                const unsigned ra = ((sh >= 7 ? x >> (sh - 7) : x << (7 - sh)) & 0x7f80u) | lane4;
+                const unsigned e = *reinterpret_cast<const unsigned *>(tab_b + ra);
+                a1 = __funnelshift_l(e, a1, 1);
+                if (DOUBLE) a2 = __funnelshift_l(e << 1, a2, 1);
+            }
+            unsigned h = a1;
+            if (DOUBLE) {
+                const unsigned e16 = cs_tab[nxt[k] * 32 + lane];            // the byte after the chunk
+                const unsigned need = ((a2 << 1) | ((e16 >> 30) & 1u)) & 0xffffu;  // set 2 holds the byte after byte i
+                h = a1 & need;
+                // the last byte of the data has no successor: a member of set 1 there counts (vermicelliDoubleExec)
+                if (len - 1 >= ch * 16 && len - 1 < ch * 16 + 16) h |= a1 & (0x8000u >> (unsigned)(len - 1 - ch * 16));
+            }
+            // bytes past the end of the data (zero padding) are not part of the search
+            if (ch >= chunks) h = 0;
+            else if (ch * 16 + 16 > len) h &= 0xffffu << (unsigned)(ch * 16 + 16 - len);
+            hits[k] = h & 0xffffu;
+        }
+        if (!REVERSE) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const unsigned vote = __ballot_sync(0xffffffffu, hits[k] != 0);
+                if (vote) {
+                    const unsigned src = __ffs(vote) - 1;
+                    const unsigned h = __shfl_sync(0xffffffffu, hits[k], src);
+                    if (lane == 0) atomicMin(result, (tile * CS_TILE_CHUNKS + (unsigned)k * 32 + src) * 16ull + (unsigned)(__clz(h) - 16));
+                    return;  // this warp's later tiles lie behind this hit
+                }
+            }
+        } else {
+#pragma unroll
+            for (int k = 3; k >= 0; k--) {
+                const unsigned vote = __ballot_sync(0xffffffffu, hits[k] != 0);
+                if (vote) {
+                    const unsigned src = 31 - __clz(vote);
+                    const unsigned h = __shfl_sync(0xffffffffu, hits[k], src);
+                    if (lane == 0) atomicMax(result, (tile * CS_TILE_CHUNKS + (unsigned)k * 32 + src) * 16ull + (unsigned)(15 - (__ffs(h) - 1)) + 1ull);
+                    return;
+                }
+            }
+        }
+    }
+}
+
 struct Workspace {
     uint8_t *d_buf = nullptr;
     size_t cap = 0;
     unsigned long long *d_res = nullptr;
+    unsigned *d_tab = nullptr;  // 256-entry class table of k_class_scan
     size_t len = 0;
 };
 
@@ -142,6 +239,28 @@ long long search_staged(const ClassParams &p, bool reverse, int repeats, float *
     const unsigned long long chunks = (len + 15) / 16;
     unsigned grid = (unsigned)((chunks + 255) / 256);
     if (grid > 148 * 8) grid = 148 * 8;
+    // every kind but the double shufti is a per-byte set test: one table, one kernel (k_class_scan)
+    const bool table_kind = p.kind != DSHUFTI;
+    const bool dbl = p.kind == DVERM;
+    if (table_kind) {
+        unsigned tab[256];
+        for (unsigned c = 0; c < 256; c++) {
+            bool in1, in2 = false;
+            switch (p.kind) {
+            case SHUFTI: in1 = (p.a[c & 15] & p.b[c >> 4]) != 0; break;
+            case TRUFFLE: in1 = ((((c & 0x80) ? p.b : p.a)[c & 15] >> ((c >> 4) & 7)) & 1) != 0; break;
+            case VERM: in1 = (uint8_t)(c & p.casemask) == p.c1; break;
+            case NVERM: in1 = (uint8_t)(c & p.casemask) != p.c1; break;
+            default: in1 = (uint8_t)(c & p.casemask) == p.c1; in2 = (uint8_t)(c & p.casemask) == p.c2; break;
+            }
+            tab[c] = (in1 ? 0x80000000u : 0u) | (in2 ? 0x40000000u : 0u);
+        }
+        if (!ws.d_tab && cudaMalloc((void **)&ws.d_tab, sizeof(tab)) != cudaSuccess) return -2;
+        cudaMemcpy(ws.d_tab, tab, sizeof(tab), cudaMemcpyHostToDevice);
+        const unsigned long long tiles = (chunks + CS_TILE_CHUNKS - 1) / CS_TILE_CHUNKS;
+        const unsigned long long want = (tiles + (CS_THREADS / 32) * 4 - 1) / ((CS_THREADS / 32) * 4);  // >= 4 steps per warp
+        grid = (unsigned)(want < 1 ? 1 : want > 148 * 6 ? 148 * 6 : want);
+    }
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ms) { cudaEventCreate(&e0); cudaEventCreate(&e1); }
     float total = 0;
@@ -150,7 +269,11 @@ long long search_staged(const ClassParams &p, bool reverse, int repeats, float *
         const unsigned long long init = reverse ? 0ull : (unsigned long long)len;
         cudaMemcpy(ws.d_res, &init, 8, cudaMemcpyHostToDevice);
         if (ms) cudaEventRecord(e0);
-        if (reverse) k_class_search<true><<<grid, 256>>>(ws.d_buf, len, p, ws.d_res);
+        if (table_kind) {
+            if (dbl) k_class_scan<false, true><<<grid, CS_THREADS, 32768>>>(ws.d_buf, len, ws.d_tab, ws.d_res);
+            else if (reverse) k_class_scan<true, false><<<grid, CS_THREADS, 32768>>>(ws.d_buf, len, ws.d_tab, ws.d_res);
+            else k_class_scan<false, false><<<grid, CS_THREADS, 32768>>>(ws.d_buf, len, ws.d_tab, ws.d_res);
+        } else if (reverse) k_class_search<true><<<grid, 256>>>(ws.d_buf, len, p, ws.d_res);
         else k_class_search<false><<<grid, 256>>>(ws.d_buf, len, p, ws.d_res);
         if (ms) {
             cudaEventRecord(e1);

@@ -1776,16 +1776,26 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
 
 // Single-match (exhaustion key) resolution and removal of quiet records, on the host copy.
 // Records arrive sorted by (buffer, to, id): the first record of an (buffer, ekey) pair is the earliest.
-u64 resolve_exhaustion(hs_gpu_scratch *s, const Rec *recs, u64 n, hs_gpu_match_t *out) {
+u64 resolve_exhaustion(hs_gpu_scratch *s, const Rec *recs, u64 n, hs_gpu_match_t *out, u32 ekey_count) {
     (void)s;
-    std::map<std::pair<u32, u32>, bool> seen;
+    // one linear pass: a flag per exhaustion key, cleared (through the list of keys touched) when the buffer changes
+    std::vector<u8> seen((size_t)ekey_count + 1, 0);
+    std::vector<u32> touched;
+    u32 cur_buf = ~0u;
     u64 m = 0;
     for (u64 i = 0; i < n; i++) {
         const Rec &r = recs[i];
+        if (r.buf != cur_buf) {
+            for (u32 k : touched) seen[k] = 0;
+            touched.clear();
+            cur_buf = r.buf;
+        }
         if (r.aux & AUX_EKEY) {
-            auto key = std::make_pair(r.buf, r.aux & AUX_KEYMASK);
-            if (seen.count(key)) continue;
-            seen[key] = true;
+            u32 k = r.aux & AUX_KEYMASK;
+            if (k > ekey_count) k = ekey_count;
+            if (seen[k]) continue;
+            seen[k] = 1;
+            touched.push_back(k);
         }
         if (r.aux & AUX_QUIET) continue;
         out[m++] = hs_gpu_match_t{r.buf, r.id, (uint64_t)r.to};
@@ -1819,7 +1829,7 @@ hs_error_t fetch_matches(hs_gpu_scratch *s, DbImage *im) {
         if (need_recs) {
             std::vector<Rec> tmp(n);
             std::memcpy(tmp.data(), s->h_matches, n * sizeof(Rec));
-            s->n_matches = resolve_exhaustion(s, tmp.data(), n, s->h_matches);
+            s->n_matches = resolve_exhaustion(s, tmp.data(), n, s->h_matches, im->view.ekey_count);
             st.matches = s->n_matches;
         }
     }
@@ -2428,6 +2438,9 @@ hs_error_t hs_gpu_scan_corpus(const hs_database_t *db, const hs_gpu_corpus_t *co
     scratch->stats.d2h_ms = 0;
     rv = scan_device(scratch, im, *corpus);
     if (rv != HS_SUCCESS) return rv;
+    // single-match (exhaustion key) sets: the device array still holds every repeat and the quiet records; the count
+    // the caller gets is the resolved one (the resolution runs on the fetched copy)
+    if (im->view.ekey_count && (rv = fetch_matches(scratch, im)) != HS_SUCCESS) return rv;
     if (n_matches) *n_matches = scratch->n_matches;
     return HS_SUCCESS;
 }
