@@ -410,6 +410,12 @@ def main():
         brk["wall_ms"] = round(1e3 * secs / steps, 4)
         t = torch.tensor([secs], dtype=torch.float64, device="cuda")
         if world > 1:
+            # per-rank H2D time: at N = 8 the ranks share the host's memory bandwidth and PCIe switches -- the spread names
+            # the limiting resource
+            h = torch.tensor([brk["h2d_ms"]], dtype=torch.float64, device="cuda")
+            hs = [torch.zeros_like(h) for _ in range(world)]
+            dist.all_gather(hs, h)
+            brk["rank_h2d_ms"] = [round(float(x[0]), 4) for x in hs]
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return world * steps * float(flat0.nbytes) / float(t[0]) / 1e9, matches, brk
 

@@ -1,5 +1,6 @@
 """C5 of BASELINE.json: hsbench-style sweep of pattern count x buffer size on one GPU (SURVEY.md 8d "C5 concrete
-input"), literal sets.  Every cell: database from the literal writer, a corpus of `--bytes` bytes cut into equal
+input"), literal sets (default) or regex sets (--regex: the C3 templates as a full-Rose database of outfix engines,
+pattern counts 100 ... 2000).  Every cell: database from the literal writer, a corpus of `--bytes` bytes cut into equal
 buffers, `--steps` device-timed scans through the C ABI (corpus resident in HBM, L2 defeated by rotating 3
 corpora when they are smaller than L2), a parity check of the first `--check` buffers against the unmodified
 reference runtime (oracle/_ref, when present: the checker, never the thing measured) and the reference's own
@@ -28,7 +29,10 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--bytes", type=int, default=128 << 20)
     ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--check", type=int, default=64, help="buffers per cell compared with the reference runtime")
+    ap.add_argument("--check", type=int, default=64, help="buffers per cell compared with the reference runtime (at least)")
+    ap.add_argument("--check-bytes", type=int, default=4 << 20, help="... and at least this many bytes per cell")
+    ap.add_argument("--regex", action="store_true", help="regex rows: C3 templates as outfix engines of a full-Rose database")
+    ap.add_argument("--dfa-states", type=int, default=1024)
     ap.add_argument("--patterns", type=int, nargs="*", default=PATTERNS)
     ap.add_argument("--bufsizes", type=int, nargs="*", default=BUFSIZES)
     args = ap.parse_args()
@@ -40,9 +44,14 @@ def main():
     except Exception:
         pass
     for ci, npat in enumerate(args.patterns):
-        lits, flags, ids = W.sweep_patterns(npat, 20260105 + ci)
         t0 = time.perf_counter()
-        db = litdb.compile_lit_multi(lits, flags, ids)
+        if args.regex:
+            ex, fl, ids = W.c3_patterns(seed=20260105 + ci, max_patterns=npat, state_budget=1 << 30)
+            db = litdb.compile_regex_rose(ex, fl, ids, dfa_states=args.dfa_states)
+            lits = [w + b"=" for w in W._C3_WORDS]   # planted into the sweep text so that the engines have work to do
+        else:
+            lits, flags, ids = W.sweep_patterns(npat, 20260105 + ci)
+            db = litdb.compile_lit_multi(lits, flags, ids)
         compile_s = time.perf_counter() - t0
         sc = gpu.alloc_scratch(db)
         rdb = rs = None
@@ -70,11 +79,15 @@ def main():
                     "steps": args.steps, "gbps_device": round(args.bytes * args.steps / (dev_ms * 1e-3) / 1e9, 2),
                     "gbps_kernel": round(args.bytes * args.steps / (kern_ms * 1e-3) / 1e9, 2),
                     "matches_per_step": nmatch // args.steps, "db_bytes": len(db.bytecode()),
+                    "kind": "regex (outfix engines)" if args.regex else "literal",
+                    "engines": int.from_bytes(db.bytecode()[156:160], "little"),
                     "compile_s": round(compile_s, 2)}
             # parity: the first buffers of corpus 0, GPU (through hs_gpu_scan_vector_ex, host buffers) vs reference
             if ref is not None and args.check:
                 flat, off = host
                 n = min(args.check, len(off) - 1)
+                while n < len(off) - 1 and int(off[n]) < args.check_bytes // (40 if args.regex else 1):
+                    n += 1   # (the regex databases run ~100 engines per byte on the CPU: a smaller byte budget)
                 bufs = [bytes(flat[int(off[i]):int(off[i + 1])]) for i in range(n)]
                 got = [(int(b), int(i), int(t)) for b, i, t in gpu.scan_vector_ex(db, bufs, sc)]
                 exp = []

@@ -109,10 +109,10 @@ __global__ void k_class_search(const uint8_t *buf, unsigned long long len, Class
 
 // ---- k_class_scan: the single-byte classes (shufti, truffle, vermicelli, negated vermicelli) and the double vermicelli ----
 // Every one of them is "byte c is in a set" (the double form: c in set 1 and the NEXT byte in set 2), so the class is
-// turned on the host into a 256-entry table -- bit 31 = member of set 1, bit 30 = member of set 2 -- and the kernel is
+// turned on the host into a 256-entry table -- bit 0 = member of set 1, bit 16 = member of set 2 -- and the kernel is
 // one conflict-free shared-memory read per byte: the table is replicated once per bank (word c * 32 + lane, 32 KiB), as
 // k_mcclellan's symbol table.  A warp step is 2 KiB: four coalesced LDG.128 per lane issued together, then 4 instructions
-// per byte (shift, and-or address, LDS, funnel-shift the flag into the mask) -- bound by HBM, not by issue.
+// per byte -- PRMT (byte), IMAD (row address), LDS, IMAD (mask * 2 + flag) -- one on the ALU pipe, two on the FMA pipe.
 // Forward: the grid publishes the smallest hit offset (atomicMin); blocks own contiguous ranges and look at the published
 // value every few steps to stop early.  Reverse: the largest hit offset + 1 (atomicMax), ranges walked from their end.
 constexpr int CS_THREADS = 256;
@@ -121,12 +121,12 @@ constexpr int CS_TILE_CHUNKS = 128;  // 16-byte chunks per warp step (4 per lane
 template <bool REVERSE, bool DOUBLE>
 __global__ void __launch_bounds__(CS_THREADS) k_class_scan(const uint8_t *buf, unsigned long long len, const unsigned *table256,
                                                            unsigned long long *result) {
-    extern __shared__ unsigned cs_tab[];  // [256][32]
+    __shared__ unsigned cs_tab[256 * 32];  // [256][32]; static, so that its address is an immediate of the LDS
     for (unsigned i = threadIdx.x; i < 256 * 32; i += blockDim.x) cs_tab[i] = table256[i >> 5];
     __syncthreads();
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
-    const unsigned lane4 = lane * 4;
-    const unsigned char *tab_b = reinterpret_cast<const unsigned char *>(cs_tab);
+    // my bank's copy: the entry of byte c sits at shared address tab_l + c * 128
+    const unsigned tab_l = (unsigned)__cvta_generic_to_shared(cs_tab) + lane * 4;
     const unsigned long long chunks = (len + 15) / 16;
     const unsigned long long tiles = (chunks + CS_TILE_CHUNKS - 1) / CS_TILE_CHUNKS;
     const unsigned long long per_block = (tiles + gridDim.x - 1) / gridDim.x;
@@ -141,39 +141,54 @@ __global__ void __launch_bounds__(CS_THREADS) k_class_scan(const uint8_t *buf, u
             if (!REVERSE && best <= tile * (CS_TILE_CHUNKS * 16ull)) return;
             if (REVERSE && best >= (tile + 1) * (CS_TILE_CHUNKS * 16ull)) return;
         }
+        // a tile that ends before the last chunk of the data needs no bounds at all (the common case)
+        const bool inner = (tile + 1) * CS_TILE_CHUNKS < chunks;
+        const unsigned char *tp = buf + tile * (CS_TILE_CHUNKS * 16ull) + lane * 16u;
         uint4 v[4];
         unsigned nxt[4];
+        if (inner) {
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const unsigned long long ch = tile * CS_TILE_CHUNKS + (unsigned)k * 32 + lane;
-            v[k] = ch < chunks ? *reinterpret_cast<const uint4 *>(buf + ch * 16) : make_uint4(0, 0, 0, 0);
-            if (DOUBLE) nxt[k] = ch < chunks ? buf[ch * 16 + 16] : 0u;  // the staged data is padded: always readable
+            for (int k = 0; k < 4; k++) {
+                v[k] = *reinterpret_cast<const uint4 *>(tp + k * 512);
+                if (DOUBLE) nxt[k] = tp[k * 512 + 16];
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const unsigned long long ch = tile * CS_TILE_CHUNKS + (unsigned)k * 32 + lane;
+                v[k] = ch < chunks ? *reinterpret_cast<const uint4 *>(tp + k * 512) : make_uint4(0, 0, 0, 0);
+                if (DOUBLE) nxt[k] = ch < chunks ? tp[k * 512 + 16] : 0u;  // the staged data is padded: always readable
+            }
         }
         unsigned hits[4];
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            const unsigned long long ch = tile * CS_TILE_CHUNKS + (unsigned)k * 32 + lane;
             const unsigned w[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
             unsigned a1 = 0, a2 = 0;  // bit 15 - i = byte i of the chunk
 #pragma unroll
             for (int i = 0; i < 16; i++) {
-                const unsigned x = w[i >> 2], sh = 8 * (i & 3);
-                const unsigned ra = ((sh >= 7 ? x >> (sh - 7) : x << (7 - sh)) & 0x7f80u) | lane4;
-                const unsigned e = *reinterpret_cast<const unsigned *>(tab_b + ra);
-                a1 = __funnelshift_l(e, a1, 1);
-                if (DOUBLE) a2 = __funnelshift_l(e << 1, a2, 1);
+                // byte i by one PRMT (ALU pipe); its row and the mask update by multiply-adds (FMA pipe); the flag of an
+                // entry is its bit 0 (set 1) and bit 16 (set 2), so that mask * 2 + entry appends both at once
+                const unsigned c = __byte_perm(w[i >> 2], 0, 0x4440 + (i & 3));
+                unsigned e;
+                asm volatile("{ .reg .u32 a; mad.lo.u32 a, %1, 128, %2; ld.shared.u32 %0, [a]; }" : "=r"(e) : "r"(c), "r"(tab_l));
+                if (!DOUBLE) a1 = a1 * 2u + e;
+                else { a1 = a1 * 2u + (e & 1u); a2 = a2 * 2u + (e >> 16); }
             }
             unsigned h = a1;
             if (DOUBLE) {
                 const unsigned e16 = cs_tab[nxt[k] * 32 + lane];            // the byte after the chunk
-                const unsigned need = ((a2 << 1) | ((e16 >> 30) & 1u)) & 0xffffu;  // set 2 holds the byte after byte i
+                const unsigned need = ((a2 << 1) | (e16 >> 16)) & 0xffffu;   // set 2 holds the byte after byte i
                 h = a1 & need;
-                // the last byte of the data has no successor: a member of set 1 there counts (vermicelliDoubleExec)
-                if (len - 1 >= ch * 16 && len - 1 < ch * 16 + 16) h |= a1 & (0x8000u >> (unsigned)(len - 1 - ch * 16));
             }
-            // bytes past the end of the data (zero padding) are not part of the search
-            if (ch >= chunks) h = 0;
-            else if (ch * 16 + 16 > len) h &= 0xffffu << (unsigned)(ch * 16 + 16 - len);
+            if (!inner) {
+                const unsigned long long ch = tile * CS_TILE_CHUNKS + (unsigned)k * 32 + lane;
+                // the last byte of the data has no successor: a member of set 1 there counts (vermicelliDoubleExec)
+                if (DOUBLE && len - 1 >= ch * 16 && len - 1 < ch * 16 + 16) h |= a1 & (0x8000u >> (unsigned)(len - 1 - ch * 16));
+                // bytes past the end of the data (zero padding) are not part of the search
+                if (ch >= chunks) h = 0;
+                else if (ch * 16 + 16 > len) h &= 0xffffu << (unsigned)(ch * 16 + 16 - len);
+            }
             hits[k] = h & 0xffffu;
         }
         if (!REVERSE) {
@@ -253,7 +268,7 @@ long long search_staged(const ClassParams &p, bool reverse, int repeats, float *
             case NVERM: in1 = (uint8_t)(c & p.casemask) != p.c1; break;
             default: in1 = (uint8_t)(c & p.casemask) == p.c1; in2 = (uint8_t)(c & p.casemask) == p.c2; break;
             }
-            tab[c] = (in1 ? 0x80000000u : 0u) | (in2 ? 0x40000000u : 0u);
+            tab[c] = (in1 ? 1u : 0u) | (in2 ? 0x10000u : 0u);
         }
         if (!ws.d_tab && cudaMalloc((void **)&ws.d_tab, sizeof(tab)) != cudaSuccess) return -2;
         cudaMemcpy(ws.d_tab, tab, sizeof(tab), cudaMemcpyHostToDevice);
@@ -270,9 +285,9 @@ long long search_staged(const ClassParams &p, bool reverse, int repeats, float *
         cudaMemcpy(ws.d_res, &init, 8, cudaMemcpyHostToDevice);
         if (ms) cudaEventRecord(e0);
         if (table_kind) {
-            if (dbl) k_class_scan<false, true><<<grid, CS_THREADS, 32768>>>(ws.d_buf, len, ws.d_tab, ws.d_res);
-            else if (reverse) k_class_scan<true, false><<<grid, CS_THREADS, 32768>>>(ws.d_buf, len, ws.d_tab, ws.d_res);
-            else k_class_scan<false, false><<<grid, CS_THREADS, 32768>>>(ws.d_buf, len, ws.d_tab, ws.d_res);
+            if (dbl) k_class_scan<false, true><<<grid, CS_THREADS>>>(ws.d_buf, len, ws.d_tab, ws.d_res);
+            else if (reverse) k_class_scan<true, false><<<grid, CS_THREADS>>>(ws.d_buf, len, ws.d_tab, ws.d_res);
+            else k_class_scan<false, false><<<grid, CS_THREADS>>>(ws.d_buf, len, ws.d_tab, ws.d_res);
         } else if (reverse) k_class_search<true><<<grid, 256>>>(ws.d_buf, len, p, ws.d_res);
         else k_class_search<false><<<grid, 256>>>(ws.d_buf, len, p, ws.d_res);
         if (ms) {
