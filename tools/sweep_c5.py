@@ -62,7 +62,13 @@ def main():
             rot = 3 if args.bytes < (128 << 20) else 1   # 128 MiB > the 126 MB L2
             corpora, host = [], None
             for r in range(rot):
-                flat, off = W.sweep_batch(args.bytes, bufsize, lits, 20260105 + 1000 * ci + 10 * bi + r)
+                if args.regex:
+                    # the C3 corpus (synthetic HTTP payloads with the templates' words) cut into equal buffers
+                    flat, _ = W.c3_corpus(args.bytes, seed=20260105 + 1000 * ci + 10 * bi + r)
+                    off = np.minimum(np.arange(0, args.bytes + bufsize, bufsize, dtype=np.uint64), np.uint64(args.bytes))
+                    off = np.unique(off)
+                else:
+                    flat, off = W.sweep_batch(args.bytes, bufsize, lits, 20260105 + 1000 * ci + 10 * bi + r)
                 if r == 0:
                     host = (flat, off)
                 corpora.append(gpu.Corpus(flat, off))

@@ -118,12 +118,13 @@ __global__ void k_class_search(const uint8_t *buf, unsigned long long len, Class
 constexpr int CS_THREADS = 256;
 constexpr int CS_TILE_CHUNKS = 128;  // 16-byte chunks per warp step (4 per lane)
 
-template <bool REVERSE, bool DOUBLE>
+template <bool REVERSE, int MODE>
 __global__ void __launch_bounds__(CS_THREADS) k_class_scan(const uint8_t *buf, unsigned long long len, const unsigned *table256,
                                                            unsigned long long *result) {
     __shared__ unsigned cs_tab[256 * 32];  // [256][32]; static, so that its address is an immediate of the LDS
     for (unsigned i = threadIdx.x; i < 256 * 32; i += blockDim.x) cs_tab[i] = table256[i >> 5];
     __syncthreads();
+    constexpr bool DOUBLE = MODE != 0;
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
     // my bank's copy: the entry of byte c sits at shared address tab_l + c * 128
     const unsigned tab_l = (unsigned)__cvta_generic_to_shared(cs_tab) + lane * 4;
@@ -165,21 +166,45 @@ __global__ void __launch_bounds__(CS_THREADS) k_class_scan(const uint8_t *buf, u
         for (int k = 0; k < 4; k++) {
             const unsigned w[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
             unsigned a1 = 0, a2 = 0;  // bit 15 - i = byte i of the chunk
+            unsigned h;
+            if (MODE != 2) {
 #pragma unroll
-            for (int i = 0; i < 16; i++) {
-                // byte i by one PRMT (ALU pipe); its row and the mask update by multiply-adds (FMA pipe); the flag of an
-                // entry is its bit 0 (set 1) and bit 16 (set 2), so that mask * 2 + entry appends both at once
-                const unsigned c = __byte_perm(w[i >> 2], 0, 0x4440 + (i & 3));
-                unsigned e;
-                asm volatile("{ .reg .u32 a; mad.lo.u32 a, %1, 128, %2; ld.shared.u32 %0, [a]; }" : "=r"(e) : "r"(c), "r"(tab_l));
-                if (!DOUBLE) a1 = a1 * 2u + e;
-                else { a1 = a1 * 2u + (e & 1u); a2 = a2 * 2u + (e >> 16); }
-            }
-            unsigned h = a1;
-            if (DOUBLE) {
-                const unsigned e16 = cs_tab[nxt[k] * 32 + lane];            // the byte after the chunk
-                const unsigned need = ((a2 << 1) | (e16 >> 16)) & 0xffffu;   // set 2 holds the byte after byte i
-                h = a1 & need;
+                for (int i = 0; i < 16; i++) {
+                    // byte i by one PRMT (ALU pipe); its row and the mask update by multiply-adds (FMA pipe); the flag of an
+                    // entry is its bit 0 (set 1) and bit 16 (set 2), so that mask * 2 + entry appends both at once
+                    const unsigned c = __byte_perm(w[i >> 2], 0, 0x4440 + (i & 3));
+                    unsigned e;
+                    asm volatile("{ .reg .u32 a; mad.lo.u32 a, %1, 128, %2; ld.shared.u32 %0, [a]; }" : "=r"(e) : "r"(c), "r"(tab_l));
+                    if (!DOUBLE) a1 = a1 * 2u + e;
+                    else { a1 = a1 * 2u + (e & 1u); a2 = a2 * 2u + (e >> 16); }
+                }
+                h = a1;
+                if (DOUBLE) {
+                    const unsigned e16 = cs_tab[nxt[k] * 32 + lane];            // the byte after the chunk
+                    const unsigned need = ((a2 << 1) | (e16 >> 16)) & 0xffffu;   // set 2 holds the byte after byte i
+                    h = a1 & need;
+                }
+            } else {
+                // double shufti (blockDoubleMask, src/nfa/x86/shufti.hpp:49-74): entry = mask-1 byte | mask-2 byte << 8, both
+                // with CLEAR bits for members; byte i hits when (m1[c_i] | m2[c_i+1]) leaves some pair bucket clear
+                unsigned e[17];
+#pragma unroll
+                for (int i = 0; i < 16; i++) {
+                    const unsigned c = __byte_perm(w[i >> 2], 0, 0x4440 + (i & 3));
+                    asm volatile("{ .reg .u32 a; mad.lo.u32 a, %1, 128, %2; ld.shared.u32 %0, [a]; }" : "=r"(e[i]) : "r"(c), "r"(tab_l));
+                }
+                e[16] = cs_tab[nxt[k] * 32 + lane];
+                h = 0;
+#pragma unroll
+                for (int i = 0; i < 16; i++) {
+                    const unsigned pr = (e[i] | (e[i + 1] >> 8)) & 0xffu;     // 0xff = no bucket admits the pair
+                    h = h * 2u + (((pr + 1u) >> 8) ^ 1u);
+                }
+                a1 = 0;
+                if (!inner) {
+#pragma unroll
+                    for (int i = 0; i < 16; i++) a1 = a1 * 2u + ((((e[i] & 0xffu) + 1u) >> 8) ^ 1u);  // first byte alone (last-byte rule)
+                }
             }
             if (!inner) {
                 const unsigned long long ch = tile * CS_TILE_CHUNKS + (unsigned)k * 32 + lane;
@@ -255,8 +280,9 @@ long long search_staged(const ClassParams &p, bool reverse, int repeats, float *
     unsigned grid = (unsigned)((chunks + 255) / 256);
     if (grid > 148 * 8) grid = 148 * 8;
     // every kind but the double shufti is a per-byte set test: one table, one kernel (k_class_scan)
-    const bool table_kind = p.kind != DSHUFTI;
+    const bool table_kind = !(p.kind == DSHUFTI && reverse);
     const bool dbl = p.kind == DVERM;
+    const bool dsh = p.kind == DSHUFTI;
     if (table_kind) {
         unsigned tab[256];
         for (unsigned c = 0; c < 256; c++) {
@@ -266,9 +292,11 @@ long long search_staged(const ClassParams &p, bool reverse, int repeats, float *
             case TRUFFLE: in1 = ((((c & 0x80) ? p.b : p.a)[c & 15] >> ((c >> 4) & 7)) & 1) != 0; break;
             case VERM: in1 = (uint8_t)(c & p.casemask) == p.c1; break;
             case NVERM: in1 = (uint8_t)(c & p.casemask) != p.c1; break;
+            case DSHUFTI: in1 = false; break;
             default: in1 = (uint8_t)(c & p.casemask) == p.c1; in2 = (uint8_t)(c & p.casemask) == p.c2; break;
             }
             tab[c] = (in1 ? 1u : 0u) | (in2 ? 0x10000u : 0u);
+            if (dsh) tab[c] = (unsigned)(uint8_t)(p.a[c & 15] | p.b[c >> 4]) | ((unsigned)(uint8_t)(p.a2[c & 15] | p.b2[c >> 4]) << 8);
         }
         if (!ws.d_tab && cudaMalloc((void **)&ws.d_tab, sizeof(tab)) != cudaSuccess) return -2;
         cudaMemcpy(ws.d_tab, tab, sizeof(tab), cudaMemcpyHostToDevice);
@@ -285,9 +313,10 @@ long long search_staged(const ClassParams &p, bool reverse, int repeats, float *
         cudaMemcpy(ws.d_res, &init, 8, cudaMemcpyHostToDevice);
         if (ms) cudaEventRecord(e0);
         if (table_kind) {
-            if (dbl) k_class_scan<false, true><<<grid, CS_THREADS>>>(ws.d_buf, len, ws.d_tab, ws.d_res);
-            else if (reverse) k_class_scan<true, false><<<grid, CS_THREADS>>>(ws.d_buf, len, ws.d_tab, ws.d_res);
-            else k_class_scan<false, false><<<grid, CS_THREADS>>>(ws.d_buf, len, ws.d_tab, ws.d_res);
+            if (dsh) k_class_scan<false, 2><<<grid, CS_THREADS>>>(ws.d_buf, len, ws.d_tab, ws.d_res);
+            else if (dbl) k_class_scan<false, 1><<<grid, CS_THREADS>>>(ws.d_buf, len, ws.d_tab, ws.d_res);
+            else if (reverse) k_class_scan<true, 0><<<grid, CS_THREADS>>>(ws.d_buf, len, ws.d_tab, ws.d_res);
+            else k_class_scan<false, 0><<<grid, CS_THREADS>>>(ws.d_buf, len, ws.d_tab, ws.d_res);
         } else if (reverse) k_class_search<true><<<grid, 256>>>(ws.d_buf, len, p, ws.d_res);
         else k_class_search<false><<<grid, 256>>>(ws.d_buf, len, p, ws.d_res);
         if (ms) {
