@@ -262,7 +262,7 @@ def main():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--config", default="c2", choices=["c1", "c2", "c3", "c3n", "c3d", "c4", "c4l"])
     ap.add_argument("--patterns", type=int, default=6, help="c3d: number of patterns in the DFA")
-    ap.add_argument("--bytes", type=int, default=64 << 20)
+    ap.add_argument("--bytes", type=int, default=0, help="batch size (default: 64 MiB; c3: the 256 MiB corpus SURVEY 8d states)")
     ap.add_argument("--ref-sample-bytes", type=int, default=0)
     ap.add_argument("--cpu-sample-bytes", type=int, default=0)
     ap.add_argument("--frontend", type=int, default=0)
@@ -271,6 +271,8 @@ def main():
     ap.add_argument("--no-verify", action="store_true", help="skip the sharded-equals-single check")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    if not args.bytes:
+        args.bytes = (256 << 20) if args.config == "c3" else (64 << 20)
     # bounded CPU samples (the NFA path is ~100x slower per byte on the CPU than the literal path)
     if not args.ref_sample_bytes:
         args.ref_sample_bytes = (1 << 20) if args.config in ("c3", "c4") else (8 << 20) if args.config in ("c3n", "c3d") else (64 << 20)

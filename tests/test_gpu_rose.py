@@ -57,3 +57,26 @@ def test_scan_one_buffer_callback_order(ref):
     assert gpu.scan(db, text, sc, lambda i, f, t, fl, c: got.append((i, t)) or 0) == 0
     exp = sorted(regen.brute_force(ex, [0, 2, 0, 0], [5, 6, 7, 8], text), key=lambda x: (x[1], x[0]))
     assert got == exp
+
+
+def test_packed_and_single_engine_launches_agree(ref):
+    """Engines whose tables fit shared memory together share a launch (k_mcclellan_pack, work item = (buffer, engine));
+    option pack = 0 steps them one launch each.  Same matches either way, and as the reference runtime's."""
+    ex, fl, ids = W.c3_patterns(max_patterns=400, state_budget=1 << 30)
+    for dfa_states in (64, 256, 1024):      # McClellan8 packs of 4, mixed, McClellan16 pairs
+        db = litdb.compile_regex_rose(ex, fl, ids, dfa_states=dfa_states)
+        flat, offs = W.c3_corpus(1 << 19, seed=5 + dfa_states)
+        data = flat.tobytes()
+        bufs = [data[int(offs[k]):int(offs[k + 1])] for k in range(len(offs) - 1)] + [b"", b"x"]
+        out = []
+        for pack in (1, 0):
+            sc = gpu.alloc_scratch(db)
+            sc.set_option("pack", pack)
+            out.append(gpu_batch(db, bufs, sc))
+            launches = sc.stats()["kernel_launches"]
+            sc.close()
+            out.append(launches)
+        assert out[0] == out[2] and len(out[0]) > 50
+        assert out[1] < out[3]                       # fewer launches when packed
+        if dfa_states == 256:
+            assert out[0] == ref_batch(ref, db, bufs)

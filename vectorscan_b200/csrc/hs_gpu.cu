@@ -1101,6 +1101,7 @@ struct hs_gpu_scratch {
                              // tables (k_scan), 2: k_turbo, 3: k_turbo2
     long opt_grid = 0;
     long opt_warps = 0;      // k_turbo2: cap on warps per CTA (0 = as many as fit)
+    long opt_pack = 1;       // engines of a multi-engine database that fit shared memory together share a launch
     long opt_pipeline = 0;   // host batches: 0 one copy then one scan (measured fastest), 1 chunk gathered input, 2 always chunk
     size_t smem_optin_max = 227 * 1024;
     u64 arena_hint = 1 << 16;
@@ -1503,12 +1504,62 @@ hs_error_t launch_mcclellan(hs_gpu_scratch *s, const DbImage *im, const DevCorpu
 // every engine steps the whole batch (its own kernel launch; a block shorter than the engine's NFA.minWidth cannot
 // match it), all of them append to ONE event queue, and one report pass runs the Rose report programs; the finalize
 // sorts by (buffer, offset, id) and applies the dedupe keys, which is what the catch-up queue's offset order is for.
+template <bool WIDE16>
+hs_error_t launch_mcclellan_pack(hs_gpu_scratch *s, const DbImage *im, const DevMccPack &pk, size_t dyn, const DevCorpus &cp) {
+    CU_OK(ensure_smem_optin(s, (const void *)k_mcclellan_pack<WIDE16>, dyn));
+    u32 grid = s->opt_grid > 0 ? (u32)s->opt_grid : (u32)s->sm_count;
+    const unsigned long long items = (unsigned long long)cp.count * pk.n;
+    const unsigned long long need = (items + 31) / 32;
+    if (grid > need) grid = need ? (u32)need : 1;
+    CU_OK(s->recs2.reserve(s->lx_event_hint));
+    const DevLxEvents evq{reinterpret_cast<LxEvent *>(s->recs2.p), s->d_ctl + 7, s->recs2.cap};
+    k_mcclellan_pack<WIDE16><<<grid, MCC_THREADS, dyn, s->stream>>>(im->dev, pk, cp, evq, s->d_ctl + 6);
+    CU_OK(cudaGetLastError());
+    s->stats.kernel_launches++;
+    return HS_SUCCESS;
+}
+
+// Full-Rose database of outfix engines (roseBlockExec with outfixes only, src/rose/block.c:345-422, catchup.c:612-672):
+// every engine steps the whole batch (a block shorter than the engine's NFA.minWidth cannot match it), all of them append
+// to ONE event queue, and one report pass runs the Rose report programs; the finalize sorts by (buffer, offset, id) and
+// applies the dedupe keys, which is what the catch-up queue's offset order is for.  McClellan engines whose tables fit
+// shared memory together share a launch (k_mcclellan_pack: work item = (buffer, engine)); option "pack" = 0 turns that off.
 hs_error_t launch_outfixes(hs_gpu_scratch *s, const DbImage *im, const DevCorpus &cp, const DevArena &ar) {
-    for (size_t qi = 0; qi < im->subs.size(); qi++) {
+    bool first = true;
+    for (size_t qi = 0; qi < im->subs.size();) {
         const DbImage *sub = im->subs[qi];
-        if (qi) CU_OK(cudaMemsetAsync(s->d_ctl + 6, 0, sizeof(unsigned long long), s->stream));  // the buffer counter
+        if (!first) CU_OK(cudaMemsetAsync(s->d_ctl + 6, 0, sizeof(unsigned long long), s->stream));  // the work counter
+        first = false;
+        auto packable = [](const DbImage *e) {
+            return e->view.kind == ENG_MCCLELLAN && e->mcc.in_smem && !e->mcc.has_sherman;
+        };
+        if (s->opt_pack && packable(sub)) {
+            DevMccPack pk{};
+            size_t tables = 0;
+            size_t k = qi;
+            while (k < im->subs.size() && pk.n < (u32)MCC_PACK_MAX && packable(im->subs[k]) &&
+                   im->subs[k]->mcc.wide16 == sub->mcc.wide16) {
+                const size_t tb = round_up((size_t)im->subs[k]->mcc.tab_bytes + 8, 16);
+                if ((size_t)(pk.n + 1) * MCC_RM_BYTES + tables + tb > MCC_SMEM_MAX) break;
+                pk.m[pk.n] = im->subs[k]->mcc;
+                pk.tab_off[pk.n] = (u32)tables;  // relative to the end of the symbol tables; fixed up below
+                tables += tb;
+                pk.n++;
+                k++;
+            }
+            if (pk.n >= 2) {
+                for (u32 e = 0; e < pk.n; e++) pk.tab_off[e] += pk.n * (u32)MCC_RM_BYTES;
+                const size_t dyn = (size_t)pk.n * MCC_RM_BYTES + tables;
+                const hs_error_t rv = sub->mcc.wide16 ? launch_mcclellan_pack<true>(s, im, pk, dyn, cp)
+                                                       : launch_mcclellan_pack<false>(s, im, pk, dyn, cp);
+                if (rv != HS_SUCCESS) return rv;
+                qi = k;
+                continue;
+            }
+        }
         const hs_error_t rv = sub->view.kind == ENG_LIMEX ? launch_limex(s, sub, cp, ar, false) : launch_mcclellan(s, sub, cp, ar, false);
         if (rv != HS_SUCCESS) return rv;
+        qi++;
     }
     const DevLxEvents evq{reinterpret_cast<LxEvent *>(s->recs2.p), s->d_ctl + 7, s->recs2.cap};
     k_limex_report<<<(u32)s->sm_count, LX_THREADS, 0, s->stream>>>(im->dev, cp, ar, evq);
@@ -2266,6 +2317,7 @@ hs_error_t hs_gpu_clone_scratch(const hs_gpu_scratch_t *src, hs_gpu_scratch_t **
     }
     if (!d) return HS_INVALID;
     d->opt_frontend = src->opt_frontend;
+    d->opt_pack = src->opt_pack;
     d->opt_grid = src->opt_grid;
     d->opt_warps = src->opt_warps;
     *dest = d;
@@ -2548,6 +2600,7 @@ hs_error_t hs_gpu_set_option(hs_gpu_scratch_t *scratch, const char *name, long v
     if (!strcmp(name, "warps")) { scratch->opt_warps = value; return HS_SUCCESS; }
     if (!strcmp(name, "pipeline")) { scratch->opt_pipeline = value; return HS_SUCCESS; }
     if (!strcmp(name, "ordered")) { scratch->opt_ordered = value; return HS_SUCCESS; }
+    if (!strcmp(name, "pack")) { scratch->opt_pack = value; return HS_SUCCESS; }
     if (!strcmp(name, "count_ops")) {
         if (!value) { scratch->op_counts.release(); return HS_SUCCESS; }
         if (ensure_device(scratch) != HS_SUCCESS || scratch->op_counts.reserve(128) != cudaSuccess) return HS_NOMEM;
