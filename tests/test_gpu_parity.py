@@ -350,3 +350,32 @@ def test_fat_teddy_databases(ref, frontend):
         assert got == sorted((i, t) for (_, i, t) in ref_scan(ref, db, [text]))
         ran += 1
     assert ran > 15
+
+
+def test_single_match_sets_are_resolved_on_the_device(ref):
+    """HS_FLAG_SINGLEMATCH: the device array hs_gpu_scan_corpus leaves behind is already the resolved one (first record per
+    (buffer, exhaustion key), quiet records dropped) -- count, fetched matches and hs_gpu_histogram agree with the
+    reference runtime."""
+    import ctypes as C
+    import torch
+    rng = random.Random(12)
+    lits, flags, ids, _ = litgen.random_case(rng, None, 300, b"abcdefgh", 10)
+    flags = [f | (8 if k % 2 else 0) for k, f in enumerate(flags)]
+    by_id = {}
+    for k, i in enumerate(ids):
+        by_id.setdefault(i, flags[k] & 8)
+        flags[k] = (flags[k] & 1) | by_id[i]
+    db = litdb.compile_lit_multi(lits, flags, ids)
+    bufs = [bytes(rng.choice(b"abcdefgh") for _ in range(rng.choice([0, 3, 200, 3000]))) for _ in range(300)]
+    flat = np.frombuffer(b"".join(bufs), dtype=np.uint8)
+    offs = np.concatenate([[0], np.cumsum([len(b) for b in bufs])]).astype(np.uint64)
+    sc = gpu.alloc_scratch(db)
+    n = gpu.scan_corpus(db, gpu.Corpus(flat, offs), sc)
+    exp = ref_scan(ref, db, bufs)
+    assert n == len(exp) and len(exp) > 1000
+    hist = torch.zeros(max(ids) + 1, dtype=torch.int64, device="cuda")
+    assert gpu.lib().hs_gpu_histogram(sc.ptr, C.c_void_p(hist.data_ptr()), max(ids) + 1) == 0
+    got = [(int(b), int(i), int(t)) for b, i, t in gpu.fetch_matches(sc)]
+    assert got == exp
+    want = np.bincount([i for _, i, _ in exp], minlength=max(ids) + 1)
+    assert (hist.cpu().numpy() == want).all()

@@ -936,6 +936,42 @@ __global__ void k_flag_dups(const Rec *in, u8 *keep, u64 n) {
     if (i < n) keep[i] = (i && RecDup()(in[i - 1], in[i])) ? 0 : 1;
 }
 
+// ---- single-match (exhaustion key) resolution on the device ------------------------------------------------------
+// The records are sorted by (buffer, to, id): the report an exhaustible pattern keeps is the FIRST record of its
+// (buffer, ekey) pair; quiet records (SET_EXHAUST) exhaust the key and are dropped.  Pass 1 files every keyed record
+// under its pair in an open-addressing table and keeps the smallest record index (atomicMin); pass 2 keeps a keyed
+// record only when it is that smallest index.  What roseReportExhaust / CHECK_EXHAUSTED do one match at a time
+// (src/report.h:121-153, program_runtime.c:2665-2680), restated for records that are all known at once.
+__device__ __forceinline__ u32 ekey_slot(unsigned long long key, u32 mask) {
+    return (u32)((key * 0x9E3779B97F4A7C15ull) >> 32) & mask;
+}
+
+__global__ void k_ekey_insert(const Rec *recs, u64 n, unsigned long long *keys, u32 *first, u32 mask) {
+    const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const Rec r = recs[i];
+    if (!(r.aux & AUX_EKEY)) return;
+    const unsigned long long key = ((unsigned long long)r.buf << 32) | (r.aux & AUX_KEYMASK);
+    for (u32 h = ekey_slot(key, mask);; h = (h + 1) & mask) {
+        const unsigned long long prev = atomicCAS(&keys[h], ~0ull, key);
+        if (prev == ~0ull || prev == key) { atomicMin(&first[h], (u32)i); return; }
+    }
+}
+
+__global__ void k_ekey_filter(const Rec *recs, u64 n, const unsigned long long *keys, const u32 *first, u32 mask, u8 *keep) {
+    const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const Rec r = recs[i];
+    bool k = !(r.aux & AUX_QUIET);
+    if (r.aux & AUX_EKEY) {
+        const unsigned long long key = ((unsigned long long)r.buf << 32) | (r.aux & AUX_KEYMASK);
+        u32 h = ekey_slot(key, mask);
+        while (keys[h] != key) h = (h + 1) & mask;
+        k = k && first[h] == (u32)i;
+    }
+    keep[i] = k ? 1 : 0;
+}
+
 __global__ void k_histogram(const hs_gpu_match_t *m, u64 n, unsigned long long *hist, u32 n_ids) {
     const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n && m[i].id < n_ids) atomicAdd(&hist[m[i].id], 1ull);
@@ -1072,6 +1108,8 @@ struct hs_gpu_scratch {
     DevBuf<Rec> recs, recs2;
     DevBuf<hs_gpu_match_t> d_matches;
     DevBuf<u8> cub_tmp, keep;
+    DevBuf<unsigned long long> ekey_keys;   // single-match resolution: open-addressing table (pair -> first record index)
+    DevBuf<u32> ekey_first;
     DevBuf<u32> seg_count;
     u64 seg_cap_hint = 256;
     u64 out_hint = 1 << 16;                    // capacity of the ordered path's output arrays (grown on demand)
@@ -1813,7 +1851,39 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
         CU_OK(cudaGetLastError());
         st.kernel_launches += 2;  // k_flag_dups + k_convert (CUB's sort/select kernels are not counted)
     }
-    if (!small_done) {
+    if (im->view.ekey_count && n_out) {
+        // records (sorted, deduped) are in recs2: resolve the exhaustion keys there, compact into recs, convert
+        if (n_out >= 0xffffffffull) return HS_NOMEM;
+        u32 H = 1024;
+        while ((u64)H < 2 * n_out) H <<= 1;
+        CU_OK(s->ekey_keys.reserve(H));
+        CU_OK(s->ekey_first.reserve(H));
+        CU_OK(s->keep.reserve(n_out));
+        CU_OK(s->recs.reserve(n_out));
+        CU_OK(s->d_matches.reserve(n_out));
+        CU_OK(cudaMemsetAsync(s->ekey_keys.p, 0xff, (size_t)H * 8, s->stream));
+        CU_OK(cudaMemsetAsync(s->ekey_first.p, 0xff, (size_t)H * 4, s->stream));
+        const unsigned g = (unsigned)((n_out + 255) / 256);
+        k_ekey_insert<<<g, 256, 0, s->stream>>>(s->recs2.p, n_out, s->ekey_keys.p, s->ekey_first.p, H - 1);
+        k_ekey_filter<<<g, 256, 0, s->stream>>>(s->recs2.p, n_out, s->ekey_keys.p, s->ekey_first.p, H - 1, s->keep.p);
+        CU_OK(cudaGetLastError());
+        size_t tmp = 0;
+        cub::DeviceSelect::Flagged((void *)nullptr, tmp, s->recs2.p, s->keep.p, s->recs.p, (unsigned long long *)nullptr,
+                                   (long long)n_out, s->stream);
+        CU_OK(s->cub_tmp.reserve(tmp));
+        size_t tb = s->cub_tmp.bytes();
+        CU_OK(cub::DeviceSelect::Flagged(s->cub_tmp.p, tb, s->recs2.p, s->keep.p, s->recs.p, s->d_ctl + 4, (long long)n_out, s->stream));
+        CU_OK(cudaMemcpyAsync(s->h_ctl + 4, s->d_ctl + 4, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
+        CU_OK(cudaStreamSynchronize(s->stream));
+        n_out = s->h_ctl[4];
+        if (n_out) {
+            k_convert<<<(unsigned)((n_out + 255) / 256), 256, 0, s->stream>>>(s->recs.p, s->d_matches.p, n_out);
+            CU_OK(cudaGetLastError());
+        }
+        st.kernel_launches += 3;
+        CU_OK(cudaEventRecord(s->ev[3], s->stream));
+        CU_OK(cudaEventSynchronize(s->ev[3]));
+    } else if (!small_done) {
         CU_OK(cudaEventRecord(s->ev[3], s->stream));
         CU_OK(cudaEventSynchronize(s->ev[3]));
     }
@@ -1823,35 +1893,6 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
     s->n_matches = n_out;
     st.matches = n_out;
     return HS_SUCCESS;
-}
-
-// Single-match (exhaustion key) resolution and removal of quiet records, on the host copy.
-// Records arrive sorted by (buffer, to, id): the first record of an (buffer, ekey) pair is the earliest.
-u64 resolve_exhaustion(hs_gpu_scratch *s, const Rec *recs, u64 n, hs_gpu_match_t *out, u32 ekey_count) {
-    (void)s;
-    // one linear pass: a flag per exhaustion key, cleared (through the list of keys touched) when the buffer changes
-    std::vector<u8> seen((size_t)ekey_count + 1, 0);
-    std::vector<u32> touched;
-    u32 cur_buf = ~0u;
-    u64 m = 0;
-    for (u64 i = 0; i < n; i++) {
-        const Rec &r = recs[i];
-        if (r.buf != cur_buf) {
-            for (u32 k : touched) seen[k] = 0;
-            touched.clear();
-            cur_buf = r.buf;
-        }
-        if (r.aux & AUX_EKEY) {
-            u32 k = r.aux & AUX_KEYMASK;
-            if (k > ekey_count) k = ekey_count;
-            if (seen[k]) continue;
-            seen[k] = 1;
-            touched.push_back(k);
-        }
-        if (r.aux & AUX_QUIET) continue;
-        out[m++] = hs_gpu_match_t{r.buf, r.id, (uint64_t)r.to};
-    }
-    return m;
 }
 
 hs_error_t fetch_matches(hs_gpu_scratch *s, DbImage *im) {
@@ -1870,19 +1911,11 @@ hs_error_t fetch_matches(hs_gpu_scratch *s, DbImage *im) {
     }
     if (n) {
         CU_OK(cudaEventRecord(s->ev[4], s->stream));
-        const bool need_recs = im && im->view.ekey_count > 0;
-        static_assert(sizeof(Rec) == sizeof(hs_gpu_match_t), "record sizes");
-        CU_OK(cudaMemcpyAsync(s->h_matches, need_recs ? (const void *)s->recs2.p : (const void *)s->d_matches.p,
-                              n * sizeof(hs_gpu_match_t), cudaMemcpyDeviceToHost, s->stream));
+        (void)im;
+        CU_OK(cudaMemcpyAsync(s->h_matches, s->d_matches.p, n * sizeof(hs_gpu_match_t), cudaMemcpyDeviceToHost, s->stream));
         CU_OK(cudaEventRecord(s->ev[5], s->stream));
         CU_OK(cudaEventSynchronize(s->ev[5]));
         cudaEventElapsedTime(&st.d2h_ms, s->ev[4], s->ev[5]);
-        if (need_recs) {
-            std::vector<Rec> tmp(n);
-            std::memcpy(tmp.data(), s->h_matches, n * sizeof(Rec));
-            s->n_matches = resolve_exhaustion(s, tmp.data(), n, s->h_matches, im->view.ekey_count);
-            st.matches = s->n_matches;
-        }
     }
     s->fetched = true;
     return HS_SUCCESS;
@@ -2490,9 +2523,6 @@ hs_error_t hs_gpu_scan_corpus(const hs_database_t *db, const hs_gpu_corpus_t *co
     scratch->stats.d2h_ms = 0;
     rv = scan_device(scratch, im, *corpus);
     if (rv != HS_SUCCESS) return rv;
-    // single-match (exhaustion key) sets: the device array still holds every repeat and the quiet records; the count
-    // the caller gets is the resolved one (the resolution runs on the fetched copy)
-    if (im->view.ekey_count && (rv = fetch_matches(scratch, im)) != HS_SUCCESS) return rv;
     if (n_matches) *n_matches = scratch->n_matches;
     return HS_SUCCESS;
 }
@@ -2550,9 +2580,6 @@ hs_error_t hs_gpu_histogram(hs_gpu_scratch_t *scratch, void *device_hist_u64, ui
     if (!scratch || scratch->magic != 0x47505553 || !device_hist_u64) return HS_INVALID;
     InUseGuard g(scratch);
     if (!g.ok) return HS_SCRATCH_IN_USE;
-    // d_matches of a single-match (exhaustion key) set still holds every repeat and the quiet records until the fetch
-    // resolves them on the host copy: refuse rather than count them
-    if (scratch->last_image && static_cast<DbImage *>(scratch->last_image)->view.ekey_count) return HS_INVALID;
     const u64 n = scratch->n_matches;
     if (n) {
         k_histogram<<<(unsigned)((n + 255) / 256), 256, 0, scratch->stream>>>(
