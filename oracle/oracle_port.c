@@ -132,6 +132,40 @@ static int check_mask_n(const struct scan_state *s, const u8 *and_m, const u8 *c
     return 1;
 }
 
+/* roseCheckShufti16x8 ... 64x16 (rose/program_runtime.c:992-1250, validateShuftiMask* rose/validate_shufti.h:46-372):
+ * window byte k is in its class when (lo[c & 15] & hi[c >> 4] & bucket_select[k]) != 0 for one of the two bucket
+ * halves; every byte inside the buffer must have (not in class) == its neg_mask bit.  Layouts: rose/rose_program.h. */
+static int check_shufti(const struct scan_state *s, const u8 *pc, u64 end) {
+    u32 n, wide = 0, lane = 0;
+    const u8 *hi1, *lo1, *hi2 = NULL, *lo2 = NULL, *sel_lo, *sel_hi = NULL;
+    u64 neg;
+    int32_t off;
+    switch (pc[0]) {
+    case 12: n = 16; lo1 = pc + 1; hi1 = pc + 17; sel_lo = pc + 33; neg = rd32(pc + 52); off = (int32_t)rd32(pc + 56); break;
+    case 13: n = 32; hi1 = pc + 1; lo1 = pc + 17; sel_lo = pc + 33; neg = rd32(pc + 68); off = (int32_t)rd32(pc + 72); break;
+    case 14: n = 16; wide = 1; hi1 = pc + 1; hi2 = pc + 17; lo1 = pc + 33; lo2 = pc + 49; sel_lo = pc + 65; sel_hi = pc + 81;
+             neg = rd32(pc + 100); off = (int32_t)rd32(pc + 104); break;
+    case 15: n = 32; wide = 1; hi1 = pc + 1; hi2 = pc + 17; lo1 = pc + 33; lo2 = pc + 49; sel_hi = pc + 65; sel_lo = pc + 97;
+             neg = rd32(pc + 132); off = (int32_t)rd32(pc + 136); break;
+    case 67: n = 64; lane = 16; hi1 = pc + 1; lo1 = pc + 65; sel_lo = pc + 129; neg = rd64(pc + 200); off = (int32_t)rd32(pc + 208); break;
+    default: n = 64; wide = 1; lane = 16; hi1 = pc + 1; hi2 = pc + 65; lo1 = pc + 129; lo2 = pc + 193; sel_hi = pc + 257; sel_lo = pc + 321;
+             neg = rd64(pc + 392); off = (int32_t)rd32(pc + 400); break;
+    }
+    if (off < 0 && (u64)(-(int64_t)off) > end) return 0;
+    int64_t base = (int64_t)end + off;
+    for (u32 k = 0; k < n; k++) {
+        int64_t o = base + k;
+        if (o < 0 || o >= (int64_t)s->len) continue;
+        u8 c = s->buf[o];
+        u32 ln = lane ? (k & ~15u) : 0;
+        u8 hit = (u8)(lo1[ln + (c & 15)] & hi1[ln + (c >> 4)] & sel_lo[k]);
+        if (wide) hit |= (u8)(lo2[ln + (c & 15)] & hi2[ln + (c >> 4)] & sel_hi[k]);
+        if ((hit == 0) != (int)((neg >> k) & 1)) return 0;
+    }
+    return 1;
+}
+static u32 shufti_fail_at(u8 code) { return code == 12 ? 60 : code == 13 ? 76 : code == 14 ? 108 : code == 15 ? 140 : code == 67 ? 212 : 404; }
+
 static int catch_up(struct scan_state *s, u64 end);
 
 /* roseRunProgram_l.  `end` = offset one past the literal's last byte (lit_offset_adjust = 1).
@@ -167,6 +201,11 @@ static int run_program(struct scan_state *s, u32 prog, u64 end) {
             if (!check_mask_n(s, pc + 1, pc + 65, rd64(pc + 136), 64, (int32_t)rd32(pc + 144), end)) pc += rd32(pc + 148);
             else pc += 152;
             break;
+        case 12: case 13: case 14: case 15: case 67: case 68: { /* CHECK_SHUFTI_16x8, 32x8, 16x16, 32x16, 64x8, 64x16 */
+            const u32 fj = shufti_fail_at(pc[0]);
+            if (!check_shufti(s, pc, end)) pc += rd32(pc + fj); else pc += (fj + 4 + 7) & ~7u;
+            break;
+        }
         case OP_CATCH_UP: /* roseCatchUpTo(end), program_runtime.c:2499-2504: engine matches up to `end` come first */
             if (catch_up(s, end) < 0) return -1;
             pc += 8;

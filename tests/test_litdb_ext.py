@@ -151,7 +151,9 @@ def test_full_rose_literal_databases_with_class_lookarounds(ref, seed):
         for k, v in enumerate(gpu.database_opcodes(db)):
             seen[k] += v
         exp = litgen.brute_force_ext(lits, flags, ids, ext, text, goff)
-        assert sorted(ref_scan(ref, db, text)) == exp, (kind, len(lits), len(text))
+        got = ref_scan(ref, db, text)
+        assert sorted(got) == exp, (kind, len(lits), len(text))
+        assert oracle_port.scan(db, text) == (0, got)   # the C restatement incl. CHECK_SHUFTI_*: same callback sequence
         total += 1
     assert total >= 40
     assert seen[OP["CHECK_SHUFTI_16x8"]] > 0 and seen[OP["CHECK_SHUFTI_32x8"]] > 0
