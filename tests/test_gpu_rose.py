@@ -60,23 +60,35 @@ def test_scan_one_buffer_callback_order(ref):
 
 
 def test_packed_and_single_engine_launches_agree(ref):
-    """Engines whose tables fit shared memory together share a launch (k_mcclellan_pack, work item = (buffer, engine));
-    option pack = 0 steps them one launch each.  Same matches either way, and as the reference runtime's."""
+    """Multi-engine databases, option "pack": 2 (default) = k_dfa_pack, several DFAs stepped together per buffer on a
+    joint alphabet; 1 = k_mcclellan_pack, work item = (buffer, engine); 0 = one launch per engine.  Same matches every
+    way, and as the reference runtime's."""
     ex, fl, ids = W.c3_patterns(max_patterns=400, state_budget=1 << 30)
-    for dfa_states in (64, 256, 1024):      # McClellan8 packs of 4, mixed, McClellan16 pairs
+    for dfa_states in (64, 256, 1024):      # McClellan8 packs of 8, mixed, McClellan16 pairs
         db = litdb.compile_regex_rose(ex, fl, ids, dfa_states=dfa_states)
         flat, offs = W.c3_corpus(1 << 19, seed=5 + dfa_states)
         data = flat.tobytes()
         bufs = [data[int(offs[k]):int(offs[k + 1])] for k in range(len(offs) - 1)] + [b"", b"x"]
-        out = []
-        for pack in (1, 0):
+        out, launches = {}, {}
+        for pack in (2, 1, 0):
             sc = gpu.alloc_scratch(db)
             sc.set_option("pack", pack)
-            out.append(gpu_batch(db, bufs, sc))
-            launches = sc.stats()["kernel_launches"]
+            out[pack] = gpu_batch(db, bufs, sc)
+            launches[pack] = sc.stats()["kernel_launches"]
             sc.close()
-            out.append(launches)
-        assert out[0] == out[2] and len(out[0]) > 50
-        assert out[1] < out[3]                       # fewer launches when packed
+        assert out[2] == out[1] == out[0] and len(out[0]) > 50
+        assert launches[2] < launches[0] and launches[1] < launches[0]      # fewer launches when packed
         if dfa_states == 256:
-            assert out[0] == ref_batch(ref, db, bufs)
+            assert out[2] == ref_batch(ref, db, bufs)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_fused_packs_on_random_sets(ref, seed):
+    """k_dfa_pack on seeded sets with small DFA groups (many engines per pack: D = 2, 4, 8), ragged buffers."""
+    rng = random.Random(9300 + seed)
+    ex, fl, ids, smp = regen.random_set(rng, rng.randint(6, 14), True)
+    db = litdb.compile_regex_rose(ex, fl, ids, dfa_states=rng.choice([12, 24, 60]))
+    bufs = [regen.random_text(rng, ex, rng.choice([0, 1, 15, 16, 17, 33, 200, 1400]), smp) for _ in range(80)]
+    got = gpu_batch(db, bufs)
+    assert got == ref_batch(ref, db, bufs)
+    assert got == brute_batch(ex, fl, ids, bufs)

@@ -857,6 +857,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_scan(const DevDb db, const DevCo
 #include "turbo2.cuh"
 #include "limex.cuh"
 #include "mcclellan.cuh"
+#include "dfapack.cuh"
 
 // ------------------------------------------------------------------------------------------------
 // finalize: Rec (sorted, deduped) -> hs_gpu_match_t
@@ -1060,9 +1061,17 @@ struct DbImage {  // one uploaded database
     // full-Rose database of outfix engines (view.kind == ENG_MULTI): one image per queue, sharing this image's bytecode
     std::vector<DbImage *> subs;
     bool owns_bc = true;
+    // McClellan engines of `subs` re-laid on a joint alphabet and stepped together (dfapack.cuh); packed[q] = engine q is
+    // in one of them
+    struct DfaPackImage { DevDfaPack dev; u8 *d_blob = nullptr; int D = 2; };
+    std::vector<DfaPackImage> packs;
+    std::vector<u8> packed;
     void release() {
         for (DbImage *sub : subs) { sub->release(); delete sub; }
         subs.clear();
+        for (DfaPackImage &pk : packs) if (pk.d_blob) cudaFree(pk.d_blob);
+        packs.clear();
+        packed.clear();
         if (d_bc && owns_bc) cudaFree(d_bc);
         if (d_fdr) cudaFree(d_fdr);
         if (d_teddy) cudaFree(d_teddy);
@@ -1139,7 +1148,8 @@ struct hs_gpu_scratch {
                              // tables (k_scan), 2: k_turbo, 3: k_turbo2
     long opt_grid = 0;
     long opt_warps = 0;      // k_turbo2: cap on warps per CTA (0 = as many as fit)
-    long opt_pack = 1;       // engines of a multi-engine database that fit shared memory together share a launch
+    long opt_pack = 2;       // multi-engine databases: 0 one launch per engine, 1 k_mcclellan_pack (work item = (buffer,
+                             // engine)), 2 k_dfa_pack (D engines stepped together per buffer, tables on a joint alphabet)
     long opt_pipeline = 0;   // host batches: 0 one copy then one scan (measured fastest), 1 chunk gathered input, 2 always chunk
     size_t smem_optin_max = 227 * 1024;
     u64 arena_hint = 1 << 16;
@@ -1236,6 +1246,111 @@ hs_error_t build_engine_image(hs_gpu_scratch *s, DbImage *im) {
         D.has_sherman = M.wide16 && M.sherman_limit < M.states ? 1u : 0u;
     }
     return HS_SUCCESS;
+}
+
+// Packs of McClellan outfix engines for k_dfa_pack (dfapack.cuh): engines are taken in queue order while the pack's
+// tables -- every engine's successor table re-laid on the pack's JOINT alphabet, 16-bit entries with the accept flag --
+// fit shared memory beside the class table.  Two bytes share a joint class when every engine of the pack maps them to
+// the same symbol.  A pack of one is not built (k_mcclellan serves it).
+hs_error_t build_dfa_packs(hs_gpu_scratch *s, DbImage *im) {
+    const size_t nq = im->subs.size();
+    im->packed.assign(nq, 0);
+    auto packable = [&](size_t q) {
+        const DbImage *e = im->subs[q];
+        const DbView::Mcc &M = e->view.mcc;
+        return e->view.kind == ENG_MCCLELLAN && !e->mcc.has_sherman && !e->mcc.accepts_eod && M.states <= mcclellan::STATE_MASK;
+    };
+    auto joint = [&](const std::vector<size_t> &members, std::vector<u32> &cls_of) {  // -> number of joint classes
+        std::map<std::vector<u8>, u32> seen;
+        cls_of.assign(256, 0);
+        for (u32 c = 0; c < 256; c++) {
+            std::vector<u8> sig;
+            for (size_t q : members) sig.push_back(rd8(im->view.bc, im->subs[q]->view.mcc.m_off + mcclellan::remap + c));
+            auto it = seen.find(sig);
+            if (it == seen.end()) it = seen.emplace(sig, (u32)seen.size()).first;
+            cls_of[c] = it->second;
+        }
+        return (u32)seen.size();
+    };
+    auto fits = [&](const std::vector<size_t> &members, u32 &row_shift, size_t &bytes) {
+        std::vector<u32> cls;
+        const u32 J = joint(members, cls);
+        row_shift = 1;
+        while ((1u << (row_shift - 1)) < J) row_shift++;
+        bytes = 0;
+        for (size_t q : members) bytes += round_up((size_t)im->subs[q]->view.mcc.states << row_shift, 16);
+        return MCC_RM_BYTES + bytes + 16 <= MCC_SMEM_MAX;
+    };
+    std::vector<size_t> cur;
+    auto close = [&]() -> hs_error_t {
+        if (cur.size() >= 2) {
+            u32 row_shift = 1;
+            size_t bytes = 0;
+            fits(cur, row_shift, bytes);
+            std::vector<u32> cls;
+            joint(cur, cls);
+            std::vector<u8> rep_of;  // a representative byte of every joint class
+            {
+                u32 J = 0;
+                for (u32 c = 0; c < 256; c++) J = std::max(J, cls[c] + 1);
+                rep_of.assign(J, 0);
+                for (u32 c = 256; c-- > 0;) rep_of[cls[c]] = (u8)c;
+            }
+            std::vector<u8> blob(1024 + bytes, 0);
+            for (u32 c = 0; c < 256; c++) wr32(blob.data(), 4 * c, cls[c] * 2);
+            DbImage::DfaPackImage pk;
+            pk.dev = DevDfaPack{};
+            size_t at = 0;
+            for (size_t k = 0; k < cur.size(); k++) {
+                const DbImage *e = im->subs[cur[k]];
+                const DbView::Mcc &M = e->view.mcc;
+                pk.dev.tab_off[k] = (u32)at;
+                pk.dev.start[k] = M.start;
+                pk.dev.m[k] = e->mcc;
+                for (u32 st = 0; st < M.states; st++)
+                    for (u32 j = 0; j < rep_of.size(); j++) {
+                        const u32 sym = rd8(im->view.bc, M.m_off + mcclellan::remap + rep_of[j]);
+                        u32 out;
+                        if (M.wide16) {
+                            const u32 en = rd16(im->view.bc, M.tab_off + 2 * (((size_t)st << M.as) + sym));
+                            out = (en & mcclellan::STATE_MASK) | ((en & mcclellan::ACCEPT_FLAG) ? 0x8000u : 0u);
+                        } else {
+                            const u32 nx = rd8(im->view.bc, M.tab_off + ((size_t)st << M.as) + sym);
+                            out = nx | (nx >= M.accept_limit_8 ? 0x8000u : 0u);
+                        }
+                        wr16(blob.data(), 1024 + at + ((size_t)st << row_shift) + 2 * j, (u16)out);
+                    }
+                at += round_up((size_t)M.states << row_shift, 16);
+                im->packed[cur[k]] = 1;
+            }
+            pk.dev.n = (u32)cur.size();
+            pk.dev.row_shift = row_shift;
+            pk.dev.tab_bytes = (u32)bytes;
+            pk.D = cur.size() <= 2 ? 2 : cur.size() <= 4 ? 4 : 8;
+            if (cudaMalloc((void **)&pk.d_blob, blob.size()) != cudaSuccess) return HS_NOMEM;
+            cudaMemcpyAsync(pk.d_blob, blob.data(), blob.size(), cudaMemcpyHostToDevice, s->stream);
+            cudaStreamSynchronize(s->stream);  // `blob` is a local
+            pk.dev.blob = pk.d_blob;
+            im->device_bytes += blob.size();
+            im->packs.push_back(pk);
+        }
+        cur.clear();
+        return HS_SUCCESS;
+    };
+    for (size_t q = 0; q < nq; q++) {
+        if (!packable(q)) continue;
+        cur.push_back(q);
+        u32 rs_ = 0;
+        size_t b_ = 0;
+        if (cur.size() > (size_t)DP_MAX || !fits(cur, rs_, b_)) {
+            cur.pop_back();
+            const hs_error_t rv = close();
+            if (rv != HS_SUCCESS) return rv;
+            cur.push_back(q);
+            if (!fits(cur, rs_, b_)) cur.clear();   // does not even fit alone: k_mcclellan reads its table through L2
+        }
+    }
+    return close();
 }
 
 hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage **out) {
@@ -1351,6 +1466,10 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         im->device_bytes += sub->device_bytes;
     }
     if (!im->subs.empty()) im->ordered_ok = false;  // engine matches merge with the literal ones in the sorting finalize
+    if (im->subs.size() >= 2) {
+        const hs_error_t prv = build_dfa_packs(s, im);
+        if (prv != HS_SUCCESS) { im->release(); delete im; return prv; }
+    }
     d.tK = 0;
     if (v.kind != ENG_LIMEX && v.kind != ENG_MCCLELLAN && v.kind != ENG_SHENG && v.kind != ENG_MULTI && turbo::build(v, im->turbo_tabs)) {
         const turbo::Tables &tt = im->turbo_tabs;
@@ -1562,10 +1681,35 @@ hs_error_t launch_mcclellan_pack(hs_gpu_scratch *s, const DbImage *im, const Dev
 // to ONE event queue, and one report pass runs the Rose report programs; the finalize sorts by (buffer, offset, id) and
 // applies the dedupe keys, which is what the catch-up queue's offset order is for.  McClellan engines whose tables fit
 // shared memory together share a launch (k_mcclellan_pack: work item = (buffer, engine)); option "pack" = 0 turns that off.
+template <int D>
+hs_error_t launch_dfa_pack(hs_gpu_scratch *s, const DbImage *im, const DevDfaPack &pk, const DevCorpus &cp) {
+    const size_t dyn = dfapack_smem_bytes(pk);
+    CU_OK(ensure_smem_optin(s, (const void *)k_dfa_pack<D>, dyn));
+    u32 grid = s->opt_grid > 0 ? (u32)s->opt_grid : (u32)s->sm_count;
+    const u32 need = (cp.count + 31) / 32;
+    if (grid > need) grid = need ? need : 1;
+    CU_OK(s->recs2.reserve(s->lx_event_hint));
+    const DevLxEvents evq{reinterpret_cast<LxEvent *>(s->recs2.p), s->d_ctl + 7, s->recs2.cap};
+    k_dfa_pack<D><<<grid, DP_THREADS, dyn, s->stream>>>(im->dev, pk, cp, evq, s->d_ctl + 6);
+    CU_OK(cudaGetLastError());
+    s->stats.kernel_launches++;
+    return HS_SUCCESS;
+}
+
 hs_error_t launch_outfixes(hs_gpu_scratch *s, const DbImage *im, const DevCorpus &cp, const DevArena &ar) {
     bool first = true;
+    const bool fused = s->opt_pack >= 2;
+    if (fused)
+        for (const DbImage::DfaPackImage &pk : im->packs) {
+            if (!first) CU_OK(cudaMemsetAsync(s->d_ctl + 6, 0, sizeof(unsigned long long), s->stream));  // the work counter
+            first = false;
+            const hs_error_t rv = pk.D == 2 ? launch_dfa_pack<2>(s, im, pk.dev, cp) : pk.D == 4 ? launch_dfa_pack<4>(s, im, pk.dev, cp)
+                                                                                                : launch_dfa_pack<8>(s, im, pk.dev, cp);
+            if (rv != HS_SUCCESS) return rv;
+        }
     for (size_t qi = 0; qi < im->subs.size();) {
         const DbImage *sub = im->subs[qi];
+        if (fused && qi < im->packed.size() && im->packed[qi]) { qi++; continue; }
         if (!first) CU_OK(cudaMemsetAsync(s->d_ctl + 6, 0, sizeof(unsigned long long), s->stream));  // the work counter
         first = false;
         auto packable = [](const DbImage *e) {
@@ -1576,7 +1720,7 @@ hs_error_t launch_outfixes(hs_gpu_scratch *s, const DbImage *im, const DevCorpus
             size_t tables = 0;
             size_t k = qi;
             while (k < im->subs.size() && pk.n < (u32)MCC_PACK_MAX && packable(im->subs[k]) &&
-                   im->subs[k]->mcc.wide16 == sub->mcc.wide16) {
+                   im->subs[k]->mcc.wide16 == sub->mcc.wide16 && !(fused && im->packed[k])) {
                 const size_t tb = round_up((size_t)im->subs[k]->mcc.tab_bytes + 8, 16);
                 if ((size_t)(pk.n + 1) * MCC_RM_BYTES + tables + tb > MCC_SMEM_MAX) break;
                 pk.m[pk.n] = im->subs[k]->mcc;
