@@ -303,6 +303,8 @@ def main():
     sc = gpu.alloc_scratch(db)
     if args.frontend:
         sc.set_option("frontend", args.frontend)
+    if os.environ.get("HS_GPU_ORDER"):
+        sc.set_option("order", int(os.environ["HS_GPU_ORDER"]))  # engine kernels: buffers handed out by descending length (1) or as they come (0)
     if os.environ.get("HS_GPU_PACK"):
         sc.set_option("pack", int(os.environ["HS_GPU_PACK"]))   # multi-engine databases: 0 / 1 / 2 (csrc/hs_gpu.cu launch_outfixes)
     if args.pipeline >= 0:

@@ -84,12 +84,13 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_dfa_pack(const DevDb db_, con
                     nb = base + (unsigned long long)gridDim.x * blockDim.x + (u32)__popc(act & ((1u << ln) - 1u));
                 }
                 if (nb >= count) break;
-                o0 = cp_.off[nb];
-                l = (u32)(cp_.off[nb + 1] - o0);
+                const u32 b = cp_.order ? cp_.order[nb] : (u32)nb;
+                o0 = cp_.off[b];
+                l = (u32)(cp_.off[b + 1] - o0);
                 if (l && passes_gates(db_, l)) break;
             }
             if (nb >= count) break;
-            buf = (u32)nb;
+            buf = cp_.order ? cp_.order[nb] : (u32)nb;
             len = l;
             const uintptr_t ap = reinterpret_cast<uintptr_t>(cp_.text + o0);
             chunk = reinterpret_cast<const uint4 *>(ap & ~(uintptr_t)15);
@@ -114,38 +115,23 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_dfa_pack(const DevDb db_, con
             u32 s0[D], seen[D];
 #pragma unroll
             for (int d = 0; d < D; d++) { s0[d] = s[d]; seen[d] = 0; }
-            if (j0 == 0 && j1 == 16) {
-                // ---- a whole chunk inside the buffer: 16 x (classify once, D independent table reads) ----
+            // ---- 16 branch-free steps: classify once, D independent table reads; bytes outside the buffer freeze the
+            // states (one path for every chunk: lanes of a warp sit at different places of different buffers, and a
+            // separate path for boundary chunks would make the warp run both almost every time) ----
+            const u32 valid = ((1u << j1) - 1u) & ~((1u << j0) - 1u);
 #pragma unroll
-                for (int j = 0; j < 16; j++) {
-                    const u32 w = wv[j >> 2], k = 8 * (j & 3);
-                    const u32 ra = ((k >= 7 ? w >> (k - 7) : w << (7 - k)) & 0x7f80u) | lane4;
-                    const u32 co = *reinterpret_cast<const u32 *>(smem + ra);   // class offset inside a row
+            for (int j = 0; j < 16; j++) {
+                const u32 w = wv[j >> 2], k = 8 * (j & 3);
+                const u32 ra = ((k >= 7 ? w >> (k - 7) : w << (7 - k)) & 0x7f80u) | lane4;
+                const u32 co = *reinterpret_cast<const u32 *>(smem + ra);   // class offset inside a row
+                const bool in = (valid >> j) & 1u;
 #pragma unroll
-                    for (int d = 0; d < D; d++) {
-                        const u32 addr = ((s[d] & mcclellan::STATE_MASK) << rs) + (tb[d] + co);
-                        unsigned short t;
-                        asm volatile("ld.shared.u16 %0, [%1];" : "=h"(t) : "r"(addr));
-                        s[d] = t;
-                        seen[d] |= t;
-                    }
-                }
-            } else {
-                const u32 valid = ((1u << j1) - 1u) & ~((1u << j0) - 1u);
-#pragma unroll
-                for (int j = 0; j < 16; j++) {
-                    const u32 w = wv[j >> 2], k = 8 * (j & 3);
-                    const u32 ra = ((k >= 7 ? w >> (k - 7) : w << (7 - k)) & 0x7f80u) | lane4;
-                    const u32 co = *reinterpret_cast<const u32 *>(smem + ra);
-                    const bool in = (valid >> j) & 1u;
-#pragma unroll
-                    for (int d = 0; d < D; d++) {
-                        const u32 addr = ((s[d] & mcclellan::STATE_MASK) << rs) + (tb[d] + co);
-                        unsigned short t;
-                        asm volatile("ld.shared.u16 %0, [%1];" : "=h"(t) : "r"(addr));
-                        s[d] = in ? (u32)t : s[d];   // bytes outside the buffer freeze the state (its flag bit included)
-                        if (in) seen[d] |= t;
-                    }
+                for (int d = 0; d < D; d++) {
+                    const u32 addr = ((s[d] & mcclellan::STATE_MASK) << rs) + (tb[d] + co);
+                    unsigned short t;
+                    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(t) : "r"(addr));
+                    s[d] = in ? (u32)t : s[d];
+                    seen[d] |= s[d];
                 }
             }
             // ---- an engine that passed an accept: its chunk again, byte by byte, raising the events ----
@@ -164,7 +150,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_dfa_pack(const DevDb db_, con
             i += 16;
             u32 alive = 0;
 #pragma unroll
-            for (int d = 0; d < D; d++) alive |= s[d] & mcclellan::STATE_MASK;
+            for (int d = 0; d < D; d++) { s[d] &= mcclellan::STATE_MASK; alive |= s[d]; }   // no flag survives the chunk
             if (i >= (long long)len || !alive) have = false;   // end of the buffer, or every engine dead (mcclellan.c:240-243)
         }
     }

@@ -104,6 +104,8 @@ struct DevCorpus {
     u64 total;
     u32 count;
     u32 nstrips;
+    const u32 *order;        // engine kernels: work item k scans buffer order[k] (buffers by descending length, so that
+                             // the lanes of a warp finish together); null = identity
 };
 
 struct DevArena {
@@ -973,6 +975,41 @@ __global__ void k_ekey_filter(const Rec *recs, u64 n, const unsigned long long *
     keep[i] = k ? 1 : 0;
 }
 
+// ---- buffers by descending length (16-byte classes), for the engine kernels: one thread steps one buffer, so a warp
+// runs as long as its longest buffer; handing out buffers of similar length to neighbouring lanes removes the idle lanes
+// (C3's 200-1400-byte payloads: ~1.75x fewer warp-steps).  Counting sort on the device: histogram, scan, scatter.
+constexpr u32 ORDER_BUCKETS = 4096;
+__global__ void k_order_hist(const u64 *off, u32 count, u32 *hist) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const u64 len = off[i + 1] - off[i];
+    const u32 b = len >> 4 >= ORDER_BUCKETS ? ORDER_BUCKETS - 1 : (u32)(len >> 4);
+    atomicAdd(&hist[ORDER_BUCKETS - 1 - b], 1u);   // bucket 0 = the longest buffers
+}
+__global__ void k_order_scan(u32 *hist) {  // one block of 1024: exclusive prefix sum over the 4096 buckets
+    __shared__ u32 part[1024];
+    const u32 t = threadIdx.x;
+    u32 v[4], sum = 0;
+    for (int k = 0; k < 4; k++) { v[k] = hist[4 * t + k]; sum += v[k]; }
+    part[t] = sum;
+    __syncthreads();
+    for (u32 d = 1; d < 1024; d <<= 1) {
+        const u32 x = t >= d ? part[t - d] : 0;
+        __syncthreads();
+        part[t] += x;
+        __syncthreads();
+    }
+    u32 base = part[t] - sum;
+    for (int k = 0; k < 4; k++) { hist[4 * t + k] = base; base += v[k]; }
+}
+__global__ void k_order_scatter(const u64 *off, u32 count, u32 *cursor, u32 *order) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const u64 len = off[i + 1] - off[i];
+    const u32 b = len >> 4 >= ORDER_BUCKETS ? ORDER_BUCKETS - 1 : (u32)(len >> 4);
+    order[atomicAdd(&cursor[ORDER_BUCKETS - 1 - b], 1u)] = i;
+}
+
 __global__ void k_histogram(const hs_gpu_match_t *m, u64 n, unsigned long long *hist, u32 n_ids) {
     const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n && m[i].id < n_ids) atomicAdd(&hist[m[i].id], 1ull);
@@ -1098,7 +1135,7 @@ struct hs_gpu_corpus {
     u64 total = 0;
     u32 count = 0, nstrips = 0;
     DevCorpus dev() const {
-        return DevCorpus{text.p + FRONT_PAD, off.p, cell_first.p, total, count, nstrips};
+        return DevCorpus{text.p + FRONT_PAD, off.p, cell_first.p, total, count, nstrips, nullptr};
     }
 };
 
@@ -1117,6 +1154,8 @@ struct hs_gpu_scratch {
     DevBuf<Rec> recs, recs2;
     DevBuf<hs_gpu_match_t> d_matches;
     DevBuf<u8> cub_tmp, keep;
+    DevBuf<u32> order, order_hist;          // engine kernels: buffers by descending length (k_order_*)
+    long opt_order = 1;
     DevBuf<unsigned long long> ekey_keys;   // single-match resolution: open-addressing table (pair -> first record index)
     DevBuf<u32> ekey_first;
     DevBuf<u32> seg_count;
@@ -1466,6 +1505,7 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         im->device_bytes += sub->device_bytes;
     }
     if (!im->subs.empty()) im->ordered_ok = false;  // engine matches merge with the literal ones in the sorting finalize
+    im->packed.assign(im->subs.size(), 0);
     if (im->subs.size() >= 2) {
         const hs_error_t prv = build_dfa_packs(s, im);
         if (prv != HS_SUCCESS) { im->release(); delete im; return prv; }
@@ -1885,8 +1925,20 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
         st.scan_ms = st.sort_ms = st.kernel_ms = 0;
         return HS_SUCCESS;
     }
-    const DevCorpus cp = corpus.dev();
+    DevCorpus cp = corpus.dev();
     CU_OK(cudaEventRecord(s->ev[1], s->stream));  // what was queued before this point is the staging (h2d_ms = ev0 -> ev1)
+    const bool has_engines = im->view.kind == ENG_LIMEX || im->view.kind == ENG_MCCLELLAN || im->view.kind == ENG_SHENG || !im->subs.empty();
+    if (has_engines && s->opt_order && cp.count > 32) {
+        CU_OK(s->order.reserve(cp.count));
+        CU_OK(s->order_hist.reserve(ORDER_BUCKETS));
+        CU_OK(cudaMemsetAsync(s->order_hist.p, 0, ORDER_BUCKETS * sizeof(u32), s->stream));
+        const unsigned g = (cp.count + 255) / 256;
+        k_order_hist<<<g, 256, 0, s->stream>>>(cp.off, cp.count, s->order_hist.p);
+        k_order_scan<<<1, 1024, 0, s->stream>>>(s->order_hist.p);
+        k_order_scatter<<<g, 256, 0, s->stream>>>(cp.off, cp.count, s->order_hist.p, s->order.p);
+        CU_OK(cudaGetLastError());
+        cp.order = s->order.p;
+    }
     // ---- ordered fast path: turbo front end, every program pre-decoded, no dedupe / exhaustion keys ----
     if (ordered_eligible(s, im)) {
         hs_error_t orv = scan_device_ordered(s, im, cp);
@@ -2307,7 +2359,7 @@ hs_error_t stage_host_chunks(hs_gpu_scratch *s, const char *const *data, const u
         CU_OK(cudaEventRecord(s->chunk_ready[k], s->copy_stream));
         if (c.bytes)
             mem.push_back(TrainMember{DevCorpus{cp.text.p + c.text_at, cp.off.p + c.off_at, cp.cell_first.p + c.cell_at, c.bytes,
-                                                cnt, c.nstrips},
+                                                cnt, c.nstrips, nullptr},
                                       c.first, s->chunk_ready[k]});
     }
     CU_OK(cudaEventRecord(s->ev[6], s->copy_stream));  // end of the H2D work (h2d_ms = ev0 -> ev6)
@@ -2772,6 +2824,7 @@ hs_error_t hs_gpu_set_option(hs_gpu_scratch_t *scratch, const char *name, long v
     if (!strcmp(name, "pipeline")) { scratch->opt_pipeline = value; return HS_SUCCESS; }
     if (!strcmp(name, "ordered")) { scratch->opt_ordered = value; return HS_SUCCESS; }
     if (!strcmp(name, "pack")) { scratch->opt_pack = value; return HS_SUCCESS; }
+    if (!strcmp(name, "order")) { scratch->opt_order = value; return HS_SUCCESS; }
     if (!strcmp(name, "count_ops")) {
         if (!value) { scratch->op_counts.release(); return HS_SUCCESS; }
         if (ensure_device(scratch) != HS_SUCCESS || scratch->op_counts.reserve(128) != cudaSuccess) return HS_NOMEM;

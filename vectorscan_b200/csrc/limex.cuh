@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(LX_THREADS, 4) k_limex(const DevDb db_, const 
                 if (w == 0) nb = atomicAdd(next_buf, 1ull);
                 if (G > 1) nb = __shfl_sync(gmask, nb, gbase);
                 if (nb >= count) { done = true; csucc = 0; break; }  // idle from here on: nothing may switch on
-                buf = (u32)nb;
+                buf = cp_.order ? cp_.order[nb] : (u32)nb;   // longest buffers first: the tail of the launch is short buffers
                 const u64 o0 = cp_.off[buf], o1 = cp_.off[buf + 1];
                 const u32 l = (u32)(o1 - o0);
                 if (!l || !passes_gates(db_, l)) continue;

@@ -140,12 +140,13 @@ __global__ void __launch_bounds__(MCC_THREADS, 1) k_mcclellan(const DevDb db_, c
                     nb = base + (unsigned long long)gridDim.x * blockDim.x + (u32)__popc(act & ((1u << ln) - 1u));
                 }
                 if (nb >= count) break;
-                o0 = cp_.off[nb];
-                l = (u32)(cp_.off[nb + 1] - o0);
+                const u32 b = cp_.order ? cp_.order[nb] : (u32)nb;
+                o0 = cp_.off[b];
+                l = (u32)(cp_.off[b + 1] - o0);
                 if (l && passes_gates(db_, l)) break;
             }
             if (nb >= count) break;
-            buf = (u32)nb;
+            buf = cp_.order ? cp_.order[nb] : (u32)nb;
             len = l;
             const uintptr_t ap = reinterpret_cast<uintptr_t>(cp_.text + o0);
             chunk = reinterpret_cast<const uint4 *>(ap & ~(uintptr_t)15);
@@ -280,13 +281,13 @@ __global__ void __launch_bounds__(MCC_THREADS, 1) k_mcclellan_pack(const DevDb d
                     nb = base + (unsigned long long)gridDim.x * blockDim.x + (u32)__popc(act & ((1u << ln) - 1u));
                 }
                 if (nb >= items) break;
-                const u32 b = (u32)(nb / npk);
+                const u32 b = cp_.order ? cp_.order[(u32)(nb / npk)] : (u32)(nb / npk);
                 o0 = cp_.off[b];
                 l = (u32)(cp_.off[b + 1] - o0);
                 if (l && passes_gates(db_, l)) break;
             }
             if (nb >= items) break;
-            buf = (u32)(nb / npk);
+            buf = cp_.order ? cp_.order[(u32)(nb / npk)] : (u32)(nb / npk);
             eng = (u32)(nb % npk);
             {
                 const DevMcc &me = pk.m[eng];
