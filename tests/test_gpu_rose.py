@@ -60,9 +60,9 @@ def test_scan_one_buffer_callback_order(ref):
 
 
 def test_packed_and_single_engine_launches_agree(ref):
-    """Multi-engine databases, option "pack": 2 (default) = k_dfa_pack, several DFAs stepped together per buffer on a
-    joint alphabet; 1 = k_mcclellan_pack, work item = (buffer, engine); 0 = one launch per engine.  Same matches every
-    way, and as the reference runtime's."""
+    """Multi-engine databases, option "pack": 1 (default) = k_mcclellan_pack, work item = (buffer, engine); 2 = k_dfa_pack,
+    several DFAs stepped together per buffer on a joint alphabet; 0 = one launch per engine.  Option "order": buffers
+    handed out by descending length (default) or as they come.  Same matches every way, and as the reference runtime's."""
     ex, fl, ids = W.c3_patterns(max_patterns=400, state_budget=1 << 30)
     for dfa_states in (64, 256, 1024):      # McClellan8 packs of 8, mixed, McClellan16 pairs
         db = litdb.compile_regex_rose(ex, fl, ids, dfa_states=dfa_states)
@@ -73,6 +73,7 @@ def test_packed_and_single_engine_launches_agree(ref):
         for pack in (2, 1, 0):
             sc = gpu.alloc_scratch(db)
             sc.set_option("pack", pack)
+            sc.set_option("order", pack != 0)
             out[pack] = gpu_batch(db, bufs, sc)
             launches[pack] = sc.stats()["kernel_launches"]
             sc.close()
@@ -89,6 +90,9 @@ def test_fused_packs_on_random_sets(ref, seed):
     ex, fl, ids, smp = regen.random_set(rng, rng.randint(6, 14), True)
     db = litdb.compile_regex_rose(ex, fl, ids, dfa_states=rng.choice([12, 24, 60]))
     bufs = [regen.random_text(rng, ex, rng.choice([0, 1, 15, 16, 17, 33, 200, 1400]), smp) for _ in range(80)]
-    got = gpu_batch(db, bufs)
+    sc = gpu.alloc_scratch(db)
+    sc.set_option("pack", 2)
+    got = gpu_batch(db, bufs, sc)
+    sc.close()
     assert got == ref_batch(ref, db, bufs)
     assert got == brute_batch(ex, fl, ids, bufs)

@@ -19,6 +19,11 @@
 // accept in the chunk (rare) is stepped again from its saved state by the exact byte loop, which raises the events
 // {buffer, to, report list} for k_limex_report -- the scheme of k_mcclellan.  Engines with Sherman states, wide states,
 // EOD accepts or tables too large for shared memory are not packed (they keep k_mcclellan).
+//
+// MEASURED (C3, 2 000 regexes as 114 engines, 256 MiB, B200): 18.9 ms against 18.5 ms for k_mcclellan_pack -- no gain: the
+// joint alphabet doubles the row size of most 16-bit engines, so only the small engines pack at all, and with buffers
+// handed out by length the single-chain kernel already keeps its lanes busy.  Option "pack" = 2 selects this kernel; the
+// default is 1 (k_mcclellan_pack).  ncu (gpurun_out r2q): 5.2 shared-memory wavefronts per warp-step, issue 23 % at D = 4.
 #pragma once
 
 constexpr int DP_THREADS = 1024;

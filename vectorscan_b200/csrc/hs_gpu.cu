@@ -1132,6 +1132,10 @@ struct hs_gpu_corpus {
     DevBuf<u8> text;          // FRONT_PAD + total + BACK_PAD
     DevBuf<u64> off;
     DevBuf<u32> cell_first;
+    // buffers by descending length for the engine kernels (k_order_*): built by the first scan that wants it, kept while
+    // the corpus keeps its contents (the staging corpus of host batches is refilled, and reordered, every call)
+    mutable DevBuf<u32> order;
+    mutable bool order_ready = false;
     u64 total = 0;
     u32 count = 0, nstrips = 0;
     DevCorpus dev() const {
@@ -1154,7 +1158,7 @@ struct hs_gpu_scratch {
     DevBuf<Rec> recs, recs2;
     DevBuf<hs_gpu_match_t> d_matches;
     DevBuf<u8> cub_tmp, keep;
-    DevBuf<u32> order, order_hist;          // engine kernels: buffers by descending length (k_order_*)
+    DevBuf<u32> order_hist;                 // engine kernels: buffers by descending length (k_order_*, histogram)
     long opt_order = 1;
     DevBuf<unsigned long long> ekey_keys;   // single-match resolution: open-addressing table (pair -> first record index)
     DevBuf<u32> ekey_first;
@@ -1187,8 +1191,9 @@ struct hs_gpu_scratch {
                              // tables (k_scan), 2: k_turbo, 3: k_turbo2
     long opt_grid = 0;
     long opt_warps = 0;      // k_turbo2: cap on warps per CTA (0 = as many as fit)
-    long opt_pack = 2;       // multi-engine databases: 0 one launch per engine, 1 k_mcclellan_pack (work item = (buffer,
-                             // engine)), 2 k_dfa_pack (D engines stepped together per buffer, tables on a joint alphabet)
+    long opt_pack = 1;       // multi-engine databases: 0 one launch per engine, 1 k_mcclellan_pack (work item = (buffer,
+                             // engine); default), 2 k_dfa_pack (D engines stepped together per buffer on a joint alphabet;
+                             // measured on C3: 18.9 ms against 18.5 ms for mode 1 -- kept as an option, not the default)
     long opt_pipeline = 0;   // host batches: 0 one copy then one scan (measured fastest), 1 chunk gathered input, 2 always chunk
     size_t smem_optin_max = 227 * 1024;
     u64 arena_hint = 1 << 16;
@@ -1929,15 +1934,18 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
     CU_OK(cudaEventRecord(s->ev[1], s->stream));  // what was queued before this point is the staging (h2d_ms = ev0 -> ev1)
     const bool has_engines = im->view.kind == ENG_LIMEX || im->view.kind == ENG_MCCLELLAN || im->view.kind == ENG_SHENG || !im->subs.empty();
     if (has_engines && s->opt_order && cp.count > 32) {
-        CU_OK(s->order.reserve(cp.count));
-        CU_OK(s->order_hist.reserve(ORDER_BUCKETS));
-        CU_OK(cudaMemsetAsync(s->order_hist.p, 0, ORDER_BUCKETS * sizeof(u32), s->stream));
-        const unsigned g = (cp.count + 255) / 256;
-        k_order_hist<<<g, 256, 0, s->stream>>>(cp.off, cp.count, s->order_hist.p);
-        k_order_scan<<<1, 1024, 0, s->stream>>>(s->order_hist.p);
-        k_order_scatter<<<g, 256, 0, s->stream>>>(cp.off, cp.count, s->order_hist.p, s->order.p);
-        CU_OK(cudaGetLastError());
-        cp.order = s->order.p;
+        if (!corpus.order_ready) {
+            CU_OK(corpus.order.reserve(cp.count));
+            CU_OK(s->order_hist.reserve(ORDER_BUCKETS));
+            CU_OK(cudaMemsetAsync(s->order_hist.p, 0, ORDER_BUCKETS * sizeof(u32), s->stream));
+            const unsigned g = (cp.count + 255) / 256;
+            k_order_hist<<<g, 256, 0, s->stream>>>(cp.off, cp.count, s->order_hist.p);
+            k_order_scan<<<1, 1024, 0, s->stream>>>(s->order_hist.p);
+            k_order_scatter<<<g, 256, 0, s->stream>>>(cp.off, cp.count, s->order_hist.p, corpus.order.p);
+            CU_OK(cudaGetLastError());
+            corpus.order_ready = true;
+        }
+        cp.order = corpus.order.p;
     }
     // ---- ordered fast path: turbo front end, every program pre-decoded, no dedupe / exhaustion keys ----
     if (ordered_eligible(s, im)) {
@@ -2161,6 +2169,7 @@ hs_error_t stage_host_buffers(hs_gpu_scratch *s, const char *const *data, const 
     for (unsigned i = 0; i < count; i++) total += length[i];
     cp.total = total;
     cp.count = count;
+    cp.order_ready = false;
     CU_OK(cp.text.reserve(FRONT_PAD + total + BACK_PAD));
     CU_OK(cp.off.reserve((size_t)count + 1));
     CU_OK(cudaEventRecord(s->ev[0], s->stream));
@@ -2278,6 +2287,7 @@ hs_error_t stage_host_chunks(hs_gpu_scratch *s, const char *const *data, const u
     }
     cp.total = total;
     cp.count = count;
+    cp.order_ready = false;
     // the copy stream must not overtake the previous call's scan of this staging area
     CU_OK(cudaEventRecord(s->ev[1], s->stream));
     CU_OK(cudaStreamWaitEvent(s->copy_stream, s->ev[1], 0));
@@ -2700,6 +2710,7 @@ hs_error_t hs_gpu_corpus_free(hs_gpu_corpus_t *c) {
     c->text.release();
     c->off.release();
     c->cell_first.release();
+    c->order.release();
     c->magic = 0;
     delete c;
     return HS_SUCCESS;
