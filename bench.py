@@ -449,7 +449,10 @@ def main():
     # ---- N GPUs scanning a sharded corpus reproduce the 1-GPU match list and histogram -----------------
     verify = None
     if not args.no_verify:
-        vflat, voff = make_workload(args.config, 0, min(nbytes, 64 << 20), args.patterns)[2][0] if rank else batches[0]
+        # every rank shards the SAME corpus: rank 0's first batch when it is at most 64 MiB, else a 64 MiB one built from
+        # rank 0's seed on every rank (r2u: ranks > 0 used to rebuild a capped corpus while rank 0 kept its 256 MiB one)
+        vbytes = min(nbytes, 64 << 20)
+        vflat, voff = batches[0] if (rank == 0 and vbytes == nbytes) else make_workload(args.config, 0, vbytes, args.patterns)[2][0]
         if len(voff) - 1 >= world:
             bounds = shard.shard_bounds(voff, world)
             sflat, soff, first = shard.take_shard(vflat, voff, bounds, rank)

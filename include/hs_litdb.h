@@ -126,6 +126,8 @@ int hsb_compile_regex_multi(const char *const *expressions, const unsigned *flag
 #define HSB_REGEX_ENGINE_MCCLELLAN 1u
 #define HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN 2u
 #define HSB_REGEX_ENGINE_SHENG 3u /* DFA of <= 16 states as byte-shuffle masks (src/nfa/sheng_internal.h) */
+#define HSB_REGEX_ENGINE_SHENG_WIDE 4u /* Sheng32 (<= 32 states) / Sheng64 (<= 64): the AVX512VBMI forms, 64-byte masks;
+                                          only an AVX512VBMI build of the reference runtime executes them */
 int hsb_compile_regex_multi_ex(const char *const *expressions, const unsigned *flags, const unsigned *ids,
                                unsigned elements, unsigned mode, unsigned engine, hs_database_t **db,
                                char **error);

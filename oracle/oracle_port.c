@@ -498,11 +498,19 @@ static int mcclellan_scan(struct scan_state *s, const u8 *nfa) {
  * (sheng_impl.h:40-97: state = shuffle_masks[c][state]; ACCEPT flag -> fireSingleReport / fireReports, sheng.c:106-157),
  * MQE_END returns MO_DEAD for a dead state when SHENG_FLAG_CAN_DIE (:672-677), which skips the EOD check of
  * runtime.c:273; otherwise nfaExecSheng_testEOD (:796-812).  Layout: sheng_internal.h:56-79. */
-enum { SH_MASKS = 0, SH_AUX_OFFSET = 4100, SH_ANCHORED = 4113, SH_FLAGS = 4115, SH_REPORT = 4116 };
+/* struct sheng / sheng32 / sheng64 (nfa/sheng_internal.h:68-107): masks of `stride` bytes per byte value, then the trailer */
+struct sh_shape { u32 stride, accept, dead, mask, trailer; };
+static struct sh_shape sh_shape_of(u8 nfa_type) {
+    if (nfa_type == 21) return (struct sh_shape){64, 0x20, 0x40, 0x1f, 16384};
+    if (nfa_type == 22) return (struct sh_shape){64, 0x40, 0x80, 0x3f, 16384};
+    return (struct sh_shape){16, 0x10, 0x20, 0x0f, 4096};
+}
+/* trailer: u32 length, aux_offset, report_offset, accel_offset; u8 n_states, anchored, floating, flags; ReportID report */
 
-static int sh_report(struct scan_state *s, const u8 *nfa, const u8 *sh, u8 st, u64 loc, int eod) {
-    if (!eod && (sh[SH_FLAGS] & 1)) return run_program(s, rd32(sh + SH_REPORT), loc);      /* SHENG_FLAG_SINGLE_REPORT */
-    const u8 *aux = nfa + rd32(sh + SH_AUX_OFFSET) + (size_t)(st & 0xf) * 16;             /* struct sstate_aux */
+static int sh_report(struct scan_state *s, const u8 *nfa, const u8 *sh, const struct sh_shape *f, u8 st, u64 loc, int eod) {
+    const u8 *tr = sh + f->trailer;
+    if (!eod && (tr[19] & 1)) return run_program(s, rd32(tr + 20), loc);                    /* SHENG_FLAG_SINGLE_REPORT */
+    const u8 *aux = nfa + rd32(tr + 4) + (size_t)(st & f->mask) * 16;                       /* struct sstate_aux */
     u32 off = rd32(aux + (eod ? 4 : 0));
     if (!off) return 0;
     const u8 *rl = nfa + off;
@@ -514,17 +522,19 @@ static int sh_report(struct scan_state *s, const u8 *nfa, const u8 *sh, u8 st, u
 static int sheng_scan(struct scan_state *s, const u8 *nfa) {
     const u8 *sh = nfa + NFA_SIZE;
     if (nfa[NFA_RACCEL]) { s->error = 1; return -1; }
-    const int can_die = (sh[SH_FLAGS] & 2) != 0;
-    u8 st = sh[SH_ANCHORED];
+    const struct sh_shape f = sh_shape_of(nfa[NFA_TYPE]);
+    const u8 *tr = sh + f.trailer;
+    const int can_die = (tr[19] & 2) != 0;
+    u8 st = tr[17];                                                /* anchored */
     for (u32 i = 0; i < s->len; i++) {
-        if (st & 0x20) break;                                   /* SHENG_STATE_DEAD: every successor is the same state */
-        st = sh[SH_MASKS + 16 * (size_t)s->buf[i] + (st & 0xf)];
-        if ((st & 0x10) && sh_report(s, nfa, sh, st, (u64)i + 1, 0) < 0) return -1;
+        if (st & f.dead) break;                                    /* dead: every successor is the same state */
+        st = sh[(size_t)f.stride * s->buf[i] + (st & f.mask)];
+        if ((st & f.accept) && sh_report(s, nfa, sh, &f, st, (u64)i + 1, 0) < 0) return -1;
     }
-    if (can_die && (st & 0x20)) return 0;                       /* MO_DEAD: no final-state check */
+    if (can_die && (st & f.dead)) return 0;                        /* MO_DEAD: no final-state check */
     if (rd32(nfa + NFA_FLAGS) & NFA_ACCEPTS_EOD) {
-        const u8 *aux = nfa + rd32(sh + SH_AUX_OFFSET) + (size_t)(st & 0xf) * 16;
-        if (rd32(aux + 4) && sh_report(s, nfa, sh, st, s->len, 1) < 0) return -1;
+        const u8 *aux = nfa + rd32(tr + 4) + (size_t)(st & f.mask) * 16;
+        if (rd32(aux + 4) && sh_report(s, nfa, sh, &f, st, s->len, 1) < 0) return -1;
     }
     return 0;
 }
@@ -538,7 +548,7 @@ static int deferred_cmp(const void *a, const void *b) {
 
 static void engine_scan(struct scan_state *s, const u8 *nfa) {
     if (nfa[NFA_TYPE] == 6 || nfa[NFA_TYPE] == 7) mcclellan_scan(s, nfa);
-    else if (nfa[NFA_TYPE] == 17) sheng_scan(s, nfa);
+    else if (nfa[NFA_TYPE] == 17 || nfa[NFA_TYPE] == 21 || nfa[NFA_TYPE] == 22) sheng_scan(s, nfa);
     else limex_scan(s, nfa);
 }
 

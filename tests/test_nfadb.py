@@ -138,3 +138,29 @@ def test_sheng_sets_match_brute_force(ref, seed):
     got = _scan_ref(ref, db, texts)
     for t, g in zip(texts, got):
         assert g == regen.brute_force(ex, fl, ids, t), (ex, fl, t)
+
+
+# ---- Sheng32 / Sheng64 (sheng_internal.h:81-107): the AVX512VBMI forms, 64-byte succ_masks ----------------------------
+@pytest.mark.parametrize("seed", range(30))
+def test_sheng32_and_sheng64_match_brute_force(seed):
+    import oracle_port
+    import refrt
+    if refrt.pick_isa() != "avx512":
+        pytest.skip("host CPU cannot run the AVX512VBMI build of the reference runtime")
+    ref = refrt.RefRuntime("avx512")
+    rng = random.Random(7000 + seed)
+    ex, fl, ids, smp = regen.random_set(rng, rng.randint(1, 5), True)
+    ex = regen.with_eod(rng, ex, 0.3)
+    try:
+        db = litdb.compile_regex_multi(ex, fl, ids, engine=litdb.ENGINE_SHENG_WIDE)
+    except litdb.CompileError as e:
+        assert "too large" in str(e)
+        return
+    assert db.outfix_engine_type() in (21, 22)
+    texts = [regen.random_text(rng, ex, 120, smp) for _ in range(3)] + [b""]
+    rdb = ref.deserialize(db.serialize())
+    rs = ref.alloc_scratch(rdb)
+    for t in texts:
+        rv, got = ref.scan(rdb, rs, t)
+        assert rv == 0 and sorted(set(got), key=lambda x: (x[1], x[0])) == regen.brute_force(ex, fl, ids, t), (ex, fl, t)
+        assert oracle_port.scan(db, t) == (0, got)

@@ -1224,16 +1224,16 @@ cudaError_t ensure_smem_optin(hs_gpu_scratch *s, const void *fn, size_t dyn) {
 // Sheng -> state-major table (see the upload).  Reference semantics kept: state byte = id | flags
 // (shengcompile.cpp:343-357); a DEAD-flagged state is a trap without reports (census), so it may become state 0.
 void build_sheng_tables(const DbView &v, u32 at, std::vector<u8> &out, DevMcc &D) {
-    namespace sh = sheng;
     const DbView::Sheng &S = v.sheng;
+    const sheng::Shape sh = sheng::shape(S.nfa_type);   // Sheng (16 states), Sheng32, Sheng64
     const u8 *m = v.bc + S.sh_off;
     const u32 n = S.n_states;
-    bool dead[16] = {false}, acc[16] = {false};
-    auto note = [&](u8 e) { if (e & sh::STATE_DEAD) dead[e & sh::STATE_MASK] = true; };
+    bool dead[64] = {false}, acc[64] = {false};
+    auto note = [&](u8 e) { if (e & sh.dead) dead[e & sh.mask] = true; };
     note((u8)S.anchored);
-    for (u32 c = 0; c < 256; c++) for (u32 st = 0; st < n; st++) note(m[sh::shuffle_masks + 16 * c + st]);
-    for (u32 st = 0; st < n; st++) acc[st] = rd32(v.bc, S.aux_off + st * sh::aux::SIZE + sh::aux::accept) != 0;
-    u32 new_of[16], old_of[17], next = 1;
+    for (u32 c = 0; c < 256; c++) for (u32 st = 0; st < n; st++) note(m[(size_t)sh.stride * c + st]);
+    for (u32 st = 0; st < n; st++) acc[st] = rd32(v.bc, S.aux_off + st * sheng::aux::SIZE + sheng::aux::accept) != 0;
+    u32 new_of[64], old_of[65], next = 1;
     for (u32 st = 0; st < n; st++) if (dead[st]) new_of[st] = 0;
     for (u32 st = 0; st < n; st++) if (!dead[st] && !acc[st]) { old_of[next] = st; new_of[st] = next++; }
     const u32 accept_limit = next;
@@ -1242,15 +1242,15 @@ void build_sheng_tables(const DbView &v, u32 at, std::vector<u8> &out, DevMcc &D
     out.assign(256 + tab_bytes + rows * mcclellan::aux::SIZE, 0);
     for (u32 c = 0; c < 256; c++) out[c] = (u8)c;  // remap: identity, alphaShift 8
     for (u32 q = 1; q < rows; q++) {
-        for (u32 c = 0; c < 256; c++) out[256 + q * 256 + c] = (u8)new_of[m[sh::shuffle_masks + 16 * c + old_of[q]] & sh::STATE_MASK];
+        for (u32 c = 0; c < 256; c++) out[256 + q * 256 + c] = (u8)new_of[m[(size_t)sh.stride * c + old_of[q]] & sh.mask];
         u8 *a = out.data() + 256 + tab_bytes + q * mcclellan::aux::SIZE;
-        wr32(a, mcclellan::aux::accept, rd32(v.bc, S.aux_off + old_of[q] * sh::aux::SIZE + sh::aux::accept));
-        wr32(a, mcclellan::aux::accept_eod, rd32(v.bc, S.aux_off + old_of[q] * sh::aux::SIZE + sh::aux::accept_eod));
+        wr32(a, mcclellan::aux::accept, rd32(v.bc, S.aux_off + old_of[q] * sheng::aux::SIZE + sheng::aux::accept));
+        wr32(a, mcclellan::aux::accept_eod, rd32(v.bc, S.aux_off + old_of[q] * sheng::aux::SIZE + sheng::aux::accept_eod));
     }
     D = DevMcc{};
     D.remap_abs = at; D.tab_abs = at + 256; D.tab_bytes = tab_bytes; D.aux_abs = at + 256 + tab_bytes;
-    D.nfa_abs = v.nfa_off; D.sherman_abs = 0; D.wide16 = 0; D.as = 8; D.start = new_of[S.anchored & sh::STATE_MASK];
-    D.accept_limit_8 = accept_limit; D.sherman_limit = 0xffffffffu; D.single = (S.flags & sh::FLAG_SINGLE_REPORT) ? 1u : 0u;
+    D.nfa_abs = v.nfa_off; D.sherman_abs = 0; D.wide16 = 0; D.as = 8; D.start = new_of[S.anchored & sh.mask];
+    D.accept_limit_8 = accept_limit; D.sherman_limit = 0xffffffffu; D.single = (S.flags & sheng::FLAG_SINGLE_REPORT) ? 1u : 0u;
     D.arb_report = S.report; D.accepts_eod = (v.nfa_flags & nfa::ACCEPTS_EOD) ? 1u : 0u; D.in_smem = 1; D.has_sherman = 0;
 }
 

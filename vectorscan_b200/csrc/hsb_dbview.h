@@ -52,7 +52,7 @@ struct DbView {
         u32 wide16 = 0, as = 0, states = 0, start = 0, accept_limit_8 = 0, sherman_limit = 0, single = 0, arb_report = 0;
     } mcc;
     // single-outfix Sheng DFA (kind == ENG_SHENG), absolute bytecode offsets
-    struct Sheng { u32 sh_off = 0, aux_off = 0, n_states = 0, anchored = 0, flags = 0, report = 0; } sheng;
+    struct Sheng { u32 sh_off = 0, aux_off = 0, n_states = 0, anchored = 0, flags = 0, report = 0, nfa_type = 17; } sheng;
     // full-Rose database of outfix engines (kind == ENG_MULTI): one view per queue, each of kind LIMEX / MCCLELLAN
     std::vector<DbView> engines;
     u32 nfa_min_width = 0;  // NFA.minWidth of an outfix engine: blocks shorter than this do not start it
@@ -229,28 +229,28 @@ inline int parse_mcclellan(DbView &d, std::string &why) {
 // only.  A state carrying the DEAD flag must be a trap without reports (that is what the flag means; the device path
 // stops there).
 inline int parse_sheng(DbView &d, std::string &why) {
-    namespace sh = sheng;
+    const sheng::Shape sh = sheng::shape(d.limex_type);
     const u8 *r = d.bc;
     const u8 *n = r + d.nfa_off;
-    if (d.nfa_len < nfa::SIZE + sh::SIZE) { why = "Sheng truncated"; return E_INVALID; }
+    if (d.nfa_len < nfa::SIZE + sh.SIZE) { why = "Sheng truncated"; return E_INVALID; }
     DbView::Sheng &S = d.sheng;
     S.sh_off = d.nfa_off + (u32)nfa::SIZE;
     const u8 *m = r + S.sh_off;
     auto n_range = [&](size_t off, size_t len) { return off <= d.nfa_len && len <= d.nfa_len - off; };
-    S.n_states = rd8(m, sh::n_states);
-    S.anchored = rd8(m, sh::anchored);
-    S.flags = rd8(m, sh::flags);
-    S.report = rd32(m, sh::report);
-    if (!S.n_states || S.n_states > 16 || (S.anchored & sh::STATE_MASK) >= S.n_states) { why = "Sheng header inconsistent"; return E_INVALID; }
-    const u32 aux_rel = rd32(m, sh::aux_offset);
-    if (!n_range(aux_rel, (size_t)S.n_states * sh::aux::SIZE)) { why = "Sheng aux array truncated"; return E_INVALID; }
+    S.n_states = rd8(m, sh.n_states);
+    S.anchored = rd8(m, sh.anchored);
+    S.flags = rd8(m, sh.flags);
+    S.report = rd32(m, sh.report);
+    if (!S.n_states || S.n_states > sh.max_states || (S.anchored & sh.mask) >= S.n_states) { why = "Sheng header inconsistent"; return E_INVALID; }
+    const u32 aux_rel = rd32(m, sh.aux_offset);
+    if (!n_range(aux_rel, (size_t)S.n_states * sheng::aux::SIZE)) { why = "Sheng aux array truncated"; return E_INVALID; }
     S.aux_off = d.nfa_off + aux_rel;
     std::set<u32> progs;
-    if (S.flags & sh::FLAG_SINGLE_REPORT) progs.insert(S.report);
-    bool has_reports[16] = {false};
+    if (S.flags & sheng::FLAG_SINGLE_REPORT) progs.insert(S.report);
+    bool has_reports[64] = {false};
     for (u32 st = 0; st < S.n_states; st++)
-        for (size_t f : {sh::aux::accept, sh::aux::accept_eod}) {
-            const u32 rl = rd32(r, S.aux_off + st * sh::aux::SIZE + f);
+        for (size_t f : {sheng::aux::accept, sheng::aux::accept_eod}) {
+            const u32 rl = rd32(r, S.aux_off + st * sheng::aux::SIZE + f);
             if (!rl) continue;
             has_reports[st] = true;
             if ((rl & 3) || !n_range(rl, 4)) { why = "Sheng report list outside the engine"; return E_INVALID; }
@@ -260,18 +260,19 @@ inline int parse_sheng(DbView &d, std::string &why) {
         }
     for (u32 c = 0; c < 256; c++)
         for (u32 st = 0; st < S.n_states; st++) {
-            const u8 e = rd8(m, sh::shuffle_masks + 16 * c + st);
-            const u32 t = e & sh::STATE_MASK;
+            const u8 e = rd8(m, (size_t)sh.stride * c + st);
+            const u32 t = e & sh.mask;
             if (t >= S.n_states) { why = "Sheng successor out of range"; return E_INVALID; }
-            if (((e & sh::STATE_ACCEPT) != 0) != (rd32(r, S.aux_off + t * sh::aux::SIZE + sh::aux::accept) != 0)) {
+            if (((e & sh.accept) != 0) != (rd32(r, S.aux_off + t * sheng::aux::SIZE + sheng::aux::accept) != 0)) {
                 why = "Sheng accept flag disagrees with the state's report list"; return E_INVALID;
             }
-            if (e & sh::STATE_DEAD) {
+            if (e & sh.dead) {
                 if (has_reports[t]) { why = "Sheng dead state with reports"; return E_INVALID; }
                 for (u32 c2 = 0; c2 < 256; c2++)
-                    if ((rd8(m, sh::shuffle_masks + 16 * c2 + t) & sh::STATE_MASK) != t) { why = "Sheng dead state is not a trap"; return E_INVALID; }
+                    if ((rd8(m, (size_t)sh.stride * c2 + t) & sh.mask) != t) { why = "Sheng dead state is not a trap"; return E_INVALID; }
             }
         }
+    S.nfa_type = d.limex_type;
     d.kind = ENG_SHENG;
     d.max_lit_len = 8;
     for (u32 p : progs) {
@@ -373,7 +374,7 @@ inline int parse_outfix_at(DbView &d, u32 info_off, std::string &why) {
     if (!in_range(d, d.nfa_off, d.nfa_len)) { why = "NFA runs past the bytecode"; return E_INVALID; }
     if (rd8(n, nfa::rAccelType)) { why = "reverse acceleration is not supported"; return E_ARCH; }
     if (d.limex_type == nfa::MCCLELLAN_8 || d.limex_type == nfa::MCCLELLAN_16) return parse_mcclellan(d, why);
-    if (d.limex_type == nfa::SHENG) return parse_sheng(d, why);
+    if (d.limex_type == nfa::SHENG || d.limex_type == nfa::SHENG_32 || d.limex_type == nfa::SHENG_64) return parse_sheng(d, why);
     if (d.limex_type > nfa::LIMEX_512) { why = "outfix engine type " + std::to_string(d.limex_type) + " (not LimEx, McClellan or Sheng) is not supported yet"; return E_ARCH; }
     const limex::Layout L = limex::layout(d.limex_type);
     if (d.nfa_len < nfa::SIZE + L.SIZE) { why = "LimEx truncated"; return E_INVALID; }

@@ -228,7 +228,7 @@ constexpr size_t flags = 0, length = 4, type = 8, rAccelType = 9, rAccelOffset =
                  rAccelData = 12, queueIndex = 16, nPositions = 20, scratchStateSize = 24, streamStateSize = 28,
                  maxWidth = 32, minWidth = 36, maxOffset = 40, SIZE = 64;
 constexpr u8 LIMEX_32 = 0, LIMEX_64 = 1, LIMEX_128 = 2, LIMEX_256 = 3, LIMEX_384 = 4, LIMEX_512 = 5;
-constexpr u8 MCCLELLAN_8 = 6, MCCLELLAN_16 = 7, SHENG = 17;
+constexpr u8 MCCLELLAN_8 = 6, MCCLELLAN_16 = 7, SHENG = 17, SHENG_32 = 21, SHENG_64 = 22;
 constexpr u32 ACCEPTS_EOD = 1, ZOMBIE = 2;
 }
 namespace nfainfo {  // struct NfaInfo
@@ -258,6 +258,18 @@ constexpr size_t shuffle_masks = 0, length = 4096, aux_offset = 4100, report_off
 constexpr u32 STATE_ACCEPT = 0x10, STATE_DEAD = 0x20, STATE_ACCEL = 0x40, STATE_MASK = 0xf;
 constexpr u32 FLAG_SINGLE_REPORT = 1, FLAG_CAN_DIE = 2, FLAG_HAS_ACCEL = 4;
 namespace aux { constexpr size_t accept = 0, accept_eod = 4, accel = 8, top = 12, SIZE = 16; }
+// struct sheng32 / sheng64 (src/nfa/sheng_internal.h:81-107, AVX512VBMI targets): 256 succ_masks of 64 bytes, the same
+// trailer, other flag bits.  One descriptor for the three shapes:
+struct Shape {
+    u32 max_states, stride, accept, dead, mask;  // mask entry = state id | flags
+    size_t length, aux_offset, report_offset, accel_offset, n_states, anchored, floating, flags, report, SIZE;
+    u8 nfa_type;
+};
+HSB_HD Shape shape(u32 nfa_type) {
+    if (nfa_type == 21) return Shape{32, 64, 0x20, 0x40, 0x1f, 16384, 16388, 16392, 16396, 16400, 16401, 16402, 16403, 16404, 16448, 21};
+    if (nfa_type == 22) return Shape{64, 64, 0x40, 0x80, 0x3f, 16384, 16388, 16392, 16396, 16400, 16401, 16402, 16403, 16404, 16448, 22};
+    return Shape{16, 16, 0x10, 0x20, 0x0f, 4096, 4100, 4104, 4108, 4112, 4113, 4114, 4115, 4116, 4128, 17};
+}
 }
 namespace nfaaccept {  // struct NFAAccept
 constexpr size_t single_report = 0, reports = 4, squash = 8, SIZE = 12;

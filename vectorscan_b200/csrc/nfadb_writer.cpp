@@ -680,18 +680,20 @@ int emit_mcclellan(const Dfa &d, const u8 *reach_map, const std::vector<u32> &pr
 // Lay a DFA of at most 16 states out as the reference's Sheng engine (struct NFA + struct sheng + sstate_aux[] +
 // report lists), following shengcompile.cpp:337-358 (state byte = id | flags), :420-444 (header), :560-578 (masks)
 // and :640-698 (region order and sizes).  State ids are the DFA's own (dead = 0).
+// `wide`: the AVX512VBMI forms -- Sheng32 (<= 32 states) or Sheng64 (<= 64 states): 64-byte succ_masks, other flag bits
+// (shengcompile.cpp:358-385, :447-505; struct sheng32 / sheng64).
 int emit_sheng(const Dfa &d, const u8 *reach_map, const std::vector<u32> &program_of, u32 min_width, Buf &eng,
-               u32 &state_bytes, std::string &err) {
-    namespace sh = sheng;
+               u32 &state_bytes, std::string &err, bool wide = false) {
     const u32 n = (u32)d.next.size();
-    if (n > 16) { err = "DFA too large for a Sheng engine (" + std::to_string(n) + " states)"; return HSB_LIT_COMPILER_ERROR; }
+    const sheng::Shape sh = sheng::shape(!wide ? 17u : n <= 32 ? 21u : 22u);
+    if (n > sh.max_states) { err = "DFA too large for a Sheng engine (" + std::to_string(n) + " states)"; return HSB_LIT_COMPILER_ERROR; }
     state_bytes = 1;
     bool can_die = false, any_eod = false;
     for (u32 i = 1; i < n; i++) for (u32 k = 0; k < d.n_sym; k++) if (d.next[i][k] == 0) can_die = true;
     auto state_byte = [&](u32 t) -> u8 {
         u8 v = (u8)t;
-        if (!d.reports[t].empty()) v |= sh::STATE_ACCEPT;
-        if (t == 0) v |= sh::STATE_DEAD;
+        if (!d.reports[t].empty()) v |= sh.accept;
+        if (t == 0) v |= sh.dead;
         return v;
     };
     // report lists (normal and EOD share one pool, as gatherReports does)
@@ -714,8 +716,8 @@ int emit_sheng(const Dfa &d, const u8 *reach_map, const std::vector<u32> &progra
         list_eod_of[i] = intern(d.reports_eod[i]);
         if (list_eod_of[i] != ~0u) any_eod = true;
     }
-    const size_t nfa_size = round_up(nfa::SIZE + sh::SIZE, 16);
-    const size_t reports_offset = nfa_size + sh::aux::SIZE * (size_t)n;
+    const size_t nfa_size = round_up(nfa::SIZE + sh.SIZE, 16);
+    const size_t reports_offset = nfa_size + sheng::aux::SIZE * (size_t)n;
     size_t rl_size = 0;
     for (auto &l : lists) rl_size += 4 + 4 * l.size();
     const size_t accel_offset = round_up(reports_offset + rl_size, 16);
@@ -724,7 +726,7 @@ int emit_sheng(const Dfa &d, const u8 *reach_map, const std::vector<u32> &progra
     u8 *nh = eng.at(0), *m = eng.at(nfa::SIZE);
     wr32(nh, nfa::flags, any_eod ? nfa::ACCEPTS_EOD : 0);
     wr32(nh, nfa::length, (u32)total);
-    wr8(nh, nfa::type, nfa::SHENG);
+    wr8(nh, nfa::type, sh.nfa_type);
     wr32(nh, nfa::queueIndex, 0);
     wr32(nh, nfa::nPositions, n);
     wr32(nh, nfa::scratchStateSize, 1);
@@ -732,17 +734,22 @@ int emit_sheng(const Dfa &d, const u8 *reach_map, const std::vector<u32> &progra
     wr32(nh, nfa::maxWidth, 0);
     wr32(nh, nfa::minWidth, min_width);
     for (u32 c = 0; c < 256; c++)
-        for (u32 i = 0; i < n; i++) m[sh::shuffle_masks + 16 * c + i] = state_byte(d.next[i][reach_map[c]]);
-    wr32(m, sh::length, (u32)(total - nfa::SIZE));
-    wr32(m, sh::aux_offset, (u32)nfa_size);
-    wr32(m, sh::report_offset, (u32)reports_offset);
-    wr32(m, sh::accel_offset, (u32)accel_offset);
-    wr8(m, sh::n_states, (u8)n);
-    wr8(m, sh::anchored, state_byte(d.start_anchored));
-    wr8(m, sh::floating, state_byte(d.start_floating));
+        for (u32 i = 0; i < n; i++) {
+            m[(size_t)sh.stride * c + i] = state_byte(d.next[i][reach_map[c]]);
+            // Sheng32: the 64-byte permute looks at 6 bits of the state byte, one of which is its accept flag (0x20): every
+            // entry is stored again 32 places up (createShuffleMasks<sheng32>, shengcompile.cpp:578-596)
+            if (sh.nfa_type == 21) m[(size_t)sh.stride * c + 32 + i] = m[(size_t)sh.stride * c + i];
+        }
+    wr32(m, sh.length, (u32)(total - nfa::SIZE));
+    wr32(m, sh.aux_offset, (u32)nfa_size);
+    wr32(m, sh.report_offset, (u32)reports_offset);
+    wr32(m, sh.accel_offset, (u32)accel_offset);
+    wr8(m, sh.n_states, (u8)n);
+    wr8(m, sh.anchored, state_byte(d.start_anchored));
+    wr8(m, sh.floating, state_byte(d.start_floating));
     const bool single = all_reports.size() == 1;
-    wr8(m, sh::flags, (u8)((single ? sh::FLAG_SINGLE_REPORT : 0) | (can_die ? sh::FLAG_CAN_DIE : 0)));
-    wr32(m, sh::report, single ? *all_reports.begin() : 0);
+    wr8(m, sh.flags, (u8)((single ? sheng::FLAG_SINGLE_REPORT : 0) | (can_die ? sheng::FLAG_CAN_DIE : 0)));
+    wr32(m, sh.report, single ? *all_reports.begin() : 0);
     std::vector<u32> list_off(lists.size());
     size_t o = reports_offset;
     for (size_t i = 0; i < lists.size(); i++) {
@@ -752,11 +759,11 @@ int emit_sheng(const Dfa &d, const u8 *reach_map, const std::vector<u32> &progra
         o += 4 + 4 * lists[i].size();
     }
     for (u32 i = 0; i < n; i++) {
-        u8 *a = eng.at(nfa_size + sh::aux::SIZE * (size_t)i);
-        wr32(a, sh::aux::accept, list_of[i] == ~0u ? 0 : list_off[list_of[i]]);
-        wr32(a, sh::aux::accept_eod, list_eod_of[i] == ~0u ? 0 : list_off[list_eod_of[i]]);
-        wr32(a, sh::aux::accel, 0);
-        wr32(a, sh::aux::top, state_byte(d.start_floating));
+        u8 *a = eng.at(nfa_size + sheng::aux::SIZE * (size_t)i);
+        wr32(a, sheng::aux::accept, list_of[i] == ~0u ? 0 : list_off[list_of[i]]);
+        wr32(a, sheng::aux::accept_eod, list_eod_of[i] == ~0u ? 0 : list_off[list_eod_of[i]]);
+        wr32(a, sheng::aux::accel, 0);
+        wr32(a, sheng::aux::top, state_byte(d.start_floating));
     }
     return HSB_LIT_SUCCESS;
 }
@@ -1012,8 +1019,8 @@ int emit_engine(const Automaton &am, unsigned engine, const std::vector<u32> &pr
     Dfa dfa;
     if (!determinise(am, reach_rows, dfa, dfa_state_limit)) { err = "DFA too large for a McClellan engine"; return HSB_LIT_COMPILER_ERROR; }
     minimise(dfa);
-    const int rv = engine == HSB_REGEX_ENGINE_SHENG
-                       ? emit_sheng(dfa, reach_map, program_of, am.min_width, eng, stream_state, err)
+    const int rv = engine == HSB_REGEX_ENGINE_SHENG || engine == HSB_REGEX_ENGINE_SHENG_WIDE
+                       ? emit_sheng(dfa, reach_map, program_of, am.min_width, eng, stream_state, err, engine == HSB_REGEX_ENGINE_SHENG_WIDE)
                        : emit_mcclellan(dfa, reach_map, program_of, engine == HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN, am.min_width, eng, stream_state, err);
     scratch_state = stream_state;
     return rv;
@@ -1024,7 +1031,7 @@ int emit_engine(const Automaton &am, unsigned engine, const std::vector<u32> &pr
 namespace hsb_nfadb {
 
 int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &image, std::string &err) {
-    if (engine > HSB_REGEX_ENGINE_SHENG) { err = "unknown engine"; return HSB_LIT_COMPILER_ERROR; }
+    if (engine > HSB_REGEX_ENGINE_SHENG_WIDE) { err = "unknown engine"; return HSB_LIT_COMPILER_ERROR; }
     if (pats.empty()) { err = "no expressions"; return HSB_LIT_COMPILER_ERROR; }
     // ---- 1. parse every pattern, build one automaton -------------------------------------------------
     std::vector<Parsed> parsed;

@@ -210,7 +210,7 @@ def compile_lit_multi(literals, flags=None, ids=None, mode=HS_MODE_BLOCK, engine
     return Database(db.value)
 
 
-ENGINE_LIMEX, ENGINE_MCCLELLAN, ENGINE_MCCLELLAN_SHERMAN, ENGINE_SHENG = 0, 1, 2, 3
+ENGINE_LIMEX, ENGINE_MCCLELLAN, ENGINE_MCCLELLAN_SHERMAN, ENGINE_SHENG, ENGINE_SHENG_WIDE = 0, 1, 2, 3, 4
 
 
 def compile_regex_multi(expressions, flags=None, ids=None, mode=HS_MODE_BLOCK, engine=ENGINE_LIMEX):
