@@ -1416,9 +1416,19 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
     im->bc_len = v.bc_len;
     // A Sheng engine (<= 16 states as 256 shuffle masks) is re-laid at upload as a state-major byte table with the
     // McClellan8 conventions (dead = 0, accepting states numbered last) behind the bytecode, and stepped by k_mcclellan.
+    // (Sheng outfixes of a multi-engine database get their tables one behind the other in the same area.)
     std::vector<u8> derived;
     const u32 derived_at = (u32)round_up(v.bc_len, 256) + 256;
     if (v.kind == ENG_SHENG) build_sheng_tables(v, derived_at, derived, im->mcc);
+    std::vector<DevMcc> sub_sheng(v.engines.size());
+    for (size_t q = 0; q < v.engines.size(); q++) {
+        if (v.engines[q].kind != ENG_SHENG) continue;
+        std::vector<u8> one;
+        const u32 at = derived_at + (u32)round_up(derived.size(), 256);
+        build_sheng_tables(v.engines[q], at, one, sub_sheng[q]);
+        derived.resize(at - derived_at, 0);
+        derived.insert(derived.end(), one.begin(), one.end());
+    }
     const size_t image_bytes = derived_at + (derived.empty() ? 0 : round_up(derived.size(), 256) + 256);
     cudaError_t e = cudaMalloc((void **)&im->d_bc, image_bytes);
     if (e != cudaSuccess) { delete im; return HS_NOMEM; }
@@ -1505,6 +1515,7 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         sub->owns_bc = false;
         sub->dev = im->dev;
         im->subs.push_back(sub);
+        if (ev.kind == ENG_SHENG) sub->mcc = sub_sheng[im->subs.size() - 1];   // tables built with the image (above)
         const hs_error_t erv = build_engine_image(s, sub);
         if (erv != HS_SUCCESS) { im->release(); delete im; return erv; }
         im->device_bytes += sub->device_bytes;

@@ -342,7 +342,6 @@ inline int parse_outfix_queues(DbView &d, std::string &why) {
         e.ekey_count = d.ekey_count; e.dkey_count = d.dkey_count; e.groups = d.groups;
         const int rv = parse_outfix_at(e, info_off + (u32)nfainfo::SIZE * qi, why);
         if (rv != E_SUCCESS) { why = "queue " + std::to_string(qi) + ": " + why; return rv; }
-        if (e.kind == ENG_SHENG) { why = "Sheng outfixes inside a multi-engine database are not supported yet"; return E_ARCH; }
         if (e.nfa_flags & nfa::ACCEPTS_EOD) { why = "outfix with end-of-data accepts needs the EOD program (not supported yet)"; return E_ARCH; }
         for (u32 p : e.programs) progs.insert(p);
         d.max_lit_len = std::max(d.max_lit_len, e.max_lit_len);

@@ -1011,7 +1011,7 @@ int emit_limex(const Automaton &am, const std::vector<StateSet> &reach_rows, con
 
 // one engine for one automaton: LimEx, or the determinised McClellan / Sheng form
 int emit_engine(const Automaton &am, unsigned engine, const std::vector<u32> &program_of, u32 dfa_state_limit, Buf &eng,
-                u32 &stream_state, u32 &scratch_state, std::string &err) {
+                u32 &stream_state, u32 &scratch_state, std::string &err, bool sheng_if_small = false) {
     std::vector<StateSet> reach_rows;
     u8 reach_map[256];
     if (!reach_table(am, reach_rows, reach_map)) { err = "internal: reach table overflow"; return HSB_LIT_COMPILER_ERROR; }
@@ -1019,6 +1019,10 @@ int emit_engine(const Automaton &am, unsigned engine, const std::vector<u32> &pr
     Dfa dfa;
     if (!determinise(am, reach_rows, dfa, dfa_state_limit)) { err = "DFA too large for a McClellan engine"; return HSB_LIT_COMPILER_ERROR; }
     minimise(dfa);
+    // outfix engines of multi-engine databases: a DFA of at most 16 states is laid out as a Sheng engine, which is what the
+    // reference compiler tries first for every DFA (shengCompile before mcclellanCompile, src/rose/rose_build_bytecode.cpp
+    // buildOutfix / getDfa)
+    if (sheng_if_small && engine == HSB_REGEX_ENGINE_MCCLELLAN && dfa.next.size() <= 16) engine = HSB_REGEX_ENGINE_SHENG;
     const int rv = engine == HSB_REGEX_ENGINE_SHENG || engine == HSB_REGEX_ENGINE_SHENG_WIDE
                        ? emit_sheng(dfa, reach_map, program_of, am.min_width, eng, stream_state, err, engine == HSB_REGEX_ENGINE_SHENG_WIDE)
                        : emit_mcclellan(dfa, reach_map, program_of, engine == HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN, am.min_width, eng, stream_state, err);
@@ -1232,7 +1236,7 @@ int build_outfix_engines(const std::vector<Pattern> &pats, unsigned engine, u32 
         if (!make_automaton(parsed, groups[qi].members, am, total)) { err = "internal: group too large"; return HSB_LIT_COMPILER_ERROR; }
         Buf eng;
         EngineBlob blob;
-        if (emit_engine(am, groups[qi].engine, program_of, 4 * (mcclellan::STATE_MASK + 1), eng, blob.stream_state, blob.scratch_state, err) != HSB_LIT_SUCCESS)
+        if (emit_engine(am, groups[qi].engine, program_of, 4 * (mcclellan::STATE_MASK + 1), eng, blob.stream_state, blob.scratch_state, err, true) != HSB_LIT_SUCCESS)
             return HSB_LIT_COMPILER_ERROR;
         wr32(eng.at(0), nfa::queueIndex, qi);
         blob.bytes = eng.b;
