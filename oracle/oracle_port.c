@@ -68,8 +68,8 @@ struct scan_state {
     op_match_cb cb; void *ctx;
     int terminated, error;
     /* multi-outfix catch-up (rose/catchup.c): engine reports are gathered, then replayed in offset order */
-    int defer; u32 cur_queue;
-    struct deferred { u64 to; u32 queue, prog, seq; } *ev; size_t n_ev, cap_ev, ev_next;
+    int defer; u32 cur_queue; int cur_eod;   /* cur_eod: the engine is in its end-of-data check (ENGINES_EOD) */
+    struct deferred { u64 to; u32 queue, prog, seq, eod; } *ev; size_t n_ev, cap_ev, ev_next;
 };
 
 /* roseDeliverReport + the dedupe test of dedupeCatchup for external reports without SOM */
@@ -176,7 +176,7 @@ static int run_program(struct scan_state *s, u32 prog, u64 end) {
             s->cap_ev = s->cap_ev ? 2 * s->cap_ev : 256;
             s->ev = realloc(s->ev, s->cap_ev * sizeof(*s->ev));
         }
-        s->ev[s->n_ev] = (struct deferred){end, s->cur_queue, prog, (u32)s->n_ev};
+        s->ev[s->n_ev] = (struct deferred){end, s->cur_queue, prog, (u32)s->n_ev, (u32)s->cur_eod};
         s->n_ev++;
         return 0;
     }
@@ -433,8 +433,10 @@ static int limex_scan(struct scan_state *s, const u8 *nfa) {
         lx_accepts(s, limex, &l, st, l.accept, rd32(limex + LX_ACCEPT_OFF), s->len) < 0) return -1;
     u64 any = 0;
     for (u32 w = 0; w < l.words; w++) any |= st[w];
+    s->cur_eod = 1;
     if (any && (rd32(nfa + NFA_FLAGS) & NFA_ACCEPTS_EOD) && rd32(limex + LX_ACCEPT_EOD_COUNT) &&
-        lx_accepts(s, limex, &l, st, l.accept_eod, rd32(limex + LX_ACCEPT_EOD_OFF), s->len) < 0) return -1;
+        lx_accepts(s, limex, &l, st, l.accept_eod, rd32(limex + LX_ACCEPT_EOD_OFF), s->len) < 0) { s->cur_eod = 0; return -1; }
+    s->cur_eod = 0;
     return 0;
 }
 
@@ -488,7 +490,9 @@ static int mcclellan_scan(struct scan_state *s, const u8 *nfa) {
         }
         if (accept && mc_report(s, nfa, m, st, (u64)i + 1, 0) < 0) return -1;
     }
-    if (st && (rd32(nfa + NFA_FLAGS) & NFA_ACCEPTS_EOD) && mc_report(s, nfa, m, st, s->len, 1) < 0) return -1;
+    s->cur_eod = 1;
+    if (st && (rd32(nfa + NFA_FLAGS) & NFA_ACCEPTS_EOD) && mc_report(s, nfa, m, st, s->len, 1) < 0) { s->cur_eod = 0; return -1; }
+    s->cur_eod = 0;
     return 0;
 }
 
@@ -534,13 +538,17 @@ static int sheng_scan(struct scan_state *s, const u8 *nfa) {
     if (can_die && (st & f.dead)) return 0;                        /* MO_DEAD: no final-state check */
     if (rd32(nfa + NFA_FLAGS) & NFA_ACCEPTS_EOD) {
         const u8 *aux = nfa + rd32(tr + 4) + (size_t)(st & f.mask) * 16;
-        if (rd32(aux + 4) && sh_report(s, nfa, sh, &f, st, s->len, 1) < 0) return -1;
+        s->cur_eod = 1;
+        const int rv = rd32(aux + 4) ? sh_report(s, nfa, sh, &f, st, s->len, 1) : 0;
+        s->cur_eod = 0;
+        if (rv < 0) return -1;
     }
     return 0;
 }
 
 static int deferred_cmp(const void *a, const void *b) {
     const struct deferred *x = a, *y = b;
+    if (x->eod != y->eod) return x->eod < y->eod ? -1 : 1;   /* the EOD program runs after every engine was caught up */
     if (x->to != y->to) return x->to < y->to ? -1 : 1;
     if (x->queue != y->queue) return x->queue < y->queue ? -1 : 1;
     return x->seq < y->seq ? -1 : x->seq > y->seq;
@@ -555,7 +563,7 @@ static void engine_scan(struct scan_state *s, const u8 *nfa) {
 /* roseCatchUpTo (rose/catchup.h:128-167): deliver the outfix engines' pending reports with offset <= end, in offset
  * order (queue order inside one offset), through their report programs. */
 static int catch_up(struct scan_state *s, u64 end) {
-    while (s->ev_next < s->n_ev && s->ev[s->ev_next].to <= end) {
+    while (s->ev_next < s->n_ev && s->ev[s->ev_next].to <= end && !s->ev[s->ev_next].eod) {
         const struct deferred e = s->ev[s->ev_next++];
         if (run_program(s, e.prog, e.to) < 0) return -1;
     }
@@ -582,6 +590,11 @@ static void full_rose_exec(struct scan_state *s, const u8 *rose) {
     if (rd32(rose + R_FMATCHER) && s->len >= rd32(rose + 116) /* fmatcherMinWidth */ && !s->error)
         hwlm_exec(s, rose + rd32(rose + R_FMATCHER));
     if (!s->terminated && !s->error) catch_up(s, s->len);
+    /* roseBlockEodExec (rose/block.c:163-190): ENGINES_EOD -> nfaCheckFinalState of every engine still alive, queue order */
+    while (!s->terminated && !s->error && s->ev_next < s->n_ev) {
+        const struct deferred e = s->ev[s->ev_next++];
+        if (run_program(s, e.prog, e.to) < 0) break;
+    }
     free(s->ev);
     s->ev = NULL;
 }
@@ -600,7 +613,8 @@ int op_scan(const void *db, const char *data, unsigned length, op_match_cb cb, v
         /* full Rose: a floating literal matcher and / or outfix engines; no roles, leftfixes, other matchers, EOD program */
         if (rd32(rose + 88) || rd32(rose + 92) || rd32(rose + 100) || rd32(rose + 104) || rd32(rose + 108) ||
             (rd32(rose + R_FMATCHER) && (rose[1] || rd32(rose + 224) || rd32(rose + 220) != 0xffffffffu || rd32(rose + 128) != 0xffffffffu)) ||
-            rd32(rose + 84) || rd32(rose + 184) || rd32(rose + 64) || rd32(rose + 152) ||
+            rd32(rose + 84) || rd32(rose + 64) || rd32(rose + 152) ||
+            (rd32(rose + 184) && (rose[rd32(rose + 184)] != 48 || rose[rd32(rose + 184) + 8] != 0)) || /* eodProgram: ENGINES_EOD; END */
             rd32(rose + 404) != rd32(rose + 156) || rd32(rose + 400) != rd32(rose + 156) || rd32(rose + 408) != 0xffffffffu)
             return HS_ARCH_ERROR;
     }

@@ -52,6 +52,20 @@ def main():
         texts = [regen.random_text(rng, ex, rng.choice([0, 1, 40, 300, 1400]), smp) for _ in range(6)]
         cases.append({"kind": "outfixes", "exprs": [e.decode("latin-1") for e in ex], "flags": fl, "ids": ids, "engine": engine,
                       "dfa_states": ds, "texts": [t.hex() for t in texts], "expect": record(R, db, texts)})
+    for seed in range(4):          # (a') outfix engines with end-of-data patterns: EOD program (ENGINES_EOD)
+        rng = random.Random(41500 + seed)
+        ex, fl, ids, smp = regen.random_set(rng, rng.randint(3, 10), True)
+        ex = regen.with_eod(rng, ex, 0.5)
+        engine, ds = [(1, 24), (1, 300), (0, 0), (2, 600)][seed]
+        db = litdb.compile_regex_rose(ex, fl, ids, engine=engine, dfa_states=ds)
+        texts = []
+        for k in range(6):
+            t = regen.random_text(rng, ex, rng.choice([20, 60, 140]), smp)
+            if smp and k % 2 == 0:
+                t = t[:max(0, len(t) - len(smp[k % len(smp)]))] + smp[k % len(smp)]
+            texts.append(t)
+        cases.append({"kind": "outfixes", "exprs": [e.decode("latin-1") for e in ex], "flags": fl, "ids": ids, "engine": engine,
+                      "dfa_states": ds, "texts": [t.hex() for t in texts], "expect": record(R, db, texts)})
     for seed in range(6):          # (b) literals + regexes
         rng = random.Random(42000 + seed)
         lits, flags, ids, ex, fl, rids, text = mixed_case(rng, rng.choice([1, 5, 40, 300]), rng.randint(1, 8), 3000)

@@ -96,3 +96,38 @@ def test_fused_packs_on_random_sets(ref, seed):
     sc.close()
     assert got == ref_batch(ref, db, bufs)
     assert got == brute_batch(ex, fl, ids, bufs)
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_end_of_data_patterns_in_multi_engine_databases(ref, seed):
+    """\\z patterns spread over several outfix engines (EOD program = ENGINES_EOD): every engine kernel raises its own
+    end-of-data accepts; the finalize dedupes them against regular accepts at the same offset."""
+    rng = random.Random(5100 + seed)
+    ex, fl, ids, smp = regen.random_set(rng, rng.randint(3, 12), True)
+    ex = regen.with_eod(rng, ex, 0.5)
+    engine, ds = [(litdb.ENGINE_MCCLELLAN, 24), (litdb.ENGINE_MCCLELLAN, 300), (litdb.ENGINE_LIMEX, 0),
+                  (litdb.ENGINE_MCCLELLAN_SHERMAN, 600)][seed % 4]
+    db = litdb.compile_regex_rose(ex, fl, ids, engine=engine, dfa_states=ds)
+    bufs = []
+    for k in range(120):
+        t = regen.random_text(rng, ex, rng.choice([0, 1, 20, 60, 140, 1400]), smp)
+        if smp and k % 2 == 0:
+            x = smp[k % len(smp)]
+            t = t[:max(0, len(t) - len(x))] + x
+        bufs.append(t)
+    for pack in (1, 0, 2):
+        sc = gpu.alloc_scratch(db)
+        sc.set_option("pack", pack)
+        got = gpu_batch(db, bufs, sc)
+        sc.close()
+        assert got == ref_batch(ref, db, bufs), pack
+    assert got == brute_batch(ex, fl, ids, bufs) and len(got) > 10
+
+
+def test_mixed_database_with_eod_regexes(ref):
+    lits = [b"needle", b"hay", b"stack"]
+    ex = [b"abc[0-9]+\\z", b"tail\\z", b"mid[a-z]{2}x"]
+    db = litdb.compile_lit_multi(lits, [0, 1, 0], [1, 2, 3], regexes=ex, regex_flags=[0, 0, 0], regex_ids=[10, 11, 12], dfa_states=20)
+    bufs = [b"needle abc123", b"HAY midqqx tail", b"stack tail x", b"", b"abc1", b"tailtail"]
+    got = gpu_batch(db, bufs)
+    assert got == ref_batch(ref, db, bufs) and len(got) >= 8

@@ -67,11 +67,49 @@ def test_many_engines_and_shared_ids(ref):
     assert total > 5
 
 
-def test_refuses_eod_patterns_and_bad_engine():
-    with pytest.raises(litdb.CompileError):
-        litdb.compile_regex_rose([b"abc\\z", b"def"])
+def test_refuses_bad_engine():
     with pytest.raises(litdb.CompileError):
         litdb.compile_regex_rose([b"abc"], engine=litdb.ENGINE_SHENG)
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_end_of_data_patterns_in_multi_engine_databases(ref, seed):
+    """Patterns ending in \\z spread over several outfix engines: the database carries an EOD program (ENGINES_EOD over a
+    multibit sparse iterator of the queues that accept at end of data; roseBlockEodExec, src/rose/block.c:163-190).
+    Reference hs_scan == `re` brute force, and the oracle port reproduces the callback sequence."""
+    rng = random.Random(5000 + seed)
+    ex, fl, ids, smp = regen.random_set(rng, rng.randint(3, 12), True)
+    ex = regen.with_eod(rng, ex, 0.5)
+    engine, ds = rng.choice([(litdb.ENGINE_MCCLELLAN, 24), (litdb.ENGINE_MCCLELLAN, 300), (litdb.ENGINE_LIMEX, 0),
+                             (litdb.ENGINE_MCCLELLAN_SHERMAN, 600)])
+    db = litdb.compile_regex_rose(ex, fl, ids, engine=engine, dfa_states=ds)
+    texts = []
+    for k in range(6):
+        t = regen.random_text(rng, ex, rng.choice([20, 60, 140]), smp)
+        if smp and k % 2 == 0:
+            x = smp[k % len(smp)]
+            t = t[:max(0, len(t) - len(x))] + x
+        texts.append(t)
+    for t, g in zip(texts, scan_ref(ref, db, texts, ordered=True)):
+        assert sorted(set(g), key=lambda x: (x[1], x[0])) == regen.brute_force(ex, fl, ids, t), (ex, fl, t)
+        assert oracle_port.scan(db, t) == (0, g)
+
+
+def test_eod_patterns_over_more_than_64_engines(ref):
+    """65+ queues: the sparse iterator has a root record and one record per 64-queue block."""
+    words = [b"admin", b"login", b"passwd", b"select", b"union", b"script", b"eval", b"cmd", b"shell", b"upload"]
+    ex, fl, ids = [], [], []
+    for k in range(200):
+        w = words[k % 10]
+        ex.append(w + b"[0-9]{1,2}x%d" % k + (b"\\z" if k % 3 == 0 else b""))
+        fl.append(0)
+        ids.append(k)
+    db = litdb.compile_regex_rose(ex, fl, ids, dfa_states=14)
+    assert rose_header(db)["queues"] > 64
+    texts = [b"zz admin5x0", b"login12x71 tail", b"cmd7x87", b"select3x3", b"union44x4 select3x33", b"", b"shell1x198", b"eval2x186 eval2x186"]
+    for t, g in zip(texts, scan_ref(ref, db, texts, ordered=True)):
+        assert sorted(set(g), key=lambda x: (x[1], x[0])) == regen.brute_force(ex, fl, ids, t), t
+        assert oracle_port.scan(db, t) == (0, g)
 
 
 @pytest.mark.parametrize("seed", range(6))

@@ -311,11 +311,20 @@ inline int full_rose_gates(const DbView &d, std::string &why) {
     }
     const u32 nq = rd32(r, rose::queueCount);
     if (rd32(r, rose::rolesWithStateCount) || rd32(r, rose::activeLeftCount) || rd32(r, rose::roseCount) ||
-        rd32(r, rose::eodProgramOffset) || rd8(r, rose::requiresEodCheck) || rd32(r, rose::delay_count) ||
+        rd32(r, rose::delay_count) ||
         rd32(r, rose::anchored_count) || rd32(r, rose::initMpvNfa) != 0xffffffffu || rd32(r, rose::outfixBeginQueue) ||
         rd32(r, rose::outfixEndQueue) != nq || rd32(r, rose::leftfixBeginQueue) != nq || rd32(r, rose::somLocationCount)) {
-        why = "full-Rose database with roles, leftfixes, MPV, delayed literals or an EOD program is not supported yet";
+        why = "full-Rose database with roles, leftfixes, MPV or delayed literals is not supported yet";
         return E_ARCH;
+    }
+    // EOD program: only "ENGINES_EOD; END" -- the end-of-data accepts of the outfix engines (roseEnginesEod,
+    // src/rose/program_runtime.c:1739-1789), which every engine kernel raises itself at the end of a buffer
+    const u32 eodp = rd32(r, rose::eodProgramOffset);
+    if (eodp && rd8(r, rose::requiresEodCheck)) {
+        if (!in_range(d, eodp, 16) || (eodp & 7) || rd8(r, eodp) != op::ENGINES_EOD || rd8(r, eodp + 8) != op::END) {
+            why = "EOD program other than ENGINES_EOD; END is not supported yet";
+            return E_ARCH;
+        }
     }
     if (rd32(r, rose::fmatcherOffset) &&
         (rd8(r, rose::noFloatingRoots) || rd32(r, rose::floatingMinDistance) || rd32(r, rose::floatingDistance) != rose::BOUND_INF ||
@@ -335,6 +344,7 @@ inline int parse_outfix_queues(DbView &d, std::string &why) {
     const u32 info_off = rd32(r, rose::nfaInfoOffset);
     if (!in_range(d, info_off, (size_t)nfainfo::SIZE * nq)) { why = "NfaInfo array outside bytecode"; return E_INVALID; }
     std::set<u32> progs(d.programs.begin(), d.programs.end());
+    std::vector<u32> eod_queues;
     for (u32 qi = 0; qi < nq; qi++) {
         DbView e;
         e.bc = d.bc; e.bc_len = d.bc_len; e.crc = d.crc;
@@ -342,12 +352,36 @@ inline int parse_outfix_queues(DbView &d, std::string &why) {
         e.ekey_count = d.ekey_count; e.dkey_count = d.dkey_count; e.groups = d.groups;
         const int rv = parse_outfix_at(e, info_off + (u32)nfainfo::SIZE * qi, why);
         if (rv != E_SUCCESS) { why = "queue " + std::to_string(qi) + ": " + why; return rv; }
-        if (e.nfa_flags & nfa::ACCEPTS_EOD) { why = "outfix with end-of-data accepts needs the EOD program (not supported yet)"; return E_ARCH; }
+        if (e.nfa_flags & nfa::ACCEPTS_EOD) eod_queues.push_back(qi);
         for (u32 p : e.programs) progs.insert(p);
         d.max_lit_len = std::max(d.max_lit_len, e.max_lit_len);
         d.engines.push_back(std::move(e));
     }
     d.programs.assign(progs.begin(), progs.end());
+    // The engines' end-of-data accepts fire (in the reference) only through ENGINES_EOD and only for the queues its sparse
+    // iterator names: it must name exactly the engines that accept at EOD (flat multibit model, src/util/multibit.h:1136-1184)
+    if (!eod_queues.empty()) {
+        const u32 eodp = rd32(r, rose::eodProgramOffset);
+        if (!eodp || !rd8(r, rose::requiresEodCheck)) { why = "engines with end-of-data accepts but no EOD program"; return E_ARCH; }
+        if (nq > 256) { why = "ENGINES_EOD over more than 256 queues is not supported yet"; return E_ARCH; }
+        const u32 it = rd32(r, eodp + 4);
+        if ((it & 7) || !in_range(d, it, 16 * 5)) { why = "sparse iterator outside bytecode"; return E_INVALID; }
+        std::vector<u32> named;
+        if (nq <= 64) {
+            const u64 m = rd64(r, it);
+            for (u32 k = 0; k < 64; k++) if ((m >> k) & 1) named.push_back(k);
+        } else {
+            const u64 root = rd64(r, it);
+            u32 rec = rd32(r, it + 8);
+            for (u32 b = 0; b < 4; b++) {
+                if (!((root >> b) & 1)) continue;
+                const u64 m = rd64(r, it + 16 * (size_t)rec);
+                for (u32 k = 0; k < 64; k++) if ((m >> k) & 1) named.push_back(64 * b + k);
+                rec++;
+            }
+        }
+        if (named != eod_queues) { why = "ENGINES_EOD iterator does not name the engines that accept at end of data"; return E_ARCH; }
+    }
     return E_SUCCESS;
 }
 

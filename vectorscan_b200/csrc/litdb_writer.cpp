@@ -1122,7 +1122,7 @@ int build(const std::vector<FullLit> &fulls_in, const hsb_lit_options &opt, cons
     // Outfix engines beside the literal matcher (mixed literal + regex sets): report programs, one engine per queue,
     // NfaInfo array, state_init plan -- the layout of nfadb_writer.cpp build_rose.
     u32 n_queues = 0, nfa_info_off = 0, leaf_bytes = 0, scratch_total = 0, total_dkeys = (u32)dkeys.size();
-    u32 plan_u64_off = 0, plan_u64_n = 0, plan_u8_off = 0, plan_u8_n = 0;
+    u32 plan_u64_off = 0, plan_u64_n = 0, plan_u8_off = 0, plan_u8_n = 0, eod_program = 0;
     std::vector<hsb_nfadb::EngineBlob> blobs;
     std::vector<u32> nfa_at;
     const u32 leaf_off = 1;
@@ -1157,6 +1157,10 @@ int build(const std::vector<FullLit> &fulls_in, const hsb_lit_options &opt, cons
             nfa_at.push_back(at);
             min_width = std::min(min_width, blobs[qi].min_width);
         }
+        eod_program = hsb_nfadb::emit_engines_eod(rose, blobs, err);
+        if (eod_program == ~0u) return HSB_LIT_COMPILER_ERROR;
+        for (u32 qi = 0; qi < n_queues; qi++)
+            wr8(rose.at(nfa_info_off + (size_t)nfainfo::SIZE * qi), nfainfo::eod, hsb_nfadb::accepts_eod(blobs[qi]) ? 1 : 0);
         rose.align(CACHELINE);
         u32 b = 0;
         if (n_queues > 256) {  // hierarchical multibit: clearing the root block empties it (src/util/multibit.h:332-343)
@@ -1179,6 +1183,8 @@ int build(const std::vector<FullLit> &fulls_in, const hsb_lit_options &opt, cons
     wr8(r, rose::pureLiteral, full_rose ? 0 : 1);
     wr8(r, rose::runtimeImpl, full_rose ? rose::RUNTIME_FULL_ROSE : rose::RUNTIME_PURE_LITERAL);
     wr8(r, rose::hasOutfixesInSmallBlock, n_queues ? 1 : 0);
+    wr8(r, rose::requiresEodCheck, eod_program ? 1 : 0);
+    wr32(r, rose::eodProgramOffset, eod_program);
     wr8(r, rose::canExhaust, all_exhaustible && bx.regexes.empty() ? 1 : 0);
     wr32(r, rose::mode, MODE_BLOCK);
     wr32(r, rose::ekeyCount, (u32)ekeys.size());

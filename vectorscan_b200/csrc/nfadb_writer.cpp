@@ -1179,9 +1179,6 @@ int build_outfix_engines(const std::vector<Pattern> &pats, unsigned engine, u32 
     if (dfa_states > mcclellan::STATE_MASK) dfa_states = mcclellan::STATE_MASK;
     std::vector<Parsed> parsed;
     if (parse_all(pats, parsed, err) != HSB_LIT_SUCCESS) return HSB_LIT_COMPILER_ERROR;
-    for (size_t i = 0; i < parsed.size(); i++)
-        if (parsed[i].eod) { err = "expression " + std::to_string(i) + ": \\z needs an EOD program (not written for multi-engine databases)"; return HSB_LIT_COMPILER_ERROR; }
-
     struct Group { std::vector<u32> members; unsigned engine; };
     std::vector<Group> groups;
     auto dfa_fits = [&](const std::vector<u32> &members) {
@@ -1291,6 +1288,9 @@ int build_rose(const std::vector<Pattern> &pats, unsigned engine, u32 dfa_states
         scratch_total += blob.scratch_state;
         min_width = std::min(min_width, blob.min_width);
     }
+    const u32 eod_program = emit_engines_eod(rose, blobs, err);
+    if (eod_program == ~0u) return HSB_LIT_COMPILER_ERROR;
+    for (u32 qi = 0; qi < N; qi++) wr8(rose.at(nfa_info_off + (size_t)nfainfo::SIZE * qi), nfainfo::eod, accepts_eod(blobs[qi]) ? 1 : 0);
     rose.align(CACHELINE);
     // state_init: clear the active leaf array (8-byte stores, then single bytes)
     u32 plan_u64_off = 0, plan_u64_n = 0, plan_u8_off = 0, plan_u8_n = 0;
@@ -1340,6 +1340,8 @@ int build_rose(const std::vector<Pattern> &pats, unsigned engine, u32 dfa_states
     wr8(r, rose::pureLiteral, 0);
     wr8(r, rose::runtimeImpl, rose::RUNTIME_FULL_ROSE);
     wr8(r, rose::hasOutfixesInSmallBlock, 1);
+    wr8(r, rose::requiresEodCheck, eod_program ? 1 : 0);
+    wr32(r, rose::eodProgramOffset, eod_program);
     wr32(r, rose::mode, MODE_BLOCK);
     wr32(r, rose::dkeyCount, (u32)dkeys.size());
     wr32(r, rose::dkeyLogSize, fatbit_size((u32)dkeys.size()));
