@@ -136,8 +136,10 @@ int hsb_compile_regex_multi_ex(const char *const *expressions, const unsigned *f
  * (src/rose/rose_build_bytecode.cpp:3608-3890, outfix queues :2078-2116).  `engine` = HSB_REGEX_ENGINE_MCCLELLAN[_SHERMAN]:
  * patterns join a group while its DFA stays within `dfa_states` states (0 = 1024); patterns whose own DFA is larger
  * become LimEx engines, as the reference falls back when DFA construction hits its limit.  HSB_REGEX_ENGINE_LIMEX: every
- * group is a LimEx NFA of <= 512 states.  At most 256 engines; no \z patterns.  Scanned by the unmodified reference
- * runtime through roseBlockExec -> blockInitSufPQ -> roseCatchUpTo (src/rose/block.c:345-422, src/rose/catchup.c). */
+ * group is a LimEx NFA of <= 512 states.  DFAs of <= 16 states are laid out as Sheng engines.  At most 4096 engines.
+ * Patterns ending in \z (end-of-data accepts) give the database an EOD program (ENGINES_EOD; at most 256 engines then).
+ * Scanned by the unmodified reference runtime through roseBlockExec -> blockInitSufPQ -> roseCatchUpTo ->
+ * roseBlockEodExec (src/rose/block.c:163-190,345-422, src/rose/catchup.c). */
 int hsb_compile_regex_rose(const char *const *expressions, const unsigned *flags, const unsigned *ids,
                            unsigned elements, unsigned mode, unsigned engine, unsigned dfa_states,
                            hs_database_t **db, char **error);
