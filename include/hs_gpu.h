@@ -90,10 +90,13 @@ hs_error_t hs_gpu_free_scratch(hs_gpu_scratch_t *scratch);
 hs_error_t hs_gpu_scan(const hs_database_t *db, const char *data, unsigned int length, unsigned int flags,
                        hs_gpu_scratch_t *scratch, match_event_handler onEvent, void *context);
 
-/* Batch of `count` INDEPENDENT block-mode scans -- the loop of hs_scan calls that examples/pcapscan.cc:305-316
- * and tools/hsbench/main.cpp:486-512 run -- with the parameter list of hs_scan_vector (src/hs_runtime.h:522-527).
- * Offsets are per buffer.  Matches are delivered buffer by buffer in index order.  (The reference's
- * hs_scan_vector itself has stream semantics on HS_MODE_VECTORED databases; see DESIGN.md.) */
+/* On a BLOCK-mode database: a batch of `count` INDEPENDENT block-mode scans -- the loop of hs_scan calls that
+ * examples/pcapscan.cc:305-316 and tools/hsbench/main.cpp:486-512 run -- with the parameter list of hs_scan_vector
+ * (src/hs_runtime.h:522-527).  Offsets are per buffer.  Matches are delivered buffer by buffer in index order.
+ * On a VECTORED-mode database (HS_MODE_VECTORED, pure-literal databases): the reference's hs_scan_vector itself
+ * (src/runtime.c:1106-1174) -- the buffers are consecutive blocks of ONE stream: a match may straddle blocks, offsets
+ * run on across them, single-match ids stay exhausted to the end of the call; matches are delivered in (to, id) order
+ * and hs_gpu_match_t.buffer is 0.  The stream must be shorter than 4 GiB (else HS_INVALID). */
 hs_error_t hs_gpu_scan_vector(const hs_database_t *db, const char *const *data, const unsigned int *length,
                               unsigned int count, unsigned int flags, hs_gpu_scratch_t *scratch,
                               match_event_handler onEvent, void *context);
@@ -113,7 +116,8 @@ hs_error_t hs_gpu_scan_vector_ex(const hs_database_t *db, const char *const *dat
 hs_error_t hs_gpu_corpus_create(const char *flat, const uint64_t *offsets, unsigned int count,
                                 hs_gpu_corpus_t **corpus);
 hs_error_t hs_gpu_corpus_free(hs_gpu_corpus_t *corpus);
-/* Scan a resident corpus; matches stay on the device until fetched.  Only device work is done. */
+/* Scan a resident corpus; matches stay on the device until fetched.  Only device work is done.  With a vectored-mode
+ * database the corpus' buffers are the consecutive blocks of one stream (see hs_gpu_scan_vector). */
 hs_error_t hs_gpu_scan_corpus(const hs_database_t *db, const hs_gpu_corpus_t *corpus, hs_gpu_scratch_t *scratch,
                               uint64_t *n_matches);
 /* Scan n resident corpora back to back as ONE logical batch (the hsbench loop over several in-memory blocks): the
@@ -123,6 +127,12 @@ hs_error_t hs_gpu_scan_corpus(const hs_database_t *db, const hs_gpu_corpus_t *co
 hs_error_t hs_gpu_scan_corpora(const hs_database_t *db, const hs_gpu_corpus_t *const *corpora, unsigned int n,
                                hs_gpu_scratch_t *scratch, uint64_t *n_matches);
 hs_error_t hs_gpu_fetch_matches(hs_gpu_scratch_t *scratch, const hs_gpu_match_t **matches, uint64_t *n_matches);
+
+/* RoseEngine.mode of a database (src/rose/rose_internal.h:  HS_MODE_BLOCK 1, HS_MODE_STREAM 2, HS_MODE_VECTORED 4) */
+#define HS_GPU_MODE_BLOCK 1u
+#define HS_GPU_MODE_STREAM 2u
+#define HS_GPU_MODE_VECTORED 4u
+hs_error_t hs_gpu_database_mode(const hs_database_t *db, unsigned int *mode);
 
 hs_error_t hs_gpu_last_stats(const hs_gpu_scratch_t *scratch, hs_gpu_stats_t *stats);
 /* Adds, for every match of the last device scan, 1 to device_hist_u64[id] (ids >= n_ids are skipped).

@@ -1,6 +1,7 @@
 /* hs_gpu_shim.c -- link-time drop-in: the reference's block-mode runtime entry points, by their own names and
  * prototypes (/root/reference/src/hs_runtime.h:479-482 hs_scan, :555-556 hs_alloc_scratch, :576 hs_clone_scratch,
- * :593 hs_scratch_size, :609 hs_free_scratch; /root/reference/src/hs_runtime.h:125-129 match_event_handler), forwarding
+ * :593 hs_scratch_size, :609 hs_free_scratch, :522-527 hs_scan_vector; /root/reference/src/hs_runtime.h:125-129
+ * match_event_handler), forwarding
  * to libhs_gpu.so.  An application that calls hs_alloc_scratch / hs_scan keeps its source unchanged and links this
  * library ahead of libhs for these symbols; hs_compile*, hs_(de)serialize_database, hs_free_database stay the
  * reference's own.  What src/dispatcher.c:50-87 does for ISA variants, done for one more backend.
@@ -44,4 +45,17 @@ hs_error_t HS_CDECL hs_free_scratch(hs_scratch_t *scratch) {
 hs_error_t HS_CDECL hs_scan(const hs_database_t *db, const char *data, unsigned int length, unsigned int flags,
                             hs_scratch_t *scratch, match_event_handler onEvent, void *context) {
     return hs_gpu_scan(db, data, length, flags, (hs_gpu_scratch_t *)scratch, onEvent, context);
+}
+
+/* src/runtime.c:1106-1174: vectored-mode databases only (HS_DB_MODE_ERROR otherwise, :1129-1131); the buffers are
+ * consecutive blocks of one stream.  (hs_gpu_scan_vector also serves block-mode databases, as a batch of independent
+ * scans -- an extension this entry point does not expose, so that it behaves exactly as the reference's.) */
+hs_error_t HS_CDECL hs_scan_vector(const hs_database_t *db, const char *const *data, const unsigned int *length,
+                                   unsigned int count, unsigned int flags, hs_scratch_t *scratch,
+                                   match_event_handler onEvent, void *context) {
+    unsigned int mode = 0;
+    const hs_error_t rv = hs_gpu_database_mode(db, &mode);
+    if (rv != HS_SUCCESS) return rv;
+    if (mode != HS_GPU_MODE_VECTORED) return HS_DB_MODE_ERROR;
+    return hs_gpu_scan_vector(db, data, length, count, flags, (hs_gpu_scratch_t *)scratch, onEvent, context);
 }

@@ -62,6 +62,7 @@ typedef int (*op_match_cb)(unsigned id, unsigned long long from, unsigned long l
 
 struct scan_state {
     const u8 *rose; const u8 *buf; u32 len;
+    u32 start; u64 base;               /* vectored mode: buf = history + block; matches end at index >= start, stream offset = base + index */
     u64 groups;
     u8 *exhausted; u32 ekeys;          /* exhaustion vector (report.h:121-153) */
     u8 *dedupe; u32 dkeys; u64 dedupe_offset; /* dedupe log for the current report offset */
@@ -74,6 +75,7 @@ struct scan_state {
 
 /* roseDeliverReport + the dedupe test of dedupeCatchup for external reports without SOM */
 static int report(struct scan_state *s, u32 id, u64 to, u32 ekey, u32 dkey) {
+    to += s->base;
     if (dkey != 0xffffffffu) {
         if (s->dedupe_offset != to) { memset(s->dedupe, 0, (s->dkeys + 7) / 8 + 1); s->dedupe_offset = to; }
         if (s->dedupe[dkey >> 3] & (1u << (dkey & 7))) return 0; /* DEDUPE_SKIP */
@@ -311,7 +313,7 @@ static int hwlm_exec(struct scan_state *s, const u8 *hwlm) {
         u32 n = eng[N_MSK_LEN];
         u64 msk = rd64(eng + N_MSK), cmp = rd64(eng + N_CMP);
         if (s->len < n) return 0;
-        for (u32 e = n - 1; e < s->len; e++) {
+        for (u32 e = n - 1 > s->start ? n - 1 : s->start; e < s->len; e++) {
             u64 v = 0;
             for (u32 k = 0; k < n; k++) v |= (u64)s->buf[e + 1 - n + k] << (8 * k);
             if ((v & msk) == cmp && run_program(s, rd32(eng + N_ID), (u64)e + 1) < 0) return -1;
@@ -320,7 +322,7 @@ static int hwlm_exec(struct scan_state *s, const u8 *hwlm) {
     }
     u32 id = rd32(eng + F_ENGINE_ID);
     const u8 *conf_base = eng + rd32(eng + F_CONF_OFF);
-    for (u32 e = 0; e < s->len; e++) {
+    for (u32 e = s->start; e < s->len; e++) {
         u32 cand;
         if (id == 0) cand = fdr_candidates(eng, s, e);
         else if (id >= 11 && id <= 18) cand = teddy_candidates(eng, (id - 11) / 2 + 1, 1, s, e);
@@ -638,6 +640,51 @@ int op_scan(const void *db, const char *data, unsigned length, op_match_cb cb, v
     return s.terminated ? HS_SCAN_TERMINATED : HS_SUCCESS;
 }
 
+/* hs_scan_vector (runtime.c:1106-1174) for HS_MODE_VECTORED pure-literal databases: the buffers are consecutive blocks
+ * of one stream.  Block by block as hs_scan_stream_internal (runtime.c:880-975) does it: the last historyRequired bytes
+ * of the stream stand in front of the block (getHistory :77-85, maintainHistoryBuffer :483-508); the literal matcher
+ * reports only matches ending inside the block (hwlmExecStreaming) but confirms them, and runs their programs' literal
+ * and lookaround checks, against history + block (fdr_confirm_runtime.h:77-88, program_runtime.c:1988-2011); offsets
+ * run on from block to block; exhaustion lasts to the end of the call. */
+int op_scan_vector(const void *db, const char *const *data, const unsigned *length, unsigned count, op_match_cb cb, void *ctx) {
+    const u8 *d = (const u8 *)db;
+    if (!d || !data || !length || rd32(d + DB_MAGIC_OFF) != 0xdbdbdbdbu) return HS_INVALID;
+    if (rd32(d + DB_VERSION_OFF) != ((5u << 24) | (4u << 16) | (11u << 8))) return HS_DB_VERSION_ERROR;
+    const u8 *rose = d + rd32(d + DB_BYTECODE_OFF);
+    if (rd32(rose + R_MODE) != 4) return HS_DB_MODE_ERROR;
+    if (rose[R_RUNTIME_IMPL] != 1 || rose[R_HAS_SOM] || rd32(rose + R_CKEY_COUNT) || rd32(rose + R_BOUNDARY) ||
+        rd32(rose + R_BOUNDARY + 4) || rd32(rose + R_BOUNDARY + 8))
+        return HS_ARCH_ERROR; /* outside the restated path */
+    const u32 hreq = rd32(rose + 16); /* historyRequired */
+    struct scan_state s;
+    memset(&s, 0, sizeof(s));
+    s.rose = rose; s.cb = cb; s.ctx = ctx;
+    s.groups = rd64(rose + R_INIT_GROUPS) & rd64(rose + R_FLOAT_MASK);
+    s.ekeys = rd32(rose + R_EKEY_COUNT); s.dkeys = rd32(rose + R_DKEY_COUNT);
+    s.exhausted = calloc(s.ekeys / 8 + 2, 1);
+    s.dedupe = calloc(s.dkeys / 8 + 2, 1);
+    s.dedupe_offset = ~0ull;
+    u8 *hist = malloc(hreq + 1), *local = NULL;
+    u32 hlen = 0;
+    u64 offset = 0;
+    for (unsigned b = 0; b < count && !s.terminated && !s.error; b++) {
+        if (!length[b]) continue;              /* zero-length block: no work (runtime.c:895-900) */
+        if (!data[b]) { s.error = 1; break; }
+        local = realloc(local, (size_t)hlen + length[b]);
+        memcpy(local, hist, hlen);
+        memcpy(local + hlen, data[b], length[b]);
+        s.buf = local; s.len = hlen + length[b]; s.start = hlen; s.base = offset - hlen;
+        hwlm_exec(&s, rose + rd32(rose + R_FMATCHER));
+        offset += length[b];
+        const u32 keep = offset < hreq ? (u32)offset : hreq;
+        memmove(hist, local + s.len - keep, keep);
+        hlen = keep;
+    }
+    free(hist); free(local); free(s.exhausted); free(s.dedupe);
+    if (s.error) return HS_UNKNOWN_ERROR;
+    return s.terminated ? HS_SCAN_TERMINATED : HS_SUCCESS;
+}
+
 /* Convenience for tests: collect (id, to) pairs; returns the hs_error_t, *n = pairs wanted (may exceed cap). */
 struct collect { u32 *ids; u64 *tos; size_t cap, n, stop_after; };
 static int collect_cb(unsigned id, unsigned long long from, unsigned long long to, unsigned flags, void *ctx) {
@@ -651,6 +698,14 @@ int op_scan_collect(const void *db, const char *data, unsigned length, u32 *ids,
                     size_t *n) {
     struct collect c = {ids, tos, cap, 0, stop_after};
     int rv = op_scan(db, data, length, collect_cb, &c);
+    if (n) *n = c.n;
+    return rv;
+}
+
+int op_scan_vector_collect(const void *db, const char *const *data, const unsigned *length, unsigned count, u32 *ids, u64 *tos,
+                           size_t cap, size_t stop_after, size_t *n) {
+    struct collect c = {ids, tos, cap, 0, stop_after};
+    int rv = op_scan_vector(db, data, length, count, collect_cb, &c);
     if (n) *n = c.n;
     return rv;
 }

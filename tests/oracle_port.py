@@ -12,6 +12,9 @@ def lib():
         L = C.CDLL(os.path.join(_ROOT, "oracle", "liboracle_port.so"))
         L.op_scan_collect.argtypes = [C.c_void_p, C.c_char_p, C.c_uint, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64),
                                       C.c_size_t, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.op_scan_vector_collect.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_uint), C.c_uint,
+                                             C.POINTER(C.c_uint32), C.POINTER(C.c_uint64), C.c_size_t, C.c_size_t,
+                                             C.POINTER(C.c_size_t)]
         L.op_brute_force.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.POINTER(C.c_uint),
                                      C.POINTER(C.c_uint), C.c_uint, C.c_char_p, C.c_size_t, C.POINTER(C.c_uint32),
                                      C.POINTER(C.c_uint64), C.c_size_t]
@@ -30,6 +33,21 @@ def scan(db, data, stop_after=0, cap=1 << 16):
         if n.value <= cap:
             return rv, [(ids[i], tos[i]) for i in range(n.value)]
         cap = n.value + 16
+
+
+def scan_vector(db, bufs, stop_after=0, cap=1 << 16):
+    """hs_scan_vector on a vectored-mode database: (rv, [(id, to), ...]) in callback order, offsets running on."""
+    n = len(bufs)
+    arr = (C.c_char_p * n)(*bufs)
+    lens = (C.c_uint * n)(*[len(b) for b in bufs])
+    while True:
+        ids = (C.c_uint32 * cap)()
+        tos = (C.c_uint64 * cap)()
+        m = C.c_size_t()
+        rv = lib().op_scan_vector_collect(db.ptr, arr, lens, n, ids, tos, cap, stop_after, C.byref(m))
+        if m.value <= cap:
+            return rv, [(ids[i], tos[i]) for i in range(m.value)]
+        cap = m.value + 16
 
 
 def brute_force(lits, flags, ids, data, cap=1 << 16):

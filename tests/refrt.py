@@ -42,6 +42,9 @@ class RefRuntime:
         L.hs_free_database.argtypes = [C.c_void_p]
         L.hs_scan.argtypes = [C.c_void_p, C.c_char_p, C.c_uint, C.c_uint, C.c_void_p, MATCH_CB, C.c_void_p]
         L.hs_scan.restype = C.c_int
+        L.hs_scan_vector.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_uint), C.c_uint, C.c_uint, C.c_void_p,
+                                     MATCH_CB, C.c_void_p]
+        L.hs_scan_vector.restype = C.c_int
         L.hs_database_info.argtypes = [C.c_void_p, C.POINTER(C.c_char_p)]
         L.ref_shim_crc32c.argtypes = [C.c_char_p, C.c_size_t]
         L.ref_shim_crc32c.restype = C.c_uint
@@ -71,6 +74,20 @@ class RefRuntime:
             return 1 if stop_after and len(out) >= stop_after else 0
 
         rv = self.L.hs_scan(db, data, len(data), 0, scratch, MATCH_CB(cb), None)
+        return rv, out
+
+    def scan_vector(self, db, scratch, bufs, stop_after=0):
+        """hs_scan_vector (HS_MODE_VECTORED databases): (rv, [(id, to), ...]) in callback order."""
+        out = []
+
+        def cb(id_, from_, to, flags, ctx):
+            out.append((id_, to))
+            return 1 if stop_after and len(out) >= stop_after else 0
+
+        n = len(bufs)
+        arr = (C.c_char_p * n)(*bufs)
+        lens = (C.c_uint * n)(*[len(b) for b in bufs])
+        rv = self.L.hs_scan_vector(db, arr, lens, n, 0, scratch, MATCH_CB(cb), None)
         return rv, out
 
     def info(self, db):

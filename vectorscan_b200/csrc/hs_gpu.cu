@@ -1136,10 +1136,18 @@ struct hs_gpu_corpus {
     // the corpus keeps its contents (the staging corpus of host batches is refilled, and reordered, every call)
     mutable DevBuf<u32> order;
     mutable bool order_ready = false;
+    // the same text seen as ONE buffer (vectored-mode databases: the buffers are consecutive blocks of one stream):
+    // offsets {0, total} and an all-zero cell index, built by the first vectored scan of these contents
+    mutable DevBuf<u64> stream_off;
+    mutable DevBuf<u32> stream_cell;
+    mutable bool stream_ready = false;
     u64 total = 0;
     u32 count = 0, nstrips = 0;
     DevCorpus dev() const {
         return DevCorpus{text.p + FRONT_PAD, off.p, cell_first.p, total, count, nstrips, nullptr};
+    }
+    DevCorpus dev_stream() const {
+        return DevCorpus{text.p + FRONT_PAD, stream_off.p, stream_cell.p, total, 1, nstrips, nullptr};
     }
 };
 
@@ -1567,6 +1575,8 @@ cudaError_t launch_small_finalize(hs_gpu_scratch *s, const Rec *in, Rec *out_rec
 inline bool resize_ok(std::vector<u32> &v, size_t n) { v.resize(n); return true; }
 inline bool resize_ok(PinnedBuf<u32> &v, size_t n) { return v.resize(n); }
 
+__global__ void k_stream_offsets(u64 *off, u64 total) { off[0] = 0; off[1] = total; }
+
 // out[c] = buffer holding the first byte of cell c (CELL_BYTES each), out[ncells] = buffer of the last byte
 template <class Vec>
 bool build_cell_first(const u64 *off, u32 count, u64 total, Vec &out, u32 &nstrips) {
@@ -1943,6 +1953,23 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
     }
     DevCorpus cp = corpus.dev();
     CU_OK(cudaEventRecord(s->ev[1], s->stream));  // what was queued before this point is the staging (h2d_ms = ev0 -> ev1)
+    if (im->view.vectored) {
+        // hs_scan_vector on an HS_MODE_VECTORED database (src/runtime.c:1106-1174): block i continues block i - 1 with
+        // history carried over, so what is scanned is the concatenation -- which is how the corpus already lies in HBM.
+        // Offsets and buffer lengths are 32-bit on the device: a stream of 4 GiB or more is refused.
+        if (corpus.total >= 0xffffffffull - BACK_PAD) return HS_INVALID;
+        if (!corpus.stream_ready) {
+            const size_t ncells = (size_t)((corpus.total + CELL_BYTES - 1) / CELL_BYTES) + 1;
+            CU_OK(corpus.stream_off.reserve(2));
+            CU_OK(corpus.stream_cell.reserve(ncells));
+            CU_OK(cudaMemsetAsync(corpus.stream_cell.p, 0, ncells * sizeof(u32), s->stream));
+            k_stream_offsets<<<1, 1, 0, s->stream>>>(corpus.stream_off.p, corpus.total);
+            CU_OK(cudaGetLastError());
+            corpus.stream_ready = true;
+        }
+        cp = corpus.dev_stream();
+        st.buffers = 1;
+    }
     const bool has_engines = im->view.kind == ENG_LIMEX || im->view.kind == ENG_MCCLELLAN || im->view.kind == ENG_SHENG || !im->subs.empty();
     if (has_engines && s->opt_order && cp.count > 32) {
         if (!corpus.order_ready) {
@@ -2181,6 +2208,7 @@ hs_error_t stage_host_buffers(hs_gpu_scratch *s, const char *const *data, const 
     cp.total = total;
     cp.count = count;
     cp.order_ready = false;
+    cp.stream_ready = false;
     CU_OK(cp.text.reserve(FRONT_PAD + total + BACK_PAD));
     CU_OK(cp.off.reserve((size_t)count + 1));
     CU_OK(cudaEventRecord(s->ev[0], s->stream));
@@ -2299,6 +2327,7 @@ hs_error_t stage_host_chunks(hs_gpu_scratch *s, const char *const *data, const u
     cp.total = total;
     cp.count = count;
     cp.order_ready = false;
+    cp.stream_ready = false;
     // the copy stream must not overtake the previous call's scan of this staging area
     CU_OK(cudaEventRecord(s->ev[1], s->stream));
     CU_OK(cudaStreamWaitEvent(s->copy_stream, s->ev[1], 0));
@@ -2402,7 +2431,7 @@ hs_error_t scan_host_batch(const hs_database_t *db, const char *const *data, con
         return std::chrono::duration<double, std::micro>(b - a).count();
     };
     const auto t0 = now();
-    if (ordered_eligible(s, im) && s->opt_pipeline && count >= 2) {
+    if (ordered_eligible(s, im) && s->opt_pipeline && count >= 2 && !im->view.vectored) {  // chunks have no halo: not for one stream
         u64 total = 0;
         bool one_run = true;  // every buffer begins where the one before it ended
         for (unsigned i = 0; i < count; i++) {
@@ -2620,6 +2649,12 @@ hs_error_t hs_gpu_free_scratch(hs_gpu_scratch_t *s) {
     return HS_SUCCESS;
 }
 
+// RoseEngine.mode of a database that validate_scan_args has accepted
+static u32 database_mode(const hs_database_t *db) {
+    const u8 *p = reinterpret_cast<const u8 *>(db);
+    return rd32(p + rd32(p, db::bytecode), rose::mode);  // offsets as parse_database reads them (hsb_dbview.h)
+}
+
 static hs_error_t deliver(hs_gpu_scratch *s, match_event_handler onEvent, void *context, void *const *contexts) {
     if (!onEvent) return HS_SUCCESS;  // matches suppressed, as with a NULL callback in the reference
     const hs_gpu_match_t *m = s->h_matches;
@@ -2637,6 +2672,7 @@ hs_error_t hs_gpu_scan_batch(const hs_database_t *db, const char *const *data, c
     if (!scratch || !data || !length) return HS_INVALID;
     hs_error_t rv = validate_scan_args(db, scratch);
     if (rv != HS_SUCCESS) return rv;
+    if (database_mode(db) != MODE_BLOCK) return HS_DB_MODE_ERROR;  // independent scans: block-mode databases only
     InUseGuard g(scratch);
     if (!g.ok) return HS_SCRATCH_IN_USE;
     DbImage *im = nullptr;
@@ -2680,6 +2716,9 @@ hs_error_t hs_gpu_scan_vector_ex(const hs_database_t *db, const char *const *dat
 hs_error_t hs_gpu_scan(const hs_database_t *db, const char *data, unsigned int length, unsigned int flags,
                        hs_gpu_scratch_t *scratch, match_event_handler onEvent, void *context) {
     if (!scratch || !data) return HS_INVALID;
+    hs_error_t rv = validate_scan_args(db, scratch);
+    if (rv != HS_SUCCESS) return rv;
+    if (database_mode(db) != MODE_BLOCK) return HS_DB_MODE_ERROR;  // src/runtime.c:335-337
     const char *one[1] = {data};
     unsigned int len[1] = {length};
     return hs_gpu_scan_vector(db, one, len, 1, flags, scratch, onEvent, context);
@@ -2760,7 +2799,7 @@ hs_error_t hs_gpu_scan_corpora(const hs_database_t *db, const hs_gpu_corpus_t *c
     if ((rv = upload_database(scratch, db, &im)) != HS_SUCCESS) return rv;
     hs_gpu_scratch *s = scratch;
     hs_gpu_stats_t &st = s->stats;
-    if (!ordered_eligible(s, im)) return HS_ARCH_ERROR;  // a train needs the sort-free path (plain-report literal sets)
+    if (!ordered_eligible(s, im) || im->view.vectored) return HS_ARCH_ERROR;  // a train needs the sort-free path (plain-report literal sets) and independent buffers
     st = hs_gpu_stats_t{};
     s->n_matches = 0;
     s->fetched = false;
@@ -2805,6 +2844,13 @@ hs_error_t hs_gpu_histogram(hs_gpu_scratch_t *scratch, void *device_hist_u64, ui
         CU_OK(cudaGetLastError());
         CU_OK(cudaStreamSynchronize(scratch->stream));
     }
+    return HS_SUCCESS;
+}
+
+hs_error_t hs_gpu_database_mode(const hs_database_t *db, unsigned int *mode) {
+    if (!db || !mode || rd32(db, db::magic) != db::MAGIC) return HS_INVALID;
+    if (rd32(db, db::version) != db::VERSION_5_4_11) return HS_DB_VERSION_ERROR;
+    *mode = database_mode(db);
     return HS_SUCCESS;
 }
 

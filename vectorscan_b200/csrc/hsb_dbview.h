@@ -56,6 +56,9 @@ struct DbView {
     // full-Rose database of outfix engines (kind == ENG_MULTI): one view per queue, each of kind LIMEX / MCCLELLAN
     std::vector<DbView> engines;
     u32 nfa_min_width = 0;  // NFA.minWidth of an outfix engine: blocks shorter than this do not start it
+    // HS_MODE_VECTORED (src/runtime.c:1106-1174): the buffers of one hs_scan_vector call are consecutive blocks of one
+    // stream -- offsets run on, a literal may straddle blocks, exhaustion lasts to the end of the call
+    bool vectored = false;
 };
 
 inline bool in_range(const DbView &d, size_t off, size_t n) { return off <= d.bc_len && n <= d.bc_len - off; }
@@ -481,7 +484,13 @@ inline int parse_database(const void *db, DbView &d, std::string &why) {
     if ((reinterpret_cast<uintptr_t>(d.bc) & 15) != 0) { why = "bytecode not 16-byte aligned"; return E_INVALID; }
     if (d.bc_len < rose::SIZE) { why = "bytecode too short"; return E_INVALID; }
     const u8 *r = d.bc;
-    if (rd32(r, rose::mode) != MODE_BLOCK) { why = "not a block-mode database"; return E_DB_MODE; }
+    const u32 mode = rd32(r, rose::mode);
+    if (mode != MODE_BLOCK && mode != MODE_VECTORED) { why = "not a block-mode or vectored-mode database"; return E_DB_MODE; }
+    d.vectored = mode == MODE_VECTORED;
+    if (d.vectored && rd8(r, rose::runtimeImpl) != rose::RUNTIME_PURE_LITERAL) {
+        why = "vectored mode is served for pure-literal databases only (engines carry stream state from block to block)";
+        return E_ARCH;
+    }
     if (rd32(r, rose::size) > d.bc_len) { why = "engine size exceeds database length"; return E_INVALID; }
     if (rd8(r, rose::hasSom)) { why = "start-of-match databases are not supported"; return E_ARCH; }
     if (rd32(r, rose::ckeyCount) || rd32(r, rose::lkeyCount)) { why = "logical combinations are not supported"; return E_ARCH; }
@@ -496,6 +505,8 @@ inline int parse_database(const void *db, DbView &d, std::string &why) {
     d.min_width = rd32(r, rose::minWidth);
     d.min_width_excl = rd32(r, rose::minWidthExcludingBoundaries);
     d.max_bi_width = rd32(r, rose::maxBiAnchoredWidth);
+    // the stream path has no length gates (hs_scan_stream_internal, src/runtime.c:880-975, tests none of them)
+    if (d.vectored) { d.min_width = d.min_width_excl = 0; d.max_bi_width = rose::BOUND_INF; }
     d.ekey_count = rd32(r, rose::ekeyCount);
     d.dkey_count = rd32(r, rose::dkeyCount);
     d.groups = rd64(r, rose::initialGroups) & rd64(r, rose::floating_group_mask);
