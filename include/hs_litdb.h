@@ -132,6 +132,10 @@ int hsb_compile_regex_multi(const char *const *expressions, const unsigned *flag
 #define HSB_REGEX_ENGINE_SHENG 3u /* DFA of <= 16 states as byte-shuffle masks (src/nfa/sheng_internal.h) */
 #define HSB_REGEX_ENGINE_SHENG_WIDE 4u /* Sheng32 (<= 32 states) / Sheng64 (<= 64): the AVX512VBMI forms, 64-byte masks;
                                           only an AVX512VBMI build of the reference runtime executes them */
+#define HSB_REGEX_ENGINE_MCSHENG 5u /* McClellan DFA whose hot core (<= 16 non-accepting states around the start state)
+                                       steps through byte-shuffle masks: struct mcsheng, MCSHENG_NFA_8 / _16
+                                       (src/nfa/mcsheng_internal.h:63-88) -- what the reference compiler builds for a DFA
+                                       too large for Sheng (getDfa, src/rose/rose_build_bytecode.cpp) */
 int hsb_compile_regex_multi_ex(const char *const *expressions, const unsigned *flags, const unsigned *ids,
                                unsigned elements, unsigned mode, unsigned engine, hs_database_t **db,
                                char **error);

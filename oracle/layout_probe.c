@@ -22,6 +22,11 @@
 #define report_list report_list_sheng /* both engine headers define struct report_list */
 #include "nfa/sheng_internal.h"
 #undef report_list
+#define report_list report_list_mcsheng /* mcsheng_internal.h repeats McClellan's helper structs */
+#define mstate_aux mstate_aux_mcsheng
+#include "nfa/mcsheng_internal.h"
+#undef report_list
+#undef mstate_aux
 #include "util/multibit_internal.h"
 #include "hs_compile.h"
 
@@ -257,6 +262,13 @@ int main(void) {
  /* McClellan DFA */
  VAL(MCCLELLAN_NFA_8); VAL(MCCLELLAN_NFA_16); VAL(ACCEPT_FLAG); VAL(ACCEL_FLAG); VAL(STATE_MASK); VAL(MCCLELLAN_FLAG_SINGLE);
  VAL(SHERMAN_STATE); VAL(SHERMAN_FIXED_SIZE); VAL(SHERMAN_LEN_OFFSET); VAL(SHERMAN_DADDY_OFFSET); VAL(SHERMAN_CHARS_OFFSET);
+ SZ(struct mcsheng); OF(struct mcsheng, state_count); OF(struct mcsheng, length); OF(struct mcsheng, start_anchored);
+ OF(struct mcsheng, start_floating); OF(struct mcsheng, aux_offset); OF(struct mcsheng, sherman_offset);
+ OF(struct mcsheng, sherman_end); OF(struct mcsheng, sheng_end); OF(struct mcsheng, sheng_accel_limit);
+ OF(struct mcsheng, accel_limit_8); OF(struct mcsheng, accept_limit_8); OF(struct mcsheng, sherman_limit);
+ OF(struct mcsheng, alphaShift); OF(struct mcsheng, flags); OF(struct mcsheng, has_accel); OF(struct mcsheng, remap);
+ OF(struct mcsheng, arb_report); OF(struct mcsheng, accel_offset); OF(struct mcsheng, sheng_masks);
+ VAL(MCSHENG_NFA_8); VAL(MCSHENG_NFA_16);
  SZ(struct mcclellan); OF(struct mcclellan, state_count); OF(struct mcclellan, length); OF(struct mcclellan, start_anchored);
  OF(struct mcclellan, start_floating); OF(struct mcclellan, aux_offset); OF(struct mcclellan, sherman_offset);
  OF(struct mcclellan, sherman_end); OF(struct mcclellan, accel_limit_8); OF(struct mcclellan, accept_limit_8);

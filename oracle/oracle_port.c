@@ -556,8 +556,72 @@ static int deferred_cmp(const void *a, const void *b) {
     return x->seq < y->seq ? -1 : x->seq > y->seq;
 }
 
+/* McSheng hybrid DFA (nfa types 19 / 20): nfaExecMcSheng{8,16}_Q -> mcshengExec{8,16}_i (nfa/mcsheng.c:423-590, :654-810).
+ * A state below sheng_end steps through the byte-shuffle masks (doSheng :150-322: sheng_masks[c][s - 1]; the value
+ * sheng_end - 1 is the dead state, a smaller one the region state value + 1, a larger one the id of a state outside the
+ * region); any other state through the successor table, whose rows start at state sheng_end (doNormal16 :368-420,
+ * doNormal8 :612-650; Sherman states as McClellan's).  Leaving the region, the 16-bit engine reads the accept from the
+ * new state's aux record (:466), the 8-bit one from accept_limit_8 (:698).  EOD: mcshengCheckEOD (:830-840).
+ * struct mcsheng: nfa/mcsheng_internal.h:63-88. */
+enum { MS_SHENG_END = 24, MS_ACCEPT_LIMIT_8 = 30, MS_SHERMAN_LIMIT = 32, MS_ALPHA_SHIFT = 34, MS_FLAGS = 35, MS_REMAP = 37,
+       MS_ARB_REPORT = 296, MS_MASKS = 304, MS_SIZE = 4400 };
+
+static int ms_report(struct scan_state *s, const u8 *nfa, const u8 *m, u32 st, u64 loc, int eod) {
+    if (!eod && (m[MS_FLAGS] & 1)) return run_program(s, rd32(m + MS_ARB_REPORT), loc);
+    const u8 *aux = nfa + rd32(m + MC_AUX_OFFSET) + (size_t)st * MC_AUX_SIZE;
+    u32 off = rd32(aux + (eod ? MC_AUX_ACCEPT_EOD : MC_AUX_ACCEPT));
+    if (!off) return 0;
+    const u8 *rl = nfa + off;
+    for (u32 i = 0, n = rd32(rl); i < n; i++)
+        if (run_program(s, rd32(rl + 4 + 4 * (size_t)i), loc) < 0) return -1;
+    return 0;
+}
+
+static int mcsheng_scan(struct scan_state *s, const u8 *nfa) {
+    const int wide16 = nfa[NFA_TYPE] == 20;
+    const u8 *m = nfa + NFA_SIZE, *succ = m + MS_SIZE;
+    if (nfa[NFA_RACCEL]) { s->error = 1; return -1; }
+    const u32 as = m[MS_ALPHA_SHIFT], accept_limit = rd16(m + MS_ACCEPT_LIMIT_8), sheng_end = rd16(m + MS_SHENG_END);
+    const u32 sherman_limit = wide16 ? rd16(m + MS_SHERMAN_LIMIT) : 0xffffffffu;
+    const u8 *aux0 = nfa + rd32(m + MC_AUX_OFFSET);
+    u32 st = rd16(m + MC_START_ANCHORED);
+    for (u32 i = 0; i < s->len && st; i++) {
+        const u8 c = s->buf[i];
+        int accept;
+        if (st < sheng_end) {
+            const u32 v = m[MS_MASKS + 16 * (size_t)c + st - 1];
+            st = v == sheng_end - 1 ? 0 : v < sheng_end - 1 ? v + 1 : v;
+            accept = wide16 ? rd32(aux0 + (size_t)st * MC_AUX_SIZE + MC_AUX_ACCEPT) != 0 : st >= accept_limit;
+        } else {
+            const u32 cp = m[MS_REMAP + c];
+            if (wide16) {
+                u32 e;
+                if (st < sherman_limit) e = rd16(succ + 2 * (((size_t)(st - sheng_end) << as) + cp));
+                else {
+                    const u8 *sh = nfa + rd32(m + MC_SHERMAN_OFFSET) + 32 * (size_t)(st - sherman_limit);
+                    u32 len = sh[1], k;
+                    for (k = 0; k < len && sh[4 + k] != cp; k++) {}
+                    if (k < len) e = rd16(sh + 4 + len + 2 * k);
+                    else e = rd16(succ + 2 * (((size_t)(rd16(sh + 2) - sheng_end) << as) + cp));
+                }
+                accept = (e & 0x8000u) != 0;
+                st = e & 0x3fffu;
+            } else {
+                st = succ[((size_t)(st - sheng_end) << as) + cp];
+                accept = st >= accept_limit;
+            }
+        }
+        if (accept && ms_report(s, nfa, m, st, (u64)i + 1, 0) < 0) return -1;
+    }
+    s->cur_eod = 1;
+    if (st && (rd32(nfa + NFA_FLAGS) & NFA_ACCEPTS_EOD) && ms_report(s, nfa, m, st, s->len, 1) < 0) { s->cur_eod = 0; return -1; }
+    s->cur_eod = 0;
+    return 0;
+}
+
 static void engine_scan(struct scan_state *s, const u8 *nfa) {
     if (nfa[NFA_TYPE] == 6 || nfa[NFA_TYPE] == 7) mcclellan_scan(s, nfa);
+    else if (nfa[NFA_TYPE] == 19 || nfa[NFA_TYPE] == 20) mcsheng_scan(s, nfa);
     else if (nfa[NFA_TYPE] == 17 || nfa[NFA_TYPE] == 21 || nfa[NFA_TYPE] == 22) sheng_scan(s, nfa);
     else limex_scan(s, nfa);
 }

@@ -59,7 +59,7 @@ def test_refusals():
 
 
 # ---- McClellan DFA engine (mcclellan_internal.h), same acceptance: the unmodified runtime must scan it ----------
-@pytest.mark.parametrize("engine", [litdb.ENGINE_MCCLELLAN, litdb.ENGINE_MCCLELLAN_SHERMAN])
+@pytest.mark.parametrize("engine", [litdb.ENGINE_MCCLELLAN, litdb.ENGINE_MCCLELLAN_SHERMAN, litdb.ENGINE_MCSHENG])
 @pytest.mark.parametrize("seed", range(16))
 def test_mcclellan_random_sets_match_brute_force(ref, seed, engine):
     rng = random.Random(1000 + seed)
@@ -67,25 +67,26 @@ def test_mcclellan_random_sets_match_brute_force(ref, seed, engine):
     try:
         db = litdb.compile_regex_multi(ex, fl, ids, engine=engine)
     except litdb.CompileError as e:
-        assert "too large" in str(e)
+        assert "too large" in str(e) or "no Sheng region" in str(e)
         return
-    assert db.outfix_engine_type() in (6, 7)
+    assert db.outfix_engine_type() in ((19, 20) if engine == litdb.ENGINE_MCSHENG else (6, 7))
     texts = [regen.random_text(rng, ex, 140, smp) for _ in range(3)] + [b""]
     got = _scan_ref(ref, db, texts)
     for t, g in zip(texts, got):
         assert g == regen.brute_force(ex, fl, ids, t), (ex, fl, t)
 
 
-@pytest.mark.parametrize("engine", [litdb.ENGINE_MCCLELLAN, litdb.ENGINE_MCCLELLAN_SHERMAN])
+@pytest.mark.parametrize("engine", [litdb.ENGINE_MCCLELLAN, litdb.ENGINE_MCCLELLAN_SHERMAN, litdb.ENGINE_MCSHENG])
 def test_mcclellan_8_and_16_bit(ref, engine):
-    """<= 256 states -> McClellan8 (NFA.type 6), more -> McClellan16 (type 7); both accepted by nfa_api_dispatch.c."""
+    """<= 256 states -> McClellan8 (NFA.type 6), more -> McClellan16 (type 7); both accepted by nfa_api_dispatch.c.
+    McSheng (the hybrid the reference compiler prefers for DFAs too large for Sheng): types 19 / 20."""
     small = [b"abc", b"^GET /[^ ]*\\.php", b"x[0-9]{3}y"]
     big = [b"passwd\\s+[A-Za-z0-9_]{4,9}=", b"(login|admin)[^&]*&id=", b"User-Agent: [^\\r\\n]{8}", b"select.{1,12}from"]
     for ex, want in ((small, 6), (big, 7)):
         fl = [1 if k % 2 else 0 for k in range(len(ex))]
         ids = [10 + k for k in range(len(ex))]
         db = litdb.compile_regex_multi(ex, fl, ids, engine=engine)
-        assert db.outfix_engine_type() == want
+        assert db.outfix_engine_type() == (want + 13 if engine == litdb.ENGINE_MCSHENG else want)
         rng = random.Random(want)
         texts = [b"GET /a/b.php x123y abc PASSWD  user_1= login=1&id= select a,b from User-Agent: abcdefghij"] + \
                 [regen.random_text(rng, ex, 200) for _ in range(4)]
@@ -95,7 +96,7 @@ def test_mcclellan_8_and_16_bit(ref, engine):
 
 
 # ---- end-of-data accepts (\\z): LimEx acceptAtEOD / McClellan accept_eod, NFA_ACCEPTS_EOD (runtime.c:273-278) -----
-@pytest.mark.parametrize("engine", [litdb.ENGINE_LIMEX, litdb.ENGINE_MCCLELLAN, litdb.ENGINE_MCCLELLAN_SHERMAN])
+@pytest.mark.parametrize("engine", [litdb.ENGINE_LIMEX, litdb.ENGINE_MCCLELLAN, litdb.ENGINE_MCCLELLAN_SHERMAN, litdb.ENGINE_MCSHENG])
 @pytest.mark.parametrize("seed", range(10))
 def test_eod_patterns_match_brute_force(ref, seed, engine):
     rng = random.Random(3000 + seed)
@@ -104,7 +105,7 @@ def test_eod_patterns_match_brute_force(ref, seed, engine):
     try:
         db = litdb.compile_regex_multi(ex, fl, ids, engine=engine)
     except litdb.CompileError as e:
-        assert "too large" in str(e)
+        assert "too large" in str(e) or "no Sheng region" in str(e)
         return
     texts = []
     for k in range(6):
@@ -164,3 +165,52 @@ def test_sheng32_and_sheng64_match_brute_force(seed):
         rv, got = ref.scan(rdb, rs, t)
         assert rv == 0 and sorted(set(got), key=lambda x: (x[1], x[0])) == regen.brute_force(ex, fl, ids, t), (ex, fl, t)
         assert oracle_port.scan(db, t) == (0, got)
+
+
+# ---- McSheng hybrid (mcsheng_internal.h): the engine the reference compiler prefers for DFAs too large for Sheng ----
+@pytest.mark.parametrize("seed", range(12))
+def test_mcsheng_port_equals_reference_callback_order(ref, seed):
+    """McSheng8 / McSheng16 databases, single outfix and as the DFA engine of multi-engine databases: the C restatement
+    (oracle_port.c mcsheng_scan) raises the reference runtime's callbacks in the reference runtime's order."""
+    import oracle_port
+    rng = random.Random(8800 + seed)
+    ex, fl, ids, smp = regen.random_set(rng, rng.randint(2, 9), True)
+    if seed % 3 == 2:
+        ex = regen.with_eod(rng, ex, 0.4)
+    if seed % 2:
+        db = litdb.compile_regex_rose(ex, fl, ids, engine=litdb.ENGINE_MCSHENG, dfa_states=[40, 400, 2000][seed % 3])
+    else:
+        try:
+            db = litdb.compile_regex_multi(ex, fl, ids, engine=litdb.ENGINE_MCSHENG)
+        except litdb.CompileError as e:
+            assert "too large" in str(e) or "no Sheng region" in str(e)
+            return
+    rdb = ref.deserialize(db.serialize())
+    rs = ref.alloc_scratch(rdb)
+    n = 0
+    for k in range(12):
+        t = regen.random_text(rng, ex, rng.choice([0, 1, 9, 80, 500]), smp)
+        if smp and k % 3 == 0:
+            x = smp[k % len(smp)]
+            t = t[:max(0, len(t) - len(x))] + x
+        rv, got = ref.scan(rdb, rs, t)
+        assert rv == 0
+        assert sorted(set(got), key=lambda x: (x[1], x[0])) == regen.brute_force(ex, fl, ids, t)
+        assert oracle_port.scan(db, t) == (0, got)
+        n += len(got)
+    assert n > 0
+
+
+def test_mcsheng_engine_types_in_multi_engine_databases():
+    """With ENGINE_MCSHENG a multi-engine database holds Sheng engines for DFAs of at most 16 states and McSheng engines
+    (NFA.type 19 / 20) for the larger ones -- the order of getDfa (rose_build_bytecode.cpp)."""
+    ex = [b"abc", b"passwd\\s+[A-Za-z0-9_]{4,9}=", b"(login|admin)[^&]*&id=", b"User-Agent: [^\\r\\n]{8}", b"select.{1,12}from"]
+    db = litdb.compile_regex_rose(ex, [0] * 5, list(range(5)), engine=litdb.ENGINE_MCSHENG, dfa_states=300)
+    bc = db.bytecode()
+    nq = int.from_bytes(bc[156:160], "little")
+    info = int.from_bytes(bc[236:240], "little")
+    types = set()
+    for q in range(nq):
+        nfa = int.from_bytes(bc[info + 20 * q:info + 20 * q + 4], "little")
+        types.add(bc[nfa + 8])
+    assert types & {19, 20} and types <= {17, 19, 20, 6, 7}

@@ -1262,6 +1262,39 @@ void build_sheng_tables(const DbView &v, u32 at, std::vector<u8> &out, DevMcc &D
     D.arb_report = S.report; D.accepts_eod = (v.nfa_flags & nfa::ACCEPTS_EOD) ? 1u : 0u; D.in_smem = 1; D.has_sherman = 0;
 }
 
+// A McSheng engine (mcsheng_internal.h:63-88, mcsheng.c:150-322,368-420) is McClellan whose states below sheng_end step
+// through byte-shuffle masks and have no row in the successor table.  At upload the rows are made: row s of the region =
+// the mask bytes of one representative byte per symbol, translated to state ids (mask value sheng_end - 1 = dead,
+// below it id - 1, above it the id itself), with the accept flag of 16-bit entries taken from the successor's aux record
+// (the reference tests get_aux(s)->accept when the region is left, mcsheng.c:466); the rows of the other states are
+// the engine's own.  The result is a complete McClellan table behind the bytecode, stepped by k_mcclellan.
+void build_mcsheng_tables(const DbView &v, u32 at, std::vector<u8> &out, DevMcc &D) {
+    const DbView::Mcc &M = v.mcc;
+    const u32 rows = M.wide16 ? M.sherman_limit : M.states, ent = M.wide16 ? 2u : 1u, width = 1u << M.as;
+    out.assign((size_t)rows * width * ent, 0);
+    int rep[256];
+    for (int &x : rep) x = -1;
+    for (u32 c = 0; c < 256; c++) { const u32 cp = rd8(v.bc, M.remap_off + c); if (rep[cp] < 0) rep[cp] = (int)c; }
+    for (u32 st = 1; st < M.sheng_end; st++)
+        for (u32 cp = 0; cp < width; cp++) {
+            if (rep[cp] < 0) continue;  // no byte maps to this symbol (TOP)
+            const u32 mv = rd8(v.bc, M.masks_off + 16 * (u32)rep[cp] + st - 1);
+            u32 nx = mv == M.sheng_end - 1 ? 0u : mv < M.sheng_end - 1 ? mv + 1 : mv;
+            if (M.wide16 && rd32(v.bc, M.aux_off + nx * mcclellan::aux::SIZE + mcclellan::aux::accept)) nx |= mcclellan::ACCEPT_FLAG;
+            const size_t i = ((size_t)st << M.as) + cp;
+            if (M.wide16) { out[2 * i] = (u8)nx; out[2 * i + 1] = (u8)(nx >> 8); } else out[i] = (u8)nx;
+        }
+    std::memcpy(out.data() + ((size_t)M.sheng_end << M.as) * ent, v.bc + M.tab_off, M.tab_bytes);
+    D = DevMcc{};
+    D.tab_abs = at; D.tab_bytes = (u32)out.size(); D.remap_abs = M.remap_off;
+    D.nfa_abs = v.nfa_off; D.aux_abs = M.aux_off; D.sherman_abs = M.sherman_off;
+    D.wide16 = M.wide16; D.as = M.as; D.start = M.start; D.accept_limit_8 = M.accept_limit_8;
+    D.sherman_limit = M.sherman_limit; D.single = M.single; D.arb_report = M.arb_report;
+    D.accepts_eod = (v.nfa_flags & nfa::ACCEPTS_EOD) ? 1u : 0u;
+    D.in_smem = MCC_RM_BYTES + (size_t)D.tab_bytes + 8 <= MCC_SMEM_MAX ? 1u : 0u;
+    D.has_sherman = M.wide16 && M.sherman_limit < M.states ? 1u : 0u;
+}
+
 // Device tables of ONE outfix engine (im->view describes it; im->dev.bc is the uploaded bytecode it lives in).
 hs_error_t build_engine_image(hs_gpu_scratch *s, DbImage *im) {
     const DbView &v = im->view;
@@ -1282,14 +1315,14 @@ hs_error_t build_engine_image(hs_gpu_scratch *s, DbImage *im) {
         L.o_squash = t.o_squash; L.o_meta = t.o_meta; L.o_masks = t.o_masks; L.o_base = t.o_base;
         L.total_words = t.total_words; L.accept_abs = t.accept_abs; L.accept_eod_abs = t.accept_eod_abs;
         L.nfa_flags = t.nfa_flags;
-    } else if (v.kind == ENG_SHENG) {
-        // im->mcc was filled by build_sheng_tables above
+    } else if (v.kind == ENG_SHENG || (v.kind == ENG_MCCLELLAN && v.mcc.sheng_end)) {
+        // im->mcc was filled by build_sheng_tables / build_mcsheng_tables with the image
     } else if (v.kind == ENG_MCCLELLAN) {
         // the engine is stepped straight from the uploaded bytecode (mcclellan.cuh copies the table to shared memory)
         const DbView::Mcc &M = v.mcc;
         DevMcc &D = im->mcc;
         D = DevMcc{};
-        D.tab_abs = M.tab_off; D.tab_bytes = M.tab_bytes; D.remap_abs = M.m_off + (u32)mcclellan::remap;
+        D.tab_abs = M.tab_off; D.tab_bytes = M.tab_bytes; D.remap_abs = M.remap_off;
         D.nfa_abs = v.nfa_off; D.aux_abs = M.aux_off; D.sherman_abs = M.sherman_off;
         D.wide16 = M.wide16; D.as = M.as; D.start = M.start; D.accept_limit_8 = M.accept_limit_8;
         D.sherman_limit = M.sherman_limit; D.single = M.single; D.arb_report = M.arb_report;
@@ -1310,14 +1343,14 @@ hs_error_t build_dfa_packs(hs_gpu_scratch *s, DbImage *im) {
     auto packable = [&](size_t q) {
         const DbImage *e = im->subs[q];
         const DbView::Mcc &M = e->view.mcc;
-        return e->view.kind == ENG_MCCLELLAN && !e->mcc.has_sherman && !e->mcc.accepts_eod && M.states <= mcclellan::STATE_MASK;
+        return e->view.kind == ENG_MCCLELLAN && !M.sheng_end && !e->mcc.has_sherman && !e->mcc.accepts_eod && M.states <= mcclellan::STATE_MASK;
     };
     auto joint = [&](const std::vector<size_t> &members, std::vector<u32> &cls_of) {  // -> number of joint classes
         std::map<std::vector<u8>, u32> seen;
         cls_of.assign(256, 0);
         for (u32 c = 0; c < 256; c++) {
             std::vector<u8> sig;
-            for (size_t q : members) sig.push_back(rd8(im->view.bc, im->subs[q]->view.mcc.m_off + mcclellan::remap + c));
+            for (size_t q : members) sig.push_back(rd8(im->view.bc, im->subs[q]->view.mcc.remap_off + c));
             auto it = seen.find(sig);
             if (it == seen.end()) it = seen.emplace(sig, (u32)seen.size()).first;
             cls_of[c] = it->second;
@@ -1361,7 +1394,7 @@ hs_error_t build_dfa_packs(hs_gpu_scratch *s, DbImage *im) {
                 pk.dev.m[k] = e->mcc;
                 for (u32 st = 0; st < M.states; st++)
                     for (u32 j = 0; j < rep_of.size(); j++) {
-                        const u32 sym = rd8(im->view.bc, M.m_off + mcclellan::remap + rep_of[j]);
+                        const u32 sym = rd8(im->view.bc, M.remap_off + rep_of[j]);
                         u32 out;
                         if (M.wide16) {
                             const u32 en = rd16(im->view.bc, M.tab_off + 2 * (((size_t)st << M.as) + sym));
@@ -1427,13 +1460,16 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
     // (Sheng outfixes of a multi-engine database get their tables one behind the other in the same area.)
     std::vector<u8> derived;
     const u32 derived_at = (u32)round_up(v.bc_len, 256) + 256;
+    auto hybrid = [](const DbView &e) { return e.kind == ENG_MCCLELLAN && e.mcc.sheng_end != 0; };   // McSheng: rows made here too
     if (v.kind == ENG_SHENG) build_sheng_tables(v, derived_at, derived, im->mcc);
+    if (hybrid(v)) build_mcsheng_tables(v, derived_at, derived, im->mcc);
     std::vector<DevMcc> sub_sheng(v.engines.size());
     for (size_t q = 0; q < v.engines.size(); q++) {
-        if (v.engines[q].kind != ENG_SHENG) continue;
+        if (v.engines[q].kind != ENG_SHENG && !hybrid(v.engines[q])) continue;
         std::vector<u8> one;
         const u32 at = derived_at + (u32)round_up(derived.size(), 256);
-        build_sheng_tables(v.engines[q], at, one, sub_sheng[q]);
+        if (hybrid(v.engines[q])) build_mcsheng_tables(v.engines[q], at, one, sub_sheng[q]);
+        else build_sheng_tables(v.engines[q], at, one, sub_sheng[q]);
         derived.resize(at - derived_at, 0);
         derived.insert(derived.end(), one.begin(), one.end());
     }
@@ -1523,7 +1559,7 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
         sub->owns_bc = false;
         sub->dev = im->dev;
         im->subs.push_back(sub);
-        if (ev.kind == ENG_SHENG) sub->mcc = sub_sheng[im->subs.size() - 1];   // tables built with the image (above)
+        if (ev.kind == ENG_SHENG || hybrid(ev)) sub->mcc = sub_sheng[im->subs.size() - 1];   // tables built with the image (above)
         const hs_error_t erv = build_engine_image(s, sub);
         if (erv != HS_SUCCESS) { im->release(); delete im; return erv; }
         im->device_bytes += sub->device_bytes;

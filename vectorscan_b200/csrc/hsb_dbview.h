@@ -50,6 +50,8 @@ struct DbView {
     struct Mcc {
         u32 m_off = 0, tab_off = 0, tab_bytes = 0, aux_off = 0, sherman_off = 0;
         u32 wide16 = 0, as = 0, states = 0, start = 0, accept_limit_8 = 0, sherman_limit = 0, single = 0, arb_report = 0;
+        u32 remap_off = 0;                  // absolute offset of remap[256]
+        u32 sheng_end = 0, masks_off = 0;   // McSheng: first state outside the Sheng region, absolute offset of sheng_masks
     } mcc;
     // single-outfix Sheng DFA (kind == ENG_SHENG), absolute bytecode offsets
     struct Sheng { u32 sh_off = 0, aux_off = 0, n_states = 0, anchored = 0, flags = 0, report = 0, nfa_type = 17; } sheng;
@@ -156,31 +158,41 @@ inline int census_program(const DbView &d, u32 prog, std::string &why, u32 &max_
 // per-state report lists, EOD accepts.  Refused: wide states (has_wide).  Accel structures are skip-ahead only.
 inline int parse_mcclellan(DbView &d, std::string &why) {
     namespace mc = mcclellan;
+    namespace ms = mcsheng;
     const u8 *r = d.bc;
     const u8 *n = r + d.nfa_off;
     DbView::Mcc &M = d.mcc;
-    if (d.nfa_len < nfa::SIZE + mc::SIZE) { why = "McClellan truncated"; return E_INVALID; }
+    // McSheng (types 19 / 20) is McClellan with another header and a Sheng region in front (hsb_layout.h)
+    const u8 type = rd8(n, nfa::type);
+    const bool hybrid = type == nfa::MCSHENG_8 || type == nfa::MCSHENG_16;
+    const size_t HDR = hybrid ? ms::SIZE : mc::SIZE;
+    auto F = [&](size_t plain, size_t hyb) { return hybrid ? hyb : plain; };
+    if (d.nfa_len < nfa::SIZE + HDR) { why = "McClellan truncated"; return E_INVALID; }
     M.m_off = d.nfa_off + (u32)nfa::SIZE;
     const u8 *m = r + M.m_off;
     auto n_range = [&](size_t off, size_t len) { return off <= d.nfa_len && len <= d.nfa_len - off; };  // relative to NFA
-    M.wide16 = rd8(n, nfa::type) == nfa::MCCLELLAN_16;
-    if (rd8(m, mc::has_wide)) { why = "McClellan wide states are not supported yet"; return E_ARCH; }
-    M.as = rd8(m, mc::alphaShift);
+    M.wide16 = type == nfa::MCCLELLAN_16 || type == nfa::MCSHENG_16;
+    if (!hybrid && rd8(m, mc::has_wide)) { why = "McClellan wide states are not supported yet"; return E_ARCH; }
+    M.as = rd8(m, F(mc::alphaShift, ms::alphaShift));
     M.states = rd16(m, mc::state_count);
     M.start = rd16(m, mc::start_anchored);
-    M.accept_limit_8 = rd16(m, mc::accept_limit_8);
-    M.sherman_limit = M.wide16 ? rd16(m, mc::sherman_limit) : M.states;
-    M.single = (rd8(m, mc::flags) & mc::FLAG_SINGLE) ? 1 : 0;
-    M.arb_report = rd32(m, mc::arb_report);
+    M.accept_limit_8 = rd16(m, F(mc::accept_limit_8, ms::accept_limit_8));
+    M.sherman_limit = M.wide16 ? rd16(m, F(mc::sherman_limit, ms::sherman_limit)) : M.states;
+    M.single = (rd8(m, F(mc::flags, ms::flags)) & mc::FLAG_SINGLE) ? 1 : 0;
+    M.arb_report = rd32(m, F(mc::arb_report, ms::arb_report));
+    M.remap_off = M.m_off + (u32)F(mc::remap, ms::remap);
+    M.sheng_end = hybrid ? rd16(m, ms::sheng_end) : 0;
+    M.masks_off = hybrid ? M.m_off + (u32)ms::sheng_masks : 0;
     if (M.as > 8 || !M.states || M.start >= M.states || M.sherman_limit > M.states) { why = "McClellan header inconsistent"; return E_INVALID; }
     if (M.wide16 && M.states - 1 > mc::STATE_MASK) { why = "McClellan state count out of range"; return E_INVALID; }
     if (!M.wide16 && (M.states > 256 || M.accept_limit_8 > M.states)) { why = "McClellan8 limits out of range"; return E_INVALID; }
-    const u32 rows = M.wide16 ? M.sherman_limit : M.states;
-    M.tab_off = M.m_off + (u32)mc::SIZE;
+    if (hybrid && (M.sheng_end < 2 || M.sheng_end > ms::MAX_SHENG_STATES + 1 || M.sheng_end > M.sherman_limit)) { why = "McSheng region out of range"; return E_INVALID; }
+    const u32 rows = (M.wide16 ? M.sherman_limit : M.states) - M.sheng_end;   // the table has no rows for the Sheng region
+    M.tab_off = M.m_off + (u32)HDR;
     M.tab_bytes = (rows << M.as) * (M.wide16 ? 2u : 1u);
-    if (!n_range(nfa::SIZE + mc::SIZE, M.tab_bytes)) { why = "McClellan successor table truncated"; return E_INVALID; }
+    if (!n_range(nfa::SIZE + HDR, M.tab_bytes)) { why = "McClellan successor table truncated"; return E_INVALID; }
     for (u32 c = 0; c < 256; c++)
-        if (rd8(m, mc::remap + c) >= (1u << M.as)) { why = "McClellan remap out of range"; return E_INVALID; }
+        if (rd8(r, M.remap_off + c) >= (1u << M.as)) { why = "McClellan remap out of range"; return E_INVALID; }
     const u32 aux_rel = rd32(m, mc::aux_offset);
     if (!n_range(aux_rel, (size_t)M.states * mc::aux::SIZE)) { why = "McClellan aux array truncated"; return E_INVALID; }
     M.aux_off = d.nfa_off + aux_rel;
@@ -188,6 +200,14 @@ inline int parse_mcclellan(DbView &d, std::string &why) {
     for (u32 i = 0; i < (rows << M.as); i++) {
         const u32 e = M.wide16 ? (rd16(r, M.tab_off + 2 * (size_t)i) & mc::STATE_MASK) : rd8(r, M.tab_off + i);
         if (e >= M.states) { why = "McClellan successor out of range"; return E_INVALID; }
+    }
+    if (hybrid) {
+        // mask byte: < sheng_end - 1 a region state (id - 1), == sheng_end - 1 dead, above it a state id outside the region
+        for (u32 c = 0; c < 256; c++)
+            for (u32 sid = 0; sid + 1 < M.sheng_end; sid++)
+                if (rd8(r, M.masks_off + 16 * c + sid) >= M.states) { why = "McSheng mask successor out of range"; return E_INVALID; }
+        for (u32 st = 1; st < M.sheng_end; st++)
+            if (rd32(r, M.aux_off + st * mc::aux::SIZE + mc::aux::accept)) { why = "McSheng region state with reports"; return E_INVALID; }
     }
     if (M.wide16 && M.sherman_limit < M.states) {
         const u32 sh_rel = rd32(m, mc::sherman_offset);
@@ -197,7 +217,8 @@ inline int parse_mcclellan(DbView &d, std::string &why) {
         for (size_t k = 0; k < nsh; k++) {
             const u8 *sh = r + M.sherman_off + k * mc::SHERMAN_FIXED_SIZE;
             const u32 len = sh[mc::SHERMAN_LEN_OFFSET];
-            if (sh[0] != mc::SHERMAN_STATE || len > mc::MAX_SHERMAN_LIST_LEN || rd16(sh, mc::SHERMAN_DADDY_OFFSET) >= M.sherman_limit) {
+            const u32 daddy = rd16(sh, mc::SHERMAN_DADDY_OFFSET);
+            if (sh[0] != mc::SHERMAN_STATE || len > mc::MAX_SHERMAN_LIST_LEN || daddy >= M.sherman_limit || daddy < M.sheng_end) {
                 why = "McClellan Sherman state malformed"; return E_INVALID;
             }
             for (u32 q = 0; q < len; q++)
@@ -409,9 +430,11 @@ inline int parse_outfix_at(DbView &d, u32 info_off, std::string &why) {
     d.limex_type = rd8(n, nfa::type);
     if (!in_range(d, d.nfa_off, d.nfa_len)) { why = "NFA runs past the bytecode"; return E_INVALID; }
     if (rd8(n, nfa::rAccelType)) { why = "reverse acceleration is not supported"; return E_ARCH; }
-    if (d.limex_type == nfa::MCCLELLAN_8 || d.limex_type == nfa::MCCLELLAN_16) return parse_mcclellan(d, why);
+    if (d.limex_type == nfa::MCCLELLAN_8 || d.limex_type == nfa::MCCLELLAN_16 || d.limex_type == nfa::MCSHENG_8 ||
+        d.limex_type == nfa::MCSHENG_16)
+        return parse_mcclellan(d, why);
     if (d.limex_type == nfa::SHENG || d.limex_type == nfa::SHENG_32 || d.limex_type == nfa::SHENG_64) return parse_sheng(d, why);
-    if (d.limex_type > nfa::LIMEX_512) { why = "outfix engine type " + std::to_string(d.limex_type) + " (not LimEx, McClellan or Sheng) is not supported yet"; return E_ARCH; }
+    if (d.limex_type > nfa::LIMEX_512) { why = "outfix engine type " + std::to_string(d.limex_type) + " (not LimEx, McClellan, McSheng or Sheng) is not supported yet"; return E_ARCH; }
     const limex::Layout L = limex::layout(d.limex_type);
     if (d.nfa_len < nfa::SIZE + L.SIZE) { why = "LimEx truncated"; return E_INVALID; }
     d.limex_off = d.nfa_off + (u32)nfa::SIZE;

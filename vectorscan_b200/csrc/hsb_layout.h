@@ -228,7 +228,7 @@ constexpr size_t flags = 0, length = 4, type = 8, rAccelType = 9, rAccelOffset =
                  rAccelData = 12, queueIndex = 16, nPositions = 20, scratchStateSize = 24, streamStateSize = 28,
                  maxWidth = 32, minWidth = 36, maxOffset = 40, SIZE = 64;
 constexpr u8 LIMEX_32 = 0, LIMEX_64 = 1, LIMEX_128 = 2, LIMEX_256 = 3, LIMEX_384 = 4, LIMEX_512 = 5;
-constexpr u8 MCCLELLAN_8 = 6, MCCLELLAN_16 = 7, SHENG = 17, SHENG_32 = 21, SHENG_64 = 22;
+constexpr u8 MCCLELLAN_8 = 6, MCCLELLAN_16 = 7, SHENG = 17, MCSHENG_8 = 19, MCSHENG_16 = 20, SHENG_32 = 21, SHENG_64 = 22;
 constexpr u32 ACCEPTS_EOD = 1, ZOMBIE = 2;
 }
 namespace nfainfo {  // struct NfaInfo
@@ -248,6 +248,19 @@ constexpr u32 ACCEPT_FLAG = 0x8000, ACCEL_FLAG = 0x4000, STATE_MASK = 0x3fff;
 constexpr u32 SHERMAN_STATE = 1, SHERMAN_FIXED_SIZE = 32, SHERMAN_LEN_OFFSET = 1, SHERMAN_DADDY_OFFSET = 2,
               SHERMAN_CHARS_OFFSET = 4, MAX_SHERMAN_LIST_LEN = 9;
 namespace aux { constexpr size_t accept = 0, accept_eod = 4, top = 8, accel_offset = 12, SIZE = 16; }
+}
+// struct mcsheng (src/nfa/mcsheng_internal.h:63-88): a McClellan DFA whose states 1 .. sheng_end - 1 (at most 16, none of
+// them accepting) step through 256 byte-shuffle masks instead of the successor table: sheng_masks[c][s - 1] is the
+// successor of state s on byte c, written as id - 1 for a state of the region, sheng_end - 1 for the dead state, and the
+// state's own id (which must fit a byte) for a state outside the region.  The successor table that follows covers the
+// states >= sheng_end only, indexed by id - sheng_end (mcsheng.c:380-388); mstate_aux[], report lists and Sherman states
+// are McClellan's (namespace mcclellan).
+namespace mcsheng {
+constexpr size_t state_count = 0, length = 4, start_anchored = 8, start_floating = 10, aux_offset = 12,
+                 sherman_offset = 16, sherman_end = 20, sheng_end = 24, sheng_accel_limit = 26, accel_limit_8 = 28,
+                 accept_limit_8 = 30, sherman_limit = 32, alphaShift = 34, flags = 35, has_accel = 36, remap = 37,
+                 arb_report = 296, accel_offset = 300, sheng_masks = 304, SIZE = 4400;
+constexpr u32 MAX_SHENG_STATES = 16;
 }
 // struct sheng (src/nfa/sheng_internal.h:68-79): a DFA of at most 16 states as 256 byte-shuffle masks; mask[c][s] is
 // the successor of state s on byte c with flag bits (accept / dead / accel) beside the 4-bit state id.  sstate_aux[]

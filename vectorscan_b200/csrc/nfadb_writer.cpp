@@ -677,6 +677,161 @@ int emit_mcclellan(const Dfa &d, const u8 *reach_map, const std::vector<u32> &pr
 }
 
 
+// Lay the DFA out as the reference's McSheng hybrid (struct NFA + struct mcsheng + successor table of the states outside
+// the Sheng region + mstate_aux[] + report lists), the engine the reference compiler tries for every DFA too large for a
+// pure Sheng (getDfa, src/rose/rose_build_bytecode.cpp: shengCompile, then mcshengCompile, then mcclellanCompile).
+// Format: mcsheng_compile.cpp:155-204 (masks), :372-430 / :1266-1307 (ids), :1007-1084 / :1310-1360 (sizes).
+// The region: breadth first from the start state over non-accepting states ("cannot raise callbacks from sheng
+// region", mcsheng_compile.cpp:582-586), at most 16; in a 16-bit engine every state entered straight from the region
+// must have an id that fits the mask byte, so those states are numbered first and the region shrinks until they fit.
+// No Sherman states.  Fails (caller falls back to McClellan) when the start state itself accepts.
+int emit_mcsheng(const Dfa &d, const u8 *reach_map, const std::vector<u32> &program_of, u32 min_width, Buf &eng,
+                 u32 &state_bytes, std::string &err) {
+    namespace mc = mcclellan;
+    namespace ms = mcsheng;
+    const u32 n = (u32)d.next.size();
+    const u32 alpha = d.n_sym + 1;  // + TOP
+    u32 as = 0;
+    while ((1u << as) < alpha) as++;
+    const bool wide16 = n > 256;
+    if (n - 1 > mc::STATE_MASK) { err = "DFA too large for a McSheng engine (" + std::to_string(n) + " states)"; return HSB_LIT_COMPILER_ERROR; }
+    state_bytes = wide16 ? 2 : 1;
+    const u32 start = d.start_anchored ? d.start_anchored : d.start_floating;
+    std::vector<u32> region;
+    std::vector<u8> in_region(n, 0), is_succ(n, 0);
+    for (u32 cap = ms::MAX_SHENG_STATES; cap >= 1; cap--) {
+        region.clear();
+        std::fill(in_region.begin(), in_region.end(), 0);
+        std::fill(is_succ.begin(), is_succ.end(), 0);
+        std::vector<u32> queue{start};
+        std::vector<u8> seen(n, 0);
+        seen[0] = 1;
+        seen[start] = 1;
+        for (size_t h = 0; h < queue.size() && region.size() < cap; h++) {
+            const u32 q = queue[h];
+            if (!d.reports[q].empty()) continue;
+            region.push_back(q);
+            in_region[q] = 1;
+            for (u32 k = 0; k < d.n_sym; k++) { const u32 t = d.next[q][k]; if (!seen[t]) { seen[t] = 1; queue.push_back(t); } }
+        }
+        u32 n_succ = 0;
+        for (u32 q : region)
+            for (u32 k = 0; k < d.n_sym; k++) { const u32 t = d.next[q][k]; if (t && !in_region[t] && !is_succ[t]) { is_succ[t] = 1; n_succ++; } }
+        if (!wide16 || region.size() + 1 + n_succ <= 256) break;
+    }
+    if (region.empty()) { err = "no Sheng region: the start state accepts"; return HSB_LIT_COMPILER_ERROR; }
+    const u32 sheng_end = (u32)region.size() + 1;
+    // ---- implementation ids: dead 0, region 1 .., then (16-bit) region successors, the rest; (8-bit) non-accepting, accepting ----
+    std::vector<u32> impl(n, 0);
+    for (u32 i = 0; i < region.size(); i++) impl[region[i]] = i + 1;
+    u32 j = sheng_end, accel_limit_8 = 0, accept_limit_8 = 0;
+    if (wide16) {
+        for (u32 i = 1; i < n; i++) if (!in_region[i] && is_succ[i]) impl[i] = j++;
+        for (u32 i = 1; i < n; i++) if (!in_region[i] && !is_succ[i]) impl[i] = j++;
+    } else {
+        for (u32 i = 1; i < n; i++) if (!in_region[i] && d.reports[i].empty()) impl[i] = j++;
+        accel_limit_8 = accept_limit_8 = j;
+        for (u32 i = 1; i < n; i++) if (!in_region[i] && !d.reports[i].empty()) impl[i] = j++;
+    }
+    // ---- report lists ----
+    std::map<std::vector<u32>, u32> list_id;
+    std::vector<std::vector<u32>> lists;
+    std::vector<u32> list_of(n, ~0u), list_eod_of(n, ~0u);
+    std::set<u32> all_reports;
+    bool any_eod = false;
+    auto intern = [&](const std::vector<u32> &pis) {
+        std::set<u32> ps;
+        for (u32 pi : pis) ps.insert(program_of[pi]);
+        std::vector<u32> l(ps.begin(), ps.end());
+        all_reports.insert(l.begin(), l.end());
+        auto it = list_id.find(l);
+        if (it == list_id.end()) { it = list_id.emplace(l, (u32)lists.size()).first; lists.push_back(l); }
+        return it->second;
+    };
+    for (u32 i = 0; i < n; i++) {
+        if (!d.reports[i].empty()) list_of[i] = intern(d.reports[i]);
+        if (!d.reports_eod[i].empty()) { list_eod_of[i] = intern(d.reports_eod[i]); any_eod = true; }
+    }
+    const bool single = all_reports.size() == 1;
+    // ---- sizes ----
+    const size_t ent = wide16 ? 2 : 1;
+    const u32 n_normal = n - sheng_end;
+    const size_t tran_size = ((size_t)1 << as) * ent * n_normal;
+    const size_t aux_size = mc::aux::SIZE * (size_t)n;
+    const size_t aux_offset = round_up(nfa::SIZE + ms::SIZE + tran_size, 16);
+    size_t rl_size = 0;
+    for (auto &l : lists) rl_size += 4 + 4 * l.size();
+    const size_t accel_offset = round_up(aux_offset + aux_size + rl_size, 32);
+    const size_t sherman_offset = round_up(accel_offset, 16);
+    const size_t total = sherman_offset;
+    eng.grow(total);
+    eng.align(CACHELINE);
+    u8 *nh = eng.at(0), *m = eng.at(nfa::SIZE);
+    wr32(nh, nfa::flags, any_eod ? nfa::ACCEPTS_EOD : 0);
+    wr32(nh, nfa::length, (u32)eng.size());
+    wr8(nh, nfa::type, wide16 ? nfa::MCSHENG_16 : nfa::MCSHENG_8);
+    wr32(nh, nfa::queueIndex, 0);
+    wr32(nh, nfa::nPositions, n);
+    wr32(nh, nfa::scratchStateSize, state_bytes);
+    wr32(nh, nfa::streamStateSize, state_bytes);
+    wr32(nh, nfa::maxWidth, 0);
+    wr32(nh, nfa::minWidth, min_width);
+    wr16(m, ms::state_count, (u16)n);
+    wr32(m, ms::length, (u32)eng.size());
+    wr16(m, ms::start_anchored, (u16)impl[d.start_anchored]);
+    wr16(m, ms::start_floating, (u16)impl[d.start_floating]);
+    wr32(m, ms::aux_offset, (u32)aux_offset);
+    wr32(m, ms::sherman_offset, wide16 ? (u32)sherman_offset : 0);
+    wr32(m, ms::sherman_end, wide16 ? (u32)total : 0);
+    wr16(m, ms::sheng_end, (u16)sheng_end);
+    wr16(m, ms::sheng_accel_limit, (u16)(sheng_end - 1));  // no accelerable Sheng state
+    wr16(m, ms::accel_limit_8, (u16)accel_limit_8);
+    wr16(m, ms::accept_limit_8, (u16)accept_limit_8);
+    wr16(m, ms::sherman_limit, wide16 ? (u16)n : 0);
+    wr8(m, ms::alphaShift, (u8)as);
+    wr8(m, ms::flags, single ? mc::FLAG_SINGLE : 0);
+    wr8(m, ms::has_accel, 0);
+    std::memcpy(m + ms::remap, reach_map, 256);
+    wr32(m, ms::arb_report, all_reports.empty() ? 0 : *all_reports.begin());
+    wr32(m, ms::accel_offset, (u32)(accel_offset - nfa::SIZE));
+    // shuffle masks, one per byte value (createShuffleMasks)
+    for (u32 c = 0; c < 256; c++) {
+        u8 *mask = m + ms::sheng_masks + 16 * (size_t)c;
+        for (u32 sid = 0; sid < region.size(); sid++) {
+            const u32 t = impl[d.next[region[sid]][reach_map[c]]];
+            mask[sid] = (u8)(t == 0 ? sheng_end - 1 : t < sheng_end ? t - 1 : t);
+        }
+    }
+    std::vector<u32> list_off(lists.size());
+    {
+        size_t o = aux_offset + aux_size;
+        for (size_t i = 0; i < lists.size(); i++) {
+            list_off[i] = (u32)o;
+            wr32(eng.at(o), 0, (u32)lists[i].size());
+            for (size_t k = 0; k < lists[i].size(); k++) wr32(eng.at(o), 4 + 4 * k, lists[i][k]);
+            o += 4 + 4 * lists[i].size();
+        }
+    }
+    u8 *succ = m + ms::SIZE;
+    for (u32 i = 0; i < n; i++) {
+        const u32 id = impl[i];
+        u8 *a = eng.at(aux_offset + mc::aux::SIZE * (size_t)id);
+        wr32(a, mc::aux::accept, list_of[i] == ~0u ? 0 : list_off[list_of[i]]);
+        wr32(a, mc::aux::accept_eod, list_eod_of[i] == ~0u ? 0 : list_off[list_eod_of[i]]);
+        wr16(a, mc::aux::top, (u16)impl[d.start_floating]);
+        wr32(a, mc::aux::accel_offset, 0);
+        if (id < sheng_end) continue;  // dead and region states have no row
+        for (u32 k = 0; k < d.n_sym; k++) {
+            const size_t at = ((size_t)(id - sheng_end) << as) + k;
+            const u32 t = d.next[i][k];
+            if (wide16) wr16(succ, 2 * at, (u16)(impl[t] | (d.reports[t].empty() ? 0 : mc::ACCEPT_FLAG)));
+            else succ[at] = (u8)impl[t];
+        }
+    }
+    return HSB_LIT_SUCCESS;
+}
+
+
 // Lay a DFA of at most 16 states out as the reference's Sheng engine (struct NFA + struct sheng + sstate_aux[] +
 // report lists), following shengcompile.cpp:337-358 (state byte = id | flags), :420-444 (header), :560-578 (masks)
 // and :640-698 (region order and sizes).  State ids are the DFA's own (dead = 0).
@@ -1022,7 +1177,15 @@ int emit_engine(const Automaton &am, unsigned engine, const std::vector<u32> &pr
     // outfix engines of multi-engine databases: a DFA of at most 16 states is laid out as a Sheng engine, which is what the
     // reference compiler tries first for every DFA (shengCompile before mcclellanCompile, src/rose/rose_build_bytecode.cpp
     // buildOutfix / getDfa)
-    if (sheng_if_small && engine == HSB_REGEX_ENGINE_MCCLELLAN && dfa.next.size() <= 16) engine = HSB_REGEX_ENGINE_SHENG;
+    if (sheng_if_small && (engine == HSB_REGEX_ENGINE_MCCLELLAN || engine == HSB_REGEX_ENGINE_MCSHENG) && dfa.next.size() <= 16)
+        engine = HSB_REGEX_ENGINE_SHENG;
+    if (engine == HSB_REGEX_ENGINE_MCSHENG) {
+        const int mrv = emit_mcsheng(dfa, reach_map, program_of, am.min_width, eng, stream_state, err);
+        scratch_state = stream_state;
+        if (mrv == HSB_LIT_SUCCESS || !sheng_if_small) return mrv;
+        engine = HSB_REGEX_ENGINE_MCCLELLAN;  // no region (the start state accepts): plain McClellan, as getDfa falls through
+        err.clear();
+    }
     const int rv = engine == HSB_REGEX_ENGINE_SHENG || engine == HSB_REGEX_ENGINE_SHENG_WIDE
                        ? emit_sheng(dfa, reach_map, program_of, am.min_width, eng, stream_state, err, engine == HSB_REGEX_ENGINE_SHENG_WIDE)
                        : emit_mcclellan(dfa, reach_map, program_of, engine == HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN, am.min_width, eng, stream_state, err);
@@ -1035,7 +1198,7 @@ int emit_engine(const Automaton &am, unsigned engine, const std::vector<u32> &pr
 namespace hsb_nfadb {
 
 int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &image, std::string &err) {
-    if (engine > HSB_REGEX_ENGINE_SHENG_WIDE) { err = "unknown engine"; return HSB_LIT_COMPILER_ERROR; }
+    if (engine > HSB_REGEX_ENGINE_MCSHENG) { err = "unknown engine"; return HSB_LIT_COMPILER_ERROR; }
     if (pats.empty()) { err = "no expressions"; return HSB_LIT_COMPILER_ERROR; }
     // ---- 1. parse every pattern, build one automaton -------------------------------------------------
     std::vector<Parsed> parsed;
@@ -1170,8 +1333,9 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
 // construction fails (src/nfagraph/ng_limex.cpp / ng_mcclellan.cpp state limits).
 int build_outfix_engines(const std::vector<Pattern> &pats, unsigned engine, u32 dfa_states,
                          const std::vector<u32> &program_of, std::vector<EngineBlob> &out, std::string &err) {
-    if (engine != HSB_REGEX_ENGINE_LIMEX && engine != HSB_REGEX_ENGINE_MCCLELLAN && engine != HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN) {
-        err = "outfix engines are LimEx or McClellan";
+    if (engine != HSB_REGEX_ENGINE_LIMEX && engine != HSB_REGEX_ENGINE_MCCLELLAN && engine != HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN &&
+        engine != HSB_REGEX_ENGINE_MCSHENG) {
+        err = "outfix engines are LimEx, McClellan or McSheng";
         return HSB_LIT_COMPILER_ERROR;
     }
     if (pats.empty()) { err = "no expressions"; return HSB_LIT_COMPILER_ERROR; }
