@@ -177,6 +177,20 @@ int hs_gpu_accel_stage(const uint8_t *buf, size_t len);
 long long hs_gpu_accel_search_staged(int kind, const uint8_t *masks, uint8_t c1, uint8_t c2, int nocase, int reverse,
                                      int repeats, float *kernel_ms);
 
+/* hs_gpu_shufti without any device allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same search, same masks, same return convention as hs_gpu_shufti (*result = offset of the first byte in
+ * the class, `len` if none; reverse: offset of the last, -1 if none); `buf` is host memory.  The scratch the search needs
+ * (result cell, class table, staged copy of the data) is a fixed file-scope device array of HS_GPU_NOALLOC_MAX_BYTES +
+ * 1328 bytes that every GPU loading the library holds until the process exits; the call makes no cudaMalloc / cudaFree /
+ * allocating library call.  len > HS_GPU_NOALLOC_MAX_BYTES -> HS_INSUFFICIENT_SPACE (and a line on stderr); no usable
+ * device or cudaGetSymbolAddress failure -> HS_ARCH_ERROR.  Every call shares the one array (it keeps the previous call's
+ * contents; each call rewrites what it reads): calls are serialised inside the process and finish before returning, and
+ * anything that made two of them overlap on the GPU would race on it. */
+#define HS_GPU_NOALLOC_MAX_BYTES (1u << 20)
+hs_error_t hs_gpu_shufti_noalloc(const uint8_t lo[16], const uint8_t hi[16], const uint8_t *buf, size_t len, int reverse,
+                                 long long *result);
+
 #ifdef __cplusplus
 }
 #endif

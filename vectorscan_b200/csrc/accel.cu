@@ -14,7 +14,9 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <cstdio>
 #include <cstring>
+#include <mutex>
 
 namespace {
 
@@ -354,6 +356,40 @@ ClassParams make_params(int kind, const uint8_t *m1, const uint8_t *m2, const ui
     return p;
 }
 
+// ---- hs_gpu_shufti_noalloc: the same search with NO device allocation (no counterpart in the reference) ---------------
+// Everything hs_gpu_shufti keeps in its cudaMalloc'ed workspace -- the result cell, the 256-entry class table, the staged
+// and padded copy of the data -- lives in ONE file-scope device array of fixed size, so a caller that may not allocate
+// (under CUDA graph capture, inside a serving loop, in a harness that forbids cudaMalloc) can still search.  Every GPU
+// that loads libhs_gpu.so holds the array until the process exits.  In host code `g_noalloc_scratch` is only the
+// host-side stand-in of the symbol: its device address comes from cudaGetSymbolAddress, once per device, with that device
+// current, and that address is what the kernel is given.
+constexpr size_t NA_RES_OFF = 0, NA_TAB_OFF = 256, NA_TEXT_OFF = 256 + 1024;
+constexpr size_t NA_PAD = 48;  // data padded to a multiple of 16 + 32 zero bytes, as stage() does
+constexpr size_t NA_BYTES = NA_TEXT_OFF + HS_GPU_NOALLOC_MAX_BYTES + NA_PAD;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NA_BYTES];
+
+constexpr int NA_MAX_DEVICES = 64;
+std::mutex g_noalloc_mutex;                       // one search at a time per process: every call shares the array
+unsigned char *g_noalloc_ptr[NA_MAX_DEVICES];     // device address of g_noalloc_scratch on device d (nullptr: not asked yet)
+
+// device address of the scratch array on the CURRENT device (asked once per device)
+int noalloc_scratch(unsigned char **out) {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= NA_MAX_DEVICES) { cudaGetLastError(); return HS_ARCH_ERROR; }
+    if (!g_noalloc_ptr[dev]) {
+        void *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) {
+            std::fprintf(stderr, "hs_gpu_shufti_noalloc: cudaGetSymbolAddress failed on device %d: %s\n", dev, cudaGetErrorString(e));
+            cudaGetLastError();
+            return HS_ARCH_ERROR;
+        }
+        g_noalloc_ptr[dev] = static_cast<unsigned char *>(p);
+    }
+    *out = g_noalloc_ptr[dev];
+    return HS_SUCCESS;
+}
+
 }  // namespace
 
 extern "C" {
@@ -410,6 +446,54 @@ long long hs_gpu_accel_search_staged(int kind, const uint8_t *masks, uint8_t c1,
     const ClassParams p = make_params(kind, masks, masks ? masks + 16 : nullptr, masks ? masks + 32 : nullptr,
                                       masks ? masks + 48 : nullptr, c1, c2, nocase);
     return search_staged(p, reverse != 0, repeats, kernel_ms);
+}
+
+// shuftiExec / rshuftiExec (src/nfa/shufti.h) with no device allocation: see the comment at g_noalloc_scratch.  `buf` is
+// host memory, *result receives what hs_gpu_shufti returns.  Calls are serialised inside the process and complete before
+// they return; the array keeps the last call's contents, so the result cell, the table and the padding behind the data
+// are rewritten by every call.
+hs_error_t hs_gpu_shufti_noalloc(const uint8_t lo[16], const uint8_t hi[16], const uint8_t *buf, size_t len, int reverse,
+                                 long long *result) {
+    if (!lo || !hi || !result || (!buf && len)) return HS_INVALID;
+    if (len > HS_GPU_NOALLOC_MAX_BYTES) {
+        std::fprintf(stderr, "hs_gpu_shufti_noalloc: %zu bytes exceed the fixed scratch of %u bytes (HS_GPU_NOALLOC_MAX_BYTES)\n",
+                     len, (unsigned)HS_GPU_NOALLOC_MAX_BYTES);
+        return HS_INSUFFICIENT_SPACE;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { cudaGetLastError(); return HS_ARCH_ERROR; }
+    if (!len) { *result = reverse ? -1 : 0; return HS_SUCCESS; }
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    unsigned char *base = nullptr;
+    const int rv = noalloc_scratch(&base);
+    if (rv != HS_SUCCESS) return rv;
+    unsigned long long *d_res = reinterpret_cast<unsigned long long *>(base + NA_RES_OFF);
+    unsigned *d_tab = reinterpret_cast<unsigned *>(base + NA_TAB_OFF);
+    unsigned char *d_text = base + NA_TEXT_OFF;
+    unsigned tab[256];
+    for (unsigned c = 0; c < 256; c++) tab[c] = (lo[c & 15] & hi[c >> 4]) != 0 ? 1u : 0u;
+    const size_t padded = (len + 15) / 16 * 16 + 32;
+    const unsigned long long init = reverse ? 0ull : (unsigned long long)len;
+    if (cudaMemcpy(d_res, &init, 8, cudaMemcpyHostToDevice) != cudaSuccess ||
+        cudaMemcpy(d_tab, tab, sizeof(tab), cudaMemcpyHostToDevice) != cudaSuccess ||
+        cudaMemcpy(d_text, buf, len, cudaMemcpyHostToDevice) != cudaSuccess ||
+        cudaMemset(d_text + len, 0, padded - len) != cudaSuccess) {
+        cudaGetLastError();
+        return HS_UNKNOWN_ERROR;
+    }
+    const unsigned long long chunks = (len + 15) / 16;
+    const unsigned long long tiles = (chunks + CS_TILE_CHUNKS - 1) / CS_TILE_CHUNKS;
+    const unsigned long long want = (tiles + (CS_THREADS / 32) * 4 - 1) / ((CS_THREADS / 32) * 4);
+    const unsigned grid = (unsigned)(want < 1 ? 1 : want > 148 * 6 ? 148 * 6 : want);
+    if (reverse) k_class_scan<true, 0><<<grid, CS_THREADS>>>(d_text, len, d_tab, d_res);
+    else k_class_scan<false, 0><<<grid, CS_THREADS>>>(d_text, len, d_tab, d_res);
+    unsigned long long res = 0;
+    if (cudaGetLastError() != cudaSuccess || cudaMemcpy(&res, d_res, 8, cudaMemcpyDeviceToHost) != cudaSuccess) {
+        cudaGetLastError();
+        return HS_UNKNOWN_ERROR;
+    }
+    *result = reverse ? (long long)res - 1 : (long long)res;
+    return HS_SUCCESS;
 }
 
 }  // extern "C"
