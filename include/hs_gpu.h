@@ -26,6 +26,8 @@ struct hs_gpu_scratch;
 typedef struct hs_gpu_scratch hs_gpu_scratch_t; /* stands where hs_scratch_t stands, src/hs_common.h:466 */
 struct hs_gpu_corpus;
 typedef struct hs_gpu_corpus hs_gpu_corpus_t;
+/* stands where hs_stream_t stands, src/hs_common.h:48 */
+typedef struct hs_gpu_stream hs_gpu_stream_t;
 
 typedef int hs_error_t;
 #define HS_SUCCESS 0
@@ -109,6 +111,27 @@ hs_error_t hs_gpu_scan_batch(const hs_database_t *db, const char *const *data, c
 hs_error_t hs_gpu_scan_vector_ex(const hs_database_t *db, const char *const *data, const unsigned int *length,
                                  unsigned int count, unsigned int flags, hs_gpu_scratch_t *scratch,
                                  const hs_gpu_match_t **matches, uint64_t *n_matches);
+
+/* ---- stream mode: HS_MODE_STREAM pure-literal databases -------------------------------------------------------------
+ * hs_open_stream / hs_scan_stream / hs_close_stream / hs_reset_stream / hs_copy_stream  (src/hs_runtime.h:148-293,
+ * src/runtime.c:543-580, 980-996, 998-1033, 1035-1060, 711-737): same parameter lists and error codes.  The stream object
+ * lives on the host: its offset, its last historyRequired bytes, the exhaustion keys of the single-match reports it has
+ * delivered.  Offsets in callbacks are stream offsets; a literal may straddle any number of blocks.  A non-zero callback
+ * return terminates the stream: this and every later call on it return HS_SCAN_TERMINATED. */
+hs_error_t hs_gpu_open_stream(const hs_database_t *db, unsigned int flags, hs_gpu_stream_t **stream);
+hs_error_t hs_gpu_scan_stream(hs_gpu_stream_t *id, const char *data, unsigned int length, unsigned int flags,
+                              hs_gpu_scratch_t *scratch, match_event_handler onEvent, void *context);
+hs_error_t hs_gpu_close_stream(hs_gpu_stream_t *id, hs_gpu_scratch_t *scratch, match_event_handler onEvent, void *context);
+hs_error_t hs_gpu_reset_stream(hs_gpu_stream_t *id, unsigned int flags, hs_gpu_scratch_t *scratch,
+                               match_event_handler onEvent, void *context);
+hs_error_t hs_gpu_copy_stream(hs_gpu_stream_t **to_id, const hs_gpu_stream_t *from_id);
+/* The batch form, which is what fills a GPU: ONE block for each of `count` DIFFERENT streams of one database (the next
+ * packet of many flows, examples/pcapscan.cc:290 scanStreams) in one device pass.  contexts[i] goes to the callbacks
+ * of stream ids[i] (contexts may be NULL).  A stream may appear once per call (HS_INVALID otherwise).  A non-zero
+ * callback return terminates ITS stream only; the call then returns HS_SCAN_TERMINATED after serving the others. */
+hs_error_t hs_gpu_scan_streams(hs_gpu_stream_t *const *ids, const char *const *data, const unsigned int *length,
+                               unsigned int count, unsigned int flags, hs_gpu_scratch_t *scratch,
+                               match_event_handler onEvent, void *const *contexts);
 
 /* Device-resident corpora: upload once, scan many times (what hsbench does with its in-memory corpus,
  * tools/hsbench/main.cpp:486-512).  The corpus is `count` buffers; `flat` holds them back to back and

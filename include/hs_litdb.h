@@ -31,6 +31,7 @@ typedef struct hs_database hs_database_t; /* same opaque type as src/hs_common.h
 #define HSB_FLAG_SINGLEMATCH 8u
 
 #define HSB_MODE_BLOCK 1u /* HS_MODE_BLOCK, src/hs_compile.h:1156 */
+#define HSB_MODE_STREAM 2u /* HS_MODE_STREAM, src/hs_compile.h:1166 */
 #define HSB_MODE_VECTORED 4u /* HS_MODE_VECTORED, src/hs_compile.h:1171 */
 
 /* literal-matcher choice; AUTO follows the reference's rules: 1 fragment -> noodle, <= 48 fragments
@@ -54,8 +55,9 @@ typedef struct hsb_lit_options {
 
 /* Same parameter meaning as hs_compile_lit_multi; `platform` is replaced by `options` (the blob is
  * always stamped for the generic x86 platform so every ISA build of the reference runtime accepts it),
- * `error` receives a malloc'ed message (hsb_free_error).  mode: HSB_MODE_BLOCK, or HSB_MODE_VECTORED for pure-literal
- * sets -- the database the reference's hs_scan_vector wants (src/runtime.c:1129-1131): RoseEngine.mode = HS_MODE_VECTORED,
+ * `error` receives a malloc'ed message (hsb_free_error).  mode: HSB_MODE_BLOCK, or HSB_MODE_VECTORED / HSB_MODE_STREAM for
+ * pure-literal sets -- the database the reference's hs_scan_vector (src/runtime.c:1129-1131) / hs_open_stream (:556-558)
+ * wants: RoseEngine.mode = HS_MODE_VECTORED / HS_MODE_STREAM,
  * historyRequired = longest literal - 1 (or the deepest lookaround), stream-state layout with a history area
  * (rose_build_bytecode.cpp:381-440). */
 int hsb_compile_lit_multi(const char *const *expressions, const unsigned *flags, const unsigned *ids,

@@ -20,6 +20,7 @@
 #endif
 #ifndef HS_SHIM_WITH_REFERENCE_HEADER
 typedef struct hs_scratch hs_scratch_t; /* opaque to the application, as in src/hs_runtime.h:48 */
+typedef struct hs_stream hs_stream_t;   /* src/hs_common.h:48 */
 #endif
 
 hs_error_t HS_CDECL hs_alloc_scratch(const hs_database_t *db, hs_scratch_t **scratch) {
@@ -58,4 +59,27 @@ hs_error_t HS_CDECL hs_scan_vector(const hs_database_t *db, const char *const *d
     if (rv != HS_SUCCESS) return rv;
     if (mode != HS_GPU_MODE_VECTORED) return HS_DB_MODE_ERROR;
     return hs_gpu_scan_vector(db, data, length, count, flags, (hs_gpu_scratch_t *)scratch, onEvent, context);
+}
+
+/* Stream mode (pure-literal HS_MODE_STREAM databases): src/hs_runtime.h:148-293. */
+hs_error_t HS_CDECL hs_open_stream(const hs_database_t *db, unsigned int flags, hs_stream_t **stream) {
+    return hs_gpu_open_stream(db, flags, (hs_gpu_stream_t **)stream);
+}
+
+hs_error_t HS_CDECL hs_scan_stream(hs_stream_t *id, const char *data, unsigned int length, unsigned int flags,
+                                   hs_scratch_t *scratch, match_event_handler onEvent, void *ctxt) {
+    return hs_gpu_scan_stream((hs_gpu_stream_t *)id, data, length, flags, (hs_gpu_scratch_t *)scratch, onEvent, ctxt);
+}
+
+hs_error_t HS_CDECL hs_close_stream(hs_stream_t *id, hs_scratch_t *scratch, match_event_handler onEvent, void *ctxt) {
+    return hs_gpu_close_stream((hs_gpu_stream_t *)id, (hs_gpu_scratch_t *)scratch, onEvent, ctxt);
+}
+
+hs_error_t HS_CDECL hs_reset_stream(hs_stream_t *id, unsigned int flags, hs_scratch_t *scratch, match_event_handler onEvent,
+                                    void *context) {
+    return hs_gpu_reset_stream((hs_gpu_stream_t *)id, flags, (hs_gpu_scratch_t *)scratch, onEvent, context);
+}
+
+hs_error_t HS_CDECL hs_copy_stream(hs_stream_t **to_id, const hs_stream_t *from_id) {
+    return hs_gpu_copy_stream((hs_gpu_stream_t **)to_id, (const hs_gpu_stream_t *)from_id);
 }

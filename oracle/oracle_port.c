@@ -715,7 +715,8 @@ int op_scan_vector(const void *db, const char *const *data, const unsigned *leng
     if (!d || !data || !length || rd32(d + DB_MAGIC_OFF) != 0xdbdbdbdbu) return HS_INVALID;
     if (rd32(d + DB_VERSION_OFF) != ((5u << 24) | (4u << 16) | (11u << 8))) return HS_DB_VERSION_ERROR;
     const u8 *rose = d + rd32(d + DB_BYTECODE_OFF);
-    if (rd32(rose + R_MODE) != 4) return HS_DB_MODE_ERROR;
+    if (rd32(rose + R_MODE) != 4 && rd32(rose + R_MODE) != 2) return HS_DB_MODE_ERROR; /* mode 2 (HS_MODE_STREAM): the same loop is
+                                                                                         * hs_open_stream, hs_scan_stream per block, hs_close_stream */
     if (rose[R_RUNTIME_IMPL] != 1 || rose[R_HAS_SOM] || rd32(rose + R_CKEY_COUNT) || rd32(rose + R_BOUNDARY) ||
         rd32(rose + R_BOUNDARY + 4) || rd32(rose + R_BOUNDARY + 8))
         return HS_ARCH_ERROR; /* outside the restated path */

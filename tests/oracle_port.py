@@ -50,6 +50,9 @@ def scan_vector(db, bufs, stop_after=0, cap=1 << 16):
         cap = m.value + 16
 
 
+scan_stream_blocks = scan_vector   # HS_MODE_STREAM databases: the same block-by-block loop (open, scan per block, close)
+
+
 def brute_force(lits, flags, ids, data, cap=1 << 16):
     n = len(lits)
     arr = (C.c_char_p * n)(*lits)

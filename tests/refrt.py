@@ -45,6 +45,11 @@ class RefRuntime:
         L.hs_scan_vector.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_uint), C.c_uint, C.c_uint, C.c_void_p,
                                      MATCH_CB, C.c_void_p]
         L.hs_scan_vector.restype = C.c_int
+        L.hs_open_stream.argtypes = [C.c_void_p, C.c_uint, C.POINTER(C.c_void_p)]
+        L.hs_scan_stream.argtypes = [C.c_void_p, C.c_char_p, C.c_uint, C.c_uint, C.c_void_p, MATCH_CB, C.c_void_p]
+        L.hs_close_stream.argtypes = [C.c_void_p, C.c_void_p, MATCH_CB, C.c_void_p]
+        L.hs_reset_stream.argtypes = [C.c_void_p, C.c_uint, C.c_void_p, MATCH_CB, C.c_void_p]
+        L.hs_copy_stream.argtypes = [C.POINTER(C.c_void_p), C.c_void_p]
         L.hs_database_info.argtypes = [C.c_void_p, C.POINTER(C.c_char_p)]
         L.ref_shim_crc32c.argtypes = [C.c_char_p, C.c_size_t]
         L.ref_shim_crc32c.restype = C.c_uint
@@ -89,6 +94,25 @@ class RefRuntime:
         lens = (C.c_uint * n)(*[len(b) for b in bufs])
         rv = self.L.hs_scan_vector(db, arr, lens, n, 0, scratch, MATCH_CB(cb), None)
         return rv, out
+
+    def scan_stream_blocks(self, db, scratch, bufs, stop_after=0):
+        """hs_open_stream, hs_scan_stream per block, hs_close_stream (HS_MODE_STREAM databases): ([rv per call], matches in
+        callback order with stream offsets)."""
+        out, rvs = [], []
+
+        def cb(id_, from_, to, flags, ctx):
+            out.append((id_, to))
+            return 1 if stop_after and len(out) >= stop_after else 0
+
+        fn = MATCH_CB(cb)
+        st = C.c_void_p()
+        rv = self.L.hs_open_stream(db, 0, C.byref(st))
+        if rv != 0:
+            return [rv], out
+        for b in bufs:
+            rvs.append(self.L.hs_scan_stream(st, b, len(b), 0, scratch, fn, None))
+        rvs.append(self.L.hs_close_stream(st, scratch, fn, None))
+        return rvs, out
 
     def info(self, db):
         s = C.c_char_p()

@@ -51,9 +51,9 @@ def test_argument_errors_without_device():
     base = (C.addressof(buf) + 63) & ~63
     C.memmove(base, bytes(raw), len(raw))
     assert L.hs_gpu_alloc_scratch(C.c_void_p(base), C.byref(s)) == gpu.HS_DB_VERSION_ERROR
-    # stream-mode database -> HS_DB_MODE_ERROR
+    # a mode that is none of block / stream / vectored -> HS_DB_MODE_ERROR
     raw = bytearray(db.raw())
-    raw[64 + 12:64 + 16] = (2).to_bytes(4, "little")
+    raw[64 + 12:64 + 16] = (8).to_bytes(4, "little")
     C.memmove(base, bytes(raw), len(raw))
     assert L.hs_gpu_alloc_scratch(C.c_void_p(base), C.byref(s)) == gpu.HS_DB_MODE_ERROR
     # SOM database -> refused, never approximated

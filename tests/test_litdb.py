@@ -38,7 +38,7 @@ def test_rejects_bad_input():
     with pytest.raises(litdb.CompileError):
         litdb.compile_lit_multi([b""])
     with pytest.raises(litdb.CompileError):
-        litdb.compile_lit_multi([b"ab"], mode=2)
+        litdb.compile_lit_multi([b"ab"], mode=3)
     with pytest.raises(litdb.CompileError):
         litdb.compile_lit_multi([b"ab", b"cd"], engine=litdb.ENGINE_NOODLE)
     with pytest.raises(litdb.CompileError):

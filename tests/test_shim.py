@@ -33,7 +33,8 @@ def test_shim_compiles_against_the_reference_header(tmp_path):
 def test_shim_exports_the_reference_entry_points():
     so = os.path.join(ROOT, "vectorscan_b200", "libhs_gpushim.so")
     syms = subprocess.run(["nm", "-D", "--defined-only", so], capture_output=True, text=True, check=True).stdout
-    for name in ("hs_alloc_scratch", "hs_clone_scratch", "hs_scratch_size", "hs_free_scratch", "hs_scan", "hs_scan_vector"):
+    for name in ("hs_alloc_scratch", "hs_clone_scratch", "hs_scratch_size", "hs_free_scratch", "hs_scan", "hs_scan_vector",
+                 "hs_open_stream", "hs_scan_stream", "hs_close_stream", "hs_reset_stream", "hs_copy_stream"):
         assert re.search(rf" T {name}$", syms, re.M), name
 
 

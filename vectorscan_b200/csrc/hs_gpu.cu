@@ -39,6 +39,7 @@
 #include <cstring>
 #include <map>
 #include <mutex>
+#include <new>
 #include <string>
 #include <thread>
 #include <vector>
@@ -1151,6 +1152,19 @@ struct hs_gpu_corpus {
     }
 };
 
+// hs_stream_t (src/state.h, runtime.c:543-600): what a pure-literal stream carries from block to block -- how far it has
+// come, its last historyRequired bytes, the exhaustion keys of the single-match reports already delivered, its status.
+struct hs_gpu_stream {
+    u32 magic = 0x5354524d;
+    const hs_database_t *db = nullptr;
+    u32 crc = 0, hreq = 0;
+    u64 offset = 0;
+    std::vector<u8> hist;        // min(offset, hreq) bytes
+    std::vector<u32> exhausted;  // sorted exhaustion keys
+    bool terminated = false;     // a callback asked to stop (STATUS_TERMINATED): later blocks return HS_SCAN_TERMINATED
+    bool in_call = false;
+};
+
 struct hs_gpu_scratch {
     u32 magic = 0x47505553;  // 'GPUS'
     std::atomic<int> in_use{0};
@@ -1163,6 +1177,7 @@ struct hs_gpu_scratch {
     size_t h_stage_cap = 0;
     PinnedBuf<u64> h_off;
     PinnedBuf<u32> h_cell_first;
+    PinnedBuf<u8> h_streams;     // hs_gpu_scan_streams: history + block of every stream of the call, back to back
     DevBuf<Rec> recs, recs2;
     DevBuf<hs_gpu_match_t> d_matches;
     DevBuf<u8> cub_tmp, keep;
@@ -2674,6 +2689,7 @@ hs_error_t hs_gpu_free_scratch(hs_gpu_scratch_t *s) {
     if (s->copy_stream) { cudaStreamSynchronize(s->copy_stream); cudaStreamDestroy(s->copy_stream); }
     s->h_off.release();
     s->h_cell_first.release();
+    s->h_streams.release();
     if (s->h_stage) cudaFreeHost(s->h_stage);
     if (s->h_matches) cudaFreeHost(s->h_matches);
     if (s->h_ctl) cudaFreeHost(s->h_ctl);
@@ -2724,6 +2740,7 @@ hs_error_t hs_gpu_scan_vector(const hs_database_t *db, const char *const *data, 
     if (!scratch || !data || !length) return HS_INVALID;
     hs_error_t rv = validate_scan_args(db, scratch);
     if (rv != HS_SUCCESS) return rv;
+    if (database_mode(db) == MODE_STREAM) return HS_DB_MODE_ERROR;  // streams: hs_gpu_scan_stream(s)
     InUseGuard g(scratch);
     if (!g.ok) return HS_SCRATCH_IN_USE;
     DbImage *im = nullptr;
@@ -2739,6 +2756,7 @@ hs_error_t hs_gpu_scan_vector_ex(const hs_database_t *db, const char *const *dat
     if (!scratch || !data || !length || !matches || !n_matches) return HS_INVALID;
     hs_error_t rv = validate_scan_args(db, scratch);
     if (rv != HS_SUCCESS) return rv;
+    if (database_mode(db) == MODE_STREAM) return HS_DB_MODE_ERROR;
     InUseGuard g(scratch);
     if (!g.ok) return HS_SCRATCH_IN_USE;
     DbImage *im = nullptr;
@@ -2758,6 +2776,173 @@ hs_error_t hs_gpu_scan(const hs_database_t *db, const char *data, unsigned int l
     const char *one[1] = {data};
     unsigned int len[1] = {length};
     return hs_gpu_scan_vector(db, one, len, 1, flags, scratch, onEvent, context);
+}
+
+// ---- stream mode (pure-literal HS_MODE_STREAM databases) ----------------------------------------------------------
+// hs_open_stream (src/runtime.c:543-580)
+hs_error_t hs_gpu_open_stream(const hs_database_t *db, unsigned int flags, hs_gpu_stream_t **stream) {
+    (void)flags;
+    if (!stream) return HS_INVALID;
+    *stream = nullptr;
+    if (!db || rd32(db, db::magic) != db::MAGIC) return HS_INVALID;
+    if (rd32(db, db::version) != db::VERSION_5_4_11) return HS_DB_VERSION_ERROR;
+    if (database_mode(db) != MODE_STREAM) return HS_DB_MODE_ERROR;
+    const u8 *p = reinterpret_cast<const u8 *>(db);
+    const u8 *r = p + rd32(p, db::bytecode);
+    if (rd8(r, rose::runtimeImpl) != rose::RUNTIME_PURE_LITERAL) return HS_ARCH_ERROR;
+    hs_gpu_stream *st = new (std::nothrow) hs_gpu_stream();
+    if (!st) return HS_NOMEM;
+    st->db = db;
+    st->crc = rd32(db, db::crc32);
+    st->hreq = rd32(r, rose::historyRequired);
+    *stream = st;
+    return HS_SUCCESS;
+}
+
+// One block for each of `count` DIFFERENT streams of one database, in one device pass: block i is scanned behind the last
+// historyRequired bytes of stream ids[i] (hs_scan_stream_internal, src/runtime.c:880-975: getHistory / populateCoreInfo
+// put the history in front of the block, pureLiteralStreamExec runs the literal matcher over the block with it); the
+// device sees `count` independent buffers history + block, the host drops what ends inside a history (reported by an
+// earlier call), turns offsets into stream offsets, applies the stream's exhaustion keys and moves the stream on
+// (maintainHistoryBuffer :483-508).  A callback that returns non-zero terminates ITS stream only.
+hs_error_t hs_gpu_scan_streams(hs_gpu_stream_t *const *ids, const char *const *data, const unsigned int *length,
+                               unsigned int count, unsigned int flags, hs_gpu_scratch_t *scratch,
+                               match_event_handler onEvent, void *const *contexts) {
+    (void)flags;
+    if (!ids || !data || !length || !scratch) return HS_INVALID;
+    if (!count) return HS_SUCCESS;
+    for (unsigned i = 0; i < count; i++)
+        if (!ids[i] || ids[i]->magic != 0x5354524d || ids[i]->db != ids[0]->db || (length[i] && !data[i])) return HS_INVALID;
+    const hs_database_t *db = ids[0]->db;
+    hs_error_t rv = validate_scan_args(db, scratch);
+    if (rv != HS_SUCCESS) return rv;
+    if (rd32(db, db::crc32) != ids[0]->crc || database_mode(db) != MODE_STREAM) return HS_INVALID;
+    InUseGuard g(scratch);
+    if (!g.ok) return HS_SCRATCH_IN_USE;
+    struct Release { hs_gpu_stream_t *const *ids; unsigned n; ~Release() { for (unsigned i = 0; i < n; i++) ids[i]->in_call = false; } } rel{ids, 0};
+    for (unsigned i = 0; i < count; i++) {
+        if (ids[i]->in_call) return HS_INVALID;   // the same stream twice in one call: its blocks would not be consecutive
+        ids[i]->in_call = true;
+        rel.n = i + 1;
+    }
+    // history + block, back to back (terminated streams and empty blocks contribute nothing: runtime.c:883-900), written
+    // straight into page-locked memory of the scratch: the staging then sees one contiguous pinned run and copies it to
+    // the device as it lies (stage_host_buffers), so the bytes are moved once on the host, by a few threads
+    std::vector<u64> at((size_t)count + 1, 0);
+    for (unsigned i = 0; i < count; i++) {
+        const bool live = !ids[i]->terminated && length[i];
+        at[i + 1] = at[i] + (live ? ids[i]->hist.size() + length[i] : 0);
+        if (at[i + 1] - at[i] > 0xffffffffull) return HS_INVALID;
+    }
+    if ((rv = ensure_device(scratch)) != HS_SUCCESS) return rv;
+    if (!scratch->h_streams.resize(at[count] + 64)) return HS_NOMEM;
+    char *arena = reinterpret_cast<char *>(scratch->h_streams.data());
+    std::vector<const char *> ptr(count);
+    std::vector<unsigned int> len(count);
+    {
+        auto part = [&](unsigned a, unsigned b) {
+            for (unsigned i = a; i < b; i++) {
+                ptr[i] = arena + at[i];
+                len[i] = (unsigned int)(at[i + 1] - at[i]);
+                if (!len[i]) continue;
+                std::memcpy(arena + at[i], ids[i]->hist.data(), ids[i]->hist.size());
+                std::memcpy(arena + at[i] + ids[i]->hist.size(), data[i], length[i]);
+            }
+        };
+        const unsigned threads = std::min<unsigned>(8, std::max<unsigned>(1, std::thread::hardware_concurrency() / 2));
+        if (count < 512 || threads < 2) part(0, count);
+        else {
+            std::vector<std::thread> pool;
+            for (unsigned t = 1; t < threads; t++) pool.emplace_back(part, (unsigned)((u64)count * t / threads), (unsigned)((u64)count * (t + 1) / threads));
+            part(0, count / threads);
+            for (std::thread &t : pool) t.join();
+        }
+    }
+    DbImage *im = nullptr;
+    rv = scan_host_batch(db, ptr.data(), len.data(), count, scratch, &im);
+    if (rv != HS_SUCCESS) return rv;
+    const std::vector<std::pair<u32, u32>> &ekey_of = im->view.stream_ekey_of;
+    const bool any_ekey = im->view.stream_any_ekey;
+    const hs_gpu_match_t *m = scratch->h_matches;
+    bool any_stop = false;
+    u64 delivered = 0;
+    for (u64 k = 0; k < scratch->n_matches; k++) {
+        hs_gpu_stream *st = ids[m[k].buffer];
+        const u64 hlen = st->hist.size();
+        if (st->terminated || m[k].to <= hlen) continue;
+        u32 ekey = ~0u;
+        if (any_ekey) {
+            auto it = std::lower_bound(ekey_of.begin(), ekey_of.end(), std::make_pair(m[k].id, 0u));
+            if (it != ekey_of.end() && it->first == m[k].id) ekey = it->second;
+        }
+        if (ekey != ~0u) {
+            auto pos = std::lower_bound(st->exhausted.begin(), st->exhausted.end(), ekey);
+            if (pos != st->exhausted.end() && *pos == ekey) continue;   // exhausted by an earlier block
+            st->exhausted.insert(pos, ekey);
+        }
+        delivered++;
+        if (onEvent && onEvent(m[k].id, 0, st->offset - hlen + m[k].to, 0, contexts ? contexts[m[k].buffer] : nullptr)) {
+            st->terminated = true;
+            any_stop = true;
+        }
+    }
+    scratch->stats.matches = delivered;
+    for (unsigned i = 0; i < count; i++) {
+        hs_gpu_stream *st = ids[i];
+        if (st->terminated || !length[i]) continue;
+        const u64 total = st->hist.size() + length[i];
+        const u64 keep = std::min<u64>(st->hreq, total);
+        const u8 *tail = reinterpret_cast<const u8 *>(arena) + at[i] + (total - keep);
+        st->hist.assign(tail, tail + keep);   // (the arena is not the vector's own storage: no aliasing)
+        st->offset += length[i];
+    }
+    return any_stop ? HS_SCAN_TERMINATED : HS_SUCCESS;
+}
+
+// hs_scan_stream (src/runtime.c:980-996)
+hs_error_t hs_gpu_scan_stream(hs_gpu_stream_t *id, const char *data, unsigned int length, unsigned int flags,
+                              hs_gpu_scratch_t *scratch, match_event_handler onEvent, void *context) {
+    if (!id || id->magic != 0x5354524d || !scratch || !data) return HS_INVALID;
+    if (id->terminated) return HS_SCAN_TERMINATED;   // runtime.c:883-893
+    hs_gpu_stream_t *ids[1] = {id};
+    const char *d[1] = {data};
+    unsigned int l[1] = {length};
+    void *c[1] = {context};
+    return hs_gpu_scan_streams(ids, d, l, 1, flags, scratch, onEvent, c);
+}
+
+// hs_close_stream (src/runtime.c:998-1033): a pure-literal database has no end-of-data work (requiresEodCheck is 0), so
+// nothing is reported; scratch / onEvent may be NULL as in the reference.
+hs_error_t hs_gpu_close_stream(hs_gpu_stream_t *id, hs_gpu_scratch_t *scratch, match_event_handler onEvent, void *context) {
+    (void)scratch; (void)onEvent; (void)context;
+    if (!id || id->magic != 0x5354524d) return HS_INVALID;
+    id->magic = 0;
+    delete id;
+    return HS_SUCCESS;
+}
+
+// hs_reset_stream (src/runtime.c:1035-1060)
+hs_error_t hs_gpu_reset_stream(hs_gpu_stream_t *id, unsigned int flags, hs_gpu_scratch_t *scratch, match_event_handler onEvent,
+                               void *context) {
+    (void)flags; (void)scratch; (void)onEvent; (void)context;
+    if (!id || id->magic != 0x5354524d) return HS_INVALID;
+    id->offset = 0;
+    id->hist.clear();
+    id->exhausted.clear();
+    id->terminated = false;
+    return HS_SUCCESS;
+}
+
+// hs_copy_stream (src/runtime.c:711-737)
+hs_error_t hs_gpu_copy_stream(hs_gpu_stream_t **to_id, const hs_gpu_stream_t *from_id) {
+    if (!to_id) return HS_INVALID;
+    *to_id = nullptr;
+    if (!from_id || from_id->magic != 0x5354524d) return HS_INVALID;
+    hs_gpu_stream *st = new (std::nothrow) hs_gpu_stream(*from_id);
+    if (!st) return HS_NOMEM;
+    st->in_call = false;
+    *to_id = st;
+    return HS_SUCCESS;
 }
 
 hs_error_t hs_gpu_corpus_create(const char *flat, const uint64_t *offsets, unsigned int count, hs_gpu_corpus_t **out) {
@@ -2807,6 +2992,7 @@ hs_error_t hs_gpu_scan_corpus(const hs_database_t *db, const hs_gpu_corpus_t *co
     if (!corpus || corpus->magic != 0x43525053) return HS_INVALID;
     hs_error_t rv = validate_scan_args(db, scratch);
     if (rv != HS_SUCCESS) return rv;
+    if (database_mode(db) == MODE_STREAM) return HS_DB_MODE_ERROR;
     InUseGuard g(scratch);
     if (!g.ok) return HS_SCRATCH_IN_USE;
     if ((rv = ensure_device(scratch)) != HS_SUCCESS) return rv;
@@ -2835,7 +3021,7 @@ hs_error_t hs_gpu_scan_corpora(const hs_database_t *db, const hs_gpu_corpus_t *c
     if ((rv = upload_database(scratch, db, &im)) != HS_SUCCESS) return rv;
     hs_gpu_scratch *s = scratch;
     hs_gpu_stats_t &st = s->stats;
-    if (!ordered_eligible(s, im) || im->view.vectored) return HS_ARCH_ERROR;  // a train needs the sort-free path (plain-report literal sets) and independent buffers
+    if (!ordered_eligible(s, im) || im->view.vectored || im->view.streaming) return HS_ARCH_ERROR;  // a train needs the sort-free path (plain-report literal sets) and independent buffers
     st = hs_gpu_stats_t{};
     s->n_matches = 0;
     s->fetched = false;

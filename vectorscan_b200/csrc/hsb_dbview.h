@@ -5,6 +5,7 @@
 #pragma once
 #include "hsb_layout.h"
 
+#include <algorithm>
 #include <set>
 #include <string>
 #include <vector>
@@ -61,6 +62,14 @@ struct DbView {
     // HS_MODE_VECTORED (src/runtime.c:1106-1174): the buffers of one hs_scan_vector call are consecutive blocks of one
     // stream -- offsets run on, a literal may straddle blocks, exhaustion lasts to the end of the call
     bool vectored = false;
+    // HS_MODE_STREAM (hs_open_stream / hs_scan_stream / hs_close_stream, src/runtime.c:543-1060): pure-literal databases
+    // only.  A block is scanned behind the stream's last historyRequired bytes (kept on the host with the stream); what
+    // must survive from call to call beside that is the exhaustion of single-match reports, which the host keeps per
+    // stream by exhaustion key: stream_ekey_of maps an external report id to its key (~0u: the report never exhausts).
+    bool streaming = false;
+    u32 history_required = 0;
+    std::vector<std::pair<u32, u32>> stream_ekey_of;
+    bool stream_any_ekey = false;
 };
 
 inline bool in_range(const DbView &d, size_t off, size_t n) { return off <= d.bc_len && n <= d.bc_len - off; }
@@ -100,7 +109,8 @@ inline size_t op_size(u8 code, size_t &fail_jump_at) {
 // inside the bytecode with its full operand block, every fail_jump must land on an instruction of this same program at
 // or before its END (the device interpreter follows them unchecked), and a DEDUPE must be followed by one of the three
 // reports the interpreter fuses it with.  INCLUDED_JUMP children are programs of other literals, walked on their own.
-inline int census_program(const DbView &d, u32 prog, std::string &why, u32 &max_lit_len, u64 *hist = nullptr) {
+inline int census_program(const DbView &d, u32 prog, std::string &why, u32 &max_lit_len, u64 *hist = nullptr,
+                          std::vector<std::pair<u32, u32>> *reports = nullptr) {  // reports: (external id, ekey or ~0u) of every reporting instruction
     size_t pc = prog;
     std::vector<size_t> starts, targets;
     for (int guard = 0; guard < 4096; guard++) {
@@ -114,6 +124,12 @@ inline int census_program(const DbView &d, u32 prog, std::string &why, u32 &max_
         }
         if (!in_range(d, pc, sz)) { why = "instruction operands run past the bytecode"; return E_INVALID; }
         if (hist) hist[code & 127]++;
+        if (reports) {
+            if (code == op::REPORT || code == op::FINAL_REPORT) reports->push_back({rd32(d.bc, pc + op::report::onmatch), ~0u});
+            if (code == op::DEDUPE_AND_REPORT) reports->push_back({rd32(d.bc, pc + op::dedupe_and_report::onmatch), ~0u});
+            if (code == op::REPORT_EXHAUST)
+                reports->push_back({rd32(d.bc, pc + op::report_exhaust::onmatch), rd32(d.bc, pc + op::report_exhaust::ekey)});
+        }
         starts.push_back(pc);
         if (fj) {
             const u32 j = rd32(d.bc, pc + fj);
@@ -508,10 +524,12 @@ inline int parse_database(const void *db, DbView &d, std::string &why) {
     if (d.bc_len < rose::SIZE) { why = "bytecode too short"; return E_INVALID; }
     const u8 *r = d.bc;
     const u32 mode = rd32(r, rose::mode);
-    if (mode != MODE_BLOCK && mode != MODE_VECTORED) { why = "not a block-mode or vectored-mode database"; return E_DB_MODE; }
+    if (mode != MODE_BLOCK && mode != MODE_VECTORED && mode != MODE_STREAM) { why = "unknown database mode"; return E_DB_MODE; }
     d.vectored = mode == MODE_VECTORED;
-    if (d.vectored && rd8(r, rose::runtimeImpl) != rose::RUNTIME_PURE_LITERAL) {
-        why = "vectored mode is served for pure-literal databases only (engines carry stream state from block to block)";
+    d.streaming = mode == MODE_STREAM;
+    d.history_required = rd32(r, rose::historyRequired);
+    if ((d.vectored || d.streaming) && rd8(r, rose::runtimeImpl) != rose::RUNTIME_PURE_LITERAL) {
+        why = "stream and vectored mode are served for pure-literal databases only (engines carry stream state from block to block)";
         return E_ARCH;
     }
     if (rd32(r, rose::size) > d.bc_len) { why = "engine size exceeds database length"; return E_INVALID; }
@@ -529,7 +547,7 @@ inline int parse_database(const void *db, DbView &d, std::string &why) {
     d.min_width_excl = rd32(r, rose::minWidthExcludingBoundaries);
     d.max_bi_width = rd32(r, rose::maxBiAnchoredWidth);
     // the stream path has no length gates (hs_scan_stream_internal, src/runtime.c:880-975, tests none of them)
-    if (d.vectored) { d.min_width = d.min_width_excl = 0; d.max_bi_width = rose::BOUND_INF; }
+    if (d.vectored || d.streaming) { d.min_width = d.min_width_excl = 0; d.max_bi_width = rose::BOUND_INF; }
     d.ekey_count = rd32(r, rose::ekeyCount);
     d.dkey_count = rd32(r, rose::dkeyCount);
     d.groups = rd64(r, rose::initialGroups) & rd64(r, rose::floating_group_mask);
@@ -633,6 +651,21 @@ inline int parse_database(const void *db, DbView &d, std::string &why) {
         int rv = census_program(d, p, why, d.max_lit_len);
         if (rv != E_SUCCESS) return rv;
         d.programs.push_back(p);
+    }
+    if (d.streaming) {
+        // one exhaustion key per external id, and no silent exhaustion: the host carries a stream's exhausted keys from
+        // call to call and sees only what is reported
+        u64 hist[128] = {0};
+        std::vector<std::pair<u32, u32>> reps;
+        u32 dummy = 0;
+        for (u32 p : d.programs) census_program(d, p, why, dummy, hist, &reps);
+        if (hist[op::SET_EXHAUST]) { why = "stream mode: quiet exhaustion (SET_EXHAUST) is not supported"; return E_ARCH; }
+        std::sort(reps.begin(), reps.end());
+        reps.erase(std::unique(reps.begin(), reps.end()), reps.end());
+        for (size_t k = 1; k < reps.size(); k++)
+            if (reps[k].first == reps[k - 1].first) { why = "stream mode: report id " + std::to_string(reps[k].first) + " has more than one exhaustion key"; return E_ARCH; }
+        d.stream_ekey_of = reps;
+        for (auto &e : reps) if (e.second != ~0u) d.stream_any_ekey = true;
     }
     if (impl == rose::RUNTIME_FULL_ROSE && rd32(r, rose::queueCount)) return parse_outfix_queues(d, why);
     return E_SUCCESS;

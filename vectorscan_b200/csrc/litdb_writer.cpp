@@ -107,6 +107,7 @@ struct BuildExt {
     u64 groups_off = 0;
     u32 max_bi_anchored_width = 0;
     bool vectored = false;  // HS_MODE_VECTORED: the buffers of one hs_scan_vector call are consecutive blocks of ONE stream
+    bool streaming = false; // HS_MODE_STREAM: the same stream state, driven through hs_open_stream / hs_scan_stream
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -1187,12 +1188,12 @@ int build(const std::vector<FullLit> &fulls_in, const hsb_lit_options &opt, cons
     wr8(r, rose::requiresEodCheck, eod_program ? 1 : 0);
     wr32(r, rose::eodProgramOffset, eod_program);
     wr8(r, rose::canExhaust, all_exhaustible && bx.regexes.empty() ? 1 : 0);
-    wr32(r, rose::mode, bx.vectored ? MODE_VECTORED : MODE_BLOCK);
+    wr32(r, rose::mode, bx.vectored ? MODE_VECTORED : bx.streaming ? MODE_STREAM : MODE_BLOCK);
     // Stream state keeps the last historyRequired bytes of the stream (src/runtime.c:77-85, maintainHistoryBuffer): the
     // literal confirm (fdr_confirm_runtime.h:77-88) and CHECK_MED_LIT (program_runtime.c:1988-2011) read a literal's
     // bytes that lie before the current block from there, so it must hold longest literal - 1 bytes.
     u32 history = 0;
-    if (bx.vectored) {
+    if (bx.vectored || bx.streaming) {
         for (auto &f : fulls_in) {
             history = std::max<u32>(history, (u32)f.s.size() ? (u32)f.s.size() - 1 : 0);
             for (auto &l : f.look)   // lookaround bytes before the block come from the history too (program_runtime.c:1253-1340)
@@ -1309,7 +1310,7 @@ int hsb_compile_mixed(const char *const *expressions, const unsigned *flags, con
     std::string err;
     auto fail = [&](const std::string &m) { if (error) *error = dup_error(m); return HSB_LIT_COMPILER_ERROR; };
     if (!expressions || !lens || !elements) return fail("invalid parameter: no expressions");
-    if (mode != hsb::MODE_BLOCK && mode != hsb::MODE_VECTORED) return fail("only HS_MODE_BLOCK and HS_MODE_VECTORED databases are written");
+    if (mode != hsb::MODE_BLOCK && mode != hsb::MODE_VECTORED && mode != hsb::MODE_STREAM) return fail("unknown mode");
     hsb_lit_options opt{};
     if (options) opt = *options;
     BuildExt bx;
@@ -1328,7 +1329,8 @@ int hsb_compile_mixed(const char *const *expressions, const unsigned *flags, con
     }
     if (build_ext && build_ext->reserved_pure_literal) bx.full_rose = !bx.regexes.empty();
     bx.vectored = mode == hsb::MODE_VECTORED;
-    if (bx.vectored && bx.full_rose) return fail("HS_MODE_VECTORED is written for pure-literal databases only");
+    bx.streaming = mode == hsb::MODE_STREAM;
+    if ((bx.vectored || bx.streaming) && bx.full_rose) return fail("HS_MODE_VECTORED / HS_MODE_STREAM are written for pure-literal databases only");
     std::vector<FullLit> fulls;
     for (unsigned i = 0; i < elements; i++) {
         unsigned f = flags ? flags[i] : 0;

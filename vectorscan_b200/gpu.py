@@ -76,6 +76,13 @@ def lib():
         L.hs_gpu_opcode_counts.argtypes = [vp, C.POINTER(C.c_ulonglong), C.c_uint]
         L.hs_gpu_database_opcodes.argtypes = [vp, C.POINTER(C.c_ulonglong), C.c_uint]
         L.hs_gpu_set_device.argtypes = [C.c_int]
+        L.hs_gpu_open_stream.argtypes = [vp, C.c_uint, C.POINTER(vp)]
+        L.hs_gpu_scan_stream.argtypes = [vp, C.c_char_p, C.c_uint, C.c_uint, vp, MATCH_CB, vp]
+        L.hs_gpu_close_stream.argtypes = [vp, vp, MATCH_CB, vp]
+        L.hs_gpu_reset_stream.argtypes = [vp, C.c_uint, vp, MATCH_CB, vp]
+        L.hs_gpu_copy_stream.argtypes = [C.POINTER(vp), vp]
+        L.hs_gpu_scan_streams.argtypes = [C.POINTER(vp), C.POINTER(C.c_char_p), u32p, C.c_uint, C.c_uint, vp, MATCH_CB,
+                                          C.POINTER(vp)]
         L.hs_gpu_version.restype = C.c_char_p
         _lib = L
     return _lib
@@ -232,3 +239,51 @@ def fetch_matches(scratch):
     if rv != HS_SUCCESS:
         raise HsGpuError(rv, "hs_gpu_fetch_matches")
     return _matches_to_list(mp, cnt.value)
+
+
+# ---- stream mode (HS_MODE_STREAM pure-literal databases) ----------------------------------------------------------------
+class Stream:
+    """hs_stream_t stand-in: hs_gpu_open_stream ... hs_gpu_close_stream."""
+
+    def __init__(self, db=None, ptr=None):
+        self.ptr = C.c_void_p() if ptr is None else ptr
+        if db is not None:
+            rv = lib().hs_gpu_open_stream(_dbptr(db), 0, C.byref(self.ptr))
+            if rv != HS_SUCCESS:
+                raise HsGpuError(rv, "hs_gpu_open_stream")
+
+    def scan(self, data, scratch, on_event=None, context=None):
+        cb = MATCH_CB(on_event) if on_event else C.cast(None, MATCH_CB)
+        return lib().hs_gpu_scan_stream(self.ptr, data, len(data), 0, scratch.ptr, cb, context)
+
+    def reset(self):
+        return lib().hs_gpu_reset_stream(self.ptr, 0, None, C.cast(None, MATCH_CB), None)
+
+    def copy(self):
+        out = C.c_void_p()
+        rv = lib().hs_gpu_copy_stream(C.byref(out), self.ptr)
+        if rv != HS_SUCCESS:
+            raise HsGpuError(rv, "hs_gpu_copy_stream")
+        return Stream(ptr=out)
+
+    def close(self):
+        if self.ptr:
+            lib().hs_gpu_close_stream(self.ptr, None, C.cast(None, MATCH_CB), None)
+            self.ptr = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def scan_streams(streams, blocks, scratch, on_event=None, contexts=None):
+    """hs_gpu_scan_streams: one block for each of several different streams in one device pass.  on_event gets
+    contexts[i] (an integer or None) as its last argument for the callbacks of streams[i]."""
+    n = len(streams)
+    ids = (C.c_void_p * n)(*[s.ptr.value for s in streams])
+    arr, lens, _ = _arrays(blocks)
+    ctxs = (C.c_void_p * n)(*(contexts if contexts is not None else [None] * n))
+    cb = MATCH_CB(on_event) if on_event else C.cast(None, MATCH_CB)
+    return lib().hs_gpu_scan_streams(ids, arr, lens, n, 0, scratch.ptr, cb, ctxs)

@@ -12,6 +12,7 @@ HS_FLAG_CASELESS = 1
 HS_FLAG_DOTALL = 2
 HS_FLAG_SINGLEMATCH = 8
 HS_MODE_BLOCK = 1
+HS_MODE_STREAM = 2
 HS_MODE_VECTORED = 4
 
 ENGINE_AUTO, ENGINE_FDR, ENGINE_TEDDY, ENGINE_NOODLE = 0, 1, 2, 3
