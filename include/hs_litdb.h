@@ -138,6 +138,9 @@ int hsb_compile_regex_multi(const char *const *expressions, const unsigned *flag
                                        steps through byte-shuffle masks: struct mcsheng, MCSHENG_NFA_8 / _16
                                        (src/nfa/mcsheng_internal.h:63-88) -- what the reference compiler builds for a DFA
                                        too large for Sheng (getDfa, src/rose/rose_build_bytecode.cpp) */
+#define HSB_REGEX_ENGINE_MCCLELLAN_WIDE 6u /* McClellan with Sherman states AND wide states: runs of >= 8 single-entry states
+                                              that leave the run the same way are stored as one "wide" state (16-bit
+                                              engines; mcclellan_internal.h:53-61, mcclellancompile.cpp:773-838) */
 int hsb_compile_regex_multi_ex(const char *const *expressions, const unsigned *flags, const unsigned *ids,
                                unsigned elements, unsigned mode, unsigned engine, hs_database_t **db,
                                char **error);

@@ -451,7 +451,7 @@ static int limex_scan(struct scan_state *s, const u8 *nfa) {
  * struct mcclellan / mstate_aux offsets: mcclellan_internal.h:63-101 (pinned by tests/test_layout.py).
  * Acceleration is a skip over bytes that cannot change the state; wide states are outside the restated path. */
 enum { MC_STATE_COUNT = 0, MC_START_ANCHORED = 8, MC_AUX_OFFSET = 12, MC_SHERMAN_OFFSET = 16, MC_ACCEPT_LIMIT_8 = 26,
-       MC_SHERMAN_LIMIT = 28, MC_ALPHA_SHIFT = 32, MC_FLAGS = 33, MC_HAS_WIDE = 35, MC_REMAP = 36, MC_ARB_REPORT = 292,
+       MC_SHERMAN_LIMIT = 28, MC_WIDE_LIMIT = 30, MC_ALPHA_SHIFT = 32, MC_FLAGS = 33, MC_HAS_WIDE = 35, MC_WIDE_OFFSET = 304, MC_REMAP = 36, MC_ARB_REPORT = 292,
        MC_SIZE = 308, MC_AUX_SIZE = 16, MC_AUX_ACCEPT = 0, MC_AUX_ACCEPT_EOD = 4 };
 
 static int mc_report(struct scan_state *s, const u8 *nfa, const u8 *m, u32 st, u64 loc, int eod) {
@@ -468,14 +468,32 @@ static int mc_report(struct scan_state *s, const u8 *nfa, const u8 *m, u32 st, u
 static int mcclellan_scan(struct scan_state *s, const u8 *nfa) {
     const int wide16 = nfa[NFA_TYPE] == 7;
     const u8 *m = nfa + NFA_SIZE, *succ = m + MC_SIZE;
-    if (nfa[NFA_RACCEL] || m[MC_HAS_WIDE]) { s->error = 1; return -1; }
+    if (nfa[NFA_RACCEL] || (m[MC_HAS_WIDE] && !wide16)) { s->error = 1; return -1; }
+    /* wide states (16-bit engines): ids >= wide_limit name entries {u16 width; u8 symbols[width]; (pad to 2); u16 next;
+     * u16 failure[alphabet]} found through the u32 offset list at wide_base + 4 (mcclellan_internal.h:53-61, :138-148) */
+    const u32 wide_limit = m[MC_HAS_WIDE] ? rd16(m + MC_WIDE_LIMIT) : 0xffffffffu;
+    const u8 *wide_base = nfa + rd32(m + MC_WIDE_OFFSET);
     const u32 as = m[MC_ALPHA_SHIFT], accept_limit = rd16(m + MC_ACCEPT_LIMIT_8), sherman_limit = rd16(m + MC_SHERMAN_LIMIT);
     u32 st = rd16(m + MC_START_ANCHORED);
+    int in_wide = 0;
     for (u32 i = 0; i < s->len && st; i++) {
         const u32 cp = m[MC_REMAP + s->buf[i]];
         int accept;
         if (wide16) {
             u32 e;
+            if (st >= wide_limit) {
+                /* doWide16 (mcclellan_common_impl.h:86-188), one call of the block scan (offset 0): the data is compared
+                 * with the state's symbols; all of them -> `next`, data ends first -> the scan ends inside the wide state
+                 * (no accept, no end-of-data accept: :615), a differing byte -> failure[that byte], which consumes it */
+                const u8 *we = wide_base + rd32(wide_base + 4 + 4 * (size_t)(st - wide_limit));
+                const u32 width = rd16(we);
+                const u8 *sym = we + 2, *tr = we + 2 + ((width + 1) & ~1u);
+                u32 j = 0;
+                while (j < width && i + j < s->len && m[MC_REMAP + s->buf[i + j]] == sym[j]) j++;
+                if (j == width) { e = rd16(tr); i += width - 1; }
+                else if (i + j == s->len) { in_wide = 1; break; }
+                else { e = rd16(tr + 2 + 2 * (size_t)m[MC_REMAP + s->buf[i + j]]); i += j; }
+            } else
             if (st < sherman_limit) e = rd16(succ + 2 * (((size_t)st << as) + cp));
             else {
                 const u8 *sh = nfa + rd32(m + MC_SHERMAN_OFFSET) + 32 * (size_t)(st - sherman_limit);
@@ -493,7 +511,7 @@ static int mcclellan_scan(struct scan_state *s, const u8 *nfa) {
         if (accept && mc_report(s, nfa, m, st, (u64)i + 1, 0) < 0) return -1;
     }
     s->cur_eod = 1;
-    if (st && (rd32(nfa + NFA_FLAGS) & NFA_ACCEPTS_EOD) && mc_report(s, nfa, m, st, s->len, 1) < 0) { s->cur_eod = 0; return -1; }
+    if (st && !in_wide && st < wide_limit && (rd32(nfa + NFA_FLAGS) & NFA_ACCEPTS_EOD) && mc_report(s, nfa, m, st, s->len, 1) < 0) { s->cur_eod = 0; return -1; }
     s->cur_eod = 0;
     return 0;
 }

@@ -214,3 +214,70 @@ def test_mcsheng_engine_types_in_multi_engine_databases():
         nfa = int.from_bytes(bc[info + 20 * q:info + 20 * q + 4], "little")
         types.add(bc[nfa + 8])
     assert types & {19, 20} and types <= {17, 19, 20, 6, 7}
+
+
+# ---- McClellan wide states (mcclellan_internal.h:53-61): runs of single-entry states stored as one state ------------
+def wide_case(rng):
+    """A pattern set whose DFA has long single-entry runs (anchored literals, so that no other pattern's states merge into
+    the runs) and more than 256 states, plus texts that walk the runs fully, partly, and leave them at every point."""
+    def word(n):
+        return bytes(rng.choice(b"abcdefghijklmnopqrstuvwxyz") for _ in range(n))
+    lits = [word(rng.randint(11, 20)) for _ in range(24)]
+    pats = [b"^" + l for l in lits[:20]] + [b"^" + lits[0][:10] + b"[0-9]+" + lits[1][:12], lits[20] + b"\\z",
+                                             b"^" + lits[2][:9] + b".*" + lits[21][:10]]
+    texts = [b""]
+    for _ in range(160):
+        l = lits[rng.randrange(len(lits))]
+        r = rng.random()
+        if r < .3:
+            t = l[:rng.randint(0, len(l))]
+        elif r < .5:
+            t = l + word(rng.randint(0, 5))
+        elif r < .6:
+            t = lits[0][:10] + b"123" + lits[1][:12]
+        elif r < .7:
+            t = lits[2][:9] + word(rng.randint(0, 30)) + lits[21][:10] + word(3)
+        elif r < .8:
+            t = word(5) + lits[20]
+        elif r < .9:
+            b = bytearray(l)
+            b[rng.randrange(len(b))] = rng.choice(b"abcxyz")
+            t = bytes(b)
+        else:
+            t = lits[2][:9] + lits[21][:rng.randint(0, 10)]
+        texts.append(t)
+    return pats, [0] * len(pats), list(range(len(pats))), texts
+
+
+def wide_header(db):
+    """(NFA.type, has_wide, wide_limit, number of wide head states) of a single-outfix McClellan database."""
+    bc = db.bytecode()
+    info = int.from_bytes(bc[236:240], "little")
+    nfa = int.from_bytes(bc[info:info + 4], "little")
+    m = nfa + 64
+    wo = int.from_bytes(bc[m + 304:m + 308], "little")
+    return bc[nfa + 8], bc[m + 35], int.from_bytes(bc[m + 30:m + 32], "little"), \
+        int.from_bytes(bc[nfa + wo + 2:nfa + wo + 4], "little") if wo else 0
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_mcclellan_wide_states_reference_brute_force_and_port(ref, seed):
+    import oracle_port
+    rng = random.Random(9900 + seed)
+    ex, fl, ids, texts = wide_case(rng)
+    db = litdb.compile_regex_multi(ex, fl, ids, engine=litdb.ENGINE_MCCLELLAN_WIDE)
+    t, has_wide, wide_limit, heads = wide_header(db)
+    assert t == 7 and has_wide == 1 and heads >= 10 and wide_limit > 0
+    rdb = ref.deserialize(db.serialize())
+    rs = ref.alloc_scratch(rdb)
+    n = 0
+    for text in texts:
+        rv, got = ref.scan(rdb, rs, text)
+        assert rv == 0
+        assert sorted(set(got), key=lambda x: (x[1], x[0])) == regen.brute_force(ex, fl, ids, text), text
+        assert oracle_port.scan(db, text) == (0, got)
+        n += len(got)
+    assert n > 40
+    # the same set without wide states reports the same
+    plain = litdb.compile_regex_multi(ex, fl, ids, engine=litdb.ENGINE_MCCLELLAN)
+    assert wide_header(plain)[1] == 0 and db.size < plain.size

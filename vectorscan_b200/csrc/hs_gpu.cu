@@ -1310,6 +1310,51 @@ void build_mcsheng_tables(const DbView &v, u32 at, std::vector<u8> &out, DevMcc 
     D.has_sherman = M.wide16 && M.sherman_limit < M.states ? 1u : 0u;
 }
 
+// A 16-bit McClellan engine with WIDE states (mcclellan_internal.h:53-61; runtime doWide16, mcclellan_common_impl.h:86-188):
+// ids >= wide_limit stand for chains of states that the compiler stored as {symbols, successor after the last symbol,
+// one shared failure row}.  At upload every chain position gets a table row again -- on its own symbol the next position
+// (the last one: the stored successor), on any other symbol the failure row's entry -- and, while a complete table is
+// being made anyway, every Sherman state its full row (daddy's row with the listed exceptions), so the engine is stepped
+// by the branch-free k_mcclellan.  Chain position j of head h: j = 0 keeps id h, the others are numbered behind the
+// heads.  The mstate_aux array is copied behind the table with empty records for the wide ids (they never accept, and
+// the end-of-data check of a scan that stops inside a wide state reports nothing, mcclellan.c:615).
+void build_wide_tables(const DbView &v, u32 at, std::vector<u8> &out, DevMcc &D) {
+    namespace mc = mcclellan;
+    const DbView::Mcc &M = v.mcc;
+    const u32 rows = M.wide_limit + M.wide_rows, width = 1u << M.as;
+    const size_t tab_bytes = (size_t)rows * width * 2, aux_at = round_up(tab_bytes, 16);
+    out.assign(aux_at + (size_t)rows * mc::aux::SIZE, 0);
+    auto put = [&](u32 row, u32 cp, u32 e) { const size_t i = ((size_t)row << M.as) + cp; out[2 * i] = (u8)e; out[2 * i + 1] = (u8)(e >> 8); };
+    std::memcpy(out.data(), v.bc + M.tab_off, M.tab_bytes);                      // rows below sherman_limit
+    for (u32 st = M.sherman_limit; st < M.wide_limit; st++) {                    // doSherman16, mcclellan_common_impl.h:54-84
+        const u8 *sh = v.bc + M.sherman_off + (size_t)mc::SHERMAN_FIXED_SIZE * (st - M.sherman_limit);
+        const u32 len = sh[mc::SHERMAN_LEN_OFFSET], daddy = rd16(sh, mc::SHERMAN_DADDY_OFFSET);
+        std::memcpy(out.data() + ((size_t)st << M.as) * 2, out.data() + ((size_t)daddy << M.as) * 2, (size_t)width * 2);
+        for (u32 k = 0; k < len; k++) put(st, sh[mc::SHERMAN_CHARS_OFFSET + k], rd16(sh, mc::SHERMAN_CHARS_OFFSET + len + 2 * k));
+    }
+    u32 inner = M.wide_limit + M.wide_number;                                    // next id of a chain position behind a head
+    for (u32 k = 0; k < M.wide_number; k++) {
+        const u8 *we = v.bc + M.wide_off + rd32(v.bc, M.wide_off + 4 + 4 * k);
+        const u32 w = rd16(we, 0);
+        const u8 *sym = we + 2, *tr = we + 2 + ((w + 1) & ~1u);
+        for (u32 j = 0; j < w; j++) {
+            const u32 row = j ? inner + j - 1 : M.wide_limit + k;
+            for (u32 cp = 0; cp < M.n_alpha; cp++) put(row, cp, rd16(tr, 2 + 2 * (size_t)cp));
+            put(row, sym[j], j + 1 < w ? inner + j : rd16(tr, 0));
+        }
+        inner += w - 1;
+    }
+    std::memcpy(out.data() + aux_at, v.bc + M.aux_off, (size_t)M.wide_limit * mc::aux::SIZE);
+    D = DevMcc{};
+    D.tab_abs = at; D.tab_bytes = (u32)tab_bytes; D.remap_abs = M.remap_off;
+    D.nfa_abs = v.nfa_off; D.aux_abs = at + (u32)aux_at; D.sherman_abs = 0;
+    D.wide16 = 1; D.as = M.as; D.start = M.start; D.accept_limit_8 = M.accept_limit_8;
+    D.sherman_limit = rows; D.single = M.single; D.arb_report = M.arb_report;
+    D.accepts_eod = (v.nfa_flags & nfa::ACCEPTS_EOD) ? 1u : 0u;
+    D.in_smem = MCC_RM_BYTES + (size_t)D.tab_bytes + 8 <= MCC_SMEM_MAX ? 1u : 0u;
+    D.has_sherman = 0;
+}
+
 // Device tables of ONE outfix engine (im->view describes it; im->dev.bc is the uploaded bytecode it lives in).
 hs_error_t build_engine_image(hs_gpu_scratch *s, DbImage *im) {
     const DbView &v = im->view;
@@ -1330,8 +1375,8 @@ hs_error_t build_engine_image(hs_gpu_scratch *s, DbImage *im) {
         L.o_squash = t.o_squash; L.o_meta = t.o_meta; L.o_masks = t.o_masks; L.o_base = t.o_base;
         L.total_words = t.total_words; L.accept_abs = t.accept_abs; L.accept_eod_abs = t.accept_eod_abs;
         L.nfa_flags = t.nfa_flags;
-    } else if (v.kind == ENG_SHENG || (v.kind == ENG_MCCLELLAN && v.mcc.sheng_end)) {
-        // im->mcc was filled by build_sheng_tables / build_mcsheng_tables with the image
+    } else if (v.kind == ENG_SHENG || (v.kind == ENG_MCCLELLAN && (v.mcc.sheng_end || v.mcc.has_wide))) {
+        // im->mcc was filled by build_sheng_tables / build_mcsheng_tables / build_wide_tables with the image
     } else if (v.kind == ENG_MCCLELLAN) {
         // the engine is stepped straight from the uploaded bytecode (mcclellan.cuh copies the table to shared memory)
         const DbView::Mcc &M = v.mcc;
@@ -1358,7 +1403,7 @@ hs_error_t build_dfa_packs(hs_gpu_scratch *s, DbImage *im) {
     auto packable = [&](size_t q) {
         const DbImage *e = im->subs[q];
         const DbView::Mcc &M = e->view.mcc;
-        return e->view.kind == ENG_MCCLELLAN && !M.sheng_end && !e->mcc.has_sherman && !e->mcc.accepts_eod && M.states <= mcclellan::STATE_MASK;
+        return e->view.kind == ENG_MCCLELLAN && !M.sheng_end && !M.has_wide && !e->mcc.has_sherman && !e->mcc.accepts_eod && M.states <= mcclellan::STATE_MASK;
     };
     auto joint = [&](const std::vector<size_t> &members, std::vector<u32> &cls_of) {  // -> number of joint classes
         std::map<std::vector<u8>, u32> seen;
@@ -1475,15 +1520,19 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
     // (Sheng outfixes of a multi-engine database get their tables one behind the other in the same area.)
     std::vector<u8> derived;
     const u32 derived_at = (u32)round_up(v.bc_len, 256) + 256;
-    auto hybrid = [](const DbView &e) { return e.kind == ENG_MCCLELLAN && e.mcc.sheng_end != 0; };   // McSheng: rows made here too
+    // McSheng and McClellan with wide states: their complete tables are made here too
+    auto hybrid = [](const DbView &e) { return e.kind == ENG_MCCLELLAN && (e.mcc.sheng_end != 0 || e.mcc.has_wide); };
+    auto build_hybrid = [](const DbView &e, u32 at, std::vector<u8> &out, DevMcc &D) {
+        if (e.mcc.has_wide) build_wide_tables(e, at, out, D); else build_mcsheng_tables(e, at, out, D);
+    };
     if (v.kind == ENG_SHENG) build_sheng_tables(v, derived_at, derived, im->mcc);
-    if (hybrid(v)) build_mcsheng_tables(v, derived_at, derived, im->mcc);
+    if (hybrid(v)) build_hybrid(v, derived_at, derived, im->mcc);
     std::vector<DevMcc> sub_sheng(v.engines.size());
     for (size_t q = 0; q < v.engines.size(); q++) {
         if (v.engines[q].kind != ENG_SHENG && !hybrid(v.engines[q])) continue;
         std::vector<u8> one;
         const u32 at = derived_at + (u32)round_up(derived.size(), 256);
-        if (hybrid(v.engines[q])) build_mcsheng_tables(v.engines[q], at, one, sub_sheng[q]);
+        if (hybrid(v.engines[q])) build_hybrid(v.engines[q], at, one, sub_sheng[q]);
         else build_sheng_tables(v.engines[q], at, one, sub_sheng[q]);
         derived.resize(at - derived_at, 0);
         derived.insert(derived.end(), one.begin(), one.end());

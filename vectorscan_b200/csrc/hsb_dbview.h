@@ -53,6 +53,9 @@ struct DbView {
         u32 wide16 = 0, as = 0, states = 0, start = 0, accept_limit_8 = 0, sherman_limit = 0, single = 0, arb_report = 0;
         u32 remap_off = 0;                  // absolute offset of remap[256]
         u32 sheng_end = 0, masks_off = 0;   // McSheng: first state outside the Sheng region, absolute offset of sheng_masks
+        // wide states (16-bit McClellan): ids >= wide_limit are heads of symbol chains stored at wide_off (absolute);
+        // wide_rows = sum of the chains' widths (every chain position becomes a table row on the device)
+        u32 has_wide = 0, wide_limit = 0, wide_off = 0, wide_number = 0, wide_rows = 0, n_alpha = 0;
     } mcc;
     // single-outfix Sheng DFA (kind == ENG_SHENG), absolute bytecode offsets
     struct Sheng { u32 sh_off = 0, aux_off = 0, n_states = 0, anchored = 0, flags = 0, report = 0, nfa_type = 17; } sheng;
@@ -171,7 +174,7 @@ inline int census_program(const DbView &d, u32 prog, std::string &why, u32 &max_
 
 
 // Single-outfix McClellan DFA (mcclellan_internal.h:77-101).  Accepted: 8- and 16-bit tables, Sherman states,
-// per-state report lists, EOD accepts.  Refused: wide states (has_wide).  Accel structures are skip-ahead only.
+// per-state report lists, EOD accepts, wide states of 16-bit engines.  Accel structures are skip-ahead only.
 inline int parse_mcclellan(DbView &d, std::string &why) {
     namespace mc = mcclellan;
     namespace ms = mcsheng;
@@ -188,7 +191,8 @@ inline int parse_mcclellan(DbView &d, std::string &why) {
     const u8 *m = r + M.m_off;
     auto n_range = [&](size_t off, size_t len) { return off <= d.nfa_len && len <= d.nfa_len - off; };  // relative to NFA
     M.wide16 = type == nfa::MCCLELLAN_16 || type == nfa::MCSHENG_16;
-    if (!hybrid && rd8(m, mc::has_wide)) { why = "McClellan wide states are not supported yet"; return E_ARCH; }
+    M.has_wide = !hybrid && rd8(m, mc::has_wide) ? 1 : 0;
+    if (M.has_wide && !M.wide16) { why = "wide states in an 8-bit McClellan engine are not supported yet"; return E_ARCH; }
     M.as = rd8(m, F(mc::alphaShift, ms::alphaShift));
     M.states = rd16(m, mc::state_count);
     M.start = rd16(m, mc::start_anchored);
@@ -200,22 +204,38 @@ inline int parse_mcclellan(DbView &d, std::string &why) {
     M.sheng_end = hybrid ? rd16(m, ms::sheng_end) : 0;
     M.masks_off = hybrid ? M.m_off + (u32)ms::sheng_masks : 0;
     if (M.as > 8 || !M.states || M.start >= M.states || M.sherman_limit > M.states) { why = "McClellan header inconsistent"; return E_INVALID; }
+    // states with an mstate_aux record and a Sherman slot end at wide_limit; ids a table may name end behind the wide heads
+    u32 n_aux = M.states, ref_limit = M.states;
+    if (M.has_wide) {
+        M.wide_limit = rd16(m, mc::wide_limit);
+        const u32 w_rel = rd32(m, mc::wide_offset);
+        if (M.wide_limit < M.sherman_limit || M.wide_limit >= M.states || (w_rel & 1) || !n_range(w_rel, 8)) { why = "McClellan wide region out of range"; return E_INVALID; }
+        M.wide_off = d.nfa_off + w_rel;
+        M.wide_number = rd16(r, M.wide_off + 2);
+        if (rd8(r, M.wide_off) != 2 || !M.wide_number || M.wide_limit + M.wide_number > M.states || !n_range(w_rel, 4 + 4 * (size_t)M.wide_number)) {
+            why = "McClellan wide region malformed"; return E_INVALID;
+        }
+        n_aux = M.wide_limit;
+        ref_limit = M.wide_limit + M.wide_number;
+        for (u32 c = 0; c < 256; c++) M.n_alpha = std::max<u32>(M.n_alpha, rd8(r, M.m_off + (u32)mc::remap + c) + 1u);
+    }
     if (M.wide16 && M.states - 1 > mc::STATE_MASK) { why = "McClellan state count out of range"; return E_INVALID; }
     if (!M.wide16 && (M.states > 256 || M.accept_limit_8 > M.states)) { why = "McClellan8 limits out of range"; return E_INVALID; }
     if (hybrid && (M.sheng_end < 2 || M.sheng_end > ms::MAX_SHENG_STATES + 1 || M.sheng_end > M.sherman_limit)) { why = "McSheng region out of range"; return E_INVALID; }
     const u32 rows = (M.wide16 ? M.sherman_limit : M.states) - M.sheng_end;   // the table has no rows for the Sheng region
+    if (M.has_wide && M.start >= ref_limit) { why = "McClellan start state out of range"; return E_INVALID; }
     M.tab_off = M.m_off + (u32)HDR;
     M.tab_bytes = (rows << M.as) * (M.wide16 ? 2u : 1u);
     if (!n_range(nfa::SIZE + HDR, M.tab_bytes)) { why = "McClellan successor table truncated"; return E_INVALID; }
     for (u32 c = 0; c < 256; c++)
         if (rd8(r, M.remap_off + c) >= (1u << M.as)) { why = "McClellan remap out of range"; return E_INVALID; }
     const u32 aux_rel = rd32(m, mc::aux_offset);
-    if (!n_range(aux_rel, (size_t)M.states * mc::aux::SIZE)) { why = "McClellan aux array truncated"; return E_INVALID; }
+    if (!n_range(aux_rel, (size_t)n_aux * mc::aux::SIZE)) { why = "McClellan aux array truncated"; return E_INVALID; }
     M.aux_off = d.nfa_off + aux_rel;
     // every table entry names a state
     for (u32 i = 0; i < (rows << M.as); i++) {
         const u32 e = M.wide16 ? (rd16(r, M.tab_off + 2 * (size_t)i) & mc::STATE_MASK) : rd8(r, M.tab_off + i);
-        if (e >= M.states) { why = "McClellan successor out of range"; return E_INVALID; }
+        if (e >= ref_limit) { why = "McClellan successor out of range"; return E_INVALID; }
     }
     if (hybrid) {
         // mask byte: < sheng_end - 1 a region state (id - 1), == sheng_end - 1 dead, above it a state id outside the region
@@ -225,9 +245,9 @@ inline int parse_mcclellan(DbView &d, std::string &why) {
         for (u32 st = 1; st < M.sheng_end; st++)
             if (rd32(r, M.aux_off + st * mc::aux::SIZE + mc::aux::accept)) { why = "McSheng region state with reports"; return E_INVALID; }
     }
-    if (M.wide16 && M.sherman_limit < M.states) {
+    if (M.wide16 && M.sherman_limit < n_aux) {
         const u32 sh_rel = rd32(m, mc::sherman_offset);
-        const size_t nsh = M.states - M.sherman_limit;
+        const size_t nsh = n_aux - M.sherman_limit;
         if ((sh_rel & 15) || !n_range(sh_rel, nsh * mc::SHERMAN_FIXED_SIZE)) { why = "McClellan Sherman region truncated"; return E_INVALID; }
         M.sherman_off = d.nfa_off + sh_rel;
         for (size_t k = 0; k < nsh; k++) {
@@ -238,12 +258,29 @@ inline int parse_mcclellan(DbView &d, std::string &why) {
                 why = "McClellan Sherman state malformed"; return E_INVALID;
             }
             for (u32 q = 0; q < len; q++)
-                if ((rd16(sh, mc::SHERMAN_CHARS_OFFSET + len + 2 * q) & mc::STATE_MASK) >= M.states) { why = "McClellan Sherman successor out of range"; return E_INVALID; }
+                if ((rd16(sh, mc::SHERMAN_CHARS_OFFSET + len + 2 * q) & mc::STATE_MASK) >= ref_limit) { why = "McClellan Sherman successor out of range"; return E_INVALID; }
         }
+    }
+    if (M.has_wide) {
+        // every entry: u16 width; u8 symbols[width]; pad to 2; u16 next; u16 failure[n_alpha]   (mcclellan_internal.h:53-61)
+        for (u32 k = 0; k < M.wide_number; k++) {
+            const u32 eo = rd32(r, M.wide_off + 4 + 4 * k);
+            const size_t e_rel = (size_t)(M.wide_off - d.nfa_off) + eo;
+            if ((eo & 1) || !n_range(e_rel, 2)) { why = "McClellan wide entry out of range"; return E_INVALID; }
+            const u32 width = rd16(r, M.wide_off + eo);
+            const size_t tr = 2 + (((size_t)width + 1) & ~(size_t)1);
+            if (!width || !n_range(e_rel, tr + 2 * (1 + (size_t)M.n_alpha))) { why = "McClellan wide entry truncated"; return E_INVALID; }
+            for (u32 q = 0; q < width; q++)
+                if (rd8(r, M.wide_off + eo + 2 + q) >= (1u << M.as)) { why = "McClellan wide symbol out of range"; return E_INVALID; }
+            for (u32 q = 0; q < 1 + M.n_alpha; q++)
+                if ((rd16(r, M.wide_off + eo + tr + 2 * q) & mc::STATE_MASK) >= ref_limit) { why = "McClellan wide successor out of range"; return E_INVALID; }
+            M.wide_rows += width;
+        }
+        if (M.wide_limit + M.wide_rows - 1 > mc::STATE_MASK) { why = "McClellan wide states: more than 16384 table rows"; return E_ARCH; }
     }
     std::set<u32> progs;
     if (M.single) progs.insert(M.arb_report);
-    for (u32 st = 0; st < M.states; st++) {
+    for (u32 st = 0; st < n_aux; st++) {
         for (size_t f : {mc::aux::accept, mc::aux::accept_eod}) {
             const u32 rl = rd32(r, M.aux_off + st * mc::aux::SIZE + f);
             if (!rl) continue;

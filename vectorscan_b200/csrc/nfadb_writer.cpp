@@ -513,8 +513,13 @@ void minimise(Dfa &d) {
 // (8-bit).  ReportIDs are Rose report-program offsets, as for every outfix engine (roseReportAdaptor).
 // `sherman`: compress states that differ from the start state or from their discovery parent in at most
 // MAX_SHERMAN_LIST_LEN symbols into 32-byte Sherman states (16-bit engines only).
+// `wide_states` (16-bit engines): chains of at least 8 non-accepting states, each entered only from its predecessor and
+// all leaving the chain the same way (one failure row), are stored as ONE wide head state -- the chain's symbols, the
+// successor after the last one, the shared failure row (mcclellancompile.cpp:773-838, struct layout
+// mcclellan_internal.h:53-61, runtime doWide16 mcclellan_common_impl.h:86-188) -- the reference's compression of
+// literal-like runs.  Chain states have no table row and no mstate_aux.
 int emit_mcclellan(const Dfa &d, const u8 *reach_map, const std::vector<u32> &program_of, bool sherman,
-                   u32 min_width, Buf &eng, u32 &state_bytes, std::string &err) {
+                   u32 min_width, Buf &eng, u32 &state_bytes, std::string &err, bool wide_states = false) {
     namespace mc = mcclellan;
     const u32 n = (u32)d.next.size();
     const u32 alpha = d.n_sym + 1;  // + TOP, the last symbol (never produced by remap)
@@ -527,7 +532,56 @@ int emit_mcclellan(const Dfa &d, const u8 *reach_map, const std::vector<u32> &pr
     std::vector<u32> impl(n, 0);
     std::vector<u32> daddy(n, 0);
     std::vector<u8> is_sherman(n, 0);
-    u32 accel_limit_8 = 0, accept_limit_8 = 0, sherman_limit = 0, n_real = n;
+    u32 accel_limit_8 = 0, accept_limit_8 = 0, sherman_limit = 0, n_real = n, wide_limit = 0;
+    // ---- wide chains ----
+    std::vector<std::vector<u32>> chain_states, chain_syms;
+    std::vector<u32> chain_target;    // successor after the chain's last symbol
+    std::vector<std::vector<u32>> chain_fail;   // the shared failure row, one successor per symbol
+    std::vector<u8> in_chain(n, 0);   // 1 head, 2 inner
+    if (wide16 && wide_states) {
+        // inner candidates: non-accepting, not a start state, entered by exactly one (state, symbol) edge and not named
+        // as the successor of an earlier chain (`pinned`: such a state must keep its table row)
+        std::vector<u32> in_edges(n, 0), pred(n, 0);
+        std::vector<u8> pinned(n, 0);
+        for (u32 q = 0; q < n; q++)
+            for (u32 k = 0; k < d.n_sym; k++) { const u32 t = d.next[q][k]; in_edges[t]++; pred[t] = q; }
+        auto plain = [&](u32 q) { return q && d.reports[q].empty() && d.reports_eod[q].empty() && q != d.start_anchored && q != d.start_floating; };
+        for (u32 h = 1; h < n; h++) {
+            if (!plain(h) || in_chain[h]) continue;
+            std::vector<u32> st{h}, sy;
+            std::vector<int> F(d.n_sym, -1);   // successor on a symbol that is not the state's own chain symbol
+            u32 cur = h;
+            while (st.size() < 4096) {
+                int own = -1;
+                for (u32 k = 0; k < d.n_sym && own < 0; k++) {
+                    const u32 t = d.next[cur][k];
+                    if (plain(t) && in_edges[t] == 1 && pred[t] == cur && !in_chain[t] && !pinned[t] && t != h) own = (int)k;
+                }
+                if (own < 0) break;
+                bool consistent = true;
+                for (u32 k = 0; k < d.n_sym && consistent; k++)
+                    if (k != (u32)own && F[k] >= 0 && (u32)F[k] != d.next[cur][k]) consistent = false;
+                if (!consistent) break;
+                for (u32 k = 0; k < d.n_sym; k++) if (k != (u32)own) F[k] = (int)d.next[cur][k];
+                sy.push_back((u32)own);
+                cur = d.next[cur][own];
+                st.push_back(cur);
+            }
+            const u32 w = (u32)sy.size();   // st holds w chain states and, last, the state the chain leads to
+            if (w < 8) continue;
+            const u32 target = st[w];
+            st.resize(w);
+            pinned[target] = 1;
+            in_chain[st[0]] = 1;
+            for (u32 j = 1; j < w; j++) in_chain[st[j]] = 2;
+            std::vector<u32> fail(d.n_sym);
+            for (u32 k = 0; k < d.n_sym; k++) fail[k] = F[k] >= 0 ? (u32)F[k] : target;   // mcclellancompile.cpp:815-829
+            chain_states.push_back(st);
+            chain_syms.push_back(sy);
+            chain_target.push_back(target);
+            chain_fail.push_back(fail);
+        }
+    }
     if (!wide16) {
         u32 j = 1;
         for (u32 i = 1; i < n; i++) if (d.reports[i].empty()) impl[i] = j++;
@@ -542,9 +596,9 @@ int emit_mcclellan(const Dfa &d, const u8 *reach_map, const std::vector<u32> &pr
             for (u32 q = 0; q < n; q++)  // ids are already in discovery order (minimise)
                 for (u32 k = 0; k < d.n_sym; k++) { const u32 t = d.next[q][k]; if (!seen[t]) { seen[t] = 1; parent[t] = q; } }
             for (u32 i = 1; i < n; i++) {
-                if (i == d.start_anchored || i == d.start_floating) continue;
+                if (i == d.start_anchored || i == d.start_floating || in_chain[i]) continue;
                 for (u32 cand : {d.start_floating ? d.start_floating : d.start_anchored, parent[i]}) {
-                    if (!cand || cand == i || is_sherman[cand]) continue;
+                    if (!cand || cand == i || is_sherman[cand] || in_chain[cand]) continue;   // a daddy needs a table row
                     u32 diff = 0;
                     for (u32 k = 0; k < d.n_sym; k++) diff += d.next[i][k] != d.next[cand][k];
                     if (diff <= mc::MAX_SHERMAN_LIST_LEN) { is_sherman[i] = 1; daddy[i] = cand; break; }
@@ -554,11 +608,16 @@ int emit_mcclellan(const Dfa &d, const u8 *reach_map, const std::vector<u32> &pr
             // decided before its children; this pass only guards that invariant
             for (u32 i = 1; i < n; i++) if (is_sherman[i] && is_sherman[daddy[i]]) is_sherman[i] = 0;
         }
-        u32 j = 1;
-        for (u32 i = 1; i < n; i++) if (!is_sherman[i]) impl[i] = j++;
+        u32 j = 1;   // allocateFSN16: normal, Sherman, wide heads, the other chain states
+        for (u32 i = 1; i < n; i++) if (!is_sherman[i] && !in_chain[i]) impl[i] = j++;
         sherman_limit = n_real = j;
         for (u32 i = 1; i < n; i++) if (is_sherman[i]) impl[i] = j++;
+        wide_limit = j;
+        for (auto &c : chain_states) impl[c[0]] = j++;
+        for (auto &c : chain_states) for (size_t q = 1; q < c.size(); q++) impl[c[q]] = j++;
     }
+    const bool has_wide = !chain_states.empty();
+    const u32 n_aux = has_wide ? wide_limit : n;   // wide states have no mstate_aux (mcclellancompile.cpp:641)
     // ---- report lists ----
     std::map<std::vector<u32>, u32> list_id;  // sorted program offsets -> index
     std::vector<std::vector<u32>> lists;
@@ -591,14 +650,21 @@ int emit_mcclellan(const Dfa &d, const u8 *reach_map, const std::vector<u32> &pr
     // ---- sizes (mcclellancompile.cpp:637-652 / :934-940) ----
     const size_t ent = wide16 ? 2 : 1;
     const size_t tran_size = ((size_t)1 << as) * ent * n_real;
-    const size_t aux_size = mc::aux::SIZE * (size_t)n;
+    const size_t aux_size = mc::aux::SIZE * (size_t)n_aux;
     const size_t aux_offset = round_up(nfa::SIZE + mc::SIZE + tran_size, 16);
     size_t rl_size = 0;
     for (auto &l : lists) rl_size += 4 + 4 * l.size();
     const size_t accel_offset = round_up(aux_offset + aux_size + rl_size, 32);
     const size_t sherman_offset = round_up(accel_offset, 16);
-    const size_t sherman_size = wide16 ? (size_t)mc::SHERMAN_FIXED_SIZE * (n - n_real) : 0;
-    const size_t total = round_up(sherman_offset + sherman_size, 16);
+    const size_t sherman_size = wide16 ? (size_t)mc::SHERMAN_FIXED_SIZE * ((has_wide ? wide_limit : n) - n_real) : 0;
+    const size_t wide_offset = round_up(sherman_offset + sherman_size, 16);
+    size_t wide_size = 0;   // calcWideRegionSize, mcclellancompile.cpp:522-539
+    if (has_wide) {
+        wide_size = 4 + 4 * chain_states.size();
+        for (auto &c : chain_syms) wide_size += round_up(c.size(), 2) + 2 * ((size_t)d.n_sym + 1) + 2;
+        wide_size = round_up(wide_size, 16);
+    }
+    const size_t total = round_up(wide_offset + wide_size, 16);
     eng.grow(total);
     eng.align(CACHELINE);
     u8 *nh = eng.at(0), *m = eng.at(nfa::SIZE);
@@ -607,6 +673,7 @@ int emit_mcclellan(const Dfa &d, const u8 *reach_map, const std::vector<u32> &pr
     wr8(nh, nfa::type, wide16 ? nfa::MCCLELLAN_16 : nfa::MCCLELLAN_8);
     wr32(nh, nfa::queueIndex, 0);
     wr32(nh, nfa::nPositions, n);
+    if (has_wide) state_bytes += 2;   // the offset inside a wide state is kept beside the state (mcclellancompile.cpp:345-349)
     wr32(nh, nfa::scratchStateSize, state_bytes);
     wr32(nh, nfa::streamStateSize, state_bytes);
     wr32(nh, nfa::maxWidth, 0);
@@ -621,11 +688,12 @@ int emit_mcclellan(const Dfa &d, const u8 *reach_map, const std::vector<u32> &pr
     wr16(m, mc::accel_limit_8, (u16)accel_limit_8);
     wr16(m, mc::accept_limit_8, (u16)accept_limit_8);
     wr16(m, mc::sherman_limit, (u16)sherman_limit);
-    wr16(m, mc::wide_limit, wide16 ? (u16)n : 0);
+    wr16(m, mc::wide_limit, has_wide ? (u16)wide_limit : wide16 ? (u16)n : 0);
+    wr32(m, mc::wide_offset, has_wide ? (u32)wide_offset : 0);
     wr8(m, mc::alphaShift, (u8)as);
     wr8(m, mc::flags, single ? mc::FLAG_SINGLE : 0);
     wr8(m, mc::has_accel, 0);
-    wr8(m, mc::has_wide, 0);
+    wr8(m, mc::has_wide, has_wide ? 1 : 0);
     std::memcpy(m + mc::remap, reach_map, 256);
     wr32(m, mc::arb_report, all_reports.empty() ? 0 : *all_reports.begin());
     wr32(m, mc::accel_offset, (u32)(accel_offset - nfa::SIZE));
@@ -642,12 +710,29 @@ int emit_mcclellan(const Dfa &d, const u8 *reach_map, const std::vector<u32> &pr
     }
     // aux + successor table
     u8 *succ = m + mc::SIZE;
-    auto flagged = [&](u32 t) -> u32 {  // markEdges, mcclellancompile.cpp:188-214
+    auto flagged = [&](u32 t) -> u32 {  // markEdges, mcclellancompile.cpp:188-284: wide states carry no flags
         u32 v = impl[t];
-        if (wide16 && !d.reports[t].empty()) v |= mc::ACCEPT_FLAG;
+        if (wide16 && !in_chain[t] && !d.reports[t].empty()) v |= mc::ACCEPT_FLAG;
         return v;
     };
+    if (has_wide) {
+        u8 *wb = eng.at(wide_offset);
+        wb[0] = 2;  // WIDE_STATE
+        wr16(wb, 2, (u16)chain_states.size());
+        size_t o = 4 + 4 * chain_states.size();
+        for (size_t c = 0; c < chain_states.size(); c++) {   // heads were numbered in this order
+            const u32 w = (u32)chain_syms[c].size();
+            wr32(wb, 4 + 4 * c, (u32)o);
+            wr16(wb, o, (u16)w);
+            for (u32 q = 0; q < w; q++) wb[o + 2 + q] = (u8)chain_syms[c][q];
+            size_t t = o + 2 + round_up(w, 2);
+            wr16(wb, t, (u16)flagged(chain_target[c]));
+            for (u32 k = 0; k < d.n_sym; k++) wr16(wb, t + 2 + 2 * (size_t)k, (u16)flagged(chain_fail[c][k]));
+            o = t + 2 * ((size_t)d.n_sym + 1);
+        }
+    }
     for (u32 i = 0; i < n; i++) {
+        if (in_chain[i]) continue;   // no row, no aux
         const u32 id = impl[i];
         u8 *a = eng.at(aux_offset + mc::aux::SIZE * (size_t)id);
         wr32(a, mc::aux::accept, list_of[i] == ~0u ? 0 : list_off[list_of[i]]);
@@ -1177,7 +1262,7 @@ int emit_engine(const Automaton &am, unsigned engine, const std::vector<u32> &pr
     // outfix engines of multi-engine databases: a DFA of at most 16 states is laid out as a Sheng engine, which is what the
     // reference compiler tries first for every DFA (shengCompile before mcclellanCompile, src/rose/rose_build_bytecode.cpp
     // buildOutfix / getDfa)
-    if (sheng_if_small && (engine == HSB_REGEX_ENGINE_MCCLELLAN || engine == HSB_REGEX_ENGINE_MCSHENG) && dfa.next.size() <= 16)
+    if (sheng_if_small && (engine == HSB_REGEX_ENGINE_MCCLELLAN || engine == HSB_REGEX_ENGINE_MCSHENG || engine == HSB_REGEX_ENGINE_MCCLELLAN_WIDE) && dfa.next.size() <= 16)
         engine = HSB_REGEX_ENGINE_SHENG;
     if (engine == HSB_REGEX_ENGINE_MCSHENG) {
         const int mrv = emit_mcsheng(dfa, reach_map, program_of, am.min_width, eng, stream_state, err);
@@ -1188,7 +1273,8 @@ int emit_engine(const Automaton &am, unsigned engine, const std::vector<u32> &pr
     }
     const int rv = engine == HSB_REGEX_ENGINE_SHENG || engine == HSB_REGEX_ENGINE_SHENG_WIDE
                        ? emit_sheng(dfa, reach_map, program_of, am.min_width, eng, stream_state, err, engine == HSB_REGEX_ENGINE_SHENG_WIDE)
-                       : emit_mcclellan(dfa, reach_map, program_of, engine == HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN, am.min_width, eng, stream_state, err);
+                       : emit_mcclellan(dfa, reach_map, program_of, engine == HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN || engine == HSB_REGEX_ENGINE_MCCLELLAN_WIDE,
+                                        am.min_width, eng, stream_state, err, engine == HSB_REGEX_ENGINE_MCCLELLAN_WIDE);
     scratch_state = stream_state;
     return rv;
 }
@@ -1198,7 +1284,7 @@ int emit_engine(const Automaton &am, unsigned engine, const std::vector<u32> &pr
 namespace hsb_nfadb {
 
 int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &image, std::string &err) {
-    if (engine > HSB_REGEX_ENGINE_MCSHENG) { err = "unknown engine"; return HSB_LIT_COMPILER_ERROR; }
+    if (engine > HSB_REGEX_ENGINE_MCCLELLAN_WIDE) { err = "unknown engine"; return HSB_LIT_COMPILER_ERROR; }
     if (pats.empty()) { err = "no expressions"; return HSB_LIT_COMPILER_ERROR; }
     // ---- 1. parse every pattern, build one automaton -------------------------------------------------
     std::vector<Parsed> parsed;
@@ -1334,7 +1420,7 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
 int build_outfix_engines(const std::vector<Pattern> &pats, unsigned engine, u32 dfa_states,
                          const std::vector<u32> &program_of, std::vector<EngineBlob> &out, std::string &err) {
     if (engine != HSB_REGEX_ENGINE_LIMEX && engine != HSB_REGEX_ENGINE_MCCLELLAN && engine != HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN &&
-        engine != HSB_REGEX_ENGINE_MCSHENG) {
+        engine != HSB_REGEX_ENGINE_MCSHENG && engine != HSB_REGEX_ENGINE_MCCLELLAN_WIDE) {
         err = "outfix engines are LimEx, McClellan or McSheng";
         return HSB_LIT_COMPILER_ERROR;
     }
