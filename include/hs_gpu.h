@@ -94,7 +94,9 @@ hs_error_t hs_gpu_scan(const hs_database_t *db, const char *data, unsigned int l
 
 /* On a BLOCK-mode database: a batch of `count` INDEPENDENT block-mode scans -- the loop of hs_scan calls that
  * examples/pcapscan.cc:305-316 and tools/hsbench/main.cpp:486-512 run -- with the parameter list of hs_scan_vector
- * (src/hs_runtime.h:522-527).  Offsets are per buffer.  Matches are delivered buffer by buffer in index order.
+ * (src/hs_runtime.h:522-527).  Offsets are per buffer.  Matches are delivered buffer by buffer in index order.  A
+ * non-zero return of the callback ends the deliveries of THAT buffer only -- as it would end that packet's hs_scan in the
+ * loop -- and the call returns HS_SCAN_TERMINATED after the remaining buffers have been delivered.
  * On a VECTORED-mode database (HS_MODE_VECTORED, pure-literal databases): the reference's hs_scan_vector itself
  * (src/runtime.c:1106-1174) -- the buffers are consecutive blocks of ONE stream: a match may straddle blocks, offsets
  * run on across them, single-match ids stay exhausted to the end of the call; matches are delivered in (to, id) order

@@ -2756,14 +2756,23 @@ static u32 database_mode(const hs_database_t *db) {
     return rd32(p + rd32(p, db::bytecode), rose::mode);  // offsets as parse_database reads them (hsb_dbview.h)
 }
 
-static hs_error_t deliver(hs_gpu_scratch *s, match_event_handler onEvent, void *context, void *const *contexts) {
+// `per_buffer` (batches of independent block scans): a non-zero return of the callback ends the deliveries of THAT buffer,
+// as it ends that packet's hs_scan in the loop this call replaces (src/runtime.c:459-461); the other buffers are still
+// delivered and the call returns HS_SCAN_TERMINATED at the end.  Otherwise (one stream) it ends the call.
+static hs_error_t deliver(hs_gpu_scratch *s, match_event_handler onEvent, void *context, void *const *contexts, bool per_buffer) {
     if (!onEvent) return HS_SUCCESS;  // matches suppressed, as with a NULL callback in the reference
     const hs_gpu_match_t *m = s->h_matches;
+    bool stopped = false;
     for (u64 i = 0; i < s->n_matches; i++) {
         void *ctx = contexts ? contexts[m[i].buffer] : context;
-        if (onEvent(m[i].id, 0, m[i].to, 0, ctx)) return HS_SCAN_TERMINATED;
+        if (onEvent(m[i].id, 0, m[i].to, 0, ctx)) {
+            if (!per_buffer) return HS_SCAN_TERMINATED;
+            stopped = true;
+            const u32 b = m[i].buffer;
+            while (i + 1 < s->n_matches && m[i + 1].buffer == b) i++;   // matches are sorted by buffer
+        }
     }
-    return HS_SUCCESS;
+    return stopped ? HS_SCAN_TERMINATED : HS_SUCCESS;
 }
 
 hs_error_t hs_gpu_scan_batch(const hs_database_t *db, const char *const *data, const unsigned int *length,
@@ -2779,7 +2788,7 @@ hs_error_t hs_gpu_scan_batch(const hs_database_t *db, const char *const *data, c
     DbImage *im = nullptr;
     rv = scan_host_batch(db, data, length, count, scratch, &im);
     if (rv != HS_SUCCESS) return rv;
-    return deliver(scratch, onEvent, nullptr, contexts);
+    return deliver(scratch, onEvent, nullptr, contexts, true);
 }
 
 hs_error_t hs_gpu_scan_vector(const hs_database_t *db, const char *const *data, const unsigned int *length,
@@ -2795,7 +2804,7 @@ hs_error_t hs_gpu_scan_vector(const hs_database_t *db, const char *const *data, 
     DbImage *im = nullptr;
     rv = scan_host_batch(db, data, length, count, scratch, &im);
     if (rv != HS_SUCCESS) return rv;
-    return deliver(scratch, onEvent, context, nullptr);
+    return deliver(scratch, onEvent, context, nullptr, database_mode(db) == MODE_BLOCK);
 }
 
 hs_error_t hs_gpu_scan_vector_ex(const hs_database_t *db, const char *const *data, const unsigned int *length,
