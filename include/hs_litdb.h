@@ -141,6 +141,9 @@ int hsb_compile_regex_multi(const char *const *expressions, const unsigned *flag
 #define HSB_REGEX_ENGINE_MCCLELLAN_WIDE 6u /* McClellan with Sherman states AND wide states: runs of >= 8 single-entry states
                                               that leave the run the same way are stored as one "wide" state (16-bit
                                               engines; mcclellan_internal.h:53-61, mcclellancompile.cpp:773-838) */
+#define HSB_REGEX_ENGINE_MCSHENG64 7u /* McSheng with a region of up to 64 states and 64-byte masks: struct mcsheng64,
+                                         MCSHENG_64_NFA_8 / _16 (mcsheng_internal.h:94-119); only an AVX512VBMI build of the
+                                         reference runtime executes it */
 int hsb_compile_regex_multi_ex(const char *const *expressions, const unsigned *flags, const unsigned *ids,
                                unsigned elements, unsigned mode, unsigned engine, hs_database_t **db,
                                char **error);

@@ -268,7 +268,9 @@ int main(void) {
  OF(struct mcsheng, accel_limit_8); OF(struct mcsheng, accept_limit_8); OF(struct mcsheng, sherman_limit);
  OF(struct mcsheng, alphaShift); OF(struct mcsheng, flags); OF(struct mcsheng, has_accel); OF(struct mcsheng, remap);
  OF(struct mcsheng, arb_report); OF(struct mcsheng, accel_offset); OF(struct mcsheng, sheng_masks);
- VAL(MCSHENG_NFA_8); VAL(MCSHENG_NFA_16);
+ VAL(MCSHENG_NFA_8); VAL(MCSHENG_NFA_16); VAL(MCSHENG_64_NFA_8); VAL(MCSHENG_64_NFA_16);
+ SZ(struct mcsheng64); OF(struct mcsheng64, sheng_end); OF(struct mcsheng64, remap); OF(struct mcsheng64, arb_report);
+ OF(struct mcsheng64, accel_offset); OF(struct mcsheng64, sheng_succ_masks);
  SZ(struct mcclellan); OF(struct mcclellan, state_count); OF(struct mcclellan, length); OF(struct mcclellan, start_anchored);
  OF(struct mcclellan, start_floating); OF(struct mcclellan, aux_offset); OF(struct mcclellan, sherman_offset);
  OF(struct mcclellan, sherman_end); OF(struct mcclellan, accel_limit_8); OF(struct mcclellan, accept_limit_8);

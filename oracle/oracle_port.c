@@ -596,8 +596,12 @@ static int ms_report(struct scan_state *s, const u8 *nfa, const u8 *m, u32 st, u
 }
 
 static int mcsheng_scan(struct scan_state *s, const u8 *nfa) {
-    const int wide16 = nfa[NFA_TYPE] == 20;
-    const u8 *m = nfa + NFA_SIZE, *succ = m + MS_SIZE;
+    /* types 23 / 24: struct mcsheng64 (mcsheng_internal.h:94-119, doSheng64 mcsheng.c:1489-1660): the same fields, up to 64
+     * region states, 64-byte masks at offset 320 */
+    const int wide64 = nfa[NFA_TYPE] == 23 || nfa[NFA_TYPE] == 24;
+    const int wide16 = nfa[NFA_TYPE] == 20 || nfa[NFA_TYPE] == 24;
+    const u32 masks_at = wide64 ? 320 : MS_MASKS, stride = wide64 ? 64 : 16;
+    const u8 *m = nfa + NFA_SIZE, *succ = m + (wide64 ? 320 + 256 * 64 : MS_SIZE);
     if (nfa[NFA_RACCEL]) { s->error = 1; return -1; }
     const u32 as = m[MS_ALPHA_SHIFT], accept_limit = rd16(m + MS_ACCEPT_LIMIT_8), sheng_end = rd16(m + MS_SHENG_END);
     const u32 sherman_limit = wide16 ? rd16(m + MS_SHERMAN_LIMIT) : 0xffffffffu;
@@ -607,7 +611,7 @@ static int mcsheng_scan(struct scan_state *s, const u8 *nfa) {
         const u8 c = s->buf[i];
         int accept;
         if (st < sheng_end) {
-            const u32 v = m[MS_MASKS + 16 * (size_t)c + st - 1];
+            const u32 v = m[masks_at + stride * (size_t)c + st - 1];
             st = v == sheng_end - 1 ? 0 : v < sheng_end - 1 ? v + 1 : v;
             accept = wide16 ? rd32(aux0 + (size_t)st * MC_AUX_SIZE + MC_AUX_ACCEPT) != 0 : st >= accept_limit;
         } else {
@@ -639,7 +643,7 @@ static int mcsheng_scan(struct scan_state *s, const u8 *nfa) {
 
 static void engine_scan(struct scan_state *s, const u8 *nfa) {
     if (nfa[NFA_TYPE] == 6 || nfa[NFA_TYPE] == 7) mcclellan_scan(s, nfa);
-    else if (nfa[NFA_TYPE] == 19 || nfa[NFA_TYPE] == 20) mcsheng_scan(s, nfa);
+    else if (nfa[NFA_TYPE] == 19 || nfa[NFA_TYPE] == 20 || nfa[NFA_TYPE] == 23 || nfa[NFA_TYPE] == 24) mcsheng_scan(s, nfa);
     else if (nfa[NFA_TYPE] == 17 || nfa[NFA_TYPE] == 21 || nfa[NFA_TYPE] == 22) sheng_scan(s, nfa);
     else limex_scan(s, nfa);
 }

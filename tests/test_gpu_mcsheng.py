@@ -22,19 +22,31 @@ def brute_batch(ex, fl, ids, bufs):
     return sorted(out, key=lambda x: (x[0], x[2], x[1]))
 
 
+def vbmi_ref(ref, engine):
+    """McSheng64 runs on the AVX512VBMI build of the reference only."""
+    if engine != litdb.ENGINE_MCSHENG64:
+        return ref
+    import refrt
+    if refrt.pick_isa() != "avx512":
+        pytest.skip("host CPU cannot run the AVX512VBMI build of the reference runtime")
+    return refrt.RefRuntime("avx512")
+
+
+@pytest.mark.parametrize("engine", [litdb.ENGINE_MCSHENG, litdb.ENGINE_MCSHENG64])
 @pytest.mark.parametrize("seed", range(5))
-def test_single_outfix_mcsheng_batches(ref, seed):
+def test_single_outfix_mcsheng_batches(ref, seed, engine):
+    ref = vbmi_ref(ref, engine)
     rng = random.Random(8600 + seed)
     for _ in range(200):
         ex, fl, ids, smp = regen.random_set(rng, rng.randint(1, 10), True)
         if seed % 4 == 3:
             ex = regen.with_eod(rng, ex, 0.4)
         try:
-            db = litdb.compile_regex_multi(ex, fl, ids, engine=litdb.ENGINE_MCSHENG)
+            db = litdb.compile_regex_multi(ex, fl, ids, engine=engine)
             break
         except litdb.CompileError:
             continue
-    assert db.outfix_engine_type() in (19, 20)
+    assert db.outfix_engine_type() in ((23, 24) if engine == litdb.ENGINE_MCSHENG64 else (19, 20))
     lens = [0, 1, 2, 15, 16, 17, 31, 33, 64, 200, 577, 1500, 4096] + [rng.randint(1, 1600) for _ in range(150)]
     bufs = [regen.random_text(rng, ex, n, smp) for n in lens]
     if smp:
@@ -50,10 +62,11 @@ def test_both_widths_are_exercised():
     small = [b"abc", b"^GET /[^ ]*\\.php", b"x[0-9]{3}y"]
     big = [b"passwd\\s+[A-Za-z0-9_]{4,9}=", b"(login|admin)[^&]*&id=", b"User-Agent: [^\\r\\n]{8}", b"select.{1,12}from"]
     text = b"GET /a/b.php x123y abc PASSWD  user_1= login=1&id= select a,b from User-Agent: abcdefghij"
-    for ex, want in ((small, 19), (big, 20)):
+    for ex, want, engine in ((small, 19, litdb.ENGINE_MCSHENG), (big, 20, litdb.ENGINE_MCSHENG),
+                             (small, 23, litdb.ENGINE_MCSHENG64), (big, 24, litdb.ENGINE_MCSHENG64)):
         fl = [1 if k % 2 else 0 for k in range(len(ex))]
         ids = [10 + k for k in range(len(ex))]
-        db = litdb.compile_regex_multi(ex, fl, ids, engine=litdb.ENGINE_MCSHENG)
+        db = litdb.compile_regex_multi(ex, fl, ids, engine=engine)
         assert db.outfix_engine_type() == want
         got = gpu_batch(db, [text, b"", text[3:]])
         assert got == brute_batch(ex, fl, ids, [text, b"", text[3:]]) and len(got) >= 3
@@ -66,11 +79,13 @@ def test_both_widths_are_exercised():
 
 @pytest.mark.parametrize("seed", range(4))
 def test_mcsheng_outfixes_in_multi_engine_and_mixed_databases(ref, seed):
+    engine = litdb.ENGINE_MCSHENG64 if seed == 3 else litdb.ENGINE_MCSHENG
+    ref = vbmi_ref(ref, engine)
     rng = random.Random(8700 + seed)
     ex, fl, ids, smp = regen.random_set(rng, rng.randint(4, 14), True)
     if seed % 2:
         ex = regen.with_eod(rng, ex, 0.3)
-    db = litdb.compile_regex_rose(ex, fl, ids, engine=litdb.ENGINE_MCSHENG, dfa_states=[40, 300, 1000, 24][seed])
+    db = litdb.compile_regex_rose(ex, fl, ids, engine=engine, dfa_states=[40, 300, 1000, 24][seed])
     bufs = [regen.random_text(rng, ex, rng.choice([0, 1, 30, 200, 1400]), smp) for _ in range(50)]
     if smp:
         bufs += [b[:max(0, len(b) - len(smp[k % len(smp)]))] + smp[k % len(smp)] for k, b in enumerate(bufs[:30])]
@@ -84,6 +99,6 @@ def test_mcsheng_outfixes_in_multi_engine_and_mixed_databases(ref, seed):
     # literals + McSheng regexes in one database
     lits = [b"needle", b"hay", b"GET /"]
     mdb = litdb.compile_lit_multi(lits, [0, 1, 0], [900, 901, 902], full_rose=True, regexes=ex, regex_flags=fl, regex_ids=ids,
-                                  regex_engine=litdb.ENGINE_MCSHENG, dfa_states=300)
+                                  regex_engine=engine, dfa_states=300)
     mb = [b + b" a needle in the HAY GET /x" for b in bufs[:25]]
     assert gpu_batch(mdb, mb) == ref_batch(ref, mdb, mb)

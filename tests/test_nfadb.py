@@ -281,3 +281,40 @@ def test_mcclellan_wide_states_reference_brute_force_and_port(ref, seed):
     # the same set without wide states reports the same
     plain = litdb.compile_regex_multi(ex, fl, ids, engine=litdb.ENGINE_MCCLELLAN)
     assert wide_header(plain)[1] == 0 and db.size < plain.size
+
+
+# ---- McSheng64 (mcsheng_internal.h:94-119): the AVX512VBMI form of the hybrid, up to 64 region states ----------------
+@pytest.mark.parametrize("seed", range(12))
+def test_mcsheng64_reference_brute_force_and_port(seed):
+    import oracle_port
+    import refrt
+    if refrt.pick_isa() != "avx512":
+        pytest.skip("host CPU cannot run the AVX512VBMI build of the reference runtime")
+    ref = refrt.RefRuntime("avx512")
+    rng = random.Random(8900 + seed)
+    ex, fl, ids, smp = regen.random_set(rng, rng.randint(2, 9), True)
+    if seed % 3 == 2:
+        ex = regen.with_eod(rng, ex, 0.4)
+    if seed % 2:
+        db = litdb.compile_regex_rose(ex, fl, ids, engine=litdb.ENGINE_MCSHENG64, dfa_states=[40, 400, 2000][seed % 3])
+    else:
+        try:
+            db = litdb.compile_regex_multi(ex, fl, ids, engine=litdb.ENGINE_MCSHENG64)
+        except litdb.CompileError as e:
+            assert "too large" in str(e) or "no Sheng region" in str(e)
+            return
+        assert db.outfix_engine_type() in (23, 24)
+    rdb = ref.deserialize(db.serialize())
+    rs = ref.alloc_scratch(rdb)
+    n = 0
+    for k in range(12):
+        t = regen.random_text(rng, ex, rng.choice([0, 1, 9, 80, 500]), smp)
+        if smp and k % 3 == 0:
+            x = smp[k % len(smp)]
+            t = t[:max(0, len(t) - len(x))] + x
+        rv, got = ref.scan(rdb, rs, t)
+        assert rv == 0
+        assert sorted(set(got), key=lambda x: (x[1], x[0])) == regen.brute_force(ex, fl, ids, t)
+        assert oracle_port.scan(db, t) == (0, got)
+        n += len(got)
+    assert n > 0

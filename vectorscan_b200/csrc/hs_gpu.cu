@@ -1293,7 +1293,7 @@ void build_mcsheng_tables(const DbView &v, u32 at, std::vector<u8> &out, DevMcc 
     for (u32 st = 1; st < M.sheng_end; st++)
         for (u32 cp = 0; cp < width; cp++) {
             if (rep[cp] < 0) continue;  // no byte maps to this symbol (TOP)
-            const u32 mv = rd8(v.bc, M.masks_off + 16 * (u32)rep[cp] + st - 1);
+            const u32 mv = rd8(v.bc, M.masks_off + M.mask_stride * (u32)rep[cp] + st - 1);
             u32 nx = mv == M.sheng_end - 1 ? 0u : mv < M.sheng_end - 1 ? mv + 1 : mv;
             if (M.wide16 && rd32(v.bc, M.aux_off + nx * mcclellan::aux::SIZE + mcclellan::aux::accept)) nx |= mcclellan::ACCEPT_FLAG;
             const size_t i = ((size_t)st << M.as) + cp;

@@ -52,7 +52,7 @@ struct DbView {
         u32 m_off = 0, tab_off = 0, tab_bytes = 0, aux_off = 0, sherman_off = 0;
         u32 wide16 = 0, as = 0, states = 0, start = 0, accept_limit_8 = 0, sherman_limit = 0, single = 0, arb_report = 0;
         u32 remap_off = 0;                  // absolute offset of remap[256]
-        u32 sheng_end = 0, masks_off = 0;   // McSheng: first state outside the Sheng region, absolute offset of sheng_masks
+        u32 sheng_end = 0, masks_off = 0, mask_stride = 16;   // McSheng: first state outside the Sheng region, absolute offset of sheng_masks, bytes per mask (64: mcsheng64)
         // wide states (16-bit McClellan): ids >= wide_limit are heads of symbol chains stored at wide_off (absolute);
         // wide_rows = sum of the chains' widths (every chain position becomes a table row on the device)
         u32 has_wide = 0, wide_limit = 0, wide_off = 0, wide_number = 0, wide_rows = 0, n_alpha = 0;
@@ -183,14 +183,15 @@ inline int parse_mcclellan(DbView &d, std::string &why) {
     DbView::Mcc &M = d.mcc;
     // McSheng (types 19 / 20) is McClellan with another header and a Sheng region in front (hsb_layout.h)
     const u8 type = rd8(n, nfa::type);
-    const bool hybrid = type == nfa::MCSHENG_8 || type == nfa::MCSHENG_16;
-    const size_t HDR = hybrid ? ms::SIZE : mc::SIZE;
+    const bool hybrid64 = type == nfa::MCSHENG64_8 || type == nfa::MCSHENG64_16;   // struct mcsheng64: 64-byte masks
+    const bool hybrid = type == nfa::MCSHENG_8 || type == nfa::MCSHENG_16 || hybrid64;
+    const size_t HDR = hybrid64 ? ms::SIZE64 : hybrid ? ms::SIZE : mc::SIZE;
     auto F = [&](size_t plain, size_t hyb) { return hybrid ? hyb : plain; };
     if (d.nfa_len < nfa::SIZE + HDR) { why = "McClellan truncated"; return E_INVALID; }
     M.m_off = d.nfa_off + (u32)nfa::SIZE;
     const u8 *m = r + M.m_off;
     auto n_range = [&](size_t off, size_t len) { return off <= d.nfa_len && len <= d.nfa_len - off; };  // relative to NFA
-    M.wide16 = type == nfa::MCCLELLAN_16 || type == nfa::MCSHENG_16;
+    M.wide16 = type == nfa::MCCLELLAN_16 || type == nfa::MCSHENG_16 || type == nfa::MCSHENG64_16;
     M.has_wide = !hybrid && rd8(m, mc::has_wide) ? 1 : 0;
     if (M.has_wide && !M.wide16) { why = "wide states in an 8-bit McClellan engine are not supported yet"; return E_ARCH; }
     M.as = rd8(m, F(mc::alphaShift, ms::alphaShift));
@@ -202,7 +203,8 @@ inline int parse_mcclellan(DbView &d, std::string &why) {
     M.arb_report = rd32(m, F(mc::arb_report, ms::arb_report));
     M.remap_off = M.m_off + (u32)F(mc::remap, ms::remap);
     M.sheng_end = hybrid ? rd16(m, ms::sheng_end) : 0;
-    M.masks_off = hybrid ? M.m_off + (u32)ms::sheng_masks : 0;
+    M.masks_off = hybrid ? M.m_off + (u32)(hybrid64 ? ms::sheng_succ_masks64 : ms::sheng_masks) : 0;
+    M.mask_stride = hybrid64 ? 64 : 16;
     if (M.as > 8 || !M.states || M.start >= M.states || M.sherman_limit > M.states) { why = "McClellan header inconsistent"; return E_INVALID; }
     // states with an mstate_aux record and a Sherman slot end at wide_limit; ids a table may name end behind the wide heads
     u32 n_aux = M.states, ref_limit = M.states;
@@ -221,7 +223,7 @@ inline int parse_mcclellan(DbView &d, std::string &why) {
     }
     if (M.wide16 && M.states - 1 > mc::STATE_MASK) { why = "McClellan state count out of range"; return E_INVALID; }
     if (!M.wide16 && (M.states > 256 || M.accept_limit_8 > M.states)) { why = "McClellan8 limits out of range"; return E_INVALID; }
-    if (hybrid && (M.sheng_end < 2 || M.sheng_end > ms::MAX_SHENG_STATES + 1 || M.sheng_end > M.sherman_limit)) { why = "McSheng region out of range"; return E_INVALID; }
+    if (hybrid && (M.sheng_end < 2 || M.sheng_end > (hybrid64 ? ms::MAX_SHENG64_STATES : ms::MAX_SHENG_STATES) + 1 || M.sheng_end > M.sherman_limit)) { why = "McSheng region out of range"; return E_INVALID; }
     const u32 rows = (M.wide16 ? M.sherman_limit : M.states) - M.sheng_end;   // the table has no rows for the Sheng region
     if (M.has_wide && M.start >= ref_limit) { why = "McClellan start state out of range"; return E_INVALID; }
     M.tab_off = M.m_off + (u32)HDR;
@@ -241,7 +243,7 @@ inline int parse_mcclellan(DbView &d, std::string &why) {
         // mask byte: < sheng_end - 1 a region state (id - 1), == sheng_end - 1 dead, above it a state id outside the region
         for (u32 c = 0; c < 256; c++)
             for (u32 sid = 0; sid + 1 < M.sheng_end; sid++)
-                if (rd8(r, M.masks_off + 16 * c + sid) >= M.states) { why = "McSheng mask successor out of range"; return E_INVALID; }
+                if (rd8(r, M.masks_off + M.mask_stride * c + sid) >= M.states) { why = "McSheng mask successor out of range"; return E_INVALID; }
         for (u32 st = 1; st < M.sheng_end; st++)
             if (rd32(r, M.aux_off + st * mc::aux::SIZE + mc::aux::accept)) { why = "McSheng region state with reports"; return E_INVALID; }
     }
@@ -484,7 +486,7 @@ inline int parse_outfix_at(DbView &d, u32 info_off, std::string &why) {
     if (!in_range(d, d.nfa_off, d.nfa_len)) { why = "NFA runs past the bytecode"; return E_INVALID; }
     if (rd8(n, nfa::rAccelType)) { why = "reverse acceleration is not supported"; return E_ARCH; }
     if (d.limex_type == nfa::MCCLELLAN_8 || d.limex_type == nfa::MCCLELLAN_16 || d.limex_type == nfa::MCSHENG_8 ||
-        d.limex_type == nfa::MCSHENG_16)
+        d.limex_type == nfa::MCSHENG_16 || d.limex_type == nfa::MCSHENG64_8 || d.limex_type == nfa::MCSHENG64_16)
         return parse_mcclellan(d, why);
     if (d.limex_type == nfa::SHENG || d.limex_type == nfa::SHENG_32 || d.limex_type == nfa::SHENG_64) return parse_sheng(d, why);
     if (d.limex_type > nfa::LIMEX_512) { why = "outfix engine type " + std::to_string(d.limex_type) + " (not LimEx, McClellan, McSheng or Sheng) is not supported yet"; return E_ARCH; }

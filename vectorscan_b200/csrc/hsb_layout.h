@@ -228,7 +228,7 @@ constexpr size_t flags = 0, length = 4, type = 8, rAccelType = 9, rAccelOffset =
                  rAccelData = 12, queueIndex = 16, nPositions = 20, scratchStateSize = 24, streamStateSize = 28,
                  maxWidth = 32, minWidth = 36, maxOffset = 40, SIZE = 64;
 constexpr u8 LIMEX_32 = 0, LIMEX_64 = 1, LIMEX_128 = 2, LIMEX_256 = 3, LIMEX_384 = 4, LIMEX_512 = 5;
-constexpr u8 MCCLELLAN_8 = 6, MCCLELLAN_16 = 7, SHENG = 17, MCSHENG_8 = 19, MCSHENG_16 = 20, SHENG_32 = 21, SHENG_64 = 22;
+constexpr u8 MCCLELLAN_8 = 6, MCCLELLAN_16 = 7, SHENG = 17, MCSHENG_8 = 19, MCSHENG_16 = 20, SHENG_32 = 21, SHENG_64 = 22, MCSHENG64_8 = 23, MCSHENG64_16 = 24;
 constexpr u32 ACCEPTS_EOD = 1, ZOMBIE = 2;
 }
 namespace nfainfo {  // struct NfaInfo
@@ -261,6 +261,10 @@ constexpr size_t state_count = 0, length = 4, start_anchored = 8, start_floating
                  accept_limit_8 = 30, sherman_limit = 32, alphaShift = 34, flags = 35, has_accel = 36, remap = 37,
                  arb_report = 296, accel_offset = 300, sheng_masks = 304, SIZE = 4400;
 constexpr u32 MAX_SHENG_STATES = 16;
+// struct mcsheng64 (mcsheng_internal.h:94-119, AVX512VBMI targets; NFA types 23 / 24): the same header, a region of up to
+// 64 states, 64-byte masks (vpermb) at the next 64-byte boundary
+constexpr size_t sheng_succ_masks64 = 320, SIZE64 = 320 + 256 * 64;
+constexpr u32 MAX_SHENG64_STATES = 64;
 }
 // struct sheng (src/nfa/sheng_internal.h:68-79): a DFA of at most 16 states as 256 byte-shuffle masks; mask[c][s] is
 // the successor of state s on byte c with flag bits (accept / dead / accel) beside the 4-bit state id.  sstate_aux[]

@@ -770,8 +770,9 @@ int emit_mcclellan(const Dfa &d, const u8 *reach_map, const std::vector<u32> &pr
 // region", mcsheng_compile.cpp:582-586), at most 16; in a 16-bit engine every state entered straight from the region
 // must have an id that fits the mask byte, so those states are numbered first and the region shrinks until they fit.
 // No Sherman states.  Fails (caller falls back to McClellan) when the start state itself accepts.
+// `wide64`: struct mcsheng64 (NFA types 23 / 24, AVX512VBMI targets): a region of up to 64 states, 64-byte masks.
 int emit_mcsheng(const Dfa &d, const u8 *reach_map, const std::vector<u32> &program_of, u32 min_width, Buf &eng,
-                 u32 &state_bytes, std::string &err) {
+                 u32 &state_bytes, std::string &err, bool wide64 = false) {
     namespace mc = mcclellan;
     namespace ms = mcsheng;
     const u32 n = (u32)d.next.size();
@@ -784,7 +785,8 @@ int emit_mcsheng(const Dfa &d, const u8 *reach_map, const std::vector<u32> &prog
     const u32 start = d.start_anchored ? d.start_anchored : d.start_floating;
     std::vector<u32> region;
     std::vector<u8> in_region(n, 0), is_succ(n, 0);
-    for (u32 cap = ms::MAX_SHENG_STATES; cap >= 1; cap--) {
+    const size_t HDR = wide64 ? ms::SIZE64 : ms::SIZE, MASKS = wide64 ? ms::sheng_succ_masks64 : ms::sheng_masks, STRIDE = wide64 ? 64 : 16;
+    for (u32 cap = wide64 ? ms::MAX_SHENG64_STATES : ms::MAX_SHENG_STATES; cap >= 1; cap--) {
         region.clear();
         std::fill(in_region.begin(), in_region.end(), 0);
         std::fill(is_succ.begin(), is_succ.end(), 0);
@@ -843,7 +845,7 @@ int emit_mcsheng(const Dfa &d, const u8 *reach_map, const std::vector<u32> &prog
     const u32 n_normal = n - sheng_end;
     const size_t tran_size = ((size_t)1 << as) * ent * n_normal;
     const size_t aux_size = mc::aux::SIZE * (size_t)n;
-    const size_t aux_offset = round_up(nfa::SIZE + ms::SIZE + tran_size, 16);
+    const size_t aux_offset = round_up(nfa::SIZE + HDR + tran_size, 16);
     size_t rl_size = 0;
     for (auto &l : lists) rl_size += 4 + 4 * l.size();
     const size_t accel_offset = round_up(aux_offset + aux_size + rl_size, 32);
@@ -854,7 +856,7 @@ int emit_mcsheng(const Dfa &d, const u8 *reach_map, const std::vector<u32> &prog
     u8 *nh = eng.at(0), *m = eng.at(nfa::SIZE);
     wr32(nh, nfa::flags, any_eod ? nfa::ACCEPTS_EOD : 0);
     wr32(nh, nfa::length, (u32)eng.size());
-    wr8(nh, nfa::type, wide16 ? nfa::MCSHENG_16 : nfa::MCSHENG_8);
+    wr8(nh, nfa::type, wide64 ? (wide16 ? nfa::MCSHENG64_16 : nfa::MCSHENG64_8) : (wide16 ? nfa::MCSHENG_16 : nfa::MCSHENG_8));
     wr32(nh, nfa::queueIndex, 0);
     wr32(nh, nfa::nPositions, n);
     wr32(nh, nfa::scratchStateSize, state_bytes);
@@ -881,7 +883,7 @@ int emit_mcsheng(const Dfa &d, const u8 *reach_map, const std::vector<u32> &prog
     wr32(m, ms::accel_offset, (u32)(accel_offset - nfa::SIZE));
     // shuffle masks, one per byte value (createShuffleMasks)
     for (u32 c = 0; c < 256; c++) {
-        u8 *mask = m + ms::sheng_masks + 16 * (size_t)c;
+        u8 *mask = m + MASKS + STRIDE * (size_t)c;
         for (u32 sid = 0; sid < region.size(); sid++) {
             const u32 t = impl[d.next[region[sid]][reach_map[c]]];
             mask[sid] = (u8)(t == 0 ? sheng_end - 1 : t < sheng_end ? t - 1 : t);
@@ -897,7 +899,7 @@ int emit_mcsheng(const Dfa &d, const u8 *reach_map, const std::vector<u32> &prog
             o += 4 + 4 * lists[i].size();
         }
     }
-    u8 *succ = m + ms::SIZE;
+    u8 *succ = m + HDR;
     for (u32 i = 0; i < n; i++) {
         const u32 id = impl[i];
         u8 *a = eng.at(aux_offset + mc::aux::SIZE * (size_t)id);
@@ -1262,10 +1264,10 @@ int emit_engine(const Automaton &am, unsigned engine, const std::vector<u32> &pr
     // outfix engines of multi-engine databases: a DFA of at most 16 states is laid out as a Sheng engine, which is what the
     // reference compiler tries first for every DFA (shengCompile before mcclellanCompile, src/rose/rose_build_bytecode.cpp
     // buildOutfix / getDfa)
-    if (sheng_if_small && (engine == HSB_REGEX_ENGINE_MCCLELLAN || engine == HSB_REGEX_ENGINE_MCSHENG || engine == HSB_REGEX_ENGINE_MCCLELLAN_WIDE) && dfa.next.size() <= 16)
+    if (sheng_if_small && (engine == HSB_REGEX_ENGINE_MCCLELLAN || engine == HSB_REGEX_ENGINE_MCSHENG || engine == HSB_REGEX_ENGINE_MCCLELLAN_WIDE || engine == HSB_REGEX_ENGINE_MCSHENG64) && dfa.next.size() <= 16)
         engine = HSB_REGEX_ENGINE_SHENG;
-    if (engine == HSB_REGEX_ENGINE_MCSHENG) {
-        const int mrv = emit_mcsheng(dfa, reach_map, program_of, am.min_width, eng, stream_state, err);
+    if (engine == HSB_REGEX_ENGINE_MCSHENG || engine == HSB_REGEX_ENGINE_MCSHENG64) {
+        const int mrv = emit_mcsheng(dfa, reach_map, program_of, am.min_width, eng, stream_state, err, engine == HSB_REGEX_ENGINE_MCSHENG64);
         scratch_state = stream_state;
         if (mrv == HSB_LIT_SUCCESS || !sheng_if_small) return mrv;
         engine = HSB_REGEX_ENGINE_MCCLELLAN;  // no region (the start state accepts): plain McClellan, as getDfa falls through
@@ -1284,7 +1286,7 @@ int emit_engine(const Automaton &am, unsigned engine, const std::vector<u32> &pr
 namespace hsb_nfadb {
 
 int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &image, std::string &err) {
-    if (engine > HSB_REGEX_ENGINE_MCCLELLAN_WIDE) { err = "unknown engine"; return HSB_LIT_COMPILER_ERROR; }
+    if (engine > HSB_REGEX_ENGINE_MCSHENG64) { err = "unknown engine"; return HSB_LIT_COMPILER_ERROR; }
     if (pats.empty()) { err = "no expressions"; return HSB_LIT_COMPILER_ERROR; }
     // ---- 1. parse every pattern, build one automaton -------------------------------------------------
     std::vector<Parsed> parsed;
@@ -1420,7 +1422,7 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
 int build_outfix_engines(const std::vector<Pattern> &pats, unsigned engine, u32 dfa_states,
                          const std::vector<u32> &program_of, std::vector<EngineBlob> &out, std::string &err) {
     if (engine != HSB_REGEX_ENGINE_LIMEX && engine != HSB_REGEX_ENGINE_MCCLELLAN && engine != HSB_REGEX_ENGINE_MCCLELLAN_SHERMAN &&
-        engine != HSB_REGEX_ENGINE_MCSHENG && engine != HSB_REGEX_ENGINE_MCCLELLAN_WIDE) {
+        engine != HSB_REGEX_ENGINE_MCSHENG && engine != HSB_REGEX_ENGINE_MCCLELLAN_WIDE && engine != HSB_REGEX_ENGINE_MCSHENG64) {
         err = "outfix engines are LimEx, McClellan or McSheng";
         return HSB_LIT_COMPILER_ERROR;
     }

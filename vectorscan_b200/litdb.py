@@ -214,6 +214,7 @@ def compile_lit_multi(literals, flags=None, ids=None, mode=HS_MODE_BLOCK, engine
 
 ENGINE_LIMEX, ENGINE_MCCLELLAN, ENGINE_MCCLELLAN_SHERMAN, ENGINE_SHENG, ENGINE_SHENG_WIDE, ENGINE_MCSHENG = 0, 1, 2, 3, 4, 5
 ENGINE_MCCLELLAN_WIDE = 6
+ENGINE_MCSHENG64 = 7
 
 
 def compile_regex_multi(expressions, flags=None, ids=None, mode=HS_MODE_BLOCK, engine=ENGINE_LIMEX):
