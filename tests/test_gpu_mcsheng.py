@@ -33,7 +33,7 @@ def vbmi_ref(ref, engine):
 
 
 @pytest.mark.parametrize("engine", [litdb.ENGINE_MCSHENG, litdb.ENGINE_MCSHENG64])
-@pytest.mark.parametrize("seed", range(5))
+@pytest.mark.parametrize("seed", range(3))
 def test_single_outfix_mcsheng_batches(ref, seed, engine):
     ref = vbmi_ref(ref, engine)
     rng = random.Random(8600 + seed)
