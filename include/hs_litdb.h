@@ -144,6 +144,8 @@ int hsb_compile_regex_multi(const char *const *expressions, const unsigned *flag
 #define HSB_REGEX_ENGINE_MCSHENG64 7u /* McSheng with a region of up to 64 states and 64-byte masks: struct mcsheng64,
                                          MCSHENG_64_NFA_8 / _16 (mcsheng_internal.h:94-119); only an AVX512VBMI build of the
                                          reference runtime executes it */
+/* mode: HSB_MODE_BLOCK, or HSB_MODE_STREAM with a DFA engine (the engine's stream state is its state id; header
+ * requiresEodCheck set when a pattern ends in \z, as hs_close_stream wants it: src/runtime.c:676-692). */
 int hsb_compile_regex_multi_ex(const char *const *expressions, const unsigned *flags, const unsigned *ids,
                                unsigned elements, unsigned mode, unsigned engine, hs_database_t **db,
                                char **error);

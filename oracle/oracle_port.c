@@ -739,6 +739,28 @@ int op_scan_vector(const void *db, const char *const *data, const unsigned *leng
     const u8 *rose = d + rd32(d + DB_BYTECODE_OFF);
     if (rd32(rose + R_MODE) != 4 && rd32(rose + R_MODE) != 2) return HS_DB_MODE_ERROR; /* mode 2 (HS_MODE_STREAM): the same loop is
                                                                                          * hs_open_stream, hs_scan_stream per block, hs_close_stream */
+    if (rose[R_RUNTIME_IMPL] == 2 && rd32(rose + R_MODE) == 2 && !rose[R_HAS_SOM] && !rd32(rose + R_CKEY_COUNT)) {
+        /* stream mode, one DFA engine (soleOutfixStreamExec, runtime.c:833-870): the engine's state is compressed into the
+         * stream state after a block and expanded before the next (nfaQueueCompressState / nfaExpandState) -- for a DFA
+         * that is its state id, so the blocks are one run of the automaton over their concatenation; restated as that.
+         * (Engines with end-of-data accepts report at hs_close_stream: engine_scan's end-of-data check is that report.) */
+        size_t total = 0;
+        for (unsigned b = 0; b < count; b++) total += length[b];
+        u8 *all = malloc(total + 1);
+        size_t at = 0;
+        for (unsigned b = 0; b < count; b++) { if (length[b]) memcpy(all + at, data[b], length[b]); at += length[b]; }
+        struct scan_state e;
+        memset(&e, 0, sizeof(e));
+        e.rose = rose; e.buf = all; e.len = (u32)total; e.cb = cb; e.ctx = ctx;
+        e.ekeys = rd32(rose + R_EKEY_COUNT); e.dkeys = rd32(rose + R_DKEY_COUNT);
+        e.exhausted = calloc(e.ekeys / 8 + 2, 1);
+        e.dedupe = calloc(e.dkeys / 8 + 2, 1);
+        e.dedupe_offset = ~0ull;
+        if (total) engine_scan(&e, rose + rd32(rose + rd32(rose + R_NFA_INFO) + NI_NFA_OFF));
+        free(all); free(e.exhausted); free(e.dedupe);
+        if (e.error) return HS_UNKNOWN_ERROR;
+        return e.terminated ? HS_SCAN_TERMINATED : HS_SUCCESS;
+    }
     if (rose[R_RUNTIME_IMPL] != 1 || rose[R_HAS_SOM] || rd32(rose + R_CKEY_COUNT) || rd32(rose + R_BOUNDARY) ||
         rd32(rose + R_BOUNDARY + 4) || rd32(rose + R_BOUNDARY + 8))
         return HS_ARCH_ERROR; /* outside the restated path */

@@ -143,3 +143,70 @@ def test_stream_api_through_the_shim_by_the_reference_names():
     assert shim.hs_close_stream(st, sc, cb, None) == 0
     assert seen == [(11, 8), (10, 10), (11, 12)]
     shim.hs_free_scratch(sc)
+
+
+# ---- stream mode of ONE DFA engine: the engine's state id goes into and comes out of every block scan -------------------
+def test_single_dfa_streams_block_by_block(ref):
+    import regen
+    from test_streammode import dfa_stream_cases
+    n = 0
+    for db, ex, fl, ids, bufs, text in dfa_stream_cases(77, eod=False):
+        sc = gpu.alloc_scratch(db)
+        st = gpu.Stream(db)
+        got = []
+        for b in bufs:
+            assert st.scan(b, sc, collect(got)) == gpu.HS_SUCCESS
+        st.close()
+        sc.close()
+        assert got == sorted(regen.brute_force(ex, fl, ids, text), key=lambda m: (m[1], m[0])), (ex, bufs)
+        assert oracle_port.scan_stream_blocks(db, bufs) == (0, got)
+        n += len(got)
+    assert n > 100
+
+
+def test_many_single_dfa_streams_per_pass_and_refusals():
+    import regen
+    rng = random.Random(23)
+    ex = [b"passwd\\s+[A-Za-z0-9_]{4,9}=", b"(login|admin)[^&]*&id=", b"User-Agent: [^\\r\\n]{8}", b"^GET /[^ ]*\\.php", b"abc"]
+    fl, ids = [1, 0, 0, 0, 0], [3, 1, 4, 5, 9]
+    db = litdb.compile_regex_multi(ex, fl, ids, engine=litdb.ENGINE_MCCLELLAN, mode=HS_MODE_STREAM)
+    flows = []
+    for k in range(200):
+        text = regen.random_text(rng, ex, rng.choice([3, 200, 1500]))
+        if k % 3 == 0:
+            text = b"GET /a/b.php " + text
+        flows.append(cut(rng, text, rng.choice([1, 2, 4, 7])))
+    sc = gpu.alloc_scratch(db)
+    streams = [gpu.Stream(db) for _ in flows]
+    got = [[] for _ in flows]
+
+    def on_event(i, f, t, fl_, ctx):
+        got[int(ctx or 0)].append((int(i), int(t)))
+        return 0
+    for rnd in range(7):
+        live = [k for k, fl_ in enumerate(flows) if rnd < len(fl_)]
+        assert gpu.scan_streams([streams[k] for k in live], [flows[k][rnd] for k in live], sc, on_event, contexts=live) == 0
+    n = 0
+    for k, blocks in enumerate(flows):
+        assert got[k] == sorted(regen.brute_force(ex, fl, ids, b"".join(blocks)), key=lambda m: (m[1], m[0])), k
+        n += len(got[k])
+    assert n > 50
+    # anchored pattern: only at stream offset 0, and not after a reset point in the middle
+    st = gpu.Stream(db)
+    one = []
+    for b in (b"GET /x", b".php GET /y.php"):
+        assert st.scan(b, sc, collect(one)) == 0
+    assert one == [(5, 10)]
+    assert st.reset() == 0
+    one = []
+    assert st.scan(b"GET /z.php", sc, collect(one)) == 0 and one == [(5, 10)]
+    st.close()
+    for s in streams:
+        s.close()
+    sc.close()
+    # refused in stream mode: engines with end-of-data accepts, LimEx engines (the writer refuses those itself)
+    edb = litdb.compile_regex_multi([b"abc\\z", b"de"], [0, 0], [1, 2], engine=litdb.ENGINE_MCCLELLAN, mode=HS_MODE_STREAM)
+    with pytest.raises(gpu.HsGpuError):
+        gpu.alloc_scratch(edb)
+    with pytest.raises(litdb.CompileError):
+        litdb.compile_regex_multi([b"abc"], [0], [1], engine=litdb.ENGINE_LIMEX, mode=HS_MODE_STREAM)

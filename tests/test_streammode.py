@@ -61,3 +61,40 @@ def test_stream_termination_and_single_match(ref):
     # stop at the second match (inside block 0): that call and every later hs_scan_stream return HS_SCAN_TERMINATED
     rvs, part = ref_stream(ref, sdb, bufs, stop_after=2)
     assert part == got[:2] and rvs[:5] == [-3] * 5
+
+
+# ---- stream mode of ONE DFA engine (single-outfix databases): the engine's state is what crosses block boundaries ----
+DFA_ENGINES = [litdb.ENGINE_MCCLELLAN, litdb.ENGINE_MCCLELLAN_SHERMAN, litdb.ENGINE_MCSHENG, litdb.ENGINE_SHENG,
+               litdb.ENGINE_MCCLELLAN_WIDE]
+
+
+def dfa_stream_cases(seed, eod):
+    """(database, patterns, flags, ids, blocks, whole text) for seeded sets over every DFA engine the writer knows."""
+    import regen
+    rng = random.Random(seed)
+    for trial in range(40):
+        ex, fl, ids, smp = regen.random_set(rng, rng.randint(1, 6), True)
+        if eod and trial % 2:
+            ex = regen.with_eod(rng, ex, 0.4)
+        try:
+            db = litdb.compile_regex_multi(ex, fl, ids, engine=DFA_ENGINES[trial % len(DFA_ENGINES)], mode=HS_MODE_STREAM)
+        except litdb.CompileError:
+            continue
+        for k in range(4):
+            text = regen.random_text(rng, ex, rng.choice([0, 5, 60, 300]), smp)
+            if smp and k % 2 == 0:
+                x = smp[k % len(smp)]
+                text = text[:max(0, len(text) - len(x))] + x
+            yield db, ex, fl, ids, cut(rng, text, rng.choice([1, 2, 5, 12])), text
+
+
+def test_reference_stream_api_on_single_dfa_databases(ref):
+    import regen
+    n = 0
+    for db, ex, fl, ids, bufs, text in dfa_stream_cases(31, eod=True):
+        rvs, got = ref_stream(ref, db, bufs)
+        assert all(rv == 0 for rv in rvs)
+        assert sorted(set(got), key=lambda x: (x[1], x[0])) == regen.brute_force(ex, fl, ids, text)
+        assert oracle_port.scan_stream_blocks(db, bufs) == (0, got)
+        n += len(got)
+    assert n > 150

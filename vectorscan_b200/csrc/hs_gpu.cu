@@ -107,6 +107,11 @@ struct DevCorpus {
     u32 nstrips;
     const u32 *order;        // engine kernels: work item k scans buffer order[k] (buffers by descending length, so that
                              // the lanes of a warp finish together); null = identity
+    // stream mode of a DFA engine (k_mcclellan): buffer b is the next block of a stream that has come to DFA state
+    // init_state[b] (device state ids); the state it leaves the block in goes to final_state[b]; no end-of-data check
+    // (the stream is not over).  Both null outside stream scans.
+    const u32 *init_state;
+    u32 *final_state;
 };
 
 struct DevArena {
@@ -1145,10 +1150,10 @@ struct hs_gpu_corpus {
     u64 total = 0;
     u32 count = 0, nstrips = 0;
     DevCorpus dev() const {
-        return DevCorpus{text.p + FRONT_PAD, off.p, cell_first.p, total, count, nstrips, nullptr};
+        return DevCorpus{text.p + FRONT_PAD, off.p, cell_first.p, total, count, nstrips, nullptr, nullptr, nullptr};
     }
     DevCorpus dev_stream() const {
-        return DevCorpus{text.p + FRONT_PAD, stream_off.p, stream_cell.p, total, 1, nstrips, nullptr};
+        return DevCorpus{text.p + FRONT_PAD, stream_off.p, stream_cell.p, total, 1, nstrips, nullptr, nullptr, nullptr};
     }
 };
 
@@ -1163,6 +1168,11 @@ struct hs_gpu_stream {
     std::vector<u32> exhausted;  // sorted exhaustion keys
     bool terminated = false;     // a callback asked to stop (STATUS_TERMINATED): later blocks return HS_SCAN_TERMINATED
     bool in_call = false;
+    // single-DFA databases: the engine's state (device state id) where the stream stands; 0 = dead (the reference marks
+    // the stream exhausted, src/runtime.c:862-866); `started` false = no block scanned yet (the first one begins in the
+    // engine's anchored start state, as MQE_TOP at stream offset 0 does, :850-854)
+    bool started = false;
+    u32 engine_state = 0;
 };
 
 struct hs_gpu_scratch {
@@ -1178,6 +1188,10 @@ struct hs_gpu_scratch {
     PinnedBuf<u64> h_off;
     PinnedBuf<u32> h_cell_first;
     PinnedBuf<u8> h_streams;     // hs_gpu_scan_streams: history + block of every stream of the call, back to back
+    // stream mode of a DFA engine: per-buffer entry / exit states of the call being served (null pointers otherwise)
+    PinnedBuf<u32> h_stream_state;   // [0, count): states the blocks start in; [count, 2 count): states they end in
+    DevBuf<u32> d_stream_state;
+    u32 stream_state_count = 0;      // > 0: the next scan_device carries DFA states in and out
     DevBuf<Rec> recs, recs2;
     DevBuf<hs_gpu_match_t> d_matches;
     DevBuf<u8> cub_tmp, keep;
@@ -2052,6 +2066,14 @@ hs_error_t scan_device(hs_gpu_scratch *s, DbImage *im, const hs_gpu_corpus &corp
         return HS_SUCCESS;
     }
     DevCorpus cp = corpus.dev();
+    if (s->stream_state_count) {
+        // stream mode of a DFA engine: entry states up, exit states back behind the scan (fetch_matches waits for the stream)
+        if (s->stream_state_count != corpus.count || (im->view.kind != ENG_MCCLELLAN && im->view.kind != ENG_SHENG)) return HS_INVALID;
+        CU_OK(s->d_stream_state.reserve(2 * (size_t)corpus.count));
+        CU_OK(cudaMemcpyAsync(s->d_stream_state.p, s->h_stream_state.data(), 2 * (size_t)corpus.count * sizeof(u32), cudaMemcpyHostToDevice, s->stream));
+        cp.init_state = s->d_stream_state.p;
+        cp.final_state = s->d_stream_state.p + corpus.count;
+    }
     CU_OK(cudaEventRecord(s->ev[1], s->stream));  // what was queued before this point is the staging (h2d_ms = ev0 -> ev1)
     if (im->view.vectored) {
         // hs_scan_vector on an HS_MODE_VECTORED database (src/runtime.c:1106-1174): block i continues block i - 1 with
@@ -2509,7 +2531,7 @@ hs_error_t stage_host_chunks(hs_gpu_scratch *s, const char *const *data, const u
         CU_OK(cudaEventRecord(s->chunk_ready[k], s->copy_stream));
         if (c.bytes)
             mem.push_back(TrainMember{DevCorpus{cp.text.p + c.text_at, cp.off.p + c.off_at, cp.cell_first.p + c.cell_at, c.bytes,
-                                                cnt, c.nstrips, nullptr},
+                                                cnt, c.nstrips, nullptr, nullptr, nullptr},
                                       c.first, s->chunk_ready[k]});
     }
     CU_OK(cudaEventRecord(s->ev[6], s->copy_stream));  // end of the H2D work (h2d_ms = ev0 -> ev6)
@@ -2739,6 +2761,8 @@ hs_error_t hs_gpu_free_scratch(hs_gpu_scratch_t *s) {
     s->h_off.release();
     s->h_cell_first.release();
     s->h_streams.release();
+    s->h_stream_state.release();
+    s->d_stream_state.release();
     if (s->h_stage) cudaFreeHost(s->h_stage);
     if (s->h_matches) cudaFreeHost(s->h_matches);
     if (s->h_ctl) cudaFreeHost(s->h_ctl);
@@ -2847,7 +2871,7 @@ hs_error_t hs_gpu_open_stream(const hs_database_t *db, unsigned int flags, hs_gp
     if (database_mode(db) != MODE_STREAM) return HS_DB_MODE_ERROR;
     const u8 *p = reinterpret_cast<const u8 *>(db);
     const u8 *r = p + rd32(p, db::bytecode);
-    if (rd8(r, rose::runtimeImpl) != rose::RUNTIME_PURE_LITERAL) return HS_ARCH_ERROR;
+    if (rd8(r, rose::runtimeImpl) == rose::RUNTIME_FULL_ROSE) return HS_ARCH_ERROR;   // pure literal or one DFA engine
     hs_gpu_stream *st = new (std::nothrow) hs_gpu_stream();
     if (!st) return HS_NOMEM;
     st->db = db;
@@ -2883,16 +2907,23 @@ hs_error_t hs_gpu_scan_streams(hs_gpu_stream_t *const *ids, const char *const *d
         ids[i]->in_call = true;
         rel.n = i + 1;
     }
+    if ((rv = ensure_device(scratch)) != HS_SUCCESS) return rv;
+    DbImage *im = nullptr;
+    if ((rv = upload_database(scratch, db, &im)) != HS_SUCCESS) return rv;
+    // a single-DFA database carries the engine's state per stream instead of history (its historyRequired is 0)
+    const bool engine = im->view.kind == ENG_MCCLELLAN || im->view.kind == ENG_SHENG;
+    if (engine)
+        for (unsigned i = 0; i < count; i++)
+            if (!ids[i]->started) { ids[i]->started = true; ids[i]->engine_state = im->mcc.start; }
     // history + block, back to back (terminated streams and empty blocks contribute nothing: runtime.c:883-900), written
     // straight into page-locked memory of the scratch: the staging then sees one contiguous pinned run and copies it to
     // the device as it lies (stage_host_buffers), so the bytes are moved once on the host, by a few threads
     std::vector<u64> at((size_t)count + 1, 0);
     for (unsigned i = 0; i < count; i++) {
-        const bool live = !ids[i]->terminated && length[i];
+        const bool live = !ids[i]->terminated && length[i] && (!engine || ids[i]->engine_state != 0);
         at[i + 1] = at[i] + (live ? ids[i]->hist.size() + length[i] : 0);
         if (at[i + 1] - at[i] > 0xffffffffull) return HS_INVALID;
     }
-    if ((rv = ensure_device(scratch)) != HS_SUCCESS) return rv;
     if (!scratch->h_streams.resize(at[count] + 64)) return HS_NOMEM;
     char *arena = reinterpret_cast<char *>(scratch->h_streams.data());
     std::vector<const char *> ptr(count);
@@ -2916,9 +2947,23 @@ hs_error_t hs_gpu_scan_streams(hs_gpu_stream_t *const *ids, const char *const *d
             for (std::thread &t : pool) t.join();
         }
     }
-    DbImage *im = nullptr;
+    struct StateGuard { hs_gpu_scratch *s; ~StateGuard() { s->stream_state_count = 0; } } state_guard{scratch};
+    if (engine) {
+        if (!scratch->h_stream_state.resize(2 * (size_t)count)) return HS_NOMEM;
+        for (unsigned i = 0; i < count; i++) {
+            scratch->h_stream_state[i] = len[i] ? ids[i]->engine_state : 0u;
+            scratch->h_stream_state[count + i] = 0;
+        }
+        scratch->stream_state_count = count;
+    }
     rv = scan_host_batch(db, ptr.data(), len.data(), count, scratch, &im);
     if (rv != HS_SUCCESS) return rv;
+    if (engine && at[count]) {   // (an all-empty call never reached the device)
+        if (cudaMemcpy(scratch->h_stream_state.data() + count, scratch->d_stream_state.p + count, (size_t)count * sizeof(u32),
+                       cudaMemcpyDeviceToHost) != cudaSuccess) { cudaGetLastError(); return HS_UNKNOWN_ERROR; }
+        for (unsigned i = 0; i < count; i++)
+            if (len[i]) ids[i]->engine_state = scratch->h_stream_state[count + i];
+    }
     const std::vector<std::pair<u32, u32>> &ekey_of = im->view.stream_ekey_of;
     const bool any_ekey = im->view.stream_any_ekey;
     const hs_gpu_match_t *m = scratch->h_matches;
@@ -2988,6 +3033,8 @@ hs_error_t hs_gpu_reset_stream(hs_gpu_stream_t *id, unsigned int flags, hs_gpu_s
     id->hist.clear();
     id->exhausted.clear();
     id->terminated = false;
+    id->started = false;
+    id->engine_state = 0;
     return HS_SUCCESS;
 }
 

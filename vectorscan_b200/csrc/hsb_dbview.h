@@ -567,8 +567,11 @@ inline int parse_database(const void *db, DbView &d, std::string &why) {
     d.vectored = mode == MODE_VECTORED;
     d.streaming = mode == MODE_STREAM;
     d.history_required = rd32(r, rose::historyRequired);
-    if ((d.vectored || d.streaming) && rd8(r, rose::runtimeImpl) != rose::RUNTIME_PURE_LITERAL) {
-        why = "stream and vectored mode are served for pure-literal databases only (engines carry stream state from block to block)";
+    // stream state that the device path carries: pure-literal databases (history, exhaustion: on the host) and, in stream
+    // mode, ONE DFA engine (its state id per stream goes into and comes out of every block scan)
+    if ((d.vectored && rd8(r, rose::runtimeImpl) != rose::RUNTIME_PURE_LITERAL) ||
+        (d.streaming && rd8(r, rose::runtimeImpl) == rose::RUNTIME_FULL_ROSE)) {
+        why = "vectored mode is served for pure-literal databases, stream mode for pure-literal and single-DFA databases only";
         return E_ARCH;
     }
     if (rd32(r, rose::size) > d.bc_len) { why = "engine size exceeds database length"; return E_INVALID; }
@@ -590,7 +593,13 @@ inline int parse_database(const void *db, DbView &d, std::string &why) {
     d.ekey_count = rd32(r, rose::ekeyCount);
     d.dkey_count = rd32(r, rose::dkeyCount);
     d.groups = rd64(r, rose::initialGroups) & rd64(r, rose::floating_group_mask);
-    if (impl == rose::RUNTIME_SINGLE_OUTFIX) return parse_single_outfix(d, why);
+    if (impl == rose::RUNTIME_SINGLE_OUTFIX) {
+        const int orv = parse_single_outfix(d, why);
+        if (orv != E_SUCCESS || !d.streaming) return orv;
+        if (d.kind != ENG_MCCLELLAN && d.kind != ENG_SHENG) { why = "stream mode: only DFA engines carry their state across blocks on the device path"; return E_ARCH; }
+        if ((d.nfa_flags & nfa::ACCEPTS_EOD) || rd8(r, rose::requiresEodCheck)) { why = "stream mode: engines with end-of-data accepts are not supported yet"; return E_ARCH; }
+        return E_SUCCESS;
+    }
     if (impl == rose::RUNTIME_FULL_ROSE) {
         // supported shapes: outfix engines only; a floating literal matcher (programs through the full interpreter,
         // roseFloatingCallback src/rose/match.c:479-523); both (literal matches and engine matches merge by offset)

@@ -154,8 +154,8 @@ __global__ void __launch_bounds__(MCC_THREADS, 1) k_mcclellan(const DevDb db_, c
             a[0] = chunk[0];             // over-reads stay inside the padded text (BACK_PAD)
             a[1] = chunk[1]; a[2] = chunk[2]; a[3] = chunk[3];
             chunk += 4;
-            s = m.start;
-            have = true;
+            s = cp_.init_state ? cp_.init_state[buf] : m.start;   // stream mode: the state the stream has come to
+            have = s != 0;                                        // (a dead stream stays dead)
         }
 #pragma unroll
       for (int q = 0; q < 4; q++) {
@@ -212,7 +212,8 @@ __global__ void __launch_bounds__(MCC_THREADS, 1) k_mcclellan(const DevDb db_, c
         i += 16;
         if (i >= (long long)len || !s) {
             // ---- end of buffer (or dead: nothing can switch on again, mcclellan.c:240-243) ----
-            if (s && m.accepts_eod) mcc_accept(evq, db_.bc, m, s, buf, len, true);
+            if (cp_.final_state) cp_.final_state[buf] = s;        // stream mode: the data goes on, no end-of-data check
+            else if (s && m.accepts_eod) mcc_accept(evq, db_.bc, m, s, buf, len, true);
             have = false;
         }
       }

@@ -365,7 +365,7 @@ struct Glushkov {
 
 #include "outfix_engines.h"
 namespace hsb_nfadb {
-int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<hsb::u8> &image, std::string &err);
+int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<hsb::u8> &image, std::string &err, unsigned mode = hsb::MODE_BLOCK);
 int build_rose(const std::vector<Pattern> &pats, unsigned engine, hsb::u32 dfa_states, std::vector<hsb::u8> &image, std::string &err);
 }
 
@@ -1285,7 +1285,7 @@ int emit_engine(const Automaton &am, unsigned engine, const std::vector<u32> &pr
 
 namespace hsb_nfadb {
 
-int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &image, std::string &err) {
+int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &image, std::string &err, unsigned mode) {
     if (engine > HSB_REGEX_ENGINE_MCSHENG64) { err = "unknown engine"; return HSB_LIT_COMPILER_ERROR; }
     if (pats.empty()) { err = "no expressions"; return HSB_LIT_COMPILER_ERROR; }
     // ---- 1. parse every pattern, build one automaton -------------------------------------------------
@@ -1367,7 +1367,10 @@ int build(const std::vector<Pattern> &pats, unsigned engine, std::vector<u8> &im
     wr8(r, rose::pureLiteral, 0);
     wr8(r, rose::runtimeImpl, rose::RUNTIME_SINGLE_OUTFIX);
     wr8(r, rose::canExhaust, 0);
-    wr32(r, rose::mode, MODE_BLOCK);
+    wr32(r, rose::mode, mode);   // stream mode: the engine's stream state sits at NfaInfo.stateOffset of the stream state
+    // hs_close_stream runs the engine's end-of-data check only when the header asks for it (report_eod_matches,
+    // src/runtime.c:676-692 -> soleOutfixEodExec); the block path looks at the engine's own flag instead (:273-278)
+    if (mode == MODE_STREAM && am.any_eod) wr8(r, rose::requiresEodCheck, 1);
     wr32(r, rose::ekeyCount, 0);
     wr32(r, rose::dkeyCount, (u32)dkeys.size());
     wr32(r, rose::dkeyLogSize, fatbit_size((u32)dkeys.size()));
@@ -1649,7 +1652,8 @@ extern "C" int hsb_compile_regex_multi_ex(const char *const *expressions, const 
         return HSB_LIT_COMPILER_ERROR;
     };
     if (!expressions || !elements) return fail("invalid parameter: no expressions");
-    if (mode != hsb::MODE_BLOCK) return fail("only HS_MODE_BLOCK databases are written");
+    if (mode != hsb::MODE_BLOCK && mode != hsb::MODE_STREAM) return fail("only HS_MODE_BLOCK and HS_MODE_STREAM databases are written");
+    if (mode == hsb::MODE_STREAM && engine == HSB_REGEX_ENGINE_LIMEX) return fail("HS_MODE_STREAM is written for DFA engines only");
     std::vector<hsb_nfadb::Pattern> pats;
     for (unsigned i = 0; i < elements; i++) {
         if (!expressions[i]) return fail("null expression");
@@ -1657,7 +1661,7 @@ extern "C" int hsb_compile_regex_multi_ex(const char *const *expressions, const 
     }
     std::vector<hsb::u8> image;
     std::string err;
-    if (hsb_nfadb::build(pats, engine, image, err) != HSB_LIT_SUCCESS) return fail(err);
+    if (hsb_nfadb::build(pats, engine, image, err, mode) != HSB_LIT_SUCCESS) return fail(err);
     void *mem = nullptr;
     if (posix_memalign(&mem, 64, image.size())) return fail("out of memory");
     std::memcpy(mem, image.data(), image.size());
