@@ -150,16 +150,18 @@ def test_single_dfa_streams_block_by_block(ref):
     import regen
     from test_streammode import dfa_stream_cases
     n = 0
-    for db, ex, fl, ids, bufs, text in dfa_stream_cases(77, eod=False):
+    for db, ex, fl, ids, bufs, text in dfa_stream_cases(77, eod=True):
         sc = gpu.alloc_scratch(db)
         st = gpu.Stream(db)
         got = []
         for b in bufs:
             assert st.scan(b, sc, collect(got)) == gpu.HS_SUCCESS
-        st.close()
+        assert st.close(sc, collect(got)) == gpu.HS_SUCCESS      # \z patterns report here, at the stream's length
         sc.close()
-        assert got == sorted(regen.brute_force(ex, fl, ids, text), key=lambda m: (m[1], m[0])), (ex, bufs)
-        assert oracle_port.scan_stream_blocks(db, bufs) == (0, got)
+        assert sorted(got) == sorted(regen.brute_force(ex, fl, ids, text)), (ex, bufs)
+        prv, pgot = oracle_port.scan_stream_blocks(db, bufs)     # callback order: by offset; within one offset the device
+        assert prv == 0 and sorted(pgot) == sorted(got)          # delivers by id, the reference by engine accept order
+        assert [t for _, t in got] == [t for _, t in pgot]
         n += len(got)
     assert n > 100
 
@@ -204,9 +206,17 @@ def test_many_single_dfa_streams_per_pass_and_refusals():
     for s in streams:
         s.close()
     sc.close()
-    # refused in stream mode: engines with end-of-data accepts, LimEx engines (the writer refuses those itself)
+    # end-of-data accepts come with hs_close_stream -- when it is given a handler -- and only if the stream ends there
     edb = litdb.compile_regex_multi([b"abc\\z", b"de"], [0, 0], [1, 2], engine=litdb.ENGINE_MCCLELLAN, mode=HS_MODE_STREAM)
-    with pytest.raises(gpu.HsGpuError):
-        gpu.alloc_scratch(edb)
+    esc = gpu.alloc_scratch(edb)
+    for blocks, want in (([b"xde ab", b"c"], [(2, 3), (1, 7)]), ([b"abc", b"de"], [(2, 5)]), ([b"abc"], [(1, 3)])):
+        st, seen = gpu.Stream(edb), []
+        for b in blocks:
+            assert st.scan(b, esc, collect(seen)) == 0
+        assert st.close(esc, collect(seen)) == 0 and seen == want, (blocks, seen)
+    st = gpu.Stream(edb)
+    assert st.scan(b"abc", esc) == 0 and st.close() == 0       # no handler: nothing to report, as in the reference
+    esc.close()
+    # refused in stream mode: LimEx engines (the writer refuses those itself)
     with pytest.raises(litdb.CompileError):
         litdb.compile_regex_multi([b"abc"], [0], [1], engine=litdb.ENGINE_LIMEX, mode=HS_MODE_STREAM)

@@ -2887,10 +2887,12 @@ hs_error_t hs_gpu_open_stream(const hs_database_t *db, unsigned int flags, hs_gp
 // device sees `count` independent buffers history + block, the host drops what ends inside a history (reported by an
 // earlier call), turns offsets into stream offsets, applies the stream's exhaustion keys and moves the stream on
 // (maintainHistoryBuffer :483-508).  A callback that returns non-zero terminates ITS stream only.
-hs_error_t hs_gpu_scan_streams(hs_gpu_stream_t *const *ids, const char *const *data, const unsigned int *length,
-                               unsigned int count, unsigned int flags, hs_gpu_scratch_t *scratch,
-                               match_event_handler onEvent, void *const *contexts) {
-    (void)flags;
+// `closing` (hs_gpu_close_stream of a single-DFA stream whose engine accepts at end of data): no data is scanned -- the
+// block is one dummy byte the kernel never looks at -- the entry state carries the close marker and the device raises the
+// end-of-data accepts of that state (soleOutfixEodExec, src/runtime.c:872-900 -> nfaCheckFinalState); the stream does not move.
+static hs_error_t scan_streams_impl(hs_gpu_stream_t *const *ids, const char *const *data, const unsigned int *length,
+                                    unsigned int count, hs_gpu_scratch_t *scratch, match_event_handler onEvent,
+                                    void *const *contexts, bool closing) {
     if (!ids || !data || !length || !scratch) return HS_INVALID;
     if (!count) return HS_SUCCESS;
     for (unsigned i = 0; i < count; i++)
@@ -2951,7 +2953,7 @@ hs_error_t hs_gpu_scan_streams(hs_gpu_stream_t *const *ids, const char *const *d
     if (engine) {
         if (!scratch->h_stream_state.resize(2 * (size_t)count)) return HS_NOMEM;
         for (unsigned i = 0; i < count; i++) {
-            scratch->h_stream_state[i] = len[i] ? ids[i]->engine_state : 0u;
+            scratch->h_stream_state[i] = len[i] ? (ids[i]->engine_state | (closing ? MCC_STREAM_CLOSE : 0u)) : 0u;
             scratch->h_stream_state[count + i] = 0;
         }
         scratch->stream_state_count = count;
@@ -2961,7 +2963,7 @@ hs_error_t hs_gpu_scan_streams(hs_gpu_stream_t *const *ids, const char *const *d
     if (engine && at[count]) {   // (an all-empty call never reached the device)
         if (cudaMemcpy(scratch->h_stream_state.data() + count, scratch->d_stream_state.p + count, (size_t)count * sizeof(u32),
                        cudaMemcpyDeviceToHost) != cudaSuccess) { cudaGetLastError(); return HS_UNKNOWN_ERROR; }
-        for (unsigned i = 0; i < count; i++)
+        for (unsigned i = 0; i < count && !closing; i++)
             if (len[i]) ids[i]->engine_state = scratch->h_stream_state[count + i];
     }
     const std::vector<std::pair<u32, u32>> &ekey_of = im->view.stream_ekey_of;
@@ -2972,7 +2974,7 @@ hs_error_t hs_gpu_scan_streams(hs_gpu_stream_t *const *ids, const char *const *d
     for (u64 k = 0; k < scratch->n_matches; k++) {
         hs_gpu_stream *st = ids[m[k].buffer];
         const u64 hlen = st->hist.size();
-        if (st->terminated || m[k].to <= hlen) continue;
+        if (st->terminated || (!closing && m[k].to <= hlen)) continue;   // (a closing pass reports at offset 0 of its data-less block)
         u32 ekey = ~0u;
         if (any_ekey) {
             auto it = std::lower_bound(ekey_of.begin(), ekey_of.end(), std::make_pair(m[k].id, 0u));
@@ -2990,7 +2992,7 @@ hs_error_t hs_gpu_scan_streams(hs_gpu_stream_t *const *ids, const char *const *d
         }
     }
     scratch->stats.matches = delivered;
-    for (unsigned i = 0; i < count; i++) {
+    for (unsigned i = 0; i < count && !closing; i++) {
         hs_gpu_stream *st = ids[i];
         if (st->terminated || !length[i]) continue;
         const u64 total = st->hist.size() + length[i];
@@ -3000,6 +3002,13 @@ hs_error_t hs_gpu_scan_streams(hs_gpu_stream_t *const *ids, const char *const *d
         st->offset += length[i];
     }
     return any_stop ? HS_SCAN_TERMINATED : HS_SUCCESS;
+}
+
+hs_error_t hs_gpu_scan_streams(hs_gpu_stream_t *const *ids, const char *const *data, const unsigned int *length,
+                               unsigned int count, unsigned int flags, hs_gpu_scratch_t *scratch,
+                               match_event_handler onEvent, void *const *contexts) {
+    (void)flags;
+    return scan_streams_impl(ids, data, length, count, scratch, onEvent, contexts, false);
 }
 
 // hs_scan_stream (src/runtime.c:980-996)
@@ -3014,14 +3023,26 @@ hs_error_t hs_gpu_scan_stream(hs_gpu_stream_t *id, const char *data, unsigned in
     return hs_gpu_scan_streams(ids, d, l, 1, flags, scratch, onEvent, c);
 }
 
-// hs_close_stream (src/runtime.c:998-1033): a pure-literal database has no end-of-data work (requiresEodCheck is 0), so
-// nothing is reported; scratch / onEvent may be NULL as in the reference.
+// hs_close_stream (src/runtime.c:998-1033, report_eod_matches :636-700).  A pure-literal database has no end-of-data work
+// (requiresEodCheck is 0).  A single-DFA database whose header asks for the check gets it when a handler is given
+// (as in the reference, scratch and onEvent may be NULL: nothing is reported then): one device pass that raises the
+// end-of-data accepts of the state the stream stands in, at the stream's length.
 hs_error_t hs_gpu_close_stream(hs_gpu_stream_t *id, hs_gpu_scratch_t *scratch, match_event_handler onEvent, void *context) {
-    (void)scratch; (void)onEvent; (void)context;
     if (!id || id->magic != 0x5354524d) return HS_INVALID;
+    hs_error_t rv = HS_SUCCESS;
+    const u8 *p = reinterpret_cast<const u8 *>(id->db);
+    const bool wants_eod = rd8(p + rd32(p, db::bytecode), rose::requiresEodCheck) != 0;
+    if (wants_eod && onEvent && scratch && id->started && id->engine_state && !id->terminated) {
+        hs_gpu_stream_t *ids[1] = {id};
+        const char dummy = 0, *d[1] = {&dummy};
+        unsigned int l[1] = {1};
+        void *c[1] = {context};
+        rv = scan_streams_impl(ids, d, l, 1, scratch, onEvent, c, true);
+        if (rv == HS_SCRATCH_IN_USE || rv == HS_INVALID) return rv;   // the stream stays open
+    }
     id->magic = 0;
     delete id;
-    return HS_SUCCESS;
+    return rv;
 }
 
 // hs_reset_stream (src/runtime.c:1035-1060)

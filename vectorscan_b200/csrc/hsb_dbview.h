@@ -597,7 +597,8 @@ inline int parse_database(const void *db, DbView &d, std::string &why) {
         const int orv = parse_single_outfix(d, why);
         if (orv != E_SUCCESS || !d.streaming) return orv;
         if (d.kind != ENG_MCCLELLAN && d.kind != ENG_SHENG) { why = "stream mode: only DFA engines carry their state across blocks on the device path"; return E_ARCH; }
-        if ((d.nfa_flags & nfa::ACCEPTS_EOD) || rd8(r, rose::requiresEodCheck)) { why = "stream mode: engines with end-of-data accepts are not supported yet"; return E_ARCH; }
+        // (end-of-data accepts are raised by hs_gpu_close_stream: needs requiresEodCheck, as the reference's close does)
+        if ((d.nfa_flags & nfa::ACCEPTS_EOD) && !rd8(r, rose::requiresEodCheck)) { why = "stream mode: engine accepts at end of data but the header does not ask for the check"; return E_INVALID; }
         return E_SUCCESS;
     }
     if (impl == rose::RUNTIME_FULL_ROSE) {

@@ -42,6 +42,7 @@ struct DevMcc {
 // in shared memory and a work item is a (buffer, engine) pair, so a launch has `n` times the items -- with one buffer
 // per thread at most (a 64 MiB batch of ~800-byte payloads has fewer buffers than the grid has threads) that is what
 // fills the machine.  Only engines the branch-free loop serves (table in shared memory, no Sherman states) are packed.
+constexpr u32 MCC_STREAM_CLOSE = 0x80000000u;   // stream mode, entry state: "no data, raise the end-of-data accepts of this state"
 constexpr int MCC_PACK_MAX = 4;
 struct DevMccPack {
     DevMcc m[MCC_PACK_MAX];
@@ -143,6 +144,13 @@ __global__ void __launch_bounds__(MCC_THREADS, 1) k_mcclellan(const DevDb db_, c
                 const u32 b = cp_.order ? cp_.order[nb] : (u32)nb;
                 o0 = cp_.off[b];
                 l = (u32)(cp_.off[b + 1] - o0);
+                if (cp_.init_state && (cp_.init_state[b] & MCC_STREAM_CLOSE)) {
+                    // the stream is being closed: nfaCheckFinalState of the state it stands in, at its end (offset 0 of
+                    // this data-less block)
+                    const u32 cs = cp_.init_state[b] & ~MCC_STREAM_CLOSE;
+                    if (cs && m.accepts_eod) mcc_accept(evq, db_.bc, m, cs, b, 0, true);
+                    continue;
+                }
                 if (l && passes_gates(db_, l)) break;
             }
             if (nb >= count) break;

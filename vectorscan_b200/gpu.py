@@ -266,10 +266,14 @@ class Stream:
             raise HsGpuError(rv, "hs_gpu_copy_stream")
         return Stream(ptr=out)
 
-    def close(self):
+    def close(self, scratch=None, on_event=None, context=None):
+        """hs_close_stream: with a scratch and a handler the end-of-data matches are reported; returns the hs_error_t."""
+        rv = HS_SUCCESS
         if self.ptr:
-            lib().hs_gpu_close_stream(self.ptr, None, C.cast(None, MATCH_CB), None)
+            cb = MATCH_CB(on_event) if on_event else C.cast(None, MATCH_CB)
+            rv = lib().hs_gpu_close_stream(self.ptr, scratch.ptr if scratch is not None else None, cb, context)
             self.ptr = C.c_void_p()
+        return rv
 
     def __del__(self):
         try:
