@@ -115,7 +115,8 @@ hs_error_t hs_gpu_scan_vector_ex(const hs_database_t *db, const char *const *dat
                                  const hs_gpu_match_t **matches, uint64_t *n_matches);
 
 /* ---- stream mode: HS_MODE_STREAM pure-literal databases, and single-outfix databases holding ONE DFA engine ----------
- * (McClellan, McSheng, Sheng; not LimEx; no end-of-data accepts: otherwise HS_ARCH_ERROR at hs_gpu_alloc_scratch)
+ * (McClellan, McSheng, Sheng; not LimEx: HS_ARCH_ERROR at hs_gpu_alloc_scratch; their end-of-data matches are reported by
+ * hs_gpu_close_stream when it is given a scratch and a handler, as by hs_close_stream)
  * hs_open_stream / hs_scan_stream / hs_close_stream / hs_reset_stream / hs_copy_stream  (src/hs_runtime.h:148-293,
  * src/runtime.c:543-580, 980-996, 998-1033, 1035-1060, 711-737): same parameter lists and error codes.  The stream object
  * lives on the host: its offset, its last historyRequired bytes, the exhaustion keys of the single-match reports it has
