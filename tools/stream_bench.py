@@ -4,7 +4,11 @@ from host packets (wall clock; the library gathers history + block per flow, cop
 reference's own hs_scan_stream on one host core over a bounded sample of the same flows beside it, which is also the
 parity check (same callbacks per flow).  One JSON line.
 
-usage: python tools/stream_bench.py [MiB=64] [flows=4096]"""
+usage: python tools/stream_bench.py [MiB=64] [flows=4096] [literal|dfa]
+
+dfa: the c3d set (6 Snort-like regexes as one McClellan16 DFA, bench.py --config c3d) in stream mode over the C3 HTTP
+payloads, each payload cut into 256-byte blocks dealt round by round; the engine's state id per stream crosses the
+blocks."""
 import ctypes as C
 import json
 import os
@@ -24,11 +28,31 @@ def main():
     mib = int(sys.argv[1]) if len(sys.argv) > 1 else 64
     flows = int(sys.argv[2]) if len(sys.argv) > 2 else 4096
     nbytes = mib << 20
-    lits, flags, ids = workloads.c2_patterns()
-    sdb = litdb.compile_lit_multi(lits, flags, ids, mode=litdb.HS_MODE_STREAM)
-    flat, off = workloads.c2_batch(nbytes, lits)
+    kind = sys.argv[3] if len(sys.argv) > 3 else "literal"
+    if kind == "dfa":
+        ex, fl, ids = workloads.c3_patterns(max_patterns=6, templates=(2, 4, 5))
+        sdb = litdb.compile_regex_multi(ex, fl, ids, engine=litdb.ENGINE_MCCLELLAN, mode=litdb.HS_MODE_STREAM)
+        pflat, poff = workloads.c3_corpus(nbytes)
+        # flow k = the k-th payload of at least 1 KiB; round r = its bytes [256 r, 256 r + 256)
+        plen = np.diff(poff).astype(np.int64)
+        pick = np.nonzero(plen >= 1024)[0][:flows]      # payloads of at least 1 KiB: 4 rounds of 256 bytes
+        assert len(pick) == flows, "corpus too small for that many flows"
+        rounds = 4
+        starts = poff[:-1][pick].astype(np.int64)
+        off = np.zeros(rounds * flows + 1, dtype=np.uint64)
+        flat = np.empty(rounds * flows * 256, dtype=np.uint8)
+        for r in range(rounds):
+            idx = (starts + 256 * r)[:, None] + np.arange(256)[None, :]
+            flat[r * flows * 256:(r + 1) * flows * 256] = pflat[idx].reshape(-1)
+        off[:] = np.arange(rounds * flows + 1, dtype=np.uint64) * 256
+        what = f"c3d set (6 regexes, one McClellan16 DFA) in HS_MODE_STREAM, {flows} HTTP payloads as flows, 256-byte blocks"
+    else:
+        lits, flags, ids = workloads.c2_patterns()
+        sdb = litdb.compile_lit_multi(lits, flags, ids, mode=litdb.HS_MODE_STREAM)
+        flat, off = workloads.c2_batch(nbytes, lits)
+        rounds = (len(off) - 1) // flows
+        what = f"C2 literal set (10000 literals) in HS_MODE_STREAM, {mib} MiB of 1500-byte packets dealt to {flows} flows"
     count = len(off) - 1
-    rounds = count // flows
     L = gpu.lib()
     sc = gpu.alloc_scratch(sdb)
     streams = [gpu.Stream(sdb) for _ in range(flows)]
@@ -93,11 +117,10 @@ def main():
         ref_hits[k] = out
     parity = all(per_flow.get(k, []) == ref_hits[k] for k in range(sample_flows))
     print(json.dumps({
-        "workload": f"C2 literal set (10000 literals) in HS_MODE_STREAM, {mib} MiB of 1500-byte packets dealt to {flows} flows, "
-                    f"{rounds} rounds of one packet per flow",
+        "workload": what + f", {rounds} rounds of one block per flow",
         "e2e_gbs": round(scanned / secs / 1e9, 2), "ms_per_round": round(1e3 * secs / rounds, 3), "matches": hits[0],
         "ref_hs_scan_stream_1core_gbs": round(cpu_bytes / cpu_s / 1e9, 3), "ref_isa": R.isa,
-        "ref_sample": f"{sample_flows} flows x {rounds} packets", "parity_on_sample": bool(parity),
+        "ref_sample": f"{sample_flows} flows x {rounds} blocks", "parity_on_sample": bool(parity),
         "note": "timed passes run with a NULL match handler on both sides; parity from a recording pass"}))
 
 
