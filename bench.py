@@ -65,7 +65,7 @@ def make_workload(config, rank, nbytes, npat=6):
         # prefers for outfixes; 6 patterns keep the 16-bit table in shared memory, 8 push it out to L2
         ex, fl, ids = W.c3_patterns(max_patterns=npat, templates=(2, 4, 5))
         batches = [W.c3_corpus(nbytes, seed=20260103 + 100 * rank + r) for r in range(ROT)]
-        db = litdb.compile_regex_multi(ex, fl, ids, engine=litdb.ENGINE_MCCLELLAN)
+        db = litdb.compile_regex_multi(ex, fl, ids, engine=int(os.environ.get("HS_BENCH_C3D_ENGINE", litdb.ENGINE_MCCLELLAN)))
         name = (f"c3d: {len(ex)} Snort-like regexes (C3 templates without counted gaps) as one McClellan"
                 f"{8 if db.outfix_engine_type() == 6 else 16} DFA (single-outfix database) over a "
                 f"{nbytes >> 20} MiB batch of 200-1400-byte synthetic HTTP payloads per step")

@@ -110,3 +110,24 @@ def test_long_buffer_anchored_only_and_table_outside_shared_memory(ref):
         bufs3.append(bytes(t))
     got3 = gpu_batch(db3, bufs3)
     assert got3 == ref_batch(ref, db3, bufs3) and len(got3) > 10
+
+
+def test_sherman_states_expanded_and_exact_forms_agree(ref, monkeypatch):
+    """16-bit engines with Sherman states: by default the device gives every Sherman state its full row at upload and runs
+    the branch-free loop; HS_GPU_SHERMAN_EXACT=1 keeps the reference's compressed form and steps it with doSherman16 per
+    byte.  Same matches both ways, equal to the reference runtime's."""
+    rng = random.Random(41)
+    ex = [b"passwd\\s+[A-Za-z0-9_]{4,9}=", b"(login|admin)[^&]*&id=", b"User-Agent: [^\\r\\n]{8}", b"select.{1,12}from", b"^GET /[^ ]*\\.php"]
+    fl, ids = [1, 0, 0, 1, 0], [3, 1, 4, 1, 5]
+    db = litdb.compile_regex_multi(ex, fl, ids, engine=litdb.ENGINE_MCCLELLAN_SHERMAN)
+    bc = db.bytecode()
+    info = int.from_bytes(bc[236:240], "little")
+    nfa = int.from_bytes(bc[info:info + 4], "little")
+    m = nfa + 64
+    assert int.from_bytes(bc[m + 28:m + 30], "little") < int.from_bytes(bc[m:m + 2], "little")    # sherman_limit < state_count
+    bufs = [b"GET /a/b.php x PASSWD  user_1= login=1&id= admin&id= select a,b from User-Agent: abcdefghij", b""] + \
+           [regen.random_text(rng, ex, rng.randint(1, 900)) for _ in range(150)]
+    want = ref_batch(ref, db, bufs)
+    assert gpu_batch(db, bufs) == want and len(want) >= 6
+    monkeypatch.setenv("HS_GPU_SHERMAN_EXACT", "1")
+    assert gpu_batch(db, bufs) == want

@@ -1389,7 +1389,7 @@ hs_error_t build_engine_image(hs_gpu_scratch *s, DbImage *im) {
         L.o_squash = t.o_squash; L.o_meta = t.o_meta; L.o_masks = t.o_masks; L.o_base = t.o_base;
         L.total_words = t.total_words; L.accept_abs = t.accept_abs; L.accept_eod_abs = t.accept_eod_abs;
         L.nfa_flags = t.nfa_flags;
-    } else if (v.kind == ENG_SHENG || (v.kind == ENG_MCCLELLAN && (v.mcc.sheng_end || v.mcc.has_wide))) {
+    } else if (v.kind == ENG_SHENG || (v.kind == ENG_MCCLELLAN && im->mcc.tab_abs)) {
         // im->mcc was filled by build_sheng_tables / build_mcsheng_tables / build_wide_tables with the image
     } else if (v.kind == ENG_MCCLELLAN) {
         // the engine is stepped straight from the uploaded bytecode (mcclellan.cuh copies the table to shared memory)
@@ -1417,7 +1417,7 @@ hs_error_t build_dfa_packs(hs_gpu_scratch *s, DbImage *im) {
     auto packable = [&](size_t q) {
         const DbImage *e = im->subs[q];
         const DbView::Mcc &M = e->view.mcc;
-        return e->view.kind == ENG_MCCLELLAN && !M.sheng_end && !M.has_wide && !e->mcc.has_sherman && !e->mcc.accepts_eod && M.states <= mcclellan::STATE_MASK;
+        return e->view.kind == ENG_MCCLELLAN && !M.sheng_end && !M.has_wide && !(M.wide16 && M.sherman_limit < M.states) && !e->mcc.has_sherman && !e->mcc.accepts_eod && M.states <= mcclellan::STATE_MASK;
     };
     auto joint = [&](const std::vector<size_t> &members, std::vector<u32> &cls_of) {  // -> number of joint classes
         std::map<std::vector<u8>, u32> seen;
@@ -1534,10 +1534,18 @@ hs_error_t upload_database(hs_gpu_scratch *s, const hs_database_t *db, DbImage *
     // (Sheng outfixes of a multi-engine database get their tables one behind the other in the same area.)
     std::vector<u8> derived;
     const u32 derived_at = (u32)round_up(v.bc_len, 256) + 256;
-    // McSheng and McClellan with wide states: their complete tables are made here too
-    auto hybrid = [](const DbView &e) { return e.kind == ENG_MCCLELLAN && (e.mcc.sheng_end != 0 || e.mcc.has_wide); };
+    // McSheng and McClellan with wide states: their complete tables are made here too.  So are those of plain 16-bit
+    // engines with Sherman states when the complete table stays small (Sherman rows are a size optimisation for a CPU
+    // cache; here a full row per state buys the branch-free loop): HS_GPU_SHERMAN_EXACT=1 keeps the reference's form,
+    // stepped by the exact loop (doSherman16 per byte).
+    const bool expand_sherman = !getenv("HS_GPU_SHERMAN_EXACT");
+    auto hybrid = [expand_sherman](const DbView &e) {
+        if (e.kind != ENG_MCCLELLAN) return false;
+        if (e.mcc.sheng_end != 0 || e.mcc.has_wide) return true;
+        return expand_sherman && e.mcc.wide16 && e.mcc.sherman_limit < e.mcc.states && ((size_t)e.mcc.states << e.mcc.as) * 2 <= (4u << 20);
+    };
     auto build_hybrid = [](const DbView &e, u32 at, std::vector<u8> &out, DevMcc &D) {
-        if (e.mcc.has_wide) build_wide_tables(e, at, out, D); else build_mcsheng_tables(e, at, out, D);
+        if (e.mcc.sheng_end) build_mcsheng_tables(e, at, out, D); else build_wide_tables(e, at, out, D);
     };
     if (v.kind == ENG_SHENG) build_sheng_tables(v, derived_at, derived, im->mcc);
     if (hybrid(v)) build_hybrid(v, derived_at, derived, im->mcc);

@@ -219,8 +219,10 @@ inline int parse_mcclellan(DbView &d, std::string &why) {
         }
         n_aux = M.wide_limit;
         ref_limit = M.wide_limit + M.wide_number;
-        for (u32 c = 0; c < 256; c++) M.n_alpha = std::max<u32>(M.n_alpha, rd8(r, M.m_off + (u32)mc::remap + c) + 1u);
+    } else {
+        M.wide_limit = M.states;   // (no wide states: every id below `states` has its aux record)
     }
+    for (u32 c = 0; c < 256; c++) M.n_alpha = std::max<u32>(M.n_alpha, rd8(r, M.remap_off + c) + 1u);
     if (M.wide16 && M.states - 1 > mc::STATE_MASK) { why = "McClellan state count out of range"; return E_INVALID; }
     if (!M.wide16 && (M.states > 256 || M.accept_limit_8 > M.states)) { why = "McClellan8 limits out of range"; return E_INVALID; }
     if (hybrid && (M.sheng_end < 2 || M.sheng_end > (hybrid64 ? ms::MAX_SHENG64_STATES : ms::MAX_SHENG_STATES) + 1 || M.sheng_end > M.sherman_limit)) { why = "McSheng region out of range"; return E_INVALID; }
