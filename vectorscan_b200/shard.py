@@ -54,3 +54,22 @@ def merge_shards(per_rank_matches, bounds):
         base = int(bounds[r])
         out.extend((int(b) + base, int(i), int(t)) for b, i, t in ms)
     return out
+
+
+# ---- stream mode: flows, not buffers, are what shards ------------------------------------------------------------------
+def stream_owner(flow_ids, world):
+    """Rank that owns each flow.  A stream's blocks must all reach the same rank (its history / engine state lives with the
+    hs_gpu_stream object there), so the split is by flow id, not by position in the batch: a multiplicative hash of the id,
+    which spreads consecutive ids and skewed id spaces evenly.  flow_ids: integer array -> int64 array of ranks."""
+    import numpy as np
+    f = np.asarray(flow_ids, dtype=np.uint64)
+    h = (f * np.uint64(0x9E3779B97F4A7C15)) >> np.uint64(33)
+    return (h % np.uint64(world)).astype(np.int64)
+
+
+def take_stream_round(flow_ids, blocks, world, rank):
+    """The part of one round (flow_ids[k] sends blocks[k]) that belongs to `rank`: (indices into the round, flow ids, blocks),
+    in the round's order."""
+    own = stream_owner(flow_ids, world)
+    idx = [k for k in range(len(blocks)) if own[k] == rank]
+    return idx, [flow_ids[k] for k in idx], [blocks[k] for k in idx]
