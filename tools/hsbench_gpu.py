@@ -10,8 +10,10 @@
               as far as the stand-in compiler's dialect goes (csrc/nfadb_writer.cpp).
 -c CORPUS     hsbench's SQLite corpus (table chunk(id, stream_id, data), tools/hsbench/data_corpus.cpp:86-87; every row is
               one block) or any other file, cut into --block-size byte blocks.
--n NUMBER     repeat the scan NUMBER times (default 20, main.cpp:185); -N block mode (the only mode, accepted for
-              compatibility); -T is accepted and ignored (one GPU stream replaces the CPU thread list).
+-n NUMBER     repeat the scan NUMBER times (default 20, main.cpp:185); -N block mode (the default here); -V vectored mode
+              (main.cpp:673-700: the blocks of one stream_id are ONE hs_scan_vector call; literal pattern files only, the
+              database is compiled HS_MODE_VECTORED; with a plain file the whole file is one stream); -T is accepted and
+              ignored (one GPU stream replaces the CPU thread list).
 The corpus is made resident once (hs_gpu_corpus_create) and each repeat is one hs_gpu_scan_corpus -- what hsbench's
 per-thread loop over blocks (main.cpp:486-512) is to the CPU runtime.  The summary lines are hsbench's (main.cpp:769-799)."""
 import argparse
@@ -52,23 +54,25 @@ def read_patterns(path):
     return lits, regs
 
 
-def read_corpus(path, block_size):
+def read_corpus(path, block_size, with_streams=False):
+    """-> blocks, or (with_streams) [(stream_id, block)] in id order."""
     with open(path, "rb") as f:
         head = f.read(16)
     if head.startswith(b"SQLite format 3"):
         con = sqlite3.connect(f"file:{path}?mode=ro", uri=True)
-        blocks = [bytes(r[2]) for r in con.execute("SELECT id, stream_id, data FROM chunk ORDER BY id")]
+        rows = [(int(r[1]), bytes(r[2])) for r in con.execute("SELECT id, stream_id, data FROM chunk ORDER BY id")]
         con.close()
-        return blocks
-    data = open(path, "rb").read()
-    return [data[i:i + block_size] for i in range(0, len(data), block_size)]
+    else:
+        data = open(path, "rb").read()
+        rows = [(0, data[i:i + block_size]) for i in range(0, len(data), block_size)]
+    return rows if with_streams else [b for _, b in rows]
 
 
-def write_corpus(path, blocks):
+def write_corpus(path, blocks, stream_ids=None):
     """The inverse of read_corpus for the SQLite shape (what tools/hsbench/scripts/*.py produce)."""
     con = sqlite3.connect(path)
     con.execute("CREATE TABLE chunk (id integer primary key, stream_id integer not null, data blob)")
-    con.executemany("INSERT INTO chunk VALUES (?, ?, ?)", [(i, i, b) for i, b in enumerate(blocks)])
+    con.executemany("INSERT INTO chunk VALUES (?, ?, ?)", [(i, stream_ids[i] if stream_ids else i, b) for i, b in enumerate(blocks)])
     con.commit()
     con.close()
 
@@ -79,6 +83,7 @@ def main():
     ap.add_argument("-c", dest="corpus", required=True)
     ap.add_argument("-n", dest="repeats", type=int, default=20)
     ap.add_argument("-N", dest="block", action="store_true")
+    ap.add_argument("-V", dest="vectored", action="store_true")
     ap.add_argument("-T", dest="threads", default=None)
     ap.add_argument("--block-size", type=int, default=1500)
     ap.add_argument("--echo-matches", action="store_true")
@@ -88,6 +93,8 @@ def main():
 
     lits, regs = read_patterns(args.patterns)
     t0 = time.perf_counter()
+    if args.vectored:
+        return vectored_main(args, lits, regs, t0)
     if lits:
         db = litdb.compile_lit_multi([e for _, e, _ in lits], [f & ~litdb.HS_FLAG_DOTALL for _, _, f in lits], [p for p, _, _ in lits],
                                      regexes=[e for _, e, _ in regs] or None, regex_flags=[f for _, _, f in regs],
@@ -127,6 +134,49 @@ def main():
     print(f"Overall block rate:        {len(blocks) * args.repeats / secs:,.2f} blocks/sec")
     print(f"Mean throughput (overall): {nbytes * args.repeats * 8 / secs / 1e6:,.2f} Mbit/sec")
     print(f"Device throughput:         {nbytes * args.repeats * 8 / (dev_ms * 1e-3) / 1e6:,.2f} Mbit/sec")
+
+
+def vectored_main(args, lits, regs, t0):
+    if regs or not lits:
+        raise SystemExit("-V: vectored mode is served for literal pattern files only")
+    db = litdb.compile_lit_multi([e for _, e, _ in lits], [f & ~litdb.HS_FLAG_DOTALL for _, _, f in lits], [p for p, _, _ in lits],
+                                 mode=litdb.HS_MODE_VECTORED)
+    print(f"Signatures:        {args.patterns}")
+    print(f"Compile:           {len(lits)} literals, {db.size} bytes, {time.perf_counter() - t0:.3f} seconds")
+    print("Scan mode:         vectored (one hs_scan_vector per stream, one GPU stream)")
+    rows = read_corpus(args.corpus, args.block_size, with_streams=True)
+    streams = {}
+    for sid, b in rows:
+        streams.setdefault(sid, []).append(b)
+    sc = gpu.alloc_scratch(db)
+    if args.frontend:
+        sc.set_option("frontend", args.frontend)
+    corpora = {}
+    for sid, blocks in streams.items():
+        offs = np.concatenate([[0], np.cumsum([len(b) for b in blocks])]).astype(np.uint64)
+        if offs[-1]:
+            corpora[sid] = gpu.Corpus(np.frombuffer(b"".join(blocks), dtype=np.uint8), offs)
+    for c in corpora.values():
+        gpu.scan_corpus(db, c, sc)        # warm-up
+    dev_ms, matches = 0.0, 0
+    t0 = time.perf_counter()
+    for r in range(args.repeats):
+        matches = 0
+        for sid, c in corpora.items():
+            matches += gpu.scan_corpus(db, c, sc)
+            st = sc.stats()
+            dev_ms += st["scan_ms"] + st["sort_ms"]
+            if args.echo_matches and r == 0:
+                for rec in gpu.fetch_matches(sc):
+                    print(f"Match @ {sid}:{int(rec['to'])} for {int(rec['id'])}")
+    secs = time.perf_counter() - t0
+    nbytes = sum(len(b) for _, b in rows)
+    print(f"Time spent scanning:       {secs:,.3f} seconds ({dev_ms / 1e3:,.3f} on the device)")
+    print(f"Corpus size:               {nbytes:,} bytes ({len(rows):,} blocks in {len(streams):,} streams)")
+    print(f"Matches per iteration:     {matches:,} ({matches * 1024.0 / max(1, nbytes):,.3f} matches/kilobyte)")
+    print(f"Overall block rate:        {len(rows) * args.repeats / secs:,.2f} blocks/sec")
+    print(f"Mean throughput (overall): {nbytes * args.repeats * 8 / secs / 1e6:,.2f} Mbit/sec")
+    print(f"Device throughput:         {nbytes * args.repeats * 8 / max(dev_ms, 1e-6) / 1e3:,.2f} Mbit/sec")
 
 
 if __name__ == "__main__":
